@@ -1,0 +1,109 @@
+/*
+ * b200_engine.h — C ABI of the B200-native GGUF inference engine (libb200engine.so).
+ *
+ * This is the drop-in boundary for the reference's generation path.  The reference worker
+ * (/root/reference/nats_llm_studio.go) reaches its backend through LMStudioClient (HTTP + `lms`
+ * CLI); a maintainer replaces that client with a cgo binding of the functions below (see
+ * INTEGRATION.md).  Conventions: plain pointers and sizes only; return 0 = ok, <0 = error
+ * (b200_last_error() gives the thread-local message); no C++ exceptions cross the boundary; the
+ * caller owns every input buffer; the engine owns all device memory; entry points are
+ * thread-safe; nothing calls back into the host language (poll-based), so cgo never re-enters.
+ */
+#ifndef B200_ENGINE_H
+#define B200_ENGINE_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200_model b200_model;
+
+enum { B200_OK = 0, B200_ERR_INVALID = -1, B200_ERR_CUDA = -2, B200_ERR_NOMEM = -3, B200_ERR_UNSUPPORTED = -4,
+       B200_ERR_NOT_FOUND = -5, B200_ERR_MORE = -6, B200_ERR_STATE = -7 };
+
+typedef struct b200_config {
+    int device;          /* CUDA device ordinal */
+    int max_ctx;         /* KV positions reserved per sequence (0 = 4096) */
+    int max_seqs;        /* concurrent sequences the KV pool is sized for (0 = 1) */
+    uint32_t flags;      /* reserved */
+} b200_config;
+
+/* ggml type ids used in the kernel-level entry points (gguf/constants.py GGMLQuantizationType) */
+enum { B200_F32 = 0, B200_F16 = 1, B200_Q8_0 = 8, B200_Q4_K = 12, B200_Q5_K = 13, B200_Q6_K = 14 };
+
+typedef struct b200_sampling {
+    float temperature;   /* <= 0: greedy */
+    int top_k;           /* 0: off */
+    float top_p;         /* >= 1: off */
+    uint64_t seed;
+    int max_tokens;
+    int stop_token;      /* -1: none (EOS from the GGUF is always honoured unless ignore_eos) */
+    int ignore_eos;
+} b200_sampling;
+
+enum { B200_EV_TOKEN = 1, B200_EV_FINISH = 2, B200_EV_ERROR = 3 };
+enum { B200_FINISH_STOP = 1, B200_FINISH_LENGTH = 2, B200_FINISH_CANCELLED = 3 };
+typedef struct b200_event {
+    uint64_t req_id; int kind; int token; int finish_reason;
+    int n_prompt; int n_generated; float ttft_ms; float decode_ms;
+} b200_event;
+
+/* ---- lifecycle.  Replaces NewLMStudioClient (nats_llm_studio.go:34-44): the backend is in-process. */
+int b200_init(const b200_config* cfg);
+int b200_shutdown(void);
+const char* b200_last_error(void);
+/* Pinned host staging for uploads (JetStream Object Store chunks land here; README.md:250-318). */
+void* b200_pinned_alloc(size_t n);
+void b200_pinned_free(void* p);
+
+/* ---- model registry.  Replaces PullModel (`lms get`, nats_llm_studio.go:46-59), ListModels
+ * (GET /api/v0/models, :136-156) and DeleteModel (`lms unload` + RemoveAll, :87-133): models are
+ * HBM-resident; pull streams .gguf bytes host -> HBM, delete frees HBM. */
+int b200_model_open(const char* id, const void* gguf_head, size_t n, b200_model** out);  /* B200_ERR_MORE: pass a longer prefix */
+int b200_model_upload(b200_model* m, uint64_t file_off, const void* bytes, size_t n);
+int b200_model_commit(b200_model* m);                    /* repack on GPU, build the decode schedule */
+int b200_model_close(b200_model* m);                     /* frees HBM, removes from registry */
+int b200_model_load_file(const char* id, const char* path, b200_model** out);   /* open+upload+commit */
+int b200_model_find(const char* id, b200_model** out);
+int b200_model_list(char* json_out, size_t cap, size_t* need);   /* {"data":[{id,publisher,...}],"object":"list"} */
+int b200_model_info(const b200_model* m, char* json_out, size_t cap, size_t* need);
+
+/* ---- generation.  Replaces LMStudioClient.Chat (POST /api/v0/chat/completions, :158-179). */
+int b200_submit(b200_model* m, const int32_t* toks, int n, const b200_sampling* s, uint64_t req_id);
+int b200_poll(b200_event* out, int max, int timeout_ms);          /* returns number of events */
+int b200_cancel(uint64_t req_id);
+/* Synchronous single-sequence forms (what submit/poll drive underneath; used by tests and bench). */
+int b200_model_generate(b200_model* m, const int32_t* prompt, int n_prompt, int n_gen, const b200_sampling* s,
+                        int32_t* out_tokens, int* n_out, float* ttft_ms, float* decode_ms);
+int b200_model_eval(b200_model* m, const int32_t* toks, int n, float* logits_all /* [n][n_vocab] or NULL */,
+                    float* logits_last /* [n_vocab] or NULL */);
+int b200_model_n_vocab(const b200_model* m);
+/* tokenizer of the loaded GGUF (byte-level for the synthetic vocab) */
+int b200_tokenize(const b200_model* m, const char* text, size_t n, int32_t* out, int cap, int* n_out);
+int b200_detokenize(const b200_model* m, const int32_t* toks, int n, char* out, size_t cap, size_t* need);
+
+/* ---- subject handlers: same payloads in, same {ok,error,data} envelope bytes out as
+ * Server.onListModels / OnPullModel / OnDeleteModel / OnChatModel (nats_llm_studio.go:228-364).
+ * subject is "lmstudio.list_models" | "lmstudio.pull_model" | "lmstudio.delete_model" |
+ * "lmstudio.chat_model".  The reply is what msg.Respond would send. */
+int b200_handle(const char* subject, const void* payload, size_t n, char* reply, size_t cap, size_t* need);
+/* where pull_model looks for "<identifier>.gguf" / "<identifier>" files (LMSTUDIO_MODELS_DIR) */
+int b200_set_models_dir(const char* dir);
+
+/* ---- kernel-level entry points (parity tests, roofline bench).  Host buffers in and out. */
+/* repack raw ggml blocks on the GPU and dequantise them back: out[n_rows*K] fp32, bit-exact */
+int b200_dequantize(int type, const void* raw_blocks, int64_t n_rows, int K, float* out);
+/* y[N] = W[N x K] . x[K] through the streaming GEMV; iters>1 repeats the launch, ms = mean per iter */
+int b200_gemv(int type, const void* raw_blocks, int64_t N, int K, const float* x, float* y, int iters, float* ms);
+/* decode-step timing: n_steps greedy tokens from the current position of a primed context */
+int b200_bench_decode(b200_model* m, int ctx_len, int n_steps, int warmup, float* ms_per_token, double* bytes_per_token);
+/* number of kernels this library has launched so far (bench.py reports the delta as gpu_launches) */
+uint64_t b200_launch_count(void);
+/* layout self-test (host only, no GPU): src_byte/dst_byte are inverse bijections for every type */
+int b200_layout_selftest(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,7 @@
+"""B200-native GGUF inference engine behind the nats-llm-studio NATS subjects.
+
+The product is `libb200engine.so` (CUDA kernels for sm_100a + C ABI, sources in `csrc/`, header in
+`include/b200_engine.h`).  This package is the thin ctypes binding used by tests, smoke and bench;
+there is no Python or CPU compute path: every call fails loudly if the library or a GPU is missing.
+"""
+from .engine import Engine, EngineError, Model, lib, GGML_TYPES  # noqa: F401

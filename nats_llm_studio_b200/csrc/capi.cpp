@@ -1,0 +1,168 @@
+// capi.cpp — extern "C" surface declared in include/b200_engine.h.
+#include <atomic>
+#include <chrono>
+#include <cstring>
+
+#include "engine.hpp"
+
+namespace b200 {
+int load_file_into(const std::string& id, const std::string& path, std::shared_ptr<Model>& out, std::string& log);
+
+// ---- request queue behind b200_submit / b200_poll (one scheduler thread owns the engine)
+struct Request { std::shared_ptr<Model> m; std::vector<int32_t> toks; b200_sampling s; uint64_t id; std::atomic<bool> cancelled{false}; };
+struct Scheduler {
+    std::mutex mu; std::condition_variable cv_req, cv_ev;
+    std::deque<std::shared_ptr<Request>> q; std::deque<b200_event> ev;
+    std::map<uint64_t, std::shared_ptr<Request>> live;
+    std::thread th; bool stop = false, started = false;
+    void start() { if (started) return; started = true; th = std::thread([this] { loop(); }); }
+    void loop() {
+        for (;;) {
+            std::shared_ptr<Request> r;
+            { std::unique_lock<std::mutex> lk(mu); cv_req.wait(lk, [&] { return stop || !q.empty(); }); if (stop) return; r = q.front(); q.pop_front(); }
+            b200_event fin{}; fin.req_id = r->id; fin.kind = B200_EV_FINISH; fin.n_prompt = (int)r->toks.size();
+            std::vector<b200_event> out;
+            if (r->cancelled) fin.finish_reason = B200_FINISH_CANCELLED;
+            else {
+                int n_gen = r->s.max_tokens > 0 ? r->s.max_tokens : 256;
+                std::vector<int32_t> toks((size_t)n_gen); int n_out = 0; float ttft = 0, dec = 0;
+                int rc = r->m->generate(r->toks.data(), (int)r->toks.size(), n_gen, &r->s, toks.data(), &n_out, &ttft, &dec);
+                if (rc != B200_OK) { fin.kind = B200_EV_ERROR; fin.finish_reason = rc; }
+                else {
+                    for (int i = 0; i < n_out; i++) { b200_event e{}; e.req_id = r->id; e.kind = B200_EV_TOKEN; e.token = toks[i]; e.n_generated = i + 1; out.push_back(e); }
+                    bool stopped = n_out > 0 && !r->s.ignore_eos && (toks[n_out - 1] == r->m->eos || toks[n_out - 1] == r->s.stop_token);
+                    fin.finish_reason = stopped ? B200_FINISH_STOP : B200_FINISH_LENGTH; fin.n_generated = n_out; fin.ttft_ms = ttft; fin.decode_ms = dec;
+                }
+            }
+            { std::lock_guard<std::mutex> lk(mu); for (auto& e : out) ev.push_back(e); ev.push_back(fin); live.erase(r->id); }
+            cv_ev.notify_all();
+        }
+    }
+    void shutdown() { { std::lock_guard<std::mutex> lk(mu); stop = true; } cv_req.notify_all(); if (th.joinable()) th.join(); started = false; stop = false; }
+};
+static Scheduler& sched() { static Scheduler s; return s; }
+}  // namespace b200
+
+using namespace b200;
+
+static int copy_out(const std::string& s, char* out, size_t cap, size_t* need) {
+    if (need) *need = s.size();
+    if (!out || cap < s.size()) return out ? fail(B200_ERR_MORE, "output buffer too small") : B200_OK;
+    memcpy(out, s.data(), s.size());
+    if (cap > s.size()) out[s.size()] = 0;
+    return B200_OK;
+}
+static std::shared_ptr<Model> find_shared(const b200_model* m) {
+    Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu);
+    for (auto& kv : R.models) if ((const b200_model*)kv.second.get() == m) return kv.second;
+    return nullptr;
+}
+
+extern "C" {
+
+int b200_init(const b200_config* cfg) { return engine().init(cfg); }
+int b200_shutdown(void) {
+    sched().shutdown();
+    Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); R.models.clear();
+    return B200_OK;
+}
+const char* b200_last_error(void) { return g_last_error.c_str(); }
+void* b200_pinned_alloc(size_t n) { void* p = nullptr; if (engine().ensure() != B200_OK) return nullptr; return cudaMallocHost(&p, n) == cudaSuccess ? p : nullptr; }
+void b200_pinned_free(void* p) { if (p) cudaFreeHost(p); }
+
+int b200_model_open(const char* id, const void* head, size_t n, b200_model** out) {
+    if (!id || !head || !out) return fail(B200_ERR_INVALID, "null argument");
+    auto m = std::make_shared<Model>();
+    int rc = m->open(id, (const uint8_t*)head, n);
+    if (rc != B200_OK) return rc;
+    { Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); R.models[id] = m; }
+    *out = (b200_model*)m.get();
+    return B200_OK;
+}
+int b200_model_upload(b200_model* m, uint64_t off, const void* bytes, size_t n) { if (!m || (!bytes && n)) return fail(B200_ERR_INVALID, "null argument"); return ((Model*)m)->upload(off, bytes, n); }
+int b200_model_commit(b200_model* m) { if (!m) return fail(B200_ERR_INVALID, "null model"); return ((Model*)m)->commit(); }
+int b200_model_close(b200_model* m) {
+    if (!m) return fail(B200_ERR_INVALID, "null model");
+    std::shared_ptr<Model> keep;
+    { Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); for (auto it = R.models.begin(); it != R.models.end(); ++it) if ((b200_model*)it->second.get() == m) { keep = it->second; R.models.erase(it); break; } }
+    if (!keep) return fail(B200_ERR_NOT_FOUND, "model is not registered");
+    std::lock_guard<std::mutex> lk(keep->run_mu); keep->release();
+    return B200_OK;
+}
+int b200_model_load_file(const char* id, const char* path, b200_model** out) {
+    if (!id || !path) return fail(B200_ERR_INVALID, "null argument");
+    std::shared_ptr<Model> m; std::string log;
+    int rc = load_file_into(id, path, m, log);
+    if (rc == B200_OK && out) *out = (b200_model*)m.get();
+    return rc;
+}
+int b200_model_find(const char* id, b200_model** out) {
+    if (!id || !out) return fail(B200_ERR_INVALID, "null argument");
+    Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu);
+    auto it = R.models.find(id); if (it == R.models.end()) return fail(B200_ERR_NOT_FOUND, std::string("model '") + id + "' is not loaded");
+    *out = (b200_model*)it->second.get(); return B200_OK;
+}
+int b200_model_list(char* out, size_t cap, size_t* need) {
+    std::string env = handle_subject("lmstudio.list_models", "");
+    // strip the envelope: {"ok":true,"data":{"http_status":200,"models":<X>}}
+    const std::string key = "\"models\":"; size_t k = env.find(key);
+    std::string models = k == std::string::npos ? "{\"data\":[],\"object\":\"list\"}" : env.substr(k + key.size(), env.size() - (k + key.size()) - 2);
+    return copy_out(models, out, cap, need);
+}
+int b200_model_info(const b200_model* m, char* out, size_t cap, size_t* need) { if (!m) return fail(B200_ERR_INVALID, "null model"); return copy_out(((const Model*)m)->info_json(), out, cap, need); }
+int b200_model_n_vocab(const b200_model* m) { return m ? ((const Model*)m)->n_vocab : 0; }
+
+int b200_model_generate(b200_model* m, const int32_t* prompt, int n_prompt, int n_gen, const b200_sampling* s, int32_t* out, int* n_out, float* ttft, float* dec) {
+    if (!m || !prompt || !out) return fail(B200_ERR_INVALID, "null argument");
+    return ((Model*)m)->generate(prompt, n_prompt, n_gen, s, out, n_out, ttft, dec);
+}
+int b200_model_eval(b200_model* m, const int32_t* toks, int n, float* all, float* last) { if (!m || !toks) return fail(B200_ERR_INVALID, "null argument"); return ((Model*)m)->eval(toks, n, all, last); }
+int b200_bench_decode(b200_model* m, int ctx, int steps, int warmup, float* ms, double* bytes) { if (!m) return fail(B200_ERR_INVALID, "null model"); return ((Model*)m)->bench_decode(ctx, steps, warmup, ms, bytes); }
+
+int b200_tokenize(const b200_model* m, const char* text, size_t n, int32_t* out, int cap, int* n_out) {
+    if (!m || (!text && n)) return fail(B200_ERR_INVALID, "null argument");
+    auto t = ((const Model*)m)->tokenize(std::string(text ? text : "", n), true);
+    if (n_out) *n_out = (int)t.size();
+    if (!out || cap < (int)t.size()) return out ? fail(B200_ERR_MORE, "token buffer too small") : B200_OK;
+    memcpy(out, t.data(), t.size() * 4); return B200_OK;
+}
+int b200_detokenize(const b200_model* m, const int32_t* toks, int n, char* out, size_t cap, size_t* need) {
+    if (!m || (!toks && n)) return fail(B200_ERR_INVALID, "null argument");
+    return copy_out(((const Model*)m)->detokenize(toks, n), out, cap, need);
+}
+
+int b200_submit(b200_model* m, const int32_t* toks, int n, const b200_sampling* s, uint64_t req_id) {
+    if (!m || !toks || n < 1) return fail(B200_ERR_INVALID, "bad submit arguments");
+    auto sp = find_shared(m); if (!sp || !sp->committed) return fail(B200_ERR_STATE, "model is not loaded");
+    auto r = std::make_shared<Request>(); r->m = sp; r->toks.assign(toks, toks + n); r->id = req_id;
+    if (s) r->s = *s; else { r->s = b200_sampling{}; r->s.max_tokens = 256; r->s.stop_token = -1; }
+    Scheduler& S = sched();
+    { std::lock_guard<std::mutex> lk(S.mu); S.start(); S.q.push_back(r); S.live[req_id] = r; }
+    S.cv_req.notify_one();
+    return B200_OK;
+}
+int b200_poll(b200_event* out, int max, int timeout_ms) {
+    if (!out || max < 1) return fail(B200_ERR_INVALID, "bad poll arguments");
+    Scheduler& S = sched(); std::unique_lock<std::mutex> lk(S.mu);
+    if (S.ev.empty() && timeout_ms != 0) S.cv_ev.wait_for(lk, std::chrono::milliseconds(timeout_ms < 0 ? 3600000 : timeout_ms), [&] { return !S.ev.empty(); });
+    int n = 0; while (n < max && !S.ev.empty()) { out[n++] = S.ev.front(); S.ev.pop_front(); }
+    return n;
+}
+int b200_cancel(uint64_t req_id) {
+    Scheduler& S = sched(); std::lock_guard<std::mutex> lk(S.mu);
+    auto it = S.live.find(req_id); if (it == S.live.end()) return fail(B200_ERR_NOT_FOUND, "no such request");
+    it->second->cancelled = true; return B200_OK;
+}
+
+int b200_handle(const char* subject, const void* payload, size_t n, char* reply, size_t cap, size_t* need) {
+    if (!subject) return fail(B200_ERR_INVALID, "null subject");
+    return copy_out(handle_subject(subject, std::string((const char*)payload, payload ? n : 0)), reply, cap, need);
+}
+int b200_set_models_dir(const char* dir) { Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); R.models_dir = dir ? dir : ""; while (R.models_dir.size() > 1 && R.models_dir.back() == '/') R.models_dir.pop_back(); return B200_OK; }
+
+int b200_dequantize(int type, const void* raw, int64_t n_rows, int K, float* out) { if ((!raw || !out) && n_rows) return fail(B200_ERR_INVALID, "null argument"); return kernel_dequantize(type, raw, n_rows, K, out); }
+int b200_gemv(int type, const void* raw, int64_t N, int K, const float* x, float* y, int iters, float* ms) { if (!raw || !x || !y) return fail(B200_ERR_INVALID, "null argument"); return kernel_gemv(type, raw, N, K, x, y, iters, ms); }
+int b200_layout_selftest(void) { return layout_selftest(); }
+uint64_t b200_launch_count(void) { return engine().launches; }
+
+}  // extern "C"

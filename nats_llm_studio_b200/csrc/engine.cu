@@ -1,0 +1,497 @@
+// engine.cu — host side of the engine: HBM-resident model registry, GGUF upload + on-GPU repack,
+// decode-schedule construction, kernel launches, and the kernel-level C ABI entry points.
+// Replaces what /root/reference/nats_llm_studio.go delegates to LM Studio (Chat :158-179,
+// PullModel :46-59, ListModels :136-156, DeleteModel :99-133).
+#include "engine.hpp"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
+
+#include "decode.cuh"
+#include "sampler.cuh"
+
+namespace b200 {
+
+thread_local std::string g_last_error;
+int fail(int code, const std::string& msg) { g_last_error = msg; return code; }
+
+#define CK(expr)                                                                                              \
+    do {                                                                                                      \
+        cudaError_t e_ = (expr);                                                                              \
+        if (e_ != cudaSuccess) return fail(B200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+Engine& engine() { static Engine e; return e; }
+
+// ------------------------------------------------------------------------------------ init
+int Engine::init(const b200_config* cfg) {
+    std::lock_guard<std::mutex> lk(mu);
+    if (ready) return B200_OK;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(B200_ERR_CUDA, std::string("no CUDA device: the engine has no CPU fallback (") + cudaGetErrorString(e) + ")");
+    device = cfg ? cfg->device : 0;
+    max_ctx = cfg && cfg->max_ctx > 0 ? cfg->max_ctx : 4096;
+    max_seqs = cfg && cfg->max_seqs > 0 ? cfg->max_seqs : 1;
+    CK(cudaSetDevice(device));
+    cudaDeviceProp p; CK(cudaGetDeviceProperties(&p, device));
+    if (p.major < 10) return fail(B200_ERR_UNSUPPORTED, "this library is built for sm_100a (B200) only");
+    n_sm = p.multiProcessorCount; smem_per_sm = (int)p.sharedMemPerMultiprocessor; smem_optin = (int)p.sharedMemPerBlockOptin;
+    CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
+    CK(cudaFuncSetAttribute(decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin));
+    ready = true;
+    return B200_OK;
+}
+
+int Engine::ensure() {
+    if (ready) { cudaSetDevice(device); return B200_OK; }
+    return init(nullptr);
+}
+
+// ------------------------------------------------------------------------------------ launch geometry
+struct LaunchCfg { int grid; uint32_t ring_bytes; int max_grp; size_t smem; };
+
+static int launch_cfg(Engine& E, int max_grp, LaunchCfg& lc) {
+    // two CTAs per SM: each gets half of the SM's shared memory minus the 1 KB system reservation
+    size_t per_cta = (size_t)E.smem_per_sm / 2 - 1024;
+    if (per_cta > (size_t)E.smem_optin) per_cta = E.smem_optin;
+    size_t fixed = smem_x_bytes(max_grp) + smem_misc_bytes();
+    if (fixed + MAX_STAGE_BYTES + 256 > per_cta) {      // very wide model: one CTA per SM
+        per_cta = E.smem_optin;
+        if (fixed + MAX_STAGE_BYTES + 256 > per_cta) return fail(B200_ERR_UNSUPPORTED, "activation vector does not fit in shared memory");
+        lc.grid = E.n_sm;
+    } else lc.grid = 2 * E.n_sm;
+    lc.ring_bytes = (uint32_t)((per_cta - fixed - 128) / 128 * 128);
+    lc.max_grp = max_grp; lc.smem = lc.ring_bytes + fixed;
+    int occ = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, decode_kernel, CTA_THREADS, lc.smem));
+    if (occ < 1) return fail(B200_ERR_CUDA, "decode kernel does not fit on an SM");
+    if (lc.grid > occ * E.n_sm) lc.grid = occ * E.n_sm;
+    return B200_OK;
+}
+
+static int launch_decode(Engine& E, const DecodeParams& P, const DecodeRun& R, const LaunchCfg& lc) {
+    void* args[] = {(void*)&P, (void*)&R, (void*)&lc.ring_bytes, (void*)&lc.max_grp};
+    CK(cudaLaunchCooperativeKernel((void*)decode_kernel, dim3(lc.grid), dim3(CTA_THREADS), args, lc.smem, E.stream));
+    E.launches++;
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------ device helpers
+template <typename T>
+static int dalloc(T** p, size_t n) {
+    cudaError_t e = cudaMalloc((void**)p, n * sizeof(T));
+    if (e != cudaSuccess) return fail(B200_ERR_NOMEM, std::string("cudaMalloc of ") + std::to_string(n * sizeof(T)) + " bytes: " + cudaGetErrorString(e));
+    return B200_OK;
+}
+
+// repack `raw` (device, ggml row-major blocks) into the engine layout at `out`
+static int repack(Engine& E, const uint8_t* raw, uint8_t* out, int type, int64_t N, int K, int interleave_parity = -1) {
+    long long chunks = (long long)N * n_groups(K) * group_bytes(type) / 16;
+    int blocks = (int)std::min<long long>((chunks + 255) / 256, 148LL * 32);
+    if (blocks < 1) blocks = 1;
+    if (interleave_parity < 0) repack_kernel<<<blocks, 256, 0, E.stream>>>(raw, out, type, N, K, 0, 0);
+    else repack_interleave_kernel<<<blocks, 256, 0, E.stream>>>(raw, out, type, N, K, interleave_parity);
+    CK(cudaGetLastError());
+    E.launches++;
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------ Model
+Model::~Model() { release(); }
+
+void Model::release() {
+    for (void* p : owned) cudaFree(p);
+    owned.clear();
+    if (d_raw) { cudaFree(d_raw); d_raw = nullptr; }
+    committed = false;
+}
+
+template <typename T>
+int Model::own(T** p, size_t n) { int rc = dalloc(p, n); if (rc == B200_OK) { owned.push_back(*p); hbm_bytes += n * sizeof(T); } return rc; }
+
+int Model::open(const std::string& id_, const uint8_t* head, size_t n) {
+    id = id_;
+    std::string err = gguf_parse(head, n, meta);
+    if (err == "need more") return fail(B200_ERR_MORE, "GGUF header longer than the supplied prefix");
+    if (!err.empty()) return fail(B200_ERR_INVALID, "GGUF: " + err);
+    arch = meta.str("general.architecture");
+    if (arch != "llama" && arch != "granite") return fail(B200_ERR_UNSUPPORTED, "unsupported architecture '" + arch + "' (llama, granite)");
+    auto an = [&](const char* k, double d) { return meta.num(arch + "." + k, d); };
+    n_layer = (int)an("block_count", 0); n_embd = (int)an("embedding_length", 0); n_head = (int)an("attention.head_count", 0);
+    n_head_kv = (int)an("attention.head_count_kv", n_head); n_ff = (int)an("feed_forward_length", 0);
+    n_ctx_train = (int)an("context_length", 4096);
+    rms_eps = (float)an("attention.layer_norm_rms_epsilon", 1e-5); rope_base = (float)an("rope.freq_base", 10000.0);
+    head_dim = n_head ? (int)an("attention.key_length", n_embd / n_head) : 0;
+    n_rot = (int)an("rope.dimension_count", head_dim);
+    emb_scale = (float)an("embedding_scale", 0); res_scale = (float)an("residual_scale", 0);
+    attn_scale = (float)an("attention.scale", 0); logit_scale = (float)an("logit_scale", 0);
+    const GgufTensor* te = meta.tensor("token_embd.weight");
+    if (!te || !n_layer || !n_embd || !n_head || !n_ff) return fail(B200_ERR_INVALID, "GGUF: missing hyper-parameters or token_embd.weight");
+    n_vocab = (int)te->ne[1];
+    if (head_dim != 64 && head_dim != 128) return fail(B200_ERR_UNSUPPORTED, "head_dim must be 64 or 128");
+    if (n_embd % 256 || n_ff % 256 || (n_head * head_dim) % 256) return fail(B200_ERR_UNSUPPORTED, "dimensions must be multiples of 256");
+    if (n_head % n_head_kv) return fail(B200_ERR_INVALID, "head_count not a multiple of head_count_kv");
+    bos = (int)meta.num("tokenizer.ggml.bos_token_id", -1); eos = (int)meta.num("tokenizer.ggml.eos_token_id", -1);
+    if (auto v = meta.find("tokenizer.ggml.tokens")) vocab = v->arr_str;
+    if (auto v = meta.find("tokenizer.ggml.token_type")) { tok_type.assign(v->arr_num.size(), 0); for (size_t i = 0; i < v->arr_num.size(); i++) tok_type[i] = (int)v->arr_num[i]; }
+    build_tokenizer();
+    Engine& E = engine();
+    if (int rc = E.ensure()) return rc;
+    cudaError_t e = cudaMalloc((void**)&d_raw, meta.data_bytes ? meta.data_bytes : 16);
+    if (e != cudaSuccess) return fail(B200_ERR_NOMEM, std::string("staging cudaMalloc: ") + cudaGetErrorString(e));
+    return B200_OK;
+}
+
+int Model::upload(uint64_t file_off, const void* bytes, size_t n) {
+    if (committed || !d_raw) return fail(B200_ERR_STATE, "upload after commit");
+    Engine& E = engine(); E.ensure();
+    uint64_t lo = std::max<uint64_t>(file_off, meta.data_offset), hi = std::min<uint64_t>(file_off + n, meta.data_offset + meta.data_bytes);
+    if (lo >= hi) return B200_OK;                                   // header or padding bytes only
+    CK(cudaMemcpyAsync(d_raw + (lo - meta.data_offset), (const uint8_t*)bytes + (lo - file_off), hi - lo, cudaMemcpyHostToDevice, E.copy_stream));
+    CK(cudaStreamSynchronize(E.copy_stream));                       // caller may reuse its buffer on return
+    uploaded += hi - lo;
+    return B200_OK;
+}
+
+int Model::load_matrix(const std::string& name, int64_t N, int K, Matrix& out) {
+    const GgufTensor* t = meta.tensor(name);
+    if (!t) return fail(B200_ERR_INVALID, "GGUF: missing tensor " + name);
+    if (t->ne[0] != K || t->ne[1] != N) return fail(B200_ERR_INVALID, "GGUF: tensor " + name + " has unexpected shape");
+    if (!is_streamable(t->type)) return fail(B200_ERR_UNSUPPORTED, "tensor " + name + ": ggml type " + std::to_string(t->type) + " is not supported for matrices (Q4_K, Q5_K, Q6_K, Q8_0)");
+    if (N % 2) return fail(B200_ERR_UNSUPPORTED, "tensor " + name + ": odd row count");
+    out.type = t->type; out.N = N; out.K = K;
+    if (int rc = own(&out.w, repacked_bytes(t->type, N, K))) return rc;
+    weight_bytes += t->nbytes;
+    return repack(engine(), d_raw + t->offset, out.w, t->type, N, K);
+}
+
+int Model::load_vector(const std::string& name, int64_t n, float** out) {
+    const GgufTensor* t = meta.tensor(name);
+    if (!t) return fail(B200_ERR_INVALID, "GGUF: missing tensor " + name);
+    if (t->type != T_F32 || t->n_elems() != n) return fail(B200_ERR_UNSUPPORTED, "tensor " + name + " must be F32[" + std::to_string(n) + "]");
+    if (int rc = own(out, (size_t)n)) return rc;
+    weight_bytes += t->nbytes;
+    CK(cudaMemcpyAsync(*out, d_raw + t->offset, (size_t)n * 4, cudaMemcpyDeviceToDevice, engine().stream));
+    return B200_OK;
+}
+
+int Model::commit() {
+    if (committed) return B200_OK;
+    if (uploaded < meta.data_bytes) return fail(B200_ERR_STATE, "commit before all tensor bytes were uploaded (" + std::to_string(uploaded) + " of " + std::to_string(meta.data_bytes) + ")");
+    Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    const int D = n_embd, F = n_ff, QD = n_head * head_dim, KVD = n_head_kv * head_dim;
+    layers.resize(n_layer);
+    if (int rc = load_matrix("token_embd.weight", n_vocab, D, tok_embd)) return rc;
+    for (int l = 0; l < n_layer; l++) {
+        Layer& L = layers[l]; std::string p = "blk." + std::to_string(l) + ".";
+        int rc;
+        if ((rc = load_vector(p + "attn_norm.weight", D, &L.attn_norm))) return rc;
+        if ((rc = load_matrix(p + "attn_q.weight", QD, D, L.wq))) return rc;
+        if ((rc = load_matrix(p + "attn_k.weight", KVD, D, L.wk))) return rc;
+        if ((rc = load_matrix(p + "attn_v.weight", KVD, D, L.wv))) return rc;
+        if ((rc = load_matrix(p + "attn_output.weight", D, QD, L.wo))) return rc;
+        if ((rc = load_vector(p + "ffn_norm.weight", D, &L.ffn_norm))) return rc;
+        const GgufTensor *tg = meta.tensor(p + "ffn_gate.weight"), *tu = meta.tensor(p + "ffn_up.weight");
+        if (!tg || !tu) return fail(B200_ERR_INVALID, "GGUF: missing ffn_gate/ffn_up in layer " + std::to_string(l));
+        if (tg->type != tu->type) return fail(B200_ERR_UNSUPPORTED, "ffn_gate and ffn_up of a layer must share a quant type");
+        if (tg->ne[0] != D || tg->ne[1] != F || tu->ne[0] != D || tu->ne[1] != F) return fail(B200_ERR_INVALID, "GGUF: ffn_gate/up shape");
+        if (!is_streamable(tg->type)) return fail(B200_ERR_UNSUPPORTED, "ffn_gate: unsupported ggml type");
+        L.wgu.type = tg->type; L.wgu.N = 2 * (int64_t)F; L.wgu.K = D;              // rows interleaved (gate_i, up_i)
+        if ((rc = own(&L.wgu.w, repacked_bytes(tg->type, 2 * (int64_t)F, D)))) return rc;
+        if ((rc = repack(E, d_raw + tg->offset, L.wgu.w, tg->type, F, D, 0))) return rc;
+        if ((rc = repack(E, d_raw + tu->offset, L.wgu.w, tu->type, F, D, 1))) return rc;
+        weight_bytes += tg->nbytes + tu->nbytes;
+        if ((rc = load_matrix(p + "ffn_down.weight", D, F, L.wd))) return rc;
+    }
+    if (int rc = load_vector("output_norm.weight", D, &out_norm)) return rc;
+    if (meta.tensor("output.weight")) { if (int rc = load_matrix("output.weight", n_vocab, D, out_w)) return rc; }
+    else out_w = tok_embd;                                                        // tied embeddings
+
+    // rope frequencies (optional rope_freqs.weight = per-frequency divisors, llama-3.1 style)
+    std::vector<float> ff(n_rot / 2, 1.0f);
+    if (const GgufTensor* rf = meta.tensor("rope_freqs.weight")) {
+        if (rf->type == T_F32 && rf->n_elems() == n_rot / 2) { CK(cudaStreamSynchronize(E.stream)); CK(cudaMemcpy(ff.data(), d_raw + rf->offset, ff.size() * 4, cudaMemcpyDeviceToHost)); }
+    }
+    std::vector<float> inv(n_rot / 2);
+    for (int i = 0; i < n_rot / 2; i++) inv[i] = (float)(std::pow((double)rope_base, -2.0 * i / n_rot) / (double)ff[i]);
+    if (int rc = own(&inv_freq, inv.size())) return rc;
+    CK(cudaMemcpyAsync(inv_freq, inv.data(), inv.size() * 4, cudaMemcpyHostToDevice, E.stream));
+    CK(cudaStreamSynchronize(E.stream));
+    cudaFree(d_raw); d_raw = nullptr;
+
+    // ---- runtime buffers
+    int max_grp = std::max({n_groups(F), n_groups(QD), 2 * n_groups(D)});
+    LaunchCfg lc; if (int rc = launch_cfg(E, max_grp, lc)) return rc;
+    grid = lc.grid; ring_bytes = lc.ring_bytes; smem_max_grp = lc.max_grp; smem_bytes = lc.smem;
+    n_splits = std::max(1, std::min(16, grid / n_head));
+    int rc;
+    if ((rc = own(&d_h, (size_t)D)) || (rc = own(&d_q, (size_t)QD)) || (rc = own(&d_act, (size_t)F)) || (rc = own(&d_logits, (size_t)n_vocab)) ||
+        (rc = own(&d_part_acc, (size_t)n_head * n_splits * head_dim)) || (rc = own(&d_part_ml, (size_t)n_head * n_splits * 2)) ||
+        (rc = own(&d_cand_val, (size_t)grid)) || (rc = own(&d_cand_idx, (size_t)grid)) || (rc = own(&d_state, (size_t)16)) ||
+        (rc = own(&d_out_tokens, (size_t)E.max_ctx + 16)) || (rc = own(&d_forced, (size_t)E.max_ctx + 16)))
+        return rc;
+    CK(cudaMemset(d_state, 0, 16 * sizeof(int)));
+    n_pages = (E.max_ctx + 15) / 16 * E.max_seqs;
+    size_t page_elems = (size_t)n_layer * 2 * n_head_kv * 16 * head_dim;
+    if ((rc = own(&d_kv, page_elems * n_pages)) || (rc = own(&d_block_table, (size_t)n_pages))) return rc;
+    std::vector<int> bt(n_pages); for (int i = 0; i < n_pages; i++) bt[i] = i;
+    CK(cudaMemcpy(d_block_table, bt.data(), bt.size() * 4, cudaMemcpyHostToDevice));
+
+    // ---- decode schedule
+    std::vector<Phase> ph;
+    auto mk_op = [&](const Matrix& m, int epi, float* out, float scale, int layer) {
+        OpDesc o{}; o.w = m.w; o.type = m.type; o.n_pairs = (int)(m.N / 2); o.n_grp = n_groups(m.K); o.epi = epi; o.out = out; o.scale = scale; o.layer = layer; return o;
+    };
+    auto gemv = [&](int K, int pro, const float* src, const float* nw, int layer, std::initializer_list<OpDesc> ops) {
+        Phase p{}; p.kind = PH_GEMV; p.K = K; p.pro = pro; p.src = src; p.norm_w = nw; p.layer = layer; p.n_ops = 0; p.total_pairs = 0;
+        for (auto& o : ops) { p.op[p.n_ops++] = o; p.total_pairs += o.n_pairs; }
+        ph.push_back(p);
+    };
+    const float rs = res_scale != 0.f ? res_scale : 1.f;
+    { Phase p{}; p.kind = PH_EMBED; ph.push_back(p); }
+    for (int l = 0; l < n_layer; l++) {
+        Layer& L = layers[l];
+        gemv(D, PRO_NORM, d_h, L.attn_norm, l, {mk_op(L.wq, EPI_ROPE_Q, d_q, 1.f, l), mk_op(L.wk, EPI_ROPE_K, nullptr, 1.f, l), mk_op(L.wv, EPI_V, nullptr, 1.f, l)});
+        { Phase p{}; p.kind = PH_ATTN; p.layer = l; ph.push_back(p); }
+        gemv(QD, PRO_ATTN, nullptr, nullptr, l, {mk_op(L.wo, EPI_RESID, d_h, rs, l)});
+        gemv(D, PRO_NORM, d_h, L.ffn_norm, l, {mk_op(L.wgu, EPI_SWIGLU, d_act, 1.f, l)});
+        gemv(F, PRO_PLAIN, d_act, nullptr, l, {mk_op(L.wd, EPI_RESID, d_h, rs, l)});
+    }
+    gemv(D, PRO_NORM, d_h, out_norm, 0, {mk_op(out_w, EPI_LOGITS, d_logits, logit_scale != 0.f ? 1.f / logit_scale : 1.f, 0)});
+    n_phases = (int)ph.size();
+    if ((rc = own(&d_phases, ph.size()))) return rc;
+    CK(cudaMemcpy(d_phases, ph.data(), ph.size() * sizeof(Phase), cudaMemcpyHostToDevice));
+    committed = true;
+    return B200_OK;
+}
+
+void Model::fill_params(DecodeParams& P) const {
+    P = DecodeParams{};
+    P.phases = d_phases; P.n_phases = n_phases;
+    P.n_embd = n_embd; P.n_head = n_head; P.n_head_kv = n_head_kv; P.head_dim = head_dim; P.n_rot = n_rot; P.n_vocab = n_vocab; P.n_splits = n_splits;
+    P.rms_eps = rms_eps; P.kq_scale = attn_scale != 0.f ? attn_scale : 1.0f / std::sqrt((float)head_dim); P.emb_scale = emb_scale;
+    P.inv_freq = inv_freq; P.embd = tok_embd.w; P.embd_type = tok_embd.type;
+    P.h = d_h; P.q = d_q; P.act = d_act; P.logits = d_logits; P.part_acc = d_part_acc; P.part_ml = d_part_ml;
+    P.cand_val = d_cand_val; P.cand_idx = d_cand_idx;
+    P.kv.pages = d_kv; P.kv.block_table = d_block_table; P.kv.n_layer = n_layer; P.kv.n_head_kv = n_head_kv; P.kv.head_dim = head_dim;
+    P.pos = d_state + 0; P.token = d_state + 1; P.bar_ctr = (unsigned*)(d_state + 2); P.epoch = (unsigned*)(d_state + 3);
+    P.out_tokens = d_out_tokens; P.n_steps = 1; P.want_argmax = 1;
+}
+
+// Runs `n_steps` decode steps.  forced (host, n_forced ints) are fed first.  reset: start at position 0.
+int Model::run_steps(int n_steps, const int32_t* forced, int n_forced, bool reset, float* logits_all_dev) {
+    Engine& E = engine();
+    if (!committed) return fail(B200_ERR_STATE, "model not committed");
+    if (n_steps <= 0) return B200_OK;
+    if (reset) { int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0; }
+    if (cur_pos + n_steps > E.max_ctx) return fail(B200_ERR_INVALID, "context overflow: " + std::to_string(cur_pos + n_steps) + " > max_ctx " + std::to_string(E.max_ctx));
+    if (n_forced > 0) CK(cudaMemcpyAsync(d_forced, forced, (size_t)n_forced * 4, cudaMemcpyHostToDevice, E.stream));
+    DecodeParams P; fill_params(P); P.n_steps = n_steps;
+    DecodeRun R{}; R.forced = d_forced; R.n_forced = n_forced; R.logits_all = logits_all_dev;
+    LaunchCfg lc; lc.grid = grid; lc.ring_bytes = ring_bytes; lc.max_grp = smem_max_grp; lc.smem = smem_bytes;
+    if (int rc = launch_decode(E, P, R, lc)) return rc;
+    cur_pos += n_steps;
+    return B200_OK;
+}
+
+int Model::generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_sampling* s, int32_t* out, int* n_out, float* ttft_ms, float* decode_ms) {
+    Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    std::lock_guard<std::mutex> lk(run_mu);
+    if (n_prompt < 1 || n_gen < 1) return fail(B200_ERR_INVALID, "need at least one prompt token and one generated token");
+    for (int i = 0; i < n_prompt; i++) if (prompt[i] < 0 || prompt[i] >= n_vocab) return fail(B200_ERR_INVALID, "prompt token out of range");
+    const bool greedy = !s || s->temperature <= 0.f;
+    const int stop = s ? s->stop_token : -1; const bool ignore_eos = s && s->ignore_eos;
+    cudaEvent_t e0, e1, e2; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreate(&e2));
+    int rc = B200_OK; int produced = 0;
+    CK(cudaEventRecord(e0, E.stream));
+    if (greedy) {
+        // prompt + first token in one launch, then the remaining tokens in chunks (EOS checked between chunks)
+        if ((rc = run_steps(n_prompt, prompt, n_prompt, true, nullptr))) goto done;
+        CK(cudaEventRecord(e1, E.stream));
+        CK(cudaMemcpyAsync(out, d_out_tokens + n_prompt - 1, 4, cudaMemcpyDeviceToHost, E.stream));
+        CK(cudaStreamSynchronize(E.stream));
+        produced = 1;
+        while (produced < n_gen) {
+            if (!ignore_eos && (out[produced - 1] == eos || out[produced - 1] == stop)) break;
+            int chunk = std::min(n_gen - produced, ignore_eos ? n_gen : 32);
+            if ((rc = run_steps(chunk, nullptr, 0, false, nullptr))) goto done;
+            CK(cudaMemcpyAsync(out + produced, d_out_tokens, (size_t)chunk * 4, cudaMemcpyDeviceToHost, E.stream));
+            CK(cudaStreamSynchronize(E.stream));
+            int k = 0;
+            for (; k < chunk; k++) { produced++; if (!ignore_eos && (out[produced - 1] == eos || out[produced - 1] == stop)) break; }
+        }
+    } else {
+        // sampled: one step per launch with logits, then the sampler kernel picks the token
+        if ((rc = run_steps(n_prompt, prompt, n_prompt, true, nullptr))) goto done;
+        for (;;) {
+            if ((rc = sample_token(E, *this, *s, (uint64_t)produced))) goto done;
+            if (produced == 0) CK(cudaEventRecord(e1, E.stream));
+            CK(cudaMemcpyAsync(out + produced, d_state + 1, 4, cudaMemcpyDeviceToHost, E.stream));
+            CK(cudaStreamSynchronize(E.stream));
+            produced++;
+            if (produced >= n_gen || (!ignore_eos && (out[produced - 1] == eos || out[produced - 1] == stop))) break;
+            if ((rc = run_steps(1, nullptr, 0, false, nullptr))) goto done;
+        }
+    }
+    CK(cudaEventRecord(e2, E.stream)); CK(cudaEventSynchronize(e2));
+    { float a = 0, b = 0; cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2); if (ttft_ms) *ttft_ms = a; if (decode_ms) *decode_ms = b; }
+    if (n_out) *n_out = produced;
+done:
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
+    return rc;
+}
+
+int Model::eval(const int32_t* toks, int n, float* logits_all, float* logits_last) {
+    Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    std::lock_guard<std::mutex> lk(run_mu);
+    if (n < 1) return fail(B200_ERR_INVALID, "empty token list");
+    for (int i = 0; i < n; i++) if (toks[i] < 0 || toks[i] >= n_vocab) return fail(B200_ERR_INVALID, "token out of range");
+    float* d_all = nullptr;
+    if (logits_all) { if (int rc = dalloc(&d_all, (size_t)n * n_vocab)) return rc; }
+    int rc = run_steps(n, toks, n, true, d_all);
+    if (!rc) {
+        cudaError_t e = cudaStreamSynchronize(E.stream);
+        if (e == cudaSuccess && logits_all) e = cudaMemcpy(logits_all, d_all, (size_t)n * n_vocab * 4, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess && logits_last) e = cudaMemcpy(logits_last, logits_all ? d_all + (size_t)(n - 1) * n_vocab : d_logits, (size_t)n_vocab * 4, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = fail(B200_ERR_CUDA, cudaGetErrorString(e));
+    }
+    if (d_all) cudaFree(d_all);
+    return rc;
+}
+
+// algorithmic bytes one decode step reads at context length ctx:
+// every matrix except token_embd (unless tied), one token_embd row, the norm vectors, fp16 K and V.
+double Model::bytes_per_token(int ctx) const {
+    const GgufTensor* te = meta.tensor("token_embd.weight");
+    double w = (double)weight_bytes;
+    if (meta.tensor("output.weight")) w -= (double)te->nbytes;
+    w += (double)te->nbytes / n_vocab;
+    return w + (double)ctx * n_layer * 2 * n_head_kv * head_dim * 2;
+}
+
+int Model::bench_decode(int ctx_len, int n_steps, int warmup, float* ms_per_token, double* bytes) {
+    Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    std::lock_guard<std::mutex> lk(run_mu);
+    if (ctx_len < 1 || ctx_len + n_steps + warmup > E.max_ctx) return fail(B200_ERR_INVALID, "bench context does not fit max_ctx");
+    // prime the KV cache: positions [0, ctx_len) hold whatever the cache holds (attention cost is
+    // data-independent); set the position and a start token, then time n_steps greedy steps.
+    int st[2] = {ctx_len, 1 % n_vocab};
+    CK(cudaMemcpyAsync(d_state, st, 8, cudaMemcpyHostToDevice, E.stream)); cur_pos = ctx_len;
+    if (warmup > 0) { if (int rc = run_steps(warmup, nullptr, 0, false, nullptr)) return rc; }
+    CK(cudaMemcpyAsync(d_state, st, 8, cudaMemcpyHostToDevice, E.stream)); cur_pos = ctx_len;
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    CK(cudaEventRecord(e0, E.stream));
+    int rc = run_steps(n_steps, nullptr, 0, false, nullptr);
+    CK(cudaEventRecord(e1, E.stream)); CK(cudaEventSynchronize(e1));
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1); cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (ms_per_token) *ms_per_token = ms / n_steps;
+    if (bytes) { double b = 0; for (int i = 0; i < n_steps; i++) b += bytes_per_token(ctx_len + i + 1); *bytes = b / n_steps; }
+    return rc;
+}
+
+int sample_token(Engine& E, Model& m, const b200_sampling& s, uint64_t step) {
+    sample_kernel<<<1, SAMPLER_THREADS, 0, E.stream>>>(m.d_logits, m.n_vocab, s.top_k, s.top_p <= 0.f ? 1.f : s.top_p, s.temperature, s.seed, step, m.d_state + 1, nullptr);
+    CK(cudaGetLastError());
+    E.launches++;
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------ kernel-level entry points
+int kernel_dequantize(int type, const void* raw, int64_t n_rows, int K, float* out) {
+    Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    if (!is_streamable(type)) return fail(B200_ERR_UNSUPPORTED, "unsupported ggml type");
+    if (n_rows < 0 || K <= 0 || K % 256) return fail(B200_ERR_INVALID, "K must be a positive multiple of 256");
+    if (n_rows == 0) return B200_OK;
+    int64_t N = n_rows + (n_rows & 1);
+    size_t rb = raw_row_bytes(type, K);
+    uint8_t *d_raw = nullptr, *d_w = nullptr; float* d_out = nullptr; int rc;
+    if ((rc = dalloc(&d_raw, (size_t)N * rb)) || (rc = dalloc(&d_w, repacked_bytes(type, N, K))) || (rc = dalloc(&d_out, (size_t)N * K))) { cudaFree(d_raw); cudaFree(d_w); cudaFree(d_out); return rc; }
+    cudaMemsetAsync(d_raw, 0, (size_t)N * rb, E.stream);
+    cudaMemcpyAsync(d_raw, raw, (size_t)n_rows * rb, cudaMemcpyHostToDevice, E.stream);
+    rc = repack(E, d_raw, d_w, type, N, K);
+    if (!rc) {
+        dequant_repacked_kernel<<<std::min<long long>((N * K + 255) / 256, 148 * 16), 256, 0, E.stream>>>(d_w, type, N, K, d_out); E.launches++;
+        cudaError_t e = cudaMemcpyAsync(out, d_out, (size_t)n_rows * K * 4, cudaMemcpyDeviceToHost, E.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(E.stream);
+        if (e != cudaSuccess) rc = fail(B200_ERR_CUDA, cudaGetErrorString(e));
+    }
+    cudaFree(d_raw); cudaFree(d_w); cudaFree(d_out);
+    return rc;
+}
+
+int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, float* y, int iters, float* ms_out) {
+    Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    if (!is_streamable(type)) return fail(B200_ERR_UNSUPPORTED, "unsupported ggml type");
+    if (N <= 0 || N % 2 || K <= 0 || K % 256) return fail(B200_ERR_INVALID, "N must be even and K a multiple of 256");
+    if (iters < 1) iters = 1;
+    size_t rb = raw_row_bytes(type, K);
+    uint8_t *d_raw = nullptr, *d_w = nullptr; float *d_x = nullptr, *d_y = nullptr, *d_cv = nullptr; int *d_ci = nullptr, *d_st = nullptr, *d_ot = nullptr; Phase* d_ph = nullptr;
+    int rc = B200_OK;
+    LaunchCfg lc;
+    auto cleanup = [&]() { cudaFree(d_raw); cudaFree(d_w); cudaFree(d_x); cudaFree(d_y); cudaFree(d_cv); cudaFree(d_ci); cudaFree(d_st); cudaFree(d_ot); cudaFree(d_ph); };
+    if ((rc = launch_cfg(E, n_groups(K), lc))) return rc;
+    if ((rc = dalloc(&d_raw, (size_t)N * rb)) || (rc = dalloc(&d_w, repacked_bytes(type, N, K))) || (rc = dalloc(&d_x, (size_t)K)) || (rc = dalloc(&d_y, (size_t)N)) ||
+        (rc = dalloc(&d_cv, (size_t)lc.grid)) || (rc = dalloc(&d_ci, (size_t)lc.grid)) || (rc = dalloc(&d_st, (size_t)16)) || (rc = dalloc(&d_ot, (size_t)iters + 1)) || (rc = dalloc(&d_ph, (size_t)1))) { cleanup(); return rc; }
+    cudaMemcpyAsync(d_raw, raw, (size_t)N * rb, cudaMemcpyHostToDevice, E.stream);
+    cudaMemcpyAsync(d_x, x, (size_t)K * 4, cudaMemcpyHostToDevice, E.stream);
+    cudaMemsetAsync(d_st, 0, 64, E.stream);
+    rc = repack(E, d_raw, d_w, type, N, K);
+    if (!rc) {
+        Phase p{}; p.kind = PH_GEMV; p.K = K; p.pro = PRO_PLAIN; p.src = d_x; p.n_ops = 1; p.total_pairs = (int)(N / 2);
+        p.op[0].w = d_w; p.op[0].type = type; p.op[0].n_pairs = (int)(N / 2); p.op[0].n_grp = n_groups(K); p.op[0].epi = EPI_STORE; p.op[0].out = d_y; p.op[0].scale = 1.f;
+        cudaMemcpyAsync(d_ph, &p, sizeof p, cudaMemcpyHostToDevice, E.stream);
+        DecodeParams P{}; P.phases = d_ph; P.n_phases = 1; P.n_embd = K; P.n_head = 1; P.n_head_kv = 1; P.head_dim = 128; P.n_vocab = (int)N; P.n_splits = 1;
+        P.cand_val = d_cv; P.cand_idx = d_ci; P.pos = d_st; P.token = d_st + 1; P.bar_ctr = (unsigned*)(d_st + 2); P.epoch = (unsigned*)(d_st + 3); P.out_tokens = d_ot;
+        P.logits = d_y; P.n_steps = 1;
+        // every step "forced" (token 0): no argmax traffic; forced[] = d_ot, zeroed, iters+1 ints
+        cudaMemsetAsync(d_ot, 0, ((size_t)iters + 1) * 4, E.stream);
+        DecodeRun R{}; R.forced = d_ot; R.n_forced = iters + 1;
+        rc = launch_decode(E, P, R, lc);                                   // warm-up + correctness
+        cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+        if (!rc) {
+            P.n_steps = iters;
+            cudaEventRecord(e0, E.stream);
+            rc = launch_decode(E, P, R, lc);
+            cudaEventRecord(e1, E.stream);
+        }
+        cudaError_t e = cudaMemcpyAsync(y, d_y, (size_t)N * 4, cudaMemcpyDeviceToHost, E.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(E.stream);
+        if (e != cudaSuccess && !rc) rc = fail(B200_ERR_CUDA, cudaGetErrorString(e));
+        float ms = 0; if (!rc) cudaEventElapsedTime(&ms, e0, e1);
+        if (ms_out) *ms_out = ms / iters;
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+    }
+    cleanup();
+    return rc;
+}
+
+int layout_selftest() {
+    const int types[] = {T_Q8_0, T_Q4_K, T_Q5_K, T_Q6_K};
+    for (int t : types) {
+        const int gb = group_bytes(t), be = block_elems(t), bb = block_bytes(t), blocks_per_group = GROUP_ELEMS / be;
+        for (int K : {256, 512, 2048, 4096, 14336 / 256 * 256}) {
+            const int ng = n_groups(K); const int64_t rrb = (int64_t)raw_row_bytes(t, K);
+            std::vector<int> hits((size_t)rrb, 0);
+            for (int g = 0; g < ng; g++)
+                for (int o = 0; o < gb; o++) {
+                    int64_t s = src_byte(t, K, g, o);
+                    if (s < 0) continue;
+                    if (s >= rrb) return fail(B200_ERR_INVALID, "layout selftest: src_byte out of range");
+                    hits[(size_t)s]++;
+                    int blk_global = (int)(s / bb), i = (int)(s % bb);
+                    if (blk_global / blocks_per_group != g) return fail(B200_ERR_INVALID, "layout selftest: group mismatch");
+                    if (dst_byte(t, blk_global % blocks_per_group, i) != o) return fail(B200_ERR_INVALID, "layout selftest: dst_byte is not the inverse of src_byte");
+                }
+            for (int h : hits) if (h != 1) return fail(B200_ERR_INVALID, "layout selftest: raw byte not covered exactly once");
+        }
+    }
+    return B200_OK;
+}
+
+}  // namespace b200

@@ -1,0 +1,101 @@
+// engine.hpp — host-side declarations shared by engine.cu, handlers.cpp and capi.cpp.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <condition_variable>
+#include <cstdint>
+#include <deque>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/b200_engine.h"
+#include "gguf.hpp"
+
+namespace b200 {
+
+struct DecodeParams;
+struct Phase;
+
+extern thread_local std::string g_last_error;
+int fail(int code, const std::string& msg);
+
+struct Matrix { uint8_t* w = nullptr; int type = 0; int64_t N = 0; int K = 0; };
+struct Layer { float* attn_norm = nullptr; float* ffn_norm = nullptr; Matrix wq, wk, wv, wo, wgu, wd; };
+
+struct Engine {
+    std::mutex mu;
+    bool ready = false;
+    int device = 0, max_ctx = 4096, max_seqs = 1, n_sm = 0, smem_per_sm = 0, smem_optin = 0;
+    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    uint64_t launches = 0;                       // kernels launched by this library (bench.py reports it)
+    int init(const b200_config* cfg);
+    int ensure();
+};
+Engine& engine();
+
+struct Model {
+    std::string id, arch;
+    GgufMeta meta;
+    int n_layer = 0, n_embd = 0, n_head = 0, n_head_kv = 0, head_dim = 0, n_ff = 0, n_vocab = 0, n_rot = 0, n_ctx_train = 0;
+    float rms_eps = 1e-5f, rope_base = 10000.f, emb_scale = 0, res_scale = 0, attn_scale = 0, logit_scale = 0;
+    int bos = -1, eos = -1;
+    std::vector<std::string> vocab; std::vector<int> tok_type;
+    // tokenizer tables
+    int byte_tok[256]; std::unordered_map<std::string, int> special; std::vector<std::string> piece;
+    // upload state
+    uint8_t* d_raw = nullptr; uint64_t uploaded = 0; bool committed = false;
+    uint64_t weight_bytes = 0, hbm_bytes = 0;
+    std::vector<void*> owned;
+    // weights
+    Matrix tok_embd, out_w; float* out_norm = nullptr; float* inv_freq = nullptr; std::vector<Layer> layers;
+    // runtime
+    Phase* d_phases = nullptr; int n_phases = 0;
+    float *d_h = nullptr, *d_q = nullptr, *d_act = nullptr, *d_logits = nullptr, *d_part_acc = nullptr, *d_part_ml = nullptr, *d_cand_val = nullptr;
+    int *d_cand_idx = nullptr, *d_state = nullptr, *d_out_tokens = nullptr, *d_forced = nullptr, *d_block_table = nullptr;
+    __half* d_kv = nullptr; int n_pages = 0, n_splits = 1;
+    int grid = 0, smem_max_grp = 0; uint32_t ring_bytes = 0; size_t smem_bytes = 0;
+    int cur_pos = 0;
+    std::mutex run_mu;
+
+    ~Model();
+    void release();
+    template <typename T> int own(T** p, size_t n);
+    int open(const std::string& id, const uint8_t* head, size_t n);
+    int upload(uint64_t file_off, const void* bytes, size_t n);
+    int commit();
+    int load_matrix(const std::string& name, int64_t N, int K, Matrix& out);
+    int load_vector(const std::string& name, int64_t n, float** out);
+    void fill_params(DecodeParams& P) const;
+    int run_steps(int n_steps, const int32_t* forced, int n_forced, bool reset, float* logits_all_dev);
+    int generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_sampling* s, int32_t* out, int* n_out, float* ttft_ms, float* decode_ms);
+    int eval(const int32_t* toks, int n, float* logits_all, float* logits_last);
+    double bytes_per_token(int ctx) const;
+    int bench_decode(int ctx_len, int n_steps, int warmup, float* ms_per_token, double* bytes);
+    // tokenizer (tokenizer.cpp)
+    void build_tokenizer();
+    std::vector<int32_t> tokenize(const std::string& text, bool parse_special) const;
+    std::string detokenize(const int32_t* toks, int n) const;
+    std::string info_json() const;
+};
+
+int sample_token(Engine& E, Model& m, const b200_sampling& s, uint64_t step);
+int kernel_dequantize(int type, const void* raw, int64_t n_rows, int K, float* out);
+int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, float* y, int iters, float* ms);
+int layout_selftest();
+
+// registry (handlers.cpp)
+struct Registry {
+    std::mutex mu;
+    std::map<std::string, std::shared_ptr<Model>> models;
+    std::string models_dir;
+};
+Registry& registry();
+std::string handle_subject(const std::string& subject, const std::string& payload);
+
+}  // namespace b200

@@ -1,0 +1,268 @@
+// handlers.cpp — C++ mirror of the reference's subject handlers and envelope
+// (/root/reference/nats_llm_studio.go:181-364): same payloads, same validation order, same error
+// strings, same {ok,error,data} bytes as Go's json.Marshal would produce.  The Go worker a
+// maintainer builds calls the same engine through cgo; this mirror exists
+// because no Go toolchain is present on the build/GPU image, and it is what tests/ and
+// bench.py's e2e leg drive.  Also: the byte-level tokenizer and the chat rendering.
+#include <algorithm>
+#include <atomic>
+#include <ctime>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <sys/stat.h>
+
+#include "engine.hpp"
+#include "json.hpp"
+
+namespace b200 {
+
+Registry& registry() { static Registry r; return r; }
+
+// ------------------------------------------------------------------------------------ tokenizer
+void Model::build_tokenizer() {
+    for (int i = 0; i < 256; i++) byte_tok[i] = -1;
+    piece.assign(vocab.size(), "");
+    for (size_t i = 0; i < vocab.size(); i++) {
+        const std::string& s = vocab[i]; int ty = i < tok_type.size() ? tok_type[i] : 1;
+        if (ty == 6 && s.size() == 6 && s.compare(0, 3, "<0x") == 0 && s[5] == '>') {      // BYTE
+            int b = (int)strtol(s.substr(3, 2).c_str(), nullptr, 16); byte_tok[b & 255] = (int)i; piece[i] = std::string(1, (char)b);
+        } else if (ty == 3 || ty == 4) { special[s] = (int)i; piece[i] = ""; }             // CONTROL / USER_DEFINED
+        else { std::string p = s; size_t k; while ((k = p.find("\xE2\x96\x81")) != std::string::npos) p.replace(k, 3, " "); piece[i] = p; }
+    }
+}
+
+std::vector<int32_t> Model::tokenize(const std::string& text, bool parse_special) const {
+    std::vector<int32_t> out;
+    size_t i = 0;
+    while (i < text.size()) {
+        if (parse_special && text[i] == '<') {
+            bool hit = false;
+            for (auto& kv : special) if (!kv.first.empty() && text.compare(i, kv.first.size(), kv.first) == 0) { out.push_back(kv.second); i += kv.first.size(); hit = true; break; }
+            if (hit) continue;
+        }
+        int t = byte_tok[(unsigned char)text[i]];
+        out.push_back(t >= 0 ? t : (int)((unsigned char)text[i]) % std::max(1, n_vocab));
+        i++;
+    }
+    return out;
+}
+
+std::string Model::detokenize(const int32_t* toks, int n) const {
+    std::string s;
+    for (int i = 0; i < n; i++) if (toks[i] >= 0 && (size_t)toks[i] < piece.size()) s += piece[toks[i]];
+    return s;
+}
+
+static std::string quant_name(int ftype) {
+    switch (ftype) { case 7: return "Q8_0"; case 14: return "Q4_K_S"; case 15: return "Q4_K_M"; case 16: return "Q5_K_S"; case 17: return "Q5_K_M"; case 18: return "Q6_K"; case 1: return "F16"; case 0: return "F32"; default: return "unknown"; }
+}
+static std::string publisher_of(const std::string& id) { size_t k = id.find('/'); return k == std::string::npos ? "local" : id.substr(0, k); }
+
+static Json model_entry(const Model& m) {
+    Json e = Json::object();
+    e.set("id", Json::string(m.id)).set("object", Json::string("model")).set("type", Json::string("llm"))
+        .set("publisher", Json::string(publisher_of(m.id))).set("arch", Json::string(m.arch)).set("compatibility_type", Json::string("gguf"))
+        .set("quantization", Json::string(quant_name((int)m.meta.num("general.file_type", -1)))).set("state", Json::string("loaded"))
+        .set("max_context_length", Json::integer(m.n_ctx_train));
+    return e;
+}
+std::string Model::info_json() const {
+    Json e = model_entry(*this);
+    e.set("n_layer", Json::integer(n_layer)).set("n_embd", Json::integer(n_embd)).set("n_head", Json::integer(n_head)).set("n_head_kv", Json::integer(n_head_kv))
+        .set("n_ff", Json::integer(n_ff)).set("n_vocab", Json::integer(n_vocab)).set("weight_bytes", Json::integer((long long)weight_bytes))
+        .set("hbm_bytes", Json::integer((long long)hbm_bytes)).set("grid", Json::integer(grid)).set("ring_bytes", Json::integer(ring_bytes))
+        .set("n_phases", Json::integer(n_phases)).set("n_splits", Json::integer(n_splits));
+    return json_dump(e);
+}
+
+// ------------------------------------------------------------------------------------ envelope (nats_llm_studio.go:186-226)
+// NATSResponse{OK bool `json:"ok"`; Error string `json:"error,omitempty"`; Data interface{} `json:"data,omitempty"`}
+static std::string envelope(bool ok, const std::string& error, const Json* data /* nullptr = nil interface (omitted) */) {
+    std::string out = ok ? "{\"ok\":true" : "{\"ok\":false";
+    if (!error.empty()) { out += ",\"error\":"; json_escape(error, out); }
+    if (data) { out += ",\"data\":"; json_write(*data, out); }
+    out.push_back('}');
+    return out;
+}
+// respondError(msg, err, nil): a typed-nil map inside the interface is NOT omitted -> "data":null
+static std::string respond_error_nil(const std::string& err) { Json n = Json::null(); return envelope(false, err, &n); }
+
+// Go-style decode of {"<field>": string} payloads (json.Unmarshal into a struct with one string field)
+static bool decode_string_field(const std::string& payload, const char* field, const char* go_struct, const char* go_type_for_value,
+                                std::string& value, std::string& err) {
+    Json doc; JsonParser ps(payload);
+    if (!ps.parse(doc)) { err = ps.err; return false; }
+    value.clear();
+    if (doc.kind == Json::Null) return true;
+    if (doc.kind != Json::Obj) { err = std::string("json: cannot unmarshal ") + doc.go_kind() + " into Go value of type " + go_type_for_value; return false; }
+    const Json* f = doc.get_fold(field);
+    if (!f || f->kind == Json::Null) return true;
+    if (f->kind != Json::Str) { err = std::string("json: cannot unmarshal ") + f->go_kind() + " into Go struct field " + go_struct + "." + field + " of type string"; return false; }
+    value = f->s; return true;
+}
+
+// ------------------------------------------------------------------------------------ list / pull / delete
+static std::string on_list_models() {                                   // onListModels :228-248
+    Json list = Json::array();
+    { Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); for (auto& kv : R.models) if (kv.second->committed) list.push(model_entry(*kv.second)); }
+    Json models = Json::object(); models.set("data", list).set("object", Json::string("list"));
+    Json data = Json::object(true); data.set("http_status", Json::integer(200)).set("models", models);
+    return envelope(true, "", &data);
+}
+
+static bool file_exists(const std::string& p) { struct stat st; return stat(p.c_str(), &st) == 0 && S_ISREG(st.st_mode); }
+
+int load_file_into(const std::string& id, const std::string& path, std::shared_ptr<Model>& out, std::string& log) {
+    auto t0 = std::chrono::steady_clock::now();
+    if (int rc0 = engine().ensure()) return rc0;                        // no GPU -> fail loudly, nothing else happens
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) return fail(B200_ERR_NOT_FOUND, "cannot open " + path);
+    auto m = std::make_shared<Model>();
+    const size_t CH = 32u << 20;
+    uint8_t* pin[2] = {(uint8_t*)b200_pinned_alloc(CH), (uint8_t*)b200_pinned_alloc(CH)};
+    if (!pin[0] || !pin[1]) { fclose(f); b200_pinned_free(pin[0]); b200_pinned_free(pin[1]); return fail(B200_ERR_NOMEM, "pinned staging allocation failed"); }
+    int rc = B200_OK; size_t got = fread(pin[0], 1, CH, f);
+    std::vector<uint8_t> head(pin[0], pin[0] + got);
+    for (;;) {                                                          // header may exceed one chunk (128k-token vocab ~ 5 MB: fits)
+        rc = m->open(id, head.data(), head.size());
+        if (rc != B200_ERR_MORE) break;
+        size_t more = fread(pin[1], 1, CH, f); if (!more) break;
+        head.insert(head.end(), pin[1], pin[1] + more);
+    }
+    if (rc == B200_OK) {
+        rc = m->upload(0, head.data(), head.size());
+        uint64_t off = head.size(); int k = 0;
+        while (rc == B200_OK) { size_t r = fread(pin[k], 1, CH, f); if (!r) break; rc = m->upload(off, pin[k], r); off += r; k ^= 1; }
+        if (rc == B200_OK) rc = m->commit();
+    }
+    fclose(f); b200_pinned_free(pin[0]); b200_pinned_free(pin[1]);
+    if (rc != B200_OK) return rc;
+    double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    char buf[256]; snprintf(buf, sizeof buf, "loaded %s: %zu tensors, %llu weight bytes resident in HBM, %.0f ms", id.c_str(), m->meta.tensors.size(), (unsigned long long)m->weight_bytes, ms);
+    log = buf;
+    { Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); R.models[id] = m; }
+    out = m;
+    return B200_OK;
+}
+
+static std::string on_pull_model(const std::string& payload) {          // OnPullModel :250-286
+    std::string id, err;
+    if (!decode_string_field(payload, "identifier", "PullModelRequest", "nats_llm_studio.PullModelRequest", id, err)) return respond_error_nil("invalid JSON in PullModel: " + err);
+    if (id.empty()) return respond_error_nil("'identifier' is required");
+    std::string dir; { Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); dir = R.models_dir; }
+    std::string path;
+    for (const std::string& c : {dir + "/" + id + ".gguf", dir + "/" + id, dir + "/" + id + "/model.gguf", id}) if (file_exists(c)) { path = c; break; }
+    Json data = Json::object(true); data.set("model", Json::string(id));
+    if (path.empty()) { data.set("output", Json::string("")); return envelope(false, "failed to pull model '" + id + "': no GGUF file under " + dir, &data); }
+    std::shared_ptr<Model> m; std::string log;
+    if (load_file_into(id, path, m, log) != B200_OK) { data.set("output", Json::string("")); return envelope(false, "failed to pull model '" + id + "': " + g_last_error, &data); }
+    data.set("output", Json::string(log));
+    return envelope(true, "", &data);
+}
+
+static std::string on_delete_model(const std::string& payload) {        // OnDeleteModel :288-324, DeleteModel :99-133
+    std::string id, err;
+    if (!decode_string_field(payload, "model_id", "DeleteModelRequest", "nats_llm_studio.DeleteModelRequest", id, err)) return respond_error_nil("invalid JSON in DeleteModel: " + err);
+    if (id.empty()) return respond_error_nil("'model_id' is required");
+    std::shared_ptr<Model> m;
+    { Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); auto it = R.models.find(id); if (it != R.models.end()) { m = it->second; R.models.erase(it); } }
+    const std::string where = "hbm://" + id;
+    Json data = Json::object(true); data.set("model_id", Json::string(id));
+    if (!m) { data.set("dir", Json::string(where)); return envelope(false, "model directory not found: " + where, &data); }
+    { std::lock_guard<std::mutex> lk(m->run_mu); m->release(); }
+    data.set("deleted_dir", Json::string(where));
+    return envelope(true, "", &data);
+}
+
+// ------------------------------------------------------------------------------------ chat
+static std::string render_prompt(const Model& m, const Json& messages, std::vector<int32_t>& toks) {
+    // fixed minimal template: <|role|>content<|end|> ... <|assistant|>
+    if (m.bos >= 0) toks.push_back(m.bos);
+    auto special_or_text = [&](const std::string& s) {
+        auto it = m.special.find(s);
+        if (it != m.special.end()) toks.push_back(it->second);
+        else { auto t = m.tokenize(s, false); toks.insert(toks.end(), t.begin(), t.end()); }
+    };
+    if (messages.kind != Json::Arr) return "'messages' must be an array";
+    for (const Json& msg : messages.arr) {
+        if (msg.kind != Json::Obj) return "each message must be an object";
+        const Json* role = msg.get("role"); const Json* content = msg.get("content");
+        if (!role || role->kind != Json::Str || !content || content->kind != Json::Str) return "each message needs string 'role' and 'content'";
+        special_or_text("<|" + role->s + "|>");
+        auto t = m.tokenize(content->s, false); toks.insert(toks.end(), t.begin(), t.end());
+        special_or_text("<|end|>");
+    }
+    special_or_text("<|assistant|>");
+    return "";
+}
+
+static Json lm_error(const std::string& message, const char* type, const char* param, const char* code) {
+    Json e = Json::object(); e.set("message", Json::string(message)).set("type", Json::string(type)).set("param", param ? Json::string(param) : Json::null()).set("code", code ? Json::string(code) : Json::null());
+    Json r = Json::object(); r.set("error", e); return r;
+}
+
+static std::string on_chat_model(const std::string& payload) {          // OnChatModel :327-364
+    if (payload.empty()) return respond_error_nil("payload vazio em ChatModel");
+    Json doc; JsonParser ps(payload);
+    if (!ps.parse(doc)) return respond_error_nil("invalid JSON in ChatModel: " + ps.err);
+    std::string model_id;
+    if (doc.kind == Json::Obj) {
+        const Json* f = doc.get_fold("model");
+        if (f && f->kind != Json::Null) { if (f->kind != Json::Str) return respond_error_nil(std::string("invalid JSON in ChatModel: json: cannot unmarshal ") + f->go_kind() + " into Go struct field .model of type string"); model_id = f->s; }
+    } else if (doc.kind != Json::Null) return respond_error_nil(std::string("invalid JSON in ChatModel: json: cannot unmarshal ") + doc.go_kind() + " into Go value of type struct { Model string \"json:\\\"model\\\"\" }");
+    if (model_id.empty()) return respond_error_nil("'model' is required in ChatModel");
+
+    auto reply = [&](int status, const Json& response) { Json data = Json::object(true); data.set("http_status", Json::integer(status)).set("response", response); return envelope(true, "", &data); };
+    std::shared_ptr<Model> m;
+    { Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); auto it = R.models.find(model_id); if (it != R.models.end() && it->second->committed) m = it->second; }
+    // the reference forwards whatever the backend answers and never inspects the status (:173-178, :356-363)
+    if (!m) return reply(404, lm_error("model '" + model_id + "' not found", "invalid_request_error", "model", "model_not_found"));
+    const Json* messages = doc.get("messages");
+    if (!messages) return reply(400, lm_error("'messages' field is required", "invalid_request_error", "messages", nullptr));
+    std::vector<int32_t> toks; std::string terr = render_prompt(*m, *messages, toks);
+    if (!terr.empty()) return reply(400, lm_error(terr, "invalid_request_error", "messages", nullptr));
+    auto numf = [&](const char* k, double d) { const Json* v = doc.get(k); return v && v->kind == Json::Num ? v->num : d; };
+    b200_sampling s{}; s.temperature = (float)numf("temperature", 0.8); s.top_k = (int)numf("top_k", 40); s.top_p = (float)numf("top_p", 0.95);
+    const Json* seed = doc.get("seed"); s.seed = seed && seed->kind == Json::Num ? (uint64_t)seed->num : (uint64_t)std::chrono::steady_clock::now().time_since_epoch().count();
+    int max_tokens = (int)numf("max_tokens", -1);
+    const int room = engine().max_ctx - (int)toks.size() - 1;
+    if (room < 1) return reply(400, lm_error("prompt of " + std::to_string(toks.size()) + " tokens exceeds the context window", "invalid_request_error", "messages", "context_length_exceeded"));
+    if (max_tokens <= 0 || max_tokens > room) max_tokens = std::min(room, max_tokens <= 0 ? 512 : max_tokens);
+    s.max_tokens = max_tokens; s.stop_token = -1; { auto it = m->special.find("<|end|>"); if (it != m->special.end()) s.stop_token = it->second; }
+    const Json* ign = doc.get("ignore_eos"); s.ignore_eos = ign && ign->kind == Json::Bool && ign->b;
+    std::vector<int32_t> out((size_t)max_tokens); int n_out = 0; float ttft = 0, dec = 0;
+    auto t0 = std::chrono::steady_clock::now();
+    if (m->generate(toks.data(), (int)toks.size(), max_tokens, &s, out.data(), &n_out, &ttft, &dec) != B200_OK)
+        return reply(500, lm_error(g_last_error, "internal_error", nullptr, nullptr));
+    double wall_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    bool stopped = n_out > 0 && !s.ignore_eos && (out[n_out - 1] == m->eos || out[n_out - 1] == s.stop_token);
+    int n_text = stopped ? n_out - 1 : n_out;
+    static std::atomic<uint64_t> counter{0};
+    char idbuf[64]; snprintf(idbuf, sizeof idbuf, "chatcmpl-%012llx", (unsigned long long)(++counter));
+    Json message = Json::object(); message.set("role", Json::string("assistant")).set("content", Json::string(m->detokenize(out.data(), n_text)));
+    Json choice = Json::object(); choice.set("index", Json::integer(0)).set("logprobs", Json::null()).set("finish_reason", Json::string(stopped ? "stop" : "length")).set("message", message);
+    Json choices = Json::array(); choices.push(choice);
+    Json usage = Json::object(); usage.set("prompt_tokens", Json::integer((long long)toks.size())).set("completion_tokens", Json::integer(n_out)).set("total_tokens", Json::integer((long long)toks.size() + n_out));
+    Json stats = Json::object();
+    stats.set("tokens_per_second", Json::number(n_out > 1 && dec > 0 ? (n_out - 1) / (dec * 1e-3) : 0.0)).set("time_to_first_token", Json::number(ttft * 1e-3))
+        .set("generation_time", Json::number(wall_s)).set("stop_reason", Json::string(stopped ? "eosFound" : "maxPredictedTokensReached"));
+    Json info = Json::object(); info.set("arch", Json::string(m->arch)).set("quant", Json::string(quant_name((int)m->meta.num("general.file_type", -1)))).set("format", Json::string("gguf")).set("context_length", Json::integer(engine().max_ctx));
+    Json fmts = Json::array(); fmts.push(Json::string("gguf"));
+    Json runtime = Json::object(); runtime.set("name", Json::string("b200-gguf-engine")).set("version", Json::string("0.1.0")).set("supported_formats", fmts);
+    Json resp = Json::object();
+    resp.set("id", Json::string(idbuf)).set("object", Json::string("chat.completion")).set("created", Json::integer((long long)time(nullptr))).set("model", Json::string(model_id))
+        .set("choices", choices).set("usage", usage).set("stats", stats).set("model_info", info).set("runtime", runtime);
+    return reply(200, resp);
+}
+
+std::string handle_subject(const std::string& subject, const std::string& payload) {
+    if (subject == "lmstudio.chat_model") return on_chat_model(payload);
+    if (subject == "lmstudio.list_models") return on_list_models();
+    if (subject == "lmstudio.pull_model") return on_pull_model(payload);
+    if (subject == "lmstudio.delete_model") return on_delete_model(payload);
+    return respond_error_nil("unknown subject " + subject);
+}
+
+}  // namespace b200

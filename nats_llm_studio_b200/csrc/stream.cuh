@@ -1,0 +1,412 @@
+// stream.cuh — the weight-streaming core of the batch-1 decode path (kernels K1, K3, K4, K6, K11 of
+// SURVEY.md §2.3 fused into one persistent kernel; replaces the arithmetic behind
+// /root/reference/nats_llm_studio.go:158-179, which the reference delegates to LM Studio).
+//
+// Design (B200-first, HBM-bound work):
+//   * one persistent cooperative grid, 2 CTAs per SM, 9 warps each: warp 8 is the PRODUCER, warps
+//     0..7 are CONSUMERS.
+//   * the producer walks the token's static weight schedule and pulls each CTA's slice of every
+//     matrix through a shared-memory byte ring with 1-D bulk-async copies (cp.async.bulk, the TMA
+//     engine; SASS UBLKCP) completing on mbarriers.  It never waits on data dependencies, only on
+//     ring space, so HBM keeps streaming across phase boundaries, grid barriers and prologues.
+//   * consumers quantise the activation vector once per phase into shared memory (int8 per
+//     256-block, the way ggml quantises activations before a quantised mat-vec), then each warp
+//     owns one ROW PAIR of a stage: every lane reads its 64 weights per row with conflict-free
+//     128-bit shared loads, unpacks nibbles with LOP3 and accumulates with dp4a (IDP.4A), integer
+//     per super-block, fp32 across super-blocks.
+//   * epilogues are fused: RoPE + KV-page write, residual add, SiLU*mul, logit scale + argmax.
+#pragma once
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include "quant.cuh"
+
+namespace b200 {
+
+constexpr int CONSUMER_WARPS = 8;
+constexpr int CONSUMER_THREADS = CONSUMER_WARPS * 32;
+constexpr int CTA_THREADS = CONSUMER_THREADS + 32;
+constexpr int PAIRS_PER_STAGE = CONSUMER_WARPS;
+constexpr int NSLOT = 8;                 // mbarrier pairs in flight
+constexpr int MAX_STAGE_BYTES = PAIRS_PER_STAGE * 2 * 2176;   // Q8_0 is the widest unit
+
+// ------------------------------------------------------------------------------------ PTX
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(CONSUMER_THREADS) : "memory"); }
+__device__ __forceinline__ int dp4a_ss(int a, int b, int c) { return __dp4a(a, b, c); }
+__device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {   // unsigned bytes x signed bytes
+    int d; asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d;
+}
+__device__ __forceinline__ uint32_t ld_acquire_u32(const unsigned* p) {
+    uint32_t v; asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v;
+}
+__device__ __forceinline__ void red_release_add(unsigned* p, unsigned v) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ------------------------------------------------------------------------------------ descriptors
+enum Epilogue : int { EPI_STORE = 0, EPI_ROPE_Q, EPI_ROPE_K, EPI_V, EPI_RESID, EPI_SWIGLU, EPI_LOGITS };
+enum Prologue : int { PRO_PLAIN = 0, PRO_NORM, PRO_ATTN };
+enum PhaseKind : int { PH_GEMV = 0, PH_ATTN, PH_EMBED };
+
+struct OpDesc {                 // one streamed matrix (engine layout, quant.cuh)
+    const uint8_t* w;
+    int type, n_pairs, n_grp, epi;
+    float* out;                 // EPI_STORE / RESID / SWIGLU / LOGITS / ROPE_Q destination
+    float scale;                // output scale (residual_scale, 1/logit_scale, 1)
+    int layer;                  // for KV epilogues
+};
+
+struct Phase {
+    int kind, n_ops, total_pairs, K;
+    int pro; int layer;
+    const float* src;           // prologue source vector (h, act) — fp32 [K]
+    const float* norm_w;        // PRO_NORM weight
+    OpDesc op[3];
+};
+
+struct KvLayout {               // paged KV cache, fp16
+    __half* pages;              // [n_pages][n_layer][2][n_head_kv][16][head_dim]
+    const int* block_table;     // [max_pages] for the sequence
+    int n_layer, n_head_kv, head_dim;
+    __device__ __forceinline__ size_t page_elems() const { return (size_t)n_layer * 2 * n_head_kv * 16 * head_dim; }
+    __device__ __forceinline__ __half* at(int layer, int kv, int kvh, int pos) const {
+        int page = block_table[pos >> 4];
+        return pages + (size_t)page * page_elems() + ((((size_t)layer * 2 + kv) * n_head_kv + kvh) * 16 + (pos & 15)) * head_dim;
+    }
+};
+
+struct DecodeParams {
+    const Phase* phases; int n_phases;
+    // model scalars
+    int n_embd, n_head, n_head_kv, head_dim, n_rot, n_vocab, n_splits;
+    float rms_eps, kq_scale, emb_scale;
+    const float* inv_freq;      // [n_rot/2] = base^(-2i/n_rot) / freq_factor_i
+    // embedding
+    const uint8_t* embd; int embd_type;   // engine layout
+    // buffers
+    float* h; float* q; float* act; float* logits;
+    float* part_acc; float* part_ml;      // attention partials [n_head][n_splits][head_dim], [..][2]
+    float* cand_val; int* cand_idx;       // per-CTA argmax candidates
+    KvLayout kv;
+    // run state (device memory)
+    int* pos; int* token; int* out_tokens; unsigned* bar_ctr; unsigned* epoch;
+    int n_steps; int want_argmax;
+};
+
+// ------------------------------------------------------------------------------------ smem carve-up
+struct Smem {
+    uint8_t* ring; uint32_t ring_bytes;
+    int8_t* xq; int16_t* xbs; float* xd;     // activation vector, engine-permuted
+    uint64_t* full; uint64_t* empty;
+    float* red;                               // 64 floats of reduction scratch
+    uint32_t* q_end;                          // producer's in-flight stage sizes [NSLOT]
+};
+__host__ __device__ inline size_t smem_x_bytes(int max_grp) { return (size_t)max_grp * (2048 + 256 + 32); }
+__host__ __device__ inline size_t smem_misc_bytes() { return NSLOT * 16 + 64 * 4 + NSLOT * 4 + 64; }
+__device__ inline Smem carve_smem(uint8_t* base, uint32_t ring_bytes, int max_grp) {
+    Smem s; s.ring = base; s.ring_bytes = ring_bytes; uint8_t* p = base + ring_bytes;
+    s.xq = (int8_t*)p; p += (size_t)max_grp * 2048;
+    s.xbs = (int16_t*)p; p += (size_t)max_grp * 256;
+    s.xd = (float*)p; p += (size_t)max_grp * 32;
+    s.full = (uint64_t*)p; p += NSLOT * 8; s.empty = (uint64_t*)p; p += NSLOT * 8;
+    s.red = (float*)p; p += 64 * 4; s.q_end = (uint32_t*)p;
+    return s;
+}
+
+// Deterministic ring allocator state; producer and consumers evolve identical copies.
+struct RingCursor {
+    uint32_t seq;        // stage sequence number
+    uint64_t head;       // virtual byte counter (includes wrap gaps)
+    __device__ __forceinline__ uint32_t place(uint32_t bytes, uint32_t ring_bytes, uint32_t& gap) {
+        uint32_t off = (uint32_t)(head % ring_bytes); gap = 0;
+        if (off + bytes > ring_bytes) { gap = ring_bytes - off; off = 0; }
+        head += gap + bytes; return off;
+    }
+};
+
+// slice of the phase's concatenated pair space owned by CTA c of G
+__device__ __forceinline__ void cta_slice(int total, int c, int G, int& lo, int& hi) {
+    lo = (int)((long long)total * c / G); hi = (int)((long long)total * (c + 1) / G);
+}
+
+// ------------------------------------------------------------------------------------ producer
+struct Producer {
+    RingCursor cur; uint64_t tail; uint32_t oldest;   // oldest unreleased stage seq
+    __device__ void init() { cur.seq = 0; cur.head = 0; tail = 0; oldest = 0; }
+
+    // called by the whole producer warp
+    __device__ void run_phase(const Phase& ph, const Smem& sm, int c, int G, int lane) {
+        int lo, hi; cta_slice(ph.total_pairs, c, G, lo, hi);
+        int off = 0;
+        for (int o = 0; o < ph.n_ops; o++) {
+            const OpDesc& op = ph.op[o];
+            int a = max(lo, off) - off, b = min(hi, off + op.n_pairs) - off; off += op.n_pairs;
+            if (a >= b) continue;
+            const uint32_t pu = 2u * group_bytes(op.type);
+            for (int rb = a; rb < b; rb += PAIRS_PER_STAGE) {
+                int np = min(PAIRS_PER_STAGE, b - rb);
+                for (int g = 0; g < op.n_grp; g++) {
+                    uint32_t bytes = np * pu, gap;
+                    uint32_t slot = cur.seq % NSLOT;
+                    // (1) barrier slot reuse: stage seq-NSLOT must be fully consumed
+                    while (cur.seq - oldest >= NSLOT) release_oldest(sm);
+                    // (2) ring space
+                    {   uint32_t o2 = (uint32_t)(cur.head % sm.ring_bytes); uint32_t gp = (o2 + bytes > sm.ring_bytes) ? sm.ring_bytes - o2 : 0;
+                        while (cur.head + gp + bytes - tail > sm.ring_bytes) release_oldest(sm); }
+                    uint32_t soff = cur.place(bytes, sm.ring_bytes, gap);
+                    __syncwarp();                 // every lane is done reading q_end[] of released stages
+                    if (lane == 0) { sm.q_end[slot] = gap + bytes; mbar_expect_tx(&sm.full[slot], bytes); }
+                    __syncwarp();
+                    if (lane < np) {
+                        const uint8_t* src = op.w + ((size_t)(rb + lane) * op.n_grp + g) * pu;
+                        bulk_g2s(sm.ring + soff + lane * pu, src, pu, &sm.full[slot]);
+                    }
+                    cur.seq++;
+                }
+            }
+        }
+    }
+    __device__ void release_oldest(const Smem& sm) {
+        uint32_t slot = oldest % NSLOT;
+        mbar_wait(&sm.empty[slot], (oldest / NSLOT) & 1);
+        tail += sm.q_end[slot]; oldest++;
+    }
+    // before the CTA exits every issued copy must have landed and been consumed
+    __device__ void drain(const Smem& sm) { while (oldest < cur.seq) release_oldest(sm); }
+};
+
+// ------------------------------------------------------------------------------------ activation prologue
+// Quantise 16 consecutive activations (one "run") and store them engine-permuted.
+// Scale rule (shared with oracle/oracle.c quantise_act_256): d = amax/127, q = rint(x * (127/amax)).
+__device__ __forceinline__ void store_run(const Smem& sm, int type, int u_global, const float v[16], float amax256) {
+    float d = amax256 / 127.0f, id = amax256 > 0.f ? 127.0f / amax256 : 0.f;
+    int grp = u_global / 128, u = u_global % 128, L, plane; act_slot(type, u, L, plane);
+    uint32_t w[4]; int bs = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        uint32_t pk = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            int q = __float2int_rn(v[4 * i + j] * id); q = max(-127, min(127, q)); bs += q;
+            pk |= (uint32_t)(q & 0xff) << (8 * j);
+        }
+        w[i] = pk;
+    }
+    *(uint4*)(sm.xq + (size_t)grp * 2048 + plane * 512 + L * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+    sm.xbs[grp * 128 + L * 4 + plane] = (int16_t)bs;
+    if ((u_global & 15) == 0) sm.xd[u_global / 16] = d;
+}
+
+__device__ __forceinline__ float half16_max(float a) {   // max over the aligned 16-lane group
+#pragma unroll
+    for (int o = 8; o; o >>= 1) a = fmaxf(a, __shfl_xor_sync(0xffffffffu, a, o));
+    return a;
+}
+
+constexpr int MAX_RUNS_PER_THREAD = 8;   // K <= 8*256*16 = 32768
+
+// Consumers only (tid 0..255).  `load(u, v)` fills v[16] with activations [16u, 16u+16) (already
+// normalised / combined); runs beyond K are zero padding.  type: weight type of the phase's ops.
+template <typename Load>
+__device__ __forceinline__ void prologue_quantise(const Smem& sm, int type, int K, int n_grp, int tid, Load load) {
+    const int n_runs = K / 16, n_runs_pad = n_grp * 128;
+    for (int u = tid; u < n_runs_pad; u += CONSUMER_THREADS) {
+        float v[16]; float amax = 0.f;
+        if (u < n_runs) {
+            load(u, v);
+#pragma unroll
+            for (int i = 0; i < 16; i++) amax = fmaxf(amax, fabsf(v[i]));
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; i++) v[i] = 0.f;
+        }
+        amax = half16_max(amax);
+        store_run(sm, type, u, v, amax);
+    }
+    consumer_sync();
+}
+
+// sum of squares of src[0..K) over the consumer threads -> rsqrt(mean + eps)
+__device__ __forceinline__ float rms_scale(const Smem& sm, const float* __restrict__ src, int K, float eps, int tid) {
+    float ss = 0.f;
+    for (int u = tid; u < K / 16; u += CONSUMER_THREADS) {
+        const float4* p = (const float4*)(src + 16 * u);
+#pragma unroll
+        for (int i = 0; i < 4; i++) { float4 t = __ldcg(p + i); ss += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w; }
+    }
+    ss = warp_sum(ss);
+    consumer_sync();                       // red[] free (previous readers done)
+    if ((tid & 31) == 0) sm.red[tid >> 5] = ss;
+    consumer_sync();
+    float tot = 0.f;
+#pragma unroll
+    for (int i = 0; i < CONSUMER_WARPS; i++) tot += sm.red[i];
+    return rsqrtf(tot / (float)K + eps);
+}
+
+__device__ __forceinline__ void load_run_f32(const float* __restrict__ src, int u, float v[16]) {
+    const float4* p = (const float4*)(src + 16 * u);
+#pragma unroll
+    for (int i = 0; i < 4; i++) { float4 t = __ldcg(p + i); v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w; }
+}
+
+// ------------------------------------------------------------------------------------ per-type lane kernels
+// Each computes, for lane L of the warp, the contribution of its 64 weights of ONE row's group to
+// that row's dot product, already multiplied by the activation block scale dx.
+struct XRegs { uint4 p[4]; int bs[4]; float dx; };
+
+__device__ __forceinline__ void load_x(const Smem& sm, int g, int lane, XRegs& x) {
+    const int8_t* xb = sm.xq + (size_t)g * 2048 + lane * 16;
+#pragma unroll
+    for (int i = 0; i < 4; i++) x.p[i] = *(const uint4*)(xb + i * 512);
+    uint2 b = *(const uint2*)(sm.xbs + g * 128 + lane * 4);
+    x.bs[0] = (int)(int16_t)(b.x & 0xffff); x.bs[1] = (int)(int16_t)(b.x >> 16);
+    x.bs[2] = (int)(int16_t)(b.y & 0xffff); x.bs[3] = (int)(int16_t)(b.y >> 16);
+    x.dx = sm.xd[g * 8 + lane / 4];
+}
+__device__ __forceinline__ uint32_t u4_get(const uint4& v, int i) { return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w; }
+
+__device__ __forceinline__ float lane_dot_q4k(const uint8_t* grp, int lane, const XRegs& x) {
+    const uint8_t* blk = grp + (lane >> 2) * 144; const int j = lane & 3;
+    const uint4 hdr = *(const uint4*)blk;                       // d, dmin, scales[12]
+    const uint4 qa = *(const uint4*)(blk + 16 + 32 * j), qb = *(const uint4*)(blk + 32 + 32 * j);
+    int s0 = 0, s1 = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        uint32_t w = u4_get(qa, i);
+        s0 = dp4a_ss((int)(w & 0x0F0F0F0Fu), (int)u4_get(x.p[0], i), s0);
+        s1 = dp4a_us(w & 0xF0F0F0F0u, (int)u4_get(x.p[2], i), s1);
+        w = u4_get(qb, i);
+        s0 = dp4a_ss((int)(w & 0x0F0F0F0Fu), (int)u4_get(x.p[1], i), s0);
+        s1 = dp4a_us(w & 0xF0F0F0F0u, (int)u4_get(x.p[3], i), s1);
+    }
+    s1 >>= 4;                                                  // exact: every term is a multiple of 16
+    // 6-bit scale / min unpack for sub-blocks 2j, 2j+1 (gguf/quants.py:480-503)
+    const uint32_t w0 = hdr.y, w1 = hdr.z, w2 = hdr.w;
+    int sc0, sc1, m0, m1;
+    if (j < 2) {
+        const int sh = 16 * j;
+        sc0 = (w0 >> sh) & 63; sc1 = (w0 >> (sh + 8)) & 63; m0 = (w1 >> sh) & 63; m1 = (w1 >> (sh + 8)) & 63;
+    } else {
+        const int sh = 16 * (j - 2);
+        sc0 = ((w2 >> sh) & 0xF) | (((w0 >> (sh + 6)) & 3) << 4);
+        sc1 = ((w2 >> (sh + 8)) & 0xF) | (((w0 >> (sh + 14)) & 3) << 4);
+        m0 = ((w2 >> (sh + 4)) & 0xF) | (((w1 >> (sh + 6)) & 3) << 4);
+        m1 = ((w2 >> (sh + 12)) & 0xF) | (((w1 >> (sh + 14)) & 3) << 4);
+    }
+    const int isum = sc0 * s0 + sc1 * s1;
+    const int msum = m0 * (x.bs[0] + x.bs[1]) + m1 * (x.bs[2] + x.bs[3]);
+    const float2 dd = __half22float2(*(const __half2*)&hdr.x);
+    return x.dx * (dd.x * (float)isum - dd.y * (float)msum);
+}
+
+__device__ __forceinline__ float lane_dot_q5k(const uint8_t* grp, int lane, const XRegs& x) {
+    const uint8_t* blk = grp + (lane >> 2) * 176; const int j = lane & 3;
+    const uint4 hdr = *(const uint4*)blk;
+    const uint4 ha = *(const uint4*)(blk + 16), hb = *(const uint4*)(blk + 32);     // qh[0..31]
+    const uint4 qa = *(const uint4*)(blk + 48 + 32 * j), qb = *(const uint4*)(blk + 64 + 32 * j);
+    int s0 = 0, s1 = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        uint32_t w = u4_get(qa, i), h = u4_get(ha, i) >> (2 * j);
+        s0 = dp4a_ss((int)((w & 0x0F0F0F0Fu) | ((h & 0x01010101u) << 4)), (int)u4_get(x.p[0], i), s0);
+        s1 = dp4a_ss((int)(((w >> 4) & 0x0F0F0F0Fu) | ((h & 0x02020202u) << 3)), (int)u4_get(x.p[2], i), s1);
+        w = u4_get(qb, i); h = u4_get(hb, i) >> (2 * j);
+        s0 = dp4a_ss((int)((w & 0x0F0F0F0Fu) | ((h & 0x01010101u) << 4)), (int)u4_get(x.p[1], i), s0);
+        s1 = dp4a_ss((int)(((w >> 4) & 0x0F0F0F0Fu) | ((h & 0x02020202u) << 3)), (int)u4_get(x.p[3], i), s1);
+    }
+    const uint32_t w0 = hdr.y, w1 = hdr.z, w2 = hdr.w;
+    int sc0, sc1, m0, m1;
+    if (j < 2) {
+        const int sh = 16 * j;
+        sc0 = (w0 >> sh) & 63; sc1 = (w0 >> (sh + 8)) & 63; m0 = (w1 >> sh) & 63; m1 = (w1 >> (sh + 8)) & 63;
+    } else {
+        const int sh = 16 * (j - 2);
+        sc0 = ((w2 >> sh) & 0xF) | (((w0 >> (sh + 6)) & 3) << 4);
+        sc1 = ((w2 >> (sh + 8)) & 0xF) | (((w0 >> (sh + 14)) & 3) << 4);
+        m0 = ((w2 >> (sh + 4)) & 0xF) | (((w1 >> (sh + 6)) & 3) << 4);
+        m1 = ((w2 >> (sh + 12)) & 0xF) | (((w1 >> (sh + 14)) & 3) << 4);
+    }
+    const int isum = sc0 * s0 + sc1 * s1;
+    const int msum = m0 * (x.bs[0] + x.bs[1]) + m1 * (x.bs[2] + x.bs[3]);
+    const float2 dd = __half22float2(*(const __half2*)&hdr.x);
+    return x.dx * (dd.x * (float)isum - dd.y * (float)msum);
+}
+
+__device__ __forceinline__ float lane_dot_q6k(const uint8_t* grp, int lane, const XRegs& x) {
+    const uint4 A = *(const uint4*)(grp + lane * 16), B = *(const uint4*)(grp + 512 + lane * 16), H = *(const uint4*)(grp + 1024 + lane * 16);
+    const uint32_t sc4 = *(const uint32_t*)(grp + 1536 + lane * 4);
+    const float d = __half2float(*(const __half*)(grp + 1664 + (lane >> 2) * 2));
+    int s[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const uint32_t a = u4_get(A, i), b = u4_get(B, i), h = u4_get(H, i);
+        s[0] = dp4a_ss((int)((a & 0x0F0F0F0Fu) | ((h << 4) & 0x30303030u)), (int)u4_get(x.p[0], i), s[0]);
+        s[1] = dp4a_ss((int)((b & 0x0F0F0F0Fu) | ((h << 2) & 0x30303030u)), (int)u4_get(x.p[1], i), s[1]);
+        s[2] = dp4a_ss((int)(((a >> 4) & 0x0F0F0F0Fu) | (h & 0x30303030u)), (int)u4_get(x.p[2], i), s[2]);
+        s[3] = dp4a_ss((int)(((b >> 4) & 0x0F0F0F0Fu) | ((h >> 2) & 0x30303030u)), (int)u4_get(x.p[3], i), s[3]);
+    }
+    int tot = 0;
+#pragma unroll
+    for (int g = 0; g < 4; g++) tot += (int)(int8_t)(sc4 >> (8 * g)) * (s[g] - 32 * x.bs[g]);
+    return x.dx * d * (float)tot;
+}
+
+__device__ __forceinline__ float lane_dot_q80(const uint8_t* grp, int lane, const XRegs& x) {
+    int s0 = 0, s1 = 0;
+#pragma unroll
+    for (int p = 0; p < 4; p++) {
+        const uint4 w = *(const uint4*)(grp + p * 512 + lane * 16);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if (p < 2) s0 = dp4a_ss((int)u4_get(w, i), (int)u4_get(x.p[p], i), s0);
+            else s1 = dp4a_ss((int)u4_get(w, i), (int)u4_get(x.p[p], i), s1);
+        }
+    }
+    const float2 dd = __half22float2(*(const __half2*)(grp + 2048 + lane * 4));
+    return x.dx * (dd.x * (float)s0 + dd.y * (float)s1);
+}
+
+__device__ __forceinline__ float lane_dot(int type, const uint8_t* grp, int lane, const XRegs& x) {
+    switch (type) {
+        case T_Q4_K: return lane_dot_q4k(grp, lane, x);
+        case T_Q6_K: return lane_dot_q6k(grp, lane, x);
+        case T_Q8_0: return lane_dot_q80(grp, lane, x);
+        default: return lane_dot_q5k(grp, lane, x);
+    }
+}
+
+}  // namespace b200

@@ -1,0 +1,196 @@
+"""ctypes binding of include/b200_engine.h (mirrors the cgo binding shown in INTEGRATION.md)."""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(HERE, "libb200engine.so")
+GGML_TYPES = {"F32": 0, "F16": 1, "Q8_0": 8, "Q4_K": 12, "Q5_K": 13, "Q6_K": 14}
+SUBJECTS = ("lmstudio.list_models", "lmstudio.pull_model", "lmstudio.delete_model", "lmstudio.chat_model")
+
+_lib = None
+
+
+class EngineError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"b200 engine error {code}: {msg}")
+        self.code = code
+        self.msg = msg
+
+
+class Config(C.Structure):
+    _fields_ = [("device", C.c_int), ("max_ctx", C.c_int), ("max_seqs", C.c_int), ("flags", C.c_uint32)]
+
+
+class Sampling(C.Structure):
+    _fields_ = [("temperature", C.c_float), ("top_k", C.c_int), ("top_p", C.c_float), ("seed", C.c_uint64),
+                ("max_tokens", C.c_int), ("stop_token", C.c_int), ("ignore_eos", C.c_int)]
+
+
+class Event(C.Structure):
+    _fields_ = [("req_id", C.c_uint64), ("kind", C.c_int), ("token", C.c_int), ("finish_reason", C.c_int),
+                ("n_prompt", C.c_int), ("n_generated", C.c_int), ("ttft_ms", C.c_float), ("decode_ms", C.c_float)]
+
+
+# every symbol include/b200_engine.h declares: name -> (restype, argtypes)
+vp, ci, sz = C.c_void_p, C.c_int, C.c_size_t
+SYMBOLS = {
+    "b200_init": (ci, [C.POINTER(Config)]), "b200_shutdown": (ci, []), "b200_last_error": (C.c_char_p, []),
+    "b200_pinned_alloc": (vp, [sz]), "b200_pinned_free": (None, [vp]),
+    "b200_model_open": (ci, [C.c_char_p, vp, sz, C.POINTER(vp)]), "b200_model_upload": (ci, [vp, C.c_uint64, vp, sz]),
+    "b200_model_commit": (ci, [vp]), "b200_model_close": (ci, [vp]),
+    "b200_model_load_file": (ci, [C.c_char_p, C.c_char_p, C.POINTER(vp)]), "b200_model_find": (ci, [C.c_char_p, C.POINTER(vp)]),
+    "b200_model_list": (ci, [vp, sz, C.POINTER(sz)]), "b200_model_info": (ci, [vp, vp, sz, C.POINTER(sz)]),
+    "b200_submit": (ci, [vp, vp, ci, C.POINTER(Sampling), C.c_uint64]), "b200_poll": (ci, [C.POINTER(Event), ci, ci]),
+    "b200_cancel": (ci, [C.c_uint64]),
+    "b200_model_generate": (ci, [vp, vp, ci, ci, C.POINTER(Sampling), vp, C.POINTER(ci), C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "b200_model_eval": (ci, [vp, vp, ci, vp, vp]), "b200_model_n_vocab": (ci, [vp]),
+    "b200_tokenize": (ci, [vp, C.c_char_p, sz, vp, ci, C.POINTER(ci)]), "b200_detokenize": (ci, [vp, vp, ci, vp, sz, C.POINTER(sz)]),
+    "b200_handle": (ci, [C.c_char_p, vp, sz, vp, sz, C.POINTER(sz)]), "b200_set_models_dir": (ci, [C.c_char_p]),
+    "b200_dequantize": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_gemv": (ci, [ci, vp, C.c_int64, ci, vp, vp, ci, C.POINTER(C.c_float)]),
+    "b200_bench_decode": (ci, [vp, ci, ci, ci, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
+    "b200_launch_count": (C.c_uint64, []), "b200_layout_selftest": (ci, []),
+}
+
+
+def lib():
+    """Loads libb200engine.so (building it if the sources are newer).  No fallback of any kind."""
+    global _lib
+    if _lib is None:
+        from . import build as _build
+        if _build.needs_build():
+            _build.build()
+        L = C.CDLL(SO_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            f = getattr(L, name)          # AttributeError if the library does not export a declared symbol
+            f.restype = res; f.argtypes = args
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc < 0:
+        raise EngineError(rc, lib().b200_last_error().decode("utf-8", "replace"))
+    return rc
+
+
+def _string_call(fn, *args):
+    need = sz(0)
+    _check(fn(*args, None, 0, C.byref(need)))
+    buf = C.create_string_buffer(need.value + 1)
+    _check(fn(*args, buf, need.value + 1, C.byref(need)))
+    return buf.raw[:need.value]
+
+
+class Model:
+    def __init__(self, handle, engine):
+        self.h = handle
+        self.engine = engine
+        self.n_vocab = lib().b200_model_n_vocab(handle)
+
+    def info(self):
+        return json.loads(_string_call(lib().b200_model_info, self.h))
+
+    def close(self):
+        if self.h:
+            _check(lib().b200_model_close(self.h)); self.h = None
+
+    def eval(self, toks, all_logits=True):
+        toks = np.ascontiguousarray(toks, dtype=np.int32)
+        if all_logits:
+            out = np.empty((len(toks), self.n_vocab), dtype=np.float32)
+            _check(lib().b200_model_eval(self.h, toks.ctypes.data, len(toks), out.ctypes.data, None))
+        else:
+            out = np.empty(self.n_vocab, dtype=np.float32)
+            _check(lib().b200_model_eval(self.h, toks.ctypes.data, len(toks), None, out.ctypes.data))
+        return out
+
+    def generate(self, prompt, n_gen, temperature=0.0, top_k=0, top_p=1.0, seed=0, ignore_eos=True, stop_token=-1):
+        prompt = np.ascontiguousarray(prompt, dtype=np.int32)
+        out = np.empty(n_gen, dtype=np.int32)
+        s = Sampling(temperature, top_k, top_p, seed, n_gen, stop_token, int(ignore_eos))
+        n_out, ttft, dec = ci(0), C.c_float(0), C.c_float(0)
+        _check(lib().b200_model_generate(self.h, prompt.ctypes.data, len(prompt), n_gen, C.byref(s), out.ctypes.data,
+                                         C.byref(n_out), C.byref(ttft), C.byref(dec)))
+        return out[:n_out.value], ttft.value, dec.value
+
+    def bench_decode(self, ctx_len, n_steps, warmup):
+        ms, by = C.c_float(0), C.c_double(0)
+        _check(lib().b200_bench_decode(self.h, ctx_len, n_steps, warmup, C.byref(ms), C.byref(by)))
+        return ms.value, by.value
+
+    def tokenize(self, text):
+        b = text.encode("utf-8") if isinstance(text, str) else text
+        n = ci(0)
+        _check(lib().b200_tokenize(self.h, b, len(b), None, 0, C.byref(n)))
+        out = np.empty(max(n.value, 1), dtype=np.int32)
+        _check(lib().b200_tokenize(self.h, b, len(b), out.ctypes.data, n.value, C.byref(n)))
+        return out[:n.value]
+
+    def detokenize(self, toks):
+        toks = np.ascontiguousarray(toks, dtype=np.int32)
+        return _string_call(lambda *a: lib().b200_detokenize(self.h, toks.ctypes.data, len(toks), *a))
+
+
+class Engine:
+    """Process-wide engine (one per GPU process)."""
+
+    def __init__(self, device=0, max_ctx=4096, max_seqs=1):
+        cfg = Config(device, max_ctx, max_seqs, 0)
+        _check(lib().b200_init(C.byref(cfg)))
+
+    def load_file(self, model_id, path):
+        h = vp()
+        _check(lib().b200_model_load_file(model_id.encode(), path.encode(), C.byref(h)))
+        return Model(h, self)
+
+    def load_bytes(self, model_id, data, chunk=1 << 20):
+        """open + chunked upload + commit: the path a JetStream Object Store reader drives."""
+        h = vp()
+        n = min(len(data), 1 << 16)
+        while True:
+            rc = lib().b200_model_open(model_id.encode(), data[:n], n, C.byref(h))
+            if rc == -6 and n < len(data):
+                n = min(len(data), n * 4); continue
+            _check(rc); break
+        for off in range(0, len(data), chunk):
+            part = data[off:off + chunk]
+            _check(lib().b200_model_upload(h, off, part, len(part)))
+        _check(lib().b200_model_commit(h))
+        return Model(h, self)
+
+    def handle(self, subject, payload=b""):
+        if isinstance(payload, str):
+            payload = payload.encode()
+        return _string_call(lambda *a: lib().b200_handle(subject.encode(), payload, len(payload), *a))
+
+    def set_models_dir(self, d):
+        _check(lib().b200_set_models_dir(d.encode()))
+
+    def list_models(self):
+        return json.loads(_string_call(lib().b200_model_list))
+
+    @staticmethod
+    def dequantize(type_name, raw, n_rows, K):
+        raw = np.ascontiguousarray(raw, dtype=np.uint8)
+        out = np.empty((n_rows, K), dtype=np.float32)
+        _check(lib().b200_dequantize(GGML_TYPES[type_name], raw.ctypes.data, n_rows, K, out.ctypes.data))
+        return out
+
+    @staticmethod
+    def gemv(type_name, raw, N, K, x, iters=1):
+        raw = np.ascontiguousarray(raw, dtype=np.uint8)
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        y = np.empty(N, dtype=np.float32)
+        ms = C.c_float(0)
+        _check(lib().b200_gemv(GGML_TYPES[type_name], raw.ctypes.data, N, K, x.ctypes.data, y.ctypes.data, iters, C.byref(ms)))
+        return y, ms.value
+
+    @staticmethod
+    def launch_count():
+        return int(lib().b200_launch_count())
+
+    def shutdown(self):
+        lib().b200_shutdown()

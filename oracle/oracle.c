@@ -476,3 +476,12 @@ int orc_generate(orc_model *m, const int32_t *prompt, int n_prompt, int n_gen, i
     }
     free(lg); return 0;
 }
+
+/* Stand-alone mat-vec on raw ggml blocks: y[N] = W[N x K] . x[K]; act_quant as in orc_set_act_quant. */
+int orc_matvec(int type, const void *raw, int N, int K, const float *x, float *y, int act_quant) {
+    if (!type_block_elems(type) || K % type_block_elems(type)) return -1;
+    orc_model m; memset(&m, 0, sizeof m); m.act_quant = act_quant;
+    orc_tensor w; memset(&w, 0, sizeof w); w.type = type; w.data = (const uint8_t *)raw;
+    matvec(&m, &w, x, y, N, K);
+    return 0;
+}

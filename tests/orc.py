@@ -93,3 +93,13 @@ class Model:
         out = np.empty(n, dtype=np.float32)
         lib().orc_tensor_f32(self.h, name.encode(), out.ctypes.data, n)
         return out
+
+
+def matvec(type_name, raw, N, K, x, act_quant=0):
+    L = lib()
+    L.orc_matvec.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+    raw = np.ascontiguousarray(raw, dtype=np.uint8); x = np.ascontiguousarray(x, dtype=np.float32)
+    y = np.empty(N, dtype=np.float32)
+    if L.orc_matvec(GGML[type_name], raw.ctypes.data, N, K, x.ctypes.data, y.ctypes.data, act_quant):
+        raise ValueError("orc_matvec failed")
+    return y
