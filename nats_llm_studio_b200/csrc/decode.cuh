@@ -14,7 +14,7 @@ __device__ __forceinline__ void grid_barrier(unsigned* ctr, unsigned& target, in
         target += (unsigned)G;
         __threadfence();
         red_release_add(ctr, 1u);
-        while ((int)(ld_acquire_u32(ctr) - target) < 0) { __nanosleep(20); }
+        while ((int)(ld_acquire_u32(ctr) - target) < 0) { }
         __threadfence();
     }
     consumer_sync();
@@ -120,7 +120,7 @@ __device__ __forceinline__ void epilogue(const DecodeParams& P, const OpDesc& op
 
 // ------------------------------------------------------------------------------------ one GEMV phase (consumers)
 __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem& sm, RingCursor& cur, int c, int G,
-                              int pos, int tid, ArgBest& best, float* logits_dst) {
+                              int pos, int tid, ArgBest& best, float* logits_dst, long long* tr) {
     const int warp = tid >> 5, lane = tid & 31;
     // ---- activation prologue: build the int8 vector(s) in shared memory
     bool fam_std = false, fam_q6 = false;
@@ -166,6 +166,7 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
         prologue_quantise(sm, fam_q6 ? T_Q6_K : T_Q4_K, ph.K, n_grp, tid, loader);
     }
 
+    if (tr && tid == 0) tr[1] = clock64();
     // ---- stream the CTA's slice
     int lo, hi; cta_slice(ph.total_pairs, c, G, lo, hi);
     int off = 0;
@@ -244,6 +245,9 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
         ArgBest best; best.v = -INFINITY; best.i = 0x7fffffff;
         for (int i = 0; i < P.n_phases; i++) {
             const Phase& ph = P.phases[i];
+            long long* tr = nullptr;
+            if (P.trace) { const int slot = c == 0 ? 0 : c == 1 ? 1 : c == G / 2 ? 2 : c == G - 1 ? 3 : -1; if (slot >= 0) tr = P.trace + (((size_t)step * P.n_phases + i) * 4 + slot) * 4; }
+            if (tr && tid == 0) tr[0] = tr[1] = clock64();
             if (ph.kind == PH_EMBED) {
                 const int ng = n_groups(P.n_embd);
                 for (int e = c * CONSUMER_THREADS + tid; e < P.n_embd; e += G * CONSUMER_THREADS) {
@@ -257,7 +261,7 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
                 }
             } else {
                 if (ph.op[0].epi == EPI_LOGITS && !need_lm) continue;
-                consume_phase(P, ph, sm, cur, c, G, pos, tid, best, logits_dst);
+                consume_phase(P, ph, sm, cur, c, G, pos, tid, best, logits_dst, tr);
                 if (ph.op[0].epi == EPI_LOGITS) {          // publish this CTA's argmax candidate
                     consumer_sync();
                     if (lane == 0) { sm.red[2 * warp] = best.v; sm.red[2 * warp + 1] = __int_as_float(best.i); }
@@ -272,7 +276,9 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
                     }
                 }
             }
+            if (tr && tid == 0) tr[2] = clock64();
             grid_barrier(P.bar_ctr, target, tid, G);
+            if (tr && tid == 0) tr[3] = clock64();
         }
         // ---- next token: forced, or argmax over the per-CTA candidates (every CTA redundantly)
         int next;

@@ -281,7 +281,7 @@ void Model::fill_params(DecodeParams& P) const {
     P.cand_val = d_cand_val; P.cand_idx = d_cand_idx;
     P.kv.pages = d_kv; P.kv.block_table = d_block_table; P.kv.n_layer = n_layer; P.kv.n_head_kv = n_head_kv; P.kv.head_dim = head_dim;
     P.pos = d_state + 0; P.token = d_state + 1; P.bar_ctr = (unsigned*)(d_state + 2); P.epoch = (unsigned*)(d_state + 3);
-    P.out_tokens = d_out_tokens; P.n_steps = 1; P.want_argmax = 1;
+    P.out_tokens = d_out_tokens; P.n_steps = 1; P.want_argmax = 1; P.trace = d_trace;
 }
 
 // Runs `n_steps` decode steps.  forced (host, n_forced ints) are fed first.  reset: start at position 0.
@@ -386,10 +386,18 @@ int Model::bench_decode(int ctx_len, int n_steps, int warmup, float* ms_per_toke
     if (warmup > 0) { if (int rc = run_steps(warmup, nullptr, 0, false, nullptr)) return rc; }
     CK(cudaMemcpyAsync(d_state, st, 8, cudaMemcpyHostToDevice, E.stream)); cur_pos = ctx_len;
     cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    const char* trace_path = getenv("B200_TRACE");                 // debug: per-phase clock64 stamps of 4 CTAs
+    size_t trace_n = (size_t)n_steps * n_phases * 16;
+    if (trace_path) { CK(cudaMalloc((void**)&d_trace, trace_n * 8)); CK(cudaMemsetAsync(d_trace, 0, trace_n * 8, E.stream)); }
     CK(cudaEventRecord(e0, E.stream));
     int rc = run_steps(n_steps, nullptr, 0, false, nullptr);
     CK(cudaEventRecord(e1, E.stream)); CK(cudaEventSynchronize(e1));
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1); cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (trace_path) {
+        std::vector<long long> tr(trace_n); cudaMemcpy(tr.data(), d_trace, trace_n * 8, cudaMemcpyDeviceToHost);
+        if (FILE* f = fopen(trace_path, "wb")) { int hdr[2] = {n_steps, n_phases}; fwrite(hdr, 4, 2, f); fwrite(tr.data(), 8, trace_n, f); fclose(f); }
+        cudaFree(d_trace); d_trace = nullptr;
+    }
     if (ms_per_token) *ms_per_token = ms / n_steps;
     if (bytes) { double b = 0; for (int i = 0; i < n_steps; i++) b += bytes_per_token(ctx_len + i + 1); *bytes = b / n_steps; }
     return rc;

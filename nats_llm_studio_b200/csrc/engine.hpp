@@ -61,6 +61,7 @@ struct Model {
     __half* d_kv = nullptr; int n_pages = 0, n_splits = 1;
     int grid = 0, smem_max_grp = 0; uint32_t ring_bytes = 0; size_t smem_bytes = 0;
     int cur_pos = 0;
+    long long* d_trace = nullptr;
     std::mutex run_mu;
 
     ~Model();

@@ -124,6 +124,7 @@ struct DecodeParams {
     // run state (device memory)
     int* pos; int* token; int* out_tokens; unsigned* bar_ctr; unsigned* epoch;
     int n_steps; int want_argmax;
+    long long* trace;           // optional [n_steps][n_phases][4 sampled CTAs][4] clock64 stamps (debug)
 };
 
 // ------------------------------------------------------------------------------------ smem carve-up
