@@ -38,6 +38,7 @@ struct Scheduler {
             cv_ev.notify_all();
         }
     }
+    ~Scheduler() { shutdown(); }
     void shutdown() { { std::lock_guard<std::mutex> lk(mu); stop = true; } cv_req.notify_all(); if (th.joinable()) th.join(); started = false; stop = false; }
 };
 static Scheduler& sched() { static Scheduler s; return s; }

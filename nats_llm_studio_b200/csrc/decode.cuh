@@ -1,23 +1,70 @@
 // decode.cuh — the persistent batch-1 decode kernel: embedding gather (K11), RMSNorm (K3), fused
-// QKV GEMV + RoPE + KV-page write (K1/K4), split-K paged-KV attention (K5), wo + residual, fused
-// gate/up GEMV + SiLU*mul (K6), down + residual, lm_head + argmax (K8 greedy).  One launch decodes
-// n_steps tokens (forced tokens first = sequential prefill, then greedy).  Phases are separated by
-// a grid barrier; the weight stream (stream.cuh Producer) is not.
+// QKV GEMV + RoPE + KV-page write (K1/K4), paged-KV attention (K5), wo + residual, fused gate/up
+// GEMV + SiLU*mul (K6), down + residual, lm_head + argmax (K8 greedy).  One launch decodes n_steps
+// tokens (forced tokens first = sequential prefill, then greedy).
+//
+// Synchronisation: there is NO grid barrier.  Every vector that crosses CTAs (hidden state, q,
+// current K/V, attention output, SwiGLU activations, argmax candidates) is published as
+// self-validating words — value and a generation tag in one atomic 4- or 8-byte store — and the
+// consuming prologue polls the words it needs until their tags match ("LL" protocol).  A phase
+// boundary therefore costs one store->load visibility latency instead of fence + atomic + spin +
+// load, which matters because under a saturated weight stream every L2 round trip queues behind
+// megabytes of bulk traffic (measured: ~4 us per round trip with a 27 MB backlog).
+// Buffer-reuse safety (single buffers suffice) is argued in DESIGN.md §3.1.
 #pragma once
 #include "stream.cuh"
 
 namespace b200 {
 
-__device__ __forceinline__ void grid_barrier(unsigned* ctr, unsigned& target, int tid, int G) {
-    consumer_sync();
-    if (tid == 0) {
-        target += (unsigned)G;
-        __threadfence();
-        red_release_add(ctr, 1u);
-        while ((int)(ld_acquire_u32(ctr) - target) < 0) { }
-        __threadfence();
+__device__ __forceinline__ long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return (long long)t; }
+
+// ------------------------------------------------------------------------------------ tagged words
+__device__ __forceinline__ uint32_t tag16_of(uint32_t seq) { return seq % 65535u + 1u; }            // never 0
+__device__ __forceinline__ uint32_t ll16_pack(float v, uint32_t tag16) {
+    v = fminf(fmaxf(v, -65504.f), 65504.f);
+    return (tag16 << 16) | (uint32_t)__half_as_ushort(__float2half_rn(v));
+}
+__device__ __forceinline__ float ll16_val(uint32_t w) { return __half2float(__ushort_as_half((unsigned short)(w & 0xffffu))); }
+__device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) { asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ void st_relaxed_v2(void* p, uint32_t a, uint32_t b) { asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(a), "r"(b) : "memory"); }
+__device__ __forceinline__ uint4 ld_relaxed_v4(const void* p) {
+    uint4 r; asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory"); return r;
+}
+__device__ __forceinline__ uint2 ld_relaxed_v2(const void* p) {
+    uint2 r; asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p) : "memory"); return r;
+}
+// broadcast vectors exist in XREP copies: writers store all, reader CTA c polls copy c % XREP
+__device__ __forceinline__ void st_rep_u32(uint32_t* base, int stride, int idx, uint32_t w) {
+#pragma unroll
+    for (int r = 0; r < XREP; r++) st_relaxed_u32(base + (size_t)r * stride + idx, w);
+}
+// 16 consecutive LL16 words (64 B), polled until every tag matches
+__device__ __forceinline__ void ll16_poll_run(const uint32_t* buf, int u, uint32_t tag16, float v[16]) {
+    const uint4* p = (const uint4*)(buf + 16 * u);
+    const uint32_t want = tag16 << 16;
+    uint4 r[4];
+    for (;;) {
+        uint32_t bad = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++) { r[i] = ld_relaxed_v4(p + i); bad |= (r[i].x ^ want) | (r[i].y ^ want) | (r[i].z ^ want) | (r[i].w ^ want); }
+        if ((bad >> 16) == 0) break;
+        __nanosleep(40);
     }
-    consumer_sync();
+#pragma unroll
+    for (int i = 0; i < 4; i++) { v[4 * i] = ll16_val(r[i].x); v[4 * i + 1] = ll16_val(r[i].y); v[4 * i + 2] = ll16_val(r[i].z); v[4 * i + 3] = ll16_val(r[i].w); }
+}
+// N consecutive LL32 elements ({bits, tag32} pairs), N even, polled
+template <int N>
+__device__ __forceinline__ void ll32_poll(const uint2* buf, uint32_t tag, float* out) {
+    uint4 r[N / 2];
+    for (;;) {
+        uint32_t bad = 0;
+#pragma unroll
+        for (int i = 0; i < N / 2; i++) { r[i] = ld_relaxed_v4((const uint4*)buf + i); bad |= (r[i].y ^ tag) | (r[i].w ^ tag); }
+        if (!bad) break;
+    }
+#pragma unroll
+    for (int i = 0; i < N / 2; i++) { out[2 * i] = __uint_as_float(r[i].x); out[2 * i + 1] = __uint_as_float(r[i].z); }
 }
 
 // ------------------------------------------------------------------------------------ embedding
@@ -30,40 +77,69 @@ __device__ __forceinline__ float embed_elem(const uint8_t* w, int type, int n_gr
 }
 
 // ------------------------------------------------------------------------------------ attention (bs1)
+// One item = (head, split).  Warps stride over positions in batches of NB for memory-level parallelism.
 template <int VEC>   // head_dim = 32*VEC
-__device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int head, int split, int pos, int warp, int lane) {
-    constexpr int HD = 32 * VEC;
+__device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int head, int split, int pos, uint32_t seq_in, uint32_t seq_out, int warp, int lane) {
+    constexpr int HD = 32 * VEC, NB = 4;
     const int n_ctx = pos + 1, chunk = (n_ctx + P.n_splits - 1) / P.n_splits;
     const int p0 = split * chunk, p1 = min(n_ctx, p0 + chunk);
-    const int kvh = head / (P.n_head / P.n_head_kv);
+    const int kvh = head / (P.n_head / P.n_head_kv), KVD = P.n_head_kv * HD;
     float qv[VEC], acc[VEC];
+    {   // q of this head: LL32, tag of the QKV phase
+        float t[VEC];
+        ll32_poll<VEC>(P.q_ll + head * HD + lane * VEC, seq_in, t);
 #pragma unroll
-    for (int i = 0; i < VEC; i++) { qv[i] = __ldcg(P.q + head * HD + lane * VEC + i) * P.kq_scale; acc[i] = 0.f; }
+        for (int i = 0; i < VEC; i++) { qv[i] = t[i] * P.kq_scale; acc[i] = 0.f; }
+    }
     float m = -INFINITY, l = 0.f;
-    for (int p = p0 + warp; p < p1; p += CONSUMER_WARPS) {
-        const __half* kp = P.kv.at(layer, 0, kvh, p) + lane * VEC;
-        const __half* vp = P.kv.at(layer, 1, kvh, p) + lane * VEC;
-        float kf[VEC], vf[VEC];
-        if constexpr (VEC == 4) {
-            uint2 kr = __ldcg((const uint2*)kp), vr = __ldcg((const uint2*)vp);
-            float2 a = __half22float2(*(__half2*)&kr.x), b = __half22float2(*(__half2*)&kr.y);
-            kf[0] = a.x; kf[1] = a.y; kf[2] = b.x; kf[3] = b.y;
-            a = __half22float2(*(__half2*)&vr.x); b = __half22float2(*(__half2*)&vr.y);
-            vf[0] = a.x; vf[1] = a.y; vf[2] = b.x; vf[3] = b.y;
-        } else {
-            uint32_t kr = __ldcg((const uint32_t*)kp), vr = __ldcg((const uint32_t*)vp);
-            float2 a = __half22float2(*(__half2*)&kr); kf[0] = a.x; kf[1] = a.y;
-            a = __half22float2(*(__half2*)&vr); vf[0] = a.x; vf[1] = a.y;
+    for (int pb = p0 + warp * NB; pb < p1; pb += CONSUMER_WARPS * NB) {
+        float kf[NB][VEC], vf[NB][VEC]; bool live[NB];
+#pragma unroll
+        for (int b = 0; b < NB; b++) {
+            const int p = pb + b; live[b] = p < p1;
+            if (live[b] && p < pos) {                                    // cached position: fp16 pages
+                const __half* kp = P.kv.at(layer, 0, kvh, p) + lane * VEC;
+                const __half* vp = P.kv.at(layer, 1, kvh, p) + lane * VEC;
+                if constexpr (VEC == 4) {
+                    uint2 kr = __ldcg((const uint2*)kp), vr = __ldcg((const uint2*)vp);
+                    float2 a = __half22float2(*(__half2*)&kr.x), c2 = __half22float2(*(__half2*)&kr.y);
+                    kf[b][0] = a.x; kf[b][1] = a.y; kf[b][2] = c2.x; kf[b][3] = c2.y;
+                    a = __half22float2(*(__half2*)&vr.x); c2 = __half22float2(*(__half2*)&vr.y);
+                    vf[b][0] = a.x; vf[b][1] = a.y; vf[b][2] = c2.x; vf[b][3] = c2.y;
+                } else {
+                    uint32_t kr = __ldcg((const uint32_t*)kp), vr = __ldcg((const uint32_t*)vp);
+                    float2 a = __half22float2(*(__half2*)&kr); kf[b][0] = a.x; kf[b][1] = a.y;
+                    a = __half22float2(*(__half2*)&vr); vf[b][0] = a.x; vf[b][1] = a.y;
+                }
+            } else if (live[b]) {                                         // the token being decoded: tagged exchange words
+                const uint32_t want = tag16_of(seq_in) << 16;
+                const uint32_t* kw = P.kv_ll + kvh * HD + lane * VEC; const uint32_t* vw = P.kv_ll + KVD + kvh * HD + lane * VEC;
+                uint32_t kk[VEC], vv[VEC];
+                for (;;) {
+                    uint32_t bad = 0;
+                    if constexpr (VEC == 4) { uint4 a = ld_relaxed_v4(kw), c2 = ld_relaxed_v4(vw); kk[0] = a.x; kk[1] = a.y; kk[2] = a.z; kk[3] = a.w; vv[0] = c2.x; vv[1] = c2.y; vv[2] = c2.z; vv[3] = c2.w; }
+                    else { uint2 a = ld_relaxed_v2(kw), c2 = ld_relaxed_v2(vw); kk[0] = a.x; kk[1] = a.y; vv[0] = c2.x; vv[1] = c2.y; }
+#pragma unroll
+                    for (int i = 0; i < VEC; i++) bad |= (kk[i] ^ want) | (vv[i] ^ want);
+                    if ((bad >> 16) == 0) break;
+                }
+#pragma unroll
+                for (int i = 0; i < VEC; i++) { kf[b][i] = ll16_val(kk[i]); vf[b][i] = ll16_val(vv[i]); }
+            }
         }
-        float s = 0.f;
 #pragma unroll
-        for (int i = 0; i < VEC; i++) s += qv[i] * kf[i];
-        s = warp_sum(s);
-        const float mn = fmaxf(m, s), corr = __expf(m - mn), pe = __expf(s - mn);
-        l = l * corr + pe;
+        for (int b = 0; b < NB; b++) {
+            if (!live[b]) continue;                                      // warp-uniform
+            float s = 0.f;
 #pragma unroll
-        for (int i = 0; i < VEC; i++) acc[i] = acc[i] * corr + pe * vf[i];
-        m = mn;
+            for (int i = 0; i < VEC; i++) s += qv[i] * kf[b][i];
+            s = warp_sum(s);
+            const float mn = fmaxf(m, s), corr = __expf(m - mn), pe = __expf(s - mn);
+            l = l * corr + pe;
+#pragma unroll
+            for (int i = 0; i < VEC; i++) acc[i] = acc[i] * corr + pe * vf[b][i];
+            m = mn;
+        }
     }
     // cross-warp combine through shared memory (aliases the activation buffer, idle in this phase)
     float* scr = (float*)sm.xq;                     // [8 warps][HD + 2]
@@ -84,9 +160,46 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
             const float f = mw == -INFINITY ? 0.f : __expf(mw - M);
             a += f * scr[w * (HD + 2) + tid]; L += f * scr[w * (HD + 2) + HD + 1];
         }
-        const size_t o = (size_t)head * P.n_splits + split;
-        P.part_acc[o * HD + tid] = a;
-        if (tid == 0) { P.part_ml[o * 2] = M; P.part_ml[o * 2 + 1] = L; }
+        if (P.n_splits == 1) st_rep_u32(P.att_ll, P.att_stride, head * HD + tid, ll16_pack(a / L, tag16_of(seq_out)));
+        else if (split != 0) {
+            const size_t o = ((size_t)head * P.n_splits + split) * (HD + 2);
+            st_relaxed_v2(P.part_ll + o + tid, __float_as_uint(a), seq_out);
+            if (tid == 0) { st_relaxed_v2(P.part_ll + o + HD, __float_as_uint(M), seq_out); st_relaxed_v2(P.part_ll + o + HD + 1, __float_as_uint(L), seq_out); }
+        } else { scr[CONSUMER_WARPS * (HD + 2) + tid] = a; if (tid == 0) { scr[CONSUMER_WARPS * (HD + 2) + HD] = M; scr[CONSUMER_WARPS * (HD + 2) + HD + 1] = L; } }
+    }
+    if (P.n_splits > 1 && split == 0) {
+        // This CTA is the head's combiner: gather the other splits' partials (all loads in flight together,
+        // re-polled until every tag matches), merge with its own, publish the head's output once.
+        const int S = P.n_splits;
+        float* own = scr + CONSUMER_WARPS * (HD + 2);            // [HD + 2]: a[], M, L of split 0
+        float* mls = own + HD + 2;                               // [16][2]
+        if (tid >= HD && tid < HD + S - 1) {
+            const int s = tid - HD + 1; float t[2];
+            ll32_poll<2>(P.part_ll + ((size_t)head * S + s) * (HD + 2) + HD, seq_out, t);
+            mls[2 * s] = t[0]; mls[2 * s + 1] = t[1];
+        }
+        uint32_t av[16];
+        if (tid < HD) {
+            for (;;) {
+                uint32_t bad = 0;
+#pragma unroll
+                for (int s = 1; s < 16; s++) if (s < S) { uint2 w = ld_relaxed_v2(P.part_ll + ((size_t)head * S + s) * (HD + 2) + tid); av[s] = w.x; bad |= w.y ^ seq_out; }
+                if (!bad) break;
+            }
+        }
+        consumer_sync();
+        if (tid < HD) {
+            float M = own[HD];
+            for (int s = 1; s < S; s++) M = fmaxf(M, mls[2 * s]);
+            const float f0 = own[HD] == -INFINITY ? 0.f : __expf(own[HD] - M);
+            float a = f0 * own[tid], L = f0 * own[HD + 1];
+#pragma unroll
+            for (int s = 1; s < 16; s++) if (s < S) {
+                const float ms = mls[2 * s], f = ms == -INFINITY ? 0.f : __expf(ms - M);
+                a += f * __uint_as_float(av[s]); L += f * mls[2 * s + 1];
+            }
+            st_rep_u32(P.att_ll, P.att_stride, head * HD + tid, ll16_pack(a / L, tag16_of(seq_out)));
+        }
     }
 }
 
@@ -100,27 +213,82 @@ __device__ __forceinline__ void rope_pair(const DecodeParams& P, int d, int pos,
     }
 }
 
-__device__ __forceinline__ void epilogue(const DecodeParams& P, const OpDesc& op, int pair, float a0, float a1, int pos, ArgBest& best, float* logits_dst) {
-    const int row = 2 * pair, HD = P.head_dim;
+// lp: index of the pair inside this CTA's slice of the op (for the owned hidden-state rows)
+__device__ __forceinline__ void epilogue(const DecodeParams& P, const OpDesc& op, const Smem& sm, int pair, int lp, float a0, float a1, int pos,
+                                         uint32_t seq, ArgBest& best, float* logits_dst) {
+    const int row = 2 * pair, HD = P.head_dim; const uint32_t t16 = tag16_of(seq);
     switch (op.epi) {
         case EPI_STORE: *(float2*)(op.out + row) = make_float2(a0 * op.scale, a1 * op.scale); break;
-        case EPI_RESID: { float2 o = __ldcg((const float2*)(op.out + row)); o.x += op.scale * a0; o.y += op.scale * a1; *(float2*)(op.out + row) = o; } break;
-        case EPI_SWIGLU: op.out[pair] = a0 / (1.f + __expf(-a0)) * a1; break;
-        case EPI_LOGITS: {
-            a0 *= op.scale; a1 *= op.scale; *(float2*)(logits_dst + row) = make_float2(a0, a1);
-            if (a0 > best.v) { best.v = a0; best.i = row; }
-            if (a1 > best.v) { best.v = a1; best.i = row + 1; }
+        case EPI_RESID: {
+            const float h0 = sm.hown[2 * lp] + op.scale * a0, h1 = sm.hown[2 * lp + 1] + op.scale * a1;
+            sm.hown[2 * lp] = h0; sm.hown[2 * lp + 1] = h1;
+            const uint32_t w0 = ll16_pack(h0, t16), w1 = ll16_pack(h1, t16);
+#pragma unroll
+            for (int r = 0; r < XREP; r++) st_relaxed_v2(P.h_ll + (size_t)r * P.h_stride + row, w0, w1);
         } break;
-        case EPI_ROPE_Q: rope_pair(P, row % HD, pos, a0, a1); *(float2*)(op.out + row) = make_float2(a0, a1); break;
-        case EPI_ROPE_K: rope_pair(P, row % HD, pos, a0, a1);
-            *(__half2*)(P.kv.at(op.layer, 0, row / HD, pos) + row % HD) = __floats2half2_rn(a0, a1); break;
-        case EPI_V: *(__half2*)(P.kv.at(op.layer, 1, row / HD, pos) + row % HD) = __floats2half2_rn(a0, a1); break;
+        case EPI_SWIGLU: st_rep_u32(P.act_ll, P.act_stride, pair, ll16_pack(a0 / (1.f + __expf(-a0)) * a1, t16)); break;
+        case EPI_LOGITS: {
+            a0 *= op.scale; a1 *= op.scale;
+            logits_dst[row] = a0; if (row + 1 < op.n_rows) logits_dst[row + 1] = a1;
+            if (a0 > best.v) { best.v = a0; best.i = row; }
+            if (row + 1 < op.n_rows && a1 > best.v) { best.v = a1; best.i = row + 1; }
+        } break;
+        case EPI_ROPE_Q:
+            rope_pair(P, row % HD, pos, a0, a1);
+            st_relaxed_v2(P.q_ll + row, __float_as_uint(a0), seq); st_relaxed_v2(P.q_ll + row + 1, __float_as_uint(a1), seq); break;
+        case EPI_ROPE_K: {
+            rope_pair(P, row % HD, pos, a0, a1);
+            const __half2 hv = __floats2half2_rn(a0, a1);
+            *(__half2*)(P.kv.at(op.layer, 0, row / HD, pos) + row % HD) = hv;
+            st_relaxed_v2(P.kv_ll + row, (t16 << 16) | __half_as_ushort(__low2half(hv)), (t16 << 16) | __half_as_ushort(__high2half(hv)));
+        } break;
+        case EPI_V: {
+            const __half2 hv = __floats2half2_rn(a0, a1);
+            *(__half2*)(P.kv.at(op.layer, 1, row / HD, pos) + row % HD) = hv;
+            st_relaxed_v2(P.kv_ll + P.n_head_kv * HD + row, (t16 << 16) | __half_as_ushort(__low2half(hv)), (t16 << 16) | __half_as_ushort(__high2half(hv)));
+        } break;
+    }
+}
+
+// ------------------------------------------------------------------------------------ streaming one op's slice (consumers)
+// Pairs [a, b) of `op`, eight pairs per stage (one per warp), one stage per 2048-element group.
+template <int TYPE>
+__device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& op, const Smem& sm, const Smem& sx, RingCursor& cur, int a, int b,
+                                          int pos, int warp, int lane, uint32_t seq, ArgBest& best, float* logits_dst, long long* tr) {
+    constexpr int GB = TYPE == T_Q4_K ? 1152 : TYPE == T_Q5_K ? 1408 : TYPE == T_Q6_K ? 1680 : 2176;
+    constexpr uint32_t PU = 2u * GB;
+    const int n_grp = op.n_grp;
+    const uint8_t* my_unit = sm.ring + warp * PU;
+    for (int rb = a; rb < b; rb += PAIRS_PER_STAGE) {
+        const int np = min(PAIRS_PER_STAGE, b - rb);
+        const bool mine = warp < np;
+        float acc0 = 0.f, acc1 = 0.f;
+        for (int g = 0; g < n_grp; g++) {
+            uint32_t gap; const uint32_t soff = cur.place(np * PU, sm.ring_bytes, gap);
+            const uint32_t slot = cur.seq % NSLOT;
+            mbar_wait(&sm.full[slot], (cur.seq / NSLOT) & 1);
+            if (tr && warp == 0 && lane == 0 && rb == a && g == 0) tr[4] = gtime();
+            if (mine) {
+                XRegs x; load_x(sx, g, lane, x);
+                acc0 += lane_dot<TYPE>(my_unit + soff, lane, x);
+                acc1 += lane_dot<TYPE>(my_unit + soff + GB, lane, x);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.empty[slot]);
+            cur.seq++;
+        }
+        if (tr && warp == 0 && lane == 0) tr[5] = gtime();
+        if (mine) {
+            acc0 = warp_sum(acc0); acc1 = warp_sum(acc1);
+            if (lane == 0) epilogue(P, op, sm, rb + warp, rb + warp - a, acc0, acc1, pos, seq, best, logits_dst);
+        }
     }
 }
 
 // ------------------------------------------------------------------------------------ one GEMV phase (consumers)
+// seq: this phase's generation number; inputs carry seq-1's tags.
 __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem& sm, RingCursor& cur, int c, int G,
-                              int pos, int tid, ArgBest& best, float* logits_dst, long long* tr) {
+                              int pos, int tid, uint32_t seq, ArgBest& best, float* logits_dst, long long* tr) {
     const int warp = tid >> 5, lane = tid & 31;
     // ---- activation prologue: build the int8 vector(s) in shared memory
     bool fam_std = false, fam_q6 = false;
@@ -128,45 +296,89 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
     const int n_grp = n_groups(ph.K);
     Smem s2 = sm;                                   // second layout family lives behind the first
     if (fam_std && fam_q6) { s2.xq += (size_t)n_grp * 2048; s2.xbs += n_grp * 128; s2.xd += n_grp * 8; }
-    float rs = 1.f;
-    if (ph.pro == PRO_NORM) rs = rms_scale(sm, ph.src, ph.K, P.rms_eps, tid);
-    auto loader = [&](int u, float v[16]) {
-        if (ph.pro == PRO_ATTN) {
-            const int HD = P.head_dim, head = (16 * u) / HD, d0 = (16 * u) % HD, S = P.n_splits;
-            float M = -INFINITY;
-            for (int s = 0; s < S; s++) M = fmaxf(M, __ldcg(P.part_ml + ((size_t)head * S + s) * 2));
-            float den = 0.f;
+    const uint32_t tin16 = tag16_of(seq - 1);
+    const int n_runs = ph.K / 16, n_runs_pad = n_grp * 128;
+    const int rep = c % XREP;
+    const uint32_t* xsrc = ph.pro == PRO_ATTN ? P.att_ll + (size_t)rep * P.att_stride : ph.pro == PRO_NORM ? P.h_ll + (size_t)rep * P.h_stride : P.act_ll + (size_t)rep * P.act_stride;
+    // fetch (poll) one run of 16 activations
+    auto fetch = [&](int u, float* v) {
+        if (ph.pro == PRO_PLAIN) load_run_f32(ph.src, u, v);
+        else ll16_poll_run(xsrc, u, tin16, v);
+    };
+    auto quantise_store = [&](int u, float* v) {
+        float amax = 0.f;
 #pragma unroll
-            for (int i = 0; i < 16; i++) v[i] = 0.f;
-            for (int s = 0; s < S; s++) {
-                const size_t o = (size_t)head * S + s;
-                const float ms = __ldcg(P.part_ml + o * 2), f = ms == -INFINITY ? 0.f : __expf(ms - M);
-                den += f * __ldcg(P.part_ml + o * 2 + 1);
-                const float4* pa = (const float4*)(P.part_acc + o * HD + d0);
+        for (int i = 0; i < 16; i++) amax = fmaxf(amax, fabsf(v[i]));
+        amax = half16_max(amax);
+        if (fam_std) store_run(sm, T_Q4_K, u, v, amax);
+        if (fam_q6) store_run(s2, T_Q6_K, u, v, amax);
+    };
+    if (ph.pro == PRO_NORM) {
+        // two passes (sum of squares, then scale).  The thread's first run stays in registers between them and its
+        // norm weights are requested BEFORE the poll (they do not depend on the exchange); wider inputs re-poll.
+        float v[16], w[16]; float ss = 0.f;
+        const bool have = tid < n_runs;
+        if (have) {
+            const float4* wv = (const float4*)(ph.norm_w + 16 * tid);
 #pragma unroll
-                for (int i = 0; i < 4; i++) { float4 t = __ldcg(pa + i); v[4 * i] += f * t.x; v[4 * i + 1] += f * t.y; v[4 * i + 2] += f * t.z; v[4 * i + 3] += f * t.w; }
-            }
-            const float inv = 1.f / den;
+            for (int i = 0; i < 4; i++) { float4 t = __ldg(wv + i); w[4 * i] = t.x; w[4 * i + 1] = t.y; w[4 * i + 2] = t.z; w[4 * i + 3] = t.w; }
+            fetch(tid, v);
 #pragma unroll
-            for (int i = 0; i < 16; i++) v[i] *= inv;
-        } else {
-            load_run_f32(ph.src, u, v);
-            if (ph.pro == PRO_NORM) {
+            for (int i = 0; i < 16; i++) ss += v[i] * v[i];
+        }
+        for (int u = tid + CONSUMER_THREADS; u < n_runs; u += CONSUMER_THREADS) {
+            float t[16]; fetch(u, t);
+#pragma unroll
+            for (int i = 0; i < 16; i++) ss += t[i] * t[i];
+        }
+        if (tr && tid == 0) tr[1] = gtime();
+        ss = warp_sum(ss);
+        consumer_sync();                                    // red[] and xq free (previous phase's readers done)
+        if (lane == 0) sm.red[warp] = ss;
+        consumer_sync();
+        float tot = 0.f;
+#pragma unroll
+        for (int i = 0; i < CONSUMER_WARPS; i++) tot += sm.red[i];
+        const float rs = rsqrtf(tot / (float)ph.K + P.rms_eps);
+        if (tr && tid == 0) tr[2] = gtime();
+        if (tid < n_runs_pad) {
+#pragma unroll
+            for (int i = 0; i < 16; i++) v[i] = have ? v[i] * rs * w[i] : 0.f;
+            quantise_store(tid, v);
+        }
+        for (int u = tid + CONSUMER_THREADS; u < n_runs_pad; u += CONSUMER_THREADS) {
+            float t[16];
+            if (u < n_runs) {
+                fetch(u, t);
                 const float4* wv = (const float4*)(ph.norm_w + 16 * u);
 #pragma unroll
-                for (int i = 0; i < 4; i++) { float4 t = __ldg(wv + i); v[4 * i] *= rs * t.x; v[4 * i + 1] *= rs * t.y; v[4 * i + 2] *= rs * t.z; v[4 * i + 3] *= rs * t.w; }
+                for (int i = 0; i < 4; i++) { float4 q4 = __ldg(wv + i); t[4 * i] *= rs * q4.x; t[4 * i + 1] *= rs * q4.y; t[4 * i + 2] *= rs * q4.z; t[4 * i + 3] *= rs * q4.w; }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; i++) t[i] = 0.f;
             }
+            quantise_store(u, t);
         }
-    };
-    if (fam_std && fam_q6) {
-        // both layouts: quantise once per family (cheap: K = n_embd here)
-        prologue_quantise(sm, T_Q4_K, ph.K, n_grp, tid, loader);
-        prologue_quantise(s2, T_Q6_K, ph.K, n_grp, tid, loader);
     } else {
-        prologue_quantise(sm, fam_q6 ? T_Q6_K : T_Q4_K, ph.K, n_grp, tid, loader);
+        // single pass; poll the first run before the barrier so the wait overlaps the other warps' tails
+        float t[16]; const bool first = tid < n_runs;
+        if (first) fetch(tid, t);
+        if (tr && tid == 0) tr[1] = tr[2] = gtime();
+        consumer_sync();                                    // xq free (previous phase's readers done)
+        for (int u = tid; u < n_runs_pad; u += CONSUMER_THREADS) {
+            if (u != tid || !first) {
+                if (u < n_runs) fetch(u, t);
+                else {
+#pragma unroll
+                    for (int i = 0; i < 16; i++) t[i] = 0.f;
+                }
+            }
+            quantise_store(u, t);
+        }
     }
+    consumer_sync();
+    if (tr && tid == 0) tr[3] = gtime();
 
-    if (tr && tid == 0) tr[1] = clock64();
     // ---- stream the CTA's slice
     int lo, hi; cta_slice(ph.total_pairs, c, G, lo, hi);
     int off = 0;
@@ -174,29 +386,12 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
         const OpDesc& op = ph.op[o];
         const int a = max(lo, off) - off, b = min(hi, off + op.n_pairs) - off; off += op.n_pairs;
         if (a >= b) continue;
-        const int gb = group_bytes(op.type); const uint32_t pu = 2u * gb;
         const Smem& sx = (op.type == T_Q6_K) ? s2 : sm;
-        for (int rb = a; rb < b; rb += PAIRS_PER_STAGE) {
-            const int np = min(PAIRS_PER_STAGE, b - rb);
-            float acc0 = 0.f, acc1 = 0.f;
-            for (int g = 0; g < op.n_grp; g++) {
-                uint32_t gap; const uint32_t soff = cur.place(np * pu, sm.ring_bytes, gap);
-                const uint32_t slot = cur.seq % NSLOT, parity = (cur.seq / NSLOT) & 1;
-                mbar_wait(&sm.full[slot], parity);
-                if (warp < np) {
-                    XRegs x; load_x(sx, g, lane, x);
-                    const uint8_t* unit = sm.ring + soff + warp * pu;
-                    acc0 += lane_dot(op.type, unit, lane, x);
-                    acc1 += lane_dot(op.type, unit + gb, lane, x);
-                }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&sm.empty[slot]);
-                cur.seq++;
-            }
-            if (warp < np) {
-                acc0 = warp_sum(acc0); acc1 = warp_sum(acc1);
-                if (lane == 0) epilogue(P, op, rb + warp, acc0, acc1, pos, best, logits_dst);
-            }
+        switch (op.type) {
+            case T_Q4_K: stream_op<T_Q4_K>(P, op, sm, sx, cur, a, b, pos, warp, lane, seq, best, logits_dst, tr); break;
+            case T_Q6_K: stream_op<T_Q6_K>(P, op, sm, sx, cur, a, b, pos, warp, lane, seq, best, logits_dst, tr); break;
+            case T_Q8_0: stream_op<T_Q8_0>(P, op, sm, sx, cur, a, b, pos, warp, lane, seq, best, logits_dst, tr); break;
+            default: stream_op<T_Q5_K>(P, op, sm, sx, cur, a, b, pos, warp, lane, seq, best, logits_dst, tr); break;
         }
     }
 }
@@ -210,7 +405,7 @@ struct DecodeRun {
 __global__ void __launch_bounds__(CTA_THREADS, 2)
 decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes, const int max_grp) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    const Smem sm = carve_smem(smem_raw, ring_bytes, max_grp);
+    const Smem sm = carve_smem(smem_raw, ring_bytes, max_grp, P.hown_cap);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, c = blockIdx.x, G = gridDim.x;
     if (tid == 0) {
         for (int i = 0; i < NSLOT; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], CONSUMER_WARPS); }
@@ -219,7 +414,7 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
     __syncthreads();
 
     if (warp == CONSUMER_WARPS) {           // ===== producer warp =====
-        Producer pr; pr.init();
+        Producer pr; pr.init(P.max_inflight);
         for (int step = 0; step < P.n_steps; step++) {
             const bool need_lm = (step + 1 >= R.n_forced) || R.logits_all;
             for (int i = 0; i < P.n_phases; i++) {
@@ -234,10 +429,11 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
     }
 
     // ===== consumer warps =====
-    unsigned target = *(volatile unsigned*)P.epoch;
+    uint32_t seq = *(volatile unsigned*)P.epoch;          // generation counter: one per executed phase
     const int pos0 = *(volatile int*)P.pos;
     int token = R.n_forced > 0 ? R.forced[0] : *(volatile int*)P.token;
-    RingCursor cur; cur.seq = 0; cur.head = 0;
+    RingCursor cur; cur.init();
+    int hlo, hhi; cta_slice(P.n_embd / 2, c, G, hlo, hhi);  // hidden-state row pairs this CTA owns (== its wo/down slices)
     for (int step = 0; step < P.n_steps; step++) {
         const int pos = pos0 + step;
         const bool need_lm = (step + 1 >= R.n_forced) || R.logits_all;
@@ -245,23 +441,27 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
         ArgBest best; best.v = -INFINITY; best.i = 0x7fffffff;
         for (int i = 0; i < P.n_phases; i++) {
             const Phase& ph = P.phases[i];
+            if (ph.kind == PH_GEMV && ph.op[0].epi == EPI_LOGITS && !need_lm) continue;
+            seq++;
             long long* tr = nullptr;
-            if (P.trace) { const int slot = c == 0 ? 0 : c == 1 ? 1 : c == G / 2 ? 2 : c == G - 1 ? 3 : -1; if (slot >= 0) tr = P.trace + (((size_t)step * P.n_phases + i) * 4 + slot) * 4; }
-            if (tr && tid == 0) tr[0] = tr[1] = clock64();
+            if (P.trace) tr = P.trace + (((size_t)step * P.n_phases + i) * G + c) * 8;
+            if (tr && tid == 0) { const long long t0 = gtime(); for (int k = 0; k < 7; k++) tr[k] = t0; }
             if (ph.kind == PH_EMBED) {
-                const int ng = n_groups(P.n_embd);
-                for (int e = c * CONSUMER_THREADS + tid; e < P.n_embd; e += G * CONSUMER_THREADS) {
+                const int ng = n_groups(P.n_embd); const uint32_t t16 = tag16_of(seq);
+                for (int e = 2 * hlo + tid; e < 2 * hhi; e += CONSUMER_THREADS) {
                     float v = embed_elem(P.embd, P.embd_type, ng, token, e);
-                    P.h[e] = P.emb_scale != 0.f ? v * P.emb_scale : v;
+                    if (P.emb_scale != 0.f) v *= P.emb_scale;
+                    sm.hown[e - 2 * hlo] = v;
+                    st_rep_u32(P.h_ll, P.h_stride, e, ll16_pack(v, t16));
                 }
+                consumer_sync();
             } else if (ph.kind == PH_ATTN) {
                 for (int it = c; it < P.n_head * P.n_splits; it += G) {
-                    if (P.head_dim == 128) attn_item<4>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, warp, lane);
-                    else attn_item<2>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, warp, lane);
+                    if (P.head_dim == 128) attn_item<4>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane);
+                    else attn_item<2>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane);
                 }
             } else {
-                if (ph.op[0].epi == EPI_LOGITS && !need_lm) continue;
-                consume_phase(P, ph, sm, cur, c, G, pos, tid, best, logits_dst, tr);
+                consume_phase(P, ph, sm, cur, c, G, pos, tid, seq, best, logits_dst, tr);
                 if (ph.op[0].epi == EPI_LOGITS) {          // publish this CTA's argmax candidate
                     consumer_sync();
                     if (lane == 0) { sm.red[2 * warp] = best.v; sm.red[2 * warp + 1] = __int_as_float(best.i); }
@@ -269,16 +469,14 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
                     if (tid == 0) {
                         float bv = -INFINITY; int bi = 0x7fffffff;
                         for (int w = 0; w < CONSUMER_WARPS; w++) {
-                            const float v = sm.red[2 * w]; const int ix = __float_as_int(sm.red[2 * w + 1]);
-                            if (v > bv || (v == bv && ix < bi)) { bv = v; bi = ix; }
+                            const float vv = sm.red[2 * w]; const int ix = __float_as_int(sm.red[2 * w + 1]);
+                            if (vv > bv || (vv == bv && ix < bi)) { bv = vv; bi = ix; }
                         }
-                        P.cand_val[c] = bv; P.cand_idx[c] = bi;
+                        st_relaxed_v2(P.cand_ll + 2 * c, __float_as_uint(bv), seq); st_relaxed_v2(P.cand_ll + 2 * c + 1, (uint32_t)bi, seq);
                     }
                 }
             }
-            if (tr && tid == 0) tr[2] = clock64();
-            grid_barrier(P.bar_ctr, target, tid, G);
-            if (tr && tid == 0) tr[3] = clock64();
+            if (tr && tid == 0) { tr[6] = gtime(); unsigned smid; asm("mov.u32 %0, %%smid;" : "=r"(smid)); tr[7] = smid; }
         }
         // ---- next token: forced, or argmax over the per-CTA candidates (every CTA redundantly)
         int next;
@@ -286,34 +484,36 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
         else {
             float bv = -INFINITY; int bi = 0x7fffffff;
             for (int k = tid; k < G; k += CONSUMER_THREADS) {
-                const float v = __ldcg(P.cand_val + k); const int ix = __ldcg(P.cand_idx + k);
-                if (v > bv || (v == bv && ix < bi)) { bv = v; bi = ix; }
+                float t[2]; ll32_poll<2>(P.cand_ll + 2 * k, seq, t);
+                const float vv = t[0]; const int ix = __float_as_int(t[1]);
+                if (vv > bv || (vv == bv && ix < bi)) { bv = vv; bi = ix; }
             }
 #pragma unroll
             for (int o = 16; o; o >>= 1) {
-                const float v = __shfl_xor_sync(0xffffffffu, bv, o); const int ix = __shfl_xor_sync(0xffffffffu, bi, o);
-                if (v > bv || (v == bv && ix < bi)) { bv = v; bi = ix; }
+                const float vv = __shfl_xor_sync(0xffffffffu, bv, o); const int ix = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (vv > bv || (vv == bv && ix < bi)) { bv = vv; bi = ix; }
             }
             consumer_sync();
             if (lane == 0) { sm.red[2 * warp] = bv; sm.red[2 * warp + 1] = __int_as_float(bi); }
             consumer_sync();
             bv = -INFINITY; bi = 0x7fffffff;
             for (int w = 0; w < CONSUMER_WARPS; w++) {
-                const float v = sm.red[2 * w]; const int ix = __float_as_int(sm.red[2 * w + 1]);
-                if (v > bv || (v == bv && ix < bi)) { bv = v; bi = ix; }
+                const float vv = sm.red[2 * w]; const int ix = __float_as_int(sm.red[2 * w + 1]);
+                if (vv > bv || (vv == bv && ix < bi)) { bv = vv; bi = ix; }
             }
             next = bi;
         }
         if (c == 0 && tid == 0) P.out_tokens[step] = next;
         token = next;
+        __threadfence();     // once per token: orders this CTA's KV-page stores before anything a later step publishes
     }
-    if (c == 0 && tid == 0) { *P.pos = pos0 + P.n_steps; *P.token = token; *P.epoch = target; }
+    if (c == 0 && tid == 0) { *P.pos = pos0 + P.n_steps; *P.token = token; *P.epoch = seq; }
 }
 
 // ------------------------------------------------------------------------------------ repack (K9) and test kernels
-// One thread per 16 output bytes; source bytes gathered through src_byte().
-__global__ void repack_kernel(const uint8_t* __restrict__ raw, uint8_t* __restrict__ out, int type, long long N, int K,
-                              long long row0, long long row_stride_pairs /*unused*/) {
+// One thread per 16 output bytes; source bytes gathered through src_byte().  parity >= 0 interleaves:
+// raw row r goes to engine row 2r + parity (gate/up fusion).  Rows >= n_src are zero (odd-N padding).
+__global__ void repack_kernel(const uint8_t* __restrict__ raw, uint8_t* __restrict__ out, int type, long long N, long long n_src, int K, int parity) {
     const int gb = group_bytes(type), ng = n_groups(K); const size_t rrb = raw_row_bytes(type, K);
     const long long chunks_per_row = (long long)ng * gb / 16, total = N * chunks_per_row;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -321,23 +521,9 @@ __global__ void repack_kernel(const uint8_t* __restrict__ raw, uint8_t* __restri
         const int g = rem / (gb / 16), o = (rem % (gb / 16)) * 16;
         uint8_t b[16];
 #pragma unroll
-        for (int k = 0; k < 16; k++) { long long s = src_byte(type, K, g, o + k); b[k] = s < 0 ? 0 : raw[(size_t)row * rrb + s]; }
-        const long long orow = row0 + row;
+        for (int k = 0; k < 16; k++) { long long s = row < n_src ? src_byte(type, K, g, o + k) : -1; b[k] = s < 0 ? 0 : raw[(size_t)row * rrb + s]; }
+        const long long orow = parity < 0 ? row : 2 * row + parity;
         uint8_t* dst = out + ((((size_t)(orow >> 1)) * ng + g) * 2 + (orow & 1)) * gb + o;
-        *(uint4*)dst = *(uint4*)b;
-    }
-}
-// interleaving variant: raw row r goes to engine row 2r + parity (gate/up fusion)
-__global__ void repack_interleave_kernel(const uint8_t* __restrict__ raw, uint8_t* __restrict__ out, int type, long long N, int K, int parity) {
-    const int gb = group_bytes(type), ng = n_groups(K); const size_t rrb = raw_row_bytes(type, K);
-    const long long chunks_per_row = (long long)ng * gb / 16, total = N * chunks_per_row;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const long long row = i / chunks_per_row; const int rem = (int)(i % chunks_per_row);
-        const int g = rem / (gb / 16), o = (rem % (gb / 16)) * 16;
-        uint8_t b[16];
-#pragma unroll
-        for (int k = 0; k < 16; k++) { long long s = src_byte(type, K, g, o + k); b[k] = s < 0 ? 0 : raw[(size_t)row * rrb + s]; }
-        uint8_t* dst = out + (((size_t)row * ng + g) * 2 + parity) * gb + o;
         *(uint4*)dst = *(uint4*)b;
     }
 }

@@ -56,17 +56,20 @@ int Engine::ensure() {
 // ------------------------------------------------------------------------------------ launch geometry
 struct LaunchCfg { int grid; uint32_t ring_bytes; int max_grp; size_t smem; };
 
-static int launch_cfg(Engine& E, int max_grp, LaunchCfg& lc) {
+static int launch_cfg(Engine& E, int max_grp, int hown_cap, LaunchCfg& lc) {
     // two CTAs per SM: each gets half of the SM's shared memory minus the 1 KB system reservation
     size_t per_cta = (size_t)E.smem_per_sm / 2 - 1024;
     if (per_cta > (size_t)E.smem_optin) per_cta = E.smem_optin;
-    size_t fixed = smem_x_bytes(max_grp) + smem_misc_bytes();
-    if (fixed + MAX_STAGE_BYTES + 256 > per_cta) {      // very wide model: one CTA per SM
+    size_t fixed = smem_x_bytes(max_grp) + smem_misc_bytes(hown_cap);
+    if (fixed + 2 * MAX_STAGE_BYTES + 256 > per_cta) {      // very wide model: one CTA per SM
         per_cta = E.smem_optin;
-        if (fixed + MAX_STAGE_BYTES + 256 > per_cta) return fail(B200_ERR_UNSUPPORTED, "activation vector does not fit in shared memory");
+        if (fixed + 2 * MAX_STAGE_BYTES + 256 > per_cta) return fail(B200_ERR_UNSUPPORTED, "activation vector does not fit in shared memory");
         lc.grid = E.n_sm;
     } else lc.grid = 2 * E.n_sm;
     lc.ring_bytes = (uint32_t)((per_cta - fixed - 128) / 128 * 128);
+    // the ring allocator never splits a stage across the wrap point, so a stage plus the gap it may leave behind
+    // must fit: ring >= 2 x the largest stage (otherwise the producer can wait on space that cannot exist)
+    if (const char* rk = getenv("B200_RING_KB")) { uint32_t want = (uint32_t)atoi(rk) * 1024u; if (want >= 2u * MAX_STAGE_BYTES && want < lc.ring_bytes) lc.ring_bytes = want / 128 * 128; }
     lc.max_grp = max_grp; lc.smem = lc.ring_bytes + fixed;
     int occ = 0;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, decode_kernel, CTA_THREADS, lc.smem));
@@ -91,12 +94,12 @@ static int dalloc(T** p, size_t n) {
 }
 
 // repack `raw` (device, ggml row-major blocks) into the engine layout at `out`
-static int repack(Engine& E, const uint8_t* raw, uint8_t* out, int type, int64_t N, int K, int interleave_parity = -1) {
+// (N rows written, of which the first n_src come from raw and the rest are zero padding)
+static int repack(Engine& E, const uint8_t* raw, uint8_t* out, int type, int64_t N, int64_t n_src, int K, int interleave_parity = -1) {
     long long chunks = (long long)N * n_groups(K) * group_bytes(type) / 16;
     int blocks = (int)std::min<long long>((chunks + 255) / 256, 148LL * 32);
     if (blocks < 1) blocks = 1;
-    if (interleave_parity < 0) repack_kernel<<<blocks, 256, 0, E.stream>>>(raw, out, type, N, K, 0, 0);
-    else repack_interleave_kernel<<<blocks, 256, 0, E.stream>>>(raw, out, type, N, K, interleave_parity);
+    repack_kernel<<<blocks, 256, 0, E.stream>>>(raw, out, type, N, n_src, K, interleave_parity);
     CK(cudaGetLastError());
     E.launches++;
     return B200_OK;
@@ -164,11 +167,11 @@ int Model::load_matrix(const std::string& name, int64_t N, int K, Matrix& out) {
     if (!t) return fail(B200_ERR_INVALID, "GGUF: missing tensor " + name);
     if (t->ne[0] != K || t->ne[1] != N) return fail(B200_ERR_INVALID, "GGUF: tensor " + name + " has unexpected shape");
     if (!is_streamable(t->type)) return fail(B200_ERR_UNSUPPORTED, "tensor " + name + ": ggml type " + std::to_string(t->type) + " is not supported for matrices (Q4_K, Q5_K, Q6_K, Q8_0)");
-    if (N % 2) return fail(B200_ERR_UNSUPPORTED, "tensor " + name + ": odd row count");
-    out.type = t->type; out.N = N; out.K = K;
-    if (int rc = own(&out.w, repacked_bytes(t->type, N, K))) return rc;
+    const int64_t Np = N + (N & 1);                                  // odd matrices (vocab) get one zero row
+    out.type = t->type; out.N = Np; out.n_rows = N; out.K = K;
+    if (int rc = own(&out.w, repacked_bytes(t->type, Np, K))) return rc;
     weight_bytes += t->nbytes;
-    return repack(engine(), d_raw + t->offset, out.w, t->type, N, K);
+    return repack(engine(), d_raw + t->offset, out.w, t->type, Np, N, K);
 }
 
 int Model::load_vector(const std::string& name, int64_t n, float** out) {
@@ -202,10 +205,10 @@ int Model::commit() {
         if (tg->type != tu->type) return fail(B200_ERR_UNSUPPORTED, "ffn_gate and ffn_up of a layer must share a quant type");
         if (tg->ne[0] != D || tg->ne[1] != F || tu->ne[0] != D || tu->ne[1] != F) return fail(B200_ERR_INVALID, "GGUF: ffn_gate/up shape");
         if (!is_streamable(tg->type)) return fail(B200_ERR_UNSUPPORTED, "ffn_gate: unsupported ggml type");
-        L.wgu.type = tg->type; L.wgu.N = 2 * (int64_t)F; L.wgu.K = D;              // rows interleaved (gate_i, up_i)
+        L.wgu.type = tg->type; L.wgu.N = 2 * (int64_t)F; L.wgu.n_rows = 2 * (int64_t)F; L.wgu.K = D;   // rows interleaved (gate_i, up_i)
         if ((rc = own(&L.wgu.w, repacked_bytes(tg->type, 2 * (int64_t)F, D)))) return rc;
-        if ((rc = repack(E, d_raw + tg->offset, L.wgu.w, tg->type, F, D, 0))) return rc;
-        if ((rc = repack(E, d_raw + tu->offset, L.wgu.w, tu->type, F, D, 1))) return rc;
+        if ((rc = repack(E, d_raw + tg->offset, L.wgu.w, tg->type, F, F, D, 0))) return rc;
+        if ((rc = repack(E, d_raw + tu->offset, L.wgu.w, tu->type, F, F, D, 1))) return rc;
         weight_bytes += tg->nbytes + tu->nbytes;
         if ((rc = load_matrix(p + "ffn_down.weight", D, F, L.wd))) return rc;
     }
@@ -227,15 +230,17 @@ int Model::commit() {
 
     // ---- runtime buffers
     int max_grp = std::max({n_groups(F), n_groups(QD), 2 * n_groups(D)});
-    LaunchCfg lc; if (int rc = launch_cfg(E, max_grp, lc)) return rc;
+    int n_sm2 = 2 * E.n_sm;
+    hown_cap = 2 * ((D / 2 + E.n_sm - 1) / E.n_sm + 2);                       // pairs per CTA slice (worst case: 1 CTA/SM) x 2 rows
+    LaunchCfg lc; if (int rc = launch_cfg(E, max_grp, hown_cap, lc)) return rc;
+    (void)n_sm2;
     grid = lc.grid; ring_bytes = lc.ring_bytes; smem_max_grp = lc.max_grp; smem_bytes = lc.smem;
-    n_splits = std::max(1, std::min(16, grid / n_head));
     int rc;
-    if ((rc = own(&d_h, (size_t)D)) || (rc = own(&d_q, (size_t)QD)) || (rc = own(&d_act, (size_t)F)) || (rc = own(&d_logits, (size_t)n_vocab)) ||
-        (rc = own(&d_part_acc, (size_t)n_head * n_splits * head_dim)) || (rc = own(&d_part_ml, (size_t)n_head * n_splits * 2)) ||
-        (rc = own(&d_cand_val, (size_t)grid)) || (rc = own(&d_cand_idx, (size_t)grid)) || (rc = own(&d_state, (size_t)16)) ||
+    const size_t n_ll16 = (size_t)XREP * ((size_t)D + QD + F) + 2 * (size_t)KVD, n_ll32 = (size_t)QD + (size_t)n_head * 16 * (head_dim + 2) + 2 * (size_t)grid;
+    if ((rc = own(&d_ll16, n_ll16)) || (rc = own(&d_ll32, n_ll32)) || (rc = own(&d_logits, (size_t)n_vocab + 2)) || (rc = own(&d_state, (size_t)16)) ||
         (rc = own(&d_out_tokens, (size_t)E.max_ctx + 16)) || (rc = own(&d_forced, (size_t)E.max_ctx + 16)))
         return rc;
+    CK(cudaMemset(d_ll16, 0, n_ll16 * 4)); CK(cudaMemset(d_ll32, 0, n_ll32 * 8));     // tag 0 = never valid
     CK(cudaMemset(d_state, 0, 16 * sizeof(int)));
     n_pages = (E.max_ctx + 15) / 16 * E.max_seqs;
     size_t page_elems = (size_t)n_layer * 2 * n_head_kv * 16 * head_dim;
@@ -246,7 +251,7 @@ int Model::commit() {
     // ---- decode schedule
     std::vector<Phase> ph;
     auto mk_op = [&](const Matrix& m, int epi, float* out, float scale, int layer) {
-        OpDesc o{}; o.w = m.w; o.type = m.type; o.n_pairs = (int)(m.N / 2); o.n_grp = n_groups(m.K); o.epi = epi; o.out = out; o.scale = scale; o.layer = layer; return o;
+        OpDesc o{}; o.w = m.w; o.type = m.type; o.n_pairs = (int)(m.N / 2); o.n_rows = (int)m.n_rows; o.n_grp = n_groups(m.K); o.epi = epi; o.out = out; o.scale = scale; o.layer = layer; return o;
     };
     auto gemv = [&](int K, int pro, const float* src, const float* nw, int layer, std::initializer_list<OpDesc> ops) {
         Phase p{}; p.kind = PH_GEMV; p.K = K; p.pro = pro; p.src = src; p.norm_w = nw; p.layer = layer; p.n_ops = 0; p.total_pairs = 0;
@@ -257,13 +262,13 @@ int Model::commit() {
     { Phase p{}; p.kind = PH_EMBED; ph.push_back(p); }
     for (int l = 0; l < n_layer; l++) {
         Layer& L = layers[l];
-        gemv(D, PRO_NORM, d_h, L.attn_norm, l, {mk_op(L.wq, EPI_ROPE_Q, d_q, 1.f, l), mk_op(L.wk, EPI_ROPE_K, nullptr, 1.f, l), mk_op(L.wv, EPI_V, nullptr, 1.f, l)});
+        gemv(D, PRO_NORM, nullptr, L.attn_norm, l, {mk_op(L.wq, EPI_ROPE_Q, nullptr, 1.f, l), mk_op(L.wk, EPI_ROPE_K, nullptr, 1.f, l), mk_op(L.wv, EPI_V, nullptr, 1.f, l)});
         { Phase p{}; p.kind = PH_ATTN; p.layer = l; ph.push_back(p); }
-        gemv(QD, PRO_ATTN, nullptr, nullptr, l, {mk_op(L.wo, EPI_RESID, d_h, rs, l)});
-        gemv(D, PRO_NORM, d_h, L.ffn_norm, l, {mk_op(L.wgu, EPI_SWIGLU, d_act, 1.f, l)});
-        gemv(F, PRO_PLAIN, d_act, nullptr, l, {mk_op(L.wd, EPI_RESID, d_h, rs, l)});
+        gemv(QD, PRO_ATTN, nullptr, nullptr, l, {mk_op(L.wo, EPI_RESID, nullptr, rs, l)});
+        gemv(D, PRO_NORM, nullptr, L.ffn_norm, l, {mk_op(L.wgu, EPI_SWIGLU, nullptr, 1.f, l)});
+        gemv(F, PRO_ACT, nullptr, nullptr, l, {mk_op(L.wd, EPI_RESID, nullptr, rs, l)});
     }
-    gemv(D, PRO_NORM, d_h, out_norm, 0, {mk_op(out_w, EPI_LOGITS, d_logits, logit_scale != 0.f ? 1.f / logit_scale : 1.f, 0)});
+    gemv(D, PRO_NORM, nullptr, out_norm, 0, {mk_op(out_w, EPI_LOGITS, d_logits, logit_scale != 0.f ? 1.f / logit_scale : 1.f, 0)});
     n_phases = (int)ph.size();
     if ((rc = own(&d_phases, ph.size()))) return rc;
     CK(cudaMemcpy(d_phases, ph.data(), ph.size() * sizeof(Phase), cudaMemcpyHostToDevice));
@@ -277,8 +282,12 @@ void Model::fill_params(DecodeParams& P) const {
     P.n_embd = n_embd; P.n_head = n_head; P.n_head_kv = n_head_kv; P.head_dim = head_dim; P.n_rot = n_rot; P.n_vocab = n_vocab; P.n_splits = n_splits;
     P.rms_eps = rms_eps; P.kq_scale = attn_scale != 0.f ? attn_scale : 1.0f / std::sqrt((float)head_dim); P.emb_scale = emb_scale;
     P.inv_freq = inv_freq; P.embd = tok_embd.w; P.embd_type = tok_embd.type;
-    P.h = d_h; P.q = d_q; P.act = d_act; P.logits = d_logits; P.part_acc = d_part_acc; P.part_ml = d_part_ml;
-    P.cand_val = d_cand_val; P.cand_idx = d_cand_idx;
+    P.logits = d_logits;
+    const size_t QD = (size_t)n_head * head_dim, KVD = (size_t)n_head_kv * head_dim;
+    P.h_stride = n_embd; P.att_stride = (int)QD; P.act_stride = n_ff;
+    P.h_ll = d_ll16; P.att_ll = P.h_ll + (size_t)XREP * n_embd; P.act_ll = P.att_ll + (size_t)XREP * QD; P.kv_ll = P.act_ll + (size_t)XREP * n_ff;
+    P.q_ll = d_ll32; P.part_ll = P.q_ll + QD; P.cand_ll = P.part_ll + (size_t)n_head * 16 * (head_dim + 2);
+    P.hown_cap = hown_cap; (void)KVD;
     P.kv.pages = d_kv; P.kv.block_table = d_block_table; P.kv.n_layer = n_layer; P.kv.n_head_kv = n_head_kv; P.kv.head_dim = head_dim;
     P.pos = d_state + 0; P.token = d_state + 1; P.bar_ctr = (unsigned*)(d_state + 2); P.epoch = (unsigned*)(d_state + 3);
     P.out_tokens = d_out_tokens; P.n_steps = 1; P.want_argmax = 1; P.trace = d_trace;
@@ -293,6 +302,11 @@ int Model::run_steps(int n_steps, const int32_t* forced, int n_forced, bool rese
     if (cur_pos + n_steps > E.max_ctx) return fail(B200_ERR_INVALID, "context overflow: " + std::to_string(cur_pos + n_steps) + " > max_ctx " + std::to_string(E.max_ctx));
     if (n_forced > 0) CK(cudaMemcpyAsync(d_forced, forced, (size_t)n_forced * 4, cudaMemcpyHostToDevice, E.stream));
     DecodeParams P; fill_params(P); P.n_steps = n_steps;
+    // context splits per head: as many (head, split) items as there are CTAs (each split is one memory round trip);
+    // split 0's CTA merges the partials of its head
+    P.n_splits = std::max(1, std::min({16, std::max(1, grid / n_head), (cur_pos + n_steps + 15) / 16}));
+    if (const char* e = getenv("B200_SPLITS")) P.n_splits = std::max(1, std::min({16, atoi(e), std::max(1, grid / n_head)}));
+    P.max_inflight = 2; if (const char* e = getenv("B200_INFLIGHT")) P.max_inflight = std::max(1, atoi(e));
     DecodeRun R{}; R.forced = d_forced; R.n_forced = n_forced; R.logits_all = logits_all_dev;
     LaunchCfg lc; lc.grid = grid; lc.ring_bytes = ring_bytes; lc.max_grp = smem_max_grp; lc.smem = smem_bytes;
     if (int rc = launch_decode(E, P, R, lc)) return rc;
@@ -387,7 +401,7 @@ int Model::bench_decode(int ctx_len, int n_steps, int warmup, float* ms_per_toke
     CK(cudaMemcpyAsync(d_state, st, 8, cudaMemcpyHostToDevice, E.stream)); cur_pos = ctx_len;
     cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     const char* trace_path = getenv("B200_TRACE");                 // debug: per-phase clock64 stamps of 4 CTAs
-    size_t trace_n = (size_t)n_steps * n_phases * 16;
+    size_t trace_n = (size_t)n_steps * n_phases * grid * 8;
     if (trace_path) { CK(cudaMalloc((void**)&d_trace, trace_n * 8)); CK(cudaMemsetAsync(d_trace, 0, trace_n * 8, E.stream)); }
     CK(cudaEventRecord(e0, E.stream));
     int rc = run_steps(n_steps, nullptr, 0, false, nullptr);
@@ -395,7 +409,7 @@ int Model::bench_decode(int ctx_len, int n_steps, int warmup, float* ms_per_toke
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1); cudaEventDestroy(e0); cudaEventDestroy(e1);
     if (trace_path) {
         std::vector<long long> tr(trace_n); cudaMemcpy(tr.data(), d_trace, trace_n * 8, cudaMemcpyDeviceToHost);
-        if (FILE* f = fopen(trace_path, "wb")) { int hdr[2] = {n_steps, n_phases}; fwrite(hdr, 4, 2, f); fwrite(tr.data(), 8, trace_n, f); fclose(f); }
+        if (FILE* f = fopen(trace_path, "wb")) { int hdr[3] = {n_steps, n_phases, grid}; fwrite(hdr, 4, 3, f); fwrite(tr.data(), 8, trace_n, f); fclose(f); }
         cudaFree(d_trace); d_trace = nullptr;
     }
     if (ms_per_token) *ms_per_token = ms / n_steps;
@@ -422,7 +436,7 @@ int kernel_dequantize(int type, const void* raw, int64_t n_rows, int K, float* o
     if ((rc = dalloc(&d_raw, (size_t)N * rb)) || (rc = dalloc(&d_w, repacked_bytes(type, N, K))) || (rc = dalloc(&d_out, (size_t)N * K))) { cudaFree(d_raw); cudaFree(d_w); cudaFree(d_out); return rc; }
     cudaMemsetAsync(d_raw, 0, (size_t)N * rb, E.stream);
     cudaMemcpyAsync(d_raw, raw, (size_t)n_rows * rb, cudaMemcpyHostToDevice, E.stream);
-    rc = repack(E, d_raw, d_w, type, N, K);
+    rc = repack(E, d_raw, d_w, type, N, n_rows, K);
     if (!rc) {
         dequant_repacked_kernel<<<std::min<long long>((N * K + 255) / 256, 148 * 16), 256, 0, E.stream>>>(d_w, type, N, K, d_out); E.launches++;
         cudaError_t e = cudaMemcpyAsync(out, d_out, (size_t)n_rows * K * 4, cudaMemcpyDeviceToHost, E.stream);
@@ -439,24 +453,24 @@ int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, flo
     if (N <= 0 || N % 2 || K <= 0 || K % 256) return fail(B200_ERR_INVALID, "N must be even and K a multiple of 256");
     if (iters < 1) iters = 1;
     size_t rb = raw_row_bytes(type, K);
-    uint8_t *d_raw = nullptr, *d_w = nullptr; float *d_x = nullptr, *d_y = nullptr, *d_cv = nullptr; int *d_ci = nullptr, *d_st = nullptr, *d_ot = nullptr; Phase* d_ph = nullptr;
+    uint8_t *d_raw = nullptr, *d_w = nullptr; float *d_x = nullptr, *d_y = nullptr; uint2* d_cv = nullptr; int *d_st = nullptr, *d_ot = nullptr; Phase* d_ph = nullptr;
     int rc = B200_OK;
     LaunchCfg lc;
-    auto cleanup = [&]() { cudaFree(d_raw); cudaFree(d_w); cudaFree(d_x); cudaFree(d_y); cudaFree(d_cv); cudaFree(d_ci); cudaFree(d_st); cudaFree(d_ot); cudaFree(d_ph); };
-    if ((rc = launch_cfg(E, n_groups(K), lc))) return rc;
+    auto cleanup = [&]() { cudaFree(d_raw); cudaFree(d_w); cudaFree(d_x); cudaFree(d_y); cudaFree(d_cv); cudaFree(d_st); cudaFree(d_ot); cudaFree(d_ph); };
+    if ((rc = launch_cfg(E, n_groups(K), 4, lc))) return rc;
     if ((rc = dalloc(&d_raw, (size_t)N * rb)) || (rc = dalloc(&d_w, repacked_bytes(type, N, K))) || (rc = dalloc(&d_x, (size_t)K)) || (rc = dalloc(&d_y, (size_t)N)) ||
-        (rc = dalloc(&d_cv, (size_t)lc.grid)) || (rc = dalloc(&d_ci, (size_t)lc.grid)) || (rc = dalloc(&d_st, (size_t)16)) || (rc = dalloc(&d_ot, (size_t)iters + 1)) || (rc = dalloc(&d_ph, (size_t)1))) { cleanup(); return rc; }
+        (rc = dalloc(&d_cv, (size_t)2 * lc.grid)) || (rc = dalloc(&d_st, (size_t)16)) || (rc = dalloc(&d_ot, (size_t)iters + 1)) || (rc = dalloc(&d_ph, (size_t)1))) { cleanup(); return rc; }
     cudaMemcpyAsync(d_raw, raw, (size_t)N * rb, cudaMemcpyHostToDevice, E.stream);
     cudaMemcpyAsync(d_x, x, (size_t)K * 4, cudaMemcpyHostToDevice, E.stream);
     cudaMemsetAsync(d_st, 0, 64, E.stream);
-    rc = repack(E, d_raw, d_w, type, N, K);
+    rc = repack(E, d_raw, d_w, type, N, N, K);
     if (!rc) {
         Phase p{}; p.kind = PH_GEMV; p.K = K; p.pro = PRO_PLAIN; p.src = d_x; p.n_ops = 1; p.total_pairs = (int)(N / 2);
-        p.op[0].w = d_w; p.op[0].type = type; p.op[0].n_pairs = (int)(N / 2); p.op[0].n_grp = n_groups(K); p.op[0].epi = EPI_STORE; p.op[0].out = d_y; p.op[0].scale = 1.f;
+        p.op[0].w = d_w; p.op[0].type = type; p.op[0].n_pairs = (int)(N / 2); p.op[0].n_rows = (int)N; p.op[0].n_grp = n_groups(K); p.op[0].epi = EPI_STORE; p.op[0].out = d_y; p.op[0].scale = 1.f;
         cudaMemcpyAsync(d_ph, &p, sizeof p, cudaMemcpyHostToDevice, E.stream);
         DecodeParams P{}; P.phases = d_ph; P.n_phases = 1; P.n_embd = K; P.n_head = 1; P.n_head_kv = 1; P.head_dim = 128; P.n_vocab = (int)N; P.n_splits = 1;
-        P.cand_val = d_cv; P.cand_idx = d_ci; P.pos = d_st; P.token = d_st + 1; P.bar_ctr = (unsigned*)(d_st + 2); P.epoch = (unsigned*)(d_st + 3); P.out_tokens = d_ot;
-        P.logits = d_y; P.n_steps = 1;
+        P.cand_ll = d_cv; P.hown_cap = 4; P.pos = d_st; P.token = d_st + 1; P.bar_ctr = (unsigned*)(d_st + 2); P.epoch = (unsigned*)(d_st + 3); P.out_tokens = d_ot;
+        P.logits = d_y; P.n_steps = 1; P.max_inflight = 2; if (const char* e = getenv("B200_INFLIGHT")) P.max_inflight = std::max(1, atoi(e));
         // every step "forced" (token 0): no argmax traffic; forced[] = d_ot, zeroed, iters+1 ints
         cudaMemsetAsync(d_ot, 0, ((size_t)iters + 1) * 4, E.stream);
         DecodeRun R{}; R.forced = d_ot; R.n_forced = iters + 1;

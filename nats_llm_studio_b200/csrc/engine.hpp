@@ -25,7 +25,7 @@ struct Phase;
 extern thread_local std::string g_last_error;
 int fail(int code, const std::string& msg);
 
-struct Matrix { uint8_t* w = nullptr; int type = 0; int64_t N = 0; int K = 0; };
+struct Matrix { uint8_t* w = nullptr; int type = 0; int64_t N = 0, n_rows = 0; int K = 0; };
 struct Layer { float* attn_norm = nullptr; float* ffn_norm = nullptr; Matrix wq, wk, wv, wo, wgu, wd; };
 
 struct Engine {
@@ -56,8 +56,8 @@ struct Model {
     Matrix tok_embd, out_w; float* out_norm = nullptr; float* inv_freq = nullptr; std::vector<Layer> layers;
     // runtime
     Phase* d_phases = nullptr; int n_phases = 0;
-    float *d_h = nullptr, *d_q = nullptr, *d_act = nullptr, *d_logits = nullptr, *d_part_acc = nullptr, *d_part_ml = nullptr, *d_cand_val = nullptr;
-    int *d_cand_idx = nullptr, *d_state = nullptr, *d_out_tokens = nullptr, *d_forced = nullptr, *d_block_table = nullptr;
+    float* d_logits = nullptr; uint32_t* d_ll16 = nullptr; uint2* d_ll32 = nullptr; int hown_cap = 0;
+    int *d_state = nullptr, *d_out_tokens = nullptr, *d_forced = nullptr, *d_block_table = nullptr;
     __half* d_kv = nullptr; int n_pages = 0, n_splits = 1;
     int grid = 0, smem_max_grp = 0; uint32_t ring_bytes = 0; size_t smem_bytes = 0;
     int cur_pos = 0;

@@ -27,6 +27,8 @@ constexpr int CONSUMER_THREADS = CONSUMER_WARPS * 32;
 constexpr int CTA_THREADS = CONSUMER_THREADS + 32;
 constexpr int PAIRS_PER_STAGE = CONSUMER_WARPS;
 constexpr int NSLOT = 8;                 // mbarrier pairs in flight
+constexpr int XREP = 8;                  // copies of every broadcast exchange vector (an L2 slice serves ~1 sector/clk: one copy read by
+                                         // every CTA costs ~0.6 us per line; CTA c reads copy c % XREP)
 constexpr int MAX_STAGE_BYTES = PAIRS_PER_STAGE * 2 * 2176;   // Q8_0 is the widest unit
 
 // ------------------------------------------------------------------------------------ PTX
@@ -78,13 +80,14 @@ __device__ __forceinline__ float warp_sum(float v) {
 
 // ------------------------------------------------------------------------------------ descriptors
 enum Epilogue : int { EPI_STORE = 0, EPI_ROPE_Q, EPI_ROPE_K, EPI_V, EPI_RESID, EPI_SWIGLU, EPI_LOGITS };
-enum Prologue : int { PRO_PLAIN = 0, PRO_NORM, PRO_ATTN };
+enum Prologue : int { PRO_PLAIN = 0, PRO_NORM, PRO_ATTN, PRO_ACT };   // PLAIN: fp32 src (GEMV entry point); others poll tagged vectors
 enum PhaseKind : int { PH_GEMV = 0, PH_ATTN, PH_EMBED };
 
 struct OpDesc {                 // one streamed matrix (engine layout, quant.cuh)
     const uint8_t* w;
     int type, n_pairs, n_grp, epi;
-    float* out;                 // EPI_STORE / RESID / SWIGLU / LOGITS / ROPE_Q destination
+    int n_rows;                 // valid rows (2*n_pairs, or one less when an odd matrix was padded)
+    float* out;                 // EPI_STORE destination
     float scale;                // output scale (residual_scale, 1/logit_scale, 1)
     int layer;                  // for KV epilogues
 };
@@ -92,7 +95,7 @@ struct OpDesc {                 // one streamed matrix (engine layout, quant.cuh
 struct Phase {
     int kind, n_ops, total_pairs, K;
     int pro; int layer;
-    const float* src;           // prologue source vector (h, act) — fp32 [K]
+    const float* src;           // PRO_PLAIN source vector — fp32 [K] (kernel-level GEMV entry point)
     const float* norm_w;        // PRO_NORM weight
     OpDesc op[3];
 };
@@ -117,14 +120,17 @@ struct DecodeParams {
     // embedding
     const uint8_t* embd; int embd_type;   // engine layout
     // buffers
-    float* h; float* q; float* act; float* logits;
-    float* part_acc; float* part_ml;      // attention partials [n_head][n_splits][head_dim], [..][2]
-    float* cand_val; int* cand_idx;       // per-CTA argmax candidates
+    float* logits;
+    // tagged exchange vectors (decode.cuh): LL16 = uint32 {tag16, fp16}, LL32 = uint2 {bits, tag32}
+    uint32_t* h_ll; uint32_t* att_ll; uint32_t* act_ll; uint32_t* kv_ll;   // [XREP][n_embd], [XREP][n_head*head_dim], [XREP][n_ff], [2*n_head_kv*head_dim]
+    int h_stride, att_stride, act_stride;                                   // words between copies
+    uint2* q_ll; uint2* part_ll; uint2* cand_ll;                            // [n_head*head_dim], [n_head][16][head_dim+2], [2*grid]
+    int hown_cap;                                                           // floats of owned hidden-state rows per CTA
     KvLayout kv;
     // run state (device memory)
     int* pos; int* token; int* out_tokens; unsigned* bar_ctr; unsigned* epoch;
-    int n_steps; int want_argmax;
-    long long* trace;           // optional [n_steps][n_phases][4 sampled CTAs][4] clock64 stamps (debug)
+    int n_steps; int want_argmax; int max_inflight;
+    long long* trace;           // optional [n_steps][n_phases][grid][4]: clock64 at phase start / prologue end / phase end, smid (debug)
 };
 
 // ------------------------------------------------------------------------------------ smem carve-up
@@ -134,27 +140,30 @@ struct Smem {
     uint64_t* full; uint64_t* empty;
     float* red;                               // 64 floats of reduction scratch
     uint32_t* q_end;                          // producer's in-flight stage sizes [NSLOT]
+    float* hown;                              // fp32 hidden-state rows this CTA owns (residual stream never leaves the SM)
 };
 __host__ __device__ inline size_t smem_x_bytes(int max_grp) { return (size_t)max_grp * (2048 + 256 + 32); }
-__host__ __device__ inline size_t smem_misc_bytes() { return NSLOT * 16 + 64 * 4 + NSLOT * 4 + 64; }
-__device__ inline Smem carve_smem(uint8_t* base, uint32_t ring_bytes, int max_grp) {
+__host__ __device__ inline size_t smem_misc_bytes(int hown_cap) { return NSLOT * 16 + 64 * 4 + NSLOT * 4 + (size_t)hown_cap * 4 + 64; }
+__device__ inline Smem carve_smem(uint8_t* base, uint32_t ring_bytes, int max_grp, int hown_cap) {
     Smem s; s.ring = base; s.ring_bytes = ring_bytes; uint8_t* p = base + ring_bytes;
     s.xq = (int8_t*)p; p += (size_t)max_grp * 2048;
     s.xbs = (int16_t*)p; p += (size_t)max_grp * 256;
     s.xd = (float*)p; p += (size_t)max_grp * 32;
     s.full = (uint64_t*)p; p += NSLOT * 8; s.empty = (uint64_t*)p; p += NSLOT * 8;
-    s.red = (float*)p; p += 64 * 4; s.q_end = (uint32_t*)p;
+    s.red = (float*)p; p += 64 * 4; s.q_end = (uint32_t*)p; p += NSLOT * 4; s.hown = (float*)p;
     return s;
 }
 
 // Deterministic ring allocator state; producer and consumers evolve identical copies.
 struct RingCursor {
     uint32_t seq;        // stage sequence number
-    uint64_t head;       // virtual byte counter (includes wrap gaps)
+    uint32_t off;        // byte offset where the next stage would start
+    __device__ __forceinline__ void init() { seq = 0; off = 0; }
+    // stages never straddle the wrap point: a stage that does not fit behind `off` starts at 0 and leaves a gap
     __device__ __forceinline__ uint32_t place(uint32_t bytes, uint32_t ring_bytes, uint32_t& gap) {
-        uint32_t off = (uint32_t)(head % ring_bytes); gap = 0;
+        gap = 0;
         if (off + bytes > ring_bytes) { gap = ring_bytes - off; off = 0; }
-        head += gap + bytes; return off;
+        const uint32_t at = off; off += bytes; return at;
     }
 };
 
@@ -165,8 +174,9 @@ __device__ __forceinline__ void cta_slice(int total, int c, int G, int& lo, int&
 
 // ------------------------------------------------------------------------------------ producer
 struct Producer {
-    RingCursor cur; uint64_t tail; uint32_t oldest;   // oldest unreleased stage seq
-    __device__ void init() { cur.seq = 0; cur.head = 0; tail = 0; oldest = 0; }
+    RingCursor cur; uint32_t used, oldest;            // bytes held by unreleased stages (incl. gaps); oldest unreleased stage
+    uint32_t landed, max_unlanded;                    // stages whose bytes have all arrived; cap on issued-but-unlanded stages
+    __device__ void init(int inflight) { cur.init(); used = 0; oldest = 0; landed = 0; max_unlanded = (uint32_t)max(1, inflight); }
 
     // called by the whole producer warp
     __device__ void run_phase(const Phase& ph, const Smem& sm, int c, int G, int lane) {
@@ -178,32 +188,33 @@ struct Producer {
             if (a >= b) continue;
             const uint32_t pu = 2u * group_bytes(op.type);
             for (int rb = a; rb < b; rb += PAIRS_PER_STAGE) {
-                int np = min(PAIRS_PER_STAGE, b - rb);
-                for (int g = 0; g < op.n_grp; g++) {
-                    uint32_t bytes = np * pu, gap;
-                    uint32_t slot = cur.seq % NSLOT;
+                const int np = min(PAIRS_PER_STAGE, b - rb);
+                const uint8_t* src = op.w + (size_t)(rb + min(lane, np - 1)) * op.n_grp * pu;
+                for (int g = 0; g < op.n_grp; g++, src += pu) {
+                    const uint32_t bytes = np * pu, slot = cur.seq % NSLOT;
+                    // (0) keep the number of un-landed stages small: other L2 accesses of this SM queue behind its
+                    //     outstanding bulk bytes; landed-but-unconsumed stages may still pile up to the ring's capacity
+                    while (cur.seq - landed >= max_unlanded) { mbar_wait(&sm.full[landed % NSLOT], (landed / NSLOT) & 1); landed++; }
                     // (1) barrier slot reuse: stage seq-NSLOT must be fully consumed
                     while (cur.seq - oldest >= NSLOT) release_oldest(sm);
-                    // (2) ring space
-                    {   uint32_t o2 = (uint32_t)(cur.head % sm.ring_bytes); uint32_t gp = (o2 + bytes > sm.ring_bytes) ? sm.ring_bytes - o2 : 0;
-                        while (cur.head + gp + bytes - tail > sm.ring_bytes) release_oldest(sm); }
-                    uint32_t soff = cur.place(bytes, sm.ring_bytes, gap);
+                    // (2) ring space (the stage plus the gap it would leave at the wrap point)
+                    const uint32_t gp = (cur.off + bytes > sm.ring_bytes) ? sm.ring_bytes - cur.off : 0;
+                    while (used + gp + bytes > sm.ring_bytes) release_oldest(sm);
+                    uint32_t gap; const uint32_t soff = cur.place(bytes, sm.ring_bytes, gap);
+                    used += gap + bytes;
                     __syncwarp();                 // every lane is done reading q_end[] of released stages
                     if (lane == 0) { sm.q_end[slot] = gap + bytes; mbar_expect_tx(&sm.full[slot], bytes); }
                     __syncwarp();
-                    if (lane < np) {
-                        const uint8_t* src = op.w + ((size_t)(rb + lane) * op.n_grp + g) * pu;
-                        bulk_g2s(sm.ring + soff + lane * pu, src, pu, &sm.full[slot]);
-                    }
+                    if (lane < np) bulk_g2s(sm.ring + soff + lane * pu, src, pu, &sm.full[slot]);
                     cur.seq++;
                 }
             }
         }
     }
     __device__ void release_oldest(const Smem& sm) {
-        uint32_t slot = oldest % NSLOT;
+        const uint32_t slot = oldest % NSLOT;
         mbar_wait(&sm.empty[slot], (oldest / NSLOT) & 1);
-        tail += sm.q_end[slot]; oldest++;
+        used -= sm.q_end[slot]; oldest++;
     }
     // before the CTA exits every issued copy must have landed and been consumed
     __device__ void drain(const Smem& sm) { while (oldest < cur.seq) release_oldest(sm); }
@@ -237,7 +248,7 @@ __device__ __forceinline__ float half16_max(float a) {   // max over the aligned
     return a;
 }
 
-constexpr int MAX_RUNS_PER_THREAD = 8;   // K <= 8*256*16 = 32768
+constexpr int NORM_RUNS = 1;             // RMSNorm inputs up to 256*16 = 4096 wide stay in registers between the two passes (wider: re-polled)
 
 // Consumers only (tid 0..255).  `load(u, v)` fills v[16] with activations [16u, 16u+16) (already
 // normalised / combined); runs beyond K are zero padding.  type: weight type of the phase's ops.
@@ -300,6 +311,17 @@ __device__ __forceinline__ void load_x(const Smem& sm, int g, int lane, XRegs& x
 }
 __device__ __forceinline__ uint32_t u4_get(const uint4& v, int i) { return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w; }
 
+// 6-bit scale / min unpack for sub-blocks 2j, 2j+1 of a K-quant super-block (gguf/quants.py:480-503), branch-free:
+// both sub-blocks of lane j live in the same two byte columns (2(j&1), 2(j&1)+1) of the three scale words.
+__device__ __forceinline__ void k4_scales(const uint4& hdr, int j, int& sc0, int& sc1, int& m0, int& m1) {
+    const int sh = (j & 1) << 4;
+    const uint32_t a = hdr.y >> sh, b = hdr.z >> sh, c = hdr.w >> sh;          // low 16 bits: the two bytes of interest
+    const uint32_t sc_lo = a & 0x3F3Fu, m_lo = b & 0x3F3Fu;                                     // sub-blocks 0..3
+    const uint32_t sc_hi = (c & 0x0F0Fu) | ((a >> 2) & 0x3030u), m_hi = ((c >> 4) & 0x0F0Fu) | ((b >> 2) & 0x3030u);   // 4..7
+    const uint32_t sc = j < 2 ? sc_lo : sc_hi, m = j < 2 ? m_lo : m_hi;
+    sc0 = sc & 0xFF; sc1 = sc >> 8; m0 = m & 0xFF; m1 = m >> 8;
+}
+
 __device__ __forceinline__ float lane_dot_q4k(const uint8_t* grp, int lane, const XRegs& x) {
     const uint8_t* blk = grp + (lane >> 2) * 144; const int j = lane & 3;
     const uint4 hdr = *(const uint4*)blk;                       // d, dmin, scales[12]
@@ -315,19 +337,7 @@ __device__ __forceinline__ float lane_dot_q4k(const uint8_t* grp, int lane, cons
         s1 = dp4a_us(w & 0xF0F0F0F0u, (int)u4_get(x.p[3], i), s1);
     }
     s1 >>= 4;                                                  // exact: every term is a multiple of 16
-    // 6-bit scale / min unpack for sub-blocks 2j, 2j+1 (gguf/quants.py:480-503)
-    const uint32_t w0 = hdr.y, w1 = hdr.z, w2 = hdr.w;
-    int sc0, sc1, m0, m1;
-    if (j < 2) {
-        const int sh = 16 * j;
-        sc0 = (w0 >> sh) & 63; sc1 = (w0 >> (sh + 8)) & 63; m0 = (w1 >> sh) & 63; m1 = (w1 >> (sh + 8)) & 63;
-    } else {
-        const int sh = 16 * (j - 2);
-        sc0 = ((w2 >> sh) & 0xF) | (((w0 >> (sh + 6)) & 3) << 4);
-        sc1 = ((w2 >> (sh + 8)) & 0xF) | (((w0 >> (sh + 14)) & 3) << 4);
-        m0 = ((w2 >> (sh + 4)) & 0xF) | (((w1 >> (sh + 6)) & 3) << 4);
-        m1 = ((w2 >> (sh + 12)) & 0xF) | (((w1 >> (sh + 14)) & 3) << 4);
-    }
+    int sc0, sc1, m0, m1; k4_scales(hdr, j, sc0, sc1, m0, m1);
     const int isum = sc0 * s0 + sc1 * s1;
     const int msum = m0 * (x.bs[0] + x.bs[1]) + m1 * (x.bs[2] + x.bs[3]);
     const float2 dd = __half22float2(*(const __half2*)&hdr.x);
@@ -349,18 +359,7 @@ __device__ __forceinline__ float lane_dot_q5k(const uint8_t* grp, int lane, cons
         s0 = dp4a_ss((int)((w & 0x0F0F0F0Fu) | ((h & 0x01010101u) << 4)), (int)u4_get(x.p[1], i), s0);
         s1 = dp4a_ss((int)(((w >> 4) & 0x0F0F0F0Fu) | ((h & 0x02020202u) << 3)), (int)u4_get(x.p[3], i), s1);
     }
-    const uint32_t w0 = hdr.y, w1 = hdr.z, w2 = hdr.w;
-    int sc0, sc1, m0, m1;
-    if (j < 2) {
-        const int sh = 16 * j;
-        sc0 = (w0 >> sh) & 63; sc1 = (w0 >> (sh + 8)) & 63; m0 = (w1 >> sh) & 63; m1 = (w1 >> (sh + 8)) & 63;
-    } else {
-        const int sh = 16 * (j - 2);
-        sc0 = ((w2 >> sh) & 0xF) | (((w0 >> (sh + 6)) & 3) << 4);
-        sc1 = ((w2 >> (sh + 8)) & 0xF) | (((w0 >> (sh + 14)) & 3) << 4);
-        m0 = ((w2 >> (sh + 4)) & 0xF) | (((w1 >> (sh + 6)) & 3) << 4);
-        m1 = ((w2 >> (sh + 12)) & 0xF) | (((w1 >> (sh + 14)) & 3) << 4);
-    }
+    int sc0, sc1, m0, m1; k4_scales(hdr, j, sc0, sc1, m0, m1);
     const int isum = sc0 * s0 + sc1 * s1;
     const int msum = m0 * (x.bs[0] + x.bs[1]) + m1 * (x.bs[2] + x.bs[3]);
     const float2 dd = __half22float2(*(const __half2*)&hdr.x);
@@ -401,13 +400,12 @@ __device__ __forceinline__ float lane_dot_q80(const uint8_t* grp, int lane, cons
     return x.dx * (dd.x * (float)s0 + dd.y * (float)s1);
 }
 
-__device__ __forceinline__ float lane_dot(int type, const uint8_t* grp, int lane, const XRegs& x) {
-    switch (type) {
-        case T_Q4_K: return lane_dot_q4k(grp, lane, x);
-        case T_Q6_K: return lane_dot_q6k(grp, lane, x);
-        case T_Q8_0: return lane_dot_q80(grp, lane, x);
-        default: return lane_dot_q5k(grp, lane, x);
-    }
+template <int TYPE>
+__device__ __forceinline__ float lane_dot(const uint8_t* grp, int lane, const XRegs& x) {
+    if constexpr (TYPE == T_Q4_K) return lane_dot_q4k(grp, lane, x);
+    else if constexpr (TYPE == T_Q6_K) return lane_dot_q6k(grp, lane, x);
+    else if constexpr (TYPE == T_Q8_0) return lane_dot_q80(grp, lane, x);
+    else return lane_dot_q5k(grp, lane, x);
 }
 
 }  // namespace b200

@@ -76,12 +76,18 @@ def _check(rc):
     return rc
 
 
-def _string_call(fn, *args):
+def _string_call(fn, *args, cap=1 << 20):
+    """Calls fn(*args, buf, cap, &need) once with a generous buffer (handlers EXECUTE the request on every
+    call, so a size-probing first call would run it twice); grows and retries only if it did not fit."""
     need = sz(0)
-    _check(fn(*args, None, 0, C.byref(need)))
-    buf = C.create_string_buffer(need.value + 1)
-    _check(fn(*args, buf, need.value + 1, C.byref(need)))
-    return buf.raw[:need.value]
+    while True:
+        buf = C.create_string_buffer(cap)
+        rc = fn(*args, buf, cap, C.byref(need))
+        if rc == -6 and need.value >= cap:
+            cap = need.value + 1
+            continue
+        _check(rc)
+        return buf.raw[:need.value]
 
 
 class Model:

@@ -166,6 +166,8 @@ typedef struct orc_model {
     int kv_cap, n_past; float *kc, *vc;
     int act_quant;   /* 0: fp32 activations.  1: Q8 (per-256 block) activations, the engine's GEMV numerics */
     int kv_f16;      /* 1: round cached K/V through binary16 like the engine's KV cache */
+    int xchg_f16;    /* 1: round the vectors the engine exchanges between SMs (hidden state as seen by the norms,
+                        attention output, SwiGLU output) through binary16, as the engine's tagged fp16 words do */
 } orc_model;
 
 typedef struct { const uint8_t *p, *end; int err; } rdr;
@@ -285,6 +287,7 @@ int orc_n_layer(const orc_model *m) { return m->n_layer; }
 int orc_n_past(const orc_model *m) { return m->n_past; }
 void orc_set_act_quant(orc_model *m, int mode) { m->act_quant = mode; }
 void orc_set_kv_f16(orc_model *m, int on) { m->kv_f16 = on; }
+void orc_set_xchg_f16(orc_model *m, int on) { m->xchg_f16 = on; }
 void orc_set_threads(int n) {
 #ifdef _OPENMP
     if (n > 0) omp_set_num_threads(n);
@@ -359,6 +362,10 @@ static void matvec(const orc_model *m, const orc_tensor *w, const float *x_in, f
     free(xq);
 }
 
+static uint16_t fp32_to_fp16(float f);
+static void round_f16(const float *x, float *y, int n) {
+    for (int i = 0; i < n; i++) { float v = x[i]; if (v > 65504.f) v = 65504.f; if (v < -65504.f) v = -65504.f; y[i] = fp16_to_fp32(fp32_to_fp16(v)); }
+}
 static void rmsnorm(const float *x, const float *g, float *y, int n, float eps) {
     double ss = 0; for (int i = 0; i < n; i++) ss += (double)x[i] * x[i];
     float sc = (float)(1.0 / sqrt(ss / n + (double)eps));
@@ -385,7 +392,7 @@ int orc_eval_token(orc_model *m, int32_t tok, float *logits) {
         }
         free(m->kc); free(m->vc); m->kc = nk; m->vc = nv; m->kv_cap = ncap;
     }
-    float *h = (float *)malloc((size_t)D * 4), *x = (float *)malloc((size_t)D * 4), *q = (float *)malloc((size_t)H * HD * 4);
+    float *h = (float *)malloc((size_t)D * 4), *hx = (float *)malloc((size_t)D * 4), *x = (float *)malloc((size_t)D * 4), *q = (float *)malloc((size_t)H * HD * 4);
     float *att = (float *)malloc((size_t)H * HD * 4), *o = (float *)malloc((size_t)D * 4);
     float *g = (float *)malloc((size_t)F * 4), *u = (float *)malloc((size_t)F * 4), *nw = (float *)malloc((size_t)(D > F ? D : F) * 4);
     double *sc = (double *)malloc((size_t)(pos + 1) * 8);
@@ -404,7 +411,8 @@ int orc_eval_token(orc_model *m, int32_t tok, float *logits) {
             *wd = layer_tensor(m, l, "ffn_down.weight");
         if (!an || !wq || !wk || !wv || !wo || !fn || !wg || !wu || !wd) { rc = -1; break; }
         float *kc = m->kc + ((size_t)l * m->kv_cap + pos) * KVD, *vc = m->vc + ((size_t)l * m->kv_cap + pos) * KVD;
-        orc_dequantize(an->type, an->data, D, nw); rmsnorm(h, nw, x, D, m->rms_eps);
+        orc_dequantize(an->type, an->data, D, nw);
+        if (m->xchg_f16) { round_f16(h, hx, D); rmsnorm(hx, nw, x, D, m->rms_eps); } else rmsnorm(h, nw, x, D, m->rms_eps);
         matvec(m, wq, x, q, H * HD, D); matvec(m, wk, x, kc, KVD, D); matvec(m, wv, x, vc, KVD, D);
         /* RoPE, adjacent-pair ("NORM") form: theta_i = pos * base^(-2i/n_rot) / freq_factor_i */
         for (int hh = 0; hh < H + HK; hh++) {
@@ -431,11 +439,14 @@ int orc_eval_token(orc_model *m, int32_t tok, float *logits) {
                 att[(size_t)hh * HD + d] = (float)(a / sum);
             }
         }
+        if (m->xchg_f16) round_f16(att, att, H * HD);
         matvec(m, wo, att, o, D, H * HD);
         for (int i = 0; i < D; i++) h[i] += o[i] * res;
-        orc_dequantize(fn->type, fn->data, D, nw); rmsnorm(h, nw, x, D, m->rms_eps);
+        orc_dequantize(fn->type, fn->data, D, nw);
+        if (m->xchg_f16) { round_f16(h, hx, D); rmsnorm(hx, nw, x, D, m->rms_eps); } else rmsnorm(h, nw, x, D, m->rms_eps);
         matvec(m, wg, x, g, F, D); matvec(m, wu, x, u, F, D);
         for (int i = 0; i < F; i++) g[i] = (float)((double)g[i] / (1.0 + exp(-(double)g[i]))) * u[i];
+        if (m->xchg_f16) round_f16(g, g, F);
         matvec(m, wd, g, o, D, F);
         for (int i = 0; i < D; i++) h[i] += o[i] * res;
     }
@@ -444,12 +455,13 @@ int orc_eval_token(orc_model *m, int32_t tok, float *logits) {
         const orc_tensor *on = find_tensor(m, "output_norm.weight"), *ow = find_tensor(m, "output.weight");
         if (!ow) ow = te;   /* tied embeddings (granite) */
         if (!on) rc = -1; else {
-            orc_dequantize(on->type, on->data, D, nw); rmsnorm(h, nw, x, D, m->rms_eps);
+            orc_dequantize(on->type, on->data, D, nw);
+            if (m->xchg_f16) { round_f16(h, hx, D); rmsnorm(hx, nw, x, D, m->rms_eps); } else rmsnorm(h, nw, x, D, m->rms_eps);
             matvec(m, ow, x, logits, V, D);
             if (m->logit_scale != 0.0f) { float inv = 1.0f / m->logit_scale; for (int i = 0; i < V; i++) logits[i] *= inv; }
         }
     }
-    free(h); free(x); free(q); free(att); free(o); free(g); free(u); free(nw); free(sc);
+    free(h); free(hx); free(x); free(q); free(att); free(o); free(g); free(u); free(nw); free(sc);
     return rc;
 }
 

@@ -25,7 +25,7 @@ def lib():
         L.orc_dequantize.argtypes = [ci, vp, ctypes.c_int64, vp]
         for f in ("orc_n_vocab", "orc_n_embd", "orc_n_layer", "orc_n_past"):
             getattr(L, f).argtypes = [vp]
-        L.orc_set_act_quant.argtypes = [vp, ci]; L.orc_set_kv_f16.argtypes = [vp, ci]
+        L.orc_set_act_quant.argtypes = [vp, ci]; L.orc_set_kv_f16.argtypes = [vp, ci]; L.orc_set_xchg_f16.argtypes = [vp, ci]
         L.orc_set_threads.argtypes = [ci]
         L.orc_reset.argtypes = [vp]
         L.orc_eval_token.argtypes = [vp, ctypes.c_int32, vp]
@@ -46,13 +46,15 @@ def dequantize(type_name, raw, n_elems):
 
 
 class Model:
-    def __init__(self, path, act_quant=0, kv_f16=0):
+    def __init__(self, path, act_quant=0, kv_f16=0, xchg_f16=None):
         self.h = lib().orc_load(path.encode())
         if not self.h:
             raise RuntimeError(f"oracle could not load {path}")
         self.n_vocab = lib().orc_n_vocab(self.h)
         self.n_embd = lib().orc_n_embd(self.h)
         lib().orc_set_act_quant(self.h, act_quant); lib().orc_set_kv_f16(self.h, kv_f16)
+        # engine numerics = int8 activations + fp16 KV + fp16 exchange vectors; xchg follows act_quant unless given
+        lib().orc_set_xchg_f16(self.h, int(act_quant if xchg_f16 is None else xchg_f16))
 
     def close(self):
         if self.h:

@@ -1,20 +1,23 @@
-"""Summarise a B200_TRACE dump: per-phase-kind mean cycles for prologue / stream / barrier (4 sampled CTAs)."""
+"""Summarise a B200_TRACE dump (globaltimer ns).  Stamps per (step, phase, CTA): 0 start, 1 inputs polled, 2 rms known,
+3 prologue done, 4 first stage landed (warp 0), 5 stream loop done (warp 0), 6 phase done, 7 smid."""
 import sys
 import numpy as np
 raw = open(sys.argv[1], "rb").read()
-n_steps, n_phases = np.frombuffer(raw[:8], dtype=np.int32)
-t = np.frombuffer(raw[8:], dtype=np.int64).reshape(n_steps, n_phases, 4, 4)
-mhz = float(sys.argv[2]) if len(sys.argv) > 2 else 1965.0
-t = t[1:]                                            # skip first step
-pro = (t[..., 1] - t[..., 0]) / mhz; stream = (t[..., 2] - t[..., 1]) / mhz; bar = (t[..., 3] - t[..., 2]) / mhz
-# phase index pattern: 0 embed, then per layer 5 phases (qkv, attn, wo, gu, down), last lm
+n_steps, n_phases, G = np.frombuffer(raw[:12], dtype=np.int32)
+t = np.frombuffer(raw[12:], dtype=np.int64).reshape(n_steps, n_phases, G, 8).astype(np.float64)[1:] / 1e3
 names = ["embed"] + ["qkv", "attn", "wo", "gate_up", "down"] * ((n_phases - 2) // 5) + ["lm_head"]
-print(f"{'phase':8s} {'prologue':>9s} {'stream':>9s} {'barrier':>9s} {'total':>9s}  us (mean over steps, layers, 4 CTAs); per-CTA stream max-min")
+end = t[..., 6]
+print(f"{'phase':8s} {'poll':>6s} {'rms':>6s} {'quant':>6s} {'1stld':>6s} {'strm':>6s} {'epi':>6s} | {'total':>6s} | {'wall':>7s} {'skew':>6s}   us, medians over CTAs with work; wall = last end - previous phase's last end")
 tot = 0
 for kind in ["embed", "qkv", "attn", "wo", "gate_up", "down", "lm_head"]:
     idx = [i for i, n in enumerate(names) if n == kind]
-    p, s, b = pro[:, idx].mean(), stream[:, idx].mean(), bar[:, idx].mean()
-    spread = (stream[:, idx].max(axis=2) - stream[:, idx].min(axis=2)).mean()
-    tot += (p + s + b) * len(idx)
-    print(f"{kind:8s} {p:9.2f} {s:9.2f} {b:9.2f} {p+s+b:9.2f}   x{len(idx)}  spread {spread:.2f}")
-print(f"sum over phases: {tot:.1f} us/token")
+    x = t[:, idx]
+    d = [np.median(x[..., k + 1] - x[..., k]) for k in range(6)]
+    prev = [i - 1 for i in idx]
+    wall = (end[:, idx].max(axis=2) - (end[:, prev].max(axis=2) if idx[0] > 0 else t[:, idx, :, 0].min(axis=2)))
+    if idx[0] == 0 and n_steps > 2:   # embed follows the previous step's lm_head
+        wall = end[1:, idx].max(axis=2) - end[:-1, [n_phases - 1]].max(axis=2)
+    skew = end[:, idx].max(axis=2) - np.median(end[:, idx], axis=2)
+    tot += wall.mean() * len(idx)
+    print(f"{kind:8s} " + " ".join(f"{v:6.2f}" for v in d) + f" | {np.median(x[..., 6] - x[..., 0]):6.2f} | {wall.mean():7.2f} {np.median(skew):6.2f}  x{len(idx)}")
+print(f"sum of phase wall times: {tot:.1f} us/token")
