@@ -12,6 +12,8 @@
 // megabytes of bulk traffic (measured: ~4 us per round trip with a 27 MB backlog).
 // Buffer-reuse safety (single buffers suffice) is argued in DESIGN.md §3.1.
 #pragma once
+#include <type_traits>
+
 #include "stream.cuh"
 
 namespace b200 {
@@ -77,13 +79,32 @@ __device__ __forceinline__ float embed_elem(const uint8_t* w, int type, int n_gr
 }
 
 // ------------------------------------------------------------------------------------ attention (bs1)
-// One item = (head, split).  Warps stride over positions in batches of NB for memory-level parallelism.
+// One item = (head, split).  Each warp owns a strided set of positions and keeps NB of them in flight at once; the
+// cached K/V loads are issued BEFORE q is polled (they do not depend on this token), so the exchange wait and the
+// first memory round trip overlap.
 template <int VEC>   // head_dim = 32*VEC
 __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int head, int split, int pos, uint32_t seq_in, uint32_t seq_out, int warp, int lane) {
-    constexpr int HD = 32 * VEC, NB = 4;
+    constexpr int HD = 32 * VEC, NB = 8;
+    typedef typename std::conditional<VEC == 4, uint2, uint32_t>::type raw_t;     // VEC fp16 values
     const int n_ctx = pos + 1, chunk = (n_ctx + P.n_splits - 1) / P.n_splits;
     const int p0 = split * chunk, p1 = min(n_ctx, p0 + chunk);
     const int kvh = head / (P.n_head / P.n_head_kv), KVD = P.n_head_kv * HD;
+    auto unpack = [](const raw_t& r, float* f) {
+        if constexpr (VEC == 4) { float2 a = __half22float2(*(const __half2*)&r.x), b = __half22float2(*(const __half2*)&r.y); f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; }
+        else { float2 a = __half22float2(*(const __half2*)&r); f[0] = a.x; f[1] = a.y; }
+    };
+    auto load_batch = [&](int pb, raw_t* kr, raw_t* vr) {               // cached positions only; the current one is filled in later
+#pragma unroll
+        for (int b = 0; b < NB; b++) {
+            const int p = pb + b * CONSUMER_WARPS;
+            if (p < p1 && p < pos) {
+                kr[b] = __ldcg((const raw_t*)(P.kv.at(layer, 0, kvh, p) + lane * VEC));
+                vr[b] = __ldcg((const raw_t*)(P.kv.at(layer, 1, kvh, p) + lane * VEC));
+            }
+        }
+    };
+    raw_t kr[NB], vr[NB];
+    load_batch(p0 + warp, kr, vr);
     float qv[VEC], acc[VEC];
     {   // q of this head: LL32, tag of the QKV phase
         float t[VEC];
@@ -92,26 +113,15 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
         for (int i = 0; i < VEC; i++) { qv[i] = t[i] * P.kq_scale; acc[i] = 0.f; }
     }
     float m = -INFINITY, l = 0.f;
-    for (int pb = p0 + warp * NB; pb < p1; pb += CONSUMER_WARPS * NB) {
-        float kf[NB][VEC], vf[NB][VEC]; bool live[NB];
+    for (int pb = p0 + warp; pb < p1; pb += CONSUMER_WARPS * NB) {
+        if (pb != p0 + warp) load_batch(pb, kr, vr);
 #pragma unroll
         for (int b = 0; b < NB; b++) {
-            const int p = pb + b; live[b] = p < p1;
-            if (live[b] && p < pos) {                                    // cached position: fp16 pages
-                const __half* kp = P.kv.at(layer, 0, kvh, p) + lane * VEC;
-                const __half* vp = P.kv.at(layer, 1, kvh, p) + lane * VEC;
-                if constexpr (VEC == 4) {
-                    uint2 kr = __ldcg((const uint2*)kp), vr = __ldcg((const uint2*)vp);
-                    float2 a = __half22float2(*(__half2*)&kr.x), c2 = __half22float2(*(__half2*)&kr.y);
-                    kf[b][0] = a.x; kf[b][1] = a.y; kf[b][2] = c2.x; kf[b][3] = c2.y;
-                    a = __half22float2(*(__half2*)&vr.x); c2 = __half22float2(*(__half2*)&vr.y);
-                    vf[b][0] = a.x; vf[b][1] = a.y; vf[b][2] = c2.x; vf[b][3] = c2.y;
-                } else {
-                    uint32_t kr = __ldcg((const uint32_t*)kp), vr = __ldcg((const uint32_t*)vp);
-                    float2 a = __half22float2(*(__half2*)&kr); kf[b][0] = a.x; kf[b][1] = a.y;
-                    a = __half22float2(*(__half2*)&vr); vf[b][0] = a.x; vf[b][1] = a.y;
-                }
-            } else if (live[b]) {                                         // the token being decoded: tagged exchange words
+            const int p = pb + b * CONSUMER_WARPS;
+            if (p >= p1) continue;                                       // warp-uniform
+            float kf[VEC], vf[VEC];
+            if (p < pos) { unpack(kr[b], kf); unpack(vr[b], vf); }
+            else {                                                        // the token being decoded: tagged exchange words
                 const uint32_t want = tag16_of(seq_in) << 16;
                 const uint32_t* kw = P.kv_ll + kvh * HD + lane * VEC; const uint32_t* vw = P.kv_ll + KVD + kvh * HD + lane * VEC;
                 uint32_t kk[VEC], vv[VEC];
@@ -124,20 +134,16 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
                     if ((bad >> 16) == 0) break;
                 }
 #pragma unroll
-                for (int i = 0; i < VEC; i++) { kf[b][i] = ll16_val(kk[i]); vf[b][i] = ll16_val(vv[i]); }
+                for (int i = 0; i < VEC; i++) { kf[i] = ll16_val(kk[i]); vf[i] = ll16_val(vv[i]); }
             }
-        }
-#pragma unroll
-        for (int b = 0; b < NB; b++) {
-            if (!live[b]) continue;                                      // warp-uniform
             float s = 0.f;
 #pragma unroll
-            for (int i = 0; i < VEC; i++) s += qv[i] * kf[b][i];
+            for (int i = 0; i < VEC; i++) s += qv[i] * kf[i];
             s = warp_sum(s);
             const float mn = fmaxf(m, s), corr = __expf(m - mn), pe = __expf(s - mn);
             l = l * corr + pe;
 #pragma unroll
-            for (int i = 0; i < VEC; i++) acc[i] = acc[i] * corr + pe * vf[b][i];
+            for (int i = 0; i < VEC; i++) acc[i] = acc[i] * corr + pe * vf[i];
             m = mn;
         }
     }
@@ -257,30 +263,40 @@ __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& o
                                           int pos, int warp, int lane, uint32_t seq, ArgBest& best, float* logits_dst, long long* tr) {
     constexpr int GB = TYPE == T_Q4_K ? 1152 : TYPE == T_Q5_K ? 1408 : TYPE == T_Q6_K ? 1680 : 2176;
     constexpr uint32_t PU = 2u * GB;
+    constexpr int SG = stage_groups(TYPE);
     const int n_grp = op.n_grp;
-    const uint8_t* my_unit = sm.ring + warp * PU;
-    for (int rb = a; rb < b; rb += PAIRS_PER_STAGE) {
+    const int wg = warp / GROUP_WARPS, wl = warp % GROUP_WARPS;
+    int rbi = 0;
+    for (int rb = a; rb < b; rb += PAIRS_PER_STAGE, rbi++) {
         const int np = min(PAIRS_PER_STAGE, b - rb);
-        const bool mine = warp < np;
+        const bool my_block = (rbi & (WARP_GROUPS - 1)) == wg;       // row blocks alternate between the warp groups
+        const bool mine = my_block && wl < np;
         float acc0 = 0.f, acc1 = 0.f;
-        for (int g = 0; g < n_grp; g++) {
-            uint32_t gap; const uint32_t soff = cur.place(np * PU, sm.ring_bytes, gap);
-            const uint32_t slot = cur.seq % NSLOT;
-            mbar_wait(&sm.full[slot], (cur.seq / NSLOT) & 1);
-            if (tr && warp == 0 && lane == 0 && rb == a && g == 0) tr[4] = gtime();
-            if (mine) {
-                XRegs x; load_x(sx, g, lane, x);
-                acc0 += lane_dot<TYPE>(my_unit + soff, lane, x);
-                acc1 += lane_dot<TYPE>(my_unit + soff + GB, lane, x);
+        for (int g0 = 0; g0 < n_grp; g0 += SG) {
+            const int ng = min(SG, n_grp - g0); const uint32_t cb = ng * PU;
+            uint32_t gap; const uint32_t soff = cur.place(np * cb, sm.ring_bytes, gap);   // every warp tracks every stage
+            if (my_block) {
+                const uint32_t slot = cur.seq % NSLOT;
+                mbar_wait(&sm.full[slot], (cur.seq / NSLOT) & 1);
+                if (tr && warp == 0 && lane == 0 && rb == a && g0 == 0) tr[4] = gtime();
+                if (mine) {
+                    const uint8_t* unit = sm.ring + soff + wl * cb;
+#pragma unroll
+                    for (int gg = 0; gg < SG; gg++) if (gg < ng) {
+                        XRegs x; load_x(sx, g0 + gg, lane, x);
+                        acc0 += lane_dot<TYPE>(unit + gg * PU, lane, x);
+                        acc1 += lane_dot<TYPE>(unit + gg * PU + GB, lane, x);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sm.empty[slot]);
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&sm.empty[slot]);
             cur.seq++;
         }
         if (tr && warp == 0 && lane == 0) tr[5] = gtime();
         if (mine) {
             acc0 = warp_sum(acc0); acc1 = warp_sum(acc1);
-            if (lane == 0) epilogue(P, op, sm, rb + warp, rb + warp - a, acc0, acc1, pos, seq, best, logits_dst);
+            if (lane == 0) epilogue(P, op, sm, rb + wl, rb + wl - a, acc0, acc1, pos, seq, best, logits_dst);
         }
     }
 }
@@ -402,13 +418,13 @@ struct DecodeRun {
     float* logits_all;                   // optional [n_steps][n_vocab]
 };
 
-__global__ void __launch_bounds__(CTA_THREADS, 2)
+__global__ void __launch_bounds__(CTA_THREADS, 1)
 decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes, const int max_grp) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     const Smem sm = carve_smem(smem_raw, ring_bytes, max_grp, P.hown_cap);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, c = blockIdx.x, G = gridDim.x;
     if (tid == 0) {
-        for (int i = 0; i < NSLOT; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], CONSUMER_WARPS); }
+        for (int i = 0; i < NSLOT; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], GROUP_WARPS); }
         fence_barrier_init();
     }
     __syncthreads();

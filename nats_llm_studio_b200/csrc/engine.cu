@@ -57,24 +57,20 @@ int Engine::ensure() {
 struct LaunchCfg { int grid; uint32_t ring_bytes; int max_grp; size_t smem; };
 
 static int launch_cfg(Engine& E, int max_grp, int hown_cap, LaunchCfg& lc) {
-    // two CTAs per SM: each gets half of the SM's shared memory minus the 1 KB system reservation
-    size_t per_cta = (size_t)E.smem_per_sm / 2 - 1024;
-    if (per_cta > (size_t)E.smem_optin) per_cta = E.smem_optin;
+    // one persistent CTA per SM owning (almost) all of its shared memory
+    max_grp = std::max(max_grp, 5);                       // the activation buffer doubles as attention scratch (17 x 130 floats)
+    size_t per_cta = (size_t)E.smem_optin;
     size_t fixed = smem_x_bytes(max_grp) + smem_misc_bytes(hown_cap);
-    if (fixed + 2 * MAX_STAGE_BYTES + 256 > per_cta) {      // very wide model: one CTA per SM
-        per_cta = E.smem_optin;
-        if (fixed + 2 * MAX_STAGE_BYTES + 256 > per_cta) return fail(B200_ERR_UNSUPPORTED, "activation vector does not fit in shared memory");
-        lc.grid = E.n_sm;
-    } else lc.grid = 2 * E.n_sm;
-    lc.ring_bytes = (uint32_t)((per_cta - fixed - 128) / 128 * 128);
     // the ring allocator never splits a stage across the wrap point, so a stage plus the gap it may leave behind
     // must fit: ring >= 2 x the largest stage (otherwise the producer can wait on space that cannot exist)
+    if (fixed + 2 * MAX_STAGE_BYTES + 256 > per_cta) return fail(B200_ERR_UNSUPPORTED, "activation vector does not fit in shared memory");
+    lc.grid = E.n_sm;
+    lc.ring_bytes = (uint32_t)((per_cta - fixed - 128) / 128 * 128);
     if (const char* rk = getenv("B200_RING_KB")) { uint32_t want = (uint32_t)atoi(rk) * 1024u; if (want >= 2u * MAX_STAGE_BYTES && want < lc.ring_bytes) lc.ring_bytes = want / 128 * 128; }
     lc.max_grp = max_grp; lc.smem = lc.ring_bytes + fixed;
     int occ = 0;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, decode_kernel, CTA_THREADS, lc.smem));
     if (occ < 1) return fail(B200_ERR_CUDA, "decode kernel does not fit on an SM");
-    if (lc.grid > occ * E.n_sm) lc.grid = occ * E.n_sm;
     return B200_OK;
 }
 
@@ -230,10 +226,8 @@ int Model::commit() {
 
     // ---- runtime buffers
     int max_grp = std::max({n_groups(F), n_groups(QD), 2 * n_groups(D)});
-    int n_sm2 = 2 * E.n_sm;
     hown_cap = 2 * ((D / 2 + E.n_sm - 1) / E.n_sm + 2);                       // pairs per CTA slice (worst case: 1 CTA/SM) x 2 rows
     LaunchCfg lc; if (int rc = launch_cfg(E, max_grp, hown_cap, lc)) return rc;
-    (void)n_sm2;
     grid = lc.grid; ring_bytes = lc.ring_bytes; smem_max_grp = lc.max_grp; smem_bytes = lc.smem;
     int rc;
     const size_t n_ll16 = (size_t)XREP * ((size_t)D + QD + F) + 2 * (size_t)KVD, n_ll32 = (size_t)QD + (size_t)n_head * 16 * (head_dim + 2) + 2 * (size_t)grid;
@@ -306,7 +300,7 @@ int Model::run_steps(int n_steps, const int32_t* forced, int n_forced, bool rese
     // split 0's CTA merges the partials of its head
     P.n_splits = std::max(1, std::min({16, std::max(1, grid / n_head), (cur_pos + n_steps + 15) / 16}));
     if (const char* e = getenv("B200_SPLITS")) P.n_splits = std::max(1, std::min({16, atoi(e), std::max(1, grid / n_head)}));
-    P.max_inflight = 2; if (const char* e = getenv("B200_INFLIGHT")) P.max_inflight = std::max(1, atoi(e));
+    P.max_inflight = 4; if (const char* e = getenv("B200_INFLIGHT")) P.max_inflight = std::max(1, atoi(e));
     DecodeRun R{}; R.forced = d_forced; R.n_forced = n_forced; R.logits_all = logits_all_dev;
     LaunchCfg lc; lc.grid = grid; lc.ring_bytes = ring_bytes; lc.max_grp = smem_max_grp; lc.smem = smem_bytes;
     if (int rc = launch_decode(E, P, R, lc)) return rc;
@@ -470,7 +464,7 @@ int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, flo
         cudaMemcpyAsync(d_ph, &p, sizeof p, cudaMemcpyHostToDevice, E.stream);
         DecodeParams P{}; P.phases = d_ph; P.n_phases = 1; P.n_embd = K; P.n_head = 1; P.n_head_kv = 1; P.head_dim = 128; P.n_vocab = (int)N; P.n_splits = 1;
         P.cand_ll = d_cv; P.hown_cap = 4; P.pos = d_st; P.token = d_st + 1; P.bar_ctr = (unsigned*)(d_st + 2); P.epoch = (unsigned*)(d_st + 3); P.out_tokens = d_ot;
-        P.logits = d_y; P.n_steps = 1; P.max_inflight = 2; if (const char* e = getenv("B200_INFLIGHT")) P.max_inflight = std::max(1, atoi(e));
+        P.logits = d_y; P.n_steps = 1; P.max_inflight = 4; if (const char* e = getenv("B200_INFLIGHT")) P.max_inflight = std::max(1, atoi(e));
         // every step "forced" (token 0): no argmax traffic; forced[] = d_ot, zeroed, iters+1 ints
         cudaMemsetAsync(d_ot, 0, ((size_t)iters + 1) * 4, E.stream);
         DecodeRun R{}; R.forced = d_ot; R.n_forced = iters + 1;

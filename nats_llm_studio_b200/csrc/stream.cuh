@@ -3,8 +3,8 @@
 // /root/reference/nats_llm_studio.go:158-179, which the reference delegates to LM Studio).
 //
 // Design (B200-first, HBM-bound work):
-//   * one persistent cooperative grid, 2 CTAs per SM, 9 warps each: warp 8 is the PRODUCER, warps
-//     0..7 are CONSUMERS.
+//   * one persistent cooperative grid, one CTA per SM, 17 warps: warp 16 is the PRODUCER, warps 0..15
+//     are CONSUMERS in two groups of 8 that take alternate row blocks (two stages consumed at once).
 //   * the producer walks the token's static weight schedule and pulls each CTA's slice of every
 //     matrix through a shared-memory byte ring with 1-D bulk-async copies (cp.async.bulk, the TMA
 //     engine; SASS UBLKCP) completing on mbarriers.  It never waits on data dependencies, only on
@@ -22,14 +22,19 @@
 
 namespace b200 {
 
-constexpr int CONSUMER_WARPS = 8;
+constexpr int GROUP_WARPS = 8;           // warps that share one stage (one row pair each)
+constexpr int WARP_GROUPS = 2;           // groups take alternate row blocks, so two stages are consumed concurrently
+constexpr int CONSUMER_WARPS = GROUP_WARPS * WARP_GROUPS;
 constexpr int CONSUMER_THREADS = CONSUMER_WARPS * 32;
 constexpr int CTA_THREADS = CONSUMER_THREADS + 32;
-constexpr int PAIRS_PER_STAGE = CONSUMER_WARPS;
-constexpr int NSLOT = 8;                 // mbarrier pairs in flight
+constexpr int PAIRS_PER_STAGE = GROUP_WARPS;
+constexpr int NSLOT = 16;                // mbarrier pairs in flight
 constexpr int XREP = 8;                  // copies of every broadcast exchange vector (an L2 slice serves ~1 sector/clk: one copy read by
                                          // every CTA costs ~0.6 us per line; CTA c reads copy c % XREP)
-constexpr int MAX_STAGE_BYTES = PAIRS_PER_STAGE * 2 * 2176;   // Q8_0 is the widest unit
+// groups (of 2048 elements) per stage: one bulk copy moves a pair's run of `stage_groups` consecutive groups, which
+// are contiguous in HBM — fewer, larger copies (the single producer warp issues them one by one)
+__host__ __device__ constexpr int stage_groups(int type) { return type == 8 /*Q8_0*/ ? 1 : 2; }
+constexpr int MAX_STAGE_BYTES = PAIRS_PER_STAGE * 2 * 2 * 1680;   // Q6_K, two groups
 
 // ------------------------------------------------------------------------------------ PTX
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -186,12 +191,13 @@ struct Producer {
             const OpDesc& op = ph.op[o];
             int a = max(lo, off) - off, b = min(hi, off + op.n_pairs) - off; off += op.n_pairs;
             if (a >= b) continue;
-            const uint32_t pu = 2u * group_bytes(op.type);
+            const uint32_t pu = 2u * group_bytes(op.type); const int sg = stage_groups(op.type);
             for (int rb = a; rb < b; rb += PAIRS_PER_STAGE) {
                 const int np = min(PAIRS_PER_STAGE, b - rb);
                 const uint8_t* src = op.w + (size_t)(rb + min(lane, np - 1)) * op.n_grp * pu;
-                for (int g = 0; g < op.n_grp; g++, src += pu) {
-                    const uint32_t bytes = np * pu, slot = cur.seq % NSLOT;
+                for (int g0 = 0; g0 < op.n_grp; g0 += sg) {
+                    const uint32_t cb = min(sg, op.n_grp - g0) * pu;        // bytes per pair in this stage (contiguous)
+                    const uint32_t bytes = np * cb, slot = cur.seq % NSLOT;
                     // (0) keep the number of un-landed stages small: other L2 accesses of this SM queue behind its
                     //     outstanding bulk bytes; landed-but-unconsumed stages may still pile up to the ring's capacity
                     while (cur.seq - landed >= max_unlanded) { mbar_wait(&sm.full[landed % NSLOT], (landed / NSLOT) & 1); landed++; }
@@ -205,7 +211,7 @@ struct Producer {
                     __syncwarp();                 // every lane is done reading q_end[] of released stages
                     if (lane == 0) { sm.q_end[slot] = gap + bytes; mbar_expect_tx(&sm.full[slot], bytes); }
                     __syncwarp();
-                    if (lane < np) bulk_g2s(sm.ring + soff + lane * pu, src, pu, &sm.full[slot]);
+                    if (lane < np) bulk_g2s(sm.ring + soff + lane * cb, src + (size_t)g0 * pu, cb, &sm.full[slot]);
                     cur.seq++;
                 }
             }
@@ -326,16 +332,16 @@ __device__ __forceinline__ float lane_dot_q4k(const uint8_t* grp, int lane, cons
     const uint8_t* blk = grp + (lane >> 2) * 144; const int j = lane & 3;
     const uint4 hdr = *(const uint4*)blk;                       // d, dmin, scales[12]
     const uint4 qa = *(const uint4*)(blk + 16 + 32 * j), qb = *(const uint4*)(blk + 32 + 32 * j);
-    int s0 = 0, s1 = 0;
+    int s0 = 0, s1 = 0, t0 = 0, t1 = 0;                        // four independent dp4a chains (depth 4 instead of 8)
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-        uint32_t w = u4_get(qa, i);
+        const uint32_t w = u4_get(qa, i), v = u4_get(qb, i);
         s0 = dp4a_ss((int)(w & 0x0F0F0F0Fu), (int)u4_get(x.p[0], i), s0);
         s1 = dp4a_us(w & 0xF0F0F0F0u, (int)u4_get(x.p[2], i), s1);
-        w = u4_get(qb, i);
-        s0 = dp4a_ss((int)(w & 0x0F0F0F0Fu), (int)u4_get(x.p[1], i), s0);
-        s1 = dp4a_us(w & 0xF0F0F0F0u, (int)u4_get(x.p[3], i), s1);
+        t0 = dp4a_ss((int)(v & 0x0F0F0F0Fu), (int)u4_get(x.p[1], i), t0);
+        t1 = dp4a_us(v & 0xF0F0F0F0u, (int)u4_get(x.p[3], i), t1);
     }
+    s0 += t0; s1 += t1;
     s1 >>= 4;                                                  // exact: every term is a multiple of 16
     int sc0, sc1, m0, m1; k4_scales(hdr, j, sc0, sc1, m0, m1);
     const int isum = sc0 * s0 + sc1 * s1;
