@@ -55,6 +55,26 @@ __device__ __forceinline__ void ll16_poll_run(const uint32_t* buf, int u, uint32
 #pragma unroll
     for (int i = 0; i < 4; i++) { v[4 * i] = ll16_val(r[i].x); v[4 * i + 1] = ll16_val(r[i].y); v[4 * i + 2] = ll16_val(r[i].z); v[4 * i + 3] = ll16_val(r[i].w); }
 }
+// two runs at once: all eight loads in flight before any tag is checked
+__device__ __forceinline__ void ll16_poll_run2(const uint32_t* buf, int ua, int ub, uint32_t tag16, float va[16], float vb[16]) {
+    const uint4* pa = (const uint4*)(buf + 16 * ua); const uint4* pb = (const uint4*)(buf + 16 * ub);
+    const uint32_t want = tag16 << 16;
+    uint4 r[8];
+    for (;;) {
+        uint32_t bad = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++) { r[i] = ld_relaxed_v4(pa + i); r[4 + i] = ld_relaxed_v4(pb + i); }
+#pragma unroll
+        for (int i = 0; i < 8; i++) bad |= (r[i].x ^ want) | (r[i].y ^ want) | (r[i].z ^ want) | (r[i].w ^ want);
+        if ((bad >> 16) == 0) break;
+        __nanosleep(40);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        va[4 * i] = ll16_val(r[i].x); va[4 * i + 1] = ll16_val(r[i].y); va[4 * i + 2] = ll16_val(r[i].z); va[4 * i + 3] = ll16_val(r[i].w);
+        vb[4 * i] = ll16_val(r[4 + i].x); vb[4 * i + 1] = ll16_val(r[4 + i].y); vb[4 * i + 2] = ll16_val(r[4 + i].z); vb[4 * i + 3] = ll16_val(r[4 + i].w);
+    }
+}
 // N consecutive LL32 elements ({bits, tag32} pairs), N even, polled
 template <int N>
 __device__ __forceinline__ void ll32_poll(const uint2* buf, uint32_t tag, float* out) {
@@ -212,10 +232,10 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
 // ------------------------------------------------------------------------------------ epilogues
 struct ArgBest { float v; int i; };
 
-__device__ __forceinline__ void rope_pair(const DecodeParams& P, int d, int pos, float& a, float& b) {
+__device__ __forceinline__ void rope_pair(const DecodeParams& P, const Smem& sm, int d, float& a, float& b) {
     if (d < P.n_rot) {
-        float sn, cs; sincosf((float)pos * __ldg(P.inv_freq + (d >> 1)), &sn, &cs);
-        const float x = a, y = b; a = x * cs - y * sn; b = x * sn + y * cs;
+        const float2 cs = sm.rope[d >> 1];           // filled once per token (decode_kernel), off the critical path
+        const float x = a, y = b; a = x * cs.x - y * cs.y; b = x * cs.y + y * cs.x;
     }
 }
 
@@ -240,10 +260,10 @@ __device__ __forceinline__ void epilogue(const DecodeParams& P, const OpDesc& op
             if (row + 1 < op.n_rows && a1 > best.v) { best.v = a1; best.i = row + 1; }
         } break;
         case EPI_ROPE_Q:
-            rope_pair(P, row % HD, pos, a0, a1);
+            rope_pair(P, sm, row % HD, a0, a1);
             st_relaxed_v2(P.q_ll + row, __float_as_uint(a0), seq); st_relaxed_v2(P.q_ll + row + 1, __float_as_uint(a1), seq); break;
         case EPI_ROPE_K: {
-            rope_pair(P, row % HD, pos, a0, a1);
+            rope_pair(P, sm, row % HD, a0, a1);
             const __half2 hv = __floats2half2_rn(a0, a1);
             *(__half2*)(P.kv.at(op.layer, 0, row / HD, pos) + row % HD) = hv;
             st_relaxed_v2(P.kv_ll + row, (t16 << 16) | __half_as_ushort(__low2half(hv)), (t16 << 16) | __half_as_ushort(__high2half(hv)));
@@ -321,6 +341,10 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
         if (ph.pro == PRO_PLAIN) load_run_f32(ph.src, u, v);
         else ll16_poll_run(xsrc, u, tin16, v);
     };
+    auto fetch2 = [&](int ua, int ub, float* va, float* vb) {
+        if (ph.pro == PRO_PLAIN) { load_run_f32(ph.src, ua, va); load_run_f32(ph.src, ub, vb); }
+        else ll16_poll_run2(xsrc, ua, ub, tin16, va, vb);
+    };
     auto quantise_store = [&](int u, float* v) {
         float amax = 0.f;
 #pragma unroll
@@ -376,18 +400,32 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
             quantise_store(u, t);
         }
     } else {
-        // single pass; poll the first run before the barrier so the wait overlaps the other warps' tails
-        float t[16]; const bool first = tid < n_runs;
-        if (first) fetch(tid, t);
+        // single pass; a thread's first two runs are polled together (both loads in flight) before the barrier, so the
+        // exchange wait overlaps the other warps' tails
+        float t[16], t2[16]; const int u2 = tid + CONSUMER_THREADS;
+        const bool first = tid < n_runs, second = u2 < n_runs;
+        if (second) fetch2(tid, u2, t, t2); else if (first) fetch(tid, t);
         if (tr && tid == 0) tr[1] = tr[2] = gtime();
         consumer_sync();                                    // xq free (previous phase's readers done)
-        for (int u = tid; u < n_runs_pad; u += CONSUMER_THREADS) {
-            if (u != tid || !first) {
-                if (u < n_runs) fetch(u, t);
-                else {
+        if (tid < n_runs_pad) {
+            if (!first) {
 #pragma unroll
-                    for (int i = 0; i < 16; i++) t[i] = 0.f;
-                }
+                for (int i = 0; i < 16; i++) t[i] = 0.f;
+            }
+            quantise_store(tid, t);
+        }
+        if (u2 < n_runs_pad) {
+            if (!second) {
+#pragma unroll
+                for (int i = 0; i < 16; i++) t2[i] = 0.f;
+            }
+            quantise_store(u2, t2);
+        }
+        for (int u = tid + 2 * CONSUMER_THREADS; u < n_runs_pad; u += CONSUMER_THREADS) {
+            if (u < n_runs) fetch(u, t);
+            else {
+#pragma unroll
+                for (int i = 0; i < 16; i++) t[i] = 0.f;
             }
             quantise_store(u, t);
         }
@@ -463,6 +501,10 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
             if (P.trace) tr = P.trace + (((size_t)step * P.n_phases + i) * G + c) * 8;
             if (tr && tid == 0) { const long long t0 = gtime(); for (int k = 0; k < 7; k++) tr[k] = t0; }
             if (ph.kind == PH_EMBED) {
+                // every warp must be done with the previous token (its down-proj epilogue updates hown and publishes
+                // this CTA's rows); without this a late RESID publish could overwrite the new token's tagged rows
+                consumer_sync();
+                if (tid < P.n_rot / 2 && tid < 128) { float sn, cs; sincosf((float)pos * __ldg(P.inv_freq + tid), &sn, &cs); sm.rope[tid] = make_float2(cs, sn); }
                 const int ng = n_groups(P.n_embd); const uint32_t t16 = tag16_of(seq);
                 for (int e = 2 * hlo + tid; e < 2 * hhi; e += CONSUMER_THREADS) {
                     float v = embed_elem(P.embd, P.embd_type, ng, token, e);

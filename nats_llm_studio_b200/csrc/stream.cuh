@@ -146,16 +146,17 @@ struct Smem {
     float* red;                               // 64 floats of reduction scratch
     uint32_t* q_end;                          // producer's in-flight stage sizes [NSLOT]
     float* hown;                              // fp32 hidden-state rows this CTA owns (residual stream never leaves the SM)
+    float2* rope;                             // (cos, sin) of this token's RoPE angles [128]
 };
 __host__ __device__ inline size_t smem_x_bytes(int max_grp) { return (size_t)max_grp * (2048 + 256 + 32); }
-__host__ __device__ inline size_t smem_misc_bytes(int hown_cap) { return NSLOT * 16 + 64 * 4 + NSLOT * 4 + (size_t)hown_cap * 4 + 64; }
+__host__ __device__ inline size_t smem_misc_bytes(int hown_cap) { return NSLOT * 16 + 64 * 4 + NSLOT * 4 + 128 * 8 + (size_t)hown_cap * 4 + 64; }
 __device__ inline Smem carve_smem(uint8_t* base, uint32_t ring_bytes, int max_grp, int hown_cap) {
     Smem s; s.ring = base; s.ring_bytes = ring_bytes; uint8_t* p = base + ring_bytes;
     s.xq = (int8_t*)p; p += (size_t)max_grp * 2048;
     s.xbs = (int16_t*)p; p += (size_t)max_grp * 256;
     s.xd = (float*)p; p += (size_t)max_grp * 32;
     s.full = (uint64_t*)p; p += NSLOT * 8; s.empty = (uint64_t*)p; p += NSLOT * 8;
-    s.red = (float*)p; p += 64 * 4; s.q_end = (uint32_t*)p; p += NSLOT * 4; s.hown = (float*)p;
+    s.red = (float*)p; p += 64 * 4; s.q_end = (uint32_t*)p; p += NSLOT * 4; s.rope = (float2*)p; p += 128 * 8; s.hown = (float*)p;
     return s;
 }
 
@@ -173,8 +174,8 @@ struct RingCursor {
 };
 
 // slice of the phase's concatenated pair space owned by CTA c of G
-__device__ __forceinline__ void cta_slice(int total, int c, int G, int& lo, int& hi) {
-    lo = (int)((long long)total * c / G); hi = (int)((long long)total * (c + 1) / G);
+__device__ __forceinline__ void cta_slice(int total, int c, int G, int& lo, int& hi) {   // total * G < 2^32 (pairs x SMs)
+    lo = (int)((uint32_t)total * (uint32_t)c / (uint32_t)G); hi = (int)((uint32_t)total * (uint32_t)(c + 1) / (uint32_t)G);
 }
 
 // ------------------------------------------------------------------------------------ producer

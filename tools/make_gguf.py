@@ -67,6 +67,8 @@ PRESETS = {
                        n_ctx=8192, mode="bytes"),
     "granite3-2b": dict(arch="granite", n_layer=40, n_embd=2048, n_head=32, n_head_kv=8, n_ff=8192, n_vocab=49155,
                         n_ctx=4096, rope_base=10000.0, mix="q8_0", tied=True, mode="bytes"),
+    # head_dim 128, GQA 4:1, q4_k_m mix incl. a Q6_K attn_v next to Q4_K q/k: the 8B code paths at test size
+    "small-llama": dict(arch="llama", n_layer=2, n_embd=1024, n_head=8, n_head_kv=2, n_ff=2816, n_vocab=2048),
     "tiny-llama": dict(arch="llama", n_layer=2, n_embd=256, n_head=4, n_head_kv=2, n_ff=512, n_vocab=512),
     "tiny-granite": dict(arch="granite", n_layer=2, n_embd=256, n_head=4, n_head_kv=2, n_ff=512, n_vocab=515,
                          mix="q8_0", tied=True, rope_base=10000.0),
