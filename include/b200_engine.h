@@ -94,6 +94,21 @@ int b200_set_models_dir(const char* dir);
 /* ---- kernel-level entry points (parity tests, roofline bench).  Host buffers in and out. */
 /* repack raw ggml blocks on the GPU and dequantise them back: out[n_rows*K] fp32, bit-exact */
 int b200_dequantize(int type, const void* raw_blocks, int64_t n_rows, int K, float* out);
+/* No counterpart in the reference.  b200_dequantize for callers that must not allocate device memory: a worker
+ * that has already handed every spare byte of HBM to resident models and KV pages (a cudaMalloc there can fail, or
+ * fragment the pool), or code on the request path, where cudaMalloc/cudaFree serialise against everything running on
+ * the device and would stall generations in flight.  d_raw (n_rows rows of raw ggml blocks) and d_out
+ * (n_rows*K floats) are DEVICE pointers owned by the caller; the engine-layout intermediate lives in a fixed
+ * B200_NOALLOC_SCRATCH_BYTES array built into the library (resident on every GPU that loads it until exit), so
+ * type/n_rows/K whose intermediate is larger are refused with B200_ERR_INVALID.  Neither this call nor anything it
+ * invokes calls cudaMalloc, cudaFree or another allocating routine; b200_init must have run.  The first call on a
+ * device also looks up the array's device address (make that call before starting any stream capture).  Every call
+ * reuses the same array, which keeps the previous call's bytes (harmless: each call overwrites what it reads);
+ * calls from this library are serialised, but work that overlaps on the GPU from elsewhere on the same array races.
+ * The work is queued on the engine's own stream and the call returns after it completed: inputs written on
+ * another stream must be complete before calling. */
+#define B200_NOALLOC_SCRATCH_BYTES (4u << 20)
+int b200_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K, float* d_out);
 /* y[N] = W[N x K] . x[K] through the streaming GEMV; iters>1 repeats the launch, ms = mean per iter */
 int b200_gemv(int type, const void* raw_blocks, int64_t N, int K, const float* x, float* y, int iters, float* ms);
 /* decode-step timing: n_steps greedy tokens from the current position of a primed context */

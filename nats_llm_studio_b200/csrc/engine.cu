@@ -441,6 +441,49 @@ int kernel_dequantize(int type, const void* raw, int64_t n_rows, int K, float* o
     return rc;
 }
 
+// ------------------------------------------------------------------------------------ allocation-free dequantise
+// Same two kernels as kernel_dequantize (repack into the engine layout, dequantise back), but the intermediate
+// engine-layout copy lives in a fixed array inside the module image instead of a cudaMalloc'd buffer, and the
+// caller supplies device pointers for the raw blocks and the fp32 result.  Nothing is allocated or freed here.
+// The array is one per GPU that loads this library and stays resident until the process exits.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B200_NOALLOC_SCRATCH_BYTES];
+static unsigned char* g_noalloc_ptr[64];          // device address of the array, looked up once per device
+static std::mutex g_noalloc_mu;
+
+int kernel_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K, float* d_out) {
+    Engine& E = engine();
+    if (!E.ready) return fail(B200_ERR_STATE, "b200_init must run before b200_dequantize_noalloc (this entry point creates nothing, not even streams)");
+    if (!is_streamable(type)) return fail(B200_ERR_UNSUPPORTED, "unsupported ggml type");
+    if (n_rows < 0 || K <= 0 || K % 256) return fail(B200_ERR_INVALID, "K must be a positive multiple of 256");
+    if (n_rows == 0) return B200_OK;
+    if (!d_raw || !d_out) return fail(B200_ERR_INVALID, "null device pointer");
+    const int64_t N = n_rows + (n_rows & 1);
+    const size_t need = repacked_bytes(type, N, K);
+    if (need > (size_t)B200_NOALLOC_SCRATCH_BYTES)
+        return fail(B200_ERR_INVALID, "b200_dequantize_noalloc: " + std::to_string(need) + " bytes of scratch needed, the built-in buffer holds " +
+                                          std::to_string((size_t)B200_NOALLOC_SCRATCH_BYTES) + " (use b200_dequantize, which allocates)");
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);                    // host callers of this library take turns on the shared array
+    CK(cudaSetDevice(E.device));
+    if (E.device < 0 || E.device >= 64) return fail(B200_ERR_INVALID, "device ordinal out of range");
+    if (!g_noalloc_ptr[E.device]) {
+        // First use on this device: resolve the array's device address.  In host code the array's name is only a
+        // handle for the runtime, not something a kernel can dereference.
+        unsigned char* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) return fail(B200_ERR_CUDA, std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e));
+        g_noalloc_ptr[E.device] = p;
+    }
+    unsigned char* scratch = g_noalloc_ptr[E.device];
+    // Nothing in the array has to start at zero: repack_kernel writes every byte of the `need` bytes (padding rows
+    // and padding groups included) before dequant_repacked_kernel reads them, so leftovers of earlier calls are inert.
+    if (int rc = repack(E, (const uint8_t*)d_raw, scratch, type, N, n_rows, K)) return rc;
+    dequant_repacked_kernel<<<(int)std::min<long long>((n_rows * (long long)K + 255) / 256, 148 * 16), 256, 0, E.stream>>>(scratch, type, n_rows, K, d_out);
+    CK(cudaGetLastError());
+    E.launches++;
+    CK(cudaStreamSynchronize(E.stream));                             // the array is free again when this returns
+    return B200_OK;
+}
+
 int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, float* y, int iters, float* ms_out) {
     Engine& E = engine(); if (int rc = E.ensure()) return rc;
     if (!is_streamable(type)) return fail(B200_ERR_UNSUPPORTED, "unsupported ggml type");

@@ -88,6 +88,7 @@ struct Model {
 int sample_token(Engine& E, Model& m, const b200_sampling& s, uint64_t step);
 int kernel_dequantize(int type, const void* raw, int64_t n_rows, int K, float* out);
 int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, float* y, int iters, float* ms);
+int kernel_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K, float* d_out);
 int layout_selftest();
 
 // registry (handlers.cpp)

@@ -49,7 +49,7 @@ SYMBOLS = {
     "b200_model_eval": (ci, [vp, vp, ci, vp, vp]), "b200_model_n_vocab": (ci, [vp]),
     "b200_tokenize": (ci, [vp, C.c_char_p, sz, vp, ci, C.POINTER(ci)]), "b200_detokenize": (ci, [vp, vp, ci, vp, sz, C.POINTER(sz)]),
     "b200_handle": (ci, [C.c_char_p, vp, sz, vp, sz, C.POINTER(sz)]), "b200_set_models_dir": (ci, [C.c_char_p]),
-    "b200_dequantize": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_gemv": (ci, [ci, vp, C.c_int64, ci, vp, vp, ci, C.POINTER(C.c_float)]),
+    "b200_dequantize": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_dequantize_noalloc": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_gemv": (ci, [ci, vp, C.c_int64, ci, vp, vp, ci, C.POINTER(C.c_float)]),
     "b200_bench_decode": (ci, [vp, ci, ci, ci, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
     "b200_launch_count": (C.c_uint64, []), "b200_layout_selftest": (ci, []),
 }
