@@ -95,6 +95,10 @@ __device__ __forceinline__ float embed_elem(const uint8_t* w, int type, int n_gr
     const int gb = group_bytes(type), g = e / GROUP_ELEMS, eg = e % GROUP_ELEMS, be = block_elems(type);
     const uint8_t* base = w + (((size_t)(row >> 1) * n_grp + g) * 2 + (row & 1)) * gb;
     const int blk = eg / be;
+    if (type == T_Q4_K || type == T_Q5_K) {      // scale bytes are stored re-encoded (quant.cuh k4_reencode)
+        uint8_t q[12]; k4_restore(base + dst_byte(type, blk, 4), q);
+        return dequant_elem(type, [&](int i) { return (i >= 4 && i < 16) ? q[i - 4] : base[dst_byte(type, blk, i)]; }, eg % be);
+    }
     return dequant_elem(type, [&](int i) { return base[dst_byte(type, blk, i)]; }, eg % be);
 }
 
@@ -284,12 +288,15 @@ __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& o
     constexpr int GB = TYPE == T_Q4_K ? 1152 : TYPE == T_Q5_K ? 1408 : TYPE == T_Q6_K ? 1680 : 2176;
     constexpr uint32_t PU = 2u * GB;
     constexpr int SG = stage_groups(TYPE);
+#ifdef B200_TRACE_WAIT
+    long long acc_wait = 0, acc_comp = 0, acc_n = 0;
+#endif
     const int n_grp = op.n_grp;
     const int wg = warp / GROUP_WARPS, wl = warp % GROUP_WARPS;
     int rbi = 0;
     for (int rb = a; rb < b; rb += PAIRS_PER_STAGE, rbi++) {
         const int np = min(PAIRS_PER_STAGE, b - rb);
-        const bool my_block = (rbi & (WARP_GROUPS - 1)) == wg;       // row blocks alternate between the warp groups
+        const bool my_block = (rbi % WARP_GROUPS) == wg;       // row blocks alternate between the warp groups
         const bool mine = my_block && wl < np;
         float acc0 = 0.f, acc1 = 0.f;
         for (int g0 = 0; g0 < n_grp; g0 += SG) {
@@ -297,8 +304,17 @@ __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& o
             uint32_t gap; const uint32_t soff = cur.place(np * cb, sm.ring_bytes, gap);   // every warp tracks every stage
             if (my_block) {
                 const uint32_t slot = cur.seq % NSLOT;
+#ifdef B200_TRACE_WAIT
+                long long tw0 = 0; if (tr && warp == 0 && lane == 0) tw0 = clock64();
+#endif
                 mbar_wait(&sm.full[slot], (cur.seq / NSLOT) & 1);
+#ifdef B200_TRACE_WAIT
+                if (tr && warp == 0 && lane == 0) { acc_wait += clock64() - tw0; }
+#endif
                 if (tr && warp == 0 && lane == 0 && rb == a && g0 == 0) tr[4] = gtime();
+#ifdef B200_TRACE_WAIT
+                long long cc0 = 0; if (tr && warp == 0 && lane == 0) cc0 = clock64();
+#endif
                 if (mine) {
                     const uint8_t* unit = sm.ring + soff + wl * cb;
 #pragma unroll
@@ -308,6 +324,9 @@ __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& o
                         acc1 += lane_dot<TYPE>(unit + gg * PU + GB, lane, x);
                     }
                 }
+#ifdef B200_TRACE_WAIT
+                if (tr && warp == 0 && lane == 0) { acc_comp += clock64() - cc0; acc_n += 1; }     // compute cycles, stages
+#endif
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&sm.empty[slot]);
             }
@@ -319,6 +338,9 @@ __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& o
             if (lane == 0) epilogue(P, op, sm, rb + wl, rb + wl - a, acc0, acc1, pos, seq, best, logits_dst);
         }
     }
+#ifdef B200_TRACE_WAIT
+    if (tr && warp == 0 && lane == 0) { tr[7] += acc_wait; tr[1] += acc_comp; tr[2] += acc_n; }
+#endif
 }
 
 // ------------------------------------------------------------------------------------ one GEMV phase (consumers)
@@ -432,6 +454,9 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
     }
     consumer_sync();
     if (tr && tid == 0) tr[3] = gtime();
+#ifdef B200_TRACE_WAIT
+    if (tr && tid == 0) { tr[1] = 0; tr[2] = 0; }
+#endif
 
     // ---- stream the CTA's slice
     int lo, hi; cta_slice(ph.total_pairs, c, G, lo, hi);
@@ -465,6 +490,10 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
         for (int i = 0; i < NSLOT; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], GROUP_WARPS); }
         fence_barrier_init();
     }
+    {   // schedule -> shared memory
+        const uint32_t* src = (const uint32_t*)P.phases; uint32_t* dst = (uint32_t*)sm.phases;
+        for (int i = tid; i < P.n_phases * (int)(sizeof(Phase) / 4); i += CTA_THREADS) dst[i] = __ldg(src + i);
+    }
     __syncthreads();
 
     if (warp == CONSUMER_WARPS) {           // ===== producer warp =====
@@ -472,7 +501,7 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
         for (int step = 0; step < P.n_steps; step++) {
             const bool need_lm = (step + 1 >= R.n_forced) || R.logits_all;
             for (int i = 0; i < P.n_phases; i++) {
-                const Phase& ph = P.phases[i];
+                const Phase& ph = sm.phases[i];
                 if (ph.kind != PH_GEMV) continue;
                 if (ph.op[0].epi == EPI_LOGITS && !need_lm) continue;
                 pr.run_phase(ph, sm, c, G, lane);
@@ -494,12 +523,15 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
         float* logits_dst = R.logits_all ? R.logits_all + (size_t)step * P.n_vocab : P.logits;
         ArgBest best; best.v = -INFINITY; best.i = 0x7fffffff;
         for (int i = 0; i < P.n_phases; i++) {
-            const Phase& ph = P.phases[i];
+            const Phase& ph = sm.phases[i];
             if (ph.kind == PH_GEMV && ph.op[0].epi == EPI_LOGITS && !need_lm) continue;
             seq++;
             long long* tr = nullptr;
             if (P.trace) tr = P.trace + (((size_t)step * P.n_phases + i) * G + c) * 8;
-            if (tr && tid == 0) { const long long t0 = gtime(); for (int k = 0; k < 7; k++) tr[k] = t0; }
+            if (tr && tid == 0) { const long long t0 = gtime(); for (int k = 0; k < 7; k++) tr[k] = t0; tr[7] = 0; }
+#ifdef B200_TRACE_WAIT
+            const long long cphase0 = clock64();
+#endif
             if (ph.kind == PH_EMBED) {
                 // every warp must be done with the previous token (its down-proj epilogue updates hown and publishes
                 // this CTA's rows); without this a late RESID publish could overwrite the new token's tagged rows
@@ -534,7 +566,11 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
                     }
                 }
             }
+#ifdef B200_TRACE_WAIT
+            if (tr && tid == 0) { tr[6] = gtime(); tr[4] = tr[0] + (clock64() - cphase0); }   // tr[4]-tr[0] = SM cycles of the phase; tr[7] = warp 0's wait-for-data ns
+#else
             if (tr && tid == 0) { tr[6] = gtime(); unsigned smid; asm("mov.u32 %0, %%smid;" : "=r"(smid)); tr[7] = smid; }
+#endif
         }
         // ---- next token: forced, or argmax over the per-CTA candidates (every CTA redundantly)
         int next;
@@ -580,6 +616,7 @@ __global__ void repack_kernel(const uint8_t* __restrict__ raw, uint8_t* __restri
         uint8_t b[16];
 #pragma unroll
         for (int k = 0; k < 16; k++) { long long s = row < n_src ? src_byte(type, K, g, o + k) : -1; b[k] = s < 0 ? 0 : raw[(size_t)row * rrb + s]; }
+        if ((type == T_Q4_K || type == T_Q5_K) && o % block_bytes(type) == 0) { uint8_t e[12]; k4_reencode(b + 4, e); for (int k = 0; k < 12; k++) b[4 + k] = e[k]; }
         const long long orow = parity < 0 ? row : 2 * row + parity;
         uint8_t* dst = out + ((((size_t)(orow >> 1)) * ng + g) * 2 + (orow & 1)) * gb + o;
         *(uint4*)dst = *(uint4*)b;

@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <mutex>
 
 #include "decode.cuh"
@@ -56,11 +57,11 @@ int Engine::ensure() {
 // ------------------------------------------------------------------------------------ launch geometry
 struct LaunchCfg { int grid; uint32_t ring_bytes; int max_grp; size_t smem; };
 
-static int launch_cfg(Engine& E, int max_grp, int hown_cap, LaunchCfg& lc) {
+static int launch_cfg(Engine& E, int max_grp, int hown_cap, int n_phases, LaunchCfg& lc) {
     // one persistent CTA per SM owning (almost) all of its shared memory
-    max_grp = std::max(max_grp, 5);                       // the activation buffer doubles as attention scratch (17 x 130 floats)
+    max_grp = std::max(max_grp, (int)(((CONSUMER_WARPS + 1) * 130 + 64) * 4 / 2336 + 1));   // the activation buffer doubles as attention scratch
     size_t per_cta = (size_t)E.smem_optin;
-    size_t fixed = smem_x_bytes(max_grp) + smem_misc_bytes(hown_cap);
+    size_t fixed = smem_x_bytes(max_grp) + smem_misc_bytes(hown_cap, n_phases);
     // the ring allocator never splits a stage across the wrap point, so a stage plus the gap it may leave behind
     // must fit: ring >= 2 x the largest stage (otherwise the producer can wait on space that cannot exist)
     if (fixed + 2 * MAX_STAGE_BYTES + 256 > per_cta) return fail(B200_ERR_UNSUPPORTED, "activation vector does not fit in shared memory");
@@ -227,7 +228,7 @@ int Model::commit() {
     // ---- runtime buffers
     int max_grp = std::max({n_groups(F), n_groups(QD), 2 * n_groups(D)});
     hown_cap = 2 * ((D / 2 + E.n_sm - 1) / E.n_sm + 2);                       // pairs per CTA slice (worst case: 1 CTA/SM) x 2 rows
-    LaunchCfg lc; if (int rc = launch_cfg(E, max_grp, hown_cap, lc)) return rc;
+    LaunchCfg lc; if (int rc = launch_cfg(E, max_grp, hown_cap, 5 * n_layer + 2, lc)) return rc;
     grid = lc.grid; ring_bytes = lc.ring_bytes; smem_max_grp = lc.max_grp; smem_bytes = lc.smem;
     int rc;
     const size_t n_ll16 = (size_t)XREP * ((size_t)D + QD + F) + 2 * (size_t)KVD, n_ll32 = (size_t)QD + (size_t)n_head * 16 * (head_dim + 2) + 2 * (size_t)grid;
@@ -494,7 +495,7 @@ int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, flo
     int rc = B200_OK;
     LaunchCfg lc;
     auto cleanup = [&]() { cudaFree(d_raw); cudaFree(d_w); cudaFree(d_x); cudaFree(d_y); cudaFree(d_cv); cudaFree(d_st); cudaFree(d_ot); cudaFree(d_ph); };
-    if ((rc = launch_cfg(E, n_groups(K), 4, lc))) return rc;
+    if ((rc = launch_cfg(E, n_groups(K), 4, 1, lc))) return rc;
     if ((rc = dalloc(&d_raw, (size_t)N * rb)) || (rc = dalloc(&d_w, repacked_bytes(type, N, K))) || (rc = dalloc(&d_x, (size_t)K)) || (rc = dalloc(&d_y, (size_t)N)) ||
         (rc = dalloc(&d_cv, (size_t)2 * lc.grid)) || (rc = dalloc(&d_st, (size_t)16)) || (rc = dalloc(&d_ot, (size_t)iters + 1)) || (rc = dalloc(&d_ph, (size_t)1))) { cleanup(); return rc; }
     cudaMemcpyAsync(d_raw, raw, (size_t)N * rb, cudaMemcpyHostToDevice, E.stream);
@@ -531,6 +532,15 @@ int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, flo
 }
 
 int layout_selftest() {
+    {   // K-quant scale re-encoding is an exact bijection on the 96 bits
+        uint32_t st = 12345u;
+        for (int it = 0; it < 4096; it++) {
+            uint8_t q[12], e[12], r[12];
+            for (int i = 0; i < 12; i++) { st = st * 1664525u + 1013904223u; q[i] = (uint8_t)(st >> 24); }
+            k4_reencode(q, e); k4_restore(e, r);
+            if (memcmp(q, r, 12)) return fail(B200_ERR_INVALID, "layout selftest: k4_reencode/k4_restore are not inverses");
+        }
+    }
     const int types[] = {T_Q8_0, T_Q4_K, T_Q5_K, T_Q6_K};
     for (int t : types) {
         const int gb = group_bytes(t), be = block_elems(t), bb = block_bytes(t), blocks_per_group = GROUP_ELEMS / be;

@@ -120,6 +120,37 @@ __device__ inline void scale_min_k4(int j, const uint8_t* q, int& sc, int& m) { 
     else { sc = (q[j + 4] & 0x0F) | ((q[j - 4] >> 6) << 4); m = (q[j + 4] >> 4) | ((q[j] >> 6) << 4); }
 }
 
+// ---------------------------------------------------------------------------------------------
+// K-quant scale bytes, engine form.  ggml packs the sixteen 6-bit scale/min values of a super-block into 12 bytes
+// in an order that costs ~25 ALU ops to undo per lane (quants.py:480-503).  The engine keeps the same 96 bits but
+// orders them per lane: bytes 3j..3j+2 hold, for chunk j (sub-blocks 2j, 2j+1), the 24-bit field
+//     sc[2j] | sc[2j+1] << 6 | m[2j] << 12 | m[2j+1] << 18
+// so a lane needs one funnel shift and four bit-field extracts.  k4_reencode / k4_restore are exact inverses.
+__host__ __device__ inline void k4_reencode(const uint8_t* q /*12 ggml bytes*/, uint8_t* out /*12 engine bytes*/) {
+    for (int j = 0; j < 4; j++) {
+        uint32_t f = 0;
+        for (int k = 0; k < 2; k++) {
+            const int s = 2 * j + k; uint32_t sc, m;
+            if (s < 4) { sc = q[s] & 63; m = q[s + 4] & 63; }
+            else { sc = (q[s + 4] & 0x0F) | ((q[s - 4] >> 6) << 4); m = (q[s + 4] >> 4) | ((q[s] >> 6) << 4); }
+            f |= sc << (6 * k) | m << (12 + 6 * k);
+        }
+        out[3 * j] = (uint8_t)f; out[3 * j + 1] = (uint8_t)(f >> 8); out[3 * j + 2] = (uint8_t)(f >> 16);
+    }
+}
+__host__ __device__ inline void k4_restore(const uint8_t* e /*12 engine bytes*/, uint8_t* q /*12 ggml bytes*/) {
+    uint32_t sc[8], m[8];
+    for (int j = 0; j < 4; j++) {
+        const uint32_t f = (uint32_t)e[3 * j] | ((uint32_t)e[3 * j + 1] << 8) | ((uint32_t)e[3 * j + 2] << 16);
+        sc[2 * j] = f & 63; sc[2 * j + 1] = (f >> 6) & 63; m[2 * j] = (f >> 12) & 63; m[2 * j + 1] = (f >> 18) & 63;
+    }
+    for (int i = 0; i < 4; i++) {
+        q[i] = (uint8_t)((sc[i] & 63) | ((sc[i + 4] >> 4) << 6));
+        q[i + 4] = (uint8_t)((m[i] & 63) | ((m[i + 4] >> 4) << 6));
+        q[i + 8] = (uint8_t)((sc[i + 4] & 0x0F) | ((m[i + 4] & 0x0F) << 4));
+    }
+}
+
 template <typename Rd>   // Rd: byte reader, rd(i) = i-th byte of the raw block
 __device__ inline float dequant_elem(int t, Rd rd, int e) {
     if (t == T_Q8_0) {

@@ -23,7 +23,10 @@
 namespace b200 {
 
 constexpr int GROUP_WARPS = 8;           // warps that share one stage (one row pair each)
-constexpr int WARP_GROUPS = 2;           // groups take alternate row blocks, so two stages are consumed concurrently
+#ifndef B200_WARP_GROUPS
+#define B200_WARP_GROUPS 2
+#endif
+constexpr int WARP_GROUPS = B200_WARP_GROUPS;           // groups take alternate row blocks, so two stages are consumed concurrently
 constexpr int CONSUMER_WARPS = GROUP_WARPS * WARP_GROUPS;
 constexpr int CONSUMER_THREADS = CONSUMER_WARPS * 32;
 constexpr int CTA_THREADS = CONSUMER_THREADS + 32;
@@ -147,16 +150,18 @@ struct Smem {
     uint32_t* q_end;                          // producer's in-flight stage sizes [NSLOT]
     float* hown;                              // fp32 hidden-state rows this CTA owns (residual stream never leaves the SM)
     float2* rope;                             // (cos, sin) of this token's RoPE angles [128]
+    Phase* phases;                            // the schedule, copied from global once per launch (descriptor reads are on
+                                              // every phase's critical path; an L2 round trip each would cost microseconds)
 };
 __host__ __device__ inline size_t smem_x_bytes(int max_grp) { return (size_t)max_grp * (2048 + 256 + 32); }
-__host__ __device__ inline size_t smem_misc_bytes(int hown_cap) { return NSLOT * 16 + 64 * 4 + NSLOT * 4 + 128 * 8 + (size_t)hown_cap * 4 + 64; }
-__device__ inline Smem carve_smem(uint8_t* base, uint32_t ring_bytes, int max_grp, int hown_cap) {
+__host__ __device__ inline size_t smem_misc_bytes(int hown_cap, int n_phases) { return NSLOT * 16 + 64 * 4 + NSLOT * 4 + 128 * 8 + ((size_t)hown_cap * 4 + 15) / 16 * 16 + (size_t)n_phases * sizeof(Phase) + 64; }
+__device__ inline Smem carve_smem(uint8_t* base, uint32_t ring_bytes, int max_grp, int hown_cap) {   // hown_cap: multiple of 4
     Smem s; s.ring = base; s.ring_bytes = ring_bytes; uint8_t* p = base + ring_bytes;
     s.xq = (int8_t*)p; p += (size_t)max_grp * 2048;
     s.xbs = (int16_t*)p; p += (size_t)max_grp * 256;
     s.xd = (float*)p; p += (size_t)max_grp * 32;
     s.full = (uint64_t*)p; p += NSLOT * 8; s.empty = (uint64_t*)p; p += NSLOT * 8;
-    s.red = (float*)p; p += 64 * 4; s.q_end = (uint32_t*)p; p += NSLOT * 4; s.rope = (float2*)p; p += 128 * 8; s.hown = (float*)p;
+    s.red = (float*)p; p += 64 * 4; s.q_end = (uint32_t*)p; p += NSLOT * 4; s.rope = (float2*)p; p += 128 * 8; s.hown = (float*)p; p += ((size_t)hown_cap * 4 + 15) / 16 * 16; s.phases = (Phase*)p;
     return s;
 }
 
@@ -318,15 +323,11 @@ __device__ __forceinline__ void load_x(const Smem& sm, int g, int lane, XRegs& x
 }
 __device__ __forceinline__ uint32_t u4_get(const uint4& v, int i) { return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w; }
 
-// 6-bit scale / min unpack for sub-blocks 2j, 2j+1 of a K-quant super-block (gguf/quants.py:480-503), branch-free:
-// both sub-blocks of lane j live in the same two byte columns (2(j&1), 2(j&1)+1) of the three scale words.
+// scale / min of sub-blocks 2j, 2j+1 from the engine's per-lane 24-bit fields (quant.cuh k4_reencode)
 __device__ __forceinline__ void k4_scales(const uint4& hdr, int j, int& sc0, int& sc1, int& m0, int& m1) {
-    const int sh = (j & 1) << 4;
-    const uint32_t a = hdr.y >> sh, b = hdr.z >> sh, c = hdr.w >> sh;          // low 16 bits: the two bytes of interest
-    const uint32_t sc_lo = a & 0x3F3Fu, m_lo = b & 0x3F3Fu;                                     // sub-blocks 0..3
-    const uint32_t sc_hi = (c & 0x0F0Fu) | ((a >> 2) & 0x3030u), m_hi = ((c >> 4) & 0x0F0Fu) | ((b >> 2) & 0x3030u);   // 4..7
-    const uint32_t sc = j < 2 ? sc_lo : sc_hi, m = j < 2 ? m_lo : m_hi;
-    sc0 = sc & 0xFF; sc1 = sc >> 8; m0 = m & 0xFF; m1 = m >> 8;
+    const uint32_t lo = j < 2 ? hdr.y : (j == 2 ? hdr.z : hdr.w), hi = j < 2 ? hdr.z : hdr.w;
+    const uint32_t f = __funnelshift_r(lo, hi, (32 - 8 * j) & 31);          // bits [24j, 24j+24) of the 96-bit scale field
+    sc0 = f & 63; sc1 = (f >> 6) & 63; m0 = (f >> 12) & 63; m1 = (f >> 18) & 63;
 }
 
 __device__ __forceinline__ float lane_dot_q4k(const uint8_t* grp, int lane, const XRegs& x) {

@@ -21,3 +21,11 @@ for kind in ["embed", "qkv", "attn", "wo", "gate_up", "down", "lm_head"]:
     tot += wall.mean() * len(idx)
     print(f"{kind:8s} " + " ".join(f"{v:6.2f}" for v in d) + f" | {np.median(x[..., 6] - x[..., 0]):6.2f} | {wall.mean():7.2f} {np.median(skew):6.2f}  x{len(idx)}")
 print(f"sum of phase wall times: {tot:.1f} us/token")
+if "--wait" in sys.argv:
+    for kind in ["qkv", "wo", "gate_up", "down", "lm_head"]:
+        idx = [i for i, n in enumerate(names) if n == kind]
+        w = t[:, idx, :, 7] * 1e3 / 1950.0; s_ = t[:, idx, :, 5] - t[:, idx, :, 3]
+        ghz = np.median((t[:, idx, :, 4] - t[:, idx, :, 0]) * 1e3 / np.maximum((t[:, idx, :, 6] - t[:, idx, :, 0]) * 1e3, 1))
+        print(f"  {kind:8s} SM clock during phase: {ghz:.3f} GHz")
+        cyc = t[:, idx, :, 1] * 1e3; nst = np.maximum(t[:, idx, :, 2] * 1e3, 1)
+        print(f"  {kind:8s} warp0: stream window {np.median(s_):6.2f} us, waiting for data {np.median(w):6.2f} us, stages {np.median(nst):.0f}, compute {np.median(cyc/nst):.0f} cycles/stage, total compute {np.median(cyc):.0f} cyc => {np.median(cyc)/max(np.median(s_-w),1e-9)/1e3:.2f} GHz-equivalent")
