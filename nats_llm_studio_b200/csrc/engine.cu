@@ -12,6 +12,7 @@
 #include <mutex>
 
 #include "decode.cuh"
+#include "prefill.cuh"
 #include "sampler.cuh"
 
 namespace b200 {
@@ -439,6 +440,122 @@ int kernel_dequantize(int type, const void* raw, int64_t n_rows, int K, float* o
         if (e != cudaSuccess) rc = fail(B200_ERR_CUDA, cudaGetErrorString(e));
     }
     cudaFree(d_raw); cudaFree(d_w); cudaFree(d_out);
+    return rc;
+}
+
+// ------------------------------------------------------------------------------------ prefill (batched prompt ingestion)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr; cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+// 2-D bf16 tensor [rows][cols] row-major, box = 64 cols x 128 rows, 128-byte swizzle, OOB rows read as zero
+static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols) {
+    EncodeTiledFn f = encode_tiled();
+    if (!f) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t dims[2] = {cols, rows}, strides[1] = {cols * 2};
+    cuuint32_t box[2] = {(cuuint32_t)GEMM_BK, (cuuint32_t)GEMM_BM}, estr[2] = {1, 1};
+    CUresult r = f(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed: " + std::to_string((int)r));
+    return B200_OK;
+}
+// C[M x N] (+)= A[M x K] . B[N x K]^T   (A, B bf16 device, C fp32 device)
+static int gemm_bf16(Engine& E, const __nv_bfloat16* A, const __nv_bfloat16* B, float* C, int M, int N, int K, int ldc, int mode, float scale) {
+    if (K % GEMM_BK) return fail(B200_ERR_INVALID, "GEMM K must be a multiple of 64");
+    static bool attr = false;
+    if (!attr) { CK(cudaFuncSetAttribute(gemm_bf16_tcgen05, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM)); attr = true; }
+    CUtensorMap ta, tb;
+    if (int rc = make_tmap(&ta, A, (uint64_t)M, (uint64_t)K)) return rc;
+    if (int rc = make_tmap(&tb, B, (uint64_t)N, (uint64_t)K)) return rc;
+    dim3 grid((N + GEMM_BN - 1) / GEMM_BN, (M + GEMM_BM - 1) / GEMM_BM);
+    gemm_bf16_tcgen05<<<grid, GEMM_THREADS, GEMM_SMEM, E.stream>>>(ta, tb, C, M, N, K, ldc, mode, scale);
+    CK(cudaGetLastError());
+    E.launches++;
+    return B200_OK;
+}
+
+static inline int nblk(long long n, int per = 256, int cap = 148 * 16) { return (int)std::max<long long>(1, std::min<long long>((n + per - 1) / per, cap)); }
+
+int Model::ensure_prefill_buffers() {
+    if (pf_H) return B200_OK;
+    const int D = n_embd, F = n_ff, QD = n_head * head_dim, KVD = n_head_kv * head_dim, Mc = PREFILL_CHUNK;
+    size_t wmax = std::max({(size_t)(QD + 2 * KVD) * D, (size_t)D * QD, (size_t)2 * F * D, (size_t)D * F});
+    int rc;
+    if ((rc = own(&pf_H, (size_t)Mc * D)) || (rc = own(&pf_X, (size_t)Mc * std::max(D, QD))) || (rc = own(&pf_Y, (size_t)Mc * std::max(QD + 2 * KVD, 2 * F))) ||
+        (rc = own(&pf_Q, (size_t)Mc * QD)) || (rc = own(&pf_ACT, (size_t)Mc * F)) || (rc = own(&pf_W, wmax)) || (rc = own(&pf_toks, (size_t)Mc)))
+        return rc;
+    return B200_OK;
+}
+
+// Ingest toks[0..n) at positions cur_pos.. through the tensor-core path: fills the KV pages; the hidden state of these
+// rows is discarded (the caller feeds the LAST prompt token through the decode kernel, which produces the logits).
+int Model::prefill(const int32_t* toks, int n) {
+    Engine& E = engine();
+    if (n <= 0) return B200_OK;
+    if (cur_pos + n > E.max_ctx) return fail(B200_ERR_INVALID, "context overflow in prefill");
+    if (int rc = ensure_prefill_buffers()) return rc;
+    const int D = n_embd, F = n_ff, QD = n_head * head_dim, KVD = n_head_kv * head_dim, W3 = QD + 2 * KVD;
+    const float rs = res_scale != 0.f ? res_scale : 1.f, kq = attn_scale != 0.f ? attn_scale : 1.0f / std::sqrt((float)head_dim);
+    KvLayout kv; kv.pages = d_kv; kv.block_table = d_block_table; kv.n_layer = n_layer; kv.n_head_kv = n_head_kv; kv.head_dim = head_dim;
+    auto deq = [&](const Matrix& m, __nv_bfloat16* dst) {
+        dequant_bf16_kernel<<<nblk(m.n_rows * (long long)m.K / 2), 256, 0, E.stream>>>(m.w, m.type, m.n_rows, m.K, dst); E.launches++;
+    };
+    for (int c0 = 0; c0 < n; c0 += PREFILL_CHUNK) {
+        const int M = std::min(PREFILL_CHUNK, n - c0), pos0 = cur_pos + c0;
+        CK(cudaMemcpyAsync(pf_toks, toks + c0, (size_t)M * 4, cudaMemcpyHostToDevice, E.stream));
+        embed_rows_kernel<<<nblk((long long)M * D), 256, 0, E.stream>>>(tok_embd.w, tok_embd.type, D, pf_toks, M, emb_scale, pf_H); E.launches++;
+        for (int l = 0; l < n_layer; l++) {
+            Layer& L = layers[l];
+            rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, L.attn_norm, D, M, rms_eps, pf_X); E.launches++;
+            deq(L.wq, pf_W); deq(L.wk, pf_W + (size_t)QD * D); deq(L.wv, pf_W + (size_t)(QD + KVD) * D);
+            if (int rc = gemm_bf16(E, pf_X, pf_W, pf_Y, M, W3, D, W3, 0, 1.f)) return rc;
+            rope_kv_rows_kernel<<<nblk((long long)M * W3 / 2), 256, 0, E.stream>>>(pf_Y, M, pos0, l, n_head, n_head_kv, head_dim, n_rot, inv_freq, kv, pf_Q); E.launches++;
+            if (head_dim == 128) attn_prefill_kernel<4><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, pos0, l, n_head, n_head_kv, kq, kv, pf_X);
+            else attn_prefill_kernel<2><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, pos0, l, n_head, n_head_kv, kq, kv, pf_X);
+            E.launches++;
+            deq(L.wo, pf_W);
+            if (int rc = gemm_bf16(E, pf_X, pf_W, pf_H, M, D, QD, D, 1, rs)) return rc;
+            if (l == n_layer - 1) break;                              // the last layer's FFN only feeds logits nobody reads
+            rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, L.ffn_norm, D, M, rms_eps, pf_X); E.launches++;
+            deq(L.wgu, pf_W);
+            if (int rc = gemm_bf16(E, pf_X, pf_W, pf_Y, M, 2 * F, D, 2 * F, 0, 1.f)) return rc;
+            swiglu_rows_kernel<<<nblk((long long)M * F), 256, 0, E.stream>>>(pf_Y, M, F, pf_ACT); E.launches++;
+            deq(L.wd, pf_W);
+            if (int rc = gemm_bf16(E, pf_ACT, pf_W, pf_H, M, D, F, D, 1, rs)) return rc;
+        }
+        CK(cudaGetLastError());
+    }
+    cur_pos += n;
+    int st = cur_pos; CK(cudaMemcpyAsync(d_state, &st, 4, cudaMemcpyHostToDevice, E.stream));
+    CK(cudaStreamSynchronize(E.stream));                              // toks/st are stack or caller memory
+    return B200_OK;
+}
+
+// test entry: C = A . B^T with host fp32 inputs rounded to bf16 on the way in
+int kernel_gemm_bf16(const float* A, const float* B, float* C, int M, int N, int K) {
+    Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    if (M <= 0 || N <= 0 || K <= 0 || K % GEMM_BK) return fail(B200_ERR_INVALID, "K must be a multiple of 64");
+    std::vector<__nv_bfloat16> ha((size_t)M * K), hb((size_t)N * K);
+    for (size_t i = 0; i < ha.size(); i++) ha[i] = __float2bfloat16(A[i]);
+    for (size_t i = 0; i < hb.size(); i++) hb[i] = __float2bfloat16(B[i]);
+    __nv_bfloat16 *dA = nullptr, *dB = nullptr; float* dC = nullptr; int rc;
+    if ((rc = dalloc(&dA, ha.size())) || (rc = dalloc(&dB, hb.size())) || (rc = dalloc(&dC, (size_t)M * N))) { cudaFree(dA); cudaFree(dB); cudaFree(dC); return rc; }
+    cudaMemcpyAsync(dA, ha.data(), ha.size() * 2, cudaMemcpyHostToDevice, E.stream);
+    cudaMemcpyAsync(dB, hb.data(), hb.size() * 2, cudaMemcpyHostToDevice, E.stream);
+    cudaMemsetAsync(dC, 0, (size_t)M * N * 4, E.stream);
+    rc = gemm_bf16(E, dA, dB, dC, M, N, K, N, 0, 1.f);
+    if (!rc) {
+        cudaError_t e = cudaMemcpyAsync(C, dC, (size_t)M * N * 4, cudaMemcpyDeviceToHost, E.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(E.stream);
+        if (e != cudaSuccess) rc = fail(B200_ERR_CUDA, cudaGetErrorString(e));
+    }
+    cudaFree(dA); cudaFree(dB); cudaFree(dC);
     return rc;
 }
 

@@ -1,5 +1,6 @@
 // engine.hpp — host-side declarations shared by engine.cu, handlers.cpp and capi.cpp.
 #pragma once
+#include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
@@ -62,6 +63,10 @@ struct Model {
     int grid = 0, smem_max_grp = 0; uint32_t ring_bytes = 0; size_t smem_bytes = 0;
     int cur_pos = 0;
     long long* d_trace = nullptr;
+    // prefill scratch (allocated on first use)
+    static constexpr int PREFILL_CHUNK = 512;
+    float *pf_H = nullptr, *pf_Y = nullptr; __nv_bfloat16 *pf_X = nullptr, *pf_Q = nullptr, *pf_ACT = nullptr, *pf_W = nullptr; int* pf_toks = nullptr;
+    int prefill_min = 32;                        // prompts shorter than this go through the decode kernel token by token
     std::mutex run_mu;
 
     ~Model();
@@ -78,6 +83,8 @@ struct Model {
     int eval(const int32_t* toks, int n, float* logits_all, float* logits_last);
     double bytes_per_token(int ctx) const;
     int bench_decode(int ctx_len, int n_steps, int warmup, float* ms_per_token, double* bytes);
+    int ensure_prefill_buffers();
+    int prefill(const int32_t* toks, int n);
     // tokenizer (tokenizer.cpp)
     void build_tokenizer();
     std::vector<int32_t> tokenize(const std::string& text, bool parse_special) const;
@@ -88,6 +95,7 @@ struct Model {
 int sample_token(Engine& E, Model& m, const b200_sampling& s, uint64_t step);
 int kernel_dequantize(int type, const void* raw, int64_t n_rows, int K, float* out);
 int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, float* y, int iters, float* ms);
+int kernel_gemm_bf16(const float* A, const float* B, float* C, int M, int N, int K);
 int kernel_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K, float* d_out);
 int layout_selftest();
 

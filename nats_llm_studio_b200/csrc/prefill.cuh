@@ -1,0 +1,260 @@
+// prefill.cuh — batched prompt ingestion (K2, K7 of SURVEY.md §2.3): the part of LM Studio's
+// /api/v0/chat/completions work (nats_llm_studio.go:158-179) that really is a dense contraction.
+//   * gemm_bf16_tcgen05: Y[M x N] (+)= X[M x K] . W[N x K]^T on the 5th-generation tensor cores: operands
+//     staged by TMA (cp.async.bulk.tensor, 128-byte swizzle) through a 4-deep shared-memory ring, one elected
+//     thread issues tcgen05.mma (kind::f16, bf16 x bf16 -> fp32) into a TMEM accumulator, tcgen05.commit
+//     releases ring slots and signals the epilogue, which reads TMEM with tcgen05.ld.
+//   * dequant_bf16_kernel: engine-layout quantised matrix -> bf16 rows (the GEMM's B operand).
+//   * row-wise helpers: embedding gather, RMSNorm -> bf16, RoPE + KV-page write, SwiGLU, causal attention over
+//     the paged fp16 KV cache.
+// Numerics: bf16 operands, fp32 accumulation; the KV pages it writes are consumed by the decode kernel.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+#include "decode.cuh"
+
+namespace b200 {
+
+constexpr int GEMM_BM = 128, GEMM_BN = 128, GEMM_BK = 64, GEMM_STAGES = 4;
+constexpr int GEMM_THREADS = 128;
+constexpr uint32_t GEMM_STAGE_BYTES = (GEMM_BM + GEMM_BN) * GEMM_BK * 2;      // 32 KB
+constexpr size_t GEMM_SMEM = GEMM_STAGES * GEMM_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+
+// ------------------------------------------------------------------------------------ tcgen05 / TMA wrappers
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tcgen05_alloc(uint32_t* dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tcgen05_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// D[tmem] (+)= A[smem desc] . B[smem desc]^T, bf16 inputs, fp32 accumulate
+__device__ __forceinline__ void tcgen05_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// shared-memory matrix descriptor: K-major tile, 128-byte swizzle, rows of 128 B, 8-row groups 1024 B apart
+__device__ __forceinline__ uint64_t umma_desc_sw128(const void* smem) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_u32(smem) & 0x3FFFF) >> 4);        // start address >> 4            bits [0,14)
+    d |= (uint64_t)1 << 16;                                  // leading byte offset (unused for swizzled K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;                        // stride byte offset >> 4        bits [32,46)
+    d |= (uint64_t)1 << 46;                                  // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;                                  // layout: SWIZZLE_128B
+    return d;
+}
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
+    return (1u << 4)                 // D format: F32
+         | (1u << 7)                 // A format: BF16
+         | (1u << 10)                // B format: BF16
+         | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);   // A, B K-major (bits 15,16 = 0)
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]),
+          "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
+          "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// ------------------------------------------------------------------------------------ the GEMM
+// C[M x N] fp32 row-major (ldc).  mode 0: C = acc * scale; mode 1: C += acc * scale (residual add).
+// One 128x128 output tile per CTA; K is a multiple of 64; M, N edges are zero-filled by TMA and masked on store.
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, float* __restrict__ C,
+                  int M, int N, int K, int ldc, int mode, float scale) {
+    extern __shared__ uint8_t gemm_smem_raw[];
+    uint8_t* base = (uint8_t*)(((uintptr_t)gemm_smem_raw + 1023) & ~(uintptr_t)1023);       // SWIZZLE_128B needs 1024-byte alignment
+    uint8_t* sA = base; uint8_t* sB = base + GEMM_STAGES * GEMM_BM * GEMM_BK * 2;
+    uint64_t* full = (uint64_t*)(base + GEMM_STAGES * GEMM_STAGE_BYTES);
+    uint64_t* empty = full + GEMM_STAGES; uint64_t* tmem_full = empty + GEMM_STAGES; uint32_t* tmem_slot = (uint32_t*)(tmem_full + 1);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int m0 = blockIdx.y * GEMM_BM, n0 = blockIdx.x * GEMM_BN, nkb = K / GEMM_BK;
+    if (tid == 0) {
+        for (int i = 0; i < GEMM_STAGES; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        mbar_init(tmem_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tcgen05_alloc(tmem_slot, GEMM_BN);          // 128 fp32 columns x 128 lanes
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_acc = *tmem_slot;
+
+    if (tid == 0) {                         // ===== TMA producer =====
+        for (int kb = 0; kb < nkb; kb++) {
+            const int s = kb % GEMM_STAGES; const uint32_t ph = (kb / GEMM_STAGES) & 1;
+            mbar_wait(&empty[s], ph ^ 1);
+            mbar_expect_tx(&full[s], GEMM_STAGE_BYTES);
+            tma_load_2d(sA + s * GEMM_BM * GEMM_BK * 2, &tmap_a, kb * GEMM_BK, m0, &full[s]);
+            tma_load_2d(sB + s * GEMM_BN * GEMM_BK * 2, &tmap_b, kb * GEMM_BK, n0, &full[s]);
+        }
+    } else if (tid == 32) {                 // ===== MMA issuer =====
+        constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, GEMM_BN);
+        for (int kb = 0; kb < nkb; kb++) {
+            const int s = kb % GEMM_STAGES; const uint32_t ph = (kb / GEMM_STAGES) & 1;
+            mbar_wait(&full[s], ph);
+            tcgen05_fence_after();
+            const uint64_t da = umma_desc_sw128(sA + s * GEMM_BM * GEMM_BK * 2), db = umma_desc_sw128(sB + s * GEMM_BN * GEMM_BK * 2);
+#pragma unroll
+            for (int k = 0; k < GEMM_BK / 16; k++)            // UMMA_K = 16 bf16 = 32 bytes: advance the start address by 2 (>>4 units)
+                tcgen05_mma_f16(tmem_acc, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+            tcgen05_commit(&empty[s]);                         // frees the ring slot when these MMAs have read it
+        }
+        tcgen05_commit(tmem_full);                             // accumulator complete
+    }
+    // ===== epilogue: warp w owns TMEM lanes 32w..32w+31 = output rows m0 + 32w + lane =====
+    mbar_wait(tmem_full, 0);
+    __syncwarp();                                              // tcgen05.ld is warp-collective
+    tcgen05_fence_after();
+    const int row = m0 + warp * 32 + lane;
+#pragma unroll 1
+    for (int c = 0; c < GEMM_BN; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tmem_acc + ((uint32_t)(warp * 32) << 16) + c, r);
+        if (row < M) {
+            float* dst = C + (size_t)row * ldc + n0 + c;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                if (n0 + c + j + 3 < N) {
+                    float4 v = make_float4(__uint_as_float(r[j]) * scale, __uint_as_float(r[j + 1]) * scale, __uint_as_float(r[j + 2]) * scale, __uint_as_float(r[j + 3]) * scale);
+                    if (mode == 1) { const float4 o = *(const float4*)(dst + j); v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+                    *(float4*)(dst + j) = v;
+                } else {
+                    for (int e = 0; e < 4; e++) if (n0 + c + j + e < N) { float v = __uint_as_float(r[j + e]) * scale; if (mode == 1) v += dst[j + e]; dst[j + e] = v; }
+                }
+            }
+        }
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 0) tcgen05_dealloc(tmem_acc, GEMM_BN);
+}
+
+// ------------------------------------------------------------------------------------ row-wise kernels
+// engine-layout quantised matrix -> bf16 [n_rows x K] (row r of the matrix at out + r*K)
+__global__ void dequant_bf16_kernel(const uint8_t* __restrict__ w, int type, long long n_rows, int K, __nv_bfloat16* __restrict__ out) {
+    const int ng = n_groups(K);
+    for (long long i = (blockIdx.x * (long long)blockDim.x + threadIdx.x) * 2; i < n_rows * K; i += (long long)gridDim.x * blockDim.x * 2) {
+        const int row = (int)(i / K), e = (int)(i % K);
+        const float a = embed_elem(w, type, ng, row, e), b = embed_elem(w, type, ng, row, e + 1);
+        *(__nv_bfloat162*)(out + i) = __floats2bfloat162_rn(a, b);
+    }
+}
+
+// H[m][:] = dequant(token_embd[tok[m]]) * emb_scale
+__global__ void embed_rows_kernel(const uint8_t* __restrict__ embd, int type, int D, const int* __restrict__ toks, int M, float emb_scale, float* __restrict__ H) {
+    const int ng = n_groups(D);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)M * D; i += (long long)gridDim.x * blockDim.x) {
+        const int m = (int)(i / D), e = (int)(i % D);
+        float v = embed_elem(embd, type, ng, toks[m], e);
+        H[i] = emb_scale != 0.f ? v * emb_scale : v;
+    }
+}
+
+// X[m][:] = bf16(rmsnorm(H[m]) * w); one warp per row
+__global__ void rmsnorm_rows_kernel(const float* __restrict__ H, const float* __restrict__ w, int D, int M, float eps, __nv_bfloat16* __restrict__ X) {
+    const int m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (m >= M) return;
+    const float* h = H + (size_t)m * D; float ss = 0.f;
+    for (int i = lane * 4; i < D; i += 128) { const float4 v = *(const float4*)(h + i); ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w; }
+    ss = warp_sum(ss);
+    const float rs = rsqrtf(ss / (float)D + eps);
+    for (int i = lane * 4; i < D; i += 128) {
+        const float4 v = *(const float4*)(h + i), g = *(const float4*)(w + i);
+        *(__nv_bfloat162*)(X + (size_t)m * D + i) = __floats2bfloat162_rn(v.x * rs * g.x, v.y * rs * g.y);
+        *(__nv_bfloat162*)(X + (size_t)m * D + i + 2) = __floats2bfloat162_rn(v.z * rs * g.z, v.w * rs * g.w);
+    }
+}
+
+// QKV[m][QD + 2*KVD] fp32 -> RoPE(q) as bf16 Q[m][QD]; RoPE(k), v -> fp16 KV pages at position pos0 + m
+__global__ void rope_kv_rows_kernel(const float* __restrict__ QKV, int M, int pos0, int layer, int n_head, int n_head_kv, int HD, int n_rot,
+                                    const float* __restrict__ inv_freq, KvLayout kv, __nv_bfloat16* __restrict__ Q) {
+    const int QD = n_head * HD, KVD = n_head_kv * HD, W = QD + 2 * KVD;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)M * (W / 2); i += (long long)gridDim.x * blockDim.x) {
+        const int m = (int)(i / (W / 2)), c = (int)(i % (W / 2)) * 2, pos = pos0 + m;
+        float a = QKV[(size_t)m * W + c], b = QKV[(size_t)m * W + c + 1];
+        if (c < QD + KVD) {                               // q or k: rotate the adjacent pair
+            const int d = c % HD;
+            if (d < n_rot) { float sn, cs; sincosf((float)pos * inv_freq[d >> 1], &sn, &cs); const float x = a, y = b; a = x * cs - y * sn; b = x * sn + y * cs; }
+        }
+        if (c < QD) *(__nv_bfloat162*)(Q + (size_t)m * QD + c) = __floats2bfloat162_rn(a, b);
+        else if (c < QD + KVD) { const int r = c - QD; *(__half2*)(kv.at(layer, 0, r / HD, pos) + r % HD) = __floats2half2_rn(a, b); }
+        else { const int r = c - QD - KVD; *(__half2*)(kv.at(layer, 1, r / HD, pos) + r % HD) = __floats2half2_rn(a, b); }
+    }
+}
+
+// causal attention for the M new rows (positions pos0..pos0+M-1) over the paged KV cache; one warp per (row, head)
+template <int VEC>
+__global__ void attn_prefill_kernel(const __nv_bfloat16* __restrict__ Q, int M, int pos0, int layer, int n_head, int n_head_kv, float kq_scale,
+                                    KvLayout kv, __nv_bfloat16* __restrict__ O) {
+    constexpr int HD = 32 * VEC, NB = 8;
+    const int gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (gw >= M * n_head) return;
+    const int m = gw / n_head, head = gw % n_head, kvh = head / (n_head / n_head_kv), n_ctx = pos0 + m + 1;
+    float qv[VEC], acc[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; i++) { qv[i] = __bfloat162float(Q[(size_t)m * n_head * HD + head * HD + lane * VEC + i]) * kq_scale; acc[i] = 0.f; }
+    float mx = -INFINITY, l = 0.f;
+    for (int pb = 0; pb < n_ctx; pb += NB) {
+        float kf[NB][VEC], vf[NB][VEC];
+#pragma unroll
+        for (int b = 0; b < NB; b++) {
+            const int p = pb + b;
+            if (p < n_ctx) {
+                const __half* kp = kv.at(layer, 0, kvh, p) + lane * VEC; const __half* vp = kv.at(layer, 1, kvh, p) + lane * VEC;
+#pragma unroll
+                for (int i = 0; i < VEC; i += 2) {
+                    const float2 a = __half22float2(*(const __half2*)(kp + i)), c2 = __half22float2(*(const __half2*)(vp + i));
+                    kf[b][i] = a.x; kf[b][i + 1] = a.y; vf[b][i] = c2.x; vf[b][i + 1] = c2.y;
+                }
+            }
+        }
+#pragma unroll
+        for (int b = 0; b < NB; b++) {
+            if (pb + b >= n_ctx) break;
+            float s = 0.f;
+#pragma unroll
+            for (int i = 0; i < VEC; i++) s += qv[i] * kf[b][i];
+            s = warp_sum(s);
+            const float mn = fmaxf(mx, s), corr = __expf(mx - mn), pe = __expf(s - mn);
+            l = l * corr + pe;
+#pragma unroll
+            for (int i = 0; i < VEC; i++) acc[i] = acc[i] * corr + pe * vf[b][i];
+            mx = mn;
+        }
+    }
+    const float inv = 1.f / l;
+#pragma unroll
+    for (int i = 0; i < VEC; i++) O[(size_t)m * n_head * HD + head * HD + lane * VEC + i] = __float2bfloat16(acc[i] * inv);
+}
+
+// ACT[m][i] = bf16(silu(GU[m][2i]) * GU[m][2i+1])   (gate/up rows are interleaved in the fused matrix)
+__global__ void swiglu_rows_kernel(const float* __restrict__ GU, int M, int F, __nv_bfloat16* __restrict__ ACT) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)M * F; i += (long long)gridDim.x * blockDim.x) {
+        const float2 gu = *(const float2*)(GU + 2 * i);
+        ACT[i] = __float2bfloat16(gu.x / (1.f + __expf(-gu.x)) * gu.y);
+    }
+}
+
+}  // namespace b200
