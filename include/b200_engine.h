@@ -111,6 +111,12 @@ int b200_dequantize(int type, const void* raw_blocks, int64_t n_rows, int K, flo
 int b200_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K, float* d_out);
 /* y[N] = W[N x K] . x[K] through the streaming GEMV; iters>1 repeats the launch, ms = mean per iter */
 int b200_gemv(int type, const void* raw_blocks, int64_t N, int K, const float* x, float* y, int iters, float* ms);
+/* C[M x N] = A[M x K] . B[N x K]^T through the tcgen05/TMEM/TMA GEMM that prompt ingestion uses (inputs rounded to
+ * bf16, fp32 accumulate); K % 64 == 0.  Host buffers. */
+int b200_gemm_bf16(const float* A, const float* B, float* C, int M, int N, int K);
+/* prompts with at least n tokens are ingested by the batched tensor-core path, shorter ones token by token through
+ * the decode kernel (n <= 0: never batch).  Default 32. */
+int b200_model_set_prefill_min(b200_model* m, int n);
 /* decode-step timing: n_steps greedy tokens from the current position of a primed context */
 int b200_bench_decode(b200_model* m, int ctx_len, int n_steps, int warmup, float* ms_per_token, double* bytes_per_token);
 /* number of kernels this library has launched so far (bench.py reports the delta as gpu_launches) */

@@ -321,8 +321,15 @@ int Model::generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_s
     int rc = B200_OK; int produced = 0;
     CK(cudaEventRecord(e0, E.stream));
     if (greedy) {
-        // prompt + first token in one launch, then the remaining tokens in chunks (EOS checked between chunks)
-        if ((rc = run_steps(n_prompt, prompt, n_prompt, true, nullptr))) goto done;
+        // prompt + first token, then the remaining tokens in chunks (EOS checked between chunks).  Long prompts:
+        // all but the last token go through the tensor-core prefill (KV pages only), the last one through the decode
+        // kernel, which produces the first generated token.
+        if (prefill_min > 0 && n_prompt - 1 >= prefill_min) {
+            { int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0; }
+            if ((rc = prefill(prompt, n_prompt - 1))) goto done;
+            if ((rc = run_steps(1, prompt + n_prompt - 1, 1, false, nullptr))) goto done;
+            CK(cudaMemcpyAsync(d_out_tokens + n_prompt - 1, d_out_tokens, 4, cudaMemcpyDeviceToDevice, E.stream));
+        } else if ((rc = run_steps(n_prompt, prompt, n_prompt, true, nullptr))) goto done;
         CK(cudaEventRecord(e1, E.stream));
         CK(cudaMemcpyAsync(out, d_out_tokens + n_prompt - 1, 4, cudaMemcpyDeviceToHost, E.stream));
         CK(cudaStreamSynchronize(E.stream));
@@ -338,7 +345,11 @@ int Model::generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_s
         }
     } else {
         // sampled: one step per launch with logits, then the sampler kernel picks the token
-        if ((rc = run_steps(n_prompt, prompt, n_prompt, true, nullptr))) goto done;
+        if (prefill_min > 0 && n_prompt - 1 >= prefill_min) {
+            { int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0; }
+            if ((rc = prefill(prompt, n_prompt - 1))) goto done;
+            if ((rc = run_steps(1, prompt + n_prompt - 1, 1, false, nullptr))) goto done;
+        } else if ((rc = run_steps(n_prompt, prompt, n_prompt, true, nullptr))) goto done;
         for (;;) {
             if ((rc = sample_token(E, *this, *s, (uint64_t)produced))) goto done;
             if (produced == 0) CK(cudaEventRecord(e1, E.stream));
@@ -364,7 +375,12 @@ int Model::eval(const int32_t* toks, int n, float* logits_all, float* logits_las
     for (int i = 0; i < n; i++) if (toks[i] < 0 || toks[i] >= n_vocab) return fail(B200_ERR_INVALID, "token out of range");
     float* d_all = nullptr;
     if (logits_all) { if (int rc = dalloc(&d_all, (size_t)n * n_vocab)) return rc; }
-    int rc = run_steps(n, toks, n, true, d_all);
+    int rc;
+    if (!logits_all && prefill_min > 0 && n - 1 >= prefill_min) {      // only the last position's logits: batched ingestion of the rest
+        int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0;
+        rc = prefill(toks, n - 1);
+        if (!rc) rc = run_steps(1, toks + n - 1, 1, false, nullptr);
+    } else rc = run_steps(n, toks, n, true, d_all);
     if (!rc) {
         cudaError_t e = cudaStreamSynchronize(E.stream);
         if (e == cudaSuccess && logits_all) e = cudaMemcpy(logits_all, d_all, (size_t)n * n_vocab * 4, cudaMemcpyDeviceToHost);

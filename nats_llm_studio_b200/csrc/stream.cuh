@@ -22,7 +22,10 @@
 
 namespace b200 {
 
-constexpr int GROUP_WARPS = 8;           // warps that share one stage (one row pair each)
+#ifndef B200_GROUP_WARPS
+#define B200_GROUP_WARPS 8
+#endif
+constexpr int GROUP_WARPS = B200_GROUP_WARPS;   // warps that share one stage (one row pair each)
 #ifndef B200_WARP_GROUPS
 #define B200_WARP_GROUPS 2
 #endif

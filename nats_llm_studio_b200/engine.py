@@ -51,6 +51,7 @@ SYMBOLS = {
     "b200_handle": (ci, [C.c_char_p, vp, sz, vp, sz, C.POINTER(sz)]), "b200_set_models_dir": (ci, [C.c_char_p]),
     "b200_dequantize": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_dequantize_noalloc": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_gemv": (ci, [ci, vp, C.c_int64, ci, vp, vp, ci, C.POINTER(C.c_float)]),
     "b200_bench_decode": (ci, [vp, ci, ci, ci, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
+    "b200_gemm_bf16": (ci, [vp, vp, vp, ci, ci, ci]), "b200_model_set_prefill_min": (ci, [vp, ci]),
     "b200_launch_count": (C.c_uint64, []), "b200_layout_selftest": (ci, []),
 }
 
@@ -121,6 +122,9 @@ class Model:
         _check(lib().b200_model_generate(self.h, prompt.ctypes.data, len(prompt), n_gen, C.byref(s), out.ctypes.data,
                                          C.byref(n_out), C.byref(ttft), C.byref(dec)))
         return out[:n_out.value], ttft.value, dec.value
+
+    def set_prefill_min(self, n):
+        _check(lib().b200_model_set_prefill_min(self.h, n))
 
     def bench_decode(self, ctx_len, n_steps, warmup):
         ms, by = C.c_float(0), C.c_double(0)
@@ -193,6 +197,14 @@ class Engine:
         ms = C.c_float(0)
         _check(lib().b200_gemv(GGML_TYPES[type_name], raw.ctypes.data, N, K, x.ctypes.data, y.ctypes.data, iters, C.byref(ms)))
         return y, ms.value
+
+    @staticmethod
+    def gemm_bf16(A, B):
+        A = np.ascontiguousarray(A, dtype=np.float32); B = np.ascontiguousarray(B, dtype=np.float32)
+        M, K = A.shape; N = B.shape[0]
+        Cm = np.empty((M, N), dtype=np.float32)
+        _check(lib().b200_gemm_bf16(A.ctypes.data, B.ctypes.data, Cm.ctypes.data, M, N, K))
+        return Cm
 
     @staticmethod
     def launch_count():
