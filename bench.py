@@ -129,7 +129,7 @@ def main():
         times = []
         cb = None
         for _ in range(1):                      # each "step" of this arm is one bounded sample; K/W do not multiply a 10 s/token CPU run
-            cb = cpu_reference_arm(path, 2, 3)
+            cb = cpu_reference_arm(path, 4, 12)
             times.append(cb["value"])
         line = {"metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": K, "warmup": W, "ms_per_step": 1e3 / cb["value"],
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
@@ -179,7 +179,15 @@ def main():
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0)); peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md 6.65 TB/s)"
     achieved = bytes_tok / (ms_tok * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    traffic = None; traffic_src = None
+    try:                                            # DRAM bytes/token measured by ncu --set full on this kernel (profiles/), scaled to this launch
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        if tj.get("workload_key") == f"{a.preset}-{a.mix}" and not a.n_layer:
+            traffic = tj["dram_bytes_per_token"] * K; traffic_src = tj["source"]
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                "algorithmic_bytes_per_launch": bytes_tok * K,
                 "kernel": "decode_kernel (persistent, 1 launch = K tokens)", "algorithmic_bytes_per_token": bytes_tok, "peak_source": peak_src}
 
     # ---- end to end through the reference-facing handler, host buffers
@@ -202,7 +210,7 @@ def main():
 
     cb = None
     if rank == 0 and world == 1 and not a.no_cpu:
-        cb = cpu_reference_arm(path, 2, 3)
+        cb = cpu_reference_arm(path, 4, 12)
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_total / K,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8 x int4/6/8 dp4a, fp32 accumulate", "data": "synthetic",
