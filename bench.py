@@ -37,7 +37,7 @@ UNIT = "tok/s"
 
 def model_path(preset, mix, n_layer, rank):
     import make_gguf
-    d = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else "/tmp"
+    d = os.environ.get("B200_BENCH_DIR") or ("/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else "/tmp")
     tag = f"{preset}-{mix}" + (f"-L{n_layer}" if n_layer else "")
     path = os.path.join(d, f"b200bench-{tag}.gguf")
     if not os.path.exists(path):
@@ -85,6 +85,21 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
+
+
+def reduce_max(value, dist=None, device="cpu"):
+    """Max over ranks of a per-rank time (the multi-GPU contract: never the rank-0 clock alone)."""
+    if dist is None:
+        return float(value)
+    import torch
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def aggregate_value(world, steps, ms_total_max):
+    """N independent replicas, each decoding `steps` tokens: whole-job tokens/s over the slowest rank's time."""
+    return world * steps / (ms_total_max * 1e-3)
 
 
 def cpu_reference_arm(path, n_prompt, n_gen):
@@ -169,9 +184,8 @@ def main():
     barrier()
     clk = clocks.stop()
     ms_total = ms_tok * K
-    if dist:
-        t = torch.tensor([ms_total], device="cuda", dtype=torch.float64); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms_total = float(t.item())
-    value = world * K / (ms_total * 1e-3)
+    ms_total = reduce_max(ms_total, dist, "cuda")
+    value = aggregate_value(world, K, ms_total)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -202,8 +216,7 @@ def main():
         wall = time.perf_counter() - t0
         rep = json.loads(rep_raw)["data"]["response"]
         ntok = rep["usage"]["completion_tokens"]; npr = rep["usage"]["prompt_tokens"]
-        if dist:
-            t = torch.tensor([wall], device="cuda", dtype=torch.float64); dist.all_reduce(t, op=dist.ReduceOp.MAX); wall = float(t.item())
+        wall = reduce_max(wall, dist, "cuda")
         e2e = {"value": world * ntok / wall, "unit": UNIT, "h2d_bytes_per_step": (len(req) + 4 * npr) / ntok, "d2h_bytes_per_step": 4 + len(rep_raw) / ntok,
                "wall_s": wall, "prompt_tokens": npr, "completion_tokens": ntok, "ttft_s": rep["stats"]["time_to_first_token"],
                "decode_tok_s_inside_call": rep["stats"]["tokens_per_second"]}
