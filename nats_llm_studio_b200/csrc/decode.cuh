@@ -107,7 +107,7 @@ __device__ __forceinline__ float embed_elem(const uint8_t* w, int type, int n_gr
 // cached K/V loads are issued BEFORE q is polled (they do not depend on this token), so the exchange wait and the
 // first memory round trip overlap.
 template <int VEC>   // head_dim = 32*VEC
-__device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int head, int split, int pos, uint32_t seq_in, uint32_t seq_out, int warp, int lane) {
+__device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int head, int split, int pos, uint32_t seq_in, uint32_t seq_out, int warp, int lane, long long* tr) {
     constexpr int HD = 32 * VEC, NB = 8;
     typedef typename std::conditional<VEC == 4, uint2, uint32_t>::type raw_t;     // VEC fp16 values
     const int n_ctx = pos + 1, chunk = (n_ctx + P.n_splits - 1) / P.n_splits;
@@ -122,8 +122,9 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
         for (int b = 0; b < NB; b++) {
             const int p = pb + b * CONSUMER_WARPS;
             if (p < p1 && p < pos) {
-                kr[b] = __ldcg((const raw_t*)(P.kv.at(layer, 0, kvh, p) + lane * VEC));
-                vr[b] = __ldcg((const raw_t*)(P.kv.at(layer, 1, kvh, p) + lane * VEC));
+                const int page = sm.btab[p >> 4];                     // block table cached in shared memory: no dependent L2 load
+                kr[b] = __ldcg((const raw_t*)(P.kv.at_page(page, layer, 0, kvh, p) + lane * VEC));
+                vr[b] = __ldcg((const raw_t*)(P.kv.at_page(page, layer, 1, kvh, p) + lane * VEC));
             }
         }
     };
@@ -136,6 +137,7 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
 #pragma unroll
         for (int i = 0; i < VEC; i++) { qv[i] = t[i] * P.kq_scale; acc[i] = 0.f; }
     }
+    if (tr && warp == 0 && lane == 0) tr[1] = gtime();
     float m = -INFINITY, l = 0.f;
     for (int pb = p0 + warp; pb < p1; pb += CONSUMER_WARPS * NB) {
         if (pb != p0 + warp) load_batch(pb, kr, vr);
@@ -171,6 +173,7 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
             m = mn;
         }
     }
+    if (tr && warp == 0 && lane == 0) tr[2] = gtime();
     // cross-warp combine through shared memory (aliases the activation buffer, idle in this phase)
     float* scr = (float*)sm.xq;                     // [8 warps][HD + 2]
     consumer_sync();
@@ -197,6 +200,7 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
             if (tid == 0) { st_relaxed_v2(P.part_ll + o + HD, __float_as_uint(M), seq_out); st_relaxed_v2(P.part_ll + o + HD + 1, __float_as_uint(L), seq_out); }
         } else { scr[CONSUMER_WARPS * (HD + 2) + tid] = a; if (tid == 0) { scr[CONSUMER_WARPS * (HD + 2) + HD] = M; scr[CONSUMER_WARPS * (HD + 2) + HD + 1] = L; } }
     }
+    if (tr && warp == 0 && lane == 0) tr[3] = tr[4] = tr[5] = gtime();
     if (P.n_splits > 1 && split == 0) {
         // This CTA is the head's combiner: gather the other splits' partials (all loads in flight together,
         // re-polled until every tag matches), merge with its own, publish the head's output once.
@@ -218,6 +222,7 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
             }
         }
         consumer_sync();
+        if (tr && warp == 0 && lane == 0) tr[4] = gtime();
         if (tid < HD) {
             float M = own[HD];
             for (int s = 1; s < S; s++) M = fmaxf(M, mls[2 * s]);
@@ -230,6 +235,7 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
             }
             st_rep_u32(P.att_ll, P.att_stride, head * HD + tid, ll16_pack(a / L, tag16_of(seq_out)));
         }
+        if (tr && warp == 0 && lane == 0) tr[5] = gtime();
     }
 }
 
@@ -490,6 +496,7 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
         for (int i = 0; i < NSLOT; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], GROUP_WARPS); }
         fence_barrier_init();
     }
+    for (int i = tid; i < P.n_btab; i += CTA_THREADS) sm.btab[i] = P.kv.block_table[i];
     {   // schedule -> shared memory
         const uint32_t* src = (const uint32_t*)P.phases; uint32_t* dst = (uint32_t*)sm.phases;
         for (int i = tid; i < P.n_phases * (int)(sizeof(Phase) / 4); i += CTA_THREADS) dst[i] = __ldg(src + i);
@@ -547,8 +554,8 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
                 consumer_sync();
             } else if (ph.kind == PH_ATTN) {
                 for (int it = c; it < P.n_head * P.n_splits; it += G) {
-                    if (P.head_dim == 128) attn_item<4>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane);
-                    else attn_item<2>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane);
+                    if (P.head_dim == 128) attn_item<4>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane, tr);
+                    else attn_item<2>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane, tr);
                 }
             } else {
                 consume_phase(P, ph, sm, cur, c, G, pos, tid, seq, best, logits_dst, tr);

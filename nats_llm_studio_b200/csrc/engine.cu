@@ -284,6 +284,7 @@ void Model::fill_params(DecodeParams& P) const {
     P.h_ll = d_ll16; P.att_ll = P.h_ll + (size_t)XREP * n_embd; P.act_ll = P.att_ll + (size_t)XREP * QD; P.kv_ll = P.act_ll + (size_t)XREP * n_ff;
     P.q_ll = d_ll32; P.part_ll = P.q_ll + QD; P.cand_ll = P.part_ll + (size_t)n_head * 16 * (head_dim + 2);
     P.hown_cap = hown_cap; (void)KVD;
+    P.n_btab = std::min(n_pages, BTAB_MAX);
     P.kv.pages = d_kv; P.kv.block_table = d_block_table; P.kv.n_layer = n_layer; P.kv.n_head_kv = n_head_kv; P.kv.head_dim = head_dim;
     P.pos = d_state + 0; P.token = d_state + 1; P.bar_ctr = (unsigned*)(d_state + 2); P.epoch = (unsigned*)(d_state + 3);
     P.out_tokens = d_out_tokens; P.n_steps = 1; P.want_argmax = 1; P.trace = d_trace;

@@ -116,6 +116,9 @@ struct KvLayout {               // paged KV cache, fp16
     const int* block_table;     // [max_pages] for the sequence
     int n_layer, n_head_kv, head_dim;
     __device__ __forceinline__ size_t page_elems() const { return (size_t)n_layer * 2 * n_head_kv * 16 * head_dim; }
+    __device__ __forceinline__ __half* at_page(int page, int layer, int kv, int kvh, int pos) const {
+        return pages + (size_t)page * page_elems() + ((((size_t)layer * 2 + kv) * n_head_kv + kvh) * 16 + (pos & 15)) * head_dim;
+    }
     __device__ __forceinline__ __half* at(int layer, int kv, int kvh, int pos) const {
         int page = block_table[pos >> 4];
         return pages + (size_t)page * page_elems() + ((((size_t)layer * 2 + kv) * n_head_kv + kvh) * 16 + (pos & 15)) * head_dim;
@@ -137,6 +140,7 @@ struct DecodeParams {
     int h_stride, att_stride, act_stride;                                   // words between copies
     uint2* q_ll; uint2* part_ll; uint2* cand_ll;                            // [n_head*head_dim], [n_head][16][head_dim+2], [2*grid]
     int hown_cap;                                                           // floats of owned hidden-state rows per CTA
+    int n_btab;                                                             // block-table entries copied to shared memory
     KvLayout kv;
     // run state (device memory)
     int* pos; int* token; int* out_tokens; unsigned* bar_ctr; unsigned* epoch;
@@ -153,18 +157,20 @@ struct Smem {
     uint32_t* q_end;                          // producer's in-flight stage sizes [NSLOT]
     float* hown;                              // fp32 hidden-state rows this CTA owns (residual stream never leaves the SM)
     float2* rope;                             // (cos, sin) of this token's RoPE angles [128]
+    int* btab;                                // the sequence's KV block table (page ids)
     Phase* phases;                            // the schedule, copied from global once per launch (descriptor reads are on
                                               // every phase's critical path; an L2 round trip each would cost microseconds)
 };
 __host__ __device__ inline size_t smem_x_bytes(int max_grp) { return (size_t)max_grp * (2048 + 256 + 32); }
-__host__ __device__ inline size_t smem_misc_bytes(int hown_cap, int n_phases) { return NSLOT * 16 + 64 * 4 + NSLOT * 4 + 128 * 8 + ((size_t)hown_cap * 4 + 15) / 16 * 16 + (size_t)n_phases * sizeof(Phase) + 64; }
+constexpr int BTAB_MAX = 1024;           // KV pages per sequence cached in shared memory (16384 positions)
+__host__ __device__ inline size_t smem_misc_bytes(int hown_cap, int n_phases) { return NSLOT * 16 + 64 * 4 + NSLOT * 4 + 128 * 8 + ((size_t)hown_cap * 4 + 15) / 16 * 16 + BTAB_MAX * 4 + (size_t)n_phases * sizeof(Phase) + 64; }
 __device__ inline Smem carve_smem(uint8_t* base, uint32_t ring_bytes, int max_grp, int hown_cap) {   // hown_cap: multiple of 4
     Smem s; s.ring = base; s.ring_bytes = ring_bytes; uint8_t* p = base + ring_bytes;
     s.xq = (int8_t*)p; p += (size_t)max_grp * 2048;
     s.xbs = (int16_t*)p; p += (size_t)max_grp * 256;
     s.xd = (float*)p; p += (size_t)max_grp * 32;
     s.full = (uint64_t*)p; p += NSLOT * 8; s.empty = (uint64_t*)p; p += NSLOT * 8;
-    s.red = (float*)p; p += 64 * 4; s.q_end = (uint32_t*)p; p += NSLOT * 4; s.rope = (float2*)p; p += 128 * 8; s.hown = (float*)p; p += ((size_t)hown_cap * 4 + 15) / 16 * 16; s.phases = (Phase*)p;
+    s.red = (float*)p; p += 64 * 4; s.q_end = (uint32_t*)p; p += NSLOT * 4; s.rope = (float2*)p; p += 128 * 8; s.hown = (float*)p; p += ((size_t)hown_cap * 4 + 15) / 16 * 16; s.btab = (int*)p; p += BTAB_MAX * 4; s.phases = (Phase*)p;
     return s;
 }
 

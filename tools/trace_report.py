@@ -21,6 +21,14 @@ for kind in ["embed", "qkv", "attn", "wo", "gate_up", "down", "lm_head"]:
     tot += wall.mean() * len(idx)
     print(f"{kind:8s} " + " ".join(f"{v:6.2f}" for v in d) + f" | {np.median(x[..., 6] - x[..., 0]):6.2f} | {wall.mean():7.2f} {np.median(skew):6.2f}  x{len(idx)}")
 print(f"sum of phase wall times: {tot:.1f} us/token")
+if "--attn" in sys.argv:
+    idx = [i for i, n in enumerate(names) if n == "attn"]
+    x = t[:, idx]
+    comb = (x[..., 4] - x[..., 3]) > 0
+    lab = ["q polled", "batches done", "smem combine+publish", "combiner polled", "final published", "phase end"]
+    for nm, sel in (("all items", x[..., 6] > x[..., 0]), ("combiner CTAs", comb)):
+        d = [np.median((x[..., k + 1] - x[..., k])[sel]) for k in range(6)]
+        print(f"  attn {nm:14s}: " + ", ".join(f"{l} {v:.2f}" for l, v in zip(lab, d)) + f" | total {np.median((x[..., 6] - x[..., 0])[sel]):.2f} us")
 if "--wait" in sys.argv:
     for kind in ["qkv", "wo", "gate_up", "down", "lm_head"]:
         idx = [i for i, n in enumerate(names) if n == kind]
