@@ -117,6 +117,12 @@ int b200_gemm_bf16(const float* A, const float* B, float* C, int M, int N, int K
 /* prompts with at least n tokens are ingested by the batched tensor-core path, shorter ones token by token through
  * the decode kernel (n <= 0: never batch).  Default 32. */
 int b200_model_set_prefill_min(b200_model* m, int n);
+/* Batched decode building blocks (what the b200_submit scheduler drives when max_seqs > 1): ingest a prompt prefix
+ * into sequence slot `slot`'s KV pages, and advance n sequences by one greedy token each (row i: token toks[i] of
+ * slot slots[i] at position pos[i]; logits, when not NULL, receives [n][n_vocab] fp32).  A row's result does not depend
+ * on which other rows are in the batch. */
+int b200_model_prefill_slot(b200_model* m, int slot, const int32_t* toks, int n, int pos0);
+int b200_model_batch_step(b200_model* m, const int32_t* toks, const int32_t* slots, const int32_t* pos, int n, int32_t* next, float* logits);
 /* decode-step timing: n_steps greedy tokens from the current position of a primed context */
 int b200_bench_decode(b200_model* m, int ctx_len, int n_steps, int warmup, float* ms_per_token, double* bytes_per_token);
 /* number of kernels this library has launched so far (bench.py reports the delta as gpu_launches) */

@@ -8,34 +8,98 @@
 namespace b200 {
 int load_file_into(const std::string& id, const std::string& path, std::shared_ptr<Model>& out, std::string& log);
 
-// ---- request queue behind b200_submit / b200_poll (one scheduler thread owns the engine)
-struct Request { std::shared_ptr<Model> m; std::vector<int32_t> toks; b200_sampling s; uint64_t id; std::atomic<bool> cancelled{false}; };
+// ---- request queue behind b200_submit / b200_poll (one scheduler thread owns the engine).
+// max_seqs == 1: requests run one after another through the persistent batch-1 decode kernel.
+// max_seqs  > 1: continuous batching — every iteration admits waiting requests into free sequence slots (their prompts
+// are ingested by the tensor-core prefill into the slot's KV pages) and then advances ALL active sequences by one token
+// with one batched step; finished sequences free their slot immediately.
+struct Request {
+    std::shared_ptr<Model> m; std::vector<int32_t> toks; b200_sampling s; uint64_t id; std::atomic<bool> cancelled{false};
+    std::chrono::steady_clock::time_point t_submit;
+};
+struct Seq { std::shared_ptr<Request> r; int slot, pos, cur_tok, n_gen = 0; float ttft_ms = 0; std::chrono::steady_clock::time_point t_first; };
 struct Scheduler {
     std::mutex mu; std::condition_variable cv_req, cv_ev;
     std::deque<std::shared_ptr<Request>> q; std::deque<b200_event> ev;
     std::map<uint64_t, std::shared_ptr<Request>> live;
     std::thread th; bool stop = false, started = false;
     void start() { if (started) return; started = true; th = std::thread([this] { loop(); }); }
-    void loop() {
-        for (;;) {
-            std::shared_ptr<Request> r;
-            { std::unique_lock<std::mutex> lk(mu); cv_req.wait(lk, [&] { return stop || !q.empty(); }); if (stop) return; r = q.front(); q.pop_front(); }
-            b200_event fin{}; fin.req_id = r->id; fin.kind = B200_EV_FINISH; fin.n_prompt = (int)r->toks.size();
-            std::vector<b200_event> out;
-            if (r->cancelled) fin.finish_reason = B200_FINISH_CANCELLED;
+    void push_events(std::vector<b200_event>& out, const std::vector<uint64_t>& done) {
+        { std::lock_guard<std::mutex> lk(mu); for (auto& e : out) ev.push_back(e); for (auto id : done) live.erase(id); }
+        out.clear(); cv_ev.notify_all();
+    }
+    static double ms_since(std::chrono::steady_clock::time_point t) { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t).count(); }
+
+    void run_single(const std::shared_ptr<Request>& r) {
+        b200_event fin{}; fin.req_id = r->id; fin.kind = B200_EV_FINISH; fin.n_prompt = (int)r->toks.size();
+        std::vector<b200_event> out;
+        if (r->cancelled) fin.finish_reason = B200_FINISH_CANCELLED;
+        else {
+            int n_gen = r->s.max_tokens > 0 ? r->s.max_tokens : 256;
+            std::vector<int32_t> toks((size_t)n_gen); int n_out = 0; float ttft = 0, dec = 0;
+            int rc = r->m->generate(r->toks.data(), (int)r->toks.size(), n_gen, &r->s, toks.data(), &n_out, &ttft, &dec);
+            if (rc != B200_OK) { fin.kind = B200_EV_ERROR; fin.finish_reason = rc; }
             else {
-                int n_gen = r->s.max_tokens > 0 ? r->s.max_tokens : 256;
-                std::vector<int32_t> toks((size_t)n_gen); int n_out = 0; float ttft = 0, dec = 0;
-                int rc = r->m->generate(r->toks.data(), (int)r->toks.size(), n_gen, &r->s, toks.data(), &n_out, &ttft, &dec);
-                if (rc != B200_OK) { fin.kind = B200_EV_ERROR; fin.finish_reason = rc; }
-                else {
-                    for (int i = 0; i < n_out; i++) { b200_event e{}; e.req_id = r->id; e.kind = B200_EV_TOKEN; e.token = toks[i]; e.n_generated = i + 1; out.push_back(e); }
-                    bool stopped = n_out > 0 && !r->s.ignore_eos && (toks[n_out - 1] == r->m->eos || toks[n_out - 1] == r->s.stop_token);
-                    fin.finish_reason = stopped ? B200_FINISH_STOP : B200_FINISH_LENGTH; fin.n_generated = n_out; fin.ttft_ms = ttft; fin.decode_ms = dec;
-                }
+                for (int i = 0; i < n_out; i++) { b200_event e{}; e.req_id = r->id; e.kind = B200_EV_TOKEN; e.token = toks[i]; e.n_generated = i + 1; out.push_back(e); }
+                bool stopped = n_out > 0 && !r->s.ignore_eos && (toks[n_out - 1] == r->m->eos || toks[n_out - 1] == r->s.stop_token);
+                fin.finish_reason = stopped ? B200_FINISH_STOP : B200_FINISH_LENGTH; fin.n_generated = n_out; fin.ttft_ms = ttft; fin.decode_ms = dec;
             }
-            { std::lock_guard<std::mutex> lk(mu); for (auto& e : out) ev.push_back(e); ev.push_back(fin); live.erase(r->id); }
-            cv_ev.notify_all();
+        }
+        out.push_back(fin); push_events(out, {r->id});
+    }
+
+    void loop() {
+        std::deque<std::shared_ptr<Request>> waiting; std::vector<Seq> active; std::vector<int> free_slots; std::shared_ptr<Model> cur;
+        for (;;) {
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv_req.wait(lk, [&] { return stop || !q.empty() || !active.empty() || !waiting.empty(); });
+                if (stop) return;
+                while (!q.empty()) { waiting.push_back(q.front()); q.pop_front(); }
+            }
+            const int max_seqs = engine().max_seqs, max_ctx = engine().max_ctx;
+            if (max_seqs <= 1) { while (!waiting.empty()) { auto r = waiting.front(); waiting.pop_front(); run_single(r); } continue; }
+            std::vector<b200_event> out; std::vector<uint64_t> done;
+            if (active.empty()) { free_slots.clear(); for (int i = max_seqs - 1; i >= 0; i--) free_slots.push_back(i); cur.reset(); }
+            // ---- admit
+            while (!waiting.empty() && !free_slots.empty() && (!cur || waiting.front()->m == cur)) {
+                auto r = waiting.front(); waiting.pop_front();
+                b200_event e{}; e.req_id = r->id; e.n_prompt = (int)r->toks.size();
+                if (r->cancelled) { e.kind = B200_EV_FINISH; e.finish_reason = B200_FINISH_CANCELLED; out.push_back(e); done.push_back(r->id); continue; }
+                const int n = (int)r->toks.size();
+                bool bad = n < 1 || n + 1 > max_ctx;
+                for (int t : r->toks) bad = bad || t < 0 || t >= r->m->n_vocab;
+                int rc = B200_OK; const int slot = free_slots.back();
+                if (!bad) { std::lock_guard<std::mutex> lk(r->m->run_mu); rc = r->m->prefill_slot(slot, r->toks.data(), n - 1, 0); }
+                if (bad || rc != B200_OK) { e.kind = B200_EV_ERROR; e.finish_reason = bad ? B200_ERR_INVALID : rc; out.push_back(e); done.push_back(r->id); continue; }
+                free_slots.pop_back(); cur = r->m;
+                Seq s; s.r = r; s.slot = slot; s.pos = n - 1; s.cur_tok = r->toks[n - 1]; active.push_back(s);
+            }
+            if (active.empty()) { push_events(out, done); continue; }
+            // ---- one batched step for every active sequence
+            const int B = (int)active.size();
+            std::vector<int32_t> toks(B), slots(B), pos(B), next(B);
+            for (int i = 0; i < B; i++) { toks[i] = active[i].cur_tok; slots[i] = active[i].slot; pos[i] = active[i].pos; }
+            int rc; { std::lock_guard<std::mutex> lk(cur->run_mu); rc = cur->batch_step(toks.data(), slots.data(), pos.data(), B, next.data()); }
+            std::vector<Seq> keep;
+            for (int i = 0; i < B; i++) {
+                Seq& s = active[i]; auto& r = s.r;
+                b200_event e{}; e.req_id = r->id; e.n_prompt = (int)r->toks.size();
+                if (rc != B200_OK) { e.kind = B200_EV_ERROR; e.finish_reason = rc; out.push_back(e); done.push_back(r->id); free_slots.push_back(s.slot); continue; }
+                s.n_gen++; s.pos++; s.cur_tok = next[i];
+                if (s.n_gen == 1) { s.ttft_ms = (float)ms_since(r->t_submit); s.t_first = std::chrono::steady_clock::now(); }
+                e.kind = B200_EV_TOKEN; e.token = next[i]; e.n_generated = s.n_gen; e.ttft_ms = s.ttft_ms; out.push_back(e);
+                const int max_tokens = r->s.max_tokens > 0 ? r->s.max_tokens : 256;
+                const bool stopped = !r->s.ignore_eos && (next[i] == r->m->eos || next[i] == r->s.stop_token);
+                if (stopped || s.n_gen >= max_tokens || s.pos + 1 >= max_ctx || r->cancelled) {
+                    b200_event f{}; f.req_id = r->id; f.kind = B200_EV_FINISH; f.n_prompt = e.n_prompt; f.n_generated = s.n_gen; f.ttft_ms = s.ttft_ms;
+                    f.decode_ms = (float)ms_since(s.t_first);
+                    f.finish_reason = r->cancelled ? B200_FINISH_CANCELLED : stopped ? B200_FINISH_STOP : B200_FINISH_LENGTH;
+                    out.push_back(f); done.push_back(r->id); free_slots.push_back(s.slot);
+                } else keep.push_back(s);
+            }
+            active.swap(keep);
+            push_events(out, done);
         }
     }
     ~Scheduler() { shutdown(); }
@@ -64,7 +128,8 @@ extern "C" {
 int b200_init(const b200_config* cfg) { return engine().init(cfg); }
 int b200_shutdown(void) {
     sched().shutdown();
-    Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); R.models.clear();
+    { Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); R.models.clear(); }
+    engine().shutdown();
     return B200_OK;
 }
 const char* b200_last_error(void) { return g_last_error.c_str(); }
@@ -135,7 +200,7 @@ int b200_detokenize(const b200_model* m, const int32_t* toks, int n, char* out, 
 int b200_submit(b200_model* m, const int32_t* toks, int n, const b200_sampling* s, uint64_t req_id) {
     if (!m || !toks || n < 1) return fail(B200_ERR_INVALID, "bad submit arguments");
     auto sp = find_shared(m); if (!sp || !sp->committed) return fail(B200_ERR_STATE, "model is not loaded");
-    auto r = std::make_shared<Request>(); r->m = sp; r->toks.assign(toks, toks + n); r->id = req_id;
+    auto r = std::make_shared<Request>(); r->m = sp; r->toks.assign(toks, toks + n); r->id = req_id; r->t_submit = std::chrono::steady_clock::now();
     if (s) r->s = *s; else { r->s = b200_sampling{}; r->s.max_tokens = 256; r->s.stop_token = -1; }
     Scheduler& S = sched();
     { std::lock_guard<std::mutex> lk(S.mu); S.start(); S.q.push_back(r); S.live[req_id] = r; }
@@ -166,6 +231,15 @@ int b200_gemv(int type, const void* raw, int64_t N, int K, const float* x, float
 int b200_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K, float* d_out) { return kernel_dequantize_noalloc(type, d_raw, n_rows, K, d_out); }
 int b200_gemm_bf16(const float* A, const float* B, float* C, int M, int N, int K) { if (!A || !B || !C) return fail(B200_ERR_INVALID, "null argument"); return kernel_gemm_bf16(A, B, C, M, N, K); }
 int b200_model_set_prefill_min(b200_model* m, int n) { if (!m) return fail(B200_ERR_INVALID, "null model"); ((Model*)m)->prefill_min = n; return B200_OK; }
+int b200_model_batch_step(b200_model* m, const int32_t* toks, const int32_t* slots, const int32_t* pos, int n, int32_t* next, float* logits) {
+    if (!m || !toks || !slots || !pos || !next) return fail(B200_ERR_INVALID, "null argument");
+    Model* M = (Model*)m; std::lock_guard<std::mutex> lk(M->run_mu); return M->batch_step(toks, slots, pos, n, next, logits);
+}
+int b200_model_prefill_slot(b200_model* m, int slot, const int32_t* toks, int n, int pos0) {
+    if (!m || (!toks && n)) return fail(B200_ERR_INVALID, "null argument");
+    Model* M = (Model*)m; if (slot < 0 || slot >= engine().max_seqs) return fail(B200_ERR_INVALID, "bad sequence slot");
+    std::lock_guard<std::mutex> lk(M->run_mu); return M->prefill_slot(slot, toks, n, pos0);
+}
 int b200_layout_selftest(void) { return layout_selftest(); }
 uint64_t b200_launch_count(void) { return engine().launches; }
 

@@ -50,6 +50,14 @@ int Engine::init(const b200_config* cfg) {
     return B200_OK;
 }
 
+void Engine::shutdown() {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ready) return;
+    cudaSetDevice(device); cudaDeviceSynchronize();
+    cudaStreamDestroy(stream); cudaStreamDestroy(copy_stream); stream = copy_stream = nullptr;
+    ready = false;
+}
+
 int Engine::ensure() {
     if (ready) { cudaSetDevice(device); return B200_OK; }
     return init(nullptr);
@@ -238,7 +246,8 @@ int Model::commit() {
         return rc;
     CK(cudaMemset(d_ll16, 0, n_ll16 * 4)); CK(cudaMemset(d_ll32, 0, n_ll32 * 8));     // tag 0 = never valid
     CK(cudaMemset(d_state, 0, 16 * sizeof(int)));
-    n_pages = (E.max_ctx + 15) / 16 * E.max_seqs;
+    pages_per_seq = (E.max_ctx + 15) / 16;
+    n_pages = pages_per_seq * E.max_seqs;
     size_t page_elems = (size_t)n_layer * 2 * n_head_kv * 16 * head_dim;
     if ((rc = own(&d_kv, page_elems * n_pages)) || (rc = own(&d_block_table, (size_t)n_pages))) return rc;
     std::vector<int> bt(n_pages); for (int i = 0; i < n_pages; i++) bt[i] = i;
@@ -284,8 +293,8 @@ void Model::fill_params(DecodeParams& P) const {
     P.h_ll = d_ll16; P.att_ll = P.h_ll + (size_t)XREP * n_embd; P.act_ll = P.att_ll + (size_t)XREP * QD; P.kv_ll = P.act_ll + (size_t)XREP * n_ff;
     P.q_ll = d_ll32; P.part_ll = P.q_ll + QD; P.cand_ll = P.part_ll + (size_t)n_head * 16 * (head_dim + 2);
     P.hown_cap = hown_cap; (void)KVD;
-    P.n_btab = std::min(n_pages, BTAB_MAX);
-    P.kv.pages = d_kv; P.kv.block_table = d_block_table; P.kv.n_layer = n_layer; P.kv.n_head_kv = n_head_kv; P.kv.head_dim = head_dim;
+    P.n_btab = std::min(pages_per_seq, BTAB_MAX);
+    P.kv.pages = d_kv; P.kv.block_table = d_block_table; P.kv.n_layer = n_layer; P.kv.n_head_kv = n_head_kv; P.kv.head_dim = head_dim; P.kv.pages_per_seq = pages_per_seq;
     P.pos = d_state + 0; P.token = d_state + 1; P.bar_ctr = (unsigned*)(d_state + 2); P.epoch = (unsigned*)(d_state + 3);
     P.out_tokens = d_out_tokens; P.n_steps = 1; P.want_argmax = 1; P.trace = d_trace;
 }
@@ -501,56 +510,121 @@ static inline int nblk(long long n, int per = 256, int cap = 148 * 16) { return 
 
 int Model::ensure_prefill_buffers() {
     if (pf_H) return B200_OK;
+    Engine& E = engine();
     const int D = n_embd, F = n_ff, QD = n_head * head_dim, KVD = n_head_kv * head_dim, Mc = PREFILL_CHUNK;
     size_t wmax = std::max({(size_t)(QD + 2 * KVD) * D, (size_t)D * QD, (size_t)2 * F * D, (size_t)D * F});
     int rc;
     if ((rc = own(&pf_H, (size_t)Mc * D)) || (rc = own(&pf_X, (size_t)Mc * std::max(D, QD))) || (rc = own(&pf_Y, (size_t)Mc * std::max(QD + 2 * KVD, 2 * F))) ||
-        (rc = own(&pf_Q, (size_t)Mc * QD)) || (rc = own(&pf_ACT, (size_t)Mc * F)) || (rc = own(&pf_W, wmax)) || (rc = own(&pf_toks, (size_t)Mc)))
+        (rc = own(&pf_Q, (size_t)Mc * QD)) || (rc = own(&pf_ACT, (size_t)Mc * F)) || (rc = own(&pf_W, wmax)) || (rc = own(&pf_toks, (size_t)3 * Mc)) ||
+        (rc = own(&bt_logits, (size_t)std::max(1, E.max_seqs) * ((n_vocab + 3) & ~3))) || (rc = own(&bt_next, (size_t)std::max(1, E.max_seqs))))
         return rc;
     return B200_OK;
 }
 
-// Ingest toks[0..n) at positions cur_pos.. through the tensor-core path: fills the KV pages; the hidden state of these
-// rows is discarded (the caller feeds the LAST prompt token through the decode kernel, which produces the logits).
-int Model::prefill(const int32_t* toks, int n) {
+// bf16 copies of every matrix (batched decode reads them every step; dequantising per step would cost more than the GEMMs)
+int Model::ensure_bf16_weights() {
+    if (bf16_ready) return B200_OK;
     Engine& E = engine();
-    if (n <= 0) return B200_OK;
-    if (cur_pos + n > E.max_ctx) return fail(B200_ERR_INVALID, "context overflow in prefill");
-    if (int rc = ensure_prefill_buffers()) return rc;
-    const int D = n_embd, F = n_ff, QD = n_head * head_dim, KVD = n_head_kv * head_dim, W3 = QD + 2 * KVD;
-    const float rs = res_scale != 0.f ? res_scale : 1.f, kq = attn_scale != 0.f ? attn_scale : 1.0f / std::sqrt((float)head_dim);
-    KvLayout kv; kv.pages = d_kv; kv.block_table = d_block_table; kv.n_layer = n_layer; kv.n_head_kv = n_head_kv; kv.head_dim = head_dim;
+    const int D = n_embd, F = n_ff, QD = n_head * head_dim, KVD = n_head_kv * head_dim;
     auto deq = [&](const Matrix& m, __nv_bfloat16* dst) {
         dequant_bf16_kernel<<<nblk(m.n_rows * (long long)m.K / 2), 256, 0, E.stream>>>(m.w, m.type, m.n_rows, m.K, dst); E.launches++;
     };
-    for (int c0 = 0; c0 < n; c0 += PREFILL_CHUNK) {
-        const int M = std::min(PREFILL_CHUNK, n - c0), pos0 = cur_pos + c0;
-        CK(cudaMemcpyAsync(pf_toks, toks + c0, (size_t)M * 4, cudaMemcpyHostToDevice, E.stream));
-        embed_rows_kernel<<<nblk((long long)M * D), 256, 0, E.stream>>>(tok_embd.w, tok_embd.type, D, pf_toks, M, emb_scale, pf_H); E.launches++;
-        for (int l = 0; l < n_layer; l++) {
-            Layer& L = layers[l];
-            rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, L.attn_norm, D, M, rms_eps, pf_X); E.launches++;
-            deq(L.wq, pf_W); deq(L.wk, pf_W + (size_t)QD * D); deq(L.wv, pf_W + (size_t)(QD + KVD) * D);
-            if (int rc = gemm_bf16(E, pf_X, pf_W, pf_Y, M, W3, D, W3, 0, 1.f)) return rc;
-            rope_kv_rows_kernel<<<nblk((long long)M * W3 / 2), 256, 0, E.stream>>>(pf_Y, M, pos0, l, n_head, n_head_kv, head_dim, n_rot, inv_freq, kv, pf_Q); E.launches++;
-            if (head_dim == 128) attn_prefill_kernel<4><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, pos0, l, n_head, n_head_kv, kq, kv, pf_X);
-            else attn_prefill_kernel<2><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, pos0, l, n_head, n_head_kv, kq, kv, pf_X);
-            E.launches++;
-            deq(L.wo, pf_W);
-            if (int rc = gemm_bf16(E, pf_X, pf_W, pf_H, M, D, QD, D, 1, rs)) return rc;
-            if (l == n_layer - 1) break;                              // the last layer's FFN only feeds logits nobody reads
-            rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, L.ffn_norm, D, M, rms_eps, pf_X); E.launches++;
-            deq(L.wgu, pf_W);
-            if (int rc = gemm_bf16(E, pf_X, pf_W, pf_Y, M, 2 * F, D, 2 * F, 0, 1.f)) return rc;
-            swiglu_rows_kernel<<<nblk((long long)M * F), 256, 0, E.stream>>>(pf_Y, M, F, pf_ACT); E.launches++;
-            deq(L.wd, pf_W);
-            if (int rc = gemm_bf16(E, pf_ACT, pf_W, pf_H, M, D, F, D, 1, rs)) return rc;
-        }
-        CK(cudaGetLastError());
+    int rc;
+    for (int l = 0; l < n_layer; l++) {
+        Layer& L = layers[l];
+        if ((rc = own(&L.b_qkv, (size_t)(QD + 2 * KVD) * D)) || (rc = own(&L.b_o, (size_t)D * QD)) || (rc = own(&L.b_gu, (size_t)2 * F * D)) || (rc = own(&L.b_d, (size_t)D * F))) return rc;
+        deq(L.wq, L.b_qkv); deq(L.wk, L.b_qkv + (size_t)QD * D); deq(L.wv, L.b_qkv + (size_t)(QD + KVD) * D);
+        deq(L.wo, L.b_o); deq(L.wgu, L.b_gu); deq(L.wd, L.b_d);
     }
+    if ((rc = own(&b_out, (size_t)n_vocab * D))) return rc;
+    deq(out_w, b_out);
+    CK(cudaStreamSynchronize(E.stream));
+    bf16_ready = true;
+    return B200_OK;
+}
+
+// One pass of the dense path over M activation rows (a prompt chunk of one sequence, or one row per sequence of a
+// decode batch).  want_logits: also run the last layer's FFN, the final norm and the lm_head into bt_logits[M][V].
+int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits) {
+    Engine& E = engine();
+    const int D = n_embd, F = n_ff, QD = n_head * head_dim, KVD = n_head_kv * head_dim, W3 = QD + 2 * KVD;
+    const float rs = res_scale != 0.f ? res_scale : 1.f, kq = attn_scale != 0.f ? attn_scale : 1.0f / std::sqrt((float)head_dim);
+    KvLayout kv; kv.pages = d_kv; kv.block_table = d_block_table; kv.n_layer = n_layer; kv.n_head_kv = n_head_kv; kv.head_dim = head_dim; kv.pages_per_seq = pages_per_seq;
+    RowMap rm{d_pos, d_slot, pos0, slot0};
+    auto deq = [&](const Matrix& m, __nv_bfloat16* dst) {
+        dequant_bf16_kernel<<<nblk(m.n_rows * (long long)m.K / 2), 256, 0, E.stream>>>(m.w, m.type, m.n_rows, m.K, dst); E.launches++;
+    };
+    embed_rows_kernel<<<nblk((long long)M * D), 256, 0, E.stream>>>(tok_embd.w, tok_embd.type, D, d_toks, M, emb_scale, pf_H); E.launches++;
+    for (int l = 0; l < n_layer; l++) {
+        Layer& L = layers[l];
+        const __nv_bfloat16 *wqkv = L.b_qkv, *wo = L.b_o, *wgu = L.b_gu, *wd = L.b_d;
+        rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, L.attn_norm, D, M, rms_eps, pf_X); E.launches++;
+        if (!bf16_ready) { deq(L.wq, pf_W); deq(L.wk, pf_W + (size_t)QD * D); deq(L.wv, pf_W + (size_t)(QD + KVD) * D); wqkv = pf_W; }
+        if (int rc = gemm_bf16(E, pf_X, wqkv, pf_Y, M, W3, D, W3, 0, 1.f)) return rc;
+        rope_kv_rows_kernel<<<nblk((long long)M * W3 / 2), 256, 0, E.stream>>>(pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, inv_freq, kv, pf_Q); E.launches++;
+        if (head_dim == 128) attn_prefill_kernel<4><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X);
+        else attn_prefill_kernel<2><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X);
+        E.launches++;
+        if (!bf16_ready) { deq(L.wo, pf_W); wo = pf_W; }
+        if (int rc = gemm_bf16(E, pf_X, wo, pf_H, M, D, QD, D, 1, rs)) return rc;
+        if (l == n_layer - 1 && !want_logits) break;                  // KV fill only: the last layer's FFN feeds nothing
+        rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, L.ffn_norm, D, M, rms_eps, pf_X); E.launches++;
+        if (!bf16_ready) { deq(L.wgu, pf_W); wgu = pf_W; }
+        if (int rc = gemm_bf16(E, pf_X, wgu, pf_Y, M, 2 * F, D, 2 * F, 0, 1.f)) return rc;
+        swiglu_rows_kernel<<<nblk((long long)M * F), 256, 0, E.stream>>>(pf_Y, M, F, pf_ACT); E.launches++;
+        if (!bf16_ready) { deq(L.wd, pf_W); wd = pf_W; }
+        if (int rc = gemm_bf16(E, pf_ACT, wd, pf_H, M, D, F, D, 1, rs)) return rc;
+    }
+    if (want_logits) {
+        if (!bf16_ready) return fail(B200_ERR_STATE, "logits through the dense path need the bf16 weight cache");
+        rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, out_norm, D, M, rms_eps, pf_X); E.launches++;
+        if (int rc = gemm_bf16(E, pf_X, b_out, bt_logits, M, n_vocab, D, (n_vocab + 3) & ~3, 0, logit_scale != 0.f ? 1.f / logit_scale : 1.f)) return rc;
+    }
+    CK(cudaGetLastError());
+    return B200_OK;
+}
+
+// Ingest toks[0..n) of sequence `slot` at positions pos0.. : fills its KV pages (hidden states are discarded).
+int Model::prefill_slot(int slot, const int32_t* toks, int n, int pos0) {
+    Engine& E = engine();
+    if (n <= 0) return B200_OK;
+    if (pos0 + n > E.max_ctx) return fail(B200_ERR_INVALID, "context overflow in prefill");
+    if (int rc = ensure_prefill_buffers()) return rc;
+    for (int c0 = 0; c0 < n; c0 += PREFILL_CHUNK) {
+        const int M = std::min(PREFILL_CHUNK, n - c0);
+        CK(cudaMemcpyAsync(pf_toks, toks + c0, (size_t)M * 4, cudaMemcpyHostToDevice, E.stream));
+        if (int rc = dense_rows(pf_toks, M, nullptr, nullptr, pos0 + c0, slot, false)) return rc;
+    }
+    CK(cudaStreamSynchronize(E.stream));                              // toks is caller memory
+    return B200_OK;
+}
+
+int Model::prefill(const int32_t* toks, int n) {                      // batch-1 path: sequence slot 0, continues at cur_pos
+    Engine& E = engine();
+    if (int rc = prefill_slot(0, toks, n, cur_pos)) return rc;
     cur_pos += n;
     int st = cur_pos; CK(cudaMemcpyAsync(d_state, &st, 4, cudaMemcpyHostToDevice, E.stream));
-    CK(cudaStreamSynchronize(E.stream));                              // toks/st are stack or caller memory
+    CK(cudaStreamSynchronize(E.stream));
+    return B200_OK;
+}
+
+// One decode step for B sequences: row i feeds token toks[i] of sequence slot slots[i] at position pos[i];
+// next[i] = greedy next token.  Rows are independent (a row's result does not depend on which other rows are present).
+int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* pos, int B, int32_t* next, float* logits) {
+    Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    if (B < 1 || B > E.max_seqs || B > PREFILL_CHUNK) return fail(B200_ERR_INVALID, "batch size out of range");
+    for (int i = 0; i < B; i++) if (toks[i] < 0 || toks[i] >= n_vocab || slots[i] < 0 || slots[i] >= E.max_seqs || pos[i] < 0 || pos[i] >= E.max_ctx) return fail(B200_ERR_INVALID, "bad batch row");
+    if (int rc = ensure_prefill_buffers()) return rc;
+    if (int rc = ensure_bf16_weights()) return rc;
+    const int Mc = PREFILL_CHUNK;
+    CK(cudaMemcpyAsync(pf_toks, toks, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
+    CK(cudaMemcpyAsync(pf_toks + Mc, pos, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
+    CK(cudaMemcpyAsync(pf_toks + 2 * Mc, slots, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
+    if (int rc = dense_rows(pf_toks, B, pf_toks + Mc, pf_toks + 2 * Mc, 0, 0, true)) return rc;
+    argmax_rows_kernel<<<B, 1024, 0, E.stream>>>(bt_logits, n_vocab, (n_vocab + 3) & ~3, bt_next); E.launches++;
+    CK(cudaMemcpyAsync(next, bt_next, (size_t)B * 4, cudaMemcpyDeviceToHost, E.stream));
+    if (logits) CK(cudaMemcpy2DAsync(logits, (size_t)n_vocab * 4, bt_logits, (size_t)((n_vocab + 3) & ~3) * 4, (size_t)n_vocab * 4, B, cudaMemcpyDeviceToHost, E.stream));
+    CK(cudaStreamSynchronize(E.stream));
     return B200_OK;
 }
 

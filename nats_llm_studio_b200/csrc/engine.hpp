@@ -27,7 +27,8 @@ extern thread_local std::string g_last_error;
 int fail(int code, const std::string& msg);
 
 struct Matrix { uint8_t* w = nullptr; int type = 0; int64_t N = 0, n_rows = 0; int K = 0; };
-struct Layer { float* attn_norm = nullptr; float* ffn_norm = nullptr; Matrix wq, wk, wv, wo, wgu, wd; };
+struct Layer { float* attn_norm = nullptr; float* ffn_norm = nullptr; Matrix wq, wk, wv, wo, wgu, wd;
+               __nv_bfloat16 *b_qkv = nullptr, *b_o = nullptr, *b_gu = nullptr, *b_d = nullptr; };   // bf16 copies (batched decode)
 
 struct Engine {
     std::mutex mu;
@@ -37,6 +38,7 @@ struct Engine {
     uint64_t launches = 0;                       // kernels launched by this library (bench.py reports it)
     int init(const b200_config* cfg);
     int ensure();
+    void shutdown();                             // after every model is closed: a later init() may use a different config
 };
 Engine& engine();
 
@@ -66,6 +68,7 @@ struct Model {
     // prefill scratch (allocated on first use)
     static constexpr int PREFILL_CHUNK = 512;
     float *pf_H = nullptr, *pf_Y = nullptr; __nv_bfloat16 *pf_X = nullptr, *pf_Q = nullptr, *pf_ACT = nullptr, *pf_W = nullptr; int* pf_toks = nullptr;
+    float* bt_logits = nullptr; int* bt_next = nullptr; __nv_bfloat16* b_out = nullptr; bool bf16_ready = false; int pages_per_seq = 0;
     int prefill_min = 32;                        // prompts shorter than this go through the decode kernel token by token
     std::mutex run_mu;
 
@@ -84,7 +87,11 @@ struct Model {
     double bytes_per_token(int ctx) const;
     int bench_decode(int ctx_len, int n_steps, int warmup, float* ms_per_token, double* bytes);
     int ensure_prefill_buffers();
+    int ensure_bf16_weights();
+    int dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits);
+    int prefill_slot(int slot, const int32_t* toks, int n, int pos0);
     int prefill(const int32_t* toks, int n);
+    int batch_step(const int32_t* toks, const int32_t* slots, const int32_t* pos, int B, int32_t* next, float* logits = nullptr);
     // tokenizer (tokenizer.cpp)
     void build_tokenizer();
     std::vector<int32_t> tokenize(const std::string& text, bool parse_special) const;

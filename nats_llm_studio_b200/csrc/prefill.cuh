@@ -151,6 +151,14 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (warp == 0) tcgen05_dealloc(tmem_acc, GEMM_BN);
 }
 
+// which sequence slot and position each activation row belongs to: a prompt chunk (pos0 + m, one slot) or a
+// decode batch (one row per sequence, explicit arrays)
+struct RowMap {
+    const int* pos; const int* slot; int pos0, slot0;
+    __device__ __forceinline__ int p(int m) const { return pos ? pos[m] : pos0 + m; }
+    __device__ __forceinline__ int s(int m) const { return slot ? slot[m] : slot0; }
+};
+
 // ------------------------------------------------------------------------------------ row-wise kernels
 // engine-layout quantised matrix -> bf16 [n_rows x K] (row r of the matrix at out + r*K)
 __global__ void dequant_bf16_kernel(const uint8_t* __restrict__ w, int type, long long n_rows, int K, __nv_bfloat16* __restrict__ out) {
@@ -188,30 +196,30 @@ __global__ void rmsnorm_rows_kernel(const float* __restrict__ H, const float* __
 }
 
 // QKV[m][QD + 2*KVD] fp32 -> RoPE(q) as bf16 Q[m][QD]; RoPE(k), v -> fp16 KV pages at position pos0 + m
-__global__ void rope_kv_rows_kernel(const float* __restrict__ QKV, int M, int pos0, int layer, int n_head, int n_head_kv, int HD, int n_rot,
+__global__ void rope_kv_rows_kernel(const float* __restrict__ QKV, int M, RowMap rm, int layer, int n_head, int n_head_kv, int HD, int n_rot,
                                     const float* __restrict__ inv_freq, KvLayout kv, __nv_bfloat16* __restrict__ Q) {
     const int QD = n_head * HD, KVD = n_head_kv * HD, W = QD + 2 * KVD;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)M * (W / 2); i += (long long)gridDim.x * blockDim.x) {
-        const int m = (int)(i / (W / 2)), c = (int)(i % (W / 2)) * 2, pos = pos0 + m;
+        const int m = (int)(i / (W / 2)), c = (int)(i % (W / 2)) * 2, pos = rm.p(m), slot = rm.s(m);
         float a = QKV[(size_t)m * W + c], b = QKV[(size_t)m * W + c + 1];
         if (c < QD + KVD) {                               // q or k: rotate the adjacent pair
             const int d = c % HD;
             if (d < n_rot) { float sn, cs; sincosf((float)pos * inv_freq[d >> 1], &sn, &cs); const float x = a, y = b; a = x * cs - y * sn; b = x * sn + y * cs; }
         }
         if (c < QD) *(__nv_bfloat162*)(Q + (size_t)m * QD + c) = __floats2bfloat162_rn(a, b);
-        else if (c < QD + KVD) { const int r = c - QD; *(__half2*)(kv.at(layer, 0, r / HD, pos) + r % HD) = __floats2half2_rn(a, b); }
-        else { const int r = c - QD - KVD; *(__half2*)(kv.at(layer, 1, r / HD, pos) + r % HD) = __floats2half2_rn(a, b); }
+        else if (c < QD + KVD) { const int r = c - QD; *(__half2*)(kv.at_slot(slot, layer, 0, r / HD, pos) + r % HD) = __floats2half2_rn(a, b); }
+        else { const int r = c - QD - KVD; *(__half2*)(kv.at_slot(slot, layer, 1, r / HD, pos) + r % HD) = __floats2half2_rn(a, b); }
     }
 }
 
 // causal attention for the M new rows (positions pos0..pos0+M-1) over the paged KV cache; one warp per (row, head)
 template <int VEC>
-__global__ void attn_prefill_kernel(const __nv_bfloat16* __restrict__ Q, int M, int pos0, int layer, int n_head, int n_head_kv, float kq_scale,
+__global__ void attn_prefill_kernel(const __nv_bfloat16* __restrict__ Q, int M, RowMap rm, int layer, int n_head, int n_head_kv, float kq_scale,
                                     KvLayout kv, __nv_bfloat16* __restrict__ O) {
     constexpr int HD = 32 * VEC, NB = 8;
     const int gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (gw >= M * n_head) return;
-    const int m = gw / n_head, head = gw % n_head, kvh = head / (n_head / n_head_kv), n_ctx = pos0 + m + 1;
+    const int m = gw / n_head, head = gw % n_head, kvh = head / (n_head / n_head_kv), n_ctx = rm.p(m) + 1, slot = rm.s(m);
     float qv[VEC], acc[VEC];
 #pragma unroll
     for (int i = 0; i < VEC; i++) { qv[i] = __bfloat162float(Q[(size_t)m * n_head * HD + head * HD + lane * VEC + i]) * kq_scale; acc[i] = 0.f; }
@@ -222,7 +230,7 @@ __global__ void attn_prefill_kernel(const __nv_bfloat16* __restrict__ Q, int M, 
         for (int b = 0; b < NB; b++) {
             const int p = pb + b;
             if (p < n_ctx) {
-                const __half* kp = kv.at(layer, 0, kvh, p) + lane * VEC; const __half* vp = kv.at(layer, 1, kvh, p) + lane * VEC;
+                const __half* kp = kv.at_slot(slot, layer, 0, kvh, p) + lane * VEC; const __half* vp = kv.at_slot(slot, layer, 1, kvh, p) + lane * VEC;
 #pragma unroll
                 for (int i = 0; i < VEC; i += 2) {
                     const float2 a = __half22float2(*(const __half2*)(kp + i)), c2 = __half22float2(*(const __half2*)(vp + i));
@@ -247,6 +255,21 @@ __global__ void attn_prefill_kernel(const __nv_bfloat16* __restrict__ Q, int M, 
     const float inv = 1.f / l;
 #pragma unroll
     for (int i = 0; i < VEC; i++) O[(size_t)m * n_head * HD + head * HD + lane * VEC + i] = __float2bfloat16(acc[i] * inv);
+}
+
+// next[m] = argmax_v logits[m][v] (lowest index wins ties); one block per row
+__global__ void argmax_rows_kernel(const float* __restrict__ logits, int V, int ld, int* __restrict__ next) {
+    __shared__ float sv[32]; __shared__ int si[32];
+    const float* row = logits + (size_t)blockIdx.x * ld;
+    float bv = -INFINITY; int bi = 0x7fffffff;
+    for (int i = threadIdx.x; i < V; i += blockDim.x) { const float v = row[i]; if (v > bv) { bv = v; bi = i; } }
+    for (int o = 16; o; o >>= 1) { const float v = __shfl_xor_sync(0xffffffffu, bv, o); const int ix = __shfl_xor_sync(0xffffffffu, bi, o); if (v > bv || (v == bv && ix < bi)) { bv = v; bi = ix; } }
+    if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = bv; si[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); w++) if (sv[w] > bv || (sv[w] == bv && si[w] < bi)) { bv = sv[w]; bi = si[w]; }
+        next[blockIdx.x] = bi;
+    }
 }
 
 // ACT[m][i] = bf16(silu(GU[m][2i]) * GU[m][2i+1])   (gate/up rows are interleaved in the fused matrix)

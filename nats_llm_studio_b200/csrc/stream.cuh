@@ -113,11 +113,14 @@ struct Phase {
 
 struct KvLayout {               // paged KV cache, fp16
     __half* pages;              // [n_pages][n_layer][2][n_head_kv][16][head_dim]
-    const int* block_table;     // [max_pages] for the sequence
-    int n_layer, n_head_kv, head_dim;
+    const int* block_table;     // [max_seqs][pages_per_seq]; the batch-1 decode kernel uses sequence slot 0
+    int n_layer, n_head_kv, head_dim, pages_per_seq;
     __device__ __forceinline__ size_t page_elems() const { return (size_t)n_layer * 2 * n_head_kv * 16 * head_dim; }
     __device__ __forceinline__ __half* at_page(int page, int layer, int kv, int kvh, int pos) const {
         return pages + (size_t)page * page_elems() + ((((size_t)layer * 2 + kv) * n_head_kv + kvh) * 16 + (pos & 15)) * head_dim;
+    }
+    __device__ __forceinline__ __half* at_slot(int slot, int layer, int kv, int kvh, int pos) const {
+        return at_page(block_table[slot * pages_per_seq + (pos >> 4)], layer, kv, kvh, pos);
     }
     __device__ __forceinline__ __half* at(int layer, int kv, int kvh, int pos) const {
         int page = block_table[pos >> 4];

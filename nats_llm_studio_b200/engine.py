@@ -13,6 +13,10 @@ SUBJECTS = ("lmstudio.list_models", "lmstudio.pull_model", "lmstudio.delete_mode
 _lib = None
 
 
+EV_TOKEN, EV_FINISH, EV_ERROR = 1, 2, 3                     # b200_event.kind
+FINISH_STOP, FINISH_LENGTH, FINISH_CANCELLED = 1, 2, 3      # b200_event.finish_reason
+
+
 class EngineError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__(f"b200 engine error {code}: {msg}")
@@ -51,7 +55,8 @@ SYMBOLS = {
     "b200_handle": (ci, [C.c_char_p, vp, sz, vp, sz, C.POINTER(sz)]), "b200_set_models_dir": (ci, [C.c_char_p]),
     "b200_dequantize": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_dequantize_noalloc": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_gemv": (ci, [ci, vp, C.c_int64, ci, vp, vp, ci, C.POINTER(C.c_float)]),
     "b200_bench_decode": (ci, [vp, ci, ci, ci, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
-    "b200_gemm_bf16": (ci, [vp, vp, vp, ci, ci, ci]), "b200_model_set_prefill_min": (ci, [vp, ci]),
+    "b200_gemm_bf16": (ci, [vp, vp, vp, ci, ci, ci]), "b200_model_prefill_slot": (ci, [vp, ci, vp, ci, ci]),
+    "b200_model_batch_step": (ci, [vp, vp, vp, vp, ci, vp, vp]), "b200_model_set_prefill_min": (ci, [vp, ci]),
     "b200_launch_count": (C.c_uint64, []), "b200_layout_selftest": (ci, []),
 }
 
@@ -123,6 +128,23 @@ class Model:
                                          C.byref(n_out), C.byref(ttft), C.byref(dec)))
         return out[:n_out.value], ttft.value, dec.value
 
+    def submit(self, prompt, req_id, max_tokens=256, temperature=0.0, top_k=0, top_p=1.0, seed=0, ignore_eos=True, stop_token=-1):
+        prompt = np.ascontiguousarray(prompt, dtype=np.int32)
+        s = Sampling(temperature, top_k, top_p, seed, max_tokens, stop_token, int(ignore_eos))
+        _check(lib().b200_submit(self.h, prompt.ctypes.data, len(prompt), C.byref(s), req_id))
+
+    def prefill_slot(self, slot, toks, pos0=0):
+        toks = np.ascontiguousarray(toks, dtype=np.int32)
+        _check(lib().b200_model_prefill_slot(self.h, slot, toks.ctypes.data, len(toks), pos0))
+
+    def batch_step(self, toks, slots, pos, want_logits=False):
+        toks = np.ascontiguousarray(toks, dtype=np.int32); slots = np.ascontiguousarray(slots, dtype=np.int32); pos = np.ascontiguousarray(pos, dtype=np.int32)
+        nxt = np.empty(len(toks), dtype=np.int32)
+        lg = np.empty((len(toks), self.n_vocab), dtype=np.float32) if want_logits else None
+        _check(lib().b200_model_batch_step(self.h, toks.ctypes.data, slots.ctypes.data, pos.ctypes.data, len(toks), nxt.ctypes.data,
+                                           lg.ctypes.data if want_logits else None))
+        return (nxt, lg) if want_logits else nxt
+
     def set_prefill_min(self, n):
         _check(lib().b200_model_set_prefill_min(self.h, n))
 
@@ -175,6 +197,15 @@ class Engine:
         if isinstance(payload, str):
             payload = payload.encode()
         return _string_call(lambda *a: lib().b200_handle(subject.encode(), payload, len(payload), *a))
+
+    @staticmethod
+    def poll(max_events=64, timeout_ms=1000):
+        """events the scheduler thread produced since the last poll (blocks up to timeout_ms for the first one)"""
+        buf = (Event * max_events)()
+        n = lib().b200_poll(buf, max_events, timeout_ms)
+        if n < 0:
+            _check(n)
+        return [Event.from_buffer_copy(buf[i]) for i in range(n)]
 
     def set_models_dir(self, d):
         _check(lib().b200_set_models_dir(d.encode()))

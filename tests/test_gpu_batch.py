@@ -1,0 +1,107 @@
+"""Batched decode (continuous batching, BASELINE.json configs[2]): one dense step advances every active sequence.
+Checks: a row's result is independent of its batch (bit-exact B=1 vs B=k), the batched logits agree with the oracle
+within the quantisation tolerance, and the b200_submit scheduler in continuous-batching mode returns, per request,
+exactly what the same request returns when it runs alone."""
+import os
+
+import numpy as np
+import pytest
+
+import orc
+import nats_llm_studio_b200 as b200
+from nats_llm_studio_b200.engine import lib
+
+pytestmark = pytest.mark.gpu
+MAX_SEQS = 8
+TOL_QUANT = 4e-2          # same bound as tests/test_gpu_model.py: bf16 weights/activations vs the fp32 oracle
+
+
+@pytest.fixture(scope="module")
+def engine():
+    lib().b200_shutdown()                                  # this module needs max_seqs > 1: re-initialise the engine
+    e = b200.Engine(max_ctx=1024, max_seqs=MAX_SEQS)
+    yield e
+    lib().b200_shutdown()                                  # later modules initialise with their own config
+
+
+def _prompts(n_vocab, lens, seed=11):
+    rng = np.random.default_rng(seed)
+    return [rng.integers(0, n_vocab, n).astype(np.int32) for n in lens]
+
+
+def _run(m, prompts, slots, n_gen, want_logits=False):
+    """prefill each prompt into its slot, then step all of them together; returns tokens [B][n_gen] (and first logits)."""
+    for p, s in zip(prompts, slots):
+        m.prefill_slot(s, p[:-1])
+    cur = np.array([p[-1] for p in prompts], np.int32); pos = np.array([len(p) - 1 for p in prompts], np.int32)
+    out = np.zeros((len(prompts), n_gen), np.int32); first = None
+    for t in range(n_gen):
+        if want_logits and t == 0:
+            cur, first = m.batch_step(cur, slots, pos, want_logits=True)
+        else:
+            cur = m.batch_step(cur, slots, pos)
+        out[:, t] = cur; pos += 1
+    return (out, first) if want_logits else out
+
+
+@pytest.mark.parametrize("name", ["tiny-llama", "tiny-granite"])
+def test_batch_rows_are_independent_and_match_oracle(engine, golden_dir, name):
+    path = os.path.join(golden_dir, f"{name}.gguf")
+    m = engine.load_file(f"bt/{name}", path)
+    prompts = _prompts(m.n_vocab, [5, 17, 40, 1, 33])
+    together, lg = _run(m, prompts, np.array([3, 0, 7, 1, 4], np.int32), 6, want_logits=True)
+    for i, p in enumerate(prompts):                        # each sequence alone, in a different slot: identical tokens
+        alone, lg1 = _run(m, [p], np.array([(i * 3 + 2) % MAX_SEQS], np.int32), 6, want_logits=True)
+        assert np.array_equal(alone[0], together[i])
+        assert np.array_equal(lg1[0], lg[i])               # bit-exact: batch composition does not change a row
+    o = orc.Model(path)
+    for i, p in enumerate(prompts):
+        want, ref = o.generate(p, 1, want_logits=True)
+        scale = np.abs(ref[0]).max()
+        assert np.abs(lg[i] - ref[0]).max() <= TOL_QUANT * scale
+        srt = np.sort(ref[0])
+        if srt[-1] - srt[-2] > 2 * TOL_QUANT * scale:
+            assert together[i, 0] == want[0]
+    m.close()
+
+
+def test_batch_step_argument_checks(engine, golden_dir):
+    m = engine.load_file("bt/args", os.path.join(golden_dir, "tiny-llama.gguf"))
+    one = np.zeros(1, np.int32)
+    with pytest.raises(b200.EngineError):
+        m.batch_step(np.array([m.n_vocab], np.int32), one, one)
+    with pytest.raises(b200.EngineError):
+        m.batch_step(one, np.array([MAX_SEQS], np.int32), one)
+    with pytest.raises(b200.EngineError):
+        m.batch_step(np.zeros(MAX_SEQS + 1, np.int32), np.zeros(MAX_SEQS + 1, np.int32), np.zeros(MAX_SEQS + 1, np.int32))
+    with pytest.raises(b200.EngineError):
+        m.prefill_slot(MAX_SEQS, one)
+    m.close()
+
+
+def test_scheduler_continuous_batching(engine, golden_dir):
+    """More requests than slots, different prompt lengths and max_tokens: every request gets exactly the tokens it gets
+    when it is the only sequence in the batch, in order, followed by one FINISH event."""
+    m = engine.load_file("bt/sched", os.path.join(golden_dir, "tiny-llama.gguf"))
+    lens = [3, 9, 30, 1, 12, 7, 21, 5, 16, 2, 11, 4, 19]   # 13 requests > 8 slots
+    prompts = _prompts(m.n_vocab, lens, seed=3)
+    n_gen = [4 + (i * 5) % 9 for i in range(len(prompts))]
+    want = [_run(m, [p], np.array([0], np.int32), g)[0] for p, g in zip(prompts, n_gen)]
+    for i, (p, g) in enumerate(zip(prompts, n_gen)):
+        m.submit(p, 100 + i, max_tokens=g)
+    got = {100 + i: [] for i in range(len(prompts))}; fin = {}
+    while len(fin) < len(prompts):
+        evs = engine.poll(64, 2000)
+        assert evs, "scheduler made no progress"
+        for e in evs:
+            assert e.kind != b200.EV_ERROR, e.finish_reason
+            if e.kind == b200.EV_TOKEN:
+                assert e.req_id not in fin
+                got[e.req_id].append(e.token); assert e.n_generated == len(got[e.req_id])
+            else:
+                fin[e.req_id] = e
+    for i in range(len(prompts)):
+        assert np.array_equal(np.array(got[100 + i], np.int32), want[i]), i
+        f = fin[100 + i]
+        assert f.finish_reason == b200.FINISH_LENGTH and f.n_generated == n_gen[i] and f.n_prompt == lens[i] and f.ttft_ms > 0
+    m.close()

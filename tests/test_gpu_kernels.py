@@ -1,5 +1,6 @@
 """GPU parity tests, kernel level: every call goes through the C ABI (libb200engine.so)."""
 import os
+import zlib
 
 import numpy as np
 import pytest
@@ -53,7 +54,7 @@ def test_dequant_bit_exact_golden(engine, golden_dir, t):
 def test_dequant_bit_exact_vs_oracle(engine, t, shape):
     """Ragged shapes: odd row counts, K not a multiple of the 2048 group (zero-padded groups)."""
     n_rows, K = shape
-    rng = np.random.default_rng(hash((t, shape)) % 2**32)
+    rng = np.random.default_rng(zlib.crc32(repr((t, shape)).encode()))
     raw = random_rows(rng, t, n_rows, K, sane=False)
     want = orc.dequantize(t, raw, n_rows * K).reshape(n_rows, K)
     got = engine.dequantize(t, raw, n_rows, K)
@@ -71,14 +72,15 @@ def test_dequant_empty_and_bad_args(engine):
 def test_gemv_matches_oracle(engine, t, shape):
     """Streaming GEMV vs the oracle: same int8 activation rule => tight bound; vs fp32 => stated bound."""
     N, K = shape
-    rng = np.random.default_rng(hash((t, shape, 1)) % 2**32)
+    rng = np.random.default_rng(zlib.crc32(repr((t, shape, 1)).encode()))
     raw = random_rows(rng, t, N, K)
     x = rng.standard_normal(K).astype(np.float32)
     y, _ = engine.gemv(t, raw, N, K, x)
     ref_q = orc.matvec(t, raw, N, K, x, act_quant=1)
     ref_f = orc.matvec(t, raw, N, K, x, act_quant=0)
     scale = np.abs(ref_f).max()
-    assert np.abs(y - ref_q).max() <= 2e-5 * scale          # same quantised activations: fp32 ordering noise only
+    mag = (np.abs(orc.dequantize(t, raw, N * K).reshape(N, K)) @ np.abs(x)).max()      # sum |w||x|: what fp32 ordering noise scales with
+    assert np.abs(y - ref_q).max() <= 2e-5 * scale + 1e-6 * mag         # same quantised activations: ordering noise only
     assert np.abs(y - ref_f).max() <= 3e-2 * scale          # int8 activations vs fp32 (ggml does the same)
 
 
