@@ -13,6 +13,7 @@
 
 #include "decode.cuh"
 #include "prefill.cuh"
+#include "qgemm.cuh"
 #include "sampler.cuh"
 
 namespace b200 {
@@ -55,6 +56,7 @@ void Engine::shutdown() {
     if (!ready) return;
     cudaSetDevice(device); cudaDeviceSynchronize();
     cudaStreamDestroy(stream); cudaStreamDestroy(copy_stream); stream = copy_stream = nullptr;
+    cudaFree(qg_ws); qg_ws = nullptr;
     ready = false;
 }
 
@@ -481,11 +483,11 @@ static EncodeTiledFn encode_tiled() {
     return fn;
 }
 // 2-D bf16 tensor [rows][cols] row-major, box = 64 cols x 128 rows, 128-byte swizzle, OOB rows read as zero
-static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols) {
+static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, int box_rows = GEMM_BM) {
     EncodeTiledFn f = encode_tiled();
     if (!f) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
     cuuint64_t dims[2] = {cols, rows}, strides[1] = {cols * 2};
-    cuuint32_t box[2] = {(cuuint32_t)GEMM_BK, (cuuint32_t)GEMM_BM}, estr[2] = {1, 1};
+    cuuint32_t box[2] = {(cuuint32_t)GEMM_BK, (cuuint32_t)box_rows}, estr[2] = {1, 1};
     CUresult r = f(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed: " + std::to_string((int)r));
@@ -503,6 +505,41 @@ static int gemm_bf16(Engine& E, const __nv_bfloat16* A, const __nv_bfloat16* B, 
     gemm_bf16_tcgen05<<<grid, GEMM_THREADS, GEMM_SMEM, E.stream>>>(ta, tb, C, M, N, K, ldc, mode, scale);
     CK(cudaGetLastError());
     E.launches++;
+    return B200_OK;
+}
+
+// ---- dequant-in-GEMM (qgemm.cuh): C[b][n] (+)= scale * X[b][:] . W[n][:] for up to three matrices that share X (K-permuted fp16, B <= 64 rows)
+struct QMat { const Matrix* m; float* C; };
+static int qgemm(Engine& E, const QMat* mats, int n_mat, const __nv_bfloat16* X, int B, int K, int ldc, int mode, float scale) {
+    if (B < 1 || B > QG_NB || n_mat < 1 || n_mat > 3) return fail(B200_ERR_INVALID, "qgemm: bad batch or matrix count");
+    QGemmParams P{}; int steps = 0, tiles = 0; uint32_t slot = 0;
+    for (int i = 0; i < n_mat; i++) {
+        const Matrix& m = *mats[i].m;
+        if (!m.tl || m.K != K || K % 256) return fail(B200_ERR_STATE, "qgemm: matrix has no tile layout or K mismatch");
+        QSeg& s = P.seg[i]; s.tl = m.tl; s.C = mats[i].C; s.type = m.type; s.n_tiles = (int)((m.N + QG_ROWS - 1) / QG_ROWS); s.n_rows = (int)m.n_rows;
+        s.ks = K / qg_kstep(m.type); s.step0 = steps; s.tile0 = tiles; steps += s.n_tiles * s.ks; tiles += s.n_tiles;
+        slot = std::max<uint32_t>(slot, (uint32_t)qg_blob_bytes(m.type));
+    }
+    P.n_seg = n_mat; P.total_steps = steps; P.n_tiles = tiles; P.B = B; P.ldc = ldc; P.mode = mode; P.scale = scale; P.slot_bytes = slot;
+    const size_t fixed = qg_smem_bytes(0, 0);
+    P.n_raw = (int)std::min<size_t>(QG_MAX_RAW, ((size_t)E.smem_optin - fixed) / slot);
+    if (P.n_raw < 2) return fail(B200_ERR_UNSUPPORTED, "qgemm: shared memory too small");
+    if (!E.qg_ws) { if (int rc = dalloc(&E.qg_ws, (size_t)E.n_sm * 2 * QG_NB * QG_ROWS)) return rc; }
+    P.ws = E.qg_ws;
+    static bool attr = false;
+    if (!attr) { CK(cudaFuncSetAttribute(qgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, E.smem_optin)); attr = true; }
+    CUtensorMap tx; if (int rc = make_tmap(&tx, X, (uint64_t)B, (uint64_t)K, QG_NB)) return rc;
+    const int G = E.n_sm;
+    qgemm_kernel<<<G, QG_THREADS, qg_smem_bytes(slot, P.n_raw), E.stream>>>(tx, P);
+    qgemm_fixup_kernel<<<tiles, QG_ROWS, 0, E.stream>>>(P, G);
+    CK(cudaGetLastError());
+    E.launches += 2;
+    return B200_OK;
+}
+static int tile_repack(Engine& E, Matrix& m, uint8_t* dst) {
+    const long long total = (long long)tile_bytes(m.type, m.N, m.K);
+    tile_repack_kernel<<<(int)std::min<long long>((total + 255) / 256, 148LL * 64), 256, 0, E.stream>>>(m.w, m.type, m.N, m.K, dst);
+    CK(cudaGetLastError()); E.launches++; m.tl = dst;
     return B200_OK;
 }
 
@@ -543,6 +580,23 @@ int Model::ensure_bf16_weights() {
     return B200_OK;
 }
 
+// tile-layout copies of every matrix (second resident copy of the quantised weights; 180 GB of HBM make room for it):
+// the batched decode step then reads quantised bytes once per step instead of 2-byte bf16 values
+int Model::ensure_tile_weights() {
+    if (tile_ready) return B200_OK;
+    Engine& E = engine();
+    auto mk = [&](Matrix& m) -> int { uint8_t* p = nullptr; if (int rc = own(&p, tile_bytes(m.type, m.N, m.K))) return rc; return tile_repack(E, m, p); };
+    int rc;
+    for (int l = 0; l < n_layer; l++) {
+        Layer& L = layers[l];
+        if ((rc = mk(L.wq)) || (rc = mk(L.wk)) || (rc = mk(L.wv)) || (rc = mk(L.wo)) || (rc = mk(L.wgu)) || (rc = mk(L.wd))) return rc;
+    }
+    if ((rc = mk(out_w))) return rc;
+    CK(cudaStreamSynchronize(E.stream));
+    tile_ready = true;
+    return B200_OK;
+}
+
 // One pass of the dense path over M activation rows (a prompt chunk of one sequence, or one row per sequence of a
 // decode batch).  want_logits: also run the last layer's FFN, the final norm and the lm_head into bt_logits[M][V].
 int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits) {
@@ -551,34 +605,56 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
     const float rs = res_scale != 0.f ? res_scale : 1.f, kq = attn_scale != 0.f ? attn_scale : 1.0f / std::sqrt((float)head_dim);
     KvLayout kv; kv.pages = d_kv; kv.block_table = d_block_table; kv.n_layer = n_layer; kv.n_head_kv = n_head_kv; kv.head_dim = head_dim; kv.pages_per_seq = pages_per_seq;
     RowMap rm{d_pos, d_slot, pos0, slot0};
+    // few rows (a decode batch): weights stay quantised and are expanded inside the GEMM; many rows (a prompt chunk):
+    // expand to bf16 once per chunk (or use the cache) and run the dense tensor-core GEMM
+    const bool q = tile_ready && M <= QG_NB && !getenv("B200_NO_QGEMM");
     auto deq = [&](const Matrix& m, __nv_bfloat16* dst) {
         dequant_bf16_kernel<<<nblk(m.n_rows * (long long)m.K / 2), 256, 0, E.stream>>>(m.w, m.type, m.n_rows, m.K, dst); E.launches++;
     };
+    int rc;
     embed_rows_kernel<<<nblk((long long)M * D), 256, 0, E.stream>>>(tok_embd.w, tok_embd.type, D, d_toks, M, emb_scale, pf_H); E.launches++;
     for (int l = 0; l < n_layer; l++) {
         Layer& L = layers[l];
         const __nv_bfloat16 *wqkv = L.b_qkv, *wo = L.b_o, *wgu = L.b_gu, *wd = L.b_d;
-        rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, L.attn_norm, D, M, rms_eps, pf_X); E.launches++;
-        if (!bf16_ready) { deq(L.wq, pf_W); deq(L.wk, pf_W + (size_t)QD * D); deq(L.wv, pf_W + (size_t)(QD + KVD) * D); wqkv = pf_W; }
-        if (int rc = gemm_bf16(E, pf_X, wqkv, pf_Y, M, W3, D, W3, 0, 1.f)) return rc;
+        rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, L.attn_norm, D, M, rms_eps, pf_X, q); E.launches++;
+        if (q) {
+            const QMat qkv[3] = {{&L.wq, pf_Y}, {&L.wk, pf_Y + QD}, {&L.wv, pf_Y + QD + KVD}};
+            if ((rc = qgemm(E, qkv, 3, pf_X, M, D, W3, 0, 1.f))) return rc;
+        } else {
+            if (!bf16_ready) { deq(L.wq, pf_W); deq(L.wk, pf_W + (size_t)QD * D); deq(L.wv, pf_W + (size_t)(QD + KVD) * D); wqkv = pf_W; }
+            if ((rc = gemm_bf16(E, pf_X, wqkv, pf_Y, M, W3, D, W3, 0, 1.f))) return rc;
+        }
         rope_kv_rows_kernel<<<nblk((long long)M * W3 / 2), 256, 0, E.stream>>>(pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, inv_freq, kv, pf_Q); E.launches++;
-        if (head_dim == 128) attn_prefill_kernel<4><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X);
-        else attn_prefill_kernel<2><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X);
+        if (head_dim == 128) attn_prefill_kernel<4><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q);
+        else attn_prefill_kernel<2><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q);
         E.launches++;
-        if (!bf16_ready) { deq(L.wo, pf_W); wo = pf_W; }
-        if (int rc = gemm_bf16(E, pf_X, wo, pf_H, M, D, QD, D, 1, rs)) return rc;
+        if (q) { const QMat o{&L.wo, pf_H}; if ((rc = qgemm(E, &o, 1, pf_X, M, QD, D, 1, rs))) return rc; }
+        else {
+            if (!bf16_ready) { deq(L.wo, pf_W); wo = pf_W; }
+            if ((rc = gemm_bf16(E, pf_X, wo, pf_H, M, D, QD, D, 1, rs))) return rc;
+        }
         if (l == n_layer - 1 && !want_logits) break;                  // KV fill only: the last layer's FFN feeds nothing
-        rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, L.ffn_norm, D, M, rms_eps, pf_X); E.launches++;
-        if (!bf16_ready) { deq(L.wgu, pf_W); wgu = pf_W; }
-        if (int rc = gemm_bf16(E, pf_X, wgu, pf_Y, M, 2 * F, D, 2 * F, 0, 1.f)) return rc;
-        swiglu_rows_kernel<<<nblk((long long)M * F), 256, 0, E.stream>>>(pf_Y, M, F, pf_ACT); E.launches++;
-        if (!bf16_ready) { deq(L.wd, pf_W); wd = pf_W; }
-        if (int rc = gemm_bf16(E, pf_ACT, wd, pf_H, M, D, F, D, 1, rs)) return rc;
+        rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, L.ffn_norm, D, M, rms_eps, pf_X, q); E.launches++;
+        if (q) { const QMat gu{&L.wgu, pf_Y}; if ((rc = qgemm(E, &gu, 1, pf_X, M, D, 2 * F, 0, 1.f))) return rc; }
+        else {
+            if (!bf16_ready) { deq(L.wgu, pf_W); wgu = pf_W; }
+            if ((rc = gemm_bf16(E, pf_X, wgu, pf_Y, M, 2 * F, D, 2 * F, 0, 1.f))) return rc;
+        }
+        swiglu_rows_kernel<<<nblk((long long)M * F), 256, 0, E.stream>>>(pf_Y, M, F, pf_ACT, q); E.launches++;
+        if (q) { const QMat dn{&L.wd, pf_H}; if ((rc = qgemm(E, &dn, 1, pf_ACT, M, F, D, 1, rs))) return rc; }
+        else {
+            if (!bf16_ready) { deq(L.wd, pf_W); wd = pf_W; }
+            if ((rc = gemm_bf16(E, pf_ACT, wd, pf_H, M, D, F, D, 1, rs))) return rc;
+        }
     }
     if (want_logits) {
-        if (!bf16_ready) return fail(B200_ERR_STATE, "logits through the dense path need the bf16 weight cache");
-        rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, out_norm, D, M, rms_eps, pf_X); E.launches++;
-        if (int rc = gemm_bf16(E, pf_X, b_out, bt_logits, M, n_vocab, D, (n_vocab + 3) & ~3, 0, logit_scale != 0.f ? 1.f / logit_scale : 1.f)) return rc;
+        const int ldv = (n_vocab + 3) & ~3; const float ls = logit_scale != 0.f ? 1.f / logit_scale : 1.f;
+        rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, out_norm, D, M, rms_eps, pf_X, q); E.launches++;
+        if (q) { const QMat o{&out_w, bt_logits}; if ((rc = qgemm(E, &o, 1, pf_X, M, D, ldv, 0, ls))) return rc; }
+        else {
+            if (!bf16_ready) return fail(B200_ERR_STATE, "logits through the dense path need the bf16 weight cache");
+            if ((rc = gemm_bf16(E, pf_X, b_out, bt_logits, M, n_vocab, D, ldv, 0, ls))) return rc;
+        }
     }
     CK(cudaGetLastError());
     return B200_OK;
@@ -615,7 +691,8 @@ int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* 
     if (B < 1 || B > E.max_seqs || B > PREFILL_CHUNK) return fail(B200_ERR_INVALID, "batch size out of range");
     for (int i = 0; i < B; i++) if (toks[i] < 0 || toks[i] >= n_vocab || slots[i] < 0 || slots[i] >= E.max_seqs || pos[i] < 0 || pos[i] >= E.max_ctx) return fail(B200_ERR_INVALID, "bad batch row");
     if (int rc = ensure_prefill_buffers()) return rc;
-    if (int rc = ensure_bf16_weights()) return rc;
+    if (getenv("B200_NO_QGEMM") || B > QG_NB) { if (int rc = ensure_bf16_weights()) return rc; }
+    else if (int rc = ensure_tile_weights()) return rc;
     const int Mc = PREFILL_CHUNK;
     CK(cudaMemcpyAsync(pf_toks, toks, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
     CK(cudaMemcpyAsync(pf_toks + Mc, pos, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
@@ -626,6 +703,36 @@ int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* 
     if (logits) CK(cudaMemcpy2DAsync(logits, (size_t)n_vocab * 4, bt_logits, (size_t)((n_vocab + 3) & ~3) * 4, (size_t)n_vocab * 4, B, cudaMemcpyDeviceToHost, E.stream));
     CK(cudaStreamSynchronize(E.stream));
     return B200_OK;
+}
+
+// test entry: y[b][n] = sum_k x[b][k] * W[n][k] through the dequant-in-GEMM kernel (raw ggml rows from the host)
+int kernel_qgemm(int type, const void* raw, int64_t N, int K, const float* x, int B, float* y) {
+    Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    if (!is_streamable(type)) return fail(B200_ERR_UNSUPPORTED, "unsupported ggml type");
+    if (N <= 0 || K <= 0 || K % 256 || B < 1 || B > QG_NB) return fail(B200_ERR_INVALID, "K must be a multiple of 256 and 1 <= B <= 64");
+    const int64_t Np = N + (N & 1); const size_t rb = raw_row_bytes(type, K);
+    Matrix m; m.type = type; m.N = Np; m.n_rows = N; m.K = K;
+    uint8_t *d_raw = nullptr, *d_tl = nullptr; __nv_bfloat16* d_x = nullptr; float* d_y = nullptr; int rc;
+    auto cleanup = [&]() { cudaFree(d_raw); cudaFree(m.w); cudaFree(d_tl); cudaFree(d_x); cudaFree(d_y); };
+    if ((rc = dalloc(&d_raw, (size_t)N * rb)) || (rc = dalloc(&m.w, repacked_bytes(type, Np, K))) || (rc = dalloc(&d_tl, tile_bytes(type, Np, K))) ||
+        (rc = dalloc(&d_x, (size_t)B * K)) || (rc = dalloc(&d_y, (size_t)B * N))) { cleanup(); return rc; }
+    std::vector<__nv_bfloat16> hx((size_t)B * K);
+    for (int b = 0; b < B; b++) for (int k = 0; k < K; k++) { const __half h = __float2half_rn(x[(size_t)b * K + kperm4(k)]); memcpy(&hx[(size_t)b * K + k], &h, 2); }
+    cudaMemcpyAsync(d_raw, raw, (size_t)N * rb, cudaMemcpyHostToDevice, E.stream);
+    cudaMemcpyAsync(d_x, hx.data(), hx.size() * 2, cudaMemcpyHostToDevice, E.stream);
+    cudaMemsetAsync(d_y, 0, (size_t)B * N * 4, E.stream);
+    if (!(rc = repack(E, d_raw, m.w, type, Np, N, K)) && !(rc = tile_repack(E, m, d_tl))) {
+        const QMat qm{&m, d_y};
+        rc = qgemm(E, &qm, 1, d_x, B, K, (int)N, 0, 1.f);
+    }
+    if (!rc) {
+        cudaError_t e = cudaMemcpyAsync(y, d_y, (size_t)B * N * 4, cudaMemcpyDeviceToHost, E.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(E.stream);
+        if (e != cudaSuccess) rc = fail(B200_ERR_CUDA, cudaGetErrorString(e));
+    }
+    cudaStreamSynchronize(E.stream);
+    cleanup();
+    return rc;
 }
 
 // test entry: C = A . B^T with host fp32 inputs rounded to bf16 on the way in

@@ -26,7 +26,8 @@ struct Phase;
 extern thread_local std::string g_last_error;
 int fail(int code, const std::string& msg);
 
-struct Matrix { uint8_t* w = nullptr; int type = 0; int64_t N = 0, n_rows = 0; int K = 0; };
+struct Matrix { uint8_t* w = nullptr; int type = 0; int64_t N = 0, n_rows = 0; int K = 0;
+                uint8_t* tl = nullptr; };   // tl: tile-layout copy for the dequant-in-GEMM path (qgemm.cuh), built on first batched use
 struct Layer { float* attn_norm = nullptr; float* ffn_norm = nullptr; Matrix wq, wk, wv, wo, wgu, wd;
                __nv_bfloat16 *b_qkv = nullptr, *b_o = nullptr, *b_gu = nullptr, *b_d = nullptr; };   // bf16 copies (batched decode)
 
@@ -36,6 +37,7 @@ struct Engine {
     int device = 0, max_ctx = 4096, max_seqs = 1, n_sm = 0, smem_per_sm = 0, smem_optin = 0;
     cudaStream_t stream = nullptr, copy_stream = nullptr;
     uint64_t launches = 0;                       // kernels launched by this library (bench.py reports it)
+    float* qg_ws = nullptr;                      // stream-K partial tiles of the dequant-in-GEMM kernel
     int init(const b200_config* cfg);
     int ensure();
     void shutdown();                             // after every model is closed: a later init() may use a different config
@@ -88,6 +90,8 @@ struct Model {
     int bench_decode(int ctx_len, int n_steps, int warmup, float* ms_per_token, double* bytes);
     int ensure_prefill_buffers();
     int ensure_bf16_weights();
+    int ensure_tile_weights();
+    bool tile_ready = false;
     int dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits);
     int prefill_slot(int slot, const int32_t* toks, int n, int pos0);
     int prefill(const int32_t* toks, int n);
@@ -103,6 +107,7 @@ int sample_token(Engine& E, Model& m, const b200_sampling& s, uint64_t step);
 int kernel_dequantize(int type, const void* raw, int64_t n_rows, int K, float* out);
 int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, float* y, int iters, float* ms);
 int kernel_gemm_bf16(const float* A, const float* B, float* C, int M, int N, int K);
+int kernel_qgemm(int type, const void* raw, int64_t N, int K, const float* x, int B, float* y);
 int kernel_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K, float* d_out);
 int layout_selftest();
 

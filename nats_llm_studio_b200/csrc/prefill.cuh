@@ -159,6 +159,19 @@ struct RowMap {
     __device__ __forceinline__ int s(int m) const { return slot ? slot[m] : slot0; }
 };
 
+// Activation rows that feed the dequant-in-GEMM kernel (qgemm.cuh) differ from the bf16 GEMM's in two ways, both
+// selected by `perm` in the row kernels below: inside every aligned group of four K positions the elements are stored
+// as (0, 2, 1, 3), and the 16-bit format is fp16 (clamped to the finite range) instead of bf16.
+__host__ __device__ inline int kperm4(int k) { return (k & ~3) | ((k & 1) << 1) | ((k >> 1) & 1); }
+__device__ __forceinline__ float clamp_h(float v) { return fminf(fmaxf(v, -65504.f), 65504.f); }
+__device__ __forceinline__ uint32_t pack16x2(float a, float b, bool f16) {
+    if (f16) { const __half2 h = __floats2half2_rn(clamp_h(a), clamp_h(b)); return *(const uint32_t*)&h; }
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b); return *(const uint32_t*)&h;
+}
+__device__ __forceinline__ unsigned short pack16(float a, bool f16) {
+    return f16 ? __half_as_ushort(__float2half_rn(clamp_h(a))) : __bfloat16_as_ushort(__float2bfloat16(a));
+}
+
 // ------------------------------------------------------------------------------------ row-wise kernels
 // engine-layout quantised matrix -> bf16 [n_rows x K] (row r of the matrix at out + r*K)
 __global__ void dequant_bf16_kernel(const uint8_t* __restrict__ w, int type, long long n_rows, int K, __nv_bfloat16* __restrict__ out) {
@@ -181,7 +194,7 @@ __global__ void embed_rows_kernel(const uint8_t* __restrict__ embd, int type, in
 }
 
 // X[m][:] = bf16(rmsnorm(H[m]) * w); one warp per row
-__global__ void rmsnorm_rows_kernel(const float* __restrict__ H, const float* __restrict__ w, int D, int M, float eps, __nv_bfloat16* __restrict__ X) {
+__global__ void rmsnorm_rows_kernel(const float* __restrict__ H, const float* __restrict__ w, int D, int M, float eps, __nv_bfloat16* __restrict__ X, bool perm) {
     const int m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (m >= M) return;
     const float* h = H + (size_t)m * D; float ss = 0.f;
@@ -190,8 +203,8 @@ __global__ void rmsnorm_rows_kernel(const float* __restrict__ H, const float* __
     const float rs = rsqrtf(ss / (float)D + eps);
     for (int i = lane * 4; i < D; i += 128) {
         const float4 v = *(const float4*)(h + i), g = *(const float4*)(w + i);
-        *(__nv_bfloat162*)(X + (size_t)m * D + i) = __floats2bfloat162_rn(v.x * rs * g.x, v.y * rs * g.y);
-        *(__nv_bfloat162*)(X + (size_t)m * D + i + 2) = __floats2bfloat162_rn(v.z * rs * g.z, v.w * rs * g.w);
+        const float a = v.x * rs * g.x, b = v.y * rs * g.y, c = v.z * rs * g.z, d = v.w * rs * g.w;
+        *(uint2*)(X + (size_t)m * D + i) = perm ? make_uint2(pack16x2(a, c, true), pack16x2(b, d, true)) : make_uint2(pack16x2(a, b, false), pack16x2(c, d, false));
     }
 }
 
@@ -215,7 +228,7 @@ __global__ void rope_kv_rows_kernel(const float* __restrict__ QKV, int M, RowMap
 // causal attention for the M new rows (positions pos0..pos0+M-1) over the paged KV cache; one warp per (row, head)
 template <int VEC>
 __global__ void attn_prefill_kernel(const __nv_bfloat16* __restrict__ Q, int M, RowMap rm, int layer, int n_head, int n_head_kv, float kq_scale,
-                                    KvLayout kv, __nv_bfloat16* __restrict__ O) {
+                                    KvLayout kv, __nv_bfloat16* __restrict__ O, bool perm) {
     constexpr int HD = 32 * VEC, NB = 8;
     const int gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (gw >= M * n_head) return;
@@ -254,7 +267,7 @@ __global__ void attn_prefill_kernel(const __nv_bfloat16* __restrict__ Q, int M, 
     }
     const float inv = 1.f / l;
 #pragma unroll
-    for (int i = 0; i < VEC; i++) O[(size_t)m * n_head * HD + head * HD + lane * VEC + i] = __float2bfloat16(acc[i] * inv);
+    for (int i = 0; i < VEC; i++) { const int e = lane * VEC + i; ((unsigned short*)O)[(size_t)m * n_head * HD + head * HD + (perm ? kperm4(e) : e)] = pack16(acc[i] * inv, perm); }
 }
 
 // next[m] = argmax_v logits[m][v] (lowest index wins ties); one block per row
@@ -273,10 +286,10 @@ __global__ void argmax_rows_kernel(const float* __restrict__ logits, int V, int 
 }
 
 // ACT[m][i] = bf16(silu(GU[m][2i]) * GU[m][2i+1])   (gate/up rows are interleaved in the fused matrix)
-__global__ void swiglu_rows_kernel(const float* __restrict__ GU, int M, int F, __nv_bfloat16* __restrict__ ACT) {
+__global__ void swiglu_rows_kernel(const float* __restrict__ GU, int M, int F, __nv_bfloat16* __restrict__ ACT, bool perm) {
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)M * F; i += (long long)gridDim.x * blockDim.x) {
         const float2 gu = *(const float2*)(GU + 2 * i);
-        ACT[i] = __float2bfloat16(gu.x / (1.f + __expf(-gu.x)) * gu.y);
+        ((unsigned short*)ACT)[perm ? (i - i % 4 + kperm4((int)(i % 4))) : i] = pack16(gu.x / (1.f + __expf(-gu.x)) * gu.y, perm);
     }
 }
 
