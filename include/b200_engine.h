@@ -115,8 +115,9 @@ int b200_gemv(int type, const void* raw_blocks, int64_t N, int K, const float* x
  * bf16, fp32 accumulate); K % 64 == 0.  Host buffers. */
 int b200_gemm_bf16(const float* A, const float* B, float* C, int M, int N, int K);
 /* y[B x N] = x[B x K] . W[N x K]^T through the dequant-in-GEMM kernel batched decode uses (weights stay quantised in HBM,
- * expanded to fp16 in shared memory, tcgen05 fp16 x fp16 -> fp32); raw ggml rows, B <= 64, K % 256 == 0.  Host buffers. */
-int b200_qgemm(int type, const void* raw_blocks, int64_t N, int K, const float* x, int B, float* y);
+ * expanded to fp16 in shared memory, tcgen05 fp16 x fp16 -> fp32); raw ggml rows, B <= 64, K % 256 == 0.  Host buffers;
+ * iters > 1 repeats the launch, ms = mean per iteration. */
+int b200_qgemm(int type, const void* raw_blocks, int64_t N, int K, const float* x, int B, float* y, int iters, float* ms);
 /* prompts with at least n tokens are ingested by the batched tensor-core path, shorter ones token by token through
  * the decode kernel (n <= 0: never batch).  Default 32. */
 int b200_model_set_prefill_min(b200_model* m, int n);

@@ -229,7 +229,7 @@ int b200_set_models_dir(const char* dir) { Registry& R = registry(); std::lock_g
 int b200_dequantize(int type, const void* raw, int64_t n_rows, int K, float* out) { if ((!raw || !out) && n_rows) return fail(B200_ERR_INVALID, "null argument"); return kernel_dequantize(type, raw, n_rows, K, out); }
 int b200_gemv(int type, const void* raw, int64_t N, int K, const float* x, float* y, int iters, float* ms) { if (!raw || !x || !y) return fail(B200_ERR_INVALID, "null argument"); return kernel_gemv(type, raw, N, K, x, y, iters, ms); }
 int b200_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K, float* d_out) { return kernel_dequantize_noalloc(type, d_raw, n_rows, K, d_out); }
-int b200_qgemm(int type, const void* raw, int64_t N, int K, const float* x, int B, float* y) { if (!raw || !x || !y) return fail(B200_ERR_INVALID, "null argument"); return kernel_qgemm(type, raw, N, K, x, B, y); }
+int b200_qgemm(int type, const void* raw, int64_t N, int K, const float* x, int B, float* y, int iters, float* ms) { if (!raw || !x || !y) return fail(B200_ERR_INVALID, "null argument"); return kernel_qgemm(type, raw, N, K, x, B, y, iters, ms); }
 int b200_gemm_bf16(const float* A, const float* B, float* C, int M, int N, int K) { if (!A || !B || !C) return fail(B200_ERR_INVALID, "null argument"); return kernel_gemm_bf16(A, B, C, M, N, K); }
 int b200_model_set_prefill_min(b200_model* m, int n) { if (!m) return fail(B200_ERR_INVALID, "null model"); ((Model*)m)->prefill_min = n; return B200_OK; }
 int b200_model_batch_step(b200_model* m, const int32_t* toks, const int32_t* slots, const int32_t* pos, int n, int32_t* next, float* logits) {

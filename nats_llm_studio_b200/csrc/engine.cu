@@ -526,12 +526,13 @@ static int qgemm(Engine& E, const QMat* mats, int n_mat, const __nv_bfloat16* X,
     if (P.n_raw < 2) return fail(B200_ERR_UNSUPPORTED, "qgemm: shared memory too small");
     if (!E.qg_ws) { if (int rc = dalloc(&E.qg_ws, (size_t)E.n_sm * 2 * QG_NB * QG_ROWS)) return rc; }
     P.ws = E.qg_ws;
+    if (const char* dbg = getenv("B200_QG_DEBUG")) P.debug = atoi(dbg);
     static bool attr = false;
     if (!attr) { CK(cudaFuncSetAttribute(qgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, E.smem_optin)); attr = true; }
     CUtensorMap tx; if (int rc = make_tmap(&tx, X, (uint64_t)B, (uint64_t)K, QG_NB)) return rc;
     const int G = E.n_sm;
     qgemm_kernel<<<G, QG_THREADS, qg_smem_bytes(slot, P.n_raw), E.stream>>>(tx, P);
-    qgemm_fixup_kernel<<<tiles, QG_ROWS, 0, E.stream>>>(P, G);
+    qgemm_fixup_kernel<<<dim3(tiles, (B + 7) / 8), QG_ROWS, 0, E.stream>>>(P, G);
     CK(cudaGetLastError());
     E.launches += 2;
     return B200_OK;
@@ -582,6 +583,8 @@ int Model::ensure_bf16_weights() {
 
 // tile-layout copies of every matrix (second resident copy of the quantised weights; 180 GB of HBM make room for it):
 // the batched decode step then reads quantised bytes once per step instead of 2-byte bf16 values
+bool Model::use_qgemm(int M) const { return engine().max_seqs > 1 && M <= QG_NB && !getenv("B200_NO_QGEMM"); }
+
 int Model::ensure_tile_weights() {
     if (tile_ready) return B200_OK;
     Engine& E = engine();
@@ -607,7 +610,9 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
     RowMap rm{d_pos, d_slot, pos0, slot0};
     // few rows (a decode batch): weights stay quantised and are expanded inside the GEMM; many rows (a prompt chunk):
     // expand to bf16 once per chunk (or use the cache) and run the dense tensor-core GEMM
-    const bool q = tile_ready && M <= QG_NB && !getenv("B200_NO_QGEMM");
+    // (the choice depends on the engine configuration and M only, never on what ran before: results are reproducible)
+    const bool q = use_qgemm(M);
+    if (q) { if (int rc0 = ensure_tile_weights()) return rc0; }
     auto deq = [&](const Matrix& m, __nv_bfloat16* dst) {
         dequant_bf16_kernel<<<nblk(m.n_rows * (long long)m.K / 2), 256, 0, E.stream>>>(m.w, m.type, m.n_rows, m.K, dst); E.launches++;
     };
@@ -616,7 +621,7 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
     for (int l = 0; l < n_layer; l++) {
         Layer& L = layers[l];
         const __nv_bfloat16 *wqkv = L.b_qkv, *wo = L.b_o, *wgu = L.b_gu, *wd = L.b_d;
-        rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, L.attn_norm, D, M, rms_eps, pf_X, q); E.launches++;
+        rmsnorm_rows_kernel<<<M, 256, 0, E.stream>>>(pf_H, L.attn_norm, D, M, rms_eps, pf_X, q); E.launches++;
         if (q) {
             const QMat qkv[3] = {{&L.wq, pf_Y}, {&L.wk, pf_Y + QD}, {&L.wv, pf_Y + QD + KVD}};
             if ((rc = qgemm(E, qkv, 3, pf_X, M, D, W3, 0, 1.f))) return rc;
@@ -625,8 +630,17 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
             if ((rc = gemm_bf16(E, pf_X, wqkv, pf_Y, M, W3, D, W3, 0, 1.f))) return rc;
         }
         rope_kv_rows_kernel<<<nblk((long long)M * W3 / 2), 256, 0, E.stream>>>(pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, inv_freq, kv, pf_Q); E.launches++;
-        if (head_dim == 128) attn_prefill_kernel<4><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q);
-        else attn_prefill_kernel<2><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q);
+        {
+            const int G = n_head / n_head_kv; const dim3 ag(M * n_head_kv);
+#define B200_ATTN(HD_, G_) attn_rows_kernel<HD_, G_><<<ag, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q)
+            if (head_dim == 128 && G == 4) B200_ATTN(128, 4); else if (head_dim == 128 && G == 8) B200_ATTN(128, 8);
+            else if (head_dim == 128 && G == 2) B200_ATTN(128, 2); else if (head_dim == 128 && G == 1) B200_ATTN(128, 1);
+            else if (head_dim == 64 && G == 4) B200_ATTN(64, 4); else if (head_dim == 64 && G == 8) B200_ATTN(64, 8);
+            else if (head_dim == 64 && G == 2) B200_ATTN(64, 2); else if (head_dim == 64 && G == 1) B200_ATTN(64, 1);
+            else if (head_dim == 128) attn_prefill_kernel<4><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q);
+            else attn_prefill_kernel<2><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q);
+#undef B200_ATTN
+        }
         E.launches++;
         if (q) { const QMat o{&L.wo, pf_H}; if ((rc = qgemm(E, &o, 1, pf_X, M, QD, D, 1, rs))) return rc; }
         else {
@@ -634,7 +648,7 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
             if ((rc = gemm_bf16(E, pf_X, wo, pf_H, M, D, QD, D, 1, rs))) return rc;
         }
         if (l == n_layer - 1 && !want_logits) break;                  // KV fill only: the last layer's FFN feeds nothing
-        rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, L.ffn_norm, D, M, rms_eps, pf_X, q); E.launches++;
+        rmsnorm_rows_kernel<<<M, 256, 0, E.stream>>>(pf_H, L.ffn_norm, D, M, rms_eps, pf_X, q); E.launches++;
         if (q) { const QMat gu{&L.wgu, pf_Y}; if ((rc = qgemm(E, &gu, 1, pf_X, M, D, 2 * F, 0, 1.f))) return rc; }
         else {
             if (!bf16_ready) { deq(L.wgu, pf_W); wgu = pf_W; }
@@ -649,7 +663,7 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
     }
     if (want_logits) {
         const int ldv = (n_vocab + 3) & ~3; const float ls = logit_scale != 0.f ? 1.f / logit_scale : 1.f;
-        rmsnorm_rows_kernel<<<(M + 7) / 8, 256, 0, E.stream>>>(pf_H, out_norm, D, M, rms_eps, pf_X, q); E.launches++;
+        rmsnorm_rows_kernel<<<M, 256, 0, E.stream>>>(pf_H, out_norm, D, M, rms_eps, pf_X, q); E.launches++;
         if (q) { const QMat o{&out_w, bt_logits}; if ((rc = qgemm(E, &o, 1, pf_X, M, D, ldv, 0, ls))) return rc; }
         else {
             if (!bf16_ready) return fail(B200_ERR_STATE, "logits through the dense path need the bf16 weight cache");
@@ -691,8 +705,7 @@ int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* 
     if (B < 1 || B > E.max_seqs || B > PREFILL_CHUNK) return fail(B200_ERR_INVALID, "batch size out of range");
     for (int i = 0; i < B; i++) if (toks[i] < 0 || toks[i] >= n_vocab || slots[i] < 0 || slots[i] >= E.max_seqs || pos[i] < 0 || pos[i] >= E.max_ctx) return fail(B200_ERR_INVALID, "bad batch row");
     if (int rc = ensure_prefill_buffers()) return rc;
-    if (getenv("B200_NO_QGEMM") || B > QG_NB) { if (int rc = ensure_bf16_weights()) return rc; }
-    else if (int rc = ensure_tile_weights()) return rc;
+    if (!use_qgemm(B)) { if (int rc = ensure_bf16_weights()) return rc; }
     const int Mc = PREFILL_CHUNK;
     CK(cudaMemcpyAsync(pf_toks, toks, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
     CK(cudaMemcpyAsync(pf_toks + Mc, pos, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
@@ -706,7 +719,7 @@ int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* 
 }
 
 // test entry: y[b][n] = sum_k x[b][k] * W[n][k] through the dequant-in-GEMM kernel (raw ggml rows from the host)
-int kernel_qgemm(int type, const void* raw, int64_t N, int K, const float* x, int B, float* y) {
+int kernel_qgemm(int type, const void* raw, int64_t N, int K, const float* x, int B, float* y, int iters, float* ms_out) {
     Engine& E = engine(); if (int rc = E.ensure()) return rc;
     if (!is_streamable(type)) return fail(B200_ERR_UNSUPPORTED, "unsupported ggml type");
     if (N <= 0 || K <= 0 || K % 256 || B < 1 || B > QG_NB) return fail(B200_ERR_INVALID, "K must be a multiple of 256 and 1 <= B <= 64");
@@ -724,6 +737,14 @@ int kernel_qgemm(int type, const void* raw, int64_t N, int K, const float* x, in
     if (!(rc = repack(E, d_raw, m.w, type, Np, N, K)) && !(rc = tile_repack(E, m, d_tl))) {
         const QMat qm{&m, d_y};
         rc = qgemm(E, &qm, 1, d_x, B, K, (int)N, 0, 1.f);
+        if (!rc && iters > 1) {                                    // timing: repeat the launch pair, mean per iteration
+            cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+            cudaEventRecord(e0, E.stream);
+            for (int i = 0; i < iters && !rc; i++) rc = qgemm(E, &qm, 1, d_x, B, K, (int)N, 0, 1.f);
+            cudaEventRecord(e1, E.stream); cudaEventSynchronize(e1);
+            float ms = 0.f; cudaEventElapsedTime(&ms, e0, e1); if (ms_out) *ms_out = ms / iters;
+            cudaEventDestroy(e0); cudaEventDestroy(e1);
+        }
     }
     if (!rc) {
         cudaError_t e = cudaMemcpyAsync(y, d_y, (size_t)B * N * 4, cudaMemcpyDeviceToHost, E.stream);

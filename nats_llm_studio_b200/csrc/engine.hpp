@@ -91,6 +91,7 @@ struct Model {
     int ensure_prefill_buffers();
     int ensure_bf16_weights();
     int ensure_tile_weights();
+    bool use_qgemm(int M) const;
     bool tile_ready = false;
     int dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits);
     int prefill_slot(int slot, const int32_t* toks, int n, int pos0);
@@ -107,7 +108,7 @@ int sample_token(Engine& E, Model& m, const b200_sampling& s, uint64_t step);
 int kernel_dequantize(int type, const void* raw, int64_t n_rows, int K, float* out);
 int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, float* y, int iters, float* ms);
 int kernel_gemm_bf16(const float* A, const float* B, float* C, int M, int N, int K);
-int kernel_qgemm(int type, const void* raw, int64_t N, int K, const float* x, int B, float* y);
+int kernel_qgemm(int type, const void* raw, int64_t N, int K, const float* x, int B, float* y, int iters, float* ms);
 int kernel_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K, float* d_out);
 int layout_selftest();
 

@@ -193,15 +193,20 @@ __global__ void embed_rows_kernel(const uint8_t* __restrict__ embd, int type, in
     }
 }
 
-// X[m][:] = bf16(rmsnorm(H[m]) * w); one warp per row
-__global__ void rmsnorm_rows_kernel(const float* __restrict__ H, const float* __restrict__ w, int D, int M, float eps, __nv_bfloat16* __restrict__ X, bool perm) {
-    const int m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (m >= M) return;
+// X[m][:] = 16-bit(rmsnorm(H[m]) * w); one block per row
+__global__ void __launch_bounds__(256) rmsnorm_rows_kernel(const float* __restrict__ H, const float* __restrict__ w, int D, int M, float eps, __nv_bfloat16* __restrict__ X, bool perm) {
+    __shared__ float red[8];
+    const int m = blockIdx.x, tid = threadIdx.x;
     const float* h = H + (size_t)m * D; float ss = 0.f;
-    for (int i = lane * 4; i < D; i += 128) { const float4 v = *(const float4*)(h + i); ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w; }
+    for (int i = tid * 4; i < D; i += 1024) { const float4 v = *(const float4*)(h + i); ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w; }
     ss = warp_sum(ss);
+    if ((tid & 31) == 0) red[tid >> 5] = ss;
+    __syncthreads();
+    ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; i++) ss += red[i];                       // same order in every thread
     const float rs = rsqrtf(ss / (float)D + eps);
-    for (int i = lane * 4; i < D; i += 128) {
+    for (int i = tid * 4; i < D; i += 1024) {
         const float4 v = *(const float4*)(h + i), g = *(const float4*)(w + i);
         const float a = v.x * rs * g.x, b = v.y * rs * g.y, c = v.z * rs * g.z, d = v.w * rs * g.w;
         *(uint2*)(X + (size_t)m * D + i) = perm ? make_uint2(pack16x2(a, c, true), pack16x2(b, d, true)) : make_uint2(pack16x2(a, b, false), pack16x2(c, d, false));
@@ -268,6 +273,94 @@ __global__ void attn_prefill_kernel(const __nv_bfloat16* __restrict__ Q, int M, 
     const float inv = 1.f / l;
 #pragma unroll
     for (int i = 0; i < VEC; i++) { const int e = lane * VEC + i; ((unsigned short*)O)[(size_t)m * n_head * HD + head * HD + (perm ? kperm4(e) : e)] = pack16(acc[i] * inv, perm); }
+}
+
+// Attention for M rows over the paged fp16 KV cache, one block per (row, kv head): the G query heads that share the kv
+// head are served from one pass over K and V.  Each of the 4 warps takes every fourth 32-position chunk; scores are
+// computed one position per lane (no shuffles in the dot products), probabilities are broadcast by shuffle for the
+// P.V accumulation (one output-dim slice per lane), and the four warps' online-softmax states are merged in shared memory.
+template <int HD, int G>
+__global__ void __launch_bounds__(128) attn_rows_kernel(const __nv_bfloat16* __restrict__ Q, int M, RowMap rm, int layer, int n_head, int n_head_kv,
+                                                        float kq_scale, KvLayout kv, __nv_bfloat16* __restrict__ O, bool perm) {
+    constexpr int DPL = HD / 32;
+    __shared__ __align__(16) float sq[G][HD];
+    __shared__ float sm_m[4][G], sm_l[4][G];
+    __shared__ float sm_acc[4][G][HD];
+    const int m = blockIdx.x / n_head_kv, kvh = blockIdx.x % n_head_kv, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int n_ctx = rm.p(m) + 1, slot = rm.s(m);
+    for (int i = tid; i < G * HD; i += 128) { const int g = i / HD, d = i % HD; sq[g][d] = __bfloat162float(Q[(size_t)m * n_head * HD + (kvh * G + g) * HD + d]) * kq_scale; }
+    __syncthreads();
+    float mx[G], l[G], acc[G][DPL];
+#pragma unroll
+    for (int g = 0; g < G; g++) { mx[g] = -INFINITY; l[g] = 0.f;
+#pragma unroll
+        for (int i = 0; i < DPL; i++) acc[g][i] = 0.f; }
+    for (int p0 = warp * 32; p0 < n_ctx; p0 += 128) {
+        const int p = p0 + lane; const bool ok = p < n_ctx;
+        float s[G];
+#pragma unroll
+        for (int g = 0; g < G; g++) s[g] = 0.f;
+        if (ok) {
+            const __half* kp = kv.at_slot(slot, layer, 0, kvh, p);
+#pragma unroll 4
+            for (int j = 0; j < HD / 8; j++) {
+                const uint4 kk = *(const uint4*)(kp + 8 * j);
+                const float2 k0 = __half22float2(*(const __half2*)&kk.x), k1 = __half22float2(*(const __half2*)&kk.y),
+                             k2 = __half22float2(*(const __half2*)&kk.z), k3 = __half22float2(*(const __half2*)&kk.w);
+#pragma unroll
+                for (int g = 0; g < G; g++) {
+                    const float4 qa = *(const float4*)&sq[g][8 * j], qb = *(const float4*)&sq[g][8 * j + 4];
+                    s[g] += qa.x * k0.x + qa.y * k0.y + qa.z * k1.x + qa.w * k1.y + qb.x * k2.x + qb.y * k2.y + qb.z * k3.x + qb.w * k3.y;
+                }
+            }
+        }
+        float pe[G];
+#pragma unroll
+        for (int g = 0; g < G; g++) {
+            const float sg = ok ? s[g] : -INFINITY;
+            float cm = sg;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
+            const float mn = fmaxf(mx[g], cm), corr = __expf(mx[g] - mn);
+            pe[g] = ok ? __expf(sg - mn) : 0.f;
+            l[g] = l[g] * corr + warp_sum(pe[g]);
+#pragma unroll
+            for (int i = 0; i < DPL; i++) acc[g][i] *= corr;
+            mx[g] = mn;
+        }
+        const int np = min(32, n_ctx - p0);
+        const __half* vbase = nullptr;
+        for (int pp = 0; pp < np; pp++) {
+            if ((pp & 15) == 0) vbase = kv.at_slot(slot, layer, 1, kvh, p0 + pp) + lane * DPL;      // 16 positions of a page are contiguous
+            const __half* vp = vbase + (size_t)(pp & 15) * HD;
+            float v[DPL];
+            if (DPL == 4) { const uint2 vv = *(const uint2*)vp; const float2 a = __half22float2(*(const __half2*)&vv.x), b = __half22float2(*(const __half2*)&vv.y); v[0] = a.x; v[1] = a.y; v[2 % DPL] = b.x; v[3 % DPL] = b.y; }
+            else { const float2 a = __half22float2(*(const __half2*)vp); v[0] = a.x; v[1] = a.y; }
+#pragma unroll
+            for (int g = 0; g < G; g++) {
+                const float pr = __shfl_sync(0xffffffffu, pe[g], pp);
+#pragma unroll
+                for (int i = 0; i < DPL; i++) acc[g][i] += pr * v[i];
+            }
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < G; g++) {
+        if (lane == 0) { sm_m[warp][g] = mx[g]; sm_l[warp][g] = l[g]; }
+#pragma unroll
+        for (int i = 0; i < DPL; i++) sm_acc[warp][g][lane * DPL + i] = acc[g][i];
+    }
+    __syncthreads();
+    for (int idx = tid; idx < G * HD; idx += 128) {
+        const int g = idx / HD, d = idx % HD;
+        float mm = sm_m[0][g];
+#pragma unroll
+        for (int w = 1; w < 4; w++) mm = fmaxf(mm, sm_m[w][g]);
+        float num = 0.f, den = 0.f;
+#pragma unroll
+        for (int w = 0; w < 4; w++) { const float e = __expf(sm_m[w][g] - mm); num += sm_acc[w][g][d] * e; den += sm_l[w][g] * e; }
+        ((unsigned short*)O)[(size_t)m * n_head * HD + (kvh * G + g) * HD + (perm ? kperm4(d) : d)] = pack16(num / den, perm);
+    }
 }
 
 // next[m] = argmax_v logits[m][v] (lowest index wins ties); one block per row

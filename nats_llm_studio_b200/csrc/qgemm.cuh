@@ -81,6 +81,7 @@ __global__ void tile_repack_kernel(const uint8_t* __restrict__ w, int type, int6
 struct QSeg { const uint8_t* tl; float* C; int type, n_tiles, n_rows, ks, step0, tile0; };
 struct QGemmParams {
     QSeg seg[3]; int n_seg, total_steps, n_tiles, B, ldc, mode, n_raw; float scale; float* ws; uint32_t slot_bytes;
+    int debug;      // profiling only (B200_QG_DEBUG): 1 = skip the expansion math, 2 = skip the MMAs
 };
 
 __device__ __forceinline__ int qg_seg_of_step(const QGemmParams& P, int s) { int i = 0; while (i + 1 < P.n_seg && s >= P.seg[i + 1].step0) i++; return i; }
@@ -246,6 +247,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 const QSeg& sg = P.seg[qg_seg_of_step(P, s)];
                 const int rs = it % P.n_raw; const uint32_t ph = (it / P.n_raw) & 1, bytes = qg_blob_bytes(sg.type);
                 mbar_wait(&S.raw_empty[rs], ph ^ 1);
+                if (P.debug & 8) { mbar_arrive(&S.raw_full[rs]); continue; }
                 mbar_expect_tx(&S.raw_full[rs], bytes);
                 bulk_g2s(S.raw + (size_t)rs * P.slot_bytes, sg.tl + (size_t)(s - sg.step0) * bytes, bytes, &S.raw_full[rs]);
             }
@@ -259,6 +261,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 for (int kb = 0; kb < nkb; kb++, kbc++) {
                     const int xs = kbc % QG_X_SLOTS; const uint32_t ph = (kbc / QG_X_SLOTS) & 1;
                     mbar_wait(&S.x_empty[xs], ph ^ 1);
+                    if (P.debug & 4) { mbar_arrive(&S.x_full[xs]); continue; }
                     mbar_expect_tx(&S.x_full[xs], QG_X_BYTES);
                     tma_load_2d(S.x + xs * QG_X_BYTES, &tmap_x, (kstep * nkb + kb) * 64, 0, &S.x_full[xs]);
                 }
@@ -281,7 +284,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                     tcgen05_fence_after();
                     const uint64_t da = umma_desc_sw128(S.a + as * QG_A_BYTES), db = umma_desc_sw128(S.x + xs * QG_X_BYTES);
 #pragma unroll
-                    for (int k = 0; k < 4; k++) tcgen05_mma_f16(tmem + buf * QG_NB, da + 2 * k, db + 2 * k, idesc, (i | k) ? 1u : 0u);
+                    for (int k = 0; k < 4; k++) if (!(P.debug & 2)) tcgen05_mma_f16(tmem + buf * QG_NB, da + 2 * k, db + 2 * k, idesc, (i | k) ? 1u : 0u);
                     tcgen05_commit(&S.a_empty[as]);
                     tcgen05_commit(&S.x_empty[xs]);
                 }
@@ -300,7 +303,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
             if (type == T_Q8_0) {
                 const int kb = p >> 1, as = (kbc + kb) % QG_A_SLOTS;
                 mbar_wait(&S.a_empty[as], (((kbc + kb) / QG_A_SLOTS) & 1) ^ 1);
-                dq_q80(raw, row, kb, p & 1, smem_u32(S.a + as * QG_A_BYTES));
+                if (!(P.debug & 1)) dq_q80(raw, row, kb, p & 1, smem_u32(S.a + as * QG_A_BYTES));
                 fence_proxy_async_smem(); __syncwarp();
                 if (lane == 0) mbar_arrive_n(&S.a_full[as], 2);
                 kbc += 2;
@@ -308,14 +311,15 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 const int n = p >> 1, a0 = (kbc + 2 * n) % QG_A_SLOTS, a1 = (kbc + 2 * n + 1) % QG_A_SLOTS;
                 mbar_wait(&S.a_empty[a0], (((kbc + 2 * n) / QG_A_SLOTS) & 1) ^ 1);
                 mbar_wait(&S.a_empty[a1], (((kbc + 2 * n + 1) / QG_A_SLOTS) & 1) ^ 1);
-                dq_q6k(raw, row, n, p & 1, smem_u32(S.a + a0 * QG_A_BYTES), smem_u32(S.a + a1 * QG_A_BYTES));
+                if (!(P.debug & 1)) dq_q6k(raw, row, n, p & 1, smem_u32(S.a + a0 * QG_A_BYTES), smem_u32(S.a + a1 * QG_A_BYTES));
                 fence_proxy_async_smem(); __syncwarp();
                 if (lane == 0) { mbar_arrive_n(&S.a_full[a0], 2); mbar_arrive_n(&S.a_full[a1], 2); }
                 kbc += 4;
             } else {
                 const int as = (kbc + p) % QG_A_SLOTS;
                 mbar_wait(&S.a_empty[as], (((kbc + p) / QG_A_SLOTS) & 1) ^ 1);
-                if (type == T_Q4_K) dq_k45<false>(raw, row, p, smem_u32(S.a + as * QG_A_BYTES));
+                if (P.debug & 1) {}
+                else if (type == T_Q4_K) dq_k45<false>(raw, row, p, smem_u32(S.a + as * QG_A_BYTES));
                 else dq_k45<true>(raw, row, p, smem_u32(S.a + as * QG_A_BYTES));
                 fence_proxy_async_smem(); __syncwarp();
                 if (lane == 0) mbar_arrive_n(&S.a_full[as], 4);
@@ -374,15 +378,23 @@ __global__ void qgemm_fixup_kernel(const __grid_constant__ QGemmParams P, int G)
     const int n = tl * QG_ROWS + threadIdx.x;
     if (n >= sg.n_rows) return;
     const float scale = P.scale * (1.f / QG_PRESCALE);
-    for (int b = 0; b < P.B; b++) {
-        float acc = 0.f;
-        for (int c = c_lo; c <= c_hi; c++) {
-            const int cb = (int)((long long)c * T / G), ce = (int)((long long)(c + 1) * T / G);
-            if (cb == ce) continue;                                         // CTA without work (fewer steps than CTAs)
-            const int slot = cb >= s0 ? 0 : 1;                              // slot 0: the tile is the first one CTA c touches
-            acc += P.ws[((size_t)(c * 2 + slot) * QG_NB + b) * QG_ROWS + threadIdx.x];
-        }
-        float v = acc * scale; float* dst = sg.C + (size_t)b * P.ldc + n;
+    constexpr int BB = 8;                              // batch rows per block (blockIdx.y): independent loads in flight
+    const int b0 = blockIdx.y * BB;
+    float acc[BB];
+#pragma unroll
+    for (int i = 0; i < BB; i++) acc[i] = 0.f;
+    for (int c = c_lo; c <= c_hi; c++) {
+        const int cb = (int)((long long)c * T / G), ce = (int)((long long)(c + 1) * T / G);
+        if (cb == ce) continue;                                             // CTA without work (fewer steps than CTAs)
+        const int slot = cb >= s0 ? 0 : 1;                                  // slot 0: the tile is the first one CTA c touches
+        const float* src = P.ws + ((size_t)(c * 2 + slot) * QG_NB + b0) * QG_ROWS + threadIdx.x;
+#pragma unroll
+        for (int i = 0; i < BB; i++) if (b0 + i < P.B) acc[i] += src[(size_t)i * QG_ROWS];
+    }
+#pragma unroll
+    for (int i = 0; i < BB; i++) {
+        if (b0 + i >= P.B) break;
+        float v = acc[i] * scale; float* dst = sg.C + (size_t)(b0 + i) * P.ldc + n;
         if (P.mode == 1) v += *dst;
         *dst = v;
     }

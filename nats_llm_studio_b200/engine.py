@@ -55,7 +55,7 @@ SYMBOLS = {
     "b200_handle": (ci, [C.c_char_p, vp, sz, vp, sz, C.POINTER(sz)]), "b200_set_models_dir": (ci, [C.c_char_p]),
     "b200_dequantize": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_dequantize_noalloc": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_gemv": (ci, [ci, vp, C.c_int64, ci, vp, vp, ci, C.POINTER(C.c_float)]),
     "b200_bench_decode": (ci, [vp, ci, ci, ci, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
-    "b200_gemm_bf16": (ci, [vp, vp, vp, ci, ci, ci]), "b200_qgemm": (ci, [ci, vp, C.c_int64, ci, vp, ci, vp]), "b200_model_prefill_slot": (ci, [vp, ci, vp, ci, ci]),
+    "b200_gemm_bf16": (ci, [vp, vp, vp, ci, ci, ci]), "b200_qgemm": (ci, [ci, vp, C.c_int64, ci, vp, ci, vp, ci, C.POINTER(C.c_float)]), "b200_model_prefill_slot": (ci, [vp, ci, vp, ci, ci]),
     "b200_model_batch_step": (ci, [vp, vp, vp, vp, ci, vp, vp]), "b200_model_set_prefill_min": (ci, [vp, ci]),
     "b200_launch_count": (C.c_uint64, []), "b200_layout_selftest": (ci, []),
 }
@@ -199,12 +199,13 @@ class Engine:
         return _string_call(lambda *a: lib().b200_handle(subject.encode(), payload, len(payload), *a))
 
     @staticmethod
-    def qgemm(type_name, raw, N, K, x):
+    def qgemm(type_name, raw, N, K, x, iters=1):
         """x[B x K] . W[N x K]^T with W given as raw ggml rows: the dequant-in-GEMM kernel of batched decode"""
         raw = np.ascontiguousarray(raw, dtype=np.uint8); x = np.ascontiguousarray(x, dtype=np.float32)
         y = np.empty((x.shape[0], N), dtype=np.float32)
-        _check(lib().b200_qgemm(GGML_TYPES[type_name], raw.ctypes.data, N, K, x.ctypes.data, x.shape[0], y.ctypes.data))
-        return y
+        ms = C.c_float(0)
+        _check(lib().b200_qgemm(GGML_TYPES[type_name], raw.ctypes.data, N, K, x.ctypes.data, x.shape[0], y.ctypes.data, iters, C.byref(ms)))
+        return (y, ms.value) if iters > 1 else y
 
     @staticmethod
     def poll(max_events=64, timeout_ms=1000):
