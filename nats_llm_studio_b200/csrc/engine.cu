@@ -510,17 +510,24 @@ static int gemm_bf16(Engine& E, const __nv_bfloat16* A, const __nv_bfloat16* B, 
 
 // ---- dequant-in-GEMM (qgemm.cuh): C[b][n] (+)= scale * X[b][:] . W[n][:] for up to three matrices that share X (K-permuted fp16, B <= 64 rows)
 struct QMat { const Matrix* m; float* C; };
-static int qgemm(Engine& E, const QMat* mats, int n_mat, const __nv_bfloat16* X, int B, int K, int ldc, int mode, float scale) {
+// `sp` (out): what the consuming row kernel needs to complete the tiles stream-K split across CTAs (sp->ws == nullptr
+// when there are none); whole = tile-aligned CTA ranges (nothing to complete).  The partials live in one engine-wide
+// buffer: the consumer must run before the next qgemm launch (stream order in dense_rows guarantees it).
+static int qgemm(Engine& E, const QMat* mats, int n_mat, const __nv_bfloat16* X, int B, int K, int ldc, int mode, float scale, bool whole, QgSplit* sp) {
     if (B < 1 || B > QG_NB || n_mat < 1 || n_mat > 3) return fail(B200_ERR_INVALID, "qgemm: bad batch or matrix count");
+    if (K % QG_KSTEP) return fail(B200_ERR_INVALID, "qgemm: K must be a multiple of 256");
     QGemmParams P{}; int steps = 0, tiles = 0; uint32_t slot = 0;
+    P.ks = K / QG_KSTEP;
+    *sp = QgSplit{};
     for (int i = 0; i < n_mat; i++) {
         const Matrix& m = *mats[i].m;
-        if (!m.tl || m.K != K || K % 256) return fail(B200_ERR_STATE, "qgemm: matrix has no tile layout or K mismatch");
+        if (!m.tl || m.K != K) return fail(B200_ERR_STATE, "qgemm: matrix has no tile layout or K mismatch");
         QSeg& s = P.seg[i]; s.tl = m.tl; s.C = mats[i].C; s.type = m.type; s.n_tiles = (int)((m.N + QG_ROWS - 1) / QG_ROWS); s.n_rows = (int)m.n_rows;
-        s.ks = K / qg_kstep(m.type); s.step0 = steps; s.tile0 = tiles; steps += s.n_tiles * s.ks; tiles += s.n_tiles;
+        s.step0 = steps; s.tile0 = tiles; steps += s.n_tiles * P.ks; tiles += s.n_tiles;
+        sp->step0[i] = s.step0; sp->col0[i] = (int)(mats[i].C - mats[0].C);
         slot = std::max<uint32_t>(slot, (uint32_t)qg_blob_bytes(m.type));
     }
-    P.n_seg = n_mat; P.total_steps = steps; P.n_tiles = tiles; P.B = B; P.ldc = ldc; P.mode = mode; P.scale = scale; P.slot_bytes = slot;
+    P.n_seg = n_mat; P.total_steps = steps; P.n_tiles = tiles; P.B = B; P.ldc = ldc; P.mode = mode; P.scale = scale; P.slot_bytes = slot; P.whole = whole ? 1 : 0;
     const size_t fixed = qg_smem_bytes(0, 0);
     P.n_raw = (int)std::min<size_t>(QG_MAX_RAW, ((size_t)E.smem_optin - fixed) / slot);
     if (P.n_raw < 2) return fail(B200_ERR_UNSUPPORTED, "qgemm: shared memory too small");
@@ -530,11 +537,11 @@ static int qgemm(Engine& E, const QMat* mats, int n_mat, const __nv_bfloat16* X,
     static bool attr = false;
     if (!attr) { CK(cudaFuncSetAttribute(qgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, E.smem_optin)); attr = true; }
     CUtensorMap tx; if (int rc = make_tmap(&tx, X, (uint64_t)B, (uint64_t)K, QG_NB)) return rc;
-    const int G = E.n_sm;
+    const int G = std::min(E.n_sm, whole ? tiles : steps);              // every CTA gets at least one K-step
     qgemm_kernel<<<G, QG_THREADS, qg_smem_bytes(slot, P.n_raw), E.stream>>>(tx, P);
-    qgemm_fixup_kernel<<<dim3(tiles, (B + 7) / 8), QG_ROWS, 0, E.stream>>>(P, G);
     CK(cudaGetLastError());
-    E.launches += 2;
+    E.launches++;
+    if (!whole) { sp->ws = E.qg_ws; sp->T = steps; sp->G = G; sp->ks = P.ks; sp->n_seg = n_mat; sp->mode = mode; sp->scale = scale * (1.f / QG_PRESCALE); }
     return B200_OK;
 }
 static int tile_repack(Engine& E, Matrix& m, uint8_t* dst) {
@@ -616,20 +623,20 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
     auto deq = [&](const Matrix& m, __nv_bfloat16* dst) {
         dequant_bf16_kernel<<<nblk(m.n_rows * (long long)m.K / 2), 256, 0, E.stream>>>(m.w, m.type, m.n_rows, m.K, dst); E.launches++;
     };
-    int rc;
+    int rc; QgSplit sp{}, none{};                                    // sp: partial tiles the next row kernel must complete
     embed_rows_kernel<<<nblk((long long)M * D), 256, 0, E.stream>>>(tok_embd.w, tok_embd.type, D, d_toks, M, emb_scale, pf_H); E.launches++;
     for (int l = 0; l < n_layer; l++) {
         Layer& L = layers[l];
         const __nv_bfloat16 *wqkv = L.b_qkv, *wo = L.b_o, *wgu = L.b_gu, *wd = L.b_d;
-        rmsnorm_rows_kernel<<<M, 256, 0, E.stream>>>(pf_H, L.attn_norm, D, M, rms_eps, pf_X, q); E.launches++;
+        rmsnorm_rows_kernel<<<M, 256, 0, E.stream>>>(pf_H, L.attn_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
         if (q) {
             const QMat qkv[3] = {{&L.wq, pf_Y}, {&L.wk, pf_Y + QD}, {&L.wv, pf_Y + QD + KVD}};
-            if ((rc = qgemm(E, qkv, 3, pf_X, M, D, W3, 0, 1.f))) return rc;
+            if ((rc = qgemm(E, qkv, 3, pf_X, M, D, W3, 0, 1.f, false, &sp))) return rc;
         } else {
             if (!bf16_ready) { deq(L.wq, pf_W); deq(L.wk, pf_W + (size_t)QD * D); deq(L.wv, pf_W + (size_t)(QD + KVD) * D); wqkv = pf_W; }
             if ((rc = gemm_bf16(E, pf_X, wqkv, pf_Y, M, W3, D, W3, 0, 1.f))) return rc;
         }
-        rope_kv_rows_kernel<<<nblk((long long)M * W3 / 2), 256, 0, E.stream>>>(pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, inv_freq, kv, pf_Q); E.launches++;
+        rope_kv_rows_kernel<<<nblk((long long)M * W3 / 2), 256, 0, E.stream>>>(pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, inv_freq, kv, pf_Q, sp); E.launches++; sp = none;
         {
             const int G = n_head / n_head_kv; const dim3 ag(M * n_head_kv);
 #define B200_ATTN(HD_, G_) attn_rows_kernel<HD_, G_><<<ag, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q)
@@ -642,20 +649,20 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
 #undef B200_ATTN
         }
         E.launches++;
-        if (q) { const QMat o{&L.wo, pf_H}; if ((rc = qgemm(E, &o, 1, pf_X, M, QD, D, 1, rs))) return rc; }
+        if (q) { const QMat o{&L.wo, pf_H}; if ((rc = qgemm(E, &o, 1, pf_X, M, QD, D, 1, rs, false, &sp))) return rc; }
         else {
             if (!bf16_ready) { deq(L.wo, pf_W); wo = pf_W; }
             if ((rc = gemm_bf16(E, pf_X, wo, pf_H, M, D, QD, D, 1, rs))) return rc;
         }
         if (l == n_layer - 1 && !want_logits) break;                  // KV fill only: the last layer's FFN feeds nothing
-        rmsnorm_rows_kernel<<<M, 256, 0, E.stream>>>(pf_H, L.ffn_norm, D, M, rms_eps, pf_X, q); E.launches++;
-        if (q) { const QMat gu{&L.wgu, pf_Y}; if ((rc = qgemm(E, &gu, 1, pf_X, M, D, 2 * F, 0, 1.f))) return rc; }
+        rmsnorm_rows_kernel<<<M, 256, 0, E.stream>>>(pf_H, L.ffn_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
+        if (q) { const QMat gu{&L.wgu, pf_Y}; if ((rc = qgemm(E, &gu, 1, pf_X, M, D, 2 * F, 0, 1.f, false, &sp))) return rc; }
         else {
             if (!bf16_ready) { deq(L.wgu, pf_W); wgu = pf_W; }
             if ((rc = gemm_bf16(E, pf_X, wgu, pf_Y, M, 2 * F, D, 2 * F, 0, 1.f))) return rc;
         }
-        swiglu_rows_kernel<<<nblk((long long)M * F), 256, 0, E.stream>>>(pf_Y, M, F, pf_ACT, q); E.launches++;
-        if (q) { const QMat dn{&L.wd, pf_H}; if ((rc = qgemm(E, &dn, 1, pf_ACT, M, F, D, 1, rs))) return rc; }
+        swiglu_rows_kernel<<<nblk((long long)M * F), 256, 0, E.stream>>>(pf_Y, M, F, pf_ACT, q, sp); E.launches++; sp = none;
+        if (q) { const QMat dn{&L.wd, pf_H}; if ((rc = qgemm(E, &dn, 1, pf_ACT, M, F, D, 1, rs, false, &sp))) return rc; }
         else {
             if (!bf16_ready) { deq(L.wd, pf_W); wd = pf_W; }
             if ((rc = gemm_bf16(E, pf_ACT, wd, pf_H, M, D, F, D, 1, rs))) return rc;
@@ -663,8 +670,8 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
     }
     if (want_logits) {
         const int ldv = (n_vocab + 3) & ~3; const float ls = logit_scale != 0.f ? 1.f / logit_scale : 1.f;
-        rmsnorm_rows_kernel<<<M, 256, 0, E.stream>>>(pf_H, out_norm, D, M, rms_eps, pf_X, q); E.launches++;
-        if (q) { const QMat o{&out_w, bt_logits}; if ((rc = qgemm(E, &o, 1, pf_X, M, D, ldv, 0, ls))) return rc; }
+        rmsnorm_rows_kernel<<<M, 256, 0, E.stream>>>(pf_H, out_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
+        if (q) { const QMat o{&out_w, bt_logits}; if ((rc = qgemm(E, &o, 1, pf_X, M, D, ldv, 0, ls, true, &sp))) return rc; sp = none; }
         else {
             if (!bf16_ready) return fail(B200_ERR_STATE, "logits through the dense path need the bf16 weight cache");
             if ((rc = gemm_bf16(E, pf_X, b_out, bt_logits, M, n_vocab, D, ldv, 0, ls))) return rc;
@@ -735,12 +742,14 @@ int kernel_qgemm(int type, const void* raw, int64_t N, int K, const float* x, in
     cudaMemcpyAsync(d_x, hx.data(), hx.size() * 2, cudaMemcpyHostToDevice, E.stream);
     cudaMemsetAsync(d_y, 0, (size_t)B * N * 4, E.stream);
     if (!(rc = repack(E, d_raw, m.w, type, Np, N, K)) && !(rc = tile_repack(E, m, d_tl))) {
-        const QMat qm{&m, d_y};
-        rc = qgemm(E, &qm, 1, d_x, B, K, (int)N, 0, 1.f);
+        const QMat qm{&m, d_y}; QgSplit sp{};
+        const bool whole = getenv("B200_QG_WHOLE") != nullptr;
+        rc = qgemm(E, &qm, 1, d_x, B, K, (int)N, 0, 1.f, whole, &sp);
+        if (!rc && sp.ws) { qgemm_finish_kernel<<<nblk((long long)B * N), 256, 0, E.stream>>>(sp, d_y, (int)N, B, (int)N); E.launches++; }
         if (!rc && iters > 1) {                                    // timing: repeat the launch pair, mean per iteration
             cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
             cudaEventRecord(e0, E.stream);
-            for (int i = 0; i < iters && !rc; i++) rc = qgemm(E, &qm, 1, d_x, B, K, (int)N, 0, 1.f);
+            for (int i = 0; i < iters && !rc; i++) rc = qgemm(E, &qm, 1, d_x, B, K, (int)N, 0, 1.f, whole, &sp);
             cudaEventRecord(e1, E.stream); cudaEventSynchronize(e1);
             float ms = 0.f; cudaEventElapsedTime(&ms, e0, e1); if (ms_out) *ms_out = ms / iters;
             cudaEventDestroy(e0); cudaEventDestroy(e1);

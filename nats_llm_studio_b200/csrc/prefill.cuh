@@ -172,6 +172,38 @@ __device__ __forceinline__ unsigned short pack16(float a, bool f16) {
     return f16 ? __half_as_ushort(__float2half_rn(clamp_h(a))) : __bfloat16_as_ushort(__float2bfloat16(a));
 }
 
+// How a stream-K dequant-in-GEMM launch (qgemm.cuh) left its result: row tiles whose whole K range ran in one CTA are
+// final in C; the others exist as fp32 partials of the contributing CTAs (consecutive CTA indices = ascending K).  The
+// row kernel that consumes C sums them on the fly, in CTA order — no reduction pass, no atomics, deterministic.
+struct QgSplit {
+    const float* ws;            // [cta][2 slots][64 batch rows][128 tile rows]; nullptr = nothing to gather
+    int T, G, ks, n_seg, mode;  // total K-steps, CTAs, K-steps per tile, matrices in the launch, 1 = result is added to C
+    int step0[3], col0[3];      // first global step / first output column of each matrix
+    float scale;
+};
+constexpr int QG_WS_B = 64, QG_WS_N = 128;
+// v[0..N) = final values of C[b][col .. col+N) given `v` = what C holds now (N consecutive columns of one 4-aligned group)
+template <int N>
+__device__ __forceinline__ void qg_gather(const QgSplit& sp, int b, int col, float* v) {
+    if (!sp.ws) return;
+    int si = 0; while (si + 1 < sp.n_seg && col >= sp.col0[si + 1]) si++;
+    const int nl = col - sp.col0[si], t0 = sp.step0[si] + (nl >> 7) * sp.ks;
+    const int c_lo = (int)(((long long)(t0 + 1) * sp.G + sp.T - 1) / sp.T) - 1, c_hi = (int)(((long long)(t0 + sp.ks) * sp.G + sp.T - 1) / sp.T) - 1;
+    if (c_lo == c_hi) return;                                       // tile was not split: C is final
+    float acc[N];
+#pragma unroll
+    for (int i = 0; i < N; i++) acc[i] = 0.f;
+    for (int c = c_lo; c <= c_hi; c++) {
+        const int cb = (int)((long long)c * sp.T / sp.G);
+        const float* src = sp.ws + ((size_t)(c * 2 + (cb >= t0 ? 0 : 1)) * QG_WS_B + b) * QG_WS_N + (nl & 127);
+        if (N == 4) { const float4 p = __ldcg((const float4*)src); acc[0] += p.x; acc[1] += p.y; acc[2 % N] += p.z; acc[3 % N] += p.w; }
+        else if (N == 2) { const float2 p = __ldcg((const float2*)src); acc[0] += p.x; acc[1] += p.y; }
+        else acc[0] += __ldcg(src);
+    }
+#pragma unroll
+    for (int i = 0; i < N; i++) v[i] = sp.mode == 1 ? v[i] + acc[i] * sp.scale : acc[i] * sp.scale;
+}
+
 // ------------------------------------------------------------------------------------ row-wise kernels
 // engine-layout quantised matrix -> bf16 [n_rows x K] (row r of the matrix at out + r*K)
 __global__ void dequant_bf16_kernel(const uint8_t* __restrict__ w, int type, long long n_rows, int K, __nv_bfloat16* __restrict__ out) {
@@ -193,12 +225,18 @@ __global__ void embed_rows_kernel(const uint8_t* __restrict__ embd, int type, in
     }
 }
 
-// X[m][:] = 16-bit(rmsnorm(H[m]) * w); one block per row
-__global__ void __launch_bounds__(256) rmsnorm_rows_kernel(const float* __restrict__ H, const float* __restrict__ w, int D, int M, float eps, __nv_bfloat16* __restrict__ X, bool perm) {
+// X[m][:] = 16-bit(rmsnorm(H[m]) * w); one block per row.  With a split producer (sp.ws) H[m] is first completed from
+// the partials of the residual GEMM that precedes the norm and written back.
+__global__ void __launch_bounds__(256) rmsnorm_rows_kernel(float* __restrict__ H, const float* __restrict__ w, int D, int M, float eps, __nv_bfloat16* __restrict__ X, bool perm,
+                                                           const __grid_constant__ QgSplit sp) {
     __shared__ float red[8];
     const int m = blockIdx.x, tid = threadIdx.x;
-    const float* h = H + (size_t)m * D; float ss = 0.f;
-    for (int i = tid * 4; i < D; i += 1024) { const float4 v = *(const float4*)(h + i); ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w; }
+    float* h = H + (size_t)m * D; float ss = 0.f;
+    for (int i = tid * 4; i < D; i += 1024) {
+        float4 v = *(const float4*)(h + i);
+        if (sp.ws) { float t[4] = {v.x, v.y, v.z, v.w}; qg_gather<4>(sp, m, i, t); v = make_float4(t[0], t[1], t[2], t[3]); *(float4*)(h + i) = v; }
+        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
     ss = warp_sum(ss);
     if ((tid & 31) == 0) red[tid >> 5] = ss;
     __syncthreads();
@@ -206,7 +244,7 @@ __global__ void __launch_bounds__(256) rmsnorm_rows_kernel(const float* __restri
 #pragma unroll
     for (int i = 0; i < 8; i++) ss += red[i];                       // same order in every thread
     const float rs = rsqrtf(ss / (float)D + eps);
-    for (int i = tid * 4; i < D; i += 1024) {
+    for (int i = tid * 4; i < D; i += 1024) {                       // each thread re-reads exactly what it wrote above
         const float4 v = *(const float4*)(h + i), g = *(const float4*)(w + i);
         const float a = v.x * rs * g.x, b = v.y * rs * g.y, c = v.z * rs * g.z, d = v.w * rs * g.w;
         *(uint2*)(X + (size_t)m * D + i) = perm ? make_uint2(pack16x2(a, c, true), pack16x2(b, d, true)) : make_uint2(pack16x2(a, b, false), pack16x2(c, d, false));
@@ -215,11 +253,12 @@ __global__ void __launch_bounds__(256) rmsnorm_rows_kernel(const float* __restri
 
 // QKV[m][QD + 2*KVD] fp32 -> RoPE(q) as bf16 Q[m][QD]; RoPE(k), v -> fp16 KV pages at position pos0 + m
 __global__ void rope_kv_rows_kernel(const float* __restrict__ QKV, int M, RowMap rm, int layer, int n_head, int n_head_kv, int HD, int n_rot,
-                                    const float* __restrict__ inv_freq, KvLayout kv, __nv_bfloat16* __restrict__ Q) {
+                                    const float* __restrict__ inv_freq, KvLayout kv, __nv_bfloat16* __restrict__ Q, const __grid_constant__ QgSplit sp) {
     const int QD = n_head * HD, KVD = n_head_kv * HD, W = QD + 2 * KVD;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)M * (W / 2); i += (long long)gridDim.x * blockDim.x) {
         const int m = (int)(i / (W / 2)), c = (int)(i % (W / 2)) * 2, pos = rm.p(m), slot = rm.s(m);
         float a = QKV[(size_t)m * W + c], b = QKV[(size_t)m * W + c + 1];
+        if (sp.ws) { float t[2] = {a, b}; qg_gather<2>(sp, m, c, t); a = t[0]; b = t[1]; }
         if (c < QD + KVD) {                               // q or k: rotate the adjacent pair
             const int d = c % HD;
             if (d < n_rot) { float sn, cs; sincosf((float)pos * inv_freq[d >> 1], &sn, &cs); const float x = a, y = b; a = x * cs - y * sn; b = x * sn + y * cs; }
@@ -379,9 +418,10 @@ __global__ void argmax_rows_kernel(const float* __restrict__ logits, int V, int 
 }
 
 // ACT[m][i] = bf16(silu(GU[m][2i]) * GU[m][2i+1])   (gate/up rows are interleaved in the fused matrix)
-__global__ void swiglu_rows_kernel(const float* __restrict__ GU, int M, int F, __nv_bfloat16* __restrict__ ACT, bool perm) {
+__global__ void swiglu_rows_kernel(const float* __restrict__ GU, int M, int F, __nv_bfloat16* __restrict__ ACT, bool perm, const __grid_constant__ QgSplit sp) {
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)M * F; i += (long long)gridDim.x * blockDim.x) {
-        const float2 gu = *(const float2*)(GU + 2 * i);
+        float2 gu = *(const float2*)(GU + 2 * i);
+        if (sp.ws) { float t[2] = {gu.x, gu.y}; qg_gather<2>(sp, (int)(i / F), (int)(2 * (i % F)), t); gu = make_float2(t[0], t[1]); }
         ((unsigned short*)ACT)[perm ? (i - i % 4 + kperm4((int)(i % 4))) : i] = pack16(gu.x / (1.f + __expf(-gu.x)) * gu.y, perm);
     }
 }

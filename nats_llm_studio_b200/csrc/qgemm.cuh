@@ -1,42 +1,47 @@
 // qgemm.cuh — dequant-in-GEMM for batched decode (BASELINE.json "bs64"):
 //     C[b][n] (+)= scale * sum_k X[b][k] * W[n][k],   b < B <= 64,  W quantised (Q4_K / Q5_K / Q6_K / Q8_0)
 // The weights are read ONCE per step in their quantised form (the op is HBM-bound at B <= 64),
-// expanded to fp16 in shared memory by 16 dequant warps, and contracted on the tensor cores:
-// tcgen05.mma kind::f16, A = 128 weight rows (fp16, 128-byte-swizzled K-major tiles written by the dequant
-// warps), B = the 64 activation rows (fp16, TMA), D = fp32 in TMEM (two 64-column accumulators, ping-pong).
+// expanded to fp16 by 16 dequant warps and contracted on the tensor cores: tcgen05.mma kind::f16 with
+//   A = 128 weight rows, fp16, written by the dequant warps straight into TENSOR MEMORY (tcgen05.st; lane = row,
+//       one 32-bit column = two K positions) — a ring of 12 k-blocks (3 K-steps) in TMEM columns 128..511,
+//   B = the 64 activation rows (fp16, TMA, 128-byte swizzle, shared memory),
+//   D = fp32 accumulators in TMEM columns 0..127 (two of 64 columns, ping-pong between tiles).
+// Keeping A out of shared memory leaves ~160 KB for the raw-weight ring (bulk copies in flight) and lets the
+// expansion run up to three K-steps ahead of the MMAs.
 //
 // Tile layout ("TL", built once from the streaming layout by tile_repack_kernel): the matrix is cut into tiles of
-// 128 rows and K-steps of KSTEP elements (256 for the K-quants = one super-block, 128 for Q8_0); the bytes of one
-// (tile, K-step) are one contiguous blob = one bulk copy, ordered inside so that 32 lanes = 32 consecutive rows
-// read their operands with conflict-free 128-bit shared loads:
+// 128 rows and K-steps of 256 elements; the bytes of one (tile, K-step) are one contiguous blob = one bulk copy,
+// ordered inside so that 32 lanes = 32 consecutive rows read their operands with conflict-free 128-bit shared loads:
 //   Q4_K (18432 B): hdr[row][16] (d, dmin, 12 engine-form scale bytes) | qs[j2 4][h 2][row][16]
 //   Q5_K (22528 B): hdr[row][16] | qh[h 2][row][16] | qs[j2 4][h 2][row][16]
 //   Q6_K (26880 B): ql[n 2][piece 4][row][16] | qh[n 2][h 2][row][16] | sc[n,h 4][row][4] | d[row][2]
-//   Q8_0 (17408 B): q[kb 2][piece 4][row][16] | d[kb 2][row][2 x fp16]
+//   Q8_0 (34816 B): q[kb 4][piece 4][row][16] | d[kb 4][row][2 x fp16]
 // Work split: stream-K.  The (tile, K-step) units of all matrices of one launch form one sequence that is cut into
-// n_sm equal contiguous ranges, one per CTA; a tile whose K range ends up in several CTAs is summed, in CTA order
-// (deterministic), by qgemm_fixup_kernel from fp32 partials.
-// K order: inside every aligned group of 4 K positions the A tile holds elements in the order (0, 2, 1, 3) — that is
-// how nibble pairs fall out of a 32-bit word without a permute — so X must be stored with the same permutation
+// equal contiguous ranges, one per CTA; a tile whose K range ends up in several CTAs is left as fp32 partials that the
+// consuming row kernel (RoPE, SwiGLU, the next RMSNorm) sums in CTA order on the fly — deterministic, no atomics, no
+// reduction pass (QgSplit in prefill.cuh).  Matrices with many more tiles than CTAs (lm_head) use tile-aligned ranges.
+// K order: inside every aligned group of 4 K positions the A operand holds elements in the order (0, 2, 1, 3) — that
+// is how nibble pairs fall out of a 32-bit word without a permute — so X must be stored with the same permutation
 // (kperm4); the row kernels that produce X for this path do that.
 // Numerics: weights are expanded as fp16(16 * w) (two or three fp16 roundings, rel. 2^-11 each), activations fp16
-// (clamped to the finite range by the row kernels that write them), fp32 accumulation; the factor 16 keeps small scales out of the fp16 subnormal range and is removed in the epilogue.
+// (clamped to the finite range by the row kernels that write them), fp32 accumulation; the factor 16 keeps small
+// scales out of the fp16 subnormal range and is removed in the epilogue.
 #pragma once
 #include "prefill.cuh"
 
 namespace b200 {
 
-constexpr int QG_ROWS = 128, QG_NB = 64;
+constexpr int QG_ROWS = 128, QG_NB = 64, QG_KSTEP = 256;
 constexpr int QG_DQ_WARPS = 16, QG_FIRST_DQ = 3, QG_FIRST_EPI = QG_FIRST_DQ + QG_DQ_WARPS, QG_WARPS = QG_FIRST_EPI + 4, QG_THREADS = QG_WARPS * 32;
-constexpr int QG_A_SLOTS = 4, QG_X_SLOTS = 8, QG_MAX_RAW = 8;
-constexpr uint32_t QG_A_BYTES = QG_ROWS * 128, QG_X_BYTES = QG_NB * 128;
+constexpr int QG_A_STEPS = 3, QG_X_STEPS = 2, QG_MAX_RAW = 8, QG_MAX_TILES = 4096;
+constexpr uint32_t QG_X_BYTES = 4 * QG_NB * 128;              // one K-step of activations: 4 k-blocks of 64 rows x 128 B
+constexpr uint32_t QG_TMEM_COLS = 512, QG_TMEM_A0 = 2 * QG_NB; // accumulators in columns [0,128), A ring in [128,512)
 constexpr float QG_PRESCALE = 16.f;
 
-__host__ __device__ constexpr int qg_kstep(int t) { return t == T_Q8_0 ? 128 : 256; }
 __host__ __device__ constexpr int qg_blob_bytes(int t) {
-    return t == T_Q4_K ? 128 * 144 : t == T_Q5_K ? 128 * 176 : t == T_Q6_K ? 128 * 210 : t == T_Q8_0 ? 128 * 136 : 0;
+    return t == T_Q4_K ? 128 * 144 : t == T_Q5_K ? 128 * 176 : t == T_Q6_K ? 128 * 210 : t == T_Q8_0 ? 128 * 272 : 0;
 }
-__host__ __device__ inline size_t tile_bytes(int t, int64_t N, int K) { return (size_t)((N + QG_ROWS - 1) / QG_ROWS) * (K / qg_kstep(t)) * qg_blob_bytes(t); }
+__host__ __device__ inline size_t tile_bytes(int t, int64_t N, int K) { return (size_t)((N + QG_ROWS - 1) / QG_ROWS) * (K / QG_KSTEP) * qg_blob_bytes(t); }
 
 // blob byte o -> (row in tile, raw block inside the K-step, raw byte inside that block)
 __host__ __device__ inline void tile_src(int t, int o, int& row, int& blk, int& i) {
@@ -55,14 +60,14 @@ __host__ __device__ inline void tile_src(int t, int o, int& row, int& blk, int& 
         if (o < 2048) { const int p = o / 512, n = p / 2, h = p % 2; row = (o % 512) / 4; i = 192 + 8 * n + 2 * (o % 4) + h; return; }
         o -= 2048; row = o / 2; i = 208 + o % 2; return;
     }
-    // Q8_0, K-step of 128 = 4 blocks
-    if (o < 16384) { const int pc = o / 2048, e = 16 * pc + o % 16; row = (o % 2048) / 16; blk = e / 32; i = 2 + e % 32; return; }
-    o -= 16384; { const int kb = o / 512, b = o % 4; row = (o % 512) / 4; blk = 2 * kb + b / 2; i = b % 2; }
+    // Q8_0: 8 blocks of 32 per K-step
+    if (o < 32768) { const int e = 16 * (o / 2048) + o % 16; row = (o % 2048) / 16; blk = e / 32; i = 2 + e % 32; return; }
+    o -= 32768; { const int kb = o / 512, b = o % 4; row = (o % 512) / 4; blk = 2 * kb + b / 2; i = b % 2; }
 }
 
 // streaming layout (quant.cuh) -> tile layout; rows >= N read as zero bytes
 __global__ void tile_repack_kernel(const uint8_t* __restrict__ w, int type, int64_t N, int K, uint8_t* __restrict__ out) {
-    const int ks = K / qg_kstep(type), blob = qg_blob_bytes(type), ng = n_groups(K), gb = group_bytes(type);
+    const int ks = K / QG_KSTEP, blob = qg_blob_bytes(type), ng = n_groups(K), gb = group_bytes(type);
     const int64_t n_tiles = (N + QG_ROWS - 1) / QG_ROWS, total = n_tiles * ks * (int64_t)blob;
     for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
         const int o = (int)(idx % blob); const int64_t u = idx / blob; const int kstep = (int)(u % ks); const int64_t tile = u / ks;
@@ -70,7 +75,7 @@ __global__ void tile_repack_kernel(const uint8_t* __restrict__ w, int type, int6
         const int64_t r = tile * QG_ROWS + row;
         uint8_t v = 0;
         if (r < N) {
-            const int sb = type == T_Q8_0 ? kstep * 4 + blk : kstep;          // raw block index inside the row
+            const int sb = type == T_Q8_0 ? kstep * 8 + blk : kstep;          // raw block index inside the row
             const int per_grp = type == T_Q8_0 ? 64 : 8, g = sb / per_grp;
             v = w[(((r >> 1) * ng + g) * 2 + (r & 1)) * (size_t)gb + dst_byte(type, sb % per_grp, i)];
         }
@@ -78,10 +83,11 @@ __global__ void tile_repack_kernel(const uint8_t* __restrict__ w, int type, int6
     }
 }
 
-struct QSeg { const uint8_t* tl; float* C; int type, n_tiles, n_rows, ks, step0, tile0; };
+struct QSeg { const uint8_t* tl; float* C; int type, n_tiles, n_rows, step0, tile0; };
 struct QGemmParams {
-    QSeg seg[3]; int n_seg, total_steps, n_tiles, B, ldc, mode, n_raw; float scale; float* ws; uint32_t slot_bytes;
-    int debug;      // profiling only (B200_QG_DEBUG): 1 = skip the expansion math, 2 = skip the MMAs
+    QSeg seg[3]; int n_seg, ks /*K-steps per tile*/, total_steps, n_tiles, B, ldc, mode, n_raw; float scale; float* ws; uint32_t slot_bytes;
+    int whole;      // 1 = CTA ranges are aligned to tiles (no partials; for matrices with many more tiles than CTAs)
+    int debug;      // profiling only (B200_QG_DEBUG): 1 = skip the expansion math, 2 = skip the MMAs, 4 = no X loads, 8 = no weight loads
 };
 
 __device__ __forceinline__ int qg_seg_of_step(const QGemmParams& P, int s) { int i = 0; while (i + 1 < P.n_seg && s >= P.seg[i + 1].step0) i++; return i; }
@@ -93,22 +99,39 @@ __device__ __forceinline__ uint32_t h2mul(uint32_t a, uint32_t b) { uint32_t d; 
 __device__ __forceinline__ uint32_t h2dup(float v) { uint32_t d; asm("cvt.rn.f16x2.f32 %0, %1, %1;" : "=r"(d) : "f"(v)); return d; }
 __device__ __forceinline__ float h16f(uint32_t bits) { return __half2float(__ushort_as_half((unsigned short)bits)); }
 __device__ __forceinline__ uint4 lds128(const uint8_t* p) { return *(const uint4*)p; }
-__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-// 16-byte chunk c (8 K positions) of row `row` inside a 128-row x 64-K swizzled tile
-__device__ __forceinline__ uint32_t a_chunk(uint32_t tile, int row, int c) { return tile + (row >> 3) * 1024 + (row & 7) * 128 + ((c ^ (row & 7)) << 4); }
-__device__ __forceinline__ void mbar_arrive_n(uint64_t* bar, uint32_t n) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(n) : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 constexpr uint32_t H2_MAGIC = 0x64006400u /*1024*/, H2_M1024 = 0xE400E400u, H2_1152 = 0x64806480u, H2_1056 = 0x64206420u;
 
+// ------------------------------------------------------------------------------------ tensor-memory stores / A-from-TMEM MMA
+#define QG_R8(r, o) "r"(r[o]), "r"(r[o + 1]), "r"(r[o + 2]), "r"(r[o + 3]), "r"(r[o + 4]), "r"(r[o + 5]), "r"(r[o + 6]), "r"(r[o + 7])
+// this warp's 32 lanes (TMEM lanes of its quadrant) x n consecutive 32-bit columns starting at taddr
+__device__ __forceinline__ void tmem_st_x8(uint32_t taddr, const uint32_t* r) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), QG_R8(r, 0) : "memory");
+}
+__device__ __forceinline__ void tmem_st_x32(uint32_t taddr, const uint32_t* r) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        ::"r"(taddr), QG_R8(r, 0), QG_R8(r, 8), QG_R8(r, 16), QG_R8(r, 24) : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// D[tmem] (+)= A[tmem: 128 lanes x 8 columns = 128 x 16 fp16] . B[smem desc]^T
+__device__ __forceinline__ void tcgen05_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
 // ------------------------------------------------------------------------------------ per-type expansion, one lane = one row
-// Q4_K / Q5_K: lane expands the 64 elements of chunk j2 (sub-blocks 2*j2, 2*j2+1) of its row into k-block tile `tile`
+// Each routine fills o[32] = the lane's 64 expanded elements as fp16 pairs.  A k-block (64 K positions) is 32 columns:
+// column c holds positions (2c, 2c+1), i.e. elements (e, e+2) or (e+1, e+3) of an aligned group of four (kperm4).
+// Q4_K / Q5_K: chunk j2 of the super-block (sub-blocks 2*j2: low nibbles -> columns 0..15, 2*j2+1: high -> 16..31)
 template <bool Q5>
-__device__ __forceinline__ void dq_k45(const uint8_t* raw, int row, int j2, uint32_t tile) {
+__device__ __forceinline__ void dq_k45(const uint8_t* raw, int row, int j2, uint32_t* o) {
     const uint4 hd = lds128(raw + row * 16);
     const uint32_t f = j2 == 0 ? hd.y : j2 == 1 ? __funnelshift_r(hd.y, hd.z, 24) : j2 == 2 ? __funnelshift_r(hd.z, hd.w, 16) : hd.w >> 8;
     const float d = h16f(hd.x & 0xFFFF) * QG_PRESCALE, dmin = h16f(hd.x >> 16) * QG_PRESCALE;
@@ -122,44 +145,41 @@ __device__ __forceinline__ void dq_k45(const uint8_t* raw, int row, int j2, uint
         uint4 hq = make_uint4(0, 0, 0, 0);
         if (Q5) hq = lds128(raw + 2048 + h * 2048 + row * 16);
         const uint32_t xs[4] = {q.x, q.y, q.z, q.w}, hs[4] = {hq.x, hq.y, hq.z, hq.w};
-        uint32_t lo[8], hi[8];
 #pragma unroll
-        for (int w = 0; w < 4; w++) {
+        for (int w = 0; w < 4; w++) {                              // bytes l = 16h + 4w .. +3 -> columns 8h + 2w, +1 (low) and 16 + that (high)
             const uint32_t x = xs[w], y = x >> 8;
             uint32_t l02 = (x & 0x000F000Fu) | H2_MAGIC, h02 = (x & 0x00F000F0u) | H2_MAGIC, l13 = (y & 0x000F000Fu) | H2_MAGIC, h13 = (y & 0x00F000F0u) | H2_MAGIC;
             if (Q5) {
                 const uint32_t a = hs[w] >> (2 * j2), b = a >> 8;
                 l02 |= (a << 4) & 0x00100010u; h02 |= (a << 7) & 0x01000100u; l13 |= (b << 4) & 0x00100010u; h13 |= (b << 7) & 0x01000100u;
             }
-            lo[2 * w] = h2sub(h2fma(l02, S0, C0), M0); lo[2 * w + 1] = h2sub(h2fma(l13, S0, C0), M0);
-            hi[2 * w] = h2sub(h2fma(h02, S1, C1), M1); hi[2 * w + 1] = h2sub(h2fma(h13, S1, C1), M1);
+            o[8 * h + 2 * w] = h2sub(h2fma(l02, S0, C0), M0); o[8 * h + 2 * w + 1] = h2sub(h2fma(l13, S0, C0), M0);
+            o[16 + 8 * h + 2 * w] = h2sub(h2fma(h02, S1, C1), M1); o[16 + 8 * h + 2 * w + 1] = h2sub(h2fma(h13, S1, C1), M1);
         }
-        sts128(a_chunk(tile, row, 2 * h), lo[0], lo[1], lo[2], lo[3]); sts128(a_chunk(tile, row, 2 * h + 1), lo[4], lo[5], lo[6], lo[7]);
-        sts128(a_chunk(tile, row, 4 + 2 * h), hi[0], hi[1], hi[2], hi[3]); sts128(a_chunk(tile, row, 5 + 2 * h), hi[4], hi[5], hi[6], hi[7]);
     }
 }
 
-// Q8_0: lane expands block (2*kb + half) = 32 elements of its row into chunks 4*half .. 4*half+3 of the k-block tile
-__device__ __forceinline__ void dq_q80(const uint8_t* raw, int row, int kb, int half, uint32_t tile) {
-    const uint32_t D = h2dup(h16f(*(const unsigned short*)(raw + 16384 + ((kb * 128 + row) * 2 + half) * 2)) * QG_PRESCALE);
+// Q8_0: k-block kb of the K-step = blocks 2kb, 2kb+1 (columns 0..15, 16..31)
+__device__ __forceinline__ void dq_q80(const uint8_t* raw, int row, int kb, uint32_t* o) {
+    const uint32_t dd = *(const uint32_t*)(raw + 32768 + (kb * 128 + row) * 4);
+    const uint32_t D0 = h2dup(h16f(dd & 0xFFFF) * QG_PRESCALE), D1 = h2dup(h16f(dd >> 16) * QG_PRESCALE);
 #pragma unroll
-    for (int pc = 0; pc < 2; pc++) {
-        const uint4 q = lds128(raw + (size_t)((kb * 4 + 2 * half + pc) * 128 + row) * 16);
-        const uint32_t xs[4] = {q.x, q.y, q.z, q.w}; uint32_t o[8];
+    for (int pc = 0; pc < 4; pc++) {
+        const uint4 q = lds128(raw + (size_t)((kb * 4 + pc) * 128 + row) * 16);
+        const uint32_t xs[4] = {q.x, q.y, q.z, q.w}, D = pc < 2 ? D0 : D1;
 #pragma unroll
         for (int w = 0; w < 4; w++) {
             const uint32_t u = xs[w] ^ 0x80808080u;
-            o[2 * w] = h2mul(h2sub(__byte_perm(u, 0x64646464u, 0x4240), H2_1152), D);
-            o[2 * w + 1] = h2mul(h2sub(__byte_perm(u, 0x64646464u, 0x4341), H2_1152), D);
+            o[8 * pc + 2 * w] = h2mul(h2sub(__byte_perm(u, 0x64646464u, 0x4240), H2_1152), D);
+            o[8 * pc + 2 * w + 1] = h2mul(h2sub(__byte_perm(u, 0x64646464u, 0x4341), H2_1152), D);
         }
-        const int c = 4 * half + 2 * pc;
-        sts128(a_chunk(tile, row, c), o[0], o[1], o[2], o[3]); sts128(a_chunk(tile, row, c + 1), o[4], o[5], o[6], o[7]);
     }
 }
 
-// Q6_K: lane expands, for 128-half n and 16-run h, the 64 elements (grp 0..3) x (l in [16h, 16h+16)) of its row:
-// grp 0,1 -> k-block 2n (tile0), grp 2,3 -> k-block 2n+1 (tile1)
-__device__ __forceinline__ void dq_q6k(const uint8_t* raw, int row, int n, int h, uint32_t tile0, uint32_t tile1) {
+// Q6_K: for 128-half n and 16-run h, the 64 elements (grp 0..3) x (l in [16h, 16h+16)) of the row:
+// o[0..7] = grp 0 -> k-block 2n columns 8h..8h+7; o[8..15] = grp 1 -> k-block 2n columns 16+8h..; o[16..23] = grp 2 and
+// o[24..31] = grp 3 -> the same column ranges of k-block 2n+1
+__device__ __forceinline__ void dq_q6k(const uint8_t* raw, int row, int n, int h, uint32_t* o) {
     const uint4 qa = lds128(raw + (size_t)((n * 4 + h) * 128 + row) * 16), qb = lds128(raw + (size_t)((n * 4 + 2 + h) * 128 + row) * 16);
     const uint4 qh = lds128(raw + 16384 + (size_t)((n * 2 + h) * 128 + row) * 16);
     const uint32_t sc = *(const uint32_t*)(raw + 24576 + ((n * 2 + h) * 128 + row) * 4);
@@ -167,24 +187,19 @@ __device__ __forceinline__ void dq_q6k(const uint8_t* raw, int row, int n, int h
     const uint32_t S0 = h2dup(d * (float)(int8_t)(sc & 0xFF)), S1 = h2dup(d * (float)(int8_t)((sc >> 8) & 0xFF)),
                    S2 = h2dup(d * (float)(int8_t)((sc >> 16) & 0xFF)), S3 = h2dup(d * (float)(int8_t)(sc >> 24));
     const uint32_t as[4] = {qa.x, qa.y, qa.z, qa.w}, bs[4] = {qb.x, qb.y, qb.z, qb.w}, hs[4] = {qh.x, qh.y, qh.z, qh.w};
-    uint32_t g0[8], g1[8], g2[8], g3[8];
 #pragma unroll
     for (int w = 0; w < 4; w++) {
         const uint32_t xa = as[w], xb = bs[w], hq = hs[w];
         const uint32_t m4 = 0x000F000Fu, m2 = 0x00300030u;
-        g0[2 * w]     = h2mul(h2sub(((xa)       & m4) | ((hq << 4) & m2) | H2_MAGIC, H2_1056), S0);
-        g0[2 * w + 1] = h2mul(h2sub(((xa >> 8)  & m4) | ((hq >> 4) & m2) | H2_MAGIC, H2_1056), S0);
-        g1[2 * w]     = h2mul(h2sub(((xb)       & m4) | ((hq << 2) & m2) | H2_MAGIC, H2_1056), S1);
-        g1[2 * w + 1] = h2mul(h2sub(((xb >> 8)  & m4) | ((hq >> 6) & m2) | H2_MAGIC, H2_1056), S1);
-        g2[2 * w]     = h2mul(h2sub(((xa >> 4)  & m4) | ((hq)      & m2) | H2_MAGIC, H2_1056), S2);
-        g2[2 * w + 1] = h2mul(h2sub(((xa >> 12) & m4) | ((hq >> 8) & m2) | H2_MAGIC, H2_1056), S2);
-        g3[2 * w]     = h2mul(h2sub(((xb >> 4)  & m4) | ((hq >> 2) & m2) | H2_MAGIC, H2_1056), S3);
-        g3[2 * w + 1] = h2mul(h2sub(((xb >> 12) & m4) | ((hq >> 10) & m2) | H2_MAGIC, H2_1056), S3);
+        o[2 * w]          = h2mul(h2sub(((xa)       & m4) | ((hq << 4) & m2) | H2_MAGIC, H2_1056), S0);
+        o[2 * w + 1]      = h2mul(h2sub(((xa >> 8)  & m4) | ((hq >> 4) & m2) | H2_MAGIC, H2_1056), S0);
+        o[8 + 2 * w]      = h2mul(h2sub(((xb)       & m4) | ((hq << 2) & m2) | H2_MAGIC, H2_1056), S1);
+        o[8 + 2 * w + 1]  = h2mul(h2sub(((xb >> 8)  & m4) | ((hq >> 6) & m2) | H2_MAGIC, H2_1056), S1);
+        o[16 + 2 * w]     = h2mul(h2sub(((xa >> 4)  & m4) | ((hq)      & m2) | H2_MAGIC, H2_1056), S2);
+        o[16 + 2 * w + 1] = h2mul(h2sub(((xa >> 12) & m4) | ((hq >> 8) & m2) | H2_MAGIC, H2_1056), S2);
+        o[24 + 2 * w]     = h2mul(h2sub(((xb >> 4)  & m4) | ((hq >> 2) & m2) | H2_MAGIC, H2_1056), S3);
+        o[24 + 2 * w + 1] = h2mul(h2sub(((xb >> 12) & m4) | ((hq >> 10) & m2) | H2_MAGIC, H2_1056), S3);
     }
-    sts128(a_chunk(tile0, row, 2 * h), g0[0], g0[1], g0[2], g0[3]);     sts128(a_chunk(tile0, row, 2 * h + 1), g0[4], g0[5], g0[6], g0[7]);
-    sts128(a_chunk(tile0, row, 4 + 2 * h), g1[0], g1[1], g1[2], g1[3]); sts128(a_chunk(tile0, row, 5 + 2 * h), g1[4], g1[5], g1[6], g1[7]);
-    sts128(a_chunk(tile1, row, 2 * h), g2[0], g2[1], g2[2], g2[3]);     sts128(a_chunk(tile1, row, 2 * h + 1), g2[4], g2[5], g2[6], g2[7]);
-    sts128(a_chunk(tile1, row, 4 + 2 * h), g3[0], g3[1], g3[2], g3[3]); sts128(a_chunk(tile1, row, 5 + 2 * h), g3[4], g3[5], g3[6], g3[7]);
 }
 
 __host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N) {
@@ -201,14 +216,10 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32_nowait(uint32_t taddr, uint32
         : "r"(taddr) : "memory");
 }
 
-// shared-memory carve-up (all offsets from the 1024-aligned base)
-struct QgSmem {
-    uint8_t *a, *x, *raw; uint64_t *raw_full, *raw_empty, *x_full, *x_empty, *a_full, *a_empty, *acc_full, *acc_empty; uint32_t* tmem_slot;
-};
+// shared memory: X ring (2 K-steps, 1024-aligned) | raw-weight ring | barriers
+struct QgSmem { uint8_t *x, *raw; uint64_t *raw_full, *raw_empty, *x_full, *x_empty, *a_full, *a_empty, *acc_full, *acc_empty; uint32_t* tmem_slot; };
 constexpr uint32_t QG_BAR_BYTES = 512;
-__host__ __device__ inline size_t qg_smem_bytes(uint32_t slot_bytes, int n_raw) {
-    return 1024 + QG_A_SLOTS * QG_A_BYTES + QG_X_SLOTS * QG_X_BYTES + (size_t)n_raw * slot_bytes + QG_BAR_BYTES;
-}
+__host__ __device__ inline size_t qg_smem_bytes(uint32_t slot_bytes, int n_raw) { return 1024 + QG_X_STEPS * QG_X_BYTES + (size_t)n_raw * slot_bytes + QG_BAR_BYTES; }
 
 // ------------------------------------------------------------------------------------ the kernel
 __global__ void __launch_bounds__(QG_THREADS, 1)
@@ -217,28 +228,31 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
     QgSmem S;
     {
         uint8_t* base = (uint8_t*)(((uintptr_t)qg_smem_raw + 1023) & ~(uintptr_t)1023);
-        S.a = base; S.x = S.a + QG_A_SLOTS * QG_A_BYTES; S.raw = S.x + QG_X_SLOTS * QG_X_BYTES;
+        S.x = base; S.raw = S.x + QG_X_STEPS * QG_X_BYTES;
         uint64_t* b = (uint64_t*)(S.raw + (size_t)P.n_raw * P.slot_bytes);
-        S.raw_full = b; S.raw_empty = b + QG_MAX_RAW; S.x_full = b + 2 * QG_MAX_RAW; S.x_empty = S.x_full + QG_X_SLOTS;
-        S.a_full = S.x_empty + QG_X_SLOTS; S.a_empty = S.a_full + QG_A_SLOTS; S.acc_full = S.a_empty + QG_A_SLOTS; S.acc_empty = S.acc_full + 2;
+        S.raw_full = b; S.raw_empty = b + QG_MAX_RAW; S.x_full = b + 2 * QG_MAX_RAW; S.x_empty = S.x_full + QG_X_STEPS;
+        S.a_full = S.x_empty + QG_X_STEPS; S.a_empty = S.a_full + QG_A_STEPS; S.acc_full = S.a_empty + QG_A_STEPS; S.acc_empty = S.acc_full + 2;
         S.tmem_slot = (uint32_t*)(S.acc_empty + 2);
     }
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         for (int i = 0; i < P.n_raw; i++) { mbar_init(&S.raw_full[i], 1); mbar_init(&S.raw_empty[i], QG_DQ_WARPS); }
-        for (int i = 0; i < QG_X_SLOTS; i++) { mbar_init(&S.x_full[i], 1); mbar_init(&S.x_empty[i], 1); }
-        for (int i = 0; i < QG_A_SLOTS; i++) { mbar_init(&S.a_full[i], QG_DQ_WARPS); mbar_init(&S.a_empty[i], 1); }
+        for (int i = 0; i < QG_X_STEPS; i++) { mbar_init(&S.x_full[i], 1); mbar_init(&S.x_empty[i], 1); }
+        for (int i = 0; i < QG_A_STEPS; i++) { mbar_init(&S.a_full[i], QG_DQ_WARPS); mbar_init(&S.a_empty[i], 1); }
         for (int i = 0; i < 2; i++) { mbar_init(&S.acc_full[i], 1); mbar_init(&S.acc_empty[i], 4); }
         fence_barrier_init();
     }
-    if (warp == 2) tcgen05_alloc(S.tmem_slot, 2 * QG_NB);
+    if (warp == 2) tcgen05_alloc(S.tmem_slot, QG_TMEM_COLS);
     tcgen05_fence_before();
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem = *S.tmem_slot;
 
     const int G = gridDim.x, cta = blockIdx.x;
-    const int s_begin = (int)((long long)cta * P.total_steps / G), s_end = (int)((long long)(cta + 1) * P.total_steps / G);
+    const long long T = P.total_steps;
+    int s_begin = (int)((long long)cta * T / G), s_end = (int)((long long)(cta + 1) * T / G);
+    if (P.whole) { s_begin = (int)((long long)cta * P.n_tiles / G) * P.ks; s_end = (int)((long long)(cta + 1) * P.n_tiles / G) * P.ks; }
+    if (P.debug & 16) s_end = s_begin;                 // profiling: launch + TMEM alloc/dealloc only
 
     if (warp == 0) {                                   // ===== weight producer: one bulk copy per (tile, K-step) blob =====
         if (lane == 0) {
@@ -252,39 +266,43 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 bulk_g2s(S.raw + (size_t)rs * P.slot_bytes, sg.tl + (size_t)(s - sg.step0) * bytes, bytes, &S.raw_full[rs]);
             }
         }
-    } else if (warp == 1) {                            // ===== activation producer: one 64 x 64 bf16 box per k-block =====
+    } else if (warp == 1) {                            // ===== activation producer: four 64 x 64 fp16 boxes per K-step =====
         if (lane == 0) {
-            int kbc = 0;
-            for (int s = s_begin; s < s_end; s++) {
+            int it = 0;
+            for (int s = s_begin; s < s_end; s++, it++) {
                 const QSeg& sg = P.seg[qg_seg_of_step(P, s)];
-                const int kstep = (s - sg.step0) % sg.ks, nkb = qg_kstep(sg.type) / 64;
-                for (int kb = 0; kb < nkb; kb++, kbc++) {
-                    const int xs = kbc % QG_X_SLOTS; const uint32_t ph = (kbc / QG_X_SLOTS) & 1;
-                    mbar_wait(&S.x_empty[xs], ph ^ 1);
-                    if (P.debug & 4) { mbar_arrive(&S.x_full[xs]); continue; }
-                    mbar_expect_tx(&S.x_full[xs], QG_X_BYTES);
-                    tma_load_2d(S.x + xs * QG_X_BYTES, &tmap_x, (kstep * nkb + kb) * 64, 0, &S.x_full[xs]);
-                }
+                const int kstep = (s - sg.step0) % P.ks, xs = it % QG_X_STEPS;
+                mbar_wait(&S.x_empty[xs], ((it / QG_X_STEPS) & 1) ^ 1);
+                if (P.debug & 4) { mbar_arrive(&S.x_full[xs]); continue; }
+                mbar_expect_tx(&S.x_full[xs], QG_X_BYTES);
+#pragma unroll
+                for (int kb = 0; kb < 4; kb++) tma_load_2d(S.x + xs * QG_X_BYTES + kb * (QG_NB * 128), &tmap_x, kstep * QG_KSTEP + kb * 64, 0, &S.x_full[xs]);
             }
         }
-    } else if (warp == 2) {                            // ===== MMA issuer =====
+    } else if (warp == 2) {                            // ===== MMA issuer: 16 MMAs (4 k-blocks x K=16) per K-step =====
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_f16(QG_ROWS, QG_NB);
-            int kbc = 0, piece = 0, s = s_begin;
+            int it = 0, piece = 0, s = s_begin;
             while (s < s_end) {
                 const QSeg& sg = P.seg[qg_seg_of_step(P, s)];
-                const int k0 = (s - sg.step0) % sg.ks, n_st = min(sg.ks - k0, s_end - s), nkb = qg_kstep(sg.type) / 64;
+                const int k0 = (s - sg.step0) % P.ks, n_st = min(P.ks - k0, s_end - s);
                 const int buf = piece & 1;
                 mbar_wait(&S.acc_empty[buf], ((piece >> 1) & 1) ^ 1);
                 tcgen05_fence_after();
-                for (int i = 0; i < n_st * nkb; i++, kbc++) {
-                    const int as = kbc % QG_A_SLOTS, xs = kbc % QG_X_SLOTS;
-                    mbar_wait(&S.a_full[as], (kbc / QG_A_SLOTS) & 1);
-                    mbar_wait(&S.x_full[xs], (kbc / QG_X_SLOTS) & 1);
+                for (int i = 0; i < n_st; i++, it++) {
+                    const int as = it % QG_A_STEPS, xs = it % QG_X_STEPS;
+                    mbar_wait(&S.a_full[as], (it / QG_A_STEPS) & 1);
+                    mbar_wait(&S.x_full[xs], (it / QG_X_STEPS) & 1);
                     tcgen05_fence_after();
-                    const uint64_t da = umma_desc_sw128(S.a + as * QG_A_BYTES), db = umma_desc_sw128(S.x + xs * QG_X_BYTES);
+                    if (!(P.debug & 2)) {
 #pragma unroll
-                    for (int k = 0; k < 4; k++) if (!(P.debug & 2)) tcgen05_mma_f16(tmem + buf * QG_NB, da + 2 * k, db + 2 * k, idesc, (i | k) ? 1u : 0u);
+                        for (int kb = 0; kb < 4; kb++) {
+                            const uint64_t db = umma_desc_sw128(S.x + xs * QG_X_BYTES + kb * (QG_NB * 128));
+#pragma unroll
+                            for (int k = 0; k < 4; k++)
+                                tcgen05_mma_f16_ts(tmem + buf * QG_NB, tmem + QG_TMEM_A0 + (as * 4 + kb) * 32 + k * 8, db + 2 * k, idesc, (i | kb | k) ? 1u : 0u);
+                        }
+                    }
                     tcgen05_commit(&S.a_empty[as]);
                     tcgen05_commit(&S.x_empty[xs]);
                 }
@@ -292,48 +310,45 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 s += n_st; piece++;
             }
         }
-    } else if (warp < QG_FIRST_EPI) {                  // ===== dequant warps: raw blob -> fp16 swizzled k-block tiles =====
-        const int w = warp - QG_FIRST_DQ, row = (w & 3) * 32 + lane, p = w >> 2;
-        int it = 0, kbc = 0;
+    } else if (warp < QG_FIRST_EPI) {                  // ===== dequant warps: raw blob -> fp16 A operand in tensor memory =====
+        const int row = (warp & 3) * 32 + lane, p = (warp - QG_FIRST_DQ) >> 2;      // a warp may only touch the TMEM lanes of quadrant warp % 4
+        const uint32_t lane_base = tmem + QG_TMEM_A0 + ((uint32_t)((warp & 3) * 32) << 16);
+        int it = 0;
         for (int s = s_begin; s < s_end; s++, it++) {
             const int type = P.seg[qg_seg_of_step(P, s)].type;
-            const int rs = it % P.n_raw;
+            const int rs = it % P.n_raw, as = it % QG_A_STEPS;
             const uint8_t* raw = S.raw + (size_t)rs * P.slot_bytes;
             mbar_wait(&S.raw_full[rs], (it / P.n_raw) & 1);
-            if (type == T_Q8_0) {
-                const int kb = p >> 1, as = (kbc + kb) % QG_A_SLOTS;
-                mbar_wait(&S.a_empty[as], (((kbc + kb) / QG_A_SLOTS) & 1) ^ 1);
-                if (!(P.debug & 1)) dq_q80(raw, row, kb, p & 1, smem_u32(S.a + as * QG_A_BYTES));
-                fence_proxy_async_smem(); __syncwarp();
-                if (lane == 0) mbar_arrive_n(&S.a_full[as], 2);
-                kbc += 2;
-            } else if (type == T_Q6_K) {
-                const int n = p >> 1, a0 = (kbc + 2 * n) % QG_A_SLOTS, a1 = (kbc + 2 * n + 1) % QG_A_SLOTS;
-                mbar_wait(&S.a_empty[a0], (((kbc + 2 * n) / QG_A_SLOTS) & 1) ^ 1);
-                mbar_wait(&S.a_empty[a1], (((kbc + 2 * n + 1) / QG_A_SLOTS) & 1) ^ 1);
-                if (!(P.debug & 1)) dq_q6k(raw, row, n, p & 1, smem_u32(S.a + a0 * QG_A_BYTES), smem_u32(S.a + a1 * QG_A_BYTES));
-                fence_proxy_async_smem(); __syncwarp();
-                if (lane == 0) { mbar_arrive_n(&S.a_full[a0], 2); mbar_arrive_n(&S.a_full[a1], 2); }
-                kbc += 4;
-            } else {
-                const int as = (kbc + p) % QG_A_SLOTS;
-                mbar_wait(&S.a_empty[as], (((kbc + p) / QG_A_SLOTS) & 1) ^ 1);
-                if (P.debug & 1) {}
-                else if (type == T_Q4_K) dq_k45<false>(raw, row, p, smem_u32(S.a + as * QG_A_BYTES));
-                else dq_k45<true>(raw, row, p, smem_u32(S.a + as * QG_A_BYTES));
-                fence_proxy_async_smem(); __syncwarp();
-                if (lane == 0) mbar_arrive_n(&S.a_full[as], 4);
-                kbc += 4;
-            }
-            if (lane == 0) mbar_arrive(&S.raw_empty[rs]);       // after __syncwarp: every lane has finished reading the blob
+            uint32_t o[32];
+            if (P.debug & 1) {
+#pragma unroll
+                for (int i = 0; i < 32; i++) o[i] = 0;
+            } else if (type == T_Q8_0) dq_q80(raw, row, p, o);
+            else if (type == T_Q6_K) dq_q6k(raw, row, p >> 1, p & 1, o);
+            else if (type == T_Q4_K) dq_k45<false>(raw, row, p, o);
+            else dq_k45<true>(raw, row, p, o);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&S.raw_empty[rs]);       // every lane has its operands in registers: the blob may be overwritten
+            mbar_wait(&S.a_empty[as], ((it / QG_A_STEPS) & 1) ^ 1);
+            tcgen05_fence_after();
+            const uint32_t a0 = lane_base + as * 128;           // 4 k-blocks x 32 columns per K-step
+            if (type == T_Q6_K) {
+                const int n = p >> 1, h = p & 1;
+                tmem_st_x8(a0 + (2 * n) * 32 + 8 * h, o);          tmem_st_x8(a0 + (2 * n) * 32 + 16 + 8 * h, o + 8);
+                tmem_st_x8(a0 + (2 * n + 1) * 32 + 8 * h, o + 16); tmem_st_x8(a0 + (2 * n + 1) * 32 + 16 + 8 * h, o + 24);
+            } else tmem_st_x32(a0 + p * 32, o);
+            tmem_st_wait();
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&S.a_full[as]);
         }
-    } else {                                           // ===== epilogue warps: TMEM -> C (whole tile) or fp32 partial =====
+    } else {                                           // ===== epilogue warps: TMEM -> C (whole tile) or fp32 partial + last-arriver reduction =====
         const int q = warp & 3;                        // TMEM lane quadrant this warp may read
         int piece = 0, s = s_begin;
         const float scale = P.scale * (1.f / QG_PRESCALE);
         while (s < s_end) {
-            const QSeg& sg = P.seg[qg_seg_of_step(P, s)];
-            const int tl = (s - sg.step0) / sg.ks, k0 = (s - sg.step0) % sg.ks, n_st = min(sg.ks - k0, s_end - s);
+            const int si = qg_seg_of_step(P, s); const QSeg& sg = P.seg[si];
+            const int tl = (s - sg.step0) / P.ks, k0 = (s - sg.step0) % P.ks, n_st = min(P.ks - k0, s_end - s);
             const int buf = piece & 1;
             mbar_wait(&S.acc_full[buf], (piece >> 1) & 1);
             tcgen05_fence_after();
@@ -345,58 +360,34 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
             __syncwarp();
             if (lane == 0) mbar_arrive(&S.acc_empty[buf]);      // registers hold the tile: the accumulator may be reused
             const int n = tl * QG_ROWS + q * 32 + lane;
-            if (n_st == sg.ks) {
+            float* dst = sg.C + n;
+            if (n_st == P.ks || (P.debug & 32)) {
                 if (n < sg.n_rows) {
-                    float* dst = sg.C + n;
 #pragma unroll
                     for (int b = 0; b < QG_NB; b++)
                         if (b < P.B) { float v = __uint_as_float(r[b]) * scale; if (P.mode == 1) v += dst[(size_t)b * P.ldc]; dst[(size_t)b * P.ldc] = v; }
                 }
             } else {
-                const int first_tile = qg_seg_of_step(P, s_begin) == qg_seg_of_step(P, s) && (s_begin - sg.step0) / sg.ks == tl;
-                float* dst = P.ws + ((size_t)(cta * 2 + (first_tile ? 0 : 1)) * QG_NB) * QG_ROWS + q * 32 + lane;
+                // partial K range: park it (slot 0 = the first tile this CTA touches, slot 1 = its last); the row kernel that
+                // consumes C (or qgemm_finish_kernel) sums the parts of the tile in CTA order — see QgSplit in prefill.cuh
+                const int t0 = sg.step0 + tl * P.ks;                           // first global step of the tile
+                float* part = P.ws + ((size_t)(cta * 2 + (s_begin >= t0 ? 0 : 1)) * QG_NB) * QG_ROWS + q * 32 + lane;
 #pragma unroll
-                for (int b = 0; b < QG_NB; b++) if (b < P.B) dst[(size_t)b * QG_ROWS] = __uint_as_float(r[b]);
+                for (int b = 0; b < QG_NB; b++) if (b < P.B) part[(size_t)b * QG_ROWS] = __uint_as_float(r[b]);
             }
             s += n_st; piece++;
         }
     }
     tcgen05_fence_before();
     __syncthreads();
-    if (warp == 2) tcgen05_dealloc(tmem, 2 * QG_NB);
+    if (warp == 2) tcgen05_dealloc(tmem, QG_TMEM_COLS);
 }
 
-// Sum the fp32 partials of every tile whose K range was cut across CTAs (ascending CTA = ascending K: deterministic)
-__global__ void qgemm_fixup_kernel(const __grid_constant__ QGemmParams P, int G) {
-    const int t = blockIdx.x;                          // global tile index
-    int si = 0; while (si + 1 < P.n_seg && t >= P.seg[si + 1].tile0) si++;
-    const QSeg& sg = P.seg[si];
-    const int tl = t - sg.tile0, s0 = sg.step0 + tl * sg.ks, s1 = s0 + sg.ks - 1;
-    const long long T = P.total_steps;
-    const int c_lo = (int)((((long long)s0 + 1) * G + T - 1) / T) - 1, c_hi = (int)((((long long)s1 + 1) * G + T - 1) / T) - 1;
-    if (c_lo == c_hi) return;                          // whole tile in one CTA: written directly
-    const int n = tl * QG_ROWS + threadIdx.x;
-    if (n >= sg.n_rows) return;
-    const float scale = P.scale * (1.f / QG_PRESCALE);
-    constexpr int BB = 8;                              // batch rows per block (blockIdx.y): independent loads in flight
-    const int b0 = blockIdx.y * BB;
-    float acc[BB];
-#pragma unroll
-    for (int i = 0; i < BB; i++) acc[i] = 0.f;
-    for (int c = c_lo; c <= c_hi; c++) {
-        const int cb = (int)((long long)c * T / G), ce = (int)((long long)(c + 1) * T / G);
-        if (cb == ce) continue;                                             // CTA without work (fewer steps than CTAs)
-        const int slot = cb >= s0 ? 0 : 1;                                  // slot 0: the tile is the first one CTA c touches
-        const float* src = P.ws + ((size_t)(c * 2 + slot) * QG_NB + b0) * QG_ROWS + threadIdx.x;
-#pragma unroll
-        for (int i = 0; i < BB; i++) if (b0 + i < P.B) acc[i] += src[(size_t)i * QG_ROWS];
-    }
-#pragma unroll
-    for (int i = 0; i < BB; i++) {
-        if (b0 + i >= P.B) break;
-        float v = acc[i] * scale; float* dst = sg.C + (size_t)(b0 + i) * P.ldc + n;
-        if (P.mode == 1) v += *dst;
-        *dst = v;
+// Completes C from the partials for callers that have no consuming row kernel (the test entry): one thread per 4 columns
+__global__ void qgemm_finish_kernel(const __grid_constant__ QgSplit sp, float* __restrict__ C, int ldc, int B, int N) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)B * N; i += (long long)gridDim.x * blockDim.x) {
+        const int b = (int)(i / N), n = (int)(i % N);
+        float v = C[(size_t)b * ldc + n]; qg_gather<1>(sp, b, n, &v); C[(size_t)b * ldc + n] = v;
     }
 }
 
