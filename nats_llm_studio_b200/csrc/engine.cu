@@ -623,12 +623,13 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
     auto deq = [&](const Matrix& m, __nv_bfloat16* dst) {
         dequant_bf16_kernel<<<nblk(m.n_rows * (long long)m.K / 2), 256, 0, E.stream>>>(m.w, m.type, m.n_rows, m.K, dst); E.launches++;
     };
+    const int rms_threads = std::min(1024, std::max(128, (D / 4 + 31) / 32 * 32));     // one float4 per thread where the row allows
     int rc; QgSplit sp{}, none{};                                    // sp: partial tiles the next row kernel must complete
     embed_rows_kernel<<<nblk((long long)M * D), 256, 0, E.stream>>>(tok_embd.w, tok_embd.type, D, d_toks, M, emb_scale, pf_H); E.launches++;
     for (int l = 0; l < n_layer; l++) {
         Layer& L = layers[l];
         const __nv_bfloat16 *wqkv = L.b_qkv, *wo = L.b_o, *wgu = L.b_gu, *wd = L.b_d;
-        rmsnorm_rows_kernel<<<M, 256, 0, E.stream>>>(pf_H, L.attn_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
+        rmsnorm_rows_kernel<<<M, rms_threads, 0, E.stream>>>(pf_H, L.attn_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
         if (q) {
             const QMat qkv[3] = {{&L.wq, pf_Y}, {&L.wk, pf_Y + QD}, {&L.wv, pf_Y + QD + KVD}};
             if ((rc = qgemm(E, qkv, 3, pf_X, M, D, W3, 0, 1.f, false, &sp))) return rc;
@@ -639,7 +640,7 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
         rope_kv_rows_kernel<<<nblk((long long)M * W3 / 2), 256, 0, E.stream>>>(pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, inv_freq, kv, pf_Q, sp); E.launches++; sp = none;
         {
             const int G = n_head / n_head_kv; const dim3 ag(M * n_head_kv);
-#define B200_ATTN(HD_, G_) attn_rows_kernel<HD_, G_><<<ag, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q)
+#define B200_ATTN(HD_, G_) attn_rows_kernel<HD_, G_><<<ag, ATTN_WARPS * 32, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q)
             if (head_dim == 128 && G == 4) B200_ATTN(128, 4); else if (head_dim == 128 && G == 8) B200_ATTN(128, 8);
             else if (head_dim == 128 && G == 2) B200_ATTN(128, 2); else if (head_dim == 128 && G == 1) B200_ATTN(128, 1);
             else if (head_dim == 64 && G == 4) B200_ATTN(64, 4); else if (head_dim == 64 && G == 8) B200_ATTN(64, 8);
@@ -655,7 +656,7 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
             if ((rc = gemm_bf16(E, pf_X, wo, pf_H, M, D, QD, D, 1, rs))) return rc;
         }
         if (l == n_layer - 1 && !want_logits) break;                  // KV fill only: the last layer's FFN feeds nothing
-        rmsnorm_rows_kernel<<<M, 256, 0, E.stream>>>(pf_H, L.ffn_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
+        rmsnorm_rows_kernel<<<M, rms_threads, 0, E.stream>>>(pf_H, L.ffn_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
         if (q) { const QMat gu{&L.wgu, pf_Y}; if ((rc = qgemm(E, &gu, 1, pf_X, M, D, 2 * F, 0, 1.f, false, &sp))) return rc; }
         else {
             if (!bf16_ready) { deq(L.wgu, pf_W); wgu = pf_W; }
@@ -670,7 +671,7 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
     }
     if (want_logits) {
         const int ldv = (n_vocab + 3) & ~3; const float ls = logit_scale != 0.f ? 1.f / logit_scale : 1.f;
-        rmsnorm_rows_kernel<<<M, 256, 0, E.stream>>>(pf_H, out_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
+        rmsnorm_rows_kernel<<<M, rms_threads, 0, E.stream>>>(pf_H, out_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
         if (q) { const QMat o{&out_w, bt_logits}; if ((rc = qgemm(E, &o, 1, pf_X, M, D, ldv, 0, ls, true, &sp))) return rc; sp = none; }
         else {
             if (!bf16_ready) return fail(B200_ERR_STATE, "logits through the dense path need the bf16 weight cache");

@@ -227,12 +227,12 @@ __global__ void embed_rows_kernel(const uint8_t* __restrict__ embd, int type, in
 
 // X[m][:] = 16-bit(rmsnorm(H[m]) * w); one block per row.  With a split producer (sp.ws) H[m] is first completed from
 // the partials of the residual GEMM that precedes the norm and written back.
-__global__ void __launch_bounds__(256) rmsnorm_rows_kernel(float* __restrict__ H, const float* __restrict__ w, int D, int M, float eps, __nv_bfloat16* __restrict__ X, bool perm,
+__global__ void __launch_bounds__(1024) rmsnorm_rows_kernel(float* __restrict__ H, const float* __restrict__ w, int D, int M, float eps, __nv_bfloat16* __restrict__ X, bool perm,
                                                            const __grid_constant__ QgSplit sp) {
-    __shared__ float red[8];
-    const int m = blockIdx.x, tid = threadIdx.x;
+    __shared__ float red[32];
+    const int m = blockIdx.x, tid = threadIdx.x, nth = blockDim.x;
     float* h = H + (size_t)m * D; float ss = 0.f;
-    for (int i = tid * 4; i < D; i += 1024) {
+    for (int i = tid * 4; i < D; i += nth * 4) {
         float4 v = *(const float4*)(h + i);
         if (sp.ws) { float t[4] = {v.x, v.y, v.z, v.w}; qg_gather<4>(sp, m, i, t); v = make_float4(t[0], t[1], t[2], t[3]); *(float4*)(h + i) = v; }
         ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
@@ -241,10 +241,9 @@ __global__ void __launch_bounds__(256) rmsnorm_rows_kernel(float* __restrict__ H
     if ((tid & 31) == 0) red[tid >> 5] = ss;
     __syncthreads();
     ss = 0.f;
-#pragma unroll
-    for (int i = 0; i < 8; i++) ss += red[i];                       // same order in every thread
+    for (int i = 0; i < (nth >> 5); i++) ss += red[i];              // same order in every thread
     const float rs = rsqrtf(ss / (float)D + eps);
-    for (int i = tid * 4; i < D; i += 1024) {                       // each thread re-reads exactly what it wrote above
+    for (int i = tid * 4; i < D; i += nth * 4) {                     // each thread re-reads exactly what it wrote above
         const float4 v = *(const float4*)(h + i), g = *(const float4*)(w + i);
         const float a = v.x * rs * g.x, b = v.y * rs * g.y, c = v.z * rs * g.z, d = v.w * rs * g.w;
         *(uint2*)(X + (size_t)m * D + i) = perm ? make_uint2(pack16x2(a, c, true), pack16x2(b, d, true)) : make_uint2(pack16x2(a, b, false), pack16x2(c, d, false));
@@ -315,41 +314,48 @@ __global__ void attn_prefill_kernel(const __nv_bfloat16* __restrict__ Q, int M, 
 }
 
 // Attention for M rows over the paged fp16 KV cache, one block per (row, kv head): the G query heads that share the kv
-// head are served from one pass over K and V.  Each of the 4 warps takes every fourth 32-position chunk; scores are
+// head are served from one pass over K and V.  Each of the 8 warps takes every eighth 32-position chunk; scores are
 // computed one position per lane (no shuffles in the dot products), probabilities are broadcast by shuffle for the
-// P.V accumulation (one output-dim slice per lane), and the four warps' online-softmax states are merged in shared memory.
+// P.V accumulation (one output-dim slice per lane, eight V rows in flight), and the warps' online-softmax states are
+// merged in shared memory.
+constexpr int ATTN_WARPS = 8;
+__device__ __forceinline__ float2 h2_to_f2(uint32_t u) { return __half22float2(*reinterpret_cast<const __half2*>(&u)); }
 template <int HD, int G>
-__global__ void __launch_bounds__(128) attn_rows_kernel(const __nv_bfloat16* __restrict__ Q, int M, RowMap rm, int layer, int n_head, int n_head_kv,
-                                                        float kq_scale, KvLayout kv, __nv_bfloat16* __restrict__ O, bool perm) {
-    constexpr int DPL = HD / 32;
+__global__ void __launch_bounds__(ATTN_WARPS * 32, 2) attn_rows_kernel(const __nv_bfloat16* __restrict__ Q, int M, RowMap rm, int layer, int n_head, int n_head_kv,
+                                                                   float kq_scale, KvLayout kv, __nv_bfloat16* __restrict__ O, bool perm) {
+    constexpr int DPL = HD / 32, NW = ATTN_WARPS;
     __shared__ __align__(16) float sq[G][HD];
-    __shared__ float sm_m[4][G], sm_l[4][G];
-    __shared__ float sm_acc[4][G][HD];
+    __shared__ float sm_m[NW][G], sm_l[NW][G];
+    __shared__ float sm_acc[NW][G][HD];
     const int m = blockIdx.x / n_head_kv, kvh = blockIdx.x % n_head_kv, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int n_ctx = rm.p(m) + 1, slot = rm.s(m);
-    for (int i = tid; i < G * HD; i += 128) { const int g = i / HD, d = i % HD; sq[g][d] = __bfloat162float(Q[(size_t)m * n_head * HD + (kvh * G + g) * HD + d]) * kq_scale; }
+    for (int i = tid; i < G * HD; i += NW * 32) { const int g = i / HD, d = i % HD; sq[g][d] = __bfloat162float(Q[(size_t)m * n_head * HD + (kvh * G + g) * HD + d]) * kq_scale; }
     __syncthreads();
     float mx[G], l[G], acc[G][DPL];
 #pragma unroll
     for (int g = 0; g < G; g++) { mx[g] = -INFINITY; l[g] = 0.f;
 #pragma unroll
         for (int i = 0; i < DPL; i++) acc[g][i] = 0.f; }
-    for (int p0 = warp * 32; p0 < n_ctx; p0 += 128) {
+    for (int p0 = warp * 32; p0 < n_ctx; p0 += NW * 32) {
         const int p = p0 + lane; const bool ok = p < n_ctx;
         float s[G];
 #pragma unroll
         for (int g = 0; g < G; g++) s[g] = 0.f;
-        if (ok) {
-            const __half* kp = kv.at_slot(slot, layer, 0, kvh, p);
-#pragma unroll 4
-            for (int j = 0; j < HD / 8; j++) {
-                const uint4 kk = *(const uint4*)(kp + 8 * j);
-                const float2 k0 = __half22float2(*(const __half2*)&kk.x), k1 = __half22float2(*(const __half2*)&kk.y),
-                             k2 = __half22float2(*(const __half2*)&kk.z), k3 = __half22float2(*(const __half2*)&kk.w);
+        {
+            const __half* kp = kv.at_slot(slot, layer, 0, kvh, ok ? p : n_ctx - 1);      // clamped: masked below
+#pragma unroll 1
+            for (int j0 = 0; j0 < HD / 8; j0 += 8) {
+                uint4 kk[8];
 #pragma unroll
-                for (int g = 0; g < G; g++) {
-                    const float4 qa = *(const float4*)&sq[g][8 * j], qb = *(const float4*)&sq[g][8 * j + 4];
-                    s[g] += qa.x * k0.x + qa.y * k0.y + qa.z * k1.x + qa.w * k1.y + qb.x * k2.x + qb.y * k2.y + qb.z * k3.x + qb.w * k3.y;
+                for (int j = 0; j < 8; j++) kk[j] = *(const uint4*)(kp + 8 * (j0 + j));
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const float2 k0 = h2_to_f2(kk[j].x), k1 = h2_to_f2(kk[j].y), k2 = h2_to_f2(kk[j].z), k3 = h2_to_f2(kk[j].w);
+#pragma unroll
+                    for (int g = 0; g < G; g++) {
+                        const float4 qa = *(const float4*)&sq[g][8 * (j0 + j)], qb = *(const float4*)&sq[g][8 * (j0 + j) + 4];
+                        s[g] += qa.x * k0.x + qa.y * k0.y + qa.z * k1.x + qa.w * k1.y + qb.x * k2.x + qb.y * k2.y + qb.z * k3.x + qb.w * k3.y;
+                    }
                 }
             }
         }
@@ -367,19 +373,30 @@ __global__ void __launch_bounds__(128) attn_rows_kernel(const __nv_bfloat16* __r
             for (int i = 0; i < DPL; i++) acc[g][i] *= corr;
             mx[g] = mn;
         }
-        const int np = min(32, n_ctx - p0);
-        const __half* vbase = nullptr;
-        for (int pp = 0; pp < np; pp++) {
-            if ((pp & 15) == 0) vbase = kv.at_slot(slot, layer, 1, kvh, p0 + pp) + lane * DPL;      // 16 positions of a page are contiguous
-            const __half* vp = vbase + (size_t)(pp & 15) * HD;
-            float v[DPL];
-            if (DPL == 4) { const uint2 vv = *(const uint2*)vp; const float2 a = __half22float2(*(const __half2*)&vv.x), b = __half22float2(*(const __half2*)&vv.y); v[0] = a.x; v[1] = a.y; v[2 % DPL] = b.x; v[3 % DPL] = b.y; }
-            else { const float2 a = __half22float2(*(const __half2*)vp); v[0] = a.x; v[1] = a.y; }
+        // P.V: masked positions carry probability 0, so their (clamped, valid) V rows may be read unconditionally
+        const int last = n_ctx - 1 - p0;                                           // >= 0
+        const __half* vb0 = kv.at_slot(slot, layer, 1, kvh, p0) + lane * DPL;      // 16 positions of a page are contiguous
+        const __half* vb1 = last >= 16 ? kv.at_slot(slot, layer, 1, kvh, p0 + 16) + lane * DPL : vb0;
 #pragma unroll
-            for (int g = 0; g < G; g++) {
-                const float pr = __shfl_sync(0xffffffffu, pe[g], pp);
+        for (int pp0 = 0; pp0 < 32; pp0 += 8) {
+            if (pp0 > last) break;
+            uint2 vv[8];
 #pragma unroll
-                for (int i = 0; i < DPL; i++) acc[g][i] += pr * v[i];
+            for (int j = 0; j < 8; j++) {
+                const int pp = min(pp0 + j, last);
+                const __half* vp = (pp < 16 ? vb0 : vb1) + (size_t)(pp & 15) * HD;
+                if (DPL == 4) vv[j] = *(const uint2*)vp; else { vv[j].x = *(const uint32_t*)vp; vv[j].y = 0; }
+            }
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const float2 a = h2_to_f2(vv[j].x), b = h2_to_f2(vv[j].y);
+                const float v[4] = {a.x, a.y, b.x, b.y};
+#pragma unroll
+                for (int g = 0; g < G; g++) {
+                    const float pr = __shfl_sync(0xffffffffu, pe[g], pp0 + j);
+#pragma unroll
+                    for (int i = 0; i < DPL; i++) acc[g][i] += pr * v[i];
+                }
             }
         }
     }
@@ -390,14 +407,14 @@ __global__ void __launch_bounds__(128) attn_rows_kernel(const __nv_bfloat16* __r
         for (int i = 0; i < DPL; i++) sm_acc[warp][g][lane * DPL + i] = acc[g][i];
     }
     __syncthreads();
-    for (int idx = tid; idx < G * HD; idx += 128) {
+    for (int idx = tid; idx < G * HD; idx += NW * 32) {
         const int g = idx / HD, d = idx % HD;
         float mm = sm_m[0][g];
 #pragma unroll
-        for (int w = 1; w < 4; w++) mm = fmaxf(mm, sm_m[w][g]);
+        for (int w = 1; w < NW; w++) mm = fmaxf(mm, sm_m[w][g]);
         float num = 0.f, den = 0.f;
 #pragma unroll
-        for (int w = 0; w < 4; w++) { const float e = __expf(sm_m[w][g] - mm); num += sm_acc[w][g][d] * e; den += sm_l[w][g] * e; }
+        for (int w = 0; w < NW; w++) { const float e = __expf(sm_m[w][g] - mm); num += sm_acc[w][g][d] * e; den += sm_l[w][g] * e; }
         ((unsigned short*)O)[(size_t)m * n_head * HD + (kvh * G + g) * HD + (perm ? kperm4(d) : d)] = pack16(num / den, perm);
     }
 }
@@ -407,7 +424,13 @@ __global__ void argmax_rows_kernel(const float* __restrict__ logits, int V, int 
     __shared__ float sv[32]; __shared__ int si[32];
     const float* row = logits + (size_t)blockIdx.x * ld;
     float bv = -INFINITY; int bi = 0x7fffffff;
-    for (int i = threadIdx.x; i < V; i += blockDim.x) { const float v = row[i]; if (v > bv) { bv = v; bi = i; } }
+    const int V4 = V & ~3;                                           // rows start 16-byte aligned (ld % 4 == 0)
+#pragma unroll 4
+    for (int i = threadIdx.x * 4; i < V4; i += blockDim.x * 4) {
+        const float4 v = *(const float4*)(row + i);
+        if (v.x > bv) { bv = v.x; bi = i; } if (v.y > bv) { bv = v.y; bi = i + 1; } if (v.z > bv) { bv = v.z; bi = i + 2; } if (v.w > bv) { bv = v.w; bi = i + 3; }
+    }
+    for (int i = V4 + threadIdx.x; i < V; i += blockDim.x) { const float v = row[i]; if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; } }
     for (int o = 16; o; o >>= 1) { const float v = __shfl_xor_sync(0xffffffffu, bv, o); const int ix = __shfl_xor_sync(0xffffffffu, bi, o); if (v > bv || (v == bv && ix < bi)) { bv = v; bi = ix; } }
     if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = bv; si[threadIdx.x >> 5] = bi; }
     __syncthreads();

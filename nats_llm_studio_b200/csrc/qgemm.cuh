@@ -236,9 +236,9 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
     }
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
-        for (int i = 0; i < P.n_raw; i++) { mbar_init(&S.raw_full[i], 1); mbar_init(&S.raw_empty[i], QG_DQ_WARPS); }
+        for (int i = 0; i < P.n_raw; i++) { mbar_init(&S.raw_full[i], 1); mbar_init(&S.raw_empty[i], QG_DQ_WARPS / 2); }
         for (int i = 0; i < QG_X_STEPS; i++) { mbar_init(&S.x_full[i], 1); mbar_init(&S.x_empty[i], 1); }
-        for (int i = 0; i < QG_A_STEPS; i++) { mbar_init(&S.a_full[i], QG_DQ_WARPS); mbar_init(&S.a_empty[i], 1); }
+        for (int i = 0; i < QG_A_STEPS; i++) { mbar_init(&S.a_full[i], QG_DQ_WARPS / 2); mbar_init(&S.a_empty[i], 1); }
         for (int i = 0; i < 2; i++) { mbar_init(&S.acc_full[i], 1); mbar_init(&S.acc_empty[i], 4); }
         fence_barrier_init();
     }
@@ -311,32 +311,36 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
             }
         }
     } else if (warp < QG_FIRST_EPI) {                  // ===== dequant warps: raw blob -> fp16 A operand in tensor memory =====
-        const int row = (warp & 3) * 32 + lane, p = (warp - QG_FIRST_DQ) >> 2;      // a warp may only touch the TMEM lanes of quadrant warp % 4
+        // Two groups of 8 warps take alternate K-steps, so that one group computes while the other waits on its
+        // barriers / tensor-memory stores (all warps in lockstep would expose every latency once per step).
+        // In a group, warp (slab, half) expands rows 32*slab.. of portions 2*half and 2*half+1 of the step.
+        const int idx = warp - QG_FIRST_DQ, grp = idx >> 3, half = (idx & 7) >> 2, row = (warp & 3) * 32 + lane;   // TMEM lanes of quadrant warp % 4 only
         const uint32_t lane_base = tmem + QG_TMEM_A0 + ((uint32_t)((warp & 3) * 32) << 16);
-        int it = 0;
-        for (int s = s_begin; s < s_end; s++, it++) {
-            const int type = P.seg[qg_seg_of_step(P, s)].type;
+        for (int it = grp; s_begin + it < s_end; it += 2) {
+            const int type = P.seg[qg_seg_of_step(P, s_begin + it)].type;
             const int rs = it % P.n_raw, as = it % QG_A_STEPS;
             const uint8_t* raw = S.raw + (size_t)rs * P.slot_bytes;
-            mbar_wait(&S.raw_full[rs], (it / P.n_raw) & 1);
-            uint32_t o[32];
-            if (P.debug & 1) {
-#pragma unroll
-                for (int i = 0; i < 32; i++) o[i] = 0;
-            } else if (type == T_Q8_0) dq_q80(raw, row, p, o);
-            else if (type == T_Q6_K) dq_q6k(raw, row, p >> 1, p & 1, o);
-            else if (type == T_Q4_K) dq_k45<false>(raw, row, p, o);
-            else dq_k45<true>(raw, row, p, o);
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&S.raw_empty[rs]);       // every lane has its operands in registers: the blob may be overwritten
-            mbar_wait(&S.a_empty[as], ((it / QG_A_STEPS) & 1) ^ 1);
-            tcgen05_fence_after();
             const uint32_t a0 = lane_base + as * 128;           // 4 k-blocks x 32 columns per K-step
-            if (type == T_Q6_K) {
-                const int n = p >> 1, h = p & 1;
-                tmem_st_x8(a0 + (2 * n) * 32 + 8 * h, o);          tmem_st_x8(a0 + (2 * n) * 32 + 16 + 8 * h, o + 8);
-                tmem_st_x8(a0 + (2 * n + 1) * 32 + 8 * h, o + 16); tmem_st_x8(a0 + (2 * n + 1) * 32 + 16 + 8 * h, o + 24);
-            } else tmem_st_x32(a0 + p * 32, o);
+            mbar_wait(&S.raw_full[rs], (it / P.n_raw) & 1);
+#pragma unroll
+            for (int pp = 0; pp < 2; pp++) {
+                const int p = 2 * half + pp;
+                uint32_t o[32];
+                if (P.debug & 1) {
+#pragma unroll
+                    for (int i = 0; i < 32; i++) o[i] = 0;
+                } else if (type == T_Q8_0) dq_q80(raw, row, p, o);
+                else if (type == T_Q6_K) dq_q6k(raw, row, p >> 1, p & 1, o);
+                else if (type == T_Q4_K) dq_k45<false>(raw, row, p, o);
+                else dq_k45<true>(raw, row, p, o);
+                if (pp == 0) { mbar_wait(&S.a_empty[as], ((it / QG_A_STEPS) & 1) ^ 1); tcgen05_fence_after(); }
+                else { __syncwarp(); if (lane == 0) mbar_arrive(&S.raw_empty[rs]); }     // every lane has its operands in registers
+                if (type == T_Q6_K) {
+                    const int n = p >> 1, h = p & 1;
+                    tmem_st_x8(a0 + (2 * n) * 32 + 8 * h, o);          tmem_st_x8(a0 + (2 * n) * 32 + 16 + 8 * h, o + 8);
+                    tmem_st_x8(a0 + (2 * n + 1) * 32 + 8 * h, o + 16); tmem_st_x8(a0 + (2 * n + 1) * 32 + 16 + 8 * h, o + 24);
+                } else tmem_st_x32(a0 + p * 32, o);
+            }
             tmem_st_wait();
             tcgen05_fence_before();
             __syncwarp();
