@@ -17,7 +17,7 @@ struct Request {
     std::shared_ptr<Model> m; std::vector<int32_t> toks; b200_sampling s; uint64_t id; std::atomic<bool> cancelled{false};
     std::chrono::steady_clock::time_point t_submit;
 };
-struct Seq { std::shared_ptr<Request> r; int slot, pos, cur_tok, n_gen = 0; float ttft_ms = 0; std::chrono::steady_clock::time_point t_first; };
+struct Seq { std::shared_ptr<Request> r; int slot = 0, n_fed = 0, pos = 0, cur_tok = 0, n_gen = 0; bool decoding = false; float ttft_ms = 0; std::chrono::steady_clock::time_point t_first; };
 struct Scheduler {
     std::mutex mu; std::condition_variable cv_req, cv_ev;
     std::deque<std::shared_ptr<Request>> q; std::deque<b200_event> ev;
@@ -61,7 +61,12 @@ struct Scheduler {
             if (max_seqs <= 1) { while (!waiting.empty()) { auto r = waiting.front(); waiting.pop_front(); run_single(r); } continue; }
             std::vector<b200_event> out; std::vector<uint64_t> done;
             if (active.empty()) { free_slots.clear(); for (int i = max_seqs - 1; i >= 0; i--) free_slots.push_back(i); cur.reset(); }
-            // ---- admit
+            auto finish = [&](Seq& s, int kind, int reason) {
+                b200_event f{}; f.req_id = s.r->id; f.kind = kind; f.finish_reason = reason; f.n_prompt = (int)s.r->toks.size(); f.n_generated = s.n_gen; f.ttft_ms = s.ttft_ms;
+                f.decode_ms = s.n_gen ? (float)ms_since(s.t_first) : 0.f;
+                out.push_back(f); done.push_back(s.r->id); free_slots.push_back(s.slot);
+            };
+            // ---- admit: a waiting request gets a sequence slot; its prompt is ingested in chunks below
             while (!waiting.empty() && !free_slots.empty() && (!cur || waiting.front()->m == cur)) {
                 auto r = waiting.front(); waiting.pop_front();
                 b200_event e{}; e.req_id = r->id; e.n_prompt = (int)r->toks.size();
@@ -69,34 +74,53 @@ struct Scheduler {
                 const int n = (int)r->toks.size();
                 bool bad = n < 1 || n + 1 > max_ctx;
                 for (int t : r->toks) bad = bad || t < 0 || t >= r->m->n_vocab;
-                int rc = B200_OK; const int slot = free_slots.back();
-                if (!bad) { std::lock_guard<std::mutex> lk(r->m->run_mu); rc = r->m->prefill_slot(slot, r->toks.data(), n - 1, 0); }
-                if (bad || rc != B200_OK) { e.kind = B200_EV_ERROR; e.finish_reason = bad ? B200_ERR_INVALID : rc; out.push_back(e); done.push_back(r->id); continue; }
-                free_slots.pop_back(); cur = r->m;
-                Seq s; s.r = r; s.slot = slot; s.pos = n - 1; s.cur_tok = r->toks[n - 1]; active.push_back(s);
+                if (bad) { e.kind = B200_EV_ERROR; e.finish_reason = B200_ERR_INVALID; out.push_back(e); done.push_back(r->id); continue; }
+                cur = r->m;
+                Seq s; s.r = r; s.slot = free_slots.back(); free_slots.pop_back();
+                if (n == 1) { s.decoding = true; s.cur_tok = r->toks[0]; s.pos = 0; }
+                active.push_back(s);
             }
             if (active.empty()) { push_events(out, done); continue; }
-            // ---- one batched step for every active sequence
-            const int B = (int)active.size();
+            int rc = B200_OK;
+            // ---- one prompt chunk: up to PREFILL_CHUNK rows taken, in arrival order, from the sequences still ingesting
+            {
+                std::vector<int32_t> toks, slots, pos;
+                for (Seq& s : active) {
+                    if (s.decoding || s.r->cancelled) continue;
+                    const int n = (int)s.r->toks.size(), k = std::min(n - 1 - s.n_fed, Model::PREFILL_CHUNK - (int)toks.size());
+                    for (int i = 0; i < k; i++) { toks.push_back(s.r->toks[s.n_fed + i]); slots.push_back(s.slot); pos.push_back(s.n_fed + i); }
+                    s.n_fed += k;
+                    if (s.n_fed == n - 1) { s.decoding = true; s.cur_tok = s.r->toks[n - 1]; s.pos = n - 1; }
+                    if ((int)toks.size() == Model::PREFILL_CHUNK) break;
+                }
+                if (!toks.empty()) { std::lock_guard<std::mutex> lk(cur->run_mu); rc = cur->prefill_rows(toks.data(), slots.data(), pos.data(), (int)toks.size()); }
+            }
+            // ---- one batched decode step for every sequence whose prompt is in the cache
+            std::vector<int> idx;
+            for (int i = 0; i < (int)active.size(); i++) if (active[i].decoding && !active[i].r->cancelled) idx.push_back(i);
+            const int B = (int)idx.size();
             std::vector<int32_t> toks(B), slots(B), pos(B), next(B);
-            for (int i = 0; i < B; i++) { toks[i] = active[i].cur_tok; slots[i] = active[i].slot; pos[i] = active[i].pos; }
-            int rc; { std::lock_guard<std::mutex> lk(cur->run_mu); rc = cur->batch_step(toks.data(), slots.data(), pos.data(), B, next.data()); }
-            std::vector<Seq> keep;
-            for (int i = 0; i < B; i++) {
-                Seq& s = active[i]; auto& r = s.r;
-                b200_event e{}; e.req_id = r->id; e.n_prompt = (int)r->toks.size();
-                if (rc != B200_OK) { e.kind = B200_EV_ERROR; e.finish_reason = rc; out.push_back(e); done.push_back(r->id); free_slots.push_back(s.slot); continue; }
-                s.n_gen++; s.pos++; s.cur_tok = next[i];
+            for (int j = 0; j < B; j++) { const Seq& s = active[idx[j]]; toks[j] = s.cur_tok; slots[j] = s.slot; pos[j] = s.pos; }
+            if (rc == B200_OK && B > 0) { std::lock_guard<std::mutex> lk(cur->run_mu); rc = cur->batch_step(toks.data(), slots.data(), pos.data(), B, next.data()); }
+            if (rc != B200_OK) {                                   // engine failure: every active request fails
+                for (Seq& s : active) finish(s, B200_EV_ERROR, rc);
+                active.clear(); push_events(out, done); continue;
+            }
+            for (int j = 0; j < B; j++) {
+                Seq& s = active[idx[j]]; auto& r = s.r;
+                s.n_gen++; s.pos++; s.cur_tok = next[j];
                 if (s.n_gen == 1) { s.ttft_ms = (float)ms_since(r->t_submit); s.t_first = std::chrono::steady_clock::now(); }
-                e.kind = B200_EV_TOKEN; e.token = next[i]; e.n_generated = s.n_gen; e.ttft_ms = s.ttft_ms; out.push_back(e);
+                b200_event e{}; e.req_id = r->id; e.n_prompt = (int)r->toks.size(); e.kind = B200_EV_TOKEN; e.token = next[j]; e.n_generated = s.n_gen; e.ttft_ms = s.ttft_ms; out.push_back(e);
+            }
+            std::vector<Seq> keep;
+            for (Seq& s : active) {
+                auto& r = s.r;
                 const int max_tokens = r->s.max_tokens > 0 ? r->s.max_tokens : 256;
-                const bool stopped = !r->s.ignore_eos && (next[i] == r->m->eos || next[i] == r->s.stop_token);
-                if (stopped || s.n_gen >= max_tokens || s.pos + 1 >= max_ctx || r->cancelled) {
-                    b200_event f{}; f.req_id = r->id; f.kind = B200_EV_FINISH; f.n_prompt = e.n_prompt; f.n_generated = s.n_gen; f.ttft_ms = s.ttft_ms;
-                    f.decode_ms = (float)ms_since(s.t_first);
-                    f.finish_reason = r->cancelled ? B200_FINISH_CANCELLED : stopped ? B200_FINISH_STOP : B200_FINISH_LENGTH;
-                    out.push_back(f); done.push_back(r->id); free_slots.push_back(s.slot);
-                } else keep.push_back(s);
+                const bool stopped = s.n_gen > 0 && !r->s.ignore_eos && (s.cur_tok == r->m->eos || s.cur_tok == r->s.stop_token);
+                if (r->cancelled) finish(s, B200_EV_FINISH, B200_FINISH_CANCELLED);
+                else if (stopped) finish(s, B200_EV_FINISH, B200_FINISH_STOP);
+                else if (s.n_gen >= max_tokens || (s.decoding && s.pos + 1 >= max_ctx)) finish(s, B200_EV_FINISH, B200_FINISH_LENGTH);
+                else keep.push_back(s);
             }
             active.swap(keep);
             push_events(out, done);

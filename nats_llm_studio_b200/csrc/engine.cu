@@ -609,7 +609,7 @@ int Model::ensure_tile_weights() {
 
 // One pass of the dense path over M activation rows (a prompt chunk of one sequence, or one row per sequence of a
 // decode batch).  want_logits: also run the last layer's FFN, the final norm and the lm_head into bt_logits[M][V].
-int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits) {
+int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits, bool q) {
     Engine& E = engine();
     const int D = n_embd, F = n_ff, QD = n_head * head_dim, KVD = n_head_kv * head_dim, W3 = QD + 2 * KVD;
     const float rs = res_scale != 0.f ? res_scale : 1.f, kq = attn_scale != 0.f ? attn_scale : 1.0f / std::sqrt((float)head_dim);
@@ -617,8 +617,8 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
     RowMap rm{d_pos, d_slot, pos0, slot0};
     // few rows (a decode batch): weights stay quantised and are expanded inside the GEMM; many rows (a prompt chunk):
     // expand to bf16 once per chunk (or use the cache) and run the dense tensor-core GEMM
-    // (the choice depends on the engine configuration and M only, never on what ran before: results are reproducible)
-    const bool q = use_qgemm(M);
+    // (q is chosen by the caller from the KIND of pass — decode batch or prompt ingestion — never from what ran before
+    // or how rows were packed: a request's result does not depend on the load it ran under)
     if (q) { if (int rc0 = ensure_tile_weights()) return rc0; }
     auto deq = [&](const Matrix& m, __nv_bfloat16* dst) {
         dequant_bf16_kernel<<<nblk(m.n_rows * (long long)m.K / 2), 256, 0, E.stream>>>(m.w, m.type, m.n_rows, m.K, dst); E.launches++;
@@ -691,10 +691,39 @@ int Model::prefill_slot(int slot, const int32_t* toks, int n, int pos0) {
     for (int c0 = 0; c0 < n; c0 += PREFILL_CHUNK) {
         const int M = std::min(PREFILL_CHUNK, n - c0);
         CK(cudaMemcpyAsync(pf_toks, toks + c0, (size_t)M * 4, cudaMemcpyHostToDevice, E.stream));
-        if (int rc = dense_rows(pf_toks, M, nullptr, nullptr, pos0 + c0, slot, false)) return rc;
+        if (int rc = dense_rows(pf_toks, M, nullptr, nullptr, pos0 + c0, slot, false, false)) return rc;
     }
     CK(cudaStreamSynchronize(E.stream));                              // toks is caller memory
     return B200_OK;
+}
+
+// Ingest M rows that may belong to several sequences (row i: token toks[i] of slot slots[i] at position pos[i]); rows of
+// one sequence must appear in position order.  The continuous-batching scheduler packs waiting prompts into such chunks.
+int Model::prefill_rows(const int32_t* toks, const int32_t* slots, const int32_t* pos, int M) {
+    Engine& E = engine();
+    if (M < 1 || M > PREFILL_CHUNK) return fail(B200_ERR_INVALID, "prefill chunk size out of range");
+    for (int i = 0; i < M; i++) if (toks[i] < 0 || toks[i] >= n_vocab || slots[i] < 0 || slots[i] >= E.max_seqs || pos[i] < 0 || pos[i] >= E.max_ctx) return fail(B200_ERR_INVALID, "bad prefill row");
+    if (int rc = ensure_prefill_buffers()) return rc;
+    if (E.max_seqs > 1) maybe_bf16_cache();
+    const int Mc = PREFILL_CHUNK;
+    CK(cudaMemcpyAsync(pf_toks, toks, (size_t)M * 4, cudaMemcpyHostToDevice, E.stream));
+    CK(cudaMemcpyAsync(pf_toks + Mc, pos, (size_t)M * 4, cudaMemcpyHostToDevice, E.stream));
+    CK(cudaMemcpyAsync(pf_toks + 2 * Mc, slots, (size_t)M * 4, cudaMemcpyHostToDevice, E.stream));
+    if (int rc = dense_rows(pf_toks, M, pf_toks + Mc, pf_toks + 2 * Mc, 0, 0, false, false)) return rc;
+    CK(cudaStreamSynchronize(E.stream));
+    return B200_OK;
+}
+
+// A serving engine (max_seqs > 1) ingests prompts all the time: keep bf16 copies of the matrices when HBM has room
+// (8B: 16 GB) instead of expanding them for every chunk.  Tried once; without room the per-chunk expansion stays.
+void Model::maybe_bf16_cache() {
+    if (bf16_ready || bf16_tried) return;
+    bf16_tried = true;
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return;
+    const size_t D = n_embd, F = n_ff, QD = (size_t)n_head * head_dim, KVD = (size_t)n_head_kv * head_dim;
+    const size_t need = 2 * ((size_t)n_layer * ((QD + 2 * KVD) * D + D * QD + 2 * F * D + D * F) + (size_t)n_vocab * D);
+    if (free_b > need + ((size_t)8 << 30)) { if (ensure_bf16_weights() != B200_OK) cudaGetLastError(); }
 }
 
 int Model::prefill(const int32_t* toks, int n) {                      // batch-1 path: sequence slot 0, continues at cur_pos
@@ -718,7 +747,7 @@ int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* 
     CK(cudaMemcpyAsync(pf_toks, toks, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
     CK(cudaMemcpyAsync(pf_toks + Mc, pos, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
     CK(cudaMemcpyAsync(pf_toks + 2 * Mc, slots, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
-    if (int rc = dense_rows(pf_toks, B, pf_toks + Mc, pf_toks + 2 * Mc, 0, 0, true)) return rc;
+    if (int rc = dense_rows(pf_toks, B, pf_toks + Mc, pf_toks + 2 * Mc, 0, 0, true, use_qgemm(B))) return rc;
     argmax_rows_kernel<<<B, 1024, 0, E.stream>>>(bt_logits, n_vocab, (n_vocab + 3) & ~3, bt_next); E.launches++;
     CK(cudaMemcpyAsync(next, bt_next, (size_t)B * 4, cudaMemcpyDeviceToHost, E.stream));
     if (logits) CK(cudaMemcpy2DAsync(logits, (size_t)n_vocab * 4, bt_logits, (size_t)((n_vocab + 3) & ~3) * 4, (size_t)n_vocab * 4, B, cudaMemcpyDeviceToHost, E.stream));

@@ -93,7 +93,10 @@ struct Model {
     int ensure_tile_weights();
     bool use_qgemm(int M) const;
     bool tile_ready = false;
-    int dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits);
+    int dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits, bool q);
+    int prefill_rows(const int32_t* toks, const int32_t* slots, const int32_t* pos, int M);
+    void maybe_bf16_cache();
+    bool bf16_tried = false;
     int prefill_slot(int slot, const int32_t* toks, int n, int pos0);
     int prefill(const int32_t* toks, int n);
     int batch_step(const int32_t* toks, const int32_t* slots, const int32_t* pos, int B, int32_t* next, float* logits = nullptr);
