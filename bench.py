@@ -130,6 +130,7 @@ def main():
     ap.add_argument("--ctx", type=int, default=512)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-batched", action="store_true", help="skip the bs64 / continuous-batching measurements (N=1 only)")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     W = max(a.warmup, 3); K = a.steps
@@ -224,13 +225,32 @@ def main():
     cb = None
     if rank == 0 and world == 1 and not a.no_cpu:
         cb = cpu_reference_arm(path, 4, 12)
+    # ---- batched decode (BASELINE.json metric "bs64") and config 3 (64 concurrent requests, continuous batching): the engine is
+    # re-initialised with 64 sequence slots; same files, same C ABI (b200_submit / b200_poll)
+    batched = None
+    if rank == 0 and world == 1 and not a.no_batched:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import bench_batch
+            m.close(); eng.shutdown()
+            batched = {}
+            for mix in dict.fromkeys([a.mix, "q8_0"]):             # the headline file, and config 3's all-Q8_0 file
+                eng2 = b200.Engine(device=local, max_ctx=648, max_seqs=64)
+                m2 = eng2.load_file(f"bench/batch-{mix}", model_path(a.preset, mix, a.n_layer, 0))
+                batched[mix] = bench_batch.measure(eng2, m2)
+                m2.close(); eng2.shutdown()
+            m = None
+        except (Exception, SystemExit) as ex:                      # reported, never fatal for the headline line
+            batched = {"error": str(ex)}; m = None
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_total / K,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8 x int4/6/8 dp4a, fp32 accumulate", "data": "synthetic",
                 "config": config, "roofline": roofline, "cpu_baseline": cb, "e2e": e2e, "gpu_launches": l1 - l0, "clocks": clk,
-                "load_s": load_s, "engine": {k: info[k] for k in ("grid", "ring_bytes", "n_phases", "n_splits", "weight_bytes", "hbm_bytes")}}
+                "load_s": load_s, "engine": {k: info[k] for k in ("grid", "ring_bytes", "n_phases", "n_splits", "weight_bytes", "hbm_bytes")},
+                "batched": batched}
         print(json.dumps(line))
-    m.close()
+    if m is not None:
+        m.close()
     if dist:
         dist.destroy_process_group()
 

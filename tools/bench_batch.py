@@ -18,38 +18,30 @@ import bench  # noqa: E402  (model_path)
 import nats_llm_studio_b200 as b200  # noqa: E402
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--preset", default="llama3-8b"); ap.add_argument("--mix", default="q8_0"); ap.add_argument("--n-layer", type=int, default=0)
-    ap.add_argument("--n-req", type=int, default=64); ap.add_argument("--gen", type=int, default=128)
-    ap.add_argument("--prompt-min", type=int, default=64); ap.add_argument("--prompt-max", type=int, default=512)
-    ap.add_argument("--step-iters", type=int, default=20)
-    a = ap.parse_args()
-    path = bench.model_path(a.preset, a.mix, a.n_layer, 0)
-    eng = b200.Engine(max_ctx=a.prompt_max + a.gen + 8, max_seqs=a.n_req)
-    m = eng.load_file("bench/batch", path)
-    rng = np.random.default_rng(7)
-    lens = rng.integers(a.prompt_min, a.prompt_max + 1, a.n_req)
+def measure(eng, m, n_req=64, gen=128, prompt_min=64, prompt_max=512, step_iters=20, seed=7):
+    """n_req concurrent requests through b200_submit / b200_poll (continuous batching) + the bare batched-step time."""
+    rng = np.random.default_rng(seed)
+    lens = rng.integers(prompt_min, prompt_max + 1, n_req)
     prompts = [rng.integers(0, m.n_vocab, n).astype(np.int32) for n in lens]
-
-    # warm-up: one request end to end (builds the bf16 weight cache), then a few full-batch steps
+    # warm-up: one request end to end (builds the tile-layout / bf16 weight copies), then a few full-batch steps
     m.submit(prompts[0], 1, max_tokens=4)
-    while not any(e.kind != b200.EV_TOKEN for e in eng.poll(64, 5000)):
+    while not any(e.kind != b200.EV_TOKEN for e in eng.poll(64, 60000)):
         pass
-    slots = np.arange(a.n_req, dtype=np.int32); pos = np.full(a.n_req, 300, np.int32); cur = rng.integers(0, m.n_vocab, a.n_req).astype(np.int32)
+    slots = np.arange(n_req, dtype=np.int32); pos = np.full(n_req, 300, np.int32); cur = rng.integers(0, m.n_vocab, n_req).astype(np.int32)
     for _ in range(3):
         m.batch_step(cur, slots, pos)
-    t0 = time.perf_counter()
-    for _ in range(a.step_iters):
+    l0 = int(b200.lib().b200_launch_count()); t0 = time.perf_counter()
+    for _ in range(step_iters):
         m.batch_step(cur, slots, pos)
-    step_ms = (time.perf_counter() - t0) * 1e3 / a.step_iters
+    step_ms = (time.perf_counter() - t0) * 1e3 / step_iters
+    launches_per_step = (int(b200.lib().b200_launch_count()) - l0) // step_iters
 
     t0 = time.perf_counter()
     for i, p in enumerate(prompts):
-        m.submit(p, 1000 + i, max_tokens=a.gen)
+        m.submit(p, 1000 + i, max_tokens=gen)
     first, fin, n_tok = {}, {}, 0
-    while len(fin) < a.n_req:
-        evs = eng.poll(256, 5000)
+    while len(fin) < n_req:
+        evs = eng.poll(256, 20000)
         now = time.perf_counter()
         if not evs:
             raise SystemExit("scheduler stalled")
@@ -62,11 +54,25 @@ def main():
                 raise SystemExit(f"request {e.req_id} failed: {e.finish_reason}")
     wall = max(v[0] for v in fin.values())
     ttft = np.array(sorted(first.values())) * 1e3
-    print(json.dumps({
-        "workload": f"{a.preset} {a.mix}" + (f" L{a.n_layer}" if a.n_layer else "") + f", {a.n_req} concurrent requests, prompts U[{a.prompt_min},{a.prompt_max}], {a.gen} generated each, continuous batching",
-        "aggregate_tok_s": round(n_tok / wall, 1), "wall_s": round(wall, 3), "generated": n_tok, "prompt_tokens": int(lens.sum()),
-        "ttft_ms_p50": round(float(np.percentile(ttft, 50)), 1), "ttft_ms_p90": round(float(np.percentile(ttft, 90)), 1), "ttft_ms_max": round(float(ttft.max()), 1),
-        "batch_step_ms": round(step_ms, 3), "batch_step_tok_s": round(a.n_req / step_ms * 1e3, 1), "launches": int(b200.lib().b200_launch_count())}))
+    return {"requests": n_req, "prompt_len": f"U[{prompt_min},{prompt_max}]", "generated_each": gen,
+            "aggregate_tok_s": round(n_tok / wall, 1), "wall_s": round(wall, 3), "generated": n_tok, "prompt_tokens": int(lens.sum()),
+            "ttft_ms_p50": round(float(np.percentile(ttft, 50)), 1), "ttft_ms_p90": round(float(np.percentile(ttft, 90)), 1), "ttft_ms_max": round(float(ttft.max()), 1),
+            "batch_step_ms": round(step_ms, 3), "batch_step_tok_s": round(n_req / step_ms * 1e3, 1), "batch_step_ctx": 300, "launches_per_step": launches_per_step}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--preset", default="llama3-8b"); ap.add_argument("--mix", default="q8_0"); ap.add_argument("--n-layer", type=int, default=0)
+    ap.add_argument("--n-req", type=int, default=64); ap.add_argument("--gen", type=int, default=128)
+    ap.add_argument("--prompt-min", type=int, default=64); ap.add_argument("--prompt-max", type=int, default=512)
+    ap.add_argument("--step-iters", type=int, default=20)
+    a = ap.parse_args()
+    path = bench.model_path(a.preset, a.mix, a.n_layer, 0)
+    eng = b200.Engine(max_ctx=a.prompt_max + a.gen + 8, max_seqs=a.n_req)
+    m = eng.load_file("bench/batch", path)
+    r = measure(eng, m, a.n_req, a.gen, a.prompt_min, a.prompt_max, a.step_iters)
+    r["workload"] = f"{a.preset} {a.mix}" + (f" L{a.n_layer}" if a.n_layer else "") + ", continuous batching"
+    print(json.dumps(r))
     m.close()
 
 
