@@ -127,6 +127,15 @@ int b200_model_set_prefill_min(b200_model* m, int n);
  * on which other rows are in the batch. */
 int b200_model_prefill_slot(b200_model* m, int slot, const int32_t* toks, int n, int pos0);
 int b200_model_batch_step(b200_model* m, const int32_t* toks, const int32_t* slots, const int32_t* pos, int n, int32_t* next, float* logits);
+/* ---- tensor parallelism.  No counterpart in the reference, whose only scale-out is replicas in a NATS
+ * queue group (README.md:484).  One process per GPU; rank 0 creates a 128-byte NCCL id, the host side distributes it
+ * (the Go worker would publish it on a NATS subject; tests and tools use torch.distributed), every rank then calls
+ * b200_tp_init after b200_init and before opening a model.  A model opened afterwards keeps only this rank's shard
+ * (attention heads, FFN columns, vocabulary rows) and is driven through b200_model_prefill_slot /
+ * b200_model_batch_step with identical arguments on all ranks; the partial sums of the two row-parallel products of a
+ * layer are all-reduced over NVLink (NCCL), the logits slices all-gathered. */
+int b200_tp_unique_id(void* out, size_t cap);
+int b200_tp_init(int rank, int world, const void* id, size_t n);
 /* decode-step timing: n_steps greedy tokens from the current position of a primed context */
 int b200_bench_decode(b200_model* m, int ctx_len, int n_steps, int warmup, float* ms_per_token, double* bytes_per_token);
 /* number of kernels this library has launched so far (bench.py reports the delta as gpu_launches) */

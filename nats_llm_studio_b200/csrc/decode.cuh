@@ -614,8 +614,9 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
 // ------------------------------------------------------------------------------------ repack (K9) and test kernels
 // One thread per 16 output bytes; source bytes gathered through src_byte().  parity >= 0 interleaves:
 // raw row r goes to engine row 2r + parity (gate/up fusion).  Rows >= n_src are zero (odd-N padding).
-__global__ void repack_kernel(const uint8_t* __restrict__ raw, uint8_t* __restrict__ out, int type, long long N, long long n_src, int K, int parity) {
-    const int gb = group_bytes(type), ng = n_groups(K); const size_t rrb = raw_row_bytes(type, K);
+// src_stride: bytes between source rows (0 = dense rows of K elements); a K-slice of a wider matrix passes the full row size.
+__global__ void repack_kernel(const uint8_t* __restrict__ raw, uint8_t* __restrict__ out, int type, long long N, long long n_src, int K, int parity, size_t src_stride) {
+    const int gb = group_bytes(type), ng = n_groups(K); const size_t rrb = src_stride ? src_stride : raw_row_bytes(type, K);
     const long long chunks_per_row = (long long)ng * gb / 16, total = N * chunks_per_row;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const long long row = i / chunks_per_row; const int rem = (int)(i % chunks_per_row);

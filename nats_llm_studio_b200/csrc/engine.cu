@@ -29,6 +29,67 @@ int fail(int code, const std::string& msg) { g_last_error = msg; return code; }
 
 Engine& engine() { static Engine e; return e; }
 
+// ------------------------------------------------------------------------------------ tensor parallelism: NCCL, bound at run time
+// (no link-time dependency: the library loads on a box without NCCL; one process per GPU)
+#include <dlfcn.h>
+namespace {
+struct NcclId { char internal[128]; };
+struct NcclApi {
+    int (*GetUniqueId)(NcclId*) = nullptr;
+    int (*CommInitRank)(void**, int, NcclId, int) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    bool ok = false;
+};
+NcclApi& nccl() {
+    static NcclApi a; static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (h) {
+            a.GetUniqueId = (decltype(a.GetUniqueId))dlsym(h, "ncclGetUniqueId"); a.CommInitRank = (decltype(a.CommInitRank))dlsym(h, "ncclCommInitRank");
+            a.AllReduce = (decltype(a.AllReduce))dlsym(h, "ncclAllReduce"); a.AllGather = (decltype(a.AllGather))dlsym(h, "ncclAllGather");
+            a.CommDestroy = (decltype(a.CommDestroy))dlsym(h, "ncclCommDestroy"); a.GetErrorString = (decltype(a.GetErrorString))dlsym(h, "ncclGetErrorString");
+            a.ok = a.GetUniqueId && a.CommInitRank && a.AllReduce && a.AllGather && a.CommDestroy && a.GetErrorString;
+        }
+    }
+    return a;
+}
+int nccl_fail(const char* what, int rc) { return fail(B200_ERR_CUDA, std::string(what) + ": " + (nccl().GetErrorString ? nccl().GetErrorString(rc) : "NCCL error")); }
+}  // namespace
+
+int Engine::tp_unique_id(void* out, size_t cap) {
+    if (cap < sizeof(NcclId)) return fail(B200_ERR_INVALID, "the NCCL id needs 128 bytes");
+    if (!nccl().ok) return fail(B200_ERR_UNSUPPORTED, "libnccl.so.2 not found: tensor parallelism is unavailable");
+    if (int rc = nccl().GetUniqueId((NcclId*)out)) return nccl_fail("ncclGetUniqueId", rc);
+    return B200_OK;
+}
+int Engine::tp_init(int rank, int world, const void* id, size_t n) {
+    if (int rc = ensure()) return rc;
+    if (world < 1 || rank < 0 || rank >= world || (world > 1 && (!id || n < sizeof(NcclId)))) return fail(B200_ERR_INVALID, "bad tensor-parallel rank/world/id");
+    if (nccl_comm) return fail(B200_ERR_STATE, "tensor parallelism is already initialised");
+    if (world > 1) {
+        if (!nccl().ok) return fail(B200_ERR_UNSUPPORTED, "libnccl.so.2 not found: tensor parallelism is unavailable");
+        NcclId nid; memcpy(&nid, id, sizeof nid);
+        if (int rc = nccl().CommInitRank(&nccl_comm, world, nid, rank)) return nccl_fail("ncclCommInitRank", rc);
+    }
+    tp_rank = rank; tp_world = world;
+    return B200_OK;
+}
+int Engine::all_reduce_sum(float* buf, size_t n) {
+    if (tp_world == 1) return B200_OK;
+    if (int rc = nccl().AllReduce(buf, buf, n, 7 /*ncclFloat32*/, 0 /*ncclSum*/, nccl_comm, stream)) return nccl_fail("ncclAllReduce", rc);
+    return B200_OK;
+}
+int Engine::all_gather(const float* src, float* dst, size_t n_per_rank) {
+    if (tp_world == 1) { if (src != dst) CK(cudaMemcpyAsync(dst, src, n_per_rank * 4, cudaMemcpyDeviceToDevice, stream)); return B200_OK; }
+    if (int rc = nccl().AllGather(src, dst, n_per_rank, 7, nccl_comm, stream)) return nccl_fail("ncclAllGather", rc);
+    return B200_OK;
+}
+
 // ------------------------------------------------------------------------------------ init
 int Engine::init(const b200_config* cfg) {
     std::lock_guard<std::mutex> lk(mu);
@@ -57,6 +118,8 @@ void Engine::shutdown() {
     cudaSetDevice(device); cudaDeviceSynchronize();
     cudaStreamDestroy(stream); cudaStreamDestroy(copy_stream); stream = copy_stream = nullptr;
     cudaFree(qg_ws); qg_ws = nullptr;
+    if (nccl_comm) { nccl().CommDestroy(nccl_comm); nccl_comm = nullptr; }
+    tp_rank = 0; tp_world = 1;
     ready = false;
 }
 
@@ -103,11 +166,11 @@ static int dalloc(T** p, size_t n) {
 
 // repack `raw` (device, ggml row-major blocks) into the engine layout at `out`
 // (N rows written, of which the first n_src come from raw and the rest are zero padding)
-static int repack(Engine& E, const uint8_t* raw, uint8_t* out, int type, int64_t N, int64_t n_src, int K, int interleave_parity = -1) {
+static int repack(Engine& E, const uint8_t* raw, uint8_t* out, int type, int64_t N, int64_t n_src, int K, int interleave_parity = -1, size_t src_stride = 0) {
     long long chunks = (long long)N * n_groups(K) * group_bytes(type) / 16;
     int blocks = (int)std::min<long long>((chunks + 255) / 256, 148LL * 32);
     if (blocks < 1) blocks = 1;
-    repack_kernel<<<blocks, 256, 0, E.stream>>>(raw, out, type, N, n_src, K, interleave_parity);
+    repack_kernel<<<blocks, 256, 0, E.stream>>>(raw, out, type, N, n_src, K, interleave_parity, src_stride);
     CK(cudaGetLastError());
     E.launches++;
     return B200_OK;
@@ -182,6 +245,23 @@ int Model::load_matrix(const std::string& name, int64_t N, int K, Matrix& out) {
     return repack(engine(), d_raw + t->offset, out.w, t->type, Np, N, K);
 }
 
+// Tensor-parallel shard of a matrix: rows [row0, row0+nrows) x K positions [col0, col0+ncols) of the GGUF tensor.
+// Quant blocks run along K, so a row range is a contiguous byte range and a K range (block aligned) a fixed byte window
+// of every row: the repack reads it in place from the uploaded file image.
+int Model::load_slice(const std::string& name, int64_t N_full, int K_full, int64_t row0, int64_t nrows, int col0, int ncols, Matrix& out) {
+    const GgufTensor* t = meta.tensor(name);
+    if (!t) return fail(B200_ERR_INVALID, "GGUF: missing tensor " + name);
+    if (t->ne[0] != K_full || t->ne[1] != N_full) return fail(B200_ERR_INVALID, "GGUF: tensor " + name + " has unexpected shape");
+    if (!is_streamable(t->type)) return fail(B200_ERR_UNSUPPORTED, "tensor " + name + ": unsupported ggml type for matrices");
+    if (col0 % 256 || ncols % 256 || row0 + nrows > N_full || col0 + ncols > K_full) return fail(B200_ERR_UNSUPPORTED, "tensor " + name + ": shard is not aligned to 256-element blocks");
+    const int64_t Np = nrows + (nrows & 1);
+    out.type = t->type; out.N = Np; out.n_rows = nrows; out.K = ncols;
+    if (int rc = own(&out.w, repacked_bytes(t->type, Np, ncols))) return rc;
+    const size_t rrb = raw_row_bytes(t->type, K_full);
+    weight_bytes += (uint64_t)nrows * raw_row_bytes(t->type, ncols);
+    return repack(engine(), d_raw + t->offset + (size_t)row0 * rrb + (size_t)(col0 / block_elems(t->type)) * block_bytes(t->type), out.w, t->type, Np, nrows, ncols, -1, rrb);
+}
+
 int Model::load_vector(const std::string& name, int64_t n, float** out) {
     const GgufTensor* t = meta.tensor(name);
     if (!t) return fail(B200_ERR_INVALID, "GGUF: missing tensor " + name);
@@ -196,32 +276,42 @@ int Model::commit() {
     if (committed) return B200_OK;
     if (uploaded < meta.data_bytes) return fail(B200_ERR_STATE, "commit before all tensor bytes were uploaded (" + std::to_string(uploaded) + " of " + std::to_string(meta.data_bytes) + ")");
     Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    const int W = E.tp_world, tr = E.tp_rank;
+    tp = W > 1;
+    const int gF = n_ff, gQD = n_head * head_dim, gKVD = n_head_kv * head_dim, gV = n_vocab;
+    if (tp) {                                                   // this rank's shard: heads, FFN columns and vocab rows divided by W
+        if (n_head_kv % W || n_head % W || n_ff % (256 * W) || (gQD / W) % 256 || n_vocab % (2 * W))
+            return fail(B200_ERR_UNSUPPORTED, "model dimensions do not divide over " + std::to_string(W) + " tensor-parallel ranks");
+        n_head /= W; n_head_kv /= W; n_ff /= W; n_vocab_l = n_vocab / W;
+    } else n_vocab_l = n_vocab;
     const int D = n_embd, F = n_ff, QD = n_head * head_dim, KVD = n_head_kv * head_dim;
     layers.resize(n_layer);
-    if (int rc = load_matrix("token_embd.weight", n_vocab, D, tok_embd)) return rc;
+    if (int rc = load_matrix("token_embd.weight", gV, D, tok_embd)) return rc;
     for (int l = 0; l < n_layer; l++) {
         Layer& L = layers[l]; std::string p = "blk." + std::to_string(l) + ".";
         int rc;
         if ((rc = load_vector(p + "attn_norm.weight", D, &L.attn_norm))) return rc;
-        if ((rc = load_matrix(p + "attn_q.weight", QD, D, L.wq))) return rc;
-        if ((rc = load_matrix(p + "attn_k.weight", KVD, D, L.wk))) return rc;
-        if ((rc = load_matrix(p + "attn_v.weight", KVD, D, L.wv))) return rc;
-        if ((rc = load_matrix(p + "attn_output.weight", D, QD, L.wo))) return rc;
+        if ((rc = load_slice(p + "attn_q.weight", gQD, D, (int64_t)tr * QD, QD, 0, D, L.wq))) return rc;          // column-parallel: by heads
+        if ((rc = load_slice(p + "attn_k.weight", gKVD, D, (int64_t)tr * KVD, KVD, 0, D, L.wk))) return rc;
+        if ((rc = load_slice(p + "attn_v.weight", gKVD, D, (int64_t)tr * KVD, KVD, 0, D, L.wv))) return rc;
+        if ((rc = load_slice(p + "attn_output.weight", D, gQD, 0, D, tr * QD, QD, L.wo))) return rc;              // row-parallel: K range
         if ((rc = load_vector(p + "ffn_norm.weight", D, &L.ffn_norm))) return rc;
         const GgufTensor *tg = meta.tensor(p + "ffn_gate.weight"), *tu = meta.tensor(p + "ffn_up.weight");
         if (!tg || !tu) return fail(B200_ERR_INVALID, "GGUF: missing ffn_gate/ffn_up in layer " + std::to_string(l));
         if (tg->type != tu->type) return fail(B200_ERR_UNSUPPORTED, "ffn_gate and ffn_up of a layer must share a quant type");
-        if (tg->ne[0] != D || tg->ne[1] != F || tu->ne[0] != D || tu->ne[1] != F) return fail(B200_ERR_INVALID, "GGUF: ffn_gate/up shape");
+        if (tg->ne[0] != D || tg->ne[1] != gF || tu->ne[0] != D || tu->ne[1] != gF) return fail(B200_ERR_INVALID, "GGUF: ffn_gate/up shape");
         if (!is_streamable(tg->type)) return fail(B200_ERR_UNSUPPORTED, "ffn_gate: unsupported ggml type");
         L.wgu.type = tg->type; L.wgu.N = 2 * (int64_t)F; L.wgu.n_rows = 2 * (int64_t)F; L.wgu.K = D;   // rows interleaved (gate_i, up_i)
         if ((rc = own(&L.wgu.w, repacked_bytes(tg->type, 2 * (int64_t)F, D)))) return rc;
-        if ((rc = repack(E, d_raw + tg->offset, L.wgu.w, tg->type, F, F, D, 0))) return rc;
-        if ((rc = repack(E, d_raw + tu->offset, L.wgu.w, tu->type, F, F, D, 1))) return rc;
-        weight_bytes += tg->nbytes + tu->nbytes;
-        if ((rc = load_matrix(p + "ffn_down.weight", D, F, L.wd))) return rc;
+        const size_t grb = raw_row_bytes(tg->type, D);
+        if ((rc = repack(E, d_raw + tg->offset + (size_t)tr * F * grb, L.wgu.w, tg->type, F, F, D, 0))) return rc;
+        if ((rc = repack(E, d_raw + tu->offset + (size_t)tr * F * grb, L.wgu.w, tu->type, F, F, D, 1))) return rc;
+        weight_bytes += 2 * (uint64_t)F * grb;
+        if ((rc = load_slice(p + "ffn_down.weight", D, gF, 0, D, tr * F, F, L.wd))) return rc;
     }
     if (int rc = load_vector("output_norm.weight", D, &out_norm)) return rc;
-    if (meta.tensor("output.weight")) { if (int rc = load_matrix("output.weight", n_vocab, D, out_w)) return rc; }
+    if (tp) { if (int rc = load_slice(meta.tensor("output.weight") ? "output.weight" : "token_embd.weight", gV, D, (int64_t)tr * n_vocab_l, n_vocab_l, 0, D, out_w)) return rc; }
+    else if (meta.tensor("output.weight")) { if (int rc = load_matrix("output.weight", n_vocab, D, out_w)) return rc; }
     else out_w = tok_embd;                                                        // tied embeddings
 
     // rope frequencies (optional rope_freqs.weight = per-frequency divisors, llama-3.1 style)
@@ -237,23 +327,26 @@ int Model::commit() {
     cudaFree(d_raw); d_raw = nullptr;
 
     // ---- runtime buffers
-    int max_grp = std::max({n_groups(F), n_groups(QD), 2 * n_groups(D)});
-    hown_cap = 2 * ((D / 2 + E.n_sm - 1) / E.n_sm + 2);                       // pairs per CTA slice (worst case: 1 CTA/SM) x 2 rows
-    LaunchCfg lc; if (int rc = launch_cfg(E, max_grp, hown_cap, 5 * n_layer + 2, lc)) return rc;
-    grid = lc.grid; ring_bytes = lc.ring_bytes; smem_max_grp = lc.max_grp; smem_bytes = lc.smem;
     int rc;
-    const size_t n_ll16 = (size_t)XREP * ((size_t)D + QD + F) + 2 * (size_t)KVD, n_ll32 = (size_t)QD + (size_t)n_head * 16 * (head_dim + 2) + 2 * (size_t)grid;
-    if ((rc = own(&d_ll16, n_ll16)) || (rc = own(&d_ll32, n_ll32)) || (rc = own(&d_logits, (size_t)n_vocab + 2)) || (rc = own(&d_state, (size_t)16)) ||
-        (rc = own(&d_out_tokens, (size_t)E.max_ctx + 16)) || (rc = own(&d_forced, (size_t)E.max_ctx + 16)))
-        return rc;
-    CK(cudaMemset(d_ll16, 0, n_ll16 * 4)); CK(cudaMemset(d_ll32, 0, n_ll32 * 8));     // tag 0 = never valid
-    CK(cudaMemset(d_state, 0, 16 * sizeof(int)));
     pages_per_seq = (E.max_ctx + 15) / 16;
     n_pages = pages_per_seq * E.max_seqs;
     size_t page_elems = (size_t)n_layer * 2 * n_head_kv * 16 * head_dim;
     if ((rc = own(&d_kv, page_elems * n_pages)) || (rc = own(&d_block_table, (size_t)n_pages))) return rc;
     std::vector<int> bt(n_pages); for (int i = 0; i < n_pages; i++) bt[i] = i;
     CK(cudaMemcpy(d_block_table, bt.data(), bt.size() * 4, cudaMemcpyHostToDevice));
+    // a tensor-parallel shard is served by the dense row path only (prefill_slot / batch_step, all ranks in lockstep):
+    // the persistent batch-1 kernel below has no exchange step between GPUs yet
+    if (tp) { committed = true; return B200_OK; }
+    int max_grp = std::max({n_groups(F), n_groups(QD), 2 * n_groups(D)});
+    hown_cap = 2 * ((D / 2 + E.n_sm - 1) / E.n_sm + 2);                       // pairs per CTA slice (worst case: 1 CTA/SM) x 2 rows
+    LaunchCfg lc; if (int rc2 = launch_cfg(E, max_grp, hown_cap, 5 * n_layer + 2, lc)) return rc2;
+    grid = lc.grid; ring_bytes = lc.ring_bytes; smem_max_grp = lc.max_grp; smem_bytes = lc.smem;
+    const size_t n_ll16 = (size_t)XREP * ((size_t)D + QD + F) + 2 * (size_t)KVD, n_ll32 = (size_t)QD + (size_t)n_head * 16 * (head_dim + 2) + 2 * (size_t)grid;
+    if ((rc = own(&d_ll16, n_ll16)) || (rc = own(&d_ll32, n_ll32)) || (rc = own(&d_logits, (size_t)n_vocab + 2)) || (rc = own(&d_state, (size_t)16)) ||
+        (rc = own(&d_out_tokens, (size_t)E.max_ctx + 16)) || (rc = own(&d_forced, (size_t)E.max_ctx + 16)))
+        return rc;
+    CK(cudaMemset(d_ll16, 0, n_ll16 * 4)); CK(cudaMemset(d_ll32, 0, n_ll32 * 8));     // tag 0 = never valid
+    CK(cudaMemset(d_state, 0, 16 * sizeof(int)));
 
     // ---- decode schedule
     std::vector<Phase> ph;
@@ -305,6 +398,7 @@ void Model::fill_params(DecodeParams& P) const {
 int Model::run_steps(int n_steps, const int32_t* forced, int n_forced, bool reset, float* logits_all_dev) {
     Engine& E = engine();
     if (!committed) return fail(B200_ERR_STATE, "model not committed");
+    if (tp) return fail(B200_ERR_UNSUPPORTED, "tensor-parallel shard: the batch-1 decode kernel is single-GPU");
     if (n_steps <= 0) return B200_OK;
     if (reset) { int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0; }
     if (cur_pos + n_steps > E.max_ctx) return fail(B200_ERR_INVALID, "context overflow: " + std::to_string(cur_pos + n_steps) + " > max_ctx " + std::to_string(E.max_ctx));
@@ -324,6 +418,7 @@ int Model::run_steps(int n_steps, const int32_t* forced, int n_forced, bool rese
 
 int Model::generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_sampling* s, int32_t* out, int* n_out, float* ttft_ms, float* decode_ms) {
     Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    if (tp) return fail(B200_ERR_UNSUPPORTED, "tensor-parallel shard: drive all ranks through b200_model_prefill_slot / b200_model_batch_step");
     std::lock_guard<std::mutex> lk(run_mu);
     if (n_prompt < 1 || n_gen < 1) return fail(B200_ERR_INVALID, "need at least one prompt token and one generated token");
     for (int i = 0; i < n_prompt; i++) if (prompt[i] < 0 || prompt[i] >= n_vocab) return fail(B200_ERR_INVALID, "prompt token out of range");
@@ -561,7 +656,7 @@ int Model::ensure_prefill_buffers() {
     int rc;
     if ((rc = own(&pf_H, (size_t)Mc * D)) || (rc = own(&pf_X, (size_t)Mc * std::max(D, QD))) || (rc = own(&pf_Y, (size_t)Mc * std::max(QD + 2 * KVD, 2 * F))) ||
         (rc = own(&pf_Q, (size_t)Mc * QD)) || (rc = own(&pf_ACT, (size_t)Mc * F)) || (rc = own(&pf_W, wmax)) || (rc = own(&pf_toks, (size_t)3 * Mc)) ||
-        (rc = own(&bt_logits, (size_t)std::max(1, E.max_seqs) * ((n_vocab + 3) & ~3))) || (rc = own(&bt_next, (size_t)std::max(1, E.max_seqs))))
+        (rc = own(&bt_logits, (size_t)std::max(1, E.max_seqs) * ((n_vocab_l + 3) & ~3) * (E.tp_world + (E.tp_world > 1 ? 1 : 0)))) || (tp && (rc = own(&pf_T, (size_t)Mc * D))) || (rc = own(&bt_next, (size_t)std::max(1, E.max_seqs))))
         return rc;
     return B200_OK;
 }
@@ -604,6 +699,20 @@ int Model::ensure_tile_weights() {
     if ((rc = mk(out_w))) return rc;
     CK(cudaStreamSynchronize(E.stream));
     tile_ready = true;
+    return B200_OK;
+}
+
+__global__ void add_rows_kernel(float* __restrict__ H, const float* __restrict__ T, long long n) {
+    for (long long i = (blockIdx.x * (long long)blockDim.x + threadIdx.x) * 4; i < n; i += (long long)gridDim.x * blockDim.x * 4) {
+        float4 h = *(float4*)(H + i); const float4 t = *(const float4*)(T + i); h.x += t.x; h.y += t.y; h.z += t.z; h.w += t.w; *(float4*)(H + i) = h;
+    }
+}
+// tensor-parallel residual: complete this rank's partial product in pf_T (stream-K parts), sum it over the ranks, add to H
+int Model::tp_reduce_add(int M, const QgSplit& sp) {
+    Engine& E = engine(); const int D = n_embd;
+    if (sp.ws) { qgemm_finish_kernel<<<nblk((long long)M * D), 256, 0, E.stream>>>(sp, pf_T, D, M, D); E.launches++; }
+    if (int rc = E.all_reduce_sum(pf_T, (size_t)M * D)) return rc;
+    add_rows_kernel<<<nblk((long long)M * D / 4), 256, 0, E.stream>>>(pf_H, pf_T, (long long)M * D); E.launches++;
     return B200_OK;
 }
 
@@ -650,11 +759,16 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
 #undef B200_ATTN
         }
         E.launches++;
-        if (q) { const QMat o{&L.wo, pf_H}; if ((rc = qgemm(E, &o, 1, pf_X, M, QD, D, 1, rs, false, &sp))) return rc; }
+        // residual GEMM: single GPU adds into H (in the epilogue / the next norm's gather); a tensor-parallel shard holds a K
+        // slice, so its product is a partial sum: complete it locally, all-reduce it over NVLink, then add it to H
+        float* resid = tp ? pf_T : pf_H; const int rmode = tp ? 0 : 1;
+        if (q) { const QMat o{&L.wo, resid}; if ((rc = qgemm(E, &o, 1, pf_X, M, QD, D, rmode, rs, false, &sp))) return rc; }
         else {
             if (!bf16_ready) { deq(L.wo, pf_W); wo = pf_W; }
-            if ((rc = gemm_bf16(E, pf_X, wo, pf_H, M, D, QD, D, 1, rs))) return rc;
+            if ((rc = gemm_bf16(E, pf_X, wo, resid, M, D, QD, D, rmode, rs))) return rc;
         }
+        if (tp && (rc = tp_reduce_add(M, sp))) return rc;
+        if (tp) sp = none;
         if (l == n_layer - 1 && !want_logits) break;                  // KV fill only: the last layer's FFN feeds nothing
         rmsnorm_rows_kernel<<<M, rms_threads, 0, E.stream>>>(pf_H, L.ffn_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
         if (q) { const QMat gu{&L.wgu, pf_Y}; if ((rc = qgemm(E, &gu, 1, pf_X, M, D, 2 * F, 0, 1.f, false, &sp))) return rc; }
@@ -663,20 +777,26 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
             if ((rc = gemm_bf16(E, pf_X, wgu, pf_Y, M, 2 * F, D, 2 * F, 0, 1.f))) return rc;
         }
         swiglu_rows_kernel<<<nblk((long long)M * F), 256, 0, E.stream>>>(pf_Y, M, F, pf_ACT, q, sp); E.launches++; sp = none;
-        if (q) { const QMat dn{&L.wd, pf_H}; if ((rc = qgemm(E, &dn, 1, pf_ACT, M, F, D, 1, rs, false, &sp))) return rc; }
+        if (q) { const QMat dn{&L.wd, resid}; if ((rc = qgemm(E, &dn, 1, pf_ACT, M, F, D, rmode, rs, false, &sp))) return rc; }
         else {
             if (!bf16_ready) { deq(L.wd, pf_W); wd = pf_W; }
-            if ((rc = gemm_bf16(E, pf_ACT, wd, pf_H, M, D, F, D, 1, rs))) return rc;
+            if ((rc = gemm_bf16(E, pf_ACT, wd, resid, M, D, F, D, rmode, rs))) return rc;
         }
+        if (tp && (rc = tp_reduce_add(M, sp))) return rc;
+        if (tp) sp = none;
     }
     if (want_logits) {
-        const int ldv = (n_vocab + 3) & ~3; const float ls = logit_scale != 0.f ? 1.f / logit_scale : 1.f;
+        // vocab rows are sharded: each rank computes its slice of the logits into part `rank` of bt_logits ([W][M][ldv]),
+        // an all-gather makes every part visible everywhere (argmax / sampling then run replicated)
+        const int ldv = (n_vocab_l + 3) & ~3; const float ls = logit_scale != 0.f ? 1.f / logit_scale : 1.f;
+        float* mine = tp ? bt_logits + (size_t)E.tp_world * M * ldv : bt_logits;       // scratch behind the gathered parts
         rmsnorm_rows_kernel<<<M, rms_threads, 0, E.stream>>>(pf_H, out_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
-        if (q) { const QMat o{&out_w, bt_logits}; if ((rc = qgemm(E, &o, 1, pf_X, M, D, ldv, 0, ls, true, &sp))) return rc; sp = none; }
+        if (q) { const QMat o{&out_w, mine}; if ((rc = qgemm(E, &o, 1, pf_X, M, D, ldv, 0, ls, true, &sp))) return rc; sp = none; }
         else {
             if (!bf16_ready) return fail(B200_ERR_STATE, "logits through the dense path need the bf16 weight cache");
-            if ((rc = gemm_bf16(E, pf_X, b_out, bt_logits, M, n_vocab, D, ldv, 0, ls))) return rc;
+            if ((rc = gemm_bf16(E, pf_X, b_out, mine, M, n_vocab_l, D, ldv, 0, ls))) return rc;
         }
+        if (tp && (rc = E.all_gather(mine, bt_logits, (size_t)M * ldv))) return rc;
     }
     CK(cudaGetLastError());
     return B200_OK;
@@ -748,9 +868,11 @@ int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* 
     CK(cudaMemcpyAsync(pf_toks + Mc, pos, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
     CK(cudaMemcpyAsync(pf_toks + 2 * Mc, slots, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
     if (int rc = dense_rows(pf_toks, B, pf_toks + Mc, pf_toks + 2 * Mc, 0, 0, true, use_qgemm(B))) return rc;
-    argmax_rows_kernel<<<B, 1024, 0, E.stream>>>(bt_logits, n_vocab, (n_vocab + 3) & ~3, bt_next); E.launches++;
+    const int ldv = (n_vocab_l + 3) & ~3, Wp = E.tp_world;
+    argmax_rows_kernel<<<B, 1024, 0, E.stream>>>(bt_logits, n_vocab_l, ldv, Wp, (size_t)B * ldv, bt_next); E.launches++;
     CK(cudaMemcpyAsync(next, bt_next, (size_t)B * 4, cudaMemcpyDeviceToHost, E.stream));
-    if (logits) CK(cudaMemcpy2DAsync(logits, (size_t)n_vocab * 4, bt_logits, (size_t)((n_vocab + 3) & ~3) * 4, (size_t)n_vocab * 4, B, cudaMemcpyDeviceToHost, E.stream));
+    if (logits) for (int p = 0; p < Wp; p++)
+        CK(cudaMemcpy2DAsync(logits + (size_t)p * n_vocab_l, (size_t)n_vocab * 4, bt_logits + (size_t)p * B * ldv, (size_t)ldv * 4, (size_t)n_vocab_l * 4, B, cudaMemcpyDeviceToHost, E.stream));
     CK(cudaStreamSynchronize(E.stream));
     return B200_OK;
 }

@@ -38,6 +38,12 @@ struct Engine {
     cudaStream_t stream = nullptr, copy_stream = nullptr;
     uint64_t launches = 0;                       // kernels launched by this library (bench.py reports it)
     float* qg_ws = nullptr;                      // stream-K partial tiles of the dequant-in-GEMM kernel
+    // tensor parallelism: one process per GPU, NCCL communicator created from an id the host side distributes
+    int tp_rank = 0, tp_world = 1; void* nccl_comm = nullptr;
+    int tp_unique_id(void* out, size_t cap);
+    int tp_init(int rank, int world, const void* id, size_t n);
+    int all_reduce_sum(float* buf, size_t n);                            // in place, on `stream`
+    int all_gather(const float* src, float* dst, size_t n_per_rank);     // dst = [world][n_per_rank], on `stream`
     int init(const b200_config* cfg);
     int ensure();
     void shutdown();                             // after every model is closed: a later init() may use a different config
@@ -91,6 +97,9 @@ struct Model {
     int ensure_prefill_buffers();
     int ensure_bf16_weights();
     int ensure_tile_weights();
+    int tp_reduce_add(int M, const struct QgSplit& sp);
+    int load_slice(const std::string& name, int64_t N_full, int K_full, int64_t row0, int64_t nrows, int col0, int ncols, Matrix& out);
+    bool tp = false; int n_vocab_l = 0; float* pf_T = nullptr;    // tensor-parallel shard: local vocab rows, partial-sum buffer
     bool use_qgemm(int M) const;
     bool tile_ready = false;
     int dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits, bool q);

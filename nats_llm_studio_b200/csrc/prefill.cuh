@@ -419,18 +419,22 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32, 2) attn_rows_kernel(const __n
     }
 }
 
-// next[m] = argmax_v logits[m][v] (lowest index wins ties); one block per row
-__global__ void argmax_rows_kernel(const float* __restrict__ logits, int V, int ld, int* __restrict__ next) {
+// next[m] = argmax_v logits[m][v] (lowest index wins ties); one block per row.  The vocabulary may be split into n_parts
+// slices of V columns (tensor-parallel lm_head): slice p of row m is at logits + p * part_stride + m * ld, its first
+// column is token p * V.
+__global__ void argmax_rows_kernel(const float* __restrict__ logits, int V, int ld, int n_parts, size_t part_stride, int* __restrict__ next) {
     __shared__ float sv[32]; __shared__ int si[32];
-    const float* row = logits + (size_t)blockIdx.x * ld;
     float bv = -INFINITY; int bi = 0x7fffffff;
     const int V4 = V & ~3;                                           // rows start 16-byte aligned (ld % 4 == 0)
+    for (int p = 0; p < n_parts; p++) {
+        const float* row = logits + (size_t)p * part_stride + (size_t)blockIdx.x * ld; const int base = p * V;
 #pragma unroll 4
-    for (int i = threadIdx.x * 4; i < V4; i += blockDim.x * 4) {
-        const float4 v = *(const float4*)(row + i);
-        if (v.x > bv) { bv = v.x; bi = i; } if (v.y > bv) { bv = v.y; bi = i + 1; } if (v.z > bv) { bv = v.z; bi = i + 2; } if (v.w > bv) { bv = v.w; bi = i + 3; }
+        for (int i = threadIdx.x * 4; i < V4; i += blockDim.x * 4) {
+            const float4 v = *(const float4*)(row + i);
+            if (v.x > bv) { bv = v.x; bi = base + i; } if (v.y > bv) { bv = v.y; bi = base + i + 1; } if (v.z > bv) { bv = v.z; bi = base + i + 2; } if (v.w > bv) { bv = v.w; bi = base + i + 3; }
+        }
+        for (int i = V4 + threadIdx.x; i < V; i += blockDim.x) { const float v = row[i]; if (v > bv || (v == bv && base + i < bi)) { bv = v; bi = base + i; } }
     }
-    for (int i = V4 + threadIdx.x; i < V; i += blockDim.x) { const float v = row[i]; if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; } }
     for (int o = 16; o; o >>= 1) { const float v = __shfl_xor_sync(0xffffffffu, bv, o); const int ix = __shfl_xor_sync(0xffffffffu, bi, o); if (v > bv || (v == bv && ix < bi)) { bv = v; bi = ix; } }
     if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = bv; si[threadIdx.x >> 5] = bi; }
     __syncthreads();

@@ -56,7 +56,8 @@ SYMBOLS = {
     "b200_dequantize": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_dequantize_noalloc": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_gemv": (ci, [ci, vp, C.c_int64, ci, vp, vp, ci, C.POINTER(C.c_float)]),
     "b200_bench_decode": (ci, [vp, ci, ci, ci, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
     "b200_gemm_bf16": (ci, [vp, vp, vp, ci, ci, ci]), "b200_qgemm": (ci, [ci, vp, C.c_int64, ci, vp, ci, vp, ci, C.POINTER(C.c_float)]), "b200_model_prefill_slot": (ci, [vp, ci, vp, ci, ci]),
-    "b200_model_batch_step": (ci, [vp, vp, vp, vp, ci, vp, vp]), "b200_model_set_prefill_min": (ci, [vp, ci]),
+    "b200_model_batch_step": (ci, [vp, vp, vp, vp, ci, vp, vp]),
+    "b200_tp_unique_id": (ci, [vp, sz]), "b200_tp_init": (ci, [ci, ci, vp, sz]), "b200_model_set_prefill_min": (ci, [vp, ci]),
     "b200_launch_count": (C.c_uint64, []), "b200_layout_selftest": (ci, []),
 }
 
@@ -215,6 +216,17 @@ class Engine:
         if n < 0:
             _check(n)
         return [Event.from_buffer_copy(buf[i]) for i in range(n)]
+
+    @staticmethod
+    def tp_unique_id():
+        """rank 0: the 128-byte NCCL id the other ranks need for tp_init"""
+        buf = C.create_string_buffer(128)
+        _check(lib().b200_tp_unique_id(buf, 128))
+        return buf.raw
+
+    @staticmethod
+    def tp_init(rank, world, nccl_id):
+        _check(lib().b200_tp_init(rank, world, nccl_id, len(nccl_id) if nccl_id else 0))
 
     def set_models_dir(self, d):
         _check(lib().b200_set_models_dir(d.encode()))

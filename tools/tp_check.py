@@ -1,0 +1,55 @@
+#!/usr/bin/env python
+"""Tensor-parallel parity check, run under torchrun (one rank per GPU): every rank loads its shard of the same GGUF,
+all ranks ingest the same prompt and take batched decode steps; the logits must agree with the CPU oracle within the
+quantisation tolerance and be bit-identical on all ranks.  Exit code 0 = pass."""
+import os, sys
+import numpy as np
+import torch
+import torch.distributed as dist
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tools")); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import make_gguf  # noqa: E402
+import nats_llm_studio_b200 as b200  # noqa: E402
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", "0"))
+dist.init_process_group("gloo")
+path = f"/tmp/b200-tp-check-{world}.gguf"
+if rank == 0:
+    make_gguf.write_model(path, make_gguf.spec_from_preset("small-llama", n_ff=3072, n_head_kv=max(2, world), n_head=8))
+dist.barrier()
+eng = b200.Engine(device=local, max_ctx=256, max_seqs=4)
+ids = [eng.tp_unique_id() if rank == 0 else None]
+dist.broadcast_object_list(ids, src=0)
+eng.tp_init(rank, world, ids[0])
+m = eng.load_file("tp/check", path)
+rng = np.random.default_rng(3)
+prompts = [rng.integers(0, m.n_vocab, n).astype(np.int32) for n in (40, 7, 90)]
+slots = np.array([2, 0, 3], np.int32)
+for p, s in zip(prompts, slots):
+    m.prefill_slot(int(s), p[:-1])
+cur = np.array([p[-1] for p in prompts], np.int32); pos = np.array([len(p) - 1 for p in prompts], np.int32)
+toks = []
+nxt, lg = m.batch_step(cur, slots, pos, want_logits=True)
+toks.append(nxt.copy()); cur = nxt; pos += 1
+for _ in range(4):
+    cur = m.batch_step(cur, slots, pos); toks.append(cur.copy()); pos += 1
+toks = np.stack(toks, 1)
+ok = True
+# identical on all ranks
+gl = [None] * world; dist.all_gather_object(gl, (lg.tobytes(), toks.tobytes()))
+ok &= all(g == gl[0] for g in gl)
+if rank == 0:
+    import orc
+    o = orc.Model(path)
+    for i, p in enumerate(prompts):
+        want, ref = o.generate(p, 1, want_logits=True)
+        scale = np.abs(ref[0]).max(); err = np.abs(lg[i] - ref[0]).max()
+        print(f"seq {i}: max|logit err| = {err:.4g} ({err / scale:.3%} of max |logit|), token {toks[i, 0]} vs oracle {want[0]}", flush=True)
+        ok &= bool(err <= 4e-2 * scale)
+        srt = np.sort(ref[0])
+        if srt[-1] - srt[-2] > 8e-2 * scale:
+            ok &= bool(toks[i, 0] == want[0])
+    print("TP CHECK", "PASS" if ok else "FAIL", f"world={world}", flush=True)
+flag = [ok]; dist.broadcast_object_list(flag, src=0)
+m.close(); eng.shutdown(); dist.destroy_process_group()
+sys.exit(0 if (ok and flag[0]) else 1)
