@@ -73,7 +73,10 @@ std::string Model::info_json() const {
     e.set("n_layer", Json::integer(n_layer)).set("n_embd", Json::integer(n_embd)).set("n_head", Json::integer(n_head)).set("n_head_kv", Json::integer(n_head_kv))
         .set("n_ff", Json::integer(n_ff)).set("n_vocab", Json::integer(n_vocab)).set("weight_bytes", Json::integer((long long)weight_bytes))
         .set("hbm_bytes", Json::integer((long long)hbm_bytes)).set("grid", Json::integer(grid)).set("ring_bytes", Json::integer(ring_bytes))
-        .set("n_phases", Json::integer(n_phases)).set("n_splits", Json::integer(n_splits));
+        .set("n_phases", Json::integer(n_phases)).set("n_splits", Json::integer(n_splits))
+        .set("tp_rank", Json::integer(engine().tp_rank)).set("tp_world", Json::integer(engine().tp_world))
+        .set("embd_bytes", Json::integer((long long)(meta.tensor("token_embd.weight") ? meta.tensor("token_embd.weight")->nbytes : 0)))
+        .set("kv_bytes_per_pos", Json::integer((long long)n_layer * 2 * n_head_kv * head_dim * 2));     // this rank's KV shard, fp16
     return json_dump(e);
 }
 

@@ -339,7 +339,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                     const int n = p >> 1, h = p & 1;
                     tmem_st_x8(a0 + (2 * n) * 32 + 8 * h, o);          tmem_st_x8(a0 + (2 * n) * 32 + 16 + 8 * h, o + 8);
                     tmem_st_x8(a0 + (2 * n + 1) * 32 + 8 * h, o + 16); tmem_st_x8(a0 + (2 * n + 1) * 32 + 16 + 8 * h, o + 24);
-                } else tmem_st_x32(a0 + p * 32, o);
+                } else if (!(P.debug & 64)) tmem_st_x32(a0 + p * 32, o);
             }
             tmem_st_wait();
             tcgen05_fence_before();

@@ -48,6 +48,7 @@ class ModelSpec:
     mode: str = "quantize"         # "quantize" | "bytes"
     seed: int = 1
     tied: bool = False             # no output.weight (granite-3.0-2b ties embeddings)
+    reuse_layers: bool = False     # every layer repeats the bytes of the first layer with the same (tensor, type): fast to write, same size
     gain: float = 1.0
     out_gain: float = 1.0
     name: str = "synthetic"
@@ -246,15 +247,23 @@ def write_model(path: str, spec: ModelSpec, verbose: bool = False) -> dict:
     D, F, HD = spec.n_embd, spec.n_ff, spec.hd
     total = 0
 
+    cache = {}
+
     def add_matrix(name: str, rows: int, K: int, qt: QT, gain: float):
         nonlocal total
         sigma = gain / np.sqrt(K)
+        key = (name.split(".")[-2], qt, rows, K)
+        if spec.reuse_layers and key in cache:
+            w.add_tensor(name, cache[key], raw_dtype=qt); total += cache[key].nbytes
+            return
         if spec.mode == "bytes":
             data = random_block_bytes(rng, rows, K, qt, sigma)
         else:
             data = quantize_rows(rng.standard_normal((rows, K), dtype=np.float32) * np.float32(sigma), qt)
         w.add_tensor(name, data, raw_dtype=qt)
         total += data.nbytes
+        if spec.reuse_layers:
+            cache[key] = data
         if verbose:
             print(f"  {name:32s} {qt.name:5s} {rows}x{K} {data.nbytes/1e6:.1f} MB", file=sys.stderr)
 
