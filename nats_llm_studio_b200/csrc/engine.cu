@@ -1056,7 +1056,19 @@ int layout_selftest() {
                 }
             for (int h : hits) if (h != 1) return fail(B200_ERR_INVALID, "layout selftest: raw byte not covered exactly once");
         }
+        // tile layout of the dequant-in-GEMM path (qgemm.cuh): every blob byte names one raw byte of one of the 128 rows'
+        // blocks of the K-step, and every such raw byte is named exactly once
+        const int blob = qg_blob_bytes(t), blocks_per_step = QG_KSTEP / be;
+        if (blob != QG_ROWS * blocks_per_step * bb) return fail(B200_ERR_INVALID, "layout selftest: tile blob size");
+        std::vector<int> seen((size_t)blob, 0);
+        for (int o = 0; o < blob; o++) {
+            int row, blk, i; tile_src(t, o, row, blk, i);
+            if (row < 0 || row >= QG_ROWS || blk < 0 || blk >= blocks_per_step || i < 0 || i >= bb) return fail(B200_ERR_INVALID, "layout selftest: tile_src out of range");
+            seen[((size_t)row * blocks_per_step + blk) * bb + i]++;
+        }
+        for (int h : seen) if (h != 1) return fail(B200_ERR_INVALID, "layout selftest: tile layout does not cover every raw byte exactly once");
     }
+    for (int k = 0; k < 64; k++) if (kperm4(kperm4(k)) != k || (kperm4(k) & ~3) != (k & ~3)) return fail(B200_ERR_INVALID, "layout selftest: kperm4");
     return B200_OK;
 }
 
