@@ -667,7 +667,7 @@ int Model::ensure_bf16_weights() {
     Engine& E = engine();
     const int D = n_embd, F = n_ff, QD = n_head * head_dim, KVD = n_head_kv * head_dim;
     auto deq = [&](const Matrix& m, __nv_bfloat16* dst) {
-        dequant_bf16_kernel<<<nblk(m.n_rows * (long long)m.K / 2), 256, 0, E.stream>>>(m.w, m.type, m.n_rows, m.K, dst); E.launches++;
+        dequant_bf16_kernel<<<nblk(m.n_rows * (long long)m.K / 16, 256, 148 * 32), 256, 0, E.stream>>>(m.w, m.type, m.n_rows, m.K, dst); E.launches++;
     };
     int rc;
     for (int l = 0; l < n_layer; l++) {
@@ -730,7 +730,7 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
     // or how rows were packed: a request's result does not depend on the load it ran under)
     if (q) { if (int rc0 = ensure_tile_weights()) return rc0; }
     auto deq = [&](const Matrix& m, __nv_bfloat16* dst) {
-        dequant_bf16_kernel<<<nblk(m.n_rows * (long long)m.K / 2), 256, 0, E.stream>>>(m.w, m.type, m.n_rows, m.K, dst); E.launches++;
+        dequant_bf16_kernel<<<nblk(m.n_rows * (long long)m.K / 16, 256, 148 * 32), 256, 0, E.stream>>>(m.w, m.type, m.n_rows, m.K, dst); E.launches++;
     };
     const int rms_threads = std::min(1024, std::max(128, (D / 4 + 31) / 32 * 32));     // one float4 per thread where the row allows
     int rc; QgSplit sp{}, none{};                                    // sp: partial tiles the next row kernel must complete

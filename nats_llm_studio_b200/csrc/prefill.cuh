@@ -205,13 +205,63 @@ __device__ __forceinline__ void qg_gather(const QgSplit& sp, int b, int col, flo
 }
 
 // ------------------------------------------------------------------------------------ row-wise kernels
-// engine-layout quantised matrix -> bf16 [n_rows x K] (row r of the matrix at out + r*K)
+// engine-layout quantised matrix -> bf16 [n_rows x K] (row r of the matrix at out + r*K).  One thread expands one run of
+// 16 consecutive elements (16 packed bytes + the block's scales -> 32 bytes of bf16); float op order is the bit-exact
+// dequantiser's (quant.cuh dequant_elem), the result is rounded to bf16 once.
+__device__ __forceinline__ void dequant_run16(const uint8_t* __restrict__ w, int type, int n_grp, int row, int run, float* v) {
+    const int gb = group_bytes(type), g = run >> 7, ug = run & 127;                       // 128 runs per 2048-element group
+    const uint8_t* base = w + (((size_t)(row >> 1) * n_grp + g) * 2 + (row & 1)) * gb;
+    if (type == T_Q8_0) {                                                                 // plane p = ug % 4 of lane ug / 4; block ug / 2
+        const uint4 q = *(const uint4*)(base + (ug & 3) * 512 + (ug >> 2) * 16);
+        const float d = h2f(*(const uint16_t*)(base + 2048 + (ug >> 1) * 2));
+        const uint32_t x[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int i = 0; i < 16; i++) v[i] = __fmul_rn((float)(int8_t)(x[i >> 2] >> (8 * (i & 3))), d);
+        return;
+    }
+    const int sb = ug >> 4, u = ug & 15;                                                  // super-block in group, run in super-block
+    if (type == T_Q4_K || type == T_Q5_K) {
+        const int bb = block_bytes(type), j = u >> 1, half = u & 1;                        // sub-block j (32 elements), its first/second 16
+        const uint8_t* blk = base + sb * bb;
+        const uint4 hd = *(const uint4*)blk;                                              // d, dmin, 12 engine-form scale bytes
+        const uint32_t sw[3] = {hd.y, hd.z, hd.w}; const int j2 = j >> 1, bit = 24 * j2;  // 24-bit field of chunk j2
+        const uint32_t f = bit % 32 == 0 ? sw[bit / 32] : (bit / 32 < 2 ? __funnelshift_r(sw[bit / 32], sw[bit / 32 + 1], bit % 32) : sw[2] >> (bit % 32));
+        const int sc = (f >> (6 * (j & 1))) & 63, mn = (f >> (12 + 6 * (j & 1))) & 63;
+        const float dl = __fmul_rn(h2f(hd.x & 0xFFFF), (float)sc), ml = __fmul_rn(h2f(hd.x >> 16), (float)mn);
+        const uint4 q = *(const uint4*)(blk + (type == T_Q4_K ? 16 : 48) + 32 * j2 + 16 * half);
+        uint4 hq = make_uint4(0, 0, 0, 0);
+        if (type == T_Q5_K) hq = *(const uint4*)(blk + 16 + 16 * half);
+        const uint32_t x[4] = {q.x, q.y, q.z, q.w}, hx[4] = {hq.x, hq.y, hq.z, hq.w};
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            int qv = (x[i >> 2] >> (8 * (i & 3) + 4 * (j & 1))) & 0xF;
+            if (type == T_Q5_K) qv |= ((hx[i >> 2] >> (8 * (i & 3) + j)) & 1) << 4;
+            v[i] = __fsub_rn(__fmul_rn(dl, (float)qv), ml);
+        }
+        return;
+    }
+    // Q6_K: run u -> 128-half n, 32-group grp, 16-run k; lane L = sb*4 + 2n + k holds its ql/qh bytes and scales
+    const int n = u >> 3, grp = (u & 7) >> 1, k = u & 1, L = sb * 4 + 2 * n + k;
+    const uint4 ql = *(const uint4*)(base + ((grp & 1) ? 512 : 0) + L * 16), qh = *(const uint4*)(base + 1024 + L * 16);
+    const float d = h2f(*(const uint16_t*)(base + 1664 + sb * 2));
+    const float dl = __fmul_rn(d, (float)(int8_t)base[1536 + L * 4 + grp]);
+    const uint32_t x[4] = {ql.x, ql.y, ql.z, ql.w}, hx[4] = {qh.x, qh.y, qh.z, qh.w};
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        const int lo = (x[i >> 2] >> (8 * (i & 3) + (grp >= 2 ? 4 : 0))) & 0xF, hi = (hx[i >> 2] >> (8 * (i & 3) + 2 * grp)) & 3;
+        v[i] = __fmul_rn(dl, (float)((lo | (hi << 4)) - 32));
+    }
+}
 __global__ void dequant_bf16_kernel(const uint8_t* __restrict__ w, int type, long long n_rows, int K, __nv_bfloat16* __restrict__ out) {
-    const int ng = n_groups(K);
-    for (long long i = (blockIdx.x * (long long)blockDim.x + threadIdx.x) * 2; i < n_rows * K; i += (long long)gridDim.x * blockDim.x * 2) {
-        const int row = (int)(i / K), e = (int)(i % K);
-        const float a = embed_elem(w, type, ng, row, e), b = embed_elem(w, type, ng, row, e + 1);
-        *(__nv_bfloat162*)(out + i) = __floats2bfloat162_rn(a, b);
+    const int ng = n_groups(K), rpr = K / 16;                                             // runs per row
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_rows * rpr; i += (long long)gridDim.x * blockDim.x) {
+        const int row = (int)(i / rpr), run = (int)(i % rpr);
+        float v[16]; dequant_run16(w, type, ng, row, run, v);
+        uint32_t o[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) o[j] = pack16x2(v[2 * j], v[2 * j + 1], false);
+        uint4* dst = (uint4*)(out + (size_t)row * K + run * 16);
+        dst[0] = make_uint4(o[0], o[1], o[2], o[3]); dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
     }
 }
 
