@@ -18,7 +18,7 @@
 
 namespace b200 {
 
-constexpr int GEMM_BM = 128, GEMM_BN = 128, GEMM_BK = 64, GEMM_STAGES = 4;
+constexpr int GEMM_BM = 128, GEMM_BN = 128, GEMM_BK = 64, GEMM_STAGES = 3;   // 3 stages = 97 KB: two CTAs per SM, one's epilogue overlaps the other's main loop
 constexpr int GEMM_THREADS = 128;
 constexpr uint32_t GEMM_STAGE_BYTES = (GEMM_BM + GEMM_BN) * GEMM_BK * 2;      // 32 KB
 constexpr size_t GEMM_SMEM = GEMM_STAGES * GEMM_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
@@ -80,7 +80,7 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t* r) 
 // ------------------------------------------------------------------------------------ the GEMM
 // C[M x N] fp32 row-major (ldc).  mode 0: C = acc * scale; mode 1: C += acc * scale (residual add).
 // One 128x128 output tile per CTA; K is a multiple of 64; M, N edges are zero-filled by TMA and masked on store.
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 2)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, float* __restrict__ C,
                   int M, int N, int K, int ldc, int mode, float scale) {
     extern __shared__ uint8_t gemm_smem_raw[];
@@ -193,12 +193,26 @@ __device__ __forceinline__ void qg_gather(const QgSplit& sp, int b, int col, flo
     float acc[N];
 #pragma unroll
     for (int i = 0; i < N; i++) acc[i] = 0.f;
-    for (int c = c_lo; c <= c_hi; c++) {
-        const int cb = (int)((long long)c * sp.T / sp.G);
-        const float* src = sp.ws + ((size_t)(c * 2 + (cb >= t0 ? 0 : 1)) * QG_WS_B + b) * QG_WS_N + (nl & 127);
-        if (N == 4) { const float4 p = __ldcg((const float4*)src); acc[0] += p.x; acc[1] += p.y; acc[2 % N] += p.z; acc[3 % N] += p.w; }
-        else if (N == 2) { const float2 p = __ldcg((const float2*)src); acc[0] += p.x; acc[1] += p.y; }
-        else acc[0] += __ldcg(src);
+    for (int c0 = c_lo; c0 <= c_hi; c0 += 8) {                      // eight parts' loads in flight at a time, summed in CTA order
+        float part[8][N];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+#pragma unroll
+            for (int i = 0; i < N; i++) part[j][i] = 0.f;
+            const int c = c0 + j;
+            if (c <= c_hi) {
+                const int cb = (int)((long long)c * sp.T / sp.G);
+                const float* src = sp.ws + ((size_t)(c * 2 + (cb >= t0 ? 0 : 1)) * QG_WS_B + b) * QG_WS_N + (nl & 127);
+                if (N == 4) { const float4 p = __ldcg((const float4*)src); part[j][0] = p.x; part[j][1] = p.y; part[j][2 % N] = p.z; part[j][3 % N] = p.w; }
+                else if (N == 2) { const float2 p = __ldcg((const float2*)src); part[j][0] = p.x; part[j][1] = p.y; }
+                else part[j][0] = __ldcg(src);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; j++) if (c0 + j <= c_hi) {
+#pragma unroll
+            for (int i = 0; i < N; i++) acc[i] += part[j][i];
+        }
     }
 #pragma unroll
     for (int i = 0; i < N; i++) v[i] = sp.mode == 1 ? v[i] + acc[i] * sp.scale : acc[i] * sp.scale;
