@@ -603,6 +603,16 @@ static int gemm_bf16(Engine& E, const __nv_bfloat16* A, const __nv_bfloat16* B, 
     return B200_OK;
 }
 
+// launch with programmatic stream serialization (see pdl_wait / pdl_launch_dependents in prefill.cuh)
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*k)(KArgs...), dim3 g, dim3 b, size_t smem, cudaStream_t st, Args&&... args) {
+    static const bool off = getenv("B200_NO_PDL") != nullptr;
+    cudaLaunchConfig_t cfg = {}; cfg.gridDim = g; cfg.blockDim = b; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1]; at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = off ? 0 : 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, k, std::forward<Args>(args)...);
+}
+
 // ---- dequant-in-GEMM (qgemm.cuh): C[b][n] (+)= scale * X[b][:] . W[n][:] for up to three matrices that share X (K-permuted fp16, B <= 64 rows)
 struct QMat { const Matrix* m; float* C; };
 // `sp` (out): what the consuming row kernel needs to complete the tiles stream-K split across CTAs (sp->ws == nullptr
@@ -633,7 +643,9 @@ static int qgemm(Engine& E, const QMat* mats, int n_mat, const __nv_bfloat16* X,
     if (!attr) { CK(cudaFuncSetAttribute(qgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, E.smem_optin)); attr = true; }
     CUtensorMap tx; if (int rc = make_tmap(&tx, X, (uint64_t)B, (uint64_t)K, QG_NB)) return rc;
     const int G = std::min(E.n_sm, whole ? tiles : steps);              // every CTA gets at least one K-step
-    qgemm_kernel<<<G, QG_THREADS, qg_smem_bytes(slot, P.n_raw), E.stream>>>(tx, P);
+    // programmatic dependent launch: the CTAs may start their prologue and fill the weight ring while the preceding row
+    // kernel is still running; the kernel waits (griddepcontrol.wait) before touching activations or results
+    CK(launch_pdl(qgemm_kernel, dim3(G), dim3(QG_THREADS), qg_smem_bytes(slot, P.n_raw), E.stream, tx, P));
     CK(cudaGetLastError());
     E.launches++;
     if (!whole) { sp->ws = E.qg_ws; sp->T = steps; sp->G = G; sp->ks = P.ks; sp->n_seg = n_mat; sp->mode = mode; sp->scale = scale * (1.f / QG_PRESCALE); }
@@ -738,7 +750,7 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
     for (int l = 0; l < n_layer; l++) {
         Layer& L = layers[l];
         const __nv_bfloat16 *wqkv = L.b_qkv, *wo = L.b_o, *wgu = L.b_gu, *wd = L.b_d;
-        rmsnorm_rows_kernel<<<M, rms_threads, 0, E.stream>>>(pf_H, L.attn_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
+        CK(launch_pdl(rmsnorm_rows_kernel, dim3(M), dim3(rms_threads), 0, E.stream, pf_H, (const float*)L.attn_norm, D, M, rms_eps, pf_X, q, sp)); E.launches++; sp = none;
         if (q) {
             const QMat qkv[3] = {{&L.wq, pf_Y}, {&L.wk, pf_Y + QD}, {&L.wv, pf_Y + QD + KVD}};
             if ((rc = qgemm(E, qkv, 3, pf_X, M, D, W3, 0, 1.f, false, &sp))) return rc;
@@ -746,10 +758,10 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
             if (!bf16_ready) { deq(L.wq, pf_W); deq(L.wk, pf_W + (size_t)QD * D); deq(L.wv, pf_W + (size_t)(QD + KVD) * D); wqkv = pf_W; }
             if ((rc = gemm_bf16(E, pf_X, wqkv, pf_Y, M, W3, D, W3, 0, 1.f))) return rc;
         }
-        rope_kv_rows_kernel<<<nblk((long long)M * W3 / 2), 256, 0, E.stream>>>(pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, inv_freq, kv, pf_Q, sp); E.launches++; sp = none;
+        CK(launch_pdl(rope_kv_rows_kernel, dim3(nblk((long long)M * W3 / 2)), dim3(256), 0, E.stream, (const float*)pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, (const float*)inv_freq, kv, pf_Q, sp)); E.launches++; sp = none;
         {
             const int G = n_head / n_head_kv; const dim3 ag(M * n_head_kv);
-#define B200_ATTN(HD_, G_) attn_rows_kernel<HD_, G_><<<ag, ATTN_WARPS * 32, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q)
+#define B200_ATTN(HD_, G_) CK(launch_pdl(attn_rows_kernel<HD_, G_>, ag, dim3(ATTN_WARPS * 32), 0, E.stream, (const __nv_bfloat16*)pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q))
             if (head_dim == 128 && G == 4) B200_ATTN(128, 4); else if (head_dim == 128 && G == 8) B200_ATTN(128, 8);
             else if (head_dim == 128 && G == 2) B200_ATTN(128, 2); else if (head_dim == 128 && G == 1) B200_ATTN(128, 1);
             else if (head_dim == 64 && G == 4) B200_ATTN(64, 4); else if (head_dim == 64 && G == 8) B200_ATTN(64, 8);
@@ -770,13 +782,13 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
         if (tp && (rc = tp_reduce_add(M, sp))) return rc;
         if (tp) sp = none;
         if (l == n_layer - 1 && !want_logits) break;                  // KV fill only: the last layer's FFN feeds nothing
-        rmsnorm_rows_kernel<<<M, rms_threads, 0, E.stream>>>(pf_H, L.ffn_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
+        CK(launch_pdl(rmsnorm_rows_kernel, dim3(M), dim3(rms_threads), 0, E.stream, pf_H, (const float*)L.ffn_norm, D, M, rms_eps, pf_X, q, sp)); E.launches++; sp = none;
         if (q) { const QMat gu{&L.wgu, pf_Y}; if ((rc = qgemm(E, &gu, 1, pf_X, M, D, 2 * F, 0, 1.f, false, &sp))) return rc; }
         else {
             if (!bf16_ready) { deq(L.wgu, pf_W); wgu = pf_W; }
             if ((rc = gemm_bf16(E, pf_X, wgu, pf_Y, M, 2 * F, D, 2 * F, 0, 1.f))) return rc;
         }
-        swiglu_rows_kernel<<<nblk((long long)M * F), 256, 0, E.stream>>>(pf_Y, M, F, pf_ACT, q, sp); E.launches++; sp = none;
+        CK(launch_pdl(swiglu_rows_kernel, dim3(nblk((long long)M * F)), dim3(256), 0, E.stream, (const float*)pf_Y, M, F, pf_ACT, q, sp)); E.launches++; sp = none;
         if (q) { const QMat dn{&L.wd, resid}; if ((rc = qgemm(E, &dn, 1, pf_ACT, M, F, D, rmode, rs, false, &sp))) return rc; }
         else {
             if (!bf16_ready) { deq(L.wd, pf_W); wd = pf_W; }
@@ -790,7 +802,7 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
         // an all-gather makes every part visible everywhere (argmax / sampling then run replicated)
         const int ldv = (n_vocab_l + 3) & ~3; const float ls = logit_scale != 0.f ? 1.f / logit_scale : 1.f;
         float* mine = tp ? bt_logits + (size_t)E.tp_world * M * ldv : bt_logits;       // scratch behind the gathered parts
-        rmsnorm_rows_kernel<<<M, rms_threads, 0, E.stream>>>(pf_H, out_norm, D, M, rms_eps, pf_X, q, sp); E.launches++; sp = none;
+        CK(launch_pdl(rmsnorm_rows_kernel, dim3(M), dim3(rms_threads), 0, E.stream, pf_H, (const float*)out_norm, D, M, rms_eps, pf_X, q, sp)); E.launches++; sp = none;
         if (q) { const QMat o{&out_w, mine}; if ((rc = qgemm(E, &o, 1, pf_X, M, D, ldv, 0, ls, true, &sp))) return rc; sp = none; }
         else {
             if (!bf16_ready) return fail(B200_ERR_STATE, "logits through the dense path need the bf16 weight cache");
@@ -869,7 +881,7 @@ int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* 
     CK(cudaMemcpyAsync(pf_toks + 2 * Mc, slots, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
     if (int rc = dense_rows(pf_toks, B, pf_toks + Mc, pf_toks + 2 * Mc, 0, 0, true, use_qgemm(B))) return rc;
     const int ldv = (n_vocab_l + 3) & ~3, Wp = E.tp_world;
-    argmax_rows_kernel<<<B, 1024, 0, E.stream>>>(bt_logits, n_vocab_l, ldv, Wp, (size_t)B * ldv, bt_next); E.launches++;
+    CK(launch_pdl(argmax_rows_kernel, dim3(B), dim3(1024), 0, E.stream, (const float*)bt_logits, n_vocab_l, ldv, Wp, (size_t)B * ldv, bt_next)); E.launches++;
     CK(cudaMemcpyAsync(next, bt_next, (size_t)B * 4, cudaMemcpyDeviceToHost, E.stream));
     if (logits) for (int p = 0; p < Wp; p++)
         CK(cudaMemcpy2DAsync(logits + (size_t)p * n_vocab_l, (size_t)n_vocab * 4, bt_logits + (size_t)p * B * ldv, (size_t)ldv * 4, (size_t)n_vocab_l * 4, B, cudaMemcpyDeviceToHost, E.stream));

@@ -175,6 +175,13 @@ __device__ __forceinline__ unsigned short pack16(float a, bool f16) {
 // How a stream-K dequant-in-GEMM launch (qgemm.cuh) left its result: row tiles whose whole K range ran in one CTA are
 // final in C; the others exist as fp32 partials of the contributing CTAs (consecutive CTA indices = ascending K).  The
 // row kernel that consumes C sums them on the fly, in CTA order — no reduction pass, no atomics, deterministic.
+// Programmatic dependent launch: the dequant-in-GEMM kernel that follows a row kernel is launched with
+// programmaticStreamSerialization, so its CTAs may start (barrier init, TMEM allocation, weight ring fill — nothing that
+// depends on this kernel) as soon as every CTA of the row kernel has passed this point; it waits (griddepcontrol.wait)
+// before it touches activations or results.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 struct QgSplit {
     const float* ws;            // [cta][2 slots][64 batch rows][128 tile rows]; nullptr = nothing to gather
     int T, G, ks, n_seg, mode;  // total K-steps, CTAs, K-steps per tile, matrices in the launch, 1 = result is added to C
@@ -294,6 +301,7 @@ __global__ void embed_rows_kernel(const uint8_t* __restrict__ embd, int type, in
 __global__ void __launch_bounds__(1024) rmsnorm_rows_kernel(float* __restrict__ H, const float* __restrict__ w, int D, int M, float eps, __nv_bfloat16* __restrict__ X, bool perm,
                                                            const __grid_constant__ QgSplit sp) {
     __shared__ float red[32];
+    pdl_launch_dependents(); pdl_wait();
     const int m = blockIdx.x, tid = threadIdx.x, nth = blockDim.x;
     float* h = H + (size_t)m * D; float ss = 0.f;
     for (int i = tid * 4; i < D; i += nth * 4) {
@@ -317,6 +325,7 @@ __global__ void __launch_bounds__(1024) rmsnorm_rows_kernel(float* __restrict__ 
 // QKV[m][QD + 2*KVD] fp32 -> RoPE(q) as bf16 Q[m][QD]; RoPE(k), v -> fp16 KV pages at position pos0 + m
 __global__ void rope_kv_rows_kernel(const float* __restrict__ QKV, int M, RowMap rm, int layer, int n_head, int n_head_kv, int HD, int n_rot,
                                     const float* __restrict__ inv_freq, KvLayout kv, __nv_bfloat16* __restrict__ Q, const __grid_constant__ QgSplit sp) {
+    pdl_launch_dependents(); pdl_wait();
     const int QD = n_head * HD, KVD = n_head_kv * HD, W = QD + 2 * KVD;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)M * (W / 2); i += (long long)gridDim.x * blockDim.x) {
         const int m = (int)(i / (W / 2)), c = (int)(i % (W / 2)) * 2, pos = rm.p(m), slot = rm.s(m);
@@ -391,6 +400,7 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32, 2) attn_rows_kernel(const __n
     __shared__ __align__(16) float sq[G][HD];
     __shared__ float sm_m[NW][G], sm_l[NW][G];
     __shared__ float sm_acc[NW][G][HD];
+    pdl_launch_dependents(); pdl_wait();
     const int m = blockIdx.x / n_head_kv, kvh = blockIdx.x % n_head_kv, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int n_ctx = rm.p(m) + 1, slot = rm.s(m);
     for (int i = tid; i < G * HD; i += NW * 32) { const int g = i / HD, d = i % HD; sq[g][d] = __bfloat162float(Q[(size_t)m * n_head * HD + (kvh * G + g) * HD + d]) * kq_scale; }
@@ -488,6 +498,7 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32, 2) attn_rows_kernel(const __n
 // column is token p * V.
 __global__ void argmax_rows_kernel(const float* __restrict__ logits, int V, int ld, int n_parts, size_t part_stride, int* __restrict__ next) {
     __shared__ float sv[32]; __shared__ int si[32];
+    pdl_launch_dependents(); pdl_wait();
     float bv = -INFINITY; int bi = 0x7fffffff;
     const int V4 = V & ~3;                                           // rows start 16-byte aligned (ld % 4 == 0)
     for (int p = 0; p < n_parts; p++) {
@@ -510,6 +521,7 @@ __global__ void argmax_rows_kernel(const float* __restrict__ logits, int V, int 
 
 // ACT[m][i] = bf16(silu(GU[m][2i]) * GU[m][2i+1])   (gate/up rows are interleaved in the fused matrix)
 __global__ void swiglu_rows_kernel(const float* __restrict__ GU, int M, int F, __nv_bfloat16* __restrict__ ACT, bool perm, const __grid_constant__ QgSplit sp) {
+    pdl_launch_dependents(); pdl_wait();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)M * F; i += (long long)gridDim.x * blockDim.x) {
         float2 gu = *(const float2*)(GU + 2 * i);
         if (sp.ws) { float t[2] = {gu.x, gu.y}; qg_gather<2>(sp, (int)(i / F), (int)(2 * (i % F)), t); gu = make_float2(t[0], t[1]); }

@@ -235,6 +235,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
         S.tmem_slot = (uint32_t*)(S.acc_empty + 2);
     }
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    pdl_launch_dependents();                           // the consuming row kernel may be scheduled; it waits for this grid to finish
     if (tid == 0) {
         for (int i = 0; i < P.n_raw; i++) { mbar_init(&S.raw_full[i], 1); mbar_init(&S.raw_empty[i], QG_DQ_WARPS / 2); }
         for (int i = 0; i < QG_X_STEPS; i++) { mbar_init(&S.x_full[i], 1); mbar_init(&S.x_empty[i], 1); }
@@ -268,6 +269,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
         }
     } else if (warp == 1) {                            // ===== activation producer: four 64 x 64 fp16 boxes per K-step =====
         if (lane == 0) {
+            pdl_wait();                                // the activations come from the preceding kernel (programmatic dependent launch)
             int it = 0;
             for (int s = s_begin; s < s_end; s++, it++) {
                 const QSeg& sg = P.seg[qg_seg_of_step(P, s)];
@@ -348,6 +350,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
         }
     } else {                                           // ===== epilogue warps: TMEM -> C (whole tile) or fp32 partial + last-arriver reduction =====
         const int q = warp & 3;                        // TMEM lane quadrant this warp may read
+        pdl_wait();                                    // C / the partials buffer may still be read by the preceding kernel
         int piece = 0, s = s_begin;
         const float scale = P.scale * (1.f / QG_PRESCALE);
         while (s < s_end) {
