@@ -98,8 +98,15 @@ __device__ __forceinline__ uint32_t h2sub(uint32_t a, uint32_t b) { uint32_t d; 
 __device__ __forceinline__ uint32_t h2mul(uint32_t a, uint32_t b) { uint32_t d; asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
 __device__ __forceinline__ uint32_t h2dup(float v) { uint32_t d; asm("cvt.rn.f16x2.f32 %0, %1, %1;" : "=r"(d) : "f"(v)); return d; }
 __device__ __forceinline__ float h16f(uint32_t bits) { return __half2float(__ushort_as_half((unsigned short)bits)); }
-__device__ __forceinline__ uint4 lds128(const uint8_t* p) { return *(const uint4*)p; }
+// explicit shared-space loads (a generic pointer into the dynamic shared array compiles to LD.E, not LDS)
+__device__ __forceinline__ uint4 lds128(uint32_t a) { uint4 v; asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds16(uint32_t a) { unsigned short v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a)); return v; }
 
+// (a & mask) | c in ONE LOP3: the mask is an immediate, c must sit in a register (an instruction has one immediate slot;
+// written as C the compiler folds both constants and emits two LOP3s).  h2_magic() hides the constant from the folder.
+template <uint32_t MASK> __device__ __forceinline__ uint32_t and_or_i(uint32_t a, uint32_t c) { uint32_t d; asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(d) : "r"(a), "n"(MASK), "r"(c)); return d; }
+__device__ __forceinline__ uint32_t h2_magic() { uint32_t m; asm volatile("mov.b32 %0, 0x64006400;" : "=r"(m)); return m; }
 constexpr uint32_t H2_MAGIC = 0x64006400u /*1024*/, H2_M1024 = 0xE400E400u, H2_1152 = 0x64806480u, H2_1056 = 0x64206420u;
 
 // ------------------------------------------------------------------------------------ tensor-memory stores / A-from-TMEM MMA
@@ -131,14 +138,14 @@ __device__ __forceinline__ void tcgen05_mma_f16_ts(uint32_t tmem_d, uint32_t tme
 // column c holds positions (2c, 2c+1), i.e. elements (e, e+2) or (e+1, e+3) of an aligned group of four (kperm4).
 // Q4_K / Q5_K: chunk j2 of the super-block (sub-blocks 2*j2: low nibbles -> columns 0..15, 2*j2+1: high -> 16..31)
 template <bool Q5>
-__device__ __forceinline__ void dq_k45(const uint8_t* raw, int row, int j2, uint32_t* o) {
+__device__ __forceinline__ void dq_k45(uint32_t raw, int row, int j2, uint32_t* o) {
     const uint4 hd = lds128(raw + row * 16);
     const uint32_t f = j2 == 0 ? hd.y : j2 == 1 ? __funnelshift_r(hd.y, hd.z, 24) : j2 == 2 ? __funnelshift_r(hd.z, hd.w, 16) : hd.w >> 8;
     const float d = h16f(hd.x & 0xFFFF) * QG_PRESCALE, dmin = h16f(hd.x >> 16) * QG_PRESCALE;
     const uint32_t S0 = h2dup(d * (float)(f & 63)), S1 = h2dup(d * (float)((f >> 6) & 63) * 0.0625f);
     const uint32_t M0 = h2dup(dmin * (float)((f >> 12) & 63)), M1 = h2dup(dmin * (float)((f >> 18) & 63));
-    const uint32_t C0 = h2mul(S0, H2_M1024), C1 = h2mul(S1, H2_M1024);
-    const uint8_t* qs = raw + 2048 + (Q5 ? 4096 : 0) + (size_t)(j2 * 2) * 2048 + row * 16;
+    const uint32_t C0 = h2mul(S0, H2_M1024), C1 = h2mul(S1, H2_M1024), MG = h2_magic();
+    const uint32_t qs = raw + 2048 + (Q5 ? 4096 : 0) + (j2 * 2) * 2048 + row * 16;
 #pragma unroll
     for (int h = 0; h < 2; h++) {
         const uint4 q = lds128(qs + h * 2048);
@@ -148,7 +155,7 @@ __device__ __forceinline__ void dq_k45(const uint8_t* raw, int row, int j2, uint
 #pragma unroll
         for (int w = 0; w < 4; w++) {                              // bytes l = 16h + 4w .. +3 -> columns 8h + 2w, +1 (low) and 16 + that (high)
             const uint32_t x = xs[w], y = x >> 8;
-            uint32_t l02 = (x & 0x000F000Fu) | H2_MAGIC, h02 = (x & 0x00F000F0u) | H2_MAGIC, l13 = (y & 0x000F000Fu) | H2_MAGIC, h13 = (y & 0x00F000F0u) | H2_MAGIC;
+            uint32_t l02 = and_or_i<0x000F000Fu>(x, MG), h02 = and_or_i<0x00F000F0u>(x, MG), l13 = and_or_i<0x000F000Fu>(y, MG), h13 = and_or_i<0x00F000F0u>(y, MG);
             if (Q5) {
                 const uint32_t a = hs[w] >> (2 * j2), b = a >> 8;
                 l02 |= (a << 4) & 0x00100010u; h02 |= (a << 7) & 0x01000100u; l13 |= (b << 4) & 0x00100010u; h13 |= (b << 7) & 0x01000100u;
@@ -160,12 +167,12 @@ __device__ __forceinline__ void dq_k45(const uint8_t* raw, int row, int j2, uint
 }
 
 // Q8_0: k-block kb of the K-step = blocks 2kb, 2kb+1 (columns 0..15, 16..31)
-__device__ __forceinline__ void dq_q80(const uint8_t* raw, int row, int kb, uint32_t* o) {
-    const uint32_t dd = *(const uint32_t*)(raw + 32768 + (kb * 128 + row) * 4);
+__device__ __forceinline__ void dq_q80(uint32_t raw, int row, int kb, uint32_t* o) {
+    const uint32_t dd = lds32(raw + 32768 + (kb * 128 + row) * 4);
     const uint32_t D0 = h2dup(h16f(dd & 0xFFFF) * QG_PRESCALE), D1 = h2dup(h16f(dd >> 16) * QG_PRESCALE);
 #pragma unroll
     for (int pc = 0; pc < 4; pc++) {
-        const uint4 q = lds128(raw + (size_t)((kb * 4 + pc) * 128 + row) * 16);
+        const uint4 q = lds128(raw + ((kb * 4 + pc) * 128 + row) * 16);
         const uint32_t xs[4] = {q.x, q.y, q.z, q.w}, D = pc < 2 ? D0 : D1;
 #pragma unroll
         for (int w = 0; w < 4; w++) {
@@ -179,27 +186,29 @@ __device__ __forceinline__ void dq_q80(const uint8_t* raw, int row, int kb, uint
 // Q6_K: for 128-half n and 16-run h, the 64 elements (grp 0..3) x (l in [16h, 16h+16)) of the row:
 // o[0..7] = grp 0 -> k-block 2n columns 8h..8h+7; o[8..15] = grp 1 -> k-block 2n columns 16+8h..; o[16..23] = grp 2 and
 // o[24..31] = grp 3 -> the same column ranges of k-block 2n+1
-__device__ __forceinline__ void dq_q6k(const uint8_t* raw, int row, int n, int h, uint32_t* o) {
-    const uint4 qa = lds128(raw + (size_t)((n * 4 + h) * 128 + row) * 16), qb = lds128(raw + (size_t)((n * 4 + 2 + h) * 128 + row) * 16);
-    const uint4 qh = lds128(raw + 16384 + (size_t)((n * 2 + h) * 128 + row) * 16);
-    const uint32_t sc = *(const uint32_t*)(raw + 24576 + ((n * 2 + h) * 128 + row) * 4);
-    const float d = h16f(*(const unsigned short*)(raw + 26624 + row * 2)) * QG_PRESCALE;
+__device__ __forceinline__ void dq_q6k(uint32_t raw, int row, int n, int h, uint32_t* o) {
+    const uint4 qa = lds128(raw + ((n * 4 + h) * 128 + row) * 16), qb = lds128(raw + ((n * 4 + 2 + h) * 128 + row) * 16);
+    const uint4 qh = lds128(raw + 16384 + ((n * 2 + h) * 128 + row) * 16);
+    const uint32_t sc = lds32(raw + 24576 + ((n * 2 + h) * 128 + row) * 4);
+    const float d = h16f(lds16(raw + 26624 + row * 2)) * QG_PRESCALE;
     const uint32_t S0 = h2dup(d * (float)(int8_t)(sc & 0xFF)), S1 = h2dup(d * (float)(int8_t)((sc >> 8) & 0xFF)),
                    S2 = h2dup(d * (float)(int8_t)((sc >> 16) & 0xFF)), S3 = h2dup(d * (float)(int8_t)(sc >> 24));
     const uint32_t as[4] = {qa.x, qa.y, qa.z, qa.w}, bs[4] = {qb.x, qb.y, qb.z, qb.w}, hs[4] = {qh.x, qh.y, qh.z, qh.w};
+    const uint32_t MG = h2_magic();
+#define Q6V(lo, hi) and_or_i<0x00300030u>((hi), and_or_i<0x000F000Fu>((lo), MG))      /* (lo & 0x000F000F) | (hi & 0x00300030) | 1024: two LOP3 */
 #pragma unroll
     for (int w = 0; w < 4; w++) {
         const uint32_t xa = as[w], xb = bs[w], hq = hs[w];
-        const uint32_t m4 = 0x000F000Fu, m2 = 0x00300030u;
-        o[2 * w]          = h2mul(h2sub(((xa)       & m4) | ((hq << 4) & m2) | H2_MAGIC, H2_1056), S0);
-        o[2 * w + 1]      = h2mul(h2sub(((xa >> 8)  & m4) | ((hq >> 4) & m2) | H2_MAGIC, H2_1056), S0);
-        o[8 + 2 * w]      = h2mul(h2sub(((xb)       & m4) | ((hq << 2) & m2) | H2_MAGIC, H2_1056), S1);
-        o[8 + 2 * w + 1]  = h2mul(h2sub(((xb >> 8)  & m4) | ((hq >> 6) & m2) | H2_MAGIC, H2_1056), S1);
-        o[16 + 2 * w]     = h2mul(h2sub(((xa >> 4)  & m4) | ((hq)      & m2) | H2_MAGIC, H2_1056), S2);
-        o[16 + 2 * w + 1] = h2mul(h2sub(((xa >> 12) & m4) | ((hq >> 8) & m2) | H2_MAGIC, H2_1056), S2);
-        o[24 + 2 * w]     = h2mul(h2sub(((xb >> 4)  & m4) | ((hq >> 2) & m2) | H2_MAGIC, H2_1056), S3);
-        o[24 + 2 * w + 1] = h2mul(h2sub(((xb >> 12) & m4) | ((hq >> 10) & m2) | H2_MAGIC, H2_1056), S3);
+        o[2 * w]          = h2mul(h2sub(Q6V(xa, hq << 4), H2_1056), S0);
+        o[2 * w + 1]      = h2mul(h2sub(Q6V(xa >> 8, hq >> 4), H2_1056), S0);
+        o[8 + 2 * w]      = h2mul(h2sub(Q6V(xb, hq << 2), H2_1056), S1);
+        o[8 + 2 * w + 1]  = h2mul(h2sub(Q6V(xb >> 8, hq >> 6), H2_1056), S1);
+        o[16 + 2 * w]     = h2mul(h2sub(Q6V(xa >> 4, hq), H2_1056), S2);
+        o[16 + 2 * w + 1] = h2mul(h2sub(Q6V(xa >> 12, hq >> 8), H2_1056), S2);
+        o[24 + 2 * w]     = h2mul(h2sub(Q6V(xb >> 4, hq >> 2), H2_1056), S3);
+        o[24 + 2 * w + 1] = h2mul(h2sub(Q6V(xb >> 12, hq >> 10), H2_1056), S3);
     }
+#undef Q6V
 }
 
 __host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N) {
@@ -321,7 +330,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
         for (int it = grp; s_begin + it < s_end; it += 2) {
             const int type = P.seg[qg_seg_of_step(P, s_begin + it)].type;
             const int rs = it % P.n_raw, as = it % QG_A_STEPS;
-            const uint8_t* raw = S.raw + (size_t)rs * P.slot_bytes;
+            const uint32_t raw = smem_u32(S.raw) + rs * P.slot_bytes;
             const uint32_t a0 = lane_base + as * 128;           // 4 k-blocks x 32 columns per K-step
             mbar_wait(&S.raw_full[rs], (it / P.n_raw) & 1);
 #pragma unroll
@@ -331,6 +340,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 if (P.debug & 1) {
 #pragma unroll
                     for (int i = 0; i < 32; i++) o[i] = 0;
+                    if (P.debug & 128) __nanosleep(150);
                 } else if (type == T_Q8_0) dq_q80(raw, row, p, o);
                 else if (type == T_Q6_K) dq_q6k(raw, row, p >> 1, p & 1, o);
                 else if (type == T_Q4_K) dq_k45<false>(raw, row, p, o);
