@@ -33,7 +33,8 @@ namespace b200 {
 
 constexpr int QG_ROWS = 128, QG_NB = 64, QG_KSTEP = 256;
 constexpr int QG_DQ_WARPS = 16, QG_FIRST_DQ = 3, QG_FIRST_EPI = QG_FIRST_DQ + QG_DQ_WARPS, QG_WARPS = QG_FIRST_EPI + 4, QG_THREADS = QG_WARPS * 32;
-constexpr int QG_A_STEPS = 3, QG_X_STEPS = 2, QG_MAX_RAW = 8, QG_MAX_TILES = 4096;
+// X and A rings have the same depth: one tcgen05.commit per K-step releases both (a second commit per step cost ~0.2 us)
+constexpr int QG_A_STEPS = 3, QG_X_STEPS = 3, QG_MAX_RAW = 8, QG_MAX_TILES = 4096;
 constexpr uint32_t QG_X_BYTES = 4 * QG_NB * 128;              // one K-step of activations: 4 k-blocks of 64 rows x 128 B
 constexpr uint32_t QG_TMEM_COLS = 512, QG_TMEM_A0 = 2 * QG_NB; // accumulators in columns [0,128), A ring in [128,512)
 constexpr float QG_PRESCALE = 16.f;
@@ -226,7 +227,7 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32_nowait(uint32_t taddr, uint32
 }
 
 // shared memory: X ring (2 K-steps, 1024-aligned) | raw-weight ring | barriers
-struct QgSmem { uint8_t *x, *raw; uint64_t *raw_full, *raw_empty, *x_full, *x_empty, *a_full, *a_empty, *acc_full, *acc_empty; uint32_t* tmem_slot; };
+struct QgSmem { uint8_t *x, *raw; uint64_t *raw_full, *raw_empty, *x_full, *x_empty /*unused: a_empty frees both*/, *a_full, *a_empty, *acc_full, *acc_empty; uint32_t* tmem_slot; };
 constexpr uint32_t QG_BAR_BYTES = 512;
 __host__ __device__ inline size_t qg_smem_bytes(uint32_t slot_bytes, int n_raw) { return 1024 + QG_X_STEPS * QG_X_BYTES + (size_t)n_raw * slot_bytes + QG_BAR_BYTES; }
 
@@ -283,7 +284,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
             for (int s = s_begin; s < s_end; s++, it++) {
                 const QSeg& sg = P.seg[qg_seg_of_step(P, s)];
                 const int kstep = (s - sg.step0) % P.ks, xs = it % QG_X_STEPS;
-                mbar_wait(&S.x_empty[xs], ((it / QG_X_STEPS) & 1) ^ 1);
+                mbar_wait(&S.a_empty[xs], ((it / QG_X_STEPS) & 1) ^ 1);       // freed together with the A slot of the same K-step
                 if (P.debug & 4) { mbar_arrive(&S.x_full[xs]); continue; }
                 mbar_expect_tx(&S.x_full[xs], QG_X_BYTES);
 #pragma unroll
@@ -314,8 +315,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                                 tcgen05_mma_f16_ts(tmem + buf * QG_NB, tmem + QG_TMEM_A0 + (as * 4 + kb) * 32 + k * 8, db + 2 * k, idesc, (i | kb | k) ? 1u : 0u);
                         }
                     }
-                    tcgen05_commit(&S.a_empty[as]);
-                    tcgen05_commit(&S.x_empty[xs]);
+                    tcgen05_commit(&S.a_empty[as]);                 // one commit per K-step frees both the A slot and the X slot (same ring depth)
                 }
                 tcgen05_commit(&S.acc_full[buf]);
                 s += n_st; piece++;
