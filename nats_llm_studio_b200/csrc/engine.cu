@@ -389,7 +389,7 @@ void Model::fill_params(DecodeParams& P) const {
     P.q_ll = d_ll32; P.part_ll = P.q_ll + QD; P.cand_ll = P.part_ll + (size_t)n_head * 16 * (head_dim + 2);
     P.hown_cap = hown_cap; (void)KVD;
     P.n_btab = std::min(pages_per_seq, BTAB_MAX);
-    P.kv.pages = d_kv; P.kv.block_table = d_block_table; P.kv.n_layer = n_layer; P.kv.n_head_kv = n_head_kv; P.kv.head_dim = head_dim; P.kv.pages_per_seq = pages_per_seq;
+    P.kv.pages = d_kv; P.kv.block_table = d_block_table; P.kv.n_layer = n_layer; P.kv.n_head_kv = n_head_kv; P.kv.head_dim = head_dim; P.kv.pages_per_seq = pages_per_seq; P.kv.n_pages = n_pages;
     P.pos = d_state + 0; P.token = d_state + 1; P.bar_ctr = (unsigned*)(d_state + 2); P.epoch = (unsigned*)(d_state + 3);
     P.out_tokens = d_out_tokens; P.n_steps = 1; P.want_argmax = 1; P.trace = d_trace;
 }
@@ -734,7 +734,7 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
     Engine& E = engine();
     const int D = n_embd, F = n_ff, QD = n_head * head_dim, KVD = n_head_kv * head_dim, W3 = QD + 2 * KVD;
     const float rs = res_scale != 0.f ? res_scale : 1.f, kq = attn_scale != 0.f ? attn_scale : 1.0f / std::sqrt((float)head_dim);
-    KvLayout kv; kv.pages = d_kv; kv.block_table = d_block_table; kv.n_layer = n_layer; kv.n_head_kv = n_head_kv; kv.head_dim = head_dim; kv.pages_per_seq = pages_per_seq;
+    KvLayout kv; kv.pages = d_kv; kv.block_table = d_block_table; kv.n_layer = n_layer; kv.n_head_kv = n_head_kv; kv.head_dim = head_dim; kv.pages_per_seq = pages_per_seq; kv.n_pages = n_pages;
     RowMap rm{d_pos, d_slot, pos0, slot0};
     // few rows (a decode batch): weights stay quantised and are expanded inside the GEMM; many rows (a prompt chunk):
     // expand to bf16 once per chunk (or use the cache) and run the dense tensor-core GEMM

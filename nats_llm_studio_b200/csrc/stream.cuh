@@ -112,20 +112,18 @@ struct Phase {
 };
 
 struct KvLayout {               // paged KV cache, fp16
-    __half* pages;              // [n_pages][n_layer][2][n_head_kv][16][head_dim]
+    __half* pages;              // [n_layer][n_pages][2][n_head_kv][16][head_dim]: layer-major, so that the pages one layer's
+                                // attention touches lie in one compact region (n_pages x 64 KB for 8 kv heads of 128) instead
+                                // of being strided by the size of a whole page across all layers (2 MB: a TLB miss per page)
     const int* block_table;     // [max_seqs][pages_per_seq]; the batch-1 decode kernel uses sequence slot 0
-    int n_layer, n_head_kv, head_dim, pages_per_seq;
-    __device__ __forceinline__ size_t page_elems() const { return (size_t)n_layer * 2 * n_head_kv * 16 * head_dim; }
+    int n_layer, n_head_kv, head_dim, pages_per_seq, n_pages;
     __device__ __forceinline__ __half* at_page(int page, int layer, int kv, int kvh, int pos) const {
-        return pages + (size_t)page * page_elems() + ((((size_t)layer * 2 + kv) * n_head_kv + kvh) * 16 + (pos & 15)) * head_dim;
+        return pages + (((((size_t)layer * n_pages + page) * 2 + kv) * n_head_kv + kvh) * 16 + (pos & 15)) * head_dim;
     }
     __device__ __forceinline__ __half* at_slot(int slot, int layer, int kv, int kvh, int pos) const {
         return at_page(block_table[slot * pages_per_seq + (pos >> 4)], layer, kv, kvh, pos);
     }
-    __device__ __forceinline__ __half* at(int layer, int kv, int kvh, int pos) const {
-        int page = block_table[pos >> 4];
-        return pages + (size_t)page * page_elems() + ((((size_t)layer * 2 + kv) * n_head_kv + kvh) * 16 + (pos & 15)) * head_dim;
-    }
+    __device__ __forceinline__ __half* at(int layer, int kv, int kvh, int pos) const { return at_page(block_table[pos >> 4], layer, kv, kvh, pos); }
 };
 
 struct DecodeParams {
