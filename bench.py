@@ -107,7 +107,8 @@ def cpu_reference_arm(path, n_prompt, n_gen):
     import numpy as np
     import orc
     m = orc.Model(path)
-    cores = orc.lib().orc_max_threads()
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    orc.lib().orc_set_threads(cores)            # torchrun exports OMP_NUM_THREADS=1: use every host core the process may run on
     rng = np.random.default_rng(3)
     prompt = rng.integers(0, m.n_vocab, n_prompt).astype(np.int32)
     t0 = time.perf_counter()
