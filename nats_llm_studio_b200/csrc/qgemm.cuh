@@ -34,7 +34,7 @@ namespace b200 {
 constexpr int QG_ROWS = 128, QG_NB = 64, QG_KSTEP = 256;
 constexpr int QG_DQ_WARPS = 16, QG_FIRST_DQ = 3, QG_FIRST_EPI = QG_FIRST_DQ + QG_DQ_WARPS, QG_WARPS = QG_FIRST_EPI + 4, QG_THREADS = QG_WARPS * 32;
 // X and A rings have the same depth: one tcgen05.commit per K-step releases both (a second commit per step cost ~0.2 us)
-constexpr int QG_A_STEPS = 3, QG_X_STEPS = 3, QG_MAX_RAW = 8, QG_MAX_TILES = 4096;
+constexpr int QG_A_STEPS = 3, QG_X_STEPS = QG_A_STEPS, QG_MAX_RAW = 8, QG_MAX_TILES = 4096;
 constexpr uint32_t QG_X_BYTES = 4 * QG_NB * 128;              // one K-step of activations: 4 k-blocks of 64 rows x 128 B
 constexpr uint32_t QG_TMEM_COLS = 512, QG_TMEM_A0 = 2 * QG_NB; // accumulators in columns [0,128), A ring in [128,512)
 constexpr float QG_PRESCALE = 16.f;
@@ -88,7 +88,8 @@ struct QSeg { const uint8_t* tl; float* C; int type, n_tiles, n_rows, step0, til
 struct QGemmParams {
     QSeg seg[3]; int n_seg, ks /*K-steps per tile*/, total_steps, n_tiles, B, ldc, mode, n_raw; float scale; float* ws; uint32_t slot_bytes;
     int whole;      // 1 = CTA ranges are aligned to tiles (no partials; for matrices with many more tiles than CTAs)
-    int debug;      // profiling only (B200_QG_DEBUG): 1 = skip the expansion math, 2 = skip the MMAs, 4 = no X loads, 8 = no weight loads
+    int debug;      // profiling only (B200_QG_DEBUG; results are then wrong): 1 = skip the expansion math, 2 = skip the MMAs, 4 = no X loads,
+                    // 8 = no weight loads, 16 = launch + TMEM alloc/dealloc only, 64 = skip the tensor-memory stores, 128 (with 1) = sleep instead of math
 };
 
 __device__ __forceinline__ int qg_seg_of_step(const QGemmParams& P, int s) { int i = 0; while (i + 1 < P.n_seg && s >= P.seg[i + 1].step0) i++; return i; }
@@ -227,7 +228,7 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32_nowait(uint32_t taddr, uint32
 }
 
 // shared memory: X ring (2 K-steps, 1024-aligned) | raw-weight ring | barriers
-struct QgSmem { uint8_t *x, *raw; uint64_t *raw_full, *raw_empty, *x_full, *x_empty /*unused: a_empty frees both*/, *a_full, *a_empty, *acc_full, *acc_empty; uint32_t* tmem_slot; };
+struct QgSmem { uint8_t *x, *raw; uint64_t *raw_full, *raw_empty, *x_full, *a_full, *a_empty /* frees the A slot and the X slot of a K-step */, *acc_full, *acc_empty; uint32_t* tmem_slot; };
 constexpr uint32_t QG_BAR_BYTES = 512;
 __host__ __device__ inline size_t qg_smem_bytes(uint32_t slot_bytes, int n_raw) { return 1024 + QG_X_STEPS * QG_X_BYTES + (size_t)n_raw * slot_bytes + QG_BAR_BYTES; }
 
@@ -240,15 +241,15 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
         uint8_t* base = (uint8_t*)(((uintptr_t)qg_smem_raw + 1023) & ~(uintptr_t)1023);
         S.x = base; S.raw = S.x + QG_X_STEPS * QG_X_BYTES;
         uint64_t* b = (uint64_t*)(S.raw + (size_t)P.n_raw * P.slot_bytes);
-        S.raw_full = b; S.raw_empty = b + QG_MAX_RAW; S.x_full = b + 2 * QG_MAX_RAW; S.x_empty = S.x_full + QG_X_STEPS;
-        S.a_full = S.x_empty + QG_X_STEPS; S.a_empty = S.a_full + QG_A_STEPS; S.acc_full = S.a_empty + QG_A_STEPS; S.acc_empty = S.acc_full + 2;
+        S.raw_full = b; S.raw_empty = b + QG_MAX_RAW; S.x_full = b + 2 * QG_MAX_RAW;
+        S.a_full = S.x_full + QG_X_STEPS; S.a_empty = S.a_full + QG_A_STEPS; S.acc_full = S.a_empty + QG_A_STEPS; S.acc_empty = S.acc_full + 2;
         S.tmem_slot = (uint32_t*)(S.acc_empty + 2);
     }
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     pdl_launch_dependents();                           // the consuming row kernel may be scheduled; it waits for this grid to finish
     if (tid == 0) {
         for (int i = 0; i < P.n_raw; i++) { mbar_init(&S.raw_full[i], 1); mbar_init(&S.raw_empty[i], QG_DQ_WARPS / 2); }
-        for (int i = 0; i < QG_X_STEPS; i++) { mbar_init(&S.x_full[i], 1); mbar_init(&S.x_empty[i], 1); }
+        for (int i = 0; i < QG_X_STEPS; i++) mbar_init(&S.x_full[i], 1);
         for (int i = 0; i < QG_A_STEPS; i++) { mbar_init(&S.a_full[i], QG_DQ_WARPS / 2); mbar_init(&S.a_empty[i], 1); }
         for (int i = 0; i < 2; i++) { mbar_init(&S.acc_full[i], 1); mbar_init(&S.acc_empty[i], 4); }
         fence_barrier_init();
@@ -378,7 +379,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
             if (lane == 0) mbar_arrive(&S.acc_empty[buf]);      // registers hold the tile: the accumulator may be reused
             const int n = tl * QG_ROWS + q * 32 + lane;
             float* dst = sg.C + n;
-            if (n_st == P.ks || (P.debug & 32)) {
+            if (n_st == P.ks) {
                 if (n < sg.n_rows) {
 #pragma unroll
                     for (int b = 0; b < QG_NB; b++)
