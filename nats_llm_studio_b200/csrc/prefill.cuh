@@ -391,10 +391,10 @@ __global__ void attn_prefill_kernel(const __nv_bfloat16* __restrict__ Q, int M, 
 // computed one position per lane (no shuffles in the dot products), probabilities are broadcast by shuffle for the
 // P.V accumulation (one output-dim slice per lane, eight V rows in flight), and the warps' online-softmax states are
 // merged in shared memory.
-constexpr int ATTN_WARPS = 8;
+constexpr int ATTN_WARPS = 4;
 __device__ __forceinline__ float2 h2_to_f2(uint32_t u) { return __half22float2(*reinterpret_cast<const __half2*>(&u)); }
 template <int HD, int G>
-__global__ void __launch_bounds__(ATTN_WARPS * 32, 2) attn_rows_kernel(const __nv_bfloat16* __restrict__ Q, int M, RowMap rm, int layer, int n_head, int n_head_kv,
+__global__ void __launch_bounds__(ATTN_WARPS * 32, 4) attn_rows_kernel(const __nv_bfloat16* __restrict__ Q, int M, RowMap rm, int layer, int n_head, int n_head_kv,
                                                                    float kq_scale, KvLayout kv, __nv_bfloat16* __restrict__ O, bool perm) {
     constexpr int DPL = HD / 32, NW = ATTN_WARPS;
     __shared__ __align__(16) float sq[G][HD];
@@ -451,18 +451,19 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32, 2) attn_rows_kernel(const __n
         const int last = n_ctx - 1 - p0;                                           // >= 0
         const __half* vb0 = kv.at_slot(slot, layer, 1, kvh, p0) + lane * DPL;      // 16 positions of a page are contiguous
         const __half* vb1 = last >= 16 ? kv.at_slot(slot, layer, 1, kvh, p0 + 16) + lane * DPL : vb0;
+        constexpr int NBV = (DPL == 4 && G <= 4) ? 16 : 8;                          // V rows in flight per lane (registers permitting)
 #pragma unroll
-        for (int pp0 = 0; pp0 < 32; pp0 += 8) {
+        for (int pp0 = 0; pp0 < 32; pp0 += NBV) {
             if (pp0 > last) break;
-            uint2 vv[8];
+            uint2 vv[NBV];
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
+            for (int j = 0; j < NBV; j++) {
                 const int pp = min(pp0 + j, last);
                 const __half* vp = (pp < 16 ? vb0 : vb1) + (size_t)(pp & 15) * HD;
                 if (DPL == 4) vv[j] = *(const uint2*)vp; else { vv[j].x = *(const uint32_t*)vp; vv[j].y = 0; }
             }
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
+            for (int j = 0; j < NBV; j++) {
                 const float2 a = h2_to_f2(vv[j].x), b = h2_to_f2(vv[j].y);
                 const float v[4] = {a.x, a.y, b.x, b.y};
 #pragma unroll

@@ -105,3 +105,27 @@ def test_scheduler_continuous_batching(engine, golden_dir):
         f = fin[100 + i]
         assert f.finish_reason == b200.FINISH_LENGTH and f.n_generated == n_gen[i] and f.n_prompt == lens[i] and f.ttft_ms > 0
     m.close()
+
+
+def test_scheduler_prompts_straddle_prefill_chunks(engine, golden_dir):
+    """Prompts longer than one 512-row chunk, packed back to back: a request's prompt is split across chunks shared with
+    other requests; its tokens must still equal the solo run (prefill numerics do not depend on the packing)."""
+    m = engine.load_file("bt/straddle", os.path.join(golden_dir, "tiny-llama.gguf"))
+    lens = [600, 300, 450, 20, 700]
+    prompts = _prompts(m.n_vocab, lens, seed=17)
+    want = [_run(m, [p], np.array([0], np.int32), 5)[0] for p in prompts]
+    for i, p in enumerate(prompts):
+        m.submit(p, 500 + i, max_tokens=5)
+    got = {500 + i: [] for i in range(len(prompts))}; fin = set()
+    while len(fin) < len(prompts):
+        evs = engine.poll(64, 5000)
+        assert evs, "scheduler made no progress"
+        for e in evs:
+            assert e.kind != b200.EV_ERROR, e.finish_reason
+            if e.kind == b200.EV_TOKEN:
+                got[e.req_id].append(e.token)
+            else:
+                fin.add(e.req_id)
+    for i in range(len(prompts)):
+        assert np.array_equal(np.array(got[500 + i], np.int32), want[i]), i
+    m.close()
