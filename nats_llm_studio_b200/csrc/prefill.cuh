@@ -195,7 +195,9 @@ __device__ __forceinline__ void qg_gather(const QgSplit& sp, int b, int col, flo
     if (!sp.ws) return;
     int si = 0; while (si + 1 < sp.n_seg && col >= sp.col0[si + 1]) si++;
     const int nl = col - sp.col0[si], t0 = sp.step0[si] + (nl >> 7) * sp.ks;
-    const int c_lo = (int)(((long long)(t0 + 1) * sp.G + sp.T - 1) / sp.T) - 1, c_hi = (int)(((long long)(t0 + sp.ks) * sp.G + sp.T - 1) / sp.T) - 1;
+    // 32-bit unsigned arithmetic on purpose (steps x CTAs < 2^31 is checked on the host): this runs once per group of columns
+    const unsigned uT = (unsigned)sp.T, uG = (unsigned)sp.G;
+    const int c_lo = (int)(((unsigned)(t0 + 1) * uG + uT - 1) / uT) - 1, c_hi = (int)(((unsigned)(t0 + sp.ks) * uG + uT - 1) / uT) - 1;
     if (c_lo == c_hi) return;                                       // tile was not split: C is final
     float acc[N];
 #pragma unroll
@@ -208,7 +210,7 @@ __device__ __forceinline__ void qg_gather(const QgSplit& sp, int b, int col, flo
             for (int i = 0; i < N; i++) part[j][i] = 0.f;
             const int c = c0 + j;
             if (c <= c_hi) {
-                const int cb = (int)((long long)c * sp.T / sp.G);
+                const int cb = (int)((unsigned)c * uT / uG);
                 const float* src = sp.ws + ((size_t)(c * 2 + (cb >= t0 ? 0 : 1)) * QG_WS_B + b) * QG_WS_N + (nl & 127);
                 if (N == 4) { const float4 p = __ldcg((const float4*)src); part[j][0] = p.x; part[j][1] = p.y; part[j][2 % N] = p.z; part[j][3 % N] = p.w; }
                 else if (N == 2) { const float2 p = __ldcg((const float2*)src); part[j][0] = p.x; part[j][1] = p.y; }
