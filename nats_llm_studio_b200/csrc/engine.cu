@@ -788,7 +788,7 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
             if (!bf16_ready) { deq(L.wgu, pf_W); wgu = pf_W; }
             if ((rc = gemm_bf16(E, pf_X, wgu, pf_Y, M, 2 * F, D, 2 * F, 0, 1.f))) return rc;
         }
-        CK(launch_pdl(swiglu_rows_kernel, dim3(nblk((long long)M * F)), dim3(256), 0, E.stream, (const float*)pf_Y, M, F, pf_ACT, q, sp)); E.launches++; sp = none;
+        CK(launch_pdl(swiglu_rows_kernel, dim3(nblk((long long)M * F / 4)), dim3(256), 0, E.stream, (const float*)pf_Y, M, F, pf_ACT, q, sp)); E.launches++; sp = none;
         if (q) { const QMat dn{&L.wd, resid}; if ((rc = qgemm(E, &dn, 1, pf_ACT, M, F, D, rmode, rs, false, &sp))) return rc; }
         else {
             if (!bf16_ready) { deq(L.wd, pf_W); wd = pf_W; }

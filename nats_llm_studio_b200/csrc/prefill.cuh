@@ -212,7 +212,8 @@ __device__ __forceinline__ void qg_gather(const QgSplit& sp, int b, int col, flo
             if (c <= c_hi) {
                 const int cb = (int)((unsigned)c * uT / uG);
                 const float* src = sp.ws + ((size_t)(c * 2 + (cb >= t0 ? 0 : 1)) * QG_WS_B + b) * QG_WS_N + (nl & 127);
-                if (N == 4) { const float4 p = __ldcg((const float4*)src); part[j][0] = p.x; part[j][1] = p.y; part[j][2 % N] = p.z; part[j][3 % N] = p.w; }
+                if (N == 8) { const float4 p = __ldcg((const float4*)src), q = __ldcg((const float4*)src + 1); part[j][0] = p.x; part[j][1] = p.y; part[j][2 % N] = p.z; part[j][3 % N] = p.w; part[j][4 % N] = q.x; part[j][5 % N] = q.y; part[j][6 % N] = q.z; part[j][7 % N] = q.w; }
+                else if (N == 4) { const float4 p = __ldcg((const float4*)src); part[j][0] = p.x; part[j][1] = p.y; part[j][2 % N] = p.z; part[j][3 % N] = p.w; }
                 else if (N == 2) { const float2 p = __ldcg((const float2*)src); part[j][0] = p.x; part[j][1] = p.y; }
                 else part[j][0] = __ldcg(src);
             }
@@ -525,10 +526,19 @@ __global__ void argmax_rows_kernel(const float* __restrict__ logits, int V, int 
 // ACT[m][i] = bf16(silu(GU[m][2i]) * GU[m][2i+1])   (gate/up rows are interleaved in the fused matrix)
 __global__ void swiglu_rows_kernel(const float* __restrict__ GU, int M, int F, __nv_bfloat16* __restrict__ ACT, bool perm, const __grid_constant__ QgSplit sp) {
     pdl_launch_dependents(); pdl_wait();
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)M * F; i += (long long)gridDim.x * blockDim.x) {
-        float2 gu = *(const float2*)(GU + 2 * i);
-        if (sp.ws) { float t[2] = {gu.x, gu.y}; qg_gather<2>(sp, (int)(i / F), (int)(2 * (i % F)), t); gu = make_float2(t[0], t[1]); }
-        ((unsigned short*)ACT)[perm ? (i - i % 4 + kperm4((int)(i % 4))) : i] = pack16(gu.x / (1.f + __expf(-gu.x)) * gu.y, perm);
+    // four outputs (eight interleaved gate/up columns: one tile, one partial lookup) per thread; F % 4 == 0
+    const long long n4 = (long long)M * (F / 4);
+    for (long long i4 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i4 < n4; i4 += (long long)gridDim.x * blockDim.x) {
+        const int m = (int)(i4 / (F / 4)), f0 = (int)(i4 % (F / 4)) * 4;
+        const float4* src = (const float4*)(GU + (size_t)m * 2 * F + 2 * f0);
+        const float4 a = src[0], b = src[1];
+        float t[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        if (sp.ws) qg_gather<8>(sp, m, 2 * f0, t);
+        float o[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) o[k] = t[2 * k] / (1.f + __expf(-t[2 * k])) * t[2 * k + 1];
+        uint2 w = perm ? make_uint2(pack16x2(o[0], o[2], true), pack16x2(o[1], o[3], true)) : make_uint2(pack16x2(o[0], o[1], false), pack16x2(o[2], o[3], false));
+        *(uint2*)(ACT + (size_t)m * F + f0) = w;
     }
 }
 
