@@ -641,7 +641,10 @@ static int qgemm(Engine& E, const QMat* mats, int n_mat, const __nv_bfloat16* X,
     if (const char* dbg = getenv("B200_QG_DEBUG")) P.debug = atoi(dbg);
     static bool attr = false;
     if (!attr) { CK(cudaFuncSetAttribute(qgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, E.smem_optin)); attr = true; }
-    CUtensorMap tx; if (int rc = make_tmap(&tx, X, (uint64_t)B, (uint64_t)K, QG_NB)) return rc;
+    // the activation tensor map always spans QG_NB rows of real memory (callers pass a buffer of at least QG_NB x K; rows
+    // >= B hold stale finite-or-not values whose accumulator columns are never stored): a box that hangs over the end of a
+    // shorter tensor (zero fill) faulted here when it ran next to the weight ring's bulk copies
+    CUtensorMap tx; if (int rc = make_tmap(&tx, X, (uint64_t)QG_NB, (uint64_t)K, QG_NB)) return rc;
     const int G = std::min(E.n_sm, whole ? tiles : steps);              // every CTA gets at least one K-step
     // programmatic dependent launch: the CTAs may start their prologue and fill the weight ring while the preceding row
     // kernel is still running; the kernel waits (griddepcontrol.wait) before touching activations or results
@@ -899,7 +902,8 @@ int kernel_qgemm(int type, const void* raw, int64_t N, int K, const float* x, in
     uint8_t *d_raw = nullptr, *d_tl = nullptr; __nv_bfloat16* d_x = nullptr; float* d_y = nullptr; int rc;
     auto cleanup = [&]() { cudaFree(d_raw); cudaFree(m.w); cudaFree(d_tl); cudaFree(d_x); cudaFree(d_y); };
     if ((rc = dalloc(&d_raw, (size_t)N * rb)) || (rc = dalloc(&m.w, repacked_bytes(type, Np, K))) || (rc = dalloc(&d_tl, tile_bytes(type, Np, K))) ||
-        (rc = dalloc(&d_x, (size_t)B * K)) || (rc = dalloc(&d_y, (size_t)B * N))) { cleanup(); return rc; }
+        (rc = dalloc(&d_x, (size_t)QG_NB * K)) || (rc = dalloc(&d_y, (size_t)B * N))) { cleanup(); return rc; }
+    cudaMemsetAsync(d_x, 0, (size_t)QG_NB * K * 2, E.stream);
     std::vector<__nv_bfloat16> hx((size_t)B * K);
     for (int b = 0; b < B; b++) for (int k = 0; k < K; k++) { const __half h = __float2half_rn(x[(size_t)b * K + kperm4(k)]); memcpy(&hx[(size_t)b * K + k], &h, 2); }
     cudaMemcpyAsync(d_raw, raw, (size_t)N * rb, cudaMemcpyHostToDevice, E.stream);

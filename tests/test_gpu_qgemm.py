@@ -57,6 +57,22 @@ def test_qgemm_matches_numpy(engine, t, shape):
     assert np.array_equal(y, engine.qgemm(t, raw, N, K, x))  # stream-K partials are summed in a fixed order
 
 
+def test_qgemm_many_tiles_small_batch(engine):
+    """Regression: a matrix with many row tiles (every CTA's K range crosses a tile boundary) and only 1-2 activation rows,
+    Q8_0 (largest blobs, shortest weight ring).  The activation box used to hang over the end of a B-row tensor."""
+    N, K = 14336, 4096
+    rng = np.random.default_rng(21)
+    raw = random_rows(rng, "Q8_0", N, K)
+    W = orc.dequantize("Q8_0", raw, N * K).reshape(N, K)
+    for B in (1, 2):
+        x = rng.standard_normal((B, K)).astype(np.float32)
+        y = engine.qgemm("Q8_0", raw, N, K, x)
+        xh = x.astype(np.float16).astype(np.float32)
+        want = xh @ W.T
+        mag = np.abs(xh) @ np.abs(W).T
+        assert np.all(np.abs(y - want) <= 2e-3 * mag + 1e-6)
+
+
 def test_qgemm_rows_do_not_depend_on_batch(engine):
     N, K = 1024, 2048
     rng = np.random.default_rng(9)

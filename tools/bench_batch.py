@@ -25,8 +25,12 @@ def measure(eng, m, n_req=64, gen=128, prompt_min=64, prompt_max=512, step_iters
     prompts = [rng.integers(0, m.n_vocab, n).astype(np.int32) for n in lens]
     # warm-up: one request end to end (builds the tile-layout / bf16 weight copies), then a few full-batch steps
     m.submit(prompts[0], 1, max_tokens=4)
-    while not any(e.kind != b200.EV_TOKEN for e in eng.poll(64, 60000)):
-        pass
+    done = False
+    while not done:
+        for e in eng.poll(64, 60000):
+            if e.kind == b200.EV_ERROR:
+                raise SystemExit(f"warm-up request failed: {e.finish_reason}")
+            done |= e.kind == b200.EV_FINISH
     slots = np.arange(n_req, dtype=np.int32); pos = np.full(n_req, 300, np.int32); cur = rng.integers(0, m.n_vocab, n_req).astype(np.int32)
     for _ in range(3):
         m.batch_step(cur, slots, pos)
