@@ -19,7 +19,12 @@
 namespace b200 {
 
 thread_local std::string g_last_error;
-int fail(int code, const std::string& msg) { g_last_error = msg; return code; }
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    static const bool log = getenv("B200_LOG_ERRORS") != nullptr;       // errors raised on the scheduler thread are otherwise only visible as event codes
+    if (log) fprintf(stderr, "[b200] error %d: %s\n", code, msg.c_str());
+    return code;
+}
 
 #define CK(expr)                                                                                              \
     do {                                                                                                      \
@@ -180,6 +185,7 @@ static int repack(Engine& E, const uint8_t* raw, uint8_t* out, int type, int64_t
 Model::~Model() { release(); }
 
 void Model::release() {
+    for (auto& g : step_graph) if (g) { cudaGraphExecDestroy(g); g = nullptr; }
     for (void* p : owned) cudaFree(p);
     owned.clear();
     if (d_raw) { cudaFree(d_raw); d_raw = nullptr; }
@@ -634,7 +640,8 @@ static int qgemm(Engine& E, const QMat* mats, int n_mat, const __nv_bfloat16* X,
     }
     P.n_seg = n_mat; P.total_steps = steps; P.n_tiles = tiles; P.B = B; P.ldc = ldc; P.mode = mode; P.scale = scale; P.slot_bytes = slot; P.whole = whole ? 1 : 0;
     const size_t fixed = qg_smem_bytes(0, 0);
-    P.n_raw = (int)std::min<size_t>(QG_MAX_RAW, ((size_t)E.smem_optin - fixed) / slot);
+    P.n_raw = (int)std::min<size_t>(QG_MAX_RAW, ((size_t)E.smem_optin - fixed) / slot) & ~1;      // even, see QG_A_STEPS
+    if (const char* nr = getenv("B200_QG_NRAW")) P.n_raw = std::max(2, std::min(P.n_raw, atoi(nr)) & ~1);
     if (P.n_raw < 2) return fail(B200_ERR_UNSUPPORTED, "qgemm: shared memory too small");
     if (!E.qg_ws) { if (int rc = dalloc(&E.qg_ws, (size_t)E.n_sm * 2 * QG_NB * QG_ROWS)) return rc; }
     P.ws = E.qg_ws;
@@ -648,7 +655,9 @@ static int qgemm(Engine& E, const QMat* mats, int n_mat, const __nv_bfloat16* X,
     const int G = std::min(E.n_sm, whole ? tiles : steps);              // every CTA gets at least one K-step
     // programmatic dependent launch: the CTAs may start their prologue and fill the weight ring while the preceding row
     // kernel is still running; the kernel waits (griddepcontrol.wait) before touching activations or results
-    CK(launch_pdl(qgemm_kernel, dim3(G), dim3(QG_THREADS), qg_smem_bytes(slot, P.n_raw), E.stream, tx, P));
+    { cudaError_t le = launch_pdl(qgemm_kernel, dim3(G), dim3(QG_THREADS), qg_smem_bytes(slot, P.n_raw), E.stream, tx, P);
+      if (le != cudaSuccess) return fail(B200_ERR_CUDA, std::string("qgemm_kernel launch (") + std::to_string(n_mat) + " matrices, type " + std::to_string(P.seg[0].type) + ", K " + std::to_string(K) +
+                                         ", tiles " + std::to_string(tiles) + ", B " + std::to_string(B) + ", raw slots " + std::to_string(P.n_raw) + ", whole " + std::to_string(P.whole) + "): " + cudaGetErrorString(le)); }
     CK(cudaGetLastError());
     E.launches++;
     if (!whole) { sp->ws = E.qg_ws; sp->T = steps; sp->G = G; sp->ks = P.ks; sp->n_seg = n_mat; sp->mode = mode; sp->scale = scale * (1.f / QG_PRESCALE); }
@@ -882,9 +891,38 @@ int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* 
     CK(cudaMemcpyAsync(pf_toks, toks, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
     CK(cudaMemcpyAsync(pf_toks + Mc, pos, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
     CK(cudaMemcpyAsync(pf_toks + 2 * Mc, slots, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
-    if (int rc = dense_rows(pf_toks, B, pf_toks + Mc, pf_toks + 2 * Mc, 0, 0, true, use_qgemm(B))) return rc;
     const int ldv = (n_vocab_l + 3) & ~3, Wp = E.tp_world;
-    CK(launch_pdl(argmax_rows_kernel, dim3(B), dim3(1024), 0, E.stream, (const float*)bt_logits, n_vocab_l, ldv, Wp, (size_t)B * ldv, bt_next)); E.launches++;
+    const bool q = use_qgemm(B);
+    auto body = [&]() -> int {
+        if (int rc = dense_rows(pf_toks, B, pf_toks + Mc, pf_toks + 2 * Mc, 0, 0, true, q)) return rc;
+        CK(launch_pdl(argmax_rows_kernel, dim3(B), dim3(1024), 0, E.stream, (const float*)bt_logits, n_vocab_l, ldv, Wp, (size_t)B * ldv, bt_next)); E.launches++;
+        return B200_OK;
+    };
+    // The step is a fixed chain of ~9 launches per layer whose arguments depend only on B (tokens, positions and slots are
+    // read from device buffers): the second time a batch size is seen the chain is captured into a CUDA graph and replayed
+    // from then on.  With the weights split over 8 GPUs the kernels are short enough that issuing ~1400 launches (NCCL
+    // included) from the host was the bound of the step.
+    static const bool graphs_on = getenv("B200_NO_GRAPH") == nullptr;
+    if (step_graph.empty()) { step_graph.assign(QG_NB + 1, nullptr); step_seen.assign(QG_NB + 1, 0); step_launches.assign(QG_NB + 1, 0); }
+    if (q && graphs_on && !graph_failed && step_graph[B]) {
+        CK(cudaGraphLaunch(step_graph[B], E.stream)); E.launches += step_launches[B];
+    } else if (q && graphs_on && !graph_failed && step_seen[B]) {
+        cudaGraph_t g = nullptr; const uint64_t l0 = E.launches;
+        cudaError_t ce = cudaStreamBeginCapture(E.stream, cudaStreamCaptureModeThreadLocal);
+        int rc = ce == cudaSuccess ? body() : B200_ERR_CUDA;
+        cudaError_t ee = cudaStreamEndCapture(E.stream, &g);
+        if (rc == B200_OK && ee == cudaSuccess && g && cudaGraphInstantiate(&step_graph[B], g, 0) == cudaSuccess) {
+            step_launches[B] = (int)(E.launches - l0);
+            CK(cudaGraphLaunch(step_graph[B], E.stream));
+        } else {                                                   // capture not possible here: stay with direct launches
+            graph_failed = true; step_graph[B] = nullptr; cudaGetLastError(); E.launches = l0;
+            if (int rc2 = body()) return rc2;
+        }
+        if (g) cudaGraphDestroy(g);
+    } else {
+        if (int rc = body()) return rc;
+        step_seen[B] = 1;                                          // buffers, tile weights and function attributes now exist
+    }
     CK(cudaMemcpyAsync(next, bt_next, (size_t)B * 4, cudaMemcpyDeviceToHost, E.stream));
     if (logits) for (int p = 0; p < Wp; p++)
         CK(cudaMemcpy2DAsync(logits + (size_t)p * n_vocab_l, (size_t)n_vocab * 4, bt_logits + (size_t)p * B * ldv, (size_t)ldv * 4, (size_t)n_vocab_l * 4, B, cudaMemcpyDeviceToHost, E.stream));

@@ -106,6 +106,7 @@ struct Model {
     int prefill_rows(const int32_t* toks, const int32_t* slots, const int32_t* pos, int M);
     void maybe_bf16_cache();
     bool bf16_tried = false;
+    std::vector<cudaGraphExec_t> step_graph; std::vector<char> step_seen; std::vector<int> step_launches; bool graph_failed = false;   // batch_step: one CUDA graph per batch size
     int prefill_slot(int slot, const int32_t* toks, int n, int pos0);
     int prefill(const int32_t* toks, int n);
     int batch_step(const int32_t* toks, const int32_t* slots, const int32_t* pos, int B, int32_t* next, float* logits = nullptr);

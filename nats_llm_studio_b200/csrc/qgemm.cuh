@@ -3,11 +3,11 @@
 // The weights are read ONCE per step in their quantised form (the op is HBM-bound at B <= 64),
 // expanded to fp16 by 16 dequant warps and contracted on the tensor cores: tcgen05.mma kind::f16 with
 //   A = 128 weight rows, fp16, written by the dequant warps straight into TENSOR MEMORY (tcgen05.st; lane = row,
-//       one 32-bit column = two K positions) — a ring of 12 k-blocks (3 K-steps) in TMEM columns 128..511,
+//       one 32-bit column = two K positions) — a ring of 8 k-blocks (2 K-steps) in TMEM columns 128..383,
 //   B = the 64 activation rows (fp16, TMA, 128-byte swizzle, shared memory),
 //   D = fp32 accumulators in TMEM columns 0..127 (two of 64 columns, ping-pong between tiles).
 // Keeping A out of shared memory leaves ~160 KB for the raw-weight ring (bulk copies in flight) and lets the
-// expansion run up to three K-steps ahead of the MMAs.
+// expansion run two K-steps ahead of the MMAs.
 //
 // Tile layout ("TL", built once from the streaming layout by tile_repack_kernel): the matrix is cut into tiles of
 // 128 rows and K-steps of 256 elements; the bytes of one (tile, K-step) are one contiguous blob = one bulk copy,
@@ -33,8 +33,12 @@ namespace b200 {
 
 constexpr int QG_ROWS = 128, QG_NB = 64, QG_KSTEP = 256;
 constexpr int QG_DQ_WARPS = 16, QG_FIRST_DQ = 3, QG_FIRST_EPI = QG_FIRST_DQ + QG_DQ_WARPS, QG_WARPS = QG_FIRST_EPI + 4, QG_THREADS = QG_WARPS * 32;
-// X and A rings have the same depth: one tcgen05.commit per K-step releases both (a second commit per step cost ~0.2 us)
-constexpr int QG_A_STEPS = 3, QG_X_STEPS = QG_A_STEPS, QG_MAX_RAW = 8, QG_MAX_TILES = 4096;
+// X and A rings have the same depth: one tcgen05.commit per K-step releases both (a second commit per step cost ~0.2 us).
+// Every ring depth is EVEN: the two expansion groups take alternate K-steps, so with an even depth a ring slot (and its
+// barriers) is always used by the same group, which then sees every phase of them; with an odd depth a group comes back to
+// a barrier only every second phase, and a parity wait cannot tell phase n from phase n+2 (seen as sporadic launch failures
+// with a 3-deep Q8_0 weight ring).
+constexpr int QG_A_STEPS = 2, QG_X_STEPS = QG_A_STEPS, QG_MAX_RAW = 8, QG_MAX_TILES = 4096;
 constexpr uint32_t QG_X_BYTES = 4 * QG_NB * 128;              // one K-step of activations: 4 k-blocks of 64 rows x 128 B
 constexpr uint32_t QG_TMEM_COLS = 512, QG_TMEM_A0 = 2 * QG_NB; // accumulators in columns [0,128), A ring in [128,512)
 constexpr float QG_PRESCALE = 16.f;
