@@ -420,13 +420,14 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32, 4) attn_rows_kernel(const __n
         for (int g = 0; g < G; g++) s[g] = 0.f;
         {
             const __half* kp = kv.at_slot(slot, layer, 0, kvh, ok ? p : n_ctx - 1);      // clamped: masked below
-#pragma unroll 1
-            for (int j0 = 0; j0 < HD / 8; j0 += 8) {
-                uint4 kk[8];
+            constexpr int KB = HD >= 128 ? 8 : 4;                                   // K pieces in flight per lane; at least two trips, or the
+#pragma unroll 1                                                                   // compiler hoists every q load of the chunk and spills
+            for (int j0 = 0; j0 < HD / 8; j0 += KB) {
+                uint4 kk[KB];
 #pragma unroll
-                for (int j = 0; j < 8; j++) kk[j] = *(const uint4*)(kp + 8 * (j0 + j));
+                for (int j = 0; j < KB; j++) kk[j] = *(const uint4*)(kp + 8 * (j0 + j));
 #pragma unroll
-                for (int j = 0; j < 8; j++) {
+                for (int j = 0; j < KB; j++) {
                     const float2 k0 = h2_to_f2(kk[j].x), k1 = h2_to_f2(kk[j].y), k2 = h2_to_f2(kk[j].z), k3 = h2_to_f2(kk[j].w);
 #pragma unroll
                     for (int g = 0; g < G; g++) {
