@@ -1122,6 +1122,16 @@ int layout_selftest() {
         }
         for (int h : seen) if (h != 1) return fail(B200_ERR_INVALID, "layout selftest: tile layout does not cover every raw byte exactly once");
     }
+    // stream-K arithmetic: the CTA ranges tile [0, T) in order, and qg_cta_of_step inverts qg_cta_first_step
+    for (int G : {1, 7, 148}) for (int T : {1, 5, 147, 148, 149, 512, 768, 1792, 3584, 16032, 60000}) {
+        if (qg_cta_first_step(0, T, G) != 0 || qg_cta_first_step(G, T, G) != T) return fail(B200_ERR_INVALID, "layout selftest: stream-K ranges do not cover [0, T)");
+        for (int c = 0; c < G; c++) {
+            const int b = qg_cta_first_step(c, T, G), e = qg_cta_first_step(c + 1, T, G);
+            if (e < b) return fail(B200_ERR_INVALID, "layout selftest: stream-K range is not monotone");
+            for (int st = b; st < e; st += std::max(1, (e - b) / 3)) if (qg_cta_of_step(st, T, G) != c) return fail(B200_ERR_INVALID, "layout selftest: qg_cta_of_step");
+            if (e > b && qg_cta_of_step(e - 1, T, G) != c) return fail(B200_ERR_INVALID, "layout selftest: qg_cta_of_step at a range end");
+        }
+    }
     for (int k = 0; k < 64; k++) if (kperm4(kperm4(k)) != k || (kperm4(k) & ~3) != (k & ~3)) return fail(B200_ERR_INVALID, "layout selftest: kperm4");
     return B200_OK;
 }

@@ -189,15 +189,17 @@ struct QgSplit {
     float scale;
 };
 constexpr int QG_WS_B = 64, QG_WS_N = 128;
+// Stream-K arithmetic, one definition for the kernel, the gather and the self-test (32-bit: steps x CTAs < 2^31 is checked on
+// the host).  CTA c owns the global K-steps [c*T/G, (c+1)*T/G); the CTA that owns step s is ceil((s+1)*G/T) - 1.
+__host__ __device__ inline int qg_cta_first_step(int c, int T, int G) { return (int)((unsigned)c * (unsigned)T / (unsigned)G); }
+__host__ __device__ inline int qg_cta_of_step(int s, int T, int G) { return (int)(((unsigned)(s + 1) * (unsigned)G + (unsigned)T - 1) / (unsigned)T) - 1; }
 // v[0..N) = final values of C[b][col .. col+N) given `v` = what C holds now (N consecutive columns of one 4-aligned group)
 template <int N>
 __device__ __forceinline__ void qg_gather(const QgSplit& sp, int b, int col, float* v) {
     if (!sp.ws) return;
     int si = 0; while (si + 1 < sp.n_seg && col >= sp.col0[si + 1]) si++;
     const int nl = col - sp.col0[si], t0 = sp.step0[si] + (nl >> 7) * sp.ks;
-    // 32-bit unsigned arithmetic on purpose (steps x CTAs < 2^31 is checked on the host): this runs once per group of columns
-    const unsigned uT = (unsigned)sp.T, uG = (unsigned)sp.G;
-    const int c_lo = (int)(((unsigned)(t0 + 1) * uG + uT - 1) / uT) - 1, c_hi = (int)(((unsigned)(t0 + sp.ks) * uG + uT - 1) / uT) - 1;
+    const int c_lo = qg_cta_of_step(t0, sp.T, sp.G), c_hi = qg_cta_of_step(t0 + sp.ks - 1, sp.T, sp.G);
     if (c_lo == c_hi) return;                                       // tile was not split: C is final
     float acc[N];
 #pragma unroll
@@ -210,7 +212,7 @@ __device__ __forceinline__ void qg_gather(const QgSplit& sp, int b, int col, flo
             for (int i = 0; i < N; i++) part[j][i] = 0.f;
             const int c = c0 + j;
             if (c <= c_hi) {
-                const int cb = (int)((unsigned)c * uT / uG);
+                const int cb = qg_cta_first_step(c, sp.T, sp.G);
                 const float* src = sp.ws + ((size_t)(c * 2 + (cb >= t0 ? 0 : 1)) * QG_WS_B + b) * QG_WS_N + (nl & 127);
                 if (N == 8) { const float4 p = __ldcg((const float4*)src), q = __ldcg((const float4*)src + 1); part[j][0] = p.x; part[j][1] = p.y; part[j][2 % N] = p.z; part[j][3 % N] = p.w; part[j][4 % N] = q.x; part[j][5 % N] = q.y; part[j][6 % N] = q.z; part[j][7 % N] = q.w; }
                 else if (N == 4) { const float4 p = __ldcg((const float4*)src); part[j][0] = p.x; part[j][1] = p.y; part[j][2 % N] = p.z; part[j][3 % N] = p.w; }

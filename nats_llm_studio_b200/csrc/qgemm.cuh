@@ -266,7 +266,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
 
     const int G = gridDim.x, cta = blockIdx.x;
     const long long T = P.total_steps;
-    int s_begin = (int)((long long)cta * T / G), s_end = (int)((long long)(cta + 1) * T / G);
+    int s_begin = qg_cta_first_step(cta, P.total_steps, G), s_end = qg_cta_first_step(cta + 1, P.total_steps, G);
     if (P.whole) { s_begin = (int)((long long)cta * P.n_tiles / G) * P.ks; s_end = (int)((long long)(cta + 1) * P.n_tiles / G) * P.ks; }
     if (P.debug & 16) s_end = s_begin;                 // profiling: launch + TMEM alloc/dealloc only
 
