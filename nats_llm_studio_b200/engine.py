@@ -209,6 +209,11 @@ class Engine:
         return (y, ms.value) if iters > 1 else y
 
     @staticmethod
+    def cancel(req_id):
+        """ask the scheduler to stop a request; it answers with a FINISH event (reason CANCELLED) at its next iteration"""
+        return lib().b200_cancel(req_id)
+
+    @staticmethod
     def poll(max_events=64, timeout_ms=1000):
         """events the scheduler thread produced since the last poll (blocks up to timeout_ms for the first one)"""
         buf = (Event * max_events)()

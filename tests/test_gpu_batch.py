@@ -129,3 +129,36 @@ def test_scheduler_prompts_straddle_prefill_chunks(engine, golden_dir):
     for i in range(len(prompts)):
         assert np.array_equal(np.array(got[500 + i], np.int32), want[i]), i
     m.close()
+
+
+def test_cancel_frees_the_slot_and_the_others_finish(engine, golden_dir):
+    """b200_cancel on a running request: it ends with FINISH/CANCELLED before its token budget, the other requests are
+    unaffected (same tokens as alone), and its sequence slot is reused by a request submitted afterwards."""
+    m = engine.load_file("bt/cancel", os.path.join(golden_dir, "tiny-llama.gguf"))
+    prompts = _prompts(m.n_vocab, [12, 9, 20], seed=23)
+    want1 = _run(m, [prompts[1]], np.array([0], np.int32), 6)[0]
+    m.submit(prompts[0], 900, max_tokens=900)              # would run for a long time
+    m.submit(prompts[1], 901, max_tokens=6)
+    got, fin = {900: [], 901: [], 902: []}, {}
+    cancelled = False
+    while len(fin) < 2:
+        evs = engine.poll(64, 5000)
+        assert evs, "scheduler made no progress"
+        for e in evs:
+            assert e.kind != b200.EV_ERROR, e.finish_reason
+            if e.kind == b200.EV_TOKEN:
+                got[e.req_id].append(e.token)
+                if e.req_id == 900 and len(got[900]) >= 3 and not cancelled:
+                    assert engine.cancel(900) == 0; cancelled = True
+            else:
+                fin[e.req_id] = e
+    assert fin[900].finish_reason == b200.FINISH_CANCELLED and 3 <= fin[900].n_generated < 900
+    assert fin[901].finish_reason == b200.FINISH_LENGTH and np.array_equal(np.array(got[901], np.int32), want1)
+    assert engine.cancel(12345) != 0                       # unknown request id
+    m.submit(prompts[2], 902, max_tokens=3)                # the engine keeps serving
+    while 902 not in fin:
+        for e in engine.poll(64, 5000):
+            if e.kind == b200.EV_FINISH:
+                fin[e.req_id] = e
+    assert fin[902].n_generated == 3
+    m.close()
