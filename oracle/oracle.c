@@ -20,11 +20,13 @@
  *      -> RMSNorm -> SwiGLU -> residual; final norm -> lm_head), with Granite's four scalars
  *     (gguf/constants.py:132,142,143,176).
  *
- * PARITY PINNING: the dequantisers are pinned bit-exactly against gguf-py (tests/test_oracle_*).
- * The forward pass has no reference-supplied golden vectors (the reference has zero tests,
- * SURVEY.md §4/§8c) and the reference runtime cannot be installed offline, so the forward
- * parity is "unpinned by the reference"; it is pinned instead against an independent numpy
- * forward written on gguf-py's reader/dequantiser (tests/golden/make_golden.py).
+ * PARITY PINNING: the dequantisers are pinned bit-exactly against gguf-py (tests/test_oracle.py).
+ * The reference holds no golden vectors for the forward pass (it has zero tests, SURVEY.md
+ * §4/§8c) and its runtime cannot be installed offline, so the forward pass is pinned to outputs
+ * of an imported implementation instead: Hugging Face transformers' LlamaForCausalLM /
+ * GraniteForCausalLM (CPU, float64) run on the gguf-py-dequantised tensors of the committed
+ * GGUFs (tests/golden/make_hf_golden.py -> tests/golden/*.hf.npz; measured distance 2e-7 of the
+ * largest logit), and additionally to an independent numpy forward (tests/golden/make_golden.py).
  *
  * Build: see oracle/Makefile (gcc -O2 -fopenmp -ffp-contract=off -shared -fPIC).
  */

@@ -1,4 +1,5 @@
-"""Pin the CPU oracle: dequantisers bit-exact vs gguf-py, forward vs the committed numpy goldens."""
+"""Pin the CPU oracle: dequantisers bit-exact vs gguf-py; forward vs logits produced by an IMPORTED implementation
+(transformers LlamaForCausalLM / GraniteForCausalLM, tests/golden/make_hf_golden.py) and vs the numpy goldens."""
 import os
 
 import numpy as np
@@ -67,6 +68,24 @@ def test_forward_matches_numpy_golden(golden_dir, name):
     safe = g["margin"][n_prompt - 1:-1] > 1e-3 * scale
     first_unsafe = int(np.argmin(safe)) if not safe.all() else len(out)
     assert np.array_equal(out[:first_unsafe], toks[n_prompt:n_prompt + first_unsafe])
+
+
+@pytest.mark.parametrize("name", ["tiny-llama", "tiny-granite", "small-llama"])
+def test_forward_matches_transformers(golden_dir, name, tmp_path):
+    """The pin: oracle.c's forward against Hugging Face transformers run on the same GGUF tensors (fp64, CPU).
+    Tolerance 1e-5 of the largest logit (measured 2e-7: the oracle accumulates in fp64 and rounds to fp32)."""
+    g = np.load(os.path.join(golden_dir, f"{name}.hf.npz"))
+    if name == "small-llama":                       # regenerated deterministically (not committed: 3.6 MB)
+        import make_gguf
+        path = str(tmp_path / "small-llama.gguf")
+        make_gguf.write_model(path, make_gguf.spec_from_preset("small-llama"))
+    else:
+        path = os.path.join(golden_dir, f"{name}.gguf")
+    logits = orc.Model(path).forward(g["tokens"])
+    ref = g["logits"]
+    assert logits.shape == ref.shape
+    assert np.abs(logits - ref).max() <= 1e-5 * np.abs(ref).max()
+    assert np.array_equal(logits.argmax(axis=1), ref.argmax(axis=1))
 
 
 def test_incremental_equals_teacher_forced(golden_dir):
