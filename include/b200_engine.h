@@ -40,10 +40,12 @@ typedef struct b200_sampling {
     int max_tokens;
     int stop_token;      /* -1: none (EOS from the GGUF is always honoured unless ignore_eos) */
     int ignore_eos;
+    int timeout_ms;      /* > 0: the request is ended with B200_FINISH_TIMEOUT once it has been in the engine this long
+                            (the reference bounds every handler with a context deadline, nats_llm_studio.go:328) */
 } b200_sampling;
 
 enum { B200_EV_TOKEN = 1, B200_EV_FINISH = 2, B200_EV_ERROR = 3 };
-enum { B200_FINISH_STOP = 1, B200_FINISH_LENGTH = 2, B200_FINISH_CANCELLED = 3 };
+enum { B200_FINISH_STOP = 1, B200_FINISH_LENGTH = 2, B200_FINISH_CANCELLED = 3, B200_FINISH_TIMEOUT = 4 };
 typedef struct b200_event {
     uint64_t req_id; int kind; int token; int finish_reason;
     int n_prompt; int n_generated; float ttft_ms; float decode_ms;
@@ -105,10 +107,14 @@ int b200_dequantize(int type, const void* raw_blocks, int64_t n_rows, int K, flo
  * device also looks up the array's device address (make that call before starting any stream capture).  Every call
  * reuses the same array, which keeps the previous call's bytes (harmless: each call overwrites what it reads);
  * calls from this library are serialised, but work that overlaps on the GPU from elsewhere on the same array races.
- * The work is queued on the engine's own stream and the call returns after it completed: inputs written on
- * another stream must be complete before calling. */
+ * The work is queued on a utility stream that b200_init created (not the generation stream, which the scheduler may
+ * be capturing into a CUDA graph) and the call returns after it completed: inputs written on another stream must be
+ * complete before calling. */
 #define B200_NOALLOC_SCRATCH_BYTES (4u << 20)
 int b200_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K, float* d_out);
+/* one draw of the sampler (top-k -> top-p at T=1 -> temperature -> categorical with Philox4x32-10(seed, step)) over host
+ * logits[V]: what chat_model's `temperature` / `top_p` / `top_k` / `seed` fields drive (README.md:196-205) */
+int b200_sample(const float* logits, int V, const b200_sampling* s, uint64_t step, int* token);
 /* y[N] = W[N x K] . x[K] through the streaming GEMV; iters>1 repeats the launch, ms = mean per iter */
 int b200_gemv(int type, const void* raw_blocks, int64_t N, int K, const float* x, float* y, int iters, float* ms);
 /* C[M x N] = A[M x K] . B[N x K]^T through the tcgen05/TMEM/TMA GEMM that prompt ingestion uses (inputs rounded to
@@ -127,6 +133,11 @@ int b200_model_set_prefill_min(b200_model* m, int n);
  * on which other rows are in the batch. */
 int b200_model_prefill_slot(b200_model* m, int slot, const int32_t* toks, int n, int pos0);
 int b200_model_batch_step(b200_model* m, const int32_t* toks, const int32_t* slots, const int32_t* pos, int n, int32_t* next, float* logits);
+/* The same step with per-row sampling (the `temperature`, `top_k`, `top_p`, `seed` request fields, README.md:196-205): row i
+ * with samp[i].temperature > 0 draws its token with Philox(seed, draw[i]) where draw[i] = tokens that request has generated
+ * so far — the counter the single-sequence path uses, so a seeded request yields the same tokens alone or in any batch. */
+int b200_model_batch_step_sampled(b200_model* m, const int32_t* toks, const int32_t* slots, const int32_t* pos, int n,
+                                  const b200_sampling* samp, const int32_t* draw, int32_t* next, float* logits);
 /* ---- tensor parallelism.  No counterpart in the reference, whose only scale-out is replicas in a NATS
  * queue group (README.md:484).  One process per GPU; rank 0 creates a 128-byte NCCL id, the host side distributes it
  * (the Go worker would publish it on a NATS subject; tests and tools use torch.distributed), every rank then calls

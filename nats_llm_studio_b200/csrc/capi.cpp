@@ -7,15 +7,21 @@
 
 namespace b200 {
 int load_file_into(const std::string& id, const std::string& path, std::shared_ptr<Model>& out, std::string& log);
+std::string list_models_json();
 
 // ---- request queue behind b200_submit / b200_poll (one scheduler thread owns the engine).
 // max_seqs == 1: requests run one after another through the persistent batch-1 decode kernel.
 // max_seqs  > 1: continuous batching — every iteration admits waiting requests into free sequence slots (their prompts
 // are ingested by the tensor-core prefill into the slot's KV pages) and then advances ALL active sequences by one token
 // with one batched step; finished sequences free their slot immediately.
+// A caller blocked inside the library for one request (lmstudio.chat_model through b200_handle): its events are
+// delivered here instead of the b200_poll queue.
+struct Waiter { std::mutex mu; std::condition_variable cv; std::vector<int32_t> toks; bool done = false; b200_event fin{}; };
 struct Request {
     std::shared_ptr<Model> m; std::vector<int32_t> toks; b200_sampling s; uint64_t id; std::atomic<bool> cancelled{false};
     std::chrono::steady_clock::time_point t_submit;
+    std::shared_ptr<Waiter> waiter;
+    bool expired() const { return s.timeout_ms > 0 && std::chrono::steady_clock::now() - t_submit > std::chrono::milliseconds(s.timeout_ms); }
 };
 struct Seq { std::shared_ptr<Request> r; int slot = 0, n_fed = 0, pos = 0, cur_tok = 0, n_gen = 0; bool decoding = false; float ttft_ms = 0; std::chrono::steady_clock::time_point t_first; };
 struct Scheduler {
@@ -25,7 +31,17 @@ struct Scheduler {
     std::thread th; bool stop = false, started = false;
     void start() { if (started) return; started = true; th = std::thread([this] { loop(); }); }
     void push_events(std::vector<b200_event>& out, const std::vector<uint64_t>& done) {
-        { std::lock_guard<std::mutex> lk(mu); for (auto& e : out) ev.push_back(e); for (auto id : done) live.erase(id); }
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            for (auto& e : out) {
+                auto it = live.find(e.req_id);
+                if (it != live.end() && it->second->waiter) {           // a blocked in-library caller owns this request's events
+                    Waiter& w = *it->second->waiter; std::lock_guard<std::mutex> wl(w.mu);
+                    if (e.kind == B200_EV_TOKEN) w.toks.push_back(e.token); else { w.fin = e; w.done = true; w.cv.notify_all(); }
+                } else ev.push_back(e);
+            }
+            for (auto id : done) live.erase(id);
+        }
         out.clear(); cv_ev.notify_all();
     }
     static double ms_since(std::chrono::steady_clock::time_point t) { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t).count(); }
@@ -37,12 +53,12 @@ struct Scheduler {
         else {
             int n_gen = r->s.max_tokens > 0 ? r->s.max_tokens : 256;
             std::vector<int32_t> toks((size_t)n_gen); int n_out = 0; float ttft = 0, dec = 0;
-            int rc = r->m->generate(r->toks.data(), (int)r->toks.size(), n_gen, &r->s, toks.data(), &n_out, &ttft, &dec);
+            int reason = 0;
+            int rc = r->expired() ? B200_OK : r->m->generate(r->toks.data(), (int)r->toks.size(), n_gen, &r->s, toks.data(), &n_out, &ttft, &dec, &reason, &r->t_submit);
             if (rc != B200_OK) { fin.kind = B200_EV_ERROR; fin.finish_reason = rc; }
             else {
                 for (int i = 0; i < n_out; i++) { b200_event e{}; e.req_id = r->id; e.kind = B200_EV_TOKEN; e.token = toks[i]; e.n_generated = i + 1; out.push_back(e); }
-                bool stopped = n_out > 0 && !r->s.ignore_eos && (toks[n_out - 1] == r->m->eos || toks[n_out - 1] == r->s.stop_token);
-                fin.finish_reason = stopped ? B200_FINISH_STOP : B200_FINISH_LENGTH; fin.n_generated = n_out; fin.ttft_ms = ttft; fin.decode_ms = dec;
+                fin.finish_reason = reason ? reason : B200_FINISH_TIMEOUT; fin.n_generated = n_out; fin.ttft_ms = ttft; fin.decode_ms = dec;
             }
         }
         out.push_back(fin); push_events(out, {r->id});
@@ -70,7 +86,7 @@ struct Scheduler {
             while (!waiting.empty() && !free_slots.empty() && (!cur || waiting.front()->m == cur)) {
                 auto r = waiting.front(); waiting.pop_front();
                 b200_event e{}; e.req_id = r->id; e.n_prompt = (int)r->toks.size();
-                if (r->cancelled) { e.kind = B200_EV_FINISH; e.finish_reason = B200_FINISH_CANCELLED; out.push_back(e); done.push_back(r->id); continue; }
+                if (r->cancelled || r->expired()) { e.kind = B200_EV_FINISH; e.finish_reason = r->cancelled ? B200_FINISH_CANCELLED : B200_FINISH_TIMEOUT; out.push_back(e); done.push_back(r->id); continue; }
                 const int n = (int)r->toks.size();
                 bool bad = n < 1 || n + 1 > max_ctx;
                 for (int t : r->toks) bad = bad || t < 0 || t >= r->m->n_vocab;
@@ -99,9 +115,9 @@ struct Scheduler {
             std::vector<int> idx;
             for (int i = 0; i < (int)active.size(); i++) if (active[i].decoding && !active[i].r->cancelled) idx.push_back(i);
             const int B = (int)idx.size();
-            std::vector<int32_t> toks(B), slots(B), pos(B), next(B);
-            for (int j = 0; j < B; j++) { const Seq& s = active[idx[j]]; toks[j] = s.cur_tok; slots[j] = s.slot; pos[j] = s.pos; }
-            if (rc == B200_OK && B > 0) { std::lock_guard<std::mutex> lk(cur->run_mu); rc = cur->batch_step(toks.data(), slots.data(), pos.data(), B, next.data()); }
+            std::vector<int32_t> toks(B), slots(B), pos(B), next(B), draw(B); std::vector<b200_sampling> samp(B);
+            for (int j = 0; j < B; j++) { const Seq& s = active[idx[j]]; toks[j] = s.cur_tok; slots[j] = s.slot; pos[j] = s.pos; samp[j] = s.r->s; draw[j] = s.n_gen; }
+            if (rc == B200_OK && B > 0) { std::lock_guard<std::mutex> lk(cur->run_mu); rc = cur->batch_step(toks.data(), slots.data(), pos.data(), B, next.data(), nullptr, samp.data(), draw.data()); }
             if (rc != B200_OK) {                                   // engine failure: every active request fails
                 for (Seq& s : active) finish(s, B200_EV_ERROR, rc);
                 active.clear(); push_events(out, done); continue;
@@ -118,6 +134,7 @@ struct Scheduler {
                 const int max_tokens = r->s.max_tokens > 0 ? r->s.max_tokens : 256;
                 const bool stopped = s.n_gen > 0 && !r->s.ignore_eos && (s.cur_tok == r->m->eos || s.cur_tok == r->s.stop_token);
                 if (r->cancelled) finish(s, B200_EV_FINISH, B200_FINISH_CANCELLED);
+                else if (r->expired()) finish(s, B200_EV_FINISH, B200_FINISH_TIMEOUT);
                 else if (stopped) finish(s, B200_EV_FINISH, B200_FINISH_STOP);
                 else if (s.n_gen >= max_tokens || (s.decoding && s.pos + 1 >= max_ctx)) finish(s, B200_EV_FINISH, B200_FINISH_LENGTH);
                 else keep.push_back(s);
@@ -130,6 +147,38 @@ struct Scheduler {
     void shutdown() { { std::lock_guard<std::mutex> lk(mu); stop = true; } cv_req.notify_all(); if (th.joinable()) th.join(); started = false; stop = false; }
 };
 static Scheduler& sched() { static Scheduler s; return s; }
+
+static void enqueue(const std::shared_ptr<Request>& r) {
+    Scheduler& S = sched();
+    { std::lock_guard<std::mutex> lk(S.mu); S.start(); S.q.push_back(r); S.live[r->id] = r; }
+    S.cv_req.notify_one();
+}
+
+// One blocking generation.  max_seqs == 1: the persistent batch-1 kernel, directly.  max_seqs > 1: the request joins the
+// continuous-batching scheduler like any b200_submit request (so concurrent lmstudio.chat_model calls share batched
+// steps) and this thread sleeps until its FINISH event.
+int sched_generate(const std::shared_ptr<Model>& m, const std::vector<int32_t>& prompt, const b200_sampling& s, std::vector<int32_t>& out, float* ttft_ms, float* decode_ms, int* finish_reason) {
+    const int n_gen = s.max_tokens > 0 ? s.max_tokens : 256;
+    if (engine().max_seqs <= 1) {
+        out.assign((size_t)n_gen, 0); int n_out = 0;
+        const auto t0 = std::chrono::steady_clock::now();
+        int rc = m->generate(prompt.data(), (int)prompt.size(), n_gen, &s, out.data(), &n_out, ttft_ms, decode_ms, finish_reason, &t0);
+        out.resize(rc == B200_OK ? (size_t)n_out : 0);
+        return rc;
+    }
+    static std::atomic<uint64_t> next_id{0};
+    auto r = std::make_shared<Request>(); r->m = m; r->toks = prompt; r->s = s; r->s.max_tokens = n_gen;
+    r->id = (1ull << 63) | ++next_id;                                   // internal id space, apart from b200_submit callers' ids
+    r->t_submit = std::chrono::steady_clock::now(); r->waiter = std::make_shared<Waiter>();
+    enqueue(r);
+    Waiter& w = *r->waiter; std::unique_lock<std::mutex> lk(w.mu);
+    w.cv.wait(lk, [&] { return w.done; });
+    out = w.toks;
+    if (ttft_ms) *ttft_ms = w.fin.ttft_ms; if (decode_ms) *decode_ms = w.fin.decode_ms;
+    if (w.fin.kind == B200_EV_ERROR) return fail(w.fin.finish_reason, "generation failed in the batched engine (code " + std::to_string(w.fin.finish_reason) + ")");
+    if (finish_reason) *finish_reason = w.fin.finish_reason;
+    return B200_OK;
+}
 }  // namespace b200
 
 using namespace b200;
@@ -193,11 +242,7 @@ int b200_model_find(const char* id, b200_model** out) {
     *out = (b200_model*)it->second.get(); return B200_OK;
 }
 int b200_model_list(char* out, size_t cap, size_t* need) {
-    std::string env = handle_subject("lmstudio.list_models", "");
-    // strip the envelope: {"ok":true,"data":{"http_status":200,"models":<X>}}
-    const std::string key = "\"models\":"; size_t k = env.find(key);
-    std::string models = k == std::string::npos ? "{\"data\":[],\"object\":\"list\"}" : env.substr(k + key.size(), env.size() - (k + key.size()) - 2);
-    return copy_out(models, out, cap, need);
+    return copy_out(list_models_json(), out, cap, need);
 }
 int b200_model_info(const b200_model* m, char* out, size_t cap, size_t* need) { if (!m) return fail(B200_ERR_INVALID, "null model"); return copy_out(((const Model*)m)->info_json(), out, cap, need); }
 int b200_model_n_vocab(const b200_model* m) { return m ? ((const Model*)m)->n_vocab : 0; }
@@ -226,9 +271,8 @@ int b200_submit(b200_model* m, const int32_t* toks, int n, const b200_sampling* 
     auto sp = find_shared(m); if (!sp || !sp->committed) return fail(B200_ERR_STATE, "model is not loaded");
     auto r = std::make_shared<Request>(); r->m = sp; r->toks.assign(toks, toks + n); r->id = req_id; r->t_submit = std::chrono::steady_clock::now();
     if (s) r->s = *s; else { r->s = b200_sampling{}; r->s.max_tokens = 256; r->s.stop_token = -1; }
-    Scheduler& S = sched();
-    { std::lock_guard<std::mutex> lk(S.mu); S.start(); S.q.push_back(r); S.live[req_id] = r; }
-    S.cv_req.notify_one();
+    if (req_id >> 63) return fail(B200_ERR_INVALID, "request ids with the top bit set are reserved for the library's own requests");
+    enqueue(r);
     return B200_OK;
 }
 int b200_poll(b200_event* out, int max, int timeout_ms) {
@@ -250,6 +294,7 @@ int b200_handle(const char* subject, const void* payload, size_t n, char* reply,
 }
 int b200_set_models_dir(const char* dir) { Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); R.models_dir = dir ? dir : ""; while (R.models_dir.size() > 1 && R.models_dir.back() == '/') R.models_dir.pop_back(); return B200_OK; }
 
+int b200_sample(const float* logits, int V, const b200_sampling* s, uint64_t step, int* token) { if (!logits || !s || !token) return fail(B200_ERR_INVALID, "null argument"); return kernel_sample(logits, V, *s, step, token); }
 int b200_dequantize(int type, const void* raw, int64_t n_rows, int K, float* out) { if ((!raw || !out) && n_rows) return fail(B200_ERR_INVALID, "null argument"); return kernel_dequantize(type, raw, n_rows, K, out); }
 int b200_gemv(int type, const void* raw, int64_t N, int K, const float* x, float* y, int iters, float* ms) { if (!raw || !x || !y) return fail(B200_ERR_INVALID, "null argument"); return kernel_gemv(type, raw, N, K, x, y, iters, ms); }
 int b200_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K, float* d_out) { return kernel_dequantize_noalloc(type, d_raw, n_rows, K, d_out); }
@@ -259,6 +304,10 @@ int b200_model_set_prefill_min(b200_model* m, int n) { if (!m) return fail(B200_
 int b200_model_batch_step(b200_model* m, const int32_t* toks, const int32_t* slots, const int32_t* pos, int n, int32_t* next, float* logits) {
     if (!m || !toks || !slots || !pos || !next) return fail(B200_ERR_INVALID, "null argument");
     Model* M = (Model*)m; std::lock_guard<std::mutex> lk(M->run_mu); return M->batch_step(toks, slots, pos, n, next, logits);
+}
+int b200_model_batch_step_sampled(b200_model* m, const int32_t* toks, const int32_t* slots, const int32_t* pos, int n, const b200_sampling* samp, const int32_t* draw, int32_t* next, float* logits) {
+    if (!m || !toks || !slots || !pos || !next) return fail(B200_ERR_INVALID, "null argument");
+    Model* M = (Model*)m; std::lock_guard<std::mutex> lk(M->run_mu); return M->batch_step(toks, slots, pos, n, next, logits, samp, draw);
 }
 int b200_model_prefill_slot(b200_model* m, int slot, const int32_t* toks, int n, int pos0) {
     if (!m || (!toks && n)) return fail(B200_ERR_INVALID, "null argument");

@@ -602,7 +602,7 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
                 const float vv = sm.red[2 * w]; const int ix = __float_as_int(sm.red[2 * w + 1]);
                 if (vv > bv || (vv == bv && ix < bi)) { bv = vv; bi = ix; }
             }
-            next = bi;
+            next = bi < P.n_vocab ? bi : 0;                    // all-NaN logits: stay inside the vocabulary (the token indexes the embedding table)
         }
         if (c == 0 && tid == 0) P.out_tokens[step] = next;
         token = next;

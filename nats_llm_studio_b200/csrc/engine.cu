@@ -106,12 +106,16 @@ int Engine::init(const b200_config* cfg) {
     device = cfg ? cfg->device : 0;
     max_ctx = cfg && cfg->max_ctx > 0 ? cfg->max_ctx : 4096;
     max_seqs = cfg && cfg->max_seqs > 0 ? cfg->max_seqs : 1;
+    // the batch-1 kernel caches a sequence's block table in shared memory (BTAB_MAX pages of 16 positions)
+    if (max_ctx > 16 * BTAB_MAX) return fail(B200_ERR_UNSUPPORTED, "max_ctx " + std::to_string(max_ctx) + " exceeds the supported " + std::to_string(16 * BTAB_MAX) + " positions per sequence");
+    if (device < 0 || device >= 64) return fail(B200_ERR_INVALID, "device ordinal out of range");
     CK(cudaSetDevice(device));
     cudaDeviceProp p; CK(cudaGetDeviceProperties(&p, device));
     if (p.major < 10) return fail(B200_ERR_UNSUPPORTED, "this library is built for sm_100a (B200) only");
     n_sm = p.multiProcessorCount; smem_per_sm = (int)p.sharedMemPerMultiprocessor; smem_optin = (int)p.sharedMemPerBlockOptin;
     CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&aux_stream, cudaStreamNonBlocking));
     CK(cudaFuncSetAttribute(decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin));
     ready = true;
     return B200_OK;
@@ -121,7 +125,7 @@ void Engine::shutdown() {
     std::lock_guard<std::mutex> lk(mu);
     if (!ready) return;
     cudaSetDevice(device); cudaDeviceSynchronize();
-    cudaStreamDestroy(stream); cudaStreamDestroy(copy_stream); stream = copy_stream = nullptr;
+    cudaStreamDestroy(stream); cudaStreamDestroy(copy_stream); cudaStreamDestroy(aux_stream); stream = copy_stream = aux_stream = nullptr;
     cudaFree(qg_ws); qg_ws = nullptr;
     if (nccl_comm) { nccl().CommDestroy(nccl_comm); nccl_comm = nullptr; }
     tp_rank = 0; tp_world = 1;
@@ -171,11 +175,12 @@ static int dalloc(T** p, size_t n) {
 
 // repack `raw` (device, ggml row-major blocks) into the engine layout at `out`
 // (N rows written, of which the first n_src come from raw and the rest are zero padding)
-static int repack(Engine& E, const uint8_t* raw, uint8_t* out, int type, int64_t N, int64_t n_src, int K, int interleave_parity = -1, size_t src_stride = 0) {
+static int repack(Engine& E, const uint8_t* raw, uint8_t* out, int type, int64_t N, int64_t n_src, int K, int interleave_parity = -1, size_t src_stride = 0, cudaStream_t st = nullptr) {
+    if (!st) st = E.stream;
     long long chunks = (long long)N * n_groups(K) * group_bytes(type) / 16;
     int blocks = (int)std::min<long long>((chunks + 255) / 256, 148LL * 32);
     if (blocks < 1) blocks = 1;
-    repack_kernel<<<blocks, 256, 0, E.stream>>>(raw, out, type, N, n_src, K, interleave_parity, src_stride);
+    repack_kernel<<<blocks, 256, 0, st>>>(raw, out, type, N, n_src, K, interleave_parity, src_stride);
     CK(cudaGetLastError());
     E.launches++;
     return B200_OK;
@@ -184,12 +189,24 @@ static int repack(Engine& E, const uint8_t* raw, uint8_t* out, int type, int64_t
 // ------------------------------------------------------------------------------------ Model
 Model::~Model() { release(); }
 
+// Frees every device allocation and forgets every pointer and "already built" flag derived from them: a request that
+// still holds the model (a queued chat, the scheduler's active sequences) finds committed == false under run_mu and
+// fails with B200_ERR_STATE instead of launching kernels on freed memory.  Caller holds run_mu (or is the destructor).
 void Model::release() {
+    if (engine().ready) { cudaSetDevice(engine().device); cudaStreamSynchronize(engine().stream); }
     for (auto& g : step_graph) if (g) { cudaGraphExecDestroy(g); g = nullptr; }
+    step_graph.clear(); step_seen.clear(); step_launches.clear(); graph_failed = false;
     for (void* p : owned) cudaFree(p);
     owned.clear();
     if (d_raw) { cudaFree(d_raw); d_raw = nullptr; }
     committed = false;
+    tok_embd = Matrix{}; out_w = Matrix{}; out_norm = nullptr; inv_freq = nullptr; layers.clear();
+    d_phases = nullptr; n_phases = 0; d_logits = nullptr; d_ll16 = nullptr; d_ll32 = nullptr;
+    d_state = d_out_tokens = d_forced = d_block_table = nullptr; d_kv = nullptr; n_pages = 0; cur_pos = 0;
+    pf_H = pf_Y = nullptr; pf_X = pf_Q = pf_ACT = pf_W = nullptr; pf_toks = nullptr; pf_T = nullptr;
+    bt_logits = nullptr; bt_next = nullptr; bt_samp = nullptr; b_out = nullptr;
+    bf16_ready = bf16_tried = tile_ready = false;
+    hbm_bytes = 0; weight_bytes = 0; uploaded = 0;
 }
 
 template <typename T>
@@ -335,7 +352,10 @@ int Model::commit() {
     // ---- runtime buffers
     int rc;
     pages_per_seq = (E.max_ctx + 15) / 16;
-    n_pages = pages_per_seq * E.max_seqs;
+    // a serving engine (max_seqs > 1) keeps one more sequence slot for the synchronous batch-1 path, so that
+    // b200_model_generate / b200_model_eval never write KV pages of a request the scheduler is serving
+    sync_slot = E.max_seqs > 1 ? E.max_seqs : 0;
+    n_pages = pages_per_seq * (sync_slot + 1);
     size_t page_elems = (size_t)n_layer * 2 * n_head_kv * 16 * head_dim;
     if ((rc = own(&d_kv, page_elems * n_pages)) || (rc = own(&d_block_table, (size_t)n_pages))) return rc;
     std::vector<int> bt(n_pages); for (int i = 0; i < n_pages; i++) bt[i] = i;
@@ -395,7 +415,7 @@ void Model::fill_params(DecodeParams& P) const {
     P.q_ll = d_ll32; P.part_ll = P.q_ll + QD; P.cand_ll = P.part_ll + (size_t)n_head * 16 * (head_dim + 2);
     P.hown_cap = hown_cap; (void)KVD;
     P.n_btab = std::min(pages_per_seq, BTAB_MAX);
-    P.kv.pages = d_kv; P.kv.block_table = d_block_table; P.kv.n_layer = n_layer; P.kv.n_head_kv = n_head_kv; P.kv.head_dim = head_dim; P.kv.pages_per_seq = pages_per_seq; P.kv.n_pages = n_pages;
+    P.kv.pages = d_kv; P.kv.block_table = d_block_table + (size_t)sync_slot * pages_per_seq; P.kv.n_layer = n_layer; P.kv.n_head_kv = n_head_kv; P.kv.head_dim = head_dim; P.kv.pages_per_seq = pages_per_seq; P.kv.n_pages = n_pages;
     P.pos = d_state + 0; P.token = d_state + 1; P.bar_ctr = (unsigned*)(d_state + 2); P.epoch = (unsigned*)(d_state + 3);
     P.out_tokens = d_out_tokens; P.n_steps = 1; P.want_argmax = 1; P.trace = d_trace;
 }
@@ -422,14 +442,20 @@ int Model::run_steps(int n_steps, const int32_t* forced, int n_forced, bool rese
     return B200_OK;
 }
 
-int Model::generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_sampling* s, int32_t* out, int* n_out, float* ttft_ms, float* decode_ms) {
+int Model::generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_sampling* s, int32_t* out, int* n_out, float* ttft_ms, float* decode_ms,
+                    int* finish_reason, const std::chrono::steady_clock::time_point* t_submit) {
     Engine& E = engine(); if (int rc = E.ensure()) return rc;
     if (tp) return fail(B200_ERR_UNSUPPORTED, "tensor-parallel shard: drive all ranks through b200_model_prefill_slot / b200_model_batch_step");
     std::lock_guard<std::mutex> lk(run_mu);
+    if (!committed) return fail(B200_ERR_STATE, "model '" + id + "' is not loaded (closed or deleted)");
     if (n_prompt < 1 || n_gen < 1) return fail(B200_ERR_INVALID, "need at least one prompt token and one generated token");
     for (int i = 0; i < n_prompt; i++) if (prompt[i] < 0 || prompt[i] >= n_vocab) return fail(B200_ERR_INVALID, "prompt token out of range");
     const bool greedy = !s || s->temperature <= 0.f;
     const int stop = s ? s->stop_token : -1; const bool ignore_eos = s && s->ignore_eos;
+    const bool has_deadline = s && s->timeout_ms > 0;
+    const auto deadline = (t_submit ? *t_submit : std::chrono::steady_clock::now()) + std::chrono::milliseconds(has_deadline ? s->timeout_ms : 0);
+    auto expired = [&] { return has_deadline && std::chrono::steady_clock::now() > deadline; };
+    bool timed_out = false;
     cudaEvent_t e0, e1, e2; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreate(&e2));
     int rc = B200_OK; int produced = 0;
     CK(cudaEventRecord(e0, E.stream));
@@ -449,7 +475,8 @@ int Model::generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_s
         produced = 1;
         while (produced < n_gen) {
             if (!ignore_eos && (out[produced - 1] == eos || out[produced - 1] == stop)) break;
-            int chunk = std::min(n_gen - produced, ignore_eos ? n_gen : 32);
+            if (expired()) { timed_out = true; break; }
+            int chunk = std::min(n_gen - produced, (ignore_eos && !has_deadline) ? n_gen : 32);
             if ((rc = run_steps(chunk, nullptr, 0, false, nullptr))) goto done;
             CK(cudaMemcpyAsync(out + produced, d_out_tokens, (size_t)chunk * 4, cudaMemcpyDeviceToHost, E.stream));
             CK(cudaStreamSynchronize(E.stream));
@@ -470,12 +497,17 @@ int Model::generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_s
             CK(cudaStreamSynchronize(E.stream));
             produced++;
             if (produced >= n_gen || (!ignore_eos && (out[produced - 1] == eos || out[produced - 1] == stop))) break;
+            if (expired()) { timed_out = true; break; }
             if ((rc = run_steps(1, nullptr, 0, false, nullptr))) goto done;
         }
     }
     CK(cudaEventRecord(e2, E.stream)); CK(cudaEventSynchronize(e2));
     { float a = 0, b = 0; cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2); if (ttft_ms) *ttft_ms = a; if (decode_ms) *decode_ms = b; }
     if (n_out) *n_out = produced;
+    if (finish_reason) {
+        const bool stopped = produced > 0 && !ignore_eos && (out[produced - 1] == eos || out[produced - 1] == stop);
+        *finish_reason = stopped ? B200_FINISH_STOP : timed_out ? B200_FINISH_TIMEOUT : B200_FINISH_LENGTH;
+    }
 done:
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
     return rc;
@@ -484,6 +516,7 @@ done:
 int Model::eval(const int32_t* toks, int n, float* logits_all, float* logits_last) {
     Engine& E = engine(); if (int rc = E.ensure()) return rc;
     std::lock_guard<std::mutex> lk(run_mu);
+    if (!committed) return fail(B200_ERR_STATE, "model '" + id + "' is not loaded (closed or deleted)");
     if (n < 1) return fail(B200_ERR_INVALID, "empty token list");
     for (int i = 0; i < n; i++) if (toks[i] < 0 || toks[i] >= n_vocab) return fail(B200_ERR_INVALID, "token out of range");
     float* d_all = nullptr;
@@ -517,6 +550,7 @@ double Model::bytes_per_token(int ctx) const {
 int Model::bench_decode(int ctx_len, int n_steps, int warmup, float* ms_per_token, double* bytes) {
     Engine& E = engine(); if (int rc = E.ensure()) return rc;
     std::lock_guard<std::mutex> lk(run_mu);
+    if (!committed) return fail(B200_ERR_STATE, "model '" + id + "' is not loaded (closed or deleted)");
     if (ctx_len < 1 || ctx_len + n_steps + warmup > E.max_ctx) return fail(B200_ERR_INVALID, "bench context does not fit max_ctx");
     // prime the KV cache: positions [0, ctx_len) hold whatever the cache holds (attention cost is
     // data-independent); set the position and a start token, then time n_steps greedy steps.
@@ -550,6 +584,20 @@ int sample_token(Engine& E, Model& m, const b200_sampling& s, uint64_t step) {
 }
 
 // ------------------------------------------------------------------------------------ kernel-level entry points
+// test entry: one draw of the sampler (K8) over host logits
+int kernel_sample(const float* logits, int V, const b200_sampling& s, uint64_t step, int* token) {
+    Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    if (V < 1 || !(s.temperature > 0.f)) return fail(B200_ERR_INVALID, "need V >= 1 and temperature > 0");
+    float* d_l = nullptr; int* d_t = nullptr; int rc;
+    if ((rc = dalloc(&d_l, (size_t)V)) || (rc = dalloc(&d_t, (size_t)1))) { cudaFree(d_l); cudaFree(d_t); return rc; }
+    cudaMemcpyAsync(d_l, logits, (size_t)V * 4, cudaMemcpyHostToDevice, E.stream);
+    sample_kernel<<<1, SAMPLER_THREADS, 0, E.stream>>>(d_l, V, s.top_k, s.top_p <= 0.f ? 1.f : s.top_p, s.temperature, s.seed, step, d_t, nullptr); E.launches++;
+    cudaError_t e = cudaMemcpyAsync(token, d_t, 4, cudaMemcpyDeviceToHost, E.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(E.stream);
+    cudaFree(d_l); cudaFree(d_t);
+    return e == cudaSuccess ? B200_OK : fail(B200_ERR_CUDA, cudaGetErrorString(e));
+}
+
 int kernel_dequantize(int type, const void* raw, int64_t n_rows, int K, float* out) {
     Engine& E = engine(); if (int rc = E.ensure()) return rc;
     if (!is_streamable(type)) return fail(B200_ERR_UNSUPPORTED, "unsupported ggml type");
@@ -680,7 +728,7 @@ int Model::ensure_prefill_buffers() {
     int rc;
     if ((rc = own(&pf_H, (size_t)Mc * D)) || (rc = own(&pf_X, (size_t)Mc * std::max(D, QD))) || (rc = own(&pf_Y, (size_t)Mc * std::max(QD + 2 * KVD, 2 * F))) ||
         (rc = own(&pf_Q, (size_t)Mc * QD)) || (rc = own(&pf_ACT, (size_t)Mc * F)) || (rc = own(&pf_W, wmax)) || (rc = own(&pf_toks, (size_t)3 * Mc)) ||
-        (rc = own(&bt_logits, (size_t)std::max(1, E.max_seqs) * ((n_vocab_l + 3) & ~3) * (E.tp_world + (E.tp_world > 1 ? 1 : 0)))) || (tp && (rc = own(&pf_T, (size_t)Mc * D))) || (rc = own(&bt_next, (size_t)std::max(1, E.max_seqs))))
+        (rc = own(&bt_logits, (size_t)std::max(1, E.max_seqs) * ((n_vocab_l + 3) & ~3) * (E.tp_world + (E.tp_world > 1 ? 1 : 0)))) || (tp && (rc = own(&pf_T, (size_t)Mc * D))) || (rc = own(&bt_next, (size_t)std::max(1, E.max_seqs))) || (rc = own(&bt_samp, (size_t)std::max(1, E.max_seqs))))
         return rc;
     return B200_OK;
 }
@@ -829,6 +877,7 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
 // Ingest toks[0..n) of sequence `slot` at positions pos0.. : fills its KV pages (hidden states are discarded).
 int Model::prefill_slot(int slot, const int32_t* toks, int n, int pos0) {
     Engine& E = engine();
+    if (!committed) return fail(B200_ERR_STATE, "model '" + id + "' is not loaded (closed or deleted)");
     if (n <= 0) return B200_OK;
     if (pos0 + n > E.max_ctx) return fail(B200_ERR_INVALID, "context overflow in prefill");
     if (int rc = ensure_prefill_buffers()) return rc;
@@ -845,6 +894,7 @@ int Model::prefill_slot(int slot, const int32_t* toks, int n, int pos0) {
 // one sequence must appear in position order.  The continuous-batching scheduler packs waiting prompts into such chunks.
 int Model::prefill_rows(const int32_t* toks, const int32_t* slots, const int32_t* pos, int M) {
     Engine& E = engine();
+    if (!committed) return fail(B200_ERR_STATE, "model '" + id + "' is not loaded (closed or deleted)");
     if (M < 1 || M > PREFILL_CHUNK) return fail(B200_ERR_INVALID, "prefill chunk size out of range");
     for (int i = 0; i < M; i++) if (toks[i] < 0 || toks[i] >= n_vocab || slots[i] < 0 || slots[i] >= E.max_seqs || pos[i] < 0 || pos[i] >= E.max_ctx) return fail(B200_ERR_INVALID, "bad prefill row");
     if (int rc = ensure_prefill_buffers()) return rc;
@@ -872,7 +922,7 @@ void Model::maybe_bf16_cache() {
 
 int Model::prefill(const int32_t* toks, int n) {                      // batch-1 path: sequence slot 0, continues at cur_pos
     Engine& E = engine();
-    if (int rc = prefill_slot(0, toks, n, cur_pos)) return rc;
+    if (int rc = prefill_slot(sync_slot, toks, n, cur_pos)) return rc;
     cur_pos += n;
     int st = cur_pos; CK(cudaMemcpyAsync(d_state, &st, 4, cudaMemcpyHostToDevice, E.stream));
     CK(cudaStreamSynchronize(E.stream));
@@ -881,8 +931,9 @@ int Model::prefill(const int32_t* toks, int n) {                      // batch-1
 
 // One decode step for B sequences: row i feeds token toks[i] of sequence slot slots[i] at position pos[i];
 // next[i] = greedy next token.  Rows are independent (a row's result does not depend on which other rows are present).
-int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* pos, int B, int32_t* next, float* logits) {
+int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* pos, int B, int32_t* next, float* logits, const b200_sampling* samp, const int32_t* draw) {
     Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    if (!committed) return fail(B200_ERR_STATE, "model '" + id + "' is not loaded (closed or deleted)");
     if (B < 1 || B > E.max_seqs || B > PREFILL_CHUNK) return fail(B200_ERR_INVALID, "batch size out of range");
     for (int i = 0; i < B; i++) if (toks[i] < 0 || toks[i] >= n_vocab || slots[i] < 0 || slots[i] >= E.max_seqs || pos[i] < 0 || pos[i] >= E.max_ctx) return fail(B200_ERR_INVALID, "bad batch row");
     if (int rc = ensure_prefill_buffers()) return rc;
@@ -893,9 +944,21 @@ int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* 
     CK(cudaMemcpyAsync(pf_toks + 2 * Mc, slots, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
     const int ldv = (n_vocab_l + 3) & ~3, Wp = E.tp_world;
     const bool q = use_qgemm(B);
+    {   // per-row sampling requests (temperature 0 = keep the argmax); the draw counter is the number of tokens the
+        // request has generated so far, the same counter the batch-1 path uses, so a seeded request draws the same
+        // tokens whether it runs alone or inside a batch
+        std::vector<RowSampling> rs((size_t)B);
+        for (int i = 0; i < B; i++) {
+            RowSampling r{}; if (samp && samp[i].temperature > 0.f) { r.temperature = samp[i].temperature; r.top_p = samp[i].top_p; r.top_k = samp[i].top_k; r.seed = samp[i].seed; r.step = draw ? (uint64_t)draw[i] : 0; }
+            rs[i] = r;
+        }
+        CK(cudaMemcpyAsync(bt_samp, rs.data(), (size_t)B * sizeof(RowSampling), cudaMemcpyHostToDevice, E.stream));   // pageable source: staged before the call returns
+    }
     auto body = [&]() -> int {
         if (int rc = dense_rows(pf_toks, B, pf_toks + Mc, pf_toks + 2 * Mc, 0, 0, true, q)) return rc;
         CK(launch_pdl(argmax_rows_kernel, dim3(B), dim3(1024), 0, E.stream, (const float*)bt_logits, n_vocab_l, ldv, Wp, (size_t)B * ldv, bt_next)); E.launches++;
+        sample_rows_kernel<<<B, SAMPLER_THREADS, 0, E.stream>>>((const float*)bt_logits, n_vocab, n_vocab_l, ldv, (size_t)B * ldv, (const RowSampling*)bt_samp, bt_next); E.launches++;
+        CK(cudaGetLastError());
         return B200_OK;
     };
     // The step is a fixed chain of ~9 launches per layer whose arguments depend only on B (tokens, positions and slots are
@@ -1015,8 +1078,8 @@ int kernel_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K
         return fail(B200_ERR_INVALID, "b200_dequantize_noalloc: " + std::to_string(need) + " bytes of scratch needed, the built-in buffer holds " +
                                           std::to_string((size_t)B200_NOALLOC_SCRATCH_BYTES) + " (use b200_dequantize, which allocates)");
     std::lock_guard<std::mutex> lk(g_noalloc_mu);                    // host callers of this library take turns on the shared array
-    CK(cudaSetDevice(E.device));
     if (E.device < 0 || E.device >= 64) return fail(B200_ERR_INVALID, "device ordinal out of range");
+    CK(cudaSetDevice(E.device));
     if (!g_noalloc_ptr[E.device]) {
         // First use on this device: resolve the array's device address.  In host code the array's name is only a
         // handle for the runtime, not something a kernel can dereference.
@@ -1028,11 +1091,13 @@ int kernel_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K
     unsigned char* scratch = g_noalloc_ptr[E.device];
     // Nothing in the array has to start at zero: repack_kernel writes every byte of the `need` bytes (padding rows
     // and padding groups included) before dequant_repacked_kernel reads them, so leftovers of earlier calls are inert.
-    if (int rc = repack(E, (const uint8_t*)d_raw, scratch, type, N, n_rows, K)) return rc;
-    dequant_repacked_kernel<<<(int)std::min<long long>((n_rows * (long long)K + 255) / 256, 148 * 16), 256, 0, E.stream>>>(scratch, type, n_rows, K, d_out);
+    // Queued on the engine's utility stream (created by b200_init), never on the generation stream: the scheduler may be
+    // capturing that one into a CUDA graph at this moment, and a foreign launch or a synchronise would break the capture.
+    if (int rc = repack(E, (const uint8_t*)d_raw, scratch, type, N, n_rows, K, -1, 0, E.aux_stream)) return rc;
+    dequant_repacked_kernel<<<(int)std::min<long long>((n_rows * (long long)K + 255) / 256, 148 * 16), 256, 0, E.aux_stream>>>(scratch, type, n_rows, K, d_out);
     CK(cudaGetLastError());
     E.launches++;
-    CK(cudaStreamSynchronize(E.stream));                             // the array is free again when this returns
+    CK(cudaStreamSynchronize(E.aux_stream));                         // the array is free again when this returns
     return B200_OK;
 }
 

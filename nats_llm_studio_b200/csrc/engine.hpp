@@ -4,6 +4,7 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
+#include <chrono>
 #include <condition_variable>
 #include <cstdint>
 #include <deque>
@@ -36,6 +37,7 @@ struct Engine {
     bool ready = false;
     int device = 0, max_ctx = 4096, max_seqs = 1, n_sm = 0, smem_per_sm = 0, smem_optin = 0;
     cudaStream_t stream = nullptr, copy_stream = nullptr;
+    cudaStream_t aux_stream = nullptr;           // allocation-free utility calls (never captured into a step graph)
     uint64_t launches = 0;                       // kernels launched by this library (bench.py reports it)
     float* qg_ws = nullptr;                      // stream-K partial tiles of the dequant-in-GEMM kernel
     // tensor parallelism: one process per GPU, NCCL communicator created from an id the host side distributes
@@ -70,13 +72,15 @@ struct Model {
     float* d_logits = nullptr; uint32_t* d_ll16 = nullptr; uint2* d_ll32 = nullptr; int hown_cap = 0;
     int *d_state = nullptr, *d_out_tokens = nullptr, *d_forced = nullptr, *d_block_table = nullptr;
     __half* d_kv = nullptr; int n_pages = 0, n_splits = 1;
+    int sync_slot = 0;                           // KV sequence slot of the synchronous batch-1 path (generate / eval / chat with max_seqs == 1);
+                                                 // with max_seqs > 1 it is an extra slot the scheduler never hands out
     int grid = 0, smem_max_grp = 0; uint32_t ring_bytes = 0; size_t smem_bytes = 0;
     int cur_pos = 0;
     long long* d_trace = nullptr;
     // prefill scratch (allocated on first use)
     static constexpr int PREFILL_CHUNK = 512;
     float *pf_H = nullptr, *pf_Y = nullptr; __nv_bfloat16 *pf_X = nullptr, *pf_Q = nullptr, *pf_ACT = nullptr, *pf_W = nullptr; int* pf_toks = nullptr;
-    float* bt_logits = nullptr; int* bt_next = nullptr; __nv_bfloat16* b_out = nullptr; bool bf16_ready = false; int pages_per_seq = 0;
+    float* bt_logits = nullptr; int* bt_next = nullptr; struct RowSampling* bt_samp = nullptr; __nv_bfloat16* b_out = nullptr; bool bf16_ready = false; int pages_per_seq = 0;
     int prefill_min = 32;                        // prompts shorter than this go through the decode kernel token by token
     std::mutex run_mu;
 
@@ -90,7 +94,8 @@ struct Model {
     int load_vector(const std::string& name, int64_t n, float** out);
     void fill_params(DecodeParams& P) const;
     int run_steps(int n_steps, const int32_t* forced, int n_forced, bool reset, float* logits_all_dev);
-    int generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_sampling* s, int32_t* out, int* n_out, float* ttft_ms, float* decode_ms);
+    int generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_sampling* s, int32_t* out, int* n_out, float* ttft_ms, float* decode_ms,
+                 int* finish_reason = nullptr, const std::chrono::steady_clock::time_point* t_submit = nullptr);   // t_submit: start of s->timeout_ms
     int eval(const int32_t* toks, int n, float* logits_all, float* logits_last);
     double bytes_per_token(int ctx) const;
     int bench_decode(int ctx_len, int n_steps, int warmup, float* ms_per_token, double* bytes);
@@ -109,7 +114,8 @@ struct Model {
     std::vector<cudaGraphExec_t> step_graph; std::vector<char> step_seen; std::vector<int> step_launches; bool graph_failed = false;   // batch_step: one CUDA graph per batch size
     int prefill_slot(int slot, const int32_t* toks, int n, int pos0);
     int prefill(const int32_t* toks, int n);
-    int batch_step(const int32_t* toks, const int32_t* slots, const int32_t* pos, int B, int32_t* next, float* logits = nullptr);
+    int batch_step(const int32_t* toks, const int32_t* slots, const int32_t* pos, int B, int32_t* next, float* logits = nullptr,
+                   const b200_sampling* samp = nullptr, const int32_t* draw = nullptr);   // samp[B], draw[B] (tokens already generated per row) or null = greedy
     // tokenizer (tokenizer.cpp)
     void build_tokenizer();
     std::vector<int32_t> tokenize(const std::string& text, bool parse_special) const;
@@ -118,6 +124,7 @@ struct Model {
 };
 
 int sample_token(Engine& E, Model& m, const b200_sampling& s, uint64_t step);
+int kernel_sample(const float* logits, int V, const b200_sampling& s, uint64_t step, int* token);
 int kernel_dequantize(int type, const void* raw, int64_t n_rows, int K, float* out);
 int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, float* y, int iters, float* ms);
 int kernel_gemm_bf16(const float* A, const float* B, float* C, int M, int N, int K);
@@ -133,5 +140,7 @@ struct Registry {
 };
 Registry& registry();
 std::string handle_subject(const std::string& subject, const std::string& payload);
+// blocking generation through the continuous-batching scheduler (capi.cpp): what lmstudio.chat_model uses when max_seqs > 1
+int sched_generate(const std::shared_ptr<Model>& m, const std::vector<int32_t>& prompt, const b200_sampling& s, std::vector<int32_t>& out, float* ttft_ms, float* decode_ms, int* finish_reason);
 
 }  // namespace b200

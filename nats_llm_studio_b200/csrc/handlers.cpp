@@ -107,10 +107,16 @@ static bool decode_string_field(const std::string& payload, const char* field, c
 }
 
 // ------------------------------------------------------------------------------------ list / pull / delete
-static std::string on_list_models() {                                   // onListModels :228-248
+static Json list_models() {
     Json list = Json::array();
     { Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); for (auto& kv : R.models) if (kv.second->committed) list.push(model_entry(*kv.second)); }
     Json models = Json::object(); models.set("data", list).set("object", Json::string("list"));
+    return models;
+}
+std::string list_models_json() { return json_dump(list_models()); }
+
+static std::string on_list_models() {                                   // onListModels :228-248
+    Json models = list_models();
     Json data = Json::object(true); data.set("http_status", Json::integer(200)).set("models", models);
     return envelope(true, "", &data);
 }
@@ -235,12 +241,21 @@ static std::string on_chat_model(const std::string& payload) {          // OnCha
     if (max_tokens <= 0 || max_tokens > room) max_tokens = std::min(room, max_tokens <= 0 ? 512 : max_tokens);
     s.max_tokens = max_tokens; s.stop_token = -1; { auto it = m->special.find("<|end|>"); if (it != m->special.end()) s.stop_token = it->second; }
     const Json* ign = doc.get("ignore_eos"); s.ignore_eos = ign && ign->kind == Json::Bool && ign->b;
-    std::vector<int32_t> out((size_t)max_tokens); int n_out = 0; float ttft = 0, dec = 0;
+    // the reference bounds the handler with a 2-minute context (:328); a generation that outlives it is answered the way
+    // a cancelled context would be: ok:false with Go's deadline error text.  B200_CHAT_TIMEOUT_MS overrides (tests).
+    s.timeout_ms = 120000; if (const char* e = getenv("B200_CHAT_TIMEOUT_MS")) s.timeout_ms = std::max(1, atoi(e));
+    std::vector<int32_t> out; float ttft = 0, dec = 0; int reason = 0;
     auto t0 = std::chrono::steady_clock::now();
-    if (m->generate(toks.data(), (int)toks.size(), max_tokens, &s, out.data(), &n_out, &ttft, &dec) != B200_OK)
+    // max_seqs > 1: the request joins the continuous-batching scheduler, so concurrent chat requests share batched steps
+    if (sched_generate(m, toks, s, out, &ttft, &dec, &reason) != B200_OK)
         return reply(500, lm_error(g_last_error, "internal_error", nullptr, nullptr));
+    if (reason == B200_FINISH_TIMEOUT || reason == B200_FINISH_CANCELLED) {
+        Json data = Json::object(true); data.set("http_status", Json::integer(0));
+        return envelope(false, std::string("error calling LM Studio: ") + (reason == B200_FINISH_TIMEOUT ? "context deadline exceeded" : "context canceled"), &data);
+    }
+    const int n_out = (int)out.size();
     double wall_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-    bool stopped = n_out > 0 && !s.ignore_eos && (out[n_out - 1] == m->eos || out[n_out - 1] == s.stop_token);
+    bool stopped = reason == B200_FINISH_STOP;
     int n_text = stopped ? n_out - 1 : n_out;
     static std::atomic<uint64_t> counter{0};
     char idbuf[64]; snprintf(idbuf, sizeof idbuf, "chatcmpl-%012llx", (unsigned long long)(++counter));

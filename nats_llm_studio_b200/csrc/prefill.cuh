@@ -522,7 +522,7 @@ __global__ void argmax_rows_kernel(const float* __restrict__ logits, int V, int 
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int w = 1; w < (int)(blockDim.x >> 5); w++) if (sv[w] > bv || (sv[w] == bv && si[w] < bi)) { bv = sv[w]; bi = si[w]; }
-        next[blockIdx.x] = bi;
+        next[blockIdx.x] = bi < n_parts * V ? bi : 0;                  // all-NaN logits: stay inside the vocabulary
     }
 }
 

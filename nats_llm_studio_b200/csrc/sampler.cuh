@@ -25,20 +25,46 @@ __host__ __device__ inline void philox4x32_10(uint64_t seed, uint64_t ctr, uint3
 
 __device__ __forceinline__ uint32_t float_key(float f) { uint32_t b = __float_as_uint(f); return (b & 0x80000000u) ? ~b : (b | 0x80000000u); }
 
-__global__ void __launch_bounds__(SAMPLER_THREADS, 1)
-sample_kernel(const float* __restrict__ logits, int V, int top_k, float top_p, float temperature, uint64_t seed, uint64_t step,
-              int* __restrict__ token_out, int* __restrict__ out_slot) {
+// Per-row sampling request of the batched path (device copy of the b200_sampling fields the draw needs + the draw counter).
+struct RowSampling { float temperature, top_p; int top_k, pad; uint64_t seed, step; };
+
+// Logits of one sequence.  A tensor-parallel engine holds them in `parts` slices of V_l vocabulary entries each
+// ([part][row][ldv], see Model::dense_rows); a single GPU has one part.
+struct LogitView {
+    const float* base; int V, V_l; size_t part_stride;
+    __device__ __forceinline__ float at(int i) const { return V_l >= V ? base[i] : base[(size_t)(i / V_l) * part_stride + (i % V_l)]; }
+};
+
+// inclusive prefix sum of one value per thread over the block (fixed order: warp shuffles, then the warp totals)
+__device__ __forceinline__ float block_scan(float v, float* warp_tot /* [32] shared */, float& total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const float t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += t; }
+    __syncthreads();                                   // warp_tot free (previous scan's readers done)
+    if (lane == 31) warp_tot[warp] = v;
+    __syncthreads();
+    float pre = 0.f, tot = 0.f;
+#pragma unroll
+    for (int w = 0; w < SAMPLER_THREADS / 32; w++) { const float t = warp_tot[w]; if (w < warp) pre += t; tot += t; }
+    total = tot;
+    return v + pre;
+}
+
+// One block samples one token.  Shared by the batch-1 kernel and the per-row kernel of the batched path, so a
+// request's tokens do not depend on which path (or which batch) served it.
+__device__ __forceinline__ int sample_block(const LogitView& lg, int top_k, float top_p, float temperature, uint64_t seed, uint64_t step) {
     __shared__ unsigned hist[256];
     __shared__ float cv[SAMPLER_BUF]; __shared__ int ci[SAMPLER_BUF];
-    __shared__ unsigned n_cand; __shared__ uint32_t sh_prefix; __shared__ int sh_remaining;
-    const int tid = threadIdx.x;
+    __shared__ float warp_tot[32];
+    __shared__ unsigned n_cand; __shared__ uint32_t sh_prefix; __shared__ int sh_remaining, sh_first;
+    const int tid = threadIdx.x, V = lg.V;
     const int K = (top_k > 0 && top_k < SAMPLER_CAND) ? min(top_k, V) : min(SAMPLER_CAND, V);
     // ---- radix select: key of the K-th largest logit
     uint32_t prefix = 0, mask = 0; int remaining = K;
     for (int shift = 24; shift >= 0; shift -= 8) {
         if (tid < 256) hist[tid] = 0;
         __syncthreads();
-        for (int i = tid; i < V; i += SAMPLER_THREADS) { uint32_t k = float_key(logits[i]); if ((k & mask) == prefix) atomicAdd(&hist[(k >> shift) & 255], 1u); }
+        for (int i = tid; i < V; i += SAMPLER_THREADS) { uint32_t k = float_key(lg.at(i)); if ((k & mask) == prefix) atomicAdd(&hist[(k >> shift) & 255], 1u); }
         __syncthreads();
         if (tid == 0) {
             int rem = remaining, b = 255;
@@ -53,7 +79,7 @@ sample_kernel(const float* __restrict__ logits, int V, int top_k, float top_p, f
     if (tid == 0) n_cand = 0;
     __syncthreads();
     for (int i = tid; i < V; i += SAMPLER_THREADS) {
-        float v = logits[i];
+        float v = lg.at(i);
         if (float_key(v) >= prefix) { unsigned s = atomicAdd(&n_cand, 1u); if (s < SAMPLER_BUF) { cv[s] = v; ci[s] = i; } }
     }
     __syncthreads();
@@ -72,21 +98,48 @@ sample_kernel(const float* __restrict__ logits, int V, int top_k, float top_p, f
             }
             __syncthreads();
         }
-    // ---- nucleus at T=1, then draw at temperature (thread 0; K <= 1024 terms)
-    if (tid == 0) {
-        const int kk = min(K, n);
-        const float mx = cv[0];
-        float tot = 0.f; for (int i = 0; i < kk; i++) tot += expf(cv[i] - mx);
-        int keep = kk;
-        if (top_p < 1.f) { float cum = 0.f; for (int i = 0; i < kk; i++) { cum += expf(cv[i] - mx); if (cum >= top_p * tot) { keep = i + 1; break; } } }
-        const float invT = 1.f / temperature;
-        float tot2 = 0.f; for (int i = 0; i < keep; i++) tot2 += expf((cv[i] - mx) * invT);
-        uint32_t r[4]; philox4x32_10(seed, step, r);
-        const float u = (float)(r[0] >> 8) * (1.0f / 16777216.0f) * tot2;
-        float cum = 0.f; int pick = keep - 1;
-        for (int i = 0; i < keep; i++) { cum += expf((cv[i] - mx) * invT); if (cum > u) { pick = i; break; } }
-        *token_out = ci[pick]; if (out_slot) *out_slot = ci[pick];
+    // ---- nucleus at T=1, then the draw at temperature: candidate i belongs to thread i (K <= 1024 = block size);
+    //      cumulative sums by block-wide scans, cut points by an atomic minimum over the threads that satisfy them
+    const int kk = min(K, n);
+    const float mx = cv[0];
+    int keep = kk;
+    if (top_p < 1.f) {
+        float tot; const float cum = block_scan(tid < kk ? expf(cv[tid] - mx) : 0.f, warp_tot, tot);
+        if (tid == 0) sh_first = kk - 1;
+        __syncthreads();
+        if (tid < kk && cum >= top_p * tot) atomicMin(&sh_first, tid);
+        __syncthreads();
+        keep = sh_first + 1;
+        __syncthreads();
     }
+    const float invT = 1.f / temperature;
+    float tot2; const float cum2 = block_scan(tid < keep ? expf((cv[tid] - mx) * invT) : 0.f, warp_tot, tot2);
+    uint32_t r[4]; philox4x32_10(seed, step, r);
+    const float u = (float)(r[0] >> 8) * (1.0f / 16777216.0f) * tot2;
+    if (tid == 0) sh_first = keep - 1;
+    __syncthreads();
+    if (tid < keep && cum2 > u) atomicMin(&sh_first, tid);
+    __syncthreads();
+    return ci[sh_first];
+}
+
+__global__ void __launch_bounds__(SAMPLER_THREADS, 1)
+sample_kernel(const float* __restrict__ logits, int V, int top_k, float top_p, float temperature, uint64_t seed, uint64_t step,
+              int* __restrict__ token_out, int* __restrict__ out_slot) {
+    const LogitView lg{logits, V, V, 0};
+    const int t = sample_block(lg, top_k, top_p, temperature, seed, step);
+    if (threadIdx.x == 0) { *token_out = t; if (out_slot) *out_slot = t; }
+}
+
+// Batched decode: block b draws row b's token when that row asked for sampling (temperature > 0); greedy rows keep the
+// argmax already in next[b].  Parameters come from device memory so the launch is identical from step to step (CUDA graph).
+__global__ void __launch_bounds__(SAMPLER_THREADS, 1)
+sample_rows_kernel(const float* __restrict__ logits, int V, int V_l, int ldv, size_t part_stride, const RowSampling* __restrict__ rs, int* __restrict__ next) {
+    const RowSampling s = rs[blockIdx.x];
+    if (!(s.temperature > 0.f)) return;
+    const LogitView lg{logits + (size_t)blockIdx.x * ldv, V, V_l, part_stride};
+    const int t = sample_block(lg, s.top_k, s.top_p <= 0.f ? 1.f : s.top_p, s.temperature, s.seed, s.step);
+    if (threadIdx.x == 0) next[blockIdx.x] = t;
 }
 
 }  // namespace b200

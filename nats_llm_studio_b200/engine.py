@@ -14,7 +14,7 @@ _lib = None
 
 
 EV_TOKEN, EV_FINISH, EV_ERROR = 1, 2, 3                     # b200_event.kind
-FINISH_STOP, FINISH_LENGTH, FINISH_CANCELLED = 1, 2, 3      # b200_event.finish_reason
+FINISH_STOP, FINISH_LENGTH, FINISH_CANCELLED, FINISH_TIMEOUT = 1, 2, 3, 4      # b200_event.finish_reason
 
 
 class EngineError(RuntimeError):
@@ -30,7 +30,7 @@ class Config(C.Structure):
 
 class Sampling(C.Structure):
     _fields_ = [("temperature", C.c_float), ("top_k", C.c_int), ("top_p", C.c_float), ("seed", C.c_uint64),
-                ("max_tokens", C.c_int), ("stop_token", C.c_int), ("ignore_eos", C.c_int)]
+                ("max_tokens", C.c_int), ("stop_token", C.c_int), ("ignore_eos", C.c_int), ("timeout_ms", C.c_int)]
 
 
 class Event(C.Structure):
@@ -53,10 +53,12 @@ SYMBOLS = {
     "b200_model_eval": (ci, [vp, vp, ci, vp, vp]), "b200_model_n_vocab": (ci, [vp]),
     "b200_tokenize": (ci, [vp, C.c_char_p, sz, vp, ci, C.POINTER(ci)]), "b200_detokenize": (ci, [vp, vp, ci, vp, sz, C.POINTER(sz)]),
     "b200_handle": (ci, [C.c_char_p, vp, sz, vp, sz, C.POINTER(sz)]), "b200_set_models_dir": (ci, [C.c_char_p]),
+    "b200_sample": (ci, [vp, ci, C.POINTER(Sampling), C.c_uint64, C.POINTER(ci)]),
     "b200_dequantize": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_dequantize_noalloc": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_gemv": (ci, [ci, vp, C.c_int64, ci, vp, vp, ci, C.POINTER(C.c_float)]),
     "b200_bench_decode": (ci, [vp, ci, ci, ci, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
     "b200_gemm_bf16": (ci, [vp, vp, vp, ci, ci, ci]), "b200_qgemm": (ci, [ci, vp, C.c_int64, ci, vp, ci, vp, ci, C.POINTER(C.c_float)]), "b200_model_prefill_slot": (ci, [vp, ci, vp, ci, ci]),
     "b200_model_batch_step": (ci, [vp, vp, vp, vp, ci, vp, vp]),
+    "b200_model_batch_step_sampled": (ci, [vp, vp, vp, vp, ci, vp, vp, vp, vp]),
     "b200_tp_unique_id": (ci, [vp, sz]), "b200_tp_init": (ci, [ci, ci, vp, sz]), "b200_model_set_prefill_min": (ci, [vp, ci]),
     "b200_launch_count": (C.c_uint64, []), "b200_layout_selftest": (ci, []),
 }
@@ -123,15 +125,15 @@ class Model:
     def generate(self, prompt, n_gen, temperature=0.0, top_k=0, top_p=1.0, seed=0, ignore_eos=True, stop_token=-1):
         prompt = np.ascontiguousarray(prompt, dtype=np.int32)
         out = np.empty(n_gen, dtype=np.int32)
-        s = Sampling(temperature, top_k, top_p, seed, n_gen, stop_token, int(ignore_eos))
+        s = Sampling(temperature, top_k, top_p, seed, n_gen, stop_token, int(ignore_eos), 0)
         n_out, ttft, dec = ci(0), C.c_float(0), C.c_float(0)
         _check(lib().b200_model_generate(self.h, prompt.ctypes.data, len(prompt), n_gen, C.byref(s), out.ctypes.data,
                                          C.byref(n_out), C.byref(ttft), C.byref(dec)))
         return out[:n_out.value], ttft.value, dec.value
 
-    def submit(self, prompt, req_id, max_tokens=256, temperature=0.0, top_k=0, top_p=1.0, seed=0, ignore_eos=True, stop_token=-1):
+    def submit(self, prompt, req_id, max_tokens=256, temperature=0.0, top_k=0, top_p=1.0, seed=0, ignore_eos=True, stop_token=-1, timeout_ms=0):
         prompt = np.ascontiguousarray(prompt, dtype=np.int32)
-        s = Sampling(temperature, top_k, top_p, seed, max_tokens, stop_token, int(ignore_eos))
+        s = Sampling(temperature, top_k, top_p, seed, max_tokens, stop_token, int(ignore_eos), timeout_ms)
         _check(lib().b200_submit(self.h, prompt.ctypes.data, len(prompt), C.byref(s), req_id))
 
     def prefill_slot(self, slot, toks, pos0=0):
@@ -144,6 +146,17 @@ class Model:
         lg = np.empty((len(toks), self.n_vocab), dtype=np.float32) if want_logits else None
         _check(lib().b200_model_batch_step(self.h, toks.ctypes.data, slots.ctypes.data, pos.ctypes.data, len(toks), nxt.ctypes.data,
                                            lg.ctypes.data if want_logits else None))
+        return (nxt, lg) if want_logits else nxt
+
+    def batch_step_sampled(self, toks, slots, pos, samp, draw, want_logits=False):
+        """samp: list of dicts (temperature, top_k, top_p, seed) per row; draw: tokens each row's request has generated so far"""
+        toks = np.ascontiguousarray(toks, dtype=np.int32); slots = np.ascontiguousarray(slots, dtype=np.int32); pos = np.ascontiguousarray(pos, dtype=np.int32)
+        draw = np.ascontiguousarray(draw, dtype=np.int32)
+        arr = (Sampling * len(toks))(*[Sampling(d.get("temperature", 0.0), d.get("top_k", 0), d.get("top_p", 1.0), d.get("seed", 0), 0, -1, 1, 0) for d in samp])
+        nxt = np.empty(len(toks), dtype=np.int32)
+        lg = np.empty((len(toks), self.n_vocab), dtype=np.float32) if want_logits else None
+        _check(lib().b200_model_batch_step_sampled(self.h, toks.ctypes.data, slots.ctypes.data, pos.ctypes.data, len(toks), arr, draw.ctypes.data,
+                                                   nxt.ctypes.data, lg.ctypes.data if want_logits else None))
         return (nxt, lg) if want_logits else nxt
 
     def set_prefill_min(self, n):
@@ -207,6 +220,13 @@ class Engine:
         ms = C.c_float(0)
         _check(lib().b200_qgemm(GGML_TYPES[type_name], raw.ctypes.data, N, K, x.ctypes.data, x.shape[0], y.ctypes.data, iters, C.byref(ms)))
         return (y, ms.value) if iters > 1 else y
+
+    @staticmethod
+    def sample(logits, temperature, top_k=0, top_p=1.0, seed=0, step=0):
+        logits = np.ascontiguousarray(logits, dtype=np.float32)
+        s = Sampling(temperature, top_k, top_p, seed, 0, -1, 1, 0); t = ci(0)
+        _check(lib().b200_sample(logits.ctypes.data, len(logits), C.byref(s), step, C.byref(t)))
+        return t.value
 
     @staticmethod
     def cancel(req_id):
