@@ -34,3 +34,17 @@ def test_cpu_arm_ignores_omp_num_threads(monkeypatch, golden_dir):
     r = bench.cpu_reference_arm(os.path.join(golden_dir, "tiny-llama.gguf"), 4, 4)
     want = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
     assert r["cores"] == want and r["value"] > 0 and r["kind"] == "port"
+
+
+def test_sampler_restatement_known_answers():
+    """tests/sampler_ref.py (the sampler's checker): Philox4x32-10 known-answer vector (Random123 kat_vectors:
+    counter 0, key 0), top_k=1 is the argmax, and the nucleus never keeps less than one candidate."""
+    import numpy as np
+    import sampler_ref
+    assert sampler_ref.philox4x32_10(0, 0) == [0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8]
+    lg = np.random.default_rng(0).standard_normal(300).astype(np.float32)
+    for seed in range(5):
+        assert sampler_ref.sample(lg, 0.8, top_k=1, seed=seed) == int(lg.argmax())
+        assert sampler_ref.sample(lg, 0.8, top_p=1e-9, seed=seed) == int(lg.argmax())
+        t, kept, probs, u = sampler_ref.sample(lg, 1.3, 40, 0.9, seed, 3, return_dist=True)
+        assert t in kept and len(kept) <= 40 and abs(probs.sum() - 1) < 1e-9
