@@ -149,6 +149,11 @@ int b200_tp_unique_id(void* out, size_t cap);
 int b200_tp_init(int rank, int world, const void* id, size_t n);
 /* decode-step timing: n_steps greedy tokens from the current position of a primed context */
 int b200_bench_decode(b200_model* m, int ctx_len, int n_steps, int warmup, float* ms_per_token, double* bytes_per_token);
+/* batched-step timing (BASELINE.json metric "bs64"; config 4's bs1/bs32 on a tensor-parallel engine): n_seqs sequences at
+ * context ctx advance by one token per step, `iters` steps between two CUDA events on the engine stream (no host copies
+ * inside); bytes_per_step = algorithmic HBM bytes of one step on this GPU (weights once, n_seqs embedding rows, K/V of
+ * every sequence) */
+int b200_bench_batch_step(b200_model* m, int n_seqs, int ctx, int iters, int warmup, float* ms_per_step, double* bytes_per_step);
 /* number of kernels this library has launched so far (bench.py reports the delta as gpu_launches) */
 uint64_t b200_launch_count(void);
 /* layout self-test (host only, no GPU): src_byte/dst_byte are inverse bijections for every type */

@@ -314,6 +314,7 @@ int b200_model_prefill_slot(b200_model* m, int slot, const int32_t* toks, int n,
     Model* M = (Model*)m; if (slot < 0 || slot >= engine().max_seqs) return fail(B200_ERR_INVALID, "bad sequence slot");
     std::lock_guard<std::mutex> lk(M->run_mu); return M->prefill_slot(slot, toks, n, pos0);
 }
+int b200_bench_batch_step(b200_model* m, int n_seqs, int ctx, int iters, int warmup, float* ms, double* bytes) { if (!m) return fail(B200_ERR_INVALID, "null model"); return ((Model*)m)->bench_batch(n_seqs, ctx, iters, warmup, ms, bytes); }
 int b200_tp_unique_id(void* out, size_t cap) { if (!out) return fail(B200_ERR_INVALID, "null argument"); if (int rc = engine().ensure()) return rc; return engine().tp_unique_id(out, cap); }
 int b200_tp_init(int rank, int world, const void* id, size_t n) { return engine().tp_init(rank, world, id, n); }
 int b200_layout_selftest(void) { return layout_selftest(); }

@@ -943,7 +943,6 @@ int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* 
     CK(cudaMemcpyAsync(pf_toks + Mc, pos, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
     CK(cudaMemcpyAsync(pf_toks + 2 * Mc, slots, (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
     const int ldv = (n_vocab_l + 3) & ~3, Wp = E.tp_world;
-    const bool q = use_qgemm(B);
     {   // per-row sampling requests (temperature 0 = keep the argmax); the draw counter is the number of tokens the
         // request has generated so far, the same counter the batch-1 path uses, so a seeded request draws the same
         // tokens whether it runs alone or inside a batch
@@ -954,6 +953,20 @@ int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* 
         }
         CK(cudaMemcpyAsync(bt_samp, rs.data(), (size_t)B * sizeof(RowSampling), cudaMemcpyHostToDevice, E.stream));   // pageable source: staged before the call returns
     }
+    if (int rc = step_enqueue(B)) return rc;
+    CK(cudaMemcpyAsync(next, bt_next, (size_t)B * 4, cudaMemcpyDeviceToHost, E.stream));
+    if (logits) for (int p = 0; p < Wp; p++)
+        CK(cudaMemcpy2DAsync(logits + (size_t)p * n_vocab_l, (size_t)n_vocab * 4, bt_logits + (size_t)p * B * ldv, (size_t)ldv * 4, (size_t)n_vocab_l * 4, B, cudaMemcpyDeviceToHost, E.stream));
+    CK(cudaStreamSynchronize(E.stream));
+    return B200_OK;
+}
+
+// Enqueues one batched decode step over B rows whose tokens / positions / slots / sampling requests are already in
+// the device buffers (pf_toks, bt_samp): direct launches the first time a batch size is seen, a CUDA graph afterwards.
+int Model::step_enqueue(int B) {
+    Engine& E = engine();
+    const int Mc = PREFILL_CHUNK, ldv = (n_vocab_l + 3) & ~3, Wp = E.tp_world;
+    const bool q = use_qgemm(B);
     auto body = [&]() -> int {
         if (int rc = dense_rows(pf_toks, B, pf_toks + Mc, pf_toks + 2 * Mc, 0, 0, true, q)) return rc;
         CK(launch_pdl(argmax_rows_kernel, dim3(B), dim3(1024), 0, E.stream, (const float*)bt_logits, n_vocab_l, ldv, Wp, (size_t)B * ldv, bt_next)); E.launches++;
@@ -986,11 +999,45 @@ int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* 
         if (int rc = body()) return rc;
         step_seen[B] = 1;                                          // buffers, tile weights and function attributes now exist
     }
-    CK(cudaMemcpyAsync(next, bt_next, (size_t)B * 4, cudaMemcpyDeviceToHost, E.stream));
-    if (logits) for (int p = 0; p < Wp; p++)
-        CK(cudaMemcpy2DAsync(logits + (size_t)p * n_vocab_l, (size_t)n_vocab * 4, bt_logits + (size_t)p * B * ldv, (size_t)ldv * 4, (size_t)n_vocab_l * 4, B, cudaMemcpyDeviceToHost, E.stream));
-    CK(cudaStreamSynchronize(E.stream));
     return B200_OK;
+}
+
+// Device-timed batched step (bench.py "batched" roofline): B sequences at context ctx, `iters` steps between two CUDA
+// events on the engine stream, nothing crossing PCIe inside the timed region.  The KV pages hold whatever they hold
+// (the cost of attention does not depend on the values), every step re-runs position ctx.
+// bytes = algorithmic HBM bytes of one step: every matrix except token_embd once (the batch shares the weights), B
+// embedding rows, the norm vectors, and fp16 K/V of ctx+1 positions for each of the B sequences.
+int Model::bench_batch(int B, int ctx, int iters, int warmup, float* ms_per_step, double* bytes) {
+    Engine& E = engine(); if (int rc = E.ensure()) return rc;
+    std::lock_guard<std::mutex> lk(run_mu);
+    if (!committed) return fail(B200_ERR_STATE, "model '" + id + "' is not loaded (closed or deleted)");
+    if (B < 1 || B > E.max_seqs || B > QG_NB || ctx < 1 || ctx + 1 > E.max_ctx || iters < 1) return fail(B200_ERR_INVALID, "bench_batch: batch, context or iteration count out of range");
+    if (int rc = ensure_prefill_buffers()) return rc;
+    if (!use_qgemm(B)) { if (int rc = ensure_bf16_weights()) return rc; }
+    const int Mc = PREFILL_CHUNK;
+    std::vector<int32_t> toks(B), pos(B, ctx), slots(B);
+    for (int i = 0; i < B; i++) { toks[i] = (int)((1000003u * (unsigned)(i + 1)) % (unsigned)n_vocab); slots[i] = i; }
+    std::vector<RowSampling> rs((size_t)B, RowSampling{});
+    CK(cudaMemcpyAsync(pf_toks, toks.data(), (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
+    CK(cudaMemcpyAsync(pf_toks + Mc, pos.data(), (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
+    CK(cudaMemcpyAsync(pf_toks + 2 * Mc, slots.data(), (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
+    CK(cudaMemcpyAsync(bt_samp, rs.data(), (size_t)B * sizeof(RowSampling), cudaMemcpyHostToDevice, E.stream));
+    for (int i = 0; i < std::max(warmup, 2); i++) if (int rc = step_enqueue(B)) return rc;      // >= 2: the second pass builds the graph
+    CK(cudaStreamSynchronize(E.stream));
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    CK(cudaEventRecord(e0, E.stream));
+    int rc = B200_OK;
+    for (int i = 0; i < iters && !rc; i++) rc = step_enqueue(B);
+    CK(cudaEventRecord(e1, E.stream)); CK(cudaEventSynchronize(e1));
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1); cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (ms_per_step) *ms_per_step = ms / iters;
+    if (bytes) {
+        const GgufTensor* te = meta.tensor("token_embd.weight");
+        double w = (double)weight_bytes;
+        if (meta.tensor("output.weight") || tp) w -= (double)te->nbytes;          // a shard counts token_embd and its output slice separately
+        *bytes = w + (double)B * te->nbytes / n_vocab + (double)B * (ctx + 1) * n_layer * 2 * n_head_kv * head_dim * 2;
+    }
+    return rc;
 }
 
 // test entry: y[b][n] = sum_k x[b][k] * W[n][k] through the dequant-in-GEMM kernel (raw ggml rows from the host)

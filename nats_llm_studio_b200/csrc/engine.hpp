@@ -116,6 +116,8 @@ struct Model {
     int prefill(const int32_t* toks, int n);
     int batch_step(const int32_t* toks, const int32_t* slots, const int32_t* pos, int B, int32_t* next, float* logits = nullptr,
                    const b200_sampling* samp = nullptr, const int32_t* draw = nullptr);   // samp[B], draw[B] (tokens already generated per row) or null = greedy
+    int step_enqueue(int B);
+    int bench_batch(int B, int ctx, int iters, int warmup, float* ms_per_step, double* bytes);
     // tokenizer (tokenizer.cpp)
     void build_tokenizer();
     std::vector<int32_t> tokenize(const std::string& text, bool parse_special) const;

@@ -56,6 +56,7 @@ SYMBOLS = {
     "b200_sample": (ci, [vp, ci, C.POINTER(Sampling), C.c_uint64, C.POINTER(ci)]),
     "b200_dequantize": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_dequantize_noalloc": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_gemv": (ci, [ci, vp, C.c_int64, ci, vp, vp, ci, C.POINTER(C.c_float)]),
     "b200_bench_decode": (ci, [vp, ci, ci, ci, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
+    "b200_bench_batch_step": (ci, [vp, ci, ci, ci, ci, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
     "b200_gemm_bf16": (ci, [vp, vp, vp, ci, ci, ci]), "b200_qgemm": (ci, [ci, vp, C.c_int64, ci, vp, ci, vp, ci, C.POINTER(C.c_float)]), "b200_model_prefill_slot": (ci, [vp, ci, vp, ci, ci]),
     "b200_model_batch_step": (ci, [vp, vp, vp, vp, ci, vp, vp]),
     "b200_model_batch_step_sampled": (ci, [vp, vp, vp, vp, ci, vp, vp, vp, vp]),
@@ -165,6 +166,12 @@ class Model:
     def bench_decode(self, ctx_len, n_steps, warmup):
         ms, by = C.c_float(0), C.c_double(0)
         _check(lib().b200_bench_decode(self.h, ctx_len, n_steps, warmup, C.byref(ms), C.byref(by)))
+        return ms.value, by.value
+
+    def bench_batch_step(self, n_seqs, ctx, iters=20, warmup=3):
+        """device-timed batched decode step: (ms per step, algorithmic HBM bytes per step on this GPU)"""
+        ms, by = C.c_float(0), C.c_double(0)
+        _check(lib().b200_bench_batch_step(self.h, n_seqs, ctx, iters, warmup, C.byref(ms), C.byref(by)))
         return ms.value, by.value
 
     def tokenize(self, text):

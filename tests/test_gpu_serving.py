@@ -120,7 +120,10 @@ def test_concurrent_chat_requests_share_the_scheduler(engine, golden_dir):
     m = engine.load_file("sv/chat", os.path.join(golden_dir, "tiny-llama.gguf"))
     texts = [("q%d " % i) * (1 + i % 7) for i in range(64)]
     extra = [dict(temperature=0.8, seed=1000 + i, top_k=40) if i % 4 == 3 else {} for i in range(64)]
-    solo = [_chat(engine, "sv/chat", t, **x) for t, x in zip(texts[:12], extra[:12])]
+    _chat(engine, "sv/chat", "warm")                       # one-time weight-layout builds happen here
+    l0 = engine.launch_count()
+    solo = [_chat(engine, "sv/chat", t, **x) for t, x in zip(texts, extra)]
+    launches_one_by_one = engine.launch_count() - l0
     out = [None] * 64
     def work(i):
         out[i] = _chat(engine, "sv/chat", texts[i], **extra[i])
@@ -133,11 +136,10 @@ def test_concurrent_chat_requests_share_the_scheduler(engine, golden_dir):
         assert r["ok"] and r["data"]["http_status"] == 200, r
         resp = r["data"]["response"]
         assert resp["usage"]["completion_tokens"] == 8 and resp["choices"][0]["finish_reason"] == "length"
-        if i < 12:
-            assert resp["choices"][0]["message"]["content"] == solo[i]["data"]["response"]["choices"][0]["message"]["content"], i
-            assert resp["usage"] == solo[i]["data"]["response"]["usage"]
-    # 64 requests x 8 tokens one at a time would be >= 512 decode passes of >= 10 launches each; batched, the steps are shared
-    assert launches < 64 * 8 * 10 / 3, launches
+        assert resp["choices"][0]["message"]["content"] == solo[i]["data"]["response"]["choices"][0]["message"]["content"], i
+        assert resp["usage"] == solo[i]["data"]["response"]["usage"]
+    # the concurrent requests shared batched steps: far fewer kernel launches than the same 64 requests one by one
+    assert launches < 0.7 * launches_one_by_one, (launches, launches_one_by_one)
     m.close()
 
 

@@ -18,7 +18,7 @@ import bench  # noqa: E402  (model_path)
 import nats_llm_studio_b200 as b200  # noqa: E402
 
 
-def measure(eng, m, n_req=64, gen=128, prompt_min=64, prompt_max=512, step_iters=20, seed=7):
+def measure(eng, m, n_req=64, gen=128, prompt_min=64, prompt_max=512, step_iters=20, seed=7, peak=None, step_ctx=512):
     """n_req concurrent requests through b200_submit / b200_poll (continuous batching) + the bare batched-step time."""
     rng = np.random.default_rng(seed)
     lens = rng.integers(prompt_min, prompt_max + 1, n_req)
@@ -31,14 +31,16 @@ def measure(eng, m, n_req=64, gen=128, prompt_min=64, prompt_max=512, step_iters
             if e.kind == b200.EV_ERROR:
                 raise SystemExit(f"warm-up request failed: {e.finish_reason}")
             done |= e.kind == b200.EV_FINISH
-    slots = np.arange(n_req, dtype=np.int32); pos = np.full(n_req, 300, np.int32); cur = rng.integers(0, m.n_vocab, n_req).astype(np.int32)
-    for _ in range(3):
-        m.batch_step(cur, slots, pos)
-    l0 = int(b200.lib().b200_launch_count()); t0 = time.perf_counter()
-    for _ in range(step_iters):
-        m.batch_step(cur, slots, pos)
-    step_ms = (time.perf_counter() - t0) * 1e3 / step_iters
-    launches_per_step = (int(b200.lib().b200_launch_count()) - l0) // step_iters
+    # the bare step, device-timed: CUDA events on the engine stream around step_iters graph replays, nothing crossing PCIe
+    l0 = int(b200.lib().b200_launch_count())
+    step_ms, step_bytes = m.bench_batch_step(n_req, step_ctx, step_iters, 3)
+    launches_per_step = (int(b200.lib().b200_launch_count()) - l0) // (step_iters + 3)
+    roofline = None
+    if peak:
+        ach = step_bytes / (step_ms * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None,
+                    "algorithmic_bytes_per_step": step_bytes, "kernel": "batched decode step (qgemm_kernel + row kernels, one CUDA graph)",
+                    "timing": f"CUDA events around {step_iters} steps on the engine stream"}
 
     t0 = time.perf_counter()
     for i, p in enumerate(prompts):
@@ -61,7 +63,8 @@ def measure(eng, m, n_req=64, gen=128, prompt_min=64, prompt_max=512, step_iters
     return {"requests": n_req, "prompt_len": f"U[{prompt_min},{prompt_max}]", "generated_each": gen,
             "aggregate_tok_s": round(n_tok / wall, 1), "wall_s": round(wall, 3), "generated": n_tok, "prompt_tokens": int(lens.sum()),
             "ttft_ms_p50": round(float(np.percentile(ttft, 50)), 1), "ttft_ms_p90": round(float(np.percentile(ttft, 90)), 1), "ttft_ms_max": round(float(ttft.max()), 1),
-            "batch_step_ms": round(step_ms, 3), "batch_step_tok_s": round(n_req / step_ms * 1e3, 1), "batch_step_ctx": 300, "launches_per_step": launches_per_step}
+            "batch_step_ms": round(step_ms, 3), "batch_step_tok_s": round(n_req / step_ms * 1e3, 1), "batch_step_ctx": step_ctx, "launches_per_step": launches_per_step,
+            "roofline": roofline}
 
 
 def main():
