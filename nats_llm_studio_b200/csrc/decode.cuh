@@ -137,6 +137,7 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
 #pragma unroll
         for (int i = 0; i < VEC; i++) { qv[i] = t[i] * P.kq_scale; acc[i] = 0.f; }
     }
+    if (warp == 0 && lane == 0) sm.ctrl[0] = 0x7fffffff;             // q has arrived: the producer may run ahead again
     if (tr && warp == 0 && lane == 0) tr[1] = gtime();
     float m = -INFINITY, l = 0.f;
     for (int pb = p0 + warp; pb < p1; pb += CONSUMER_WARPS * NB) {
@@ -275,83 +276,64 @@ __device__ __forceinline__ void epilogue(const DecodeParams& P, const OpDesc& op
         case EPI_ROPE_K: {
             rope_pair(P, sm, row % HD, a0, a1);
             const __half2 hv = __floats2half2_rn(a0, a1);
-            *(__half2*)(P.kv.at(op.layer, 0, row / HD, pos) + row % HD) = hv;
+            *(__half2*)(P.kv.at_page(sm.btab[pos >> 4], op.layer, 0, row / HD, pos) + row % HD) = hv;       // block table from shared memory: no dependent global load
             st_relaxed_v2(P.kv_ll + row, (t16 << 16) | __half_as_ushort(__low2half(hv)), (t16 << 16) | __half_as_ushort(__high2half(hv)));
         } break;
         case EPI_V: {
             const __half2 hv = __floats2half2_rn(a0, a1);
-            *(__half2*)(P.kv.at(op.layer, 1, row / HD, pos) + row % HD) = hv;
+            *(__half2*)(P.kv.at_page(sm.btab[pos >> 4], op.layer, 1, row / HD, pos) + row % HD) = hv;
             st_relaxed_v2(P.kv_ll + P.n_head_kv * HD + row, (t16 << 16) | __half_as_ushort(__low2half(hv)), (t16 << 16) | __half_as_ushort(__high2half(hv)));
         } break;
     }
 }
 
 // ------------------------------------------------------------------------------------ streaming one op's slice (consumers)
-// Pairs [a, b) of `op`, eight pairs per stage (one per warp), one stage per 2048-element group.
+// Pairs [a, b) of `op`, eight pairs per stage (one per warp of a group).  A warp visits only the stages of its group's
+// row blocks: their sequence numbers follow from the slice's stage order (seg_stage_index), the ring offset of a stage
+// is published by the producer next to its barrier.  seq0: sequence number of the slice's first stage.
 template <int TYPE>
-__device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& op, const Smem& sm, const Smem& sx, RingCursor& cur, int a, int b,
-                                          int pos, int warp, int lane, uint32_t seq, ArgBest& best, float* logits_dst, long long* tr) {
+__device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& op, const Smem& sm, const Smem& sx, uint32_t seq0, int a, int b,
+                                          int pos, int warp, int lane, uint32_t seq, float in_scale, ArgBest& best, float* logits_dst, long long* tr) {
     constexpr int GB = TYPE == T_Q4_K ? 1152 : TYPE == T_Q5_K ? 1408 : TYPE == T_Q6_K ? 1680 : 2176;
     constexpr uint32_t PU = 2u * GB;
     constexpr int SG = stage_groups(TYPE);
-#ifdef B200_TRACE_WAIT
-    long long acc_wait = 0, acc_comp = 0, acc_n = 0;
-#endif
-    const int n_grp = op.n_grp;
+    const int n_grp = op.n_grp, spr = (n_grp + SG - 1) / SG;
     const int wg = warp / GROUP_WARPS, wl = warp % GROUP_WARPS;
-    int rbi = 0;
-    for (int rb = a; rb < b; rb += PAIRS_PER_STAGE, rbi++) {
-        const int np = min(PAIRS_PER_STAGE, b - rb);
-        const bool my_block = (rbi % WARP_GROUPS) == wg;       // row blocks alternate between the warp groups
-        const bool mine = my_block && wl < np;
+    const int n_rb = (b - a + PAIRS_PER_STAGE - 1) / PAIRS_PER_STAGE;
+    for (int rbi = wg; rbi < n_rb; rbi += WARP_GROUPS) {
+        const int rb = a + rbi * PAIRS_PER_STAGE, np = min(PAIRS_PER_STAGE, b - rb);
+        const bool mine = wl < np;
+        const int pp = rbi >> 1, nb = min(2, n_rb - 2 * pp);
+        uint32_t sq = seq0 + pp * 2 * spr + (rbi & 1);                    // seg_stage_index(rbi, 0, ...), then += nb per stage
         float acc0 = 0.f, acc1 = 0.f;
-        for (int g0 = 0; g0 < n_grp; g0 += SG) {
-            const int ng = min(SG, n_grp - g0); const uint32_t cb = ng * PU;
-            uint32_t gap; const uint32_t soff = cur.place(np * cb, sm.ring_bytes, gap);   // every warp tracks every stage
-            if (my_block) {
-                const uint32_t slot = cur.seq % NSLOT;
-#ifdef B200_TRACE_WAIT
-                long long tw0 = 0; if (tr && warp == 0 && lane == 0) tw0 = clock64();
-#endif
-                mbar_wait(&sm.full[slot], (cur.seq / NSLOT) & 1);
-#ifdef B200_TRACE_WAIT
-                if (tr && warp == 0 && lane == 0) { acc_wait += clock64() - tw0; }
-#endif
-                if (tr && warp == 0 && lane == 0 && rb == a && g0 == 0) tr[4] = gtime();
-#ifdef B200_TRACE_WAIT
-                long long cc0 = 0; if (tr && warp == 0 && lane == 0) cc0 = clock64();
-#endif
-                if (mine) {
-                    const uint8_t* unit = sm.ring + soff + wl * cb;
+        for (int gi = 0; gi < spr; gi++, sq += nb) {
+            const int g0 = gi * SG, ng = min(SG, n_grp - g0); const uint32_t cb = ng * PU;
+            const uint32_t slot = sq % NSLOT;
+            mbar_wait(&sm.full[slot], (sq / NSLOT) & 1);
+            if (tr && warp == 0 && lane == 0 && rbi == 0 && gi == 0) tr[4] = gtime();
+            if (mine) {
+                const uint8_t* unit = sm.ring + sm.q_off[slot] + wl * cb;
 #pragma unroll
-                    for (int gg = 0; gg < SG; gg++) if (gg < ng) {
-                        XRegs x; load_x(sx, g0 + gg, lane, x);
-                        acc0 += lane_dot<TYPE>(unit + gg * PU, lane, x);
-                        acc1 += lane_dot<TYPE>(unit + gg * PU + GB, lane, x);
-                    }
+                for (int gg = 0; gg < SG; gg++) if (gg < ng) {
+                    XRegs x; load_x(sx, g0 + gg, lane, x);
+                    acc0 += lane_dot<TYPE>(unit + gg * PU, lane, x);
+                    acc1 += lane_dot<TYPE>(unit + gg * PU + GB, lane, x);
                 }
-#ifdef B200_TRACE_WAIT
-                if (tr && warp == 0 && lane == 0) { acc_comp += clock64() - cc0; acc_n += 1; }     // compute cycles, stages
-#endif
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&sm.empty[slot]);
             }
-            cur.seq++;
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.empty[slot]);
         }
         if (tr && warp == 0 && lane == 0) tr[5] = gtime();
         if (mine) {
             acc0 = warp_sum(acc0); acc1 = warp_sum(acc1);
-            if (lane == 0) epilogue(P, op, sm, rb + wl, rb + wl - a, acc0, acc1, pos, seq, best, logits_dst);
+            if (lane == 0) epilogue(P, op, sm, rb + wl, rb + wl - a, acc0 * in_scale, acc1 * in_scale, pos, seq, best, logits_dst);
         }
     }
-#ifdef B200_TRACE_WAIT
-    if (tr && warp == 0 && lane == 0) { tr[7] += acc_wait; tr[1] += acc_comp; tr[2] += acc_n; }
-#endif
 }
 
 // ------------------------------------------------------------------------------------ one GEMV phase (consumers)
 // seq: this phase's generation number; inputs carry seq-1's tags.
-__device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem& sm, RingCursor& cur, int c, int G,
+__device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem& sm, uint32_t& stage_seq, int c, int G,
                               int pos, int tid, uint32_t seq, ArgBest& best, float* logits_dst, long long* tr) {
     const int warp = tid >> 5, lane = tid & 31;
     // ---- activation prologue: build the int8 vector(s) in shared memory
@@ -381,9 +363,12 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
         if (fam_std) store_run(sm, T_Q4_K, u, v, amax);
         if (fam_q6) store_run(s2, T_Q6_K, u, v, amax);
     };
+    float in_scale = 1.f;                           // factor applied to this phase's dot products in the epilogue
     if (ph.pro == PRO_NORM) {
-        // two passes (sum of squares, then scale).  The thread's first run stays in registers between them and its
-        // norm weights are requested BEFORE the poll (they do not depend on the exchange); wider inputs re-poll.
+        // RMSNorm in one pass: a run is multiplied by its norm weights and quantised as soon as it has arrived (int8
+        // block quantisation does not depend on a common positive factor); the 1/rms factor is reduced behind the
+        // quantisation and applied to the dot products in the epilogue (in_scale).  The norm weights are requested
+        // BEFORE the poll (they do not depend on the exchange).
         float v[16], w[16]; float ss = 0.f;
         const bool have = tid < n_runs;
         if (have) {
@@ -392,26 +377,16 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
             for (int i = 0; i < 4; i++) { float4 t = __ldg(wv + i); w[4 * i] = t.x; w[4 * i + 1] = t.y; w[4 * i + 2] = t.z; w[4 * i + 3] = t.w; }
             fetch(tid, v);
 #pragma unroll
-            for (int i = 0; i < 16; i++) ss += v[i] * v[i];
+            for (int i = 0; i < 16; i++) { ss += v[i] * v[i]; v[i] *= w[i]; }
         }
-        for (int u = tid + CONSUMER_THREADS; u < n_runs; u += CONSUMER_THREADS) {
-            float t[16]; fetch(u, t);
-#pragma unroll
-            for (int i = 0; i < 16; i++) ss += t[i] * t[i];
-        }
-        if (tr && tid == 0) tr[1] = gtime();
-        ss = warp_sum(ss);
+        if (tid == 0) sm.ctrl[0] = 0x7fffffff;                       // inputs have arrived: the producer may run ahead again
+        if (tr && tid == 0) tr[1] = tr[2] = gtime();
         consumer_sync();                                    // red[] and xq free (previous phase's readers done)
-        if (lane == 0) sm.red[warp] = ss;
-        consumer_sync();
-        float tot = 0.f;
-#pragma unroll
-        for (int i = 0; i < CONSUMER_WARPS; i++) tot += sm.red[i];
-        const float rs = rsqrtf(tot / (float)ph.K + P.rms_eps);
-        if (tr && tid == 0) tr[2] = gtime();
         if (tid < n_runs_pad) {
+            if (!have) {
 #pragma unroll
-            for (int i = 0; i < 16; i++) v[i] = have ? v[i] * rs * w[i] : 0.f;
+                for (int i = 0; i < 16; i++) v[i] = 0.f;
+            }
             quantise_store(tid, v);
         }
         for (int u = tid + CONSUMER_THREADS; u < n_runs_pad; u += CONSUMER_THREADS) {
@@ -420,19 +395,26 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
                 fetch(u, t);
                 const float4* wv = (const float4*)(ph.norm_w + 16 * u);
 #pragma unroll
-                for (int i = 0; i < 4; i++) { float4 q4 = __ldg(wv + i); t[4 * i] *= rs * q4.x; t[4 * i + 1] *= rs * q4.y; t[4 * i + 2] *= rs * q4.z; t[4 * i + 3] *= rs * q4.w; }
+                for (int i = 0; i < 4; i++) {
+                    float4 q4 = __ldg(wv + i);
+                    ss += t[4 * i] * t[4 * i] + t[4 * i + 1] * t[4 * i + 1] + t[4 * i + 2] * t[4 * i + 2] + t[4 * i + 3] * t[4 * i + 3];
+                    t[4 * i] *= q4.x; t[4 * i + 1] *= q4.y; t[4 * i + 2] *= q4.z; t[4 * i + 3] *= q4.w;
+                }
             } else {
 #pragma unroll
                 for (int i = 0; i < 16; i++) t[i] = 0.f;
             }
             quantise_store(u, t);
         }
+        ss = warp_sum(ss);
+        if (lane == 0) sm.red[warp] = ss;
     } else {
         // single pass; a thread's first two runs are polled together (both loads in flight) before the barrier, so the
         // exchange wait overlaps the other warps' tails
         float t[16], t2[16]; const int u2 = tid + CONSUMER_THREADS;
         const bool first = tid < n_runs, second = u2 < n_runs;
         if (second) fetch2(tid, u2, t, t2); else if (first) fetch(tid, t);
+        if (tid == 0) sm.ctrl[0] = 0x7fffffff;
         if (tr && tid == 0) tr[1] = tr[2] = gtime();
         consumer_sync();                                    // xq free (previous phase's readers done)
         if (tid < n_runs_pad) {
@@ -459,6 +441,12 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
         }
     }
     consumer_sync();
+    if (ph.pro == PRO_NORM) {
+        float tot = 0.f;
+#pragma unroll
+        for (int i = 0; i < CONSUMER_WARPS; i++) tot += sm.red[i];
+        in_scale = rsqrtf(tot / (float)ph.K + P.rms_eps);
+    }
     if (tr && tid == 0) tr[3] = gtime();
 #ifdef B200_TRACE_WAIT
     if (tr && tid == 0) { tr[1] = 0; tr[2] = 0; }
@@ -473,11 +461,12 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
         if (a >= b) continue;
         const Smem& sx = (op.type == T_Q6_K) ? s2 : sm;
         switch (op.type) {
-            case T_Q4_K: stream_op<T_Q4_K>(P, op, sm, sx, cur, a, b, pos, warp, lane, seq, best, logits_dst, tr); break;
-            case T_Q6_K: stream_op<T_Q6_K>(P, op, sm, sx, cur, a, b, pos, warp, lane, seq, best, logits_dst, tr); break;
-            case T_Q8_0: stream_op<T_Q8_0>(P, op, sm, sx, cur, a, b, pos, warp, lane, seq, best, logits_dst, tr); break;
-            default: stream_op<T_Q5_K>(P, op, sm, sx, cur, a, b, pos, warp, lane, seq, best, logits_dst, tr); break;
+            case T_Q4_K: stream_op<T_Q4_K>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); break;
+            case T_Q6_K: stream_op<T_Q6_K>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); break;
+            case T_Q8_0: stream_op<T_Q8_0>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); break;
+            default: stream_op<T_Q5_K>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); break;
         }
+        stage_seq += (uint32_t)(((b - a + PAIRS_PER_STAGE - 1) / PAIRS_PER_STAGE) * stages_per_rb(op.type, op.n_grp));
     }
 }
 
@@ -490,11 +479,13 @@ struct DecodeRun {
 __global__ void __launch_bounds__(CTA_THREADS, 1)
 decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes, const int max_grp) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    const Smem sm = carve_smem(smem_raw, ring_bytes, max_grp, P.hown_cap);
+    Smem sm_ = carve_smem(smem_raw, ring_bytes, max_grp, P.hown_cap); carve_tail(sm_, P.n_phases);
+    const Smem sm = sm_;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, c = blockIdx.x, G = gridDim.x;
     if (tid == 0) {
         for (int i = 0; i < NSLOT; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], GROUP_WARPS); }
         fence_barrier_init();
+        sm.ctrl[0] = 0x7fffffff;
     }
     for (int i = tid; i < P.n_btab; i += CTA_THREADS) sm.btab[i] = P.kv.block_table[i];
     {   // schedule -> shared memory
@@ -505,15 +496,8 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
 
     if (warp == CONSUMER_WARPS) {           // ===== producer warp =====
         Producer pr; pr.init(P.max_inflight);
-        for (int step = 0; step < P.n_steps; step++) {
-            const bool need_lm = (step + 1 >= R.n_forced) || R.logits_all;
-            for (int i = 0; i < P.n_phases; i++) {
-                const Phase& ph = sm.phases[i];
-                if (ph.kind != PH_GEMV) continue;
-                if (ph.op[0].epi == EPI_LOGITS && !need_lm) continue;
-                pr.run_phase(ph, sm, c, G, lane);
-            }
-        }
+        const int n_seg = pr.build_segs(sm, P.n_phases, c, G, lane);
+        pr.run(sm, P, n_seg, R.n_forced, R.logits_all != nullptr, lane);
         pr.drain(sm);
         return;
     }
@@ -522,7 +506,7 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
     uint32_t seq = *(volatile unsigned*)P.epoch;          // generation counter: one per executed phase
     const int pos0 = *(volatile int*)P.pos;
     int token = R.n_forced > 0 ? R.forced[0] : *(volatile int*)P.token;
-    RingCursor cur; cur.init();
+    uint32_t stage_seq = 0;                                 // stages of this CTA consumed so far (the producer's cur.seq, on the consumer side)
     int hlo, hhi; cta_slice(P.n_embd / 2, c, G, hlo, hhi);  // hidden-state row pairs this CTA owns (== its wo/down slices)
     for (int step = 0; step < P.n_steps; step++) {
         const int pos = pos0 + step;
@@ -536,6 +520,9 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
             long long* tr = nullptr;
             if (P.trace) tr = P.trace + (((size_t)step * P.n_phases + i) * G + c) * 8;
             if (tr && tid == 0) { const long long t0 = gtime(); for (int k = 0; k < 7; k++) tr[k] = t0; tr[7] = 0; }
+            // this thread is about to poll an exchange: until its inputs have arrived the producer issues nothing beyond
+            // the phases the CTA has already entered (slower warps may still be consuming those)
+            if (tid == 0 && ph.kind != PH_EMBED) sm.ctrl[0] = step * P.n_phases + i - 1;
 #ifdef B200_TRACE_WAIT
             const long long cphase0 = clock64();
 #endif
@@ -557,8 +544,9 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
                     if (P.head_dim == 128) attn_item<4>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane, tr);
                     else attn_item<2>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane, tr);
                 }
+                if (tid == 0) sm.ctrl[0] = 0x7fffffff;                 // CTAs without an attention item polled nothing
             } else {
-                consume_phase(P, ph, sm, cur, c, G, pos, tid, seq, best, logits_dst, tr);
+                consume_phase(P, ph, sm, stage_seq, c, G, pos, tid, seq, best, logits_dst, tr);
                 if (ph.op[0].epi == EPI_LOGITS) {          // publish this CTA's argmax candidate
                     consumer_sync();
                     if (lane == 0) { sm.red[2 * warp] = best.v; sm.red[2 * warp + 1] = __int_as_float(best.i); }

@@ -435,6 +435,8 @@ int Model::run_steps(int n_steps, const int32_t* forced, int n_forced, bool rese
     P.n_splits = std::max(1, std::min({16, std::max(1, grid / n_head), (cur_pos + n_steps + 15) / 16}));
     if (const char* e = getenv("B200_SPLITS")) P.n_splits = std::max(1, std::min({16, atoi(e), std::max(1, grid / n_head)}));
     P.max_inflight = 4; if (const char* e = getenv("B200_INFLIGHT")) P.max_inflight = std::max(1, atoi(e));
+    P.quiet = 1; if (const char* e = getenv("B200_QUIET")) P.quiet = atoi(e);
+    P.l2_ahead = 0; if (const char* e = getenv("B200_L2_AHEAD_KB")) P.l2_ahead = (uint32_t)std::max(0, atoi(e)) * 1024u;
     DecodeRun R{}; R.forced = d_forced; R.n_forced = n_forced; R.logits_all = logits_all_dev;
     LaunchCfg lc; lc.grid = grid; lc.ring_bytes = ring_bytes; lc.max_grp = smem_max_grp; lc.smem = smem_bytes;
     if (int rc = launch_decode(E, P, R, lc)) return rc;
@@ -1172,6 +1174,7 @@ int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, flo
         DecodeParams P{}; P.phases = d_ph; P.n_phases = 1; P.n_embd = K; P.n_head = 1; P.n_head_kv = 1; P.head_dim = 128; P.n_vocab = (int)N; P.n_splits = 1;
         P.cand_ll = d_cv; P.hown_cap = 4; P.pos = d_st; P.token = d_st + 1; P.bar_ctr = (unsigned*)(d_st + 2); P.epoch = (unsigned*)(d_st + 3); P.out_tokens = d_ot;
         P.logits = d_y; P.n_steps = 1; P.max_inflight = 4; if (const char* e = getenv("B200_INFLIGHT")) P.max_inflight = std::max(1, atoi(e));
+        if (const char* e = getenv("B200_L2_AHEAD_KB")) P.l2_ahead = (uint32_t)std::max(0, atoi(e)) * 1024u;
         // every step "forced" (token 0): no argmax traffic; forced[] = d_ot, zeroed, iters+1 ints
         cudaMemsetAsync(d_ot, 0, ((size_t)iters + 1) * 4, E.stream);
         DecodeRun R{}; R.forced = d_ot; R.n_forced = iters + 1;

@@ -77,12 +77,6 @@ __device__ __forceinline__ int dp4a_ss(int a, int b, int c) { return __dp4a(a, b
 __device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {   // unsigned bytes x signed bytes
     int d; asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d;
 }
-__device__ __forceinline__ uint32_t ld_acquire_u32(const unsigned* p) {
-    uint32_t v; asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v;
-}
-__device__ __forceinline__ void red_release_add(unsigned* p, unsigned v) {
-    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -146,6 +140,8 @@ struct DecodeParams {
     // run state (device memory)
     int* pos; int* token; int* out_tokens; unsigned* bar_ctr; unsigned* epoch;
     int n_steps; int want_argmax; int max_inflight;
+    int quiet;                  // 1: the producer holds back copies of later phases while the CTA polls an exchange (see Smem::ctrl)
+    uint32_t l2_ahead;          // bytes per CTA the producer may prefetch into L2 beyond what the ring holds (0 = off)
     long long* trace;           // optional [n_steps][n_phases][grid][4]: clock64 at phase start / prologue end / phase end, smid (debug)
 };
 
@@ -156,23 +152,38 @@ struct Smem {
     uint64_t* full; uint64_t* empty;
     float* red;                               // 64 floats of reduction scratch
     uint32_t* q_end;                          // producer's in-flight stage sizes [NSLOT]
+    uint32_t* q_off;                          // ring offset of the stage in each barrier slot [NSLOT] (written by the producer before it arms the slot)
     float* hown;                              // fp32 hidden-state rows this CTA owns (residual stream never leaves the SM)
     float2* rope;                             // (cos, sin) of this token's RoPE angles [128]
     int* btab;                                // the sequence's KV block table (page ids)
     Phase* phases;                            // the schedule, copied from global once per launch (descriptor reads are on
                                               // every phase's critical path; an L2 round trip each would cost microseconds)
+    struct Seg* segs;                         // this CTA's slices of the token's streamed matrices, in schedule order (producer)
+    volatile int* ctrl;                       // [0] quiet_id: phase id (step * n_phases + phase) up to which copies may be issued
+                                              //     while the consumers poll an exchange; INT_MAX = no restriction
 };
+
+// One streamed slice: pairs [0, n_pairs) starting at src, n_grp groups per row, of phase `phase` of the token.
+struct Seg { const uint8_t* src; int n_pairs; short n_grp; unsigned char type, is_lm; short phase; short pad; int pad2; };
+static_assert(sizeof(Seg) == 24 || sizeof(Seg) == 32, "Seg layout");
+constexpr int MAX_SEGS_PER_PHASE = 3;
 __host__ __device__ inline size_t smem_x_bytes(int max_grp) { return (size_t)max_grp * (2048 + 256 + 32); }
 constexpr int BTAB_MAX = 1024;           // KV pages per sequence cached in shared memory (16384 positions)
-__host__ __device__ inline size_t smem_misc_bytes(int hown_cap, int n_phases) { return NSLOT * 16 + 64 * 4 + NSLOT * 4 + 128 * 8 + ((size_t)hown_cap * 4 + 15) / 16 * 16 + BTAB_MAX * 4 + (size_t)n_phases * sizeof(Phase) + 64; }
+__host__ __device__ inline size_t smem_misc_bytes(int hown_cap, int n_phases) { return NSLOT * 16 + 64 * 4 + NSLOT * 8 + 128 * 8 + ((size_t)hown_cap * 4 + 15) / 16 * 16 + BTAB_MAX * 4 + (size_t)n_phases * sizeof(Phase) + (size_t)n_phases * MAX_SEGS_PER_PHASE * sizeof(Seg) + 64 + 64; }
 __device__ inline Smem carve_smem(uint8_t* base, uint32_t ring_bytes, int max_grp, int hown_cap) {   // hown_cap: multiple of 4
     Smem s; s.ring = base; s.ring_bytes = ring_bytes; uint8_t* p = base + ring_bytes;
     s.xq = (int8_t*)p; p += (size_t)max_grp * 2048;
     s.xbs = (int16_t*)p; p += (size_t)max_grp * 256;
     s.xd = (float*)p; p += (size_t)max_grp * 32;
     s.full = (uint64_t*)p; p += NSLOT * 8; s.empty = (uint64_t*)p; p += NSLOT * 8;
-    s.red = (float*)p; p += 64 * 4; s.q_end = (uint32_t*)p; p += NSLOT * 4; s.rope = (float2*)p; p += 128 * 8; s.hown = (float*)p; p += ((size_t)hown_cap * 4 + 15) / 16 * 16; s.btab = (int*)p; p += BTAB_MAX * 4; s.phases = (Phase*)p;
-    return s;
+    s.red = (float*)p; p += 64 * 4; s.q_end = (uint32_t*)p; p += NSLOT * 4; s.q_off = (uint32_t*)p; p += NSLOT * 4; s.rope = (float2*)p; p += 128 * 8; s.hown = (float*)p; p += ((size_t)hown_cap * 4 + 15) / 16 * 16; s.btab = (int*)p; p += BTAB_MAX * 4; s.phases = (Phase*)p;
+    return s;   // segs / ctrl are placed behind the schedule by carve_tail (they need n_phases)
+}
+
+__device__ inline void carve_tail(Smem& s, int n_phases) {
+    uint8_t* p = (uint8_t*)(s.phases + n_phases); p = (uint8_t*)(((uintptr_t)p + 15) & ~(uintptr_t)15);
+    s.segs = (Seg*)p; p += (size_t)n_phases * MAX_SEGS_PER_PHASE * sizeof(Seg);
+    s.ctrl = (volatile int*)p;
 }
 
 // Deterministic ring allocator state; producer and consumers evolve identical copies.
@@ -194,43 +205,128 @@ __device__ __forceinline__ void cta_slice(int total, int c, int G, int& lo, int&
 }
 
 // ------------------------------------------------------------------------------------ producer
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n.reg .pred p;\nmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+
+// Stage order inside one slice (n_rb row blocks of 8 pairs, spr stages per row block): row blocks are taken two at a
+// time — one for each consumer warp group — and their stages alternate, so that both groups always have a stage in the
+// ring (with all of block A's stages ahead of block B's, group B would sit idle until A is nearly done: the ring holds
+// about four stages).  With one stage per row block this is simply ascending row-block order.
+__host__ __device__ inline int stages_per_rb(int type, int n_grp) { const int sg = stage_groups(type); return (n_grp + sg - 1) / sg; }
+__host__ __device__ inline int seg_stage_index(int rbi, int gi, int n_rb, int spr) {       // position of (row block rbi, stage gi) in the slice's order
+    const int pp = rbi >> 1, nb = min(2, n_rb - 2 * pp);
+    return pp * 2 * spr + gi * nb + (rbi & 1);
+}
+static_assert(WARP_GROUPS == 2, "the stage order pairs row blocks for two consumer warp groups");
+
+// Position in the CTA's stage sequence: (token step, slice, row-block pair, stage, which block of the pair).  The ring cursor
+// and the L2-prefetch cursor are two of these walking the same list.
+struct SegIter {
+    int step, si, pp, gi, w; uint32_t n;              // n: stages passed so far
+    __device__ void init() { step = 0; si = 0; pp = 0; gi = 0; w = 0; n = 0; }
+    // current slice, skipping empty ones and lm_head slices of steps that do not need logits; false = past the last step
+    __device__ bool get(const Smem& sm, int n_seg, int n_steps, int n_forced, bool logits_all, Seg& s) {
+        for (;;) {
+            if (step >= n_steps) return false;
+            if (si >= n_seg) { step++; si = 0; pp = 0; gi = 0; w = 0; continue; }
+            s = sm.segs[si];
+            const bool need_lm = (step + 1 >= n_forced) || logits_all;
+            if (s.n_pairs == 0 || (s.is_lm && !need_lm)) { si++; pp = 0; gi = 0; w = 0; continue; }
+            return true;
+        }
+    }
+    __device__ void advance(const Seg& s) {
+        const int n_rb = (s.n_pairs + PAIRS_PER_STAGE - 1) / PAIRS_PER_STAGE, spr = stages_per_rb(s.type, s.n_grp);
+        n++;
+        if (++w >= min(2, n_rb - 2 * pp)) { w = 0; if (++gi >= spr) { gi = 0; if (2 * ++pp >= n_rb) { pp = 0; si++; } } }
+    }
+};
+struct StageDesc { const uint8_t* src; uint32_t cb; int np; };            // lane's source, bytes per pair, pairs in the stage
+__device__ __forceinline__ StageDesc stage_of(const Seg& s, const SegIter& it, int lane) {
+    StageDesc d; const uint32_t pu = 2u * group_bytes(s.type); const int sg = stage_groups(s.type);
+    const int rb = (2 * it.pp + it.w) * PAIRS_PER_STAGE, g0 = it.gi * sg;
+    d.np = min(PAIRS_PER_STAGE, s.n_pairs - rb);
+    d.cb = min(sg, s.n_grp - g0) * pu;
+    d.src = s.src + ((size_t)(rb + min(lane, d.np - 1)) * s.n_grp + g0) * pu;
+    return d;
+}
+
 struct Producer {
     RingCursor cur; uint32_t used, oldest;            // bytes held by unreleased stages (incl. gaps); oldest unreleased stage
     uint32_t landed, max_unlanded;                    // stages whose bytes have all arrived; cap on issued-but-unlanded stages
     __device__ void init(int inflight) { cur.init(); used = 0; oldest = 0; landed = 0; max_unlanded = (uint32_t)max(1, inflight); }
 
-    // called by the whole producer warp
-    __device__ void run_phase(const Phase& ph, const Smem& sm, int c, int G, int lane) {
-        int lo, hi; cta_slice(ph.total_pairs, c, G, lo, hi);
-        int off = 0;
-        for (int o = 0; o < ph.n_ops; o++) {
-            const OpDesc& op = ph.op[o];
-            int a = max(lo, off) - off, b = min(hi, off + op.n_pairs) - off; off += op.n_pairs;
-            if (a >= b) continue;
-            const uint32_t pu = 2u * group_bytes(op.type); const int sg = stage_groups(op.type);
-            for (int rb = a; rb < b; rb += PAIRS_PER_STAGE) {
-                const int np = min(PAIRS_PER_STAGE, b - rb);
-                const uint8_t* src = op.w + (size_t)(rb + min(lane, np - 1)) * op.n_grp * pu;
-                for (int g0 = 0; g0 < op.n_grp; g0 += sg) {
-                    const uint32_t cb = min(sg, op.n_grp - g0) * pu;        // bytes per pair in this stage (contiguous)
-                    const uint32_t bytes = np * cb, slot = cur.seq % NSLOT;
-                    // (0) keep the number of un-landed stages small: other L2 accesses of this SM queue behind its
-                    //     outstanding bulk bytes; landed-but-unconsumed stages may still pile up to the ring's capacity
-                    while (cur.seq - landed >= max_unlanded) { mbar_wait(&sm.full[landed % NSLOT], (landed / NSLOT) & 1); landed++; }
-                    // (1) barrier slot reuse: stage seq-NSLOT must be fully consumed
-                    while (cur.seq - oldest >= NSLOT) release_oldest(sm);
-                    // (2) ring space (the stage plus the gap it would leave at the wrap point)
-                    const uint32_t gp = (cur.off + bytes > sm.ring_bytes) ? sm.ring_bytes - cur.off : 0;
-                    while (used + gp + bytes > sm.ring_bytes) release_oldest(sm);
-                    uint32_t gap; const uint32_t soff = cur.place(bytes, sm.ring_bytes, gap);
-                    used += gap + bytes;
-                    __syncwarp();                 // every lane is done reading q_end[] of released stages
-                    if (lane == 0) { sm.q_end[slot] = gap + bytes; mbar_expect_tx(&sm.full[slot], bytes); }
-                    __syncwarp();
-                    if (lane < np) bulk_g2s(sm.ring + soff + lane * cb, src + (size_t)g0 * pu, cb, &sm.full[slot]);
-                    cur.seq++;
+    // The CTA's slices of one token, in schedule order (called once per launch by the whole producer warp).
+    __device__ int build_segs(const Smem& sm, int n_phases, int c, int G, int lane) {
+        int n = 0;
+        for (int i = 0; i < n_phases; i++) {
+            const Phase& ph = sm.phases[i];
+            if (ph.kind != PH_GEMV) continue;
+            int lo, hi; cta_slice(ph.total_pairs, c, G, lo, hi);
+            int off = 0;
+            for (int o = 0; o < ph.n_ops; o++) {
+                const OpDesc& op = ph.op[o];
+                const int a = max(lo, off) - off, b = min(hi, off + op.n_pairs) - off; off += op.n_pairs;
+                if (a >= b) continue;
+                if (lane == 0) {
+                    Seg sg; sg.src = op.w + (size_t)a * op.n_grp * 2u * group_bytes(op.type); sg.n_pairs = b - a; sg.n_grp = (short)op.n_grp;
+                    sg.type = (unsigned char)op.type; sg.is_lm = op.epi == EPI_LOGITS; sg.phase = (short)i; sg.pad = 0; sg.pad2 = 0;
+                    sm.segs[n] = sg;
                 }
+                n++;
             }
+        }
+        __syncwarp();
+        return n;
+    }
+
+    // Whole producer warp.  Walks the stage sequence of all n_steps tokens; never waits on data dependencies, only on ring
+    // space — except that, while the consumers poll an exchange (ctrl[0] = id of the last phase they completed), copies of
+    // later phases are held back: the poll's replies would queue behind this SM's in-flight bulk data, and what is being
+    // fetched at that moment is never the next thing the consumers need.  While blocked on ring space the warp pulls the
+    // stages beyond the ring into L2 (cp.async.bulk.prefetch.L2), so that HBM keeps streaming through prologues and
+    // attention and the ring later refills at L2 speed.
+    __device__ void run(const Smem& sm, const DecodeParams& P, int n_seg, int n_forced, bool logits_all, int lane) {
+        SegIter it, pf; it.init(); pf.init();
+        uint32_t issued_b = 0, pf_b = 0;                           // cumulative bytes issued to the ring / prefetched (wrap-safe differences)
+        Seg s;
+        while (it.get(sm, n_seg, P.n_steps, n_forced, logits_all, s)) {
+            const StageDesc d = stage_of(s, it, lane);
+            const uint32_t bytes = d.np * d.cb, slot = cur.seq % NSLOT;
+            const int phase_id = it.step * P.n_phases + s.phase;
+            // (0) keep the number of un-landed stages small: other L2 accesses of this SM queue behind its outstanding bulk bytes
+            while (cur.seq - landed >= max_unlanded) { mbar_wait(&sm.full[landed % NSLOT], (landed / NSLOT) & 1); landed++; }
+            // (1) barrier slot reuse and (2) ring space (the stage plus the gap it would leave at the wrap point); (3) exchange quiet
+            const uint32_t gp = (cur.off + bytes > sm.ring_bytes) ? sm.ring_bytes - cur.off : 0;
+            for (;;) {
+                const bool quiet = P.quiet && phase_id > sm.ctrl[0];
+                const bool need_release = (cur.seq - oldest >= NSLOT) || (used + gp + bytes > sm.ring_bytes);
+                if (!quiet && !need_release) break;
+                if (need_release && mbar_test(&sm.empty[oldest % NSLOT], (oldest / NSLOT) & 1)) { used -= sm.q_end[oldest % NSLOT]; oldest++; continue; }
+                // blocked: use the time to prefetch into L2 (not while quiet — that traffic would delay the poll just the same)
+                if (!quiet && P.l2_ahead) {
+                    if ((int32_t)(pf.n - it.n) <= 0) { pf = it; pf.advance(s); pf_b = issued_b + bytes; }     // start just beyond the stage being issued
+                    Seg t;
+                    if (pf_b - (issued_b + bytes) < P.l2_ahead && pf.get(sm, n_seg, P.n_steps, n_forced, logits_all, t)) {
+                        const StageDesc e = stage_of(t, pf, lane);
+                        if (lane < e.np) bulk_prefetch_l2(e.src, e.cb);
+                        pf_b += e.np * e.cb; pf.advance(t);
+                        continue;
+                    }
+                }
+                __nanosleep(64);
+            }
+            uint32_t gap; const uint32_t soff = cur.place(bytes, sm.ring_bytes, gap);
+            used += gap + bytes;
+            __syncwarp();                 // every lane is done reading q_end[] of released stages
+            if (lane == 0) { sm.q_end[slot] = gap + bytes; sm.q_off[slot] = soff; mbar_expect_tx(&sm.full[slot], bytes); }
+            __syncwarp();
+            if (lane < d.np) bulk_g2s(sm.ring + soff + lane * d.cb, d.src, d.cb, &sm.full[slot]);
+            cur.seq++; issued_b += bytes;
+            it.advance(s);
         }
     }
     __device__ void release_oldest(const Smem& sm) {
@@ -268,47 +364,6 @@ __device__ __forceinline__ float half16_max(float a) {   // max over the aligned
 #pragma unroll
     for (int o = 8; o; o >>= 1) a = fmaxf(a, __shfl_xor_sync(0xffffffffu, a, o));
     return a;
-}
-
-constexpr int NORM_RUNS = 1;             // RMSNorm inputs up to 256*16 = 4096 wide stay in registers between the two passes (wider: re-polled)
-
-// Consumers only (tid 0..255).  `load(u, v)` fills v[16] with activations [16u, 16u+16) (already
-// normalised / combined); runs beyond K are zero padding.  type: weight type of the phase's ops.
-template <typename Load>
-__device__ __forceinline__ void prologue_quantise(const Smem& sm, int type, int K, int n_grp, int tid, Load load) {
-    const int n_runs = K / 16, n_runs_pad = n_grp * 128;
-    for (int u = tid; u < n_runs_pad; u += CONSUMER_THREADS) {
-        float v[16]; float amax = 0.f;
-        if (u < n_runs) {
-            load(u, v);
-#pragma unroll
-            for (int i = 0; i < 16; i++) amax = fmaxf(amax, fabsf(v[i]));
-        } else {
-#pragma unroll
-            for (int i = 0; i < 16; i++) v[i] = 0.f;
-        }
-        amax = half16_max(amax);
-        store_run(sm, type, u, v, amax);
-    }
-    consumer_sync();
-}
-
-// sum of squares of src[0..K) over the consumer threads -> rsqrt(mean + eps)
-__device__ __forceinline__ float rms_scale(const Smem& sm, const float* __restrict__ src, int K, float eps, int tid) {
-    float ss = 0.f;
-    for (int u = tid; u < K / 16; u += CONSUMER_THREADS) {
-        const float4* p = (const float4*)(src + 16 * u);
-#pragma unroll
-        for (int i = 0; i < 4; i++) { float4 t = __ldcg(p + i); ss += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w; }
-    }
-    ss = warp_sum(ss);
-    consumer_sync();                       // red[] free (previous readers done)
-    if ((tid & 31) == 0) sm.red[tid >> 5] = ss;
-    consumer_sync();
-    float tot = 0.f;
-#pragma unroll
-    for (int i = 0; i < CONSUMER_WARPS; i++) tot += sm.red[i];
-    return rsqrtf(tot / (float)K + eps);
 }
 
 __device__ __forceinline__ void load_run_f32(const float* __restrict__ src, int u, float v[16]) {

@@ -344,7 +344,7 @@ static void quantise_act_256(const float *x, int n, float *xq) {
 }
 
 /* y[N] = W[N x K] . x[K], W any supported type, dequantised per row, fp64 accumulate. */
-static void matvec(const orc_model *m, const orc_tensor *w, const float *x_in, float *y, int N, int K) {
+static void matvec_post(const orc_model *m, const orc_tensor *w, const float *x_in, float *y, int N, int K, float post) {
     float *xq = NULL; const float *x = x_in;
     if (m->act_quant && w->type != T_F32 && w->type != T_F16 && w->type != T_BF16) {
         xq = (float *)malloc((size_t)K * 4); quantise_act_256(x_in, K, xq); x = xq;
@@ -357,21 +357,29 @@ static void matvec(const orc_model *m, const orc_tensor *w, const float *x_in, f
         for (int n = 0; n < N; n++) {
             orc_dequantize(w->type, w->data + (size_t)n * rb, K, row);
             double acc = 0; for (int k = 0; k < K; k++) acc += (double)row[k] * (double)x[k];
-            y[n] = (float)acc;
+            y[n] = post == 1.0f ? (float)acc : (float)acc * post;
         }
         free(row);
     }
     free(xq);
 }
+static void matvec(const orc_model *m, const orc_tensor *w, const float *x_in, float *y, int N, int K) { matvec_post(m, w, x_in, y, N, K, 1.0f); }
 
 static uint16_t fp32_to_fp16(float f);
 static void round_f16(const float *x, float *y, int n) {
     for (int i = 0; i < n; i++) { float v = x[i]; if (v > 65504.f) v = 65504.f; if (v < -65504.f) v = -65504.f; y[i] = fp16_to_fp32(fp32_to_fp16(v)); }
 }
-static void rmsnorm(const float *x, const float *g, float *y, int n, float eps) {
+/* RMSNorm.  Returns the factor the caller still has to apply to the results of the mat-vecs that consume y: 1 in the
+ * plain mode.  In engine-numerics mode (act_quant) the engine quantises x*g block by block as the values arrive and
+ * multiplies the mat-vec results by rsqrt(mean(x^2)+eps) afterwards (int8 block quantisation is invariant under a
+ * common positive factor, so the codes are the ones x*sc*g would give up to fp32 rounding of the products); the
+ * oracle follows the same order of operations. */
+static float rmsnorm(const orc_model *m, const float *x, const float *g, float *y, int n, float eps) {
     double ss = 0; for (int i = 0; i < n; i++) ss += (double)x[i] * x[i];
     float sc = (float)(1.0 / sqrt(ss / n + (double)eps));
+    if (m->act_quant) { for (int i = 0; i < n; i++) y[i] = x[i] * g[i]; return sc; }
     for (int i = 0; i < n; i++) y[i] = x[i] * sc * g[i];
+    return 1.0f;
 }
 
 static const orc_tensor *layer_tensor(const orc_model *m, int l, const char *suffix) {
@@ -414,8 +422,9 @@ int orc_eval_token(orc_model *m, int32_t tok, float *logits) {
         if (!an || !wq || !wk || !wv || !wo || !fn || !wg || !wu || !wd) { rc = -1; break; }
         float *kc = m->kc + ((size_t)l * m->kv_cap + pos) * KVD, *vc = m->vc + ((size_t)l * m->kv_cap + pos) * KVD;
         orc_dequantize(an->type, an->data, D, nw);
-        if (m->xchg_f16) { round_f16(h, hx, D); rmsnorm(hx, nw, x, D, m->rms_eps); } else rmsnorm(h, nw, x, D, m->rms_eps);
-        matvec(m, wq, x, q, H * HD, D); matvec(m, wk, x, kc, KVD, D); matvec(m, wv, x, vc, KVD, D);
+        float ps;
+        if (m->xchg_f16) { round_f16(h, hx, D); ps = rmsnorm(m, hx, nw, x, D, m->rms_eps); } else ps = rmsnorm(m, h, nw, x, D, m->rms_eps);
+        matvec_post(m, wq, x, q, H * HD, D, ps); matvec_post(m, wk, x, kc, KVD, D, ps); matvec_post(m, wv, x, vc, KVD, D, ps);
         /* RoPE, adjacent-pair ("NORM") form: theta_i = pos * base^(-2i/n_rot) / freq_factor_i */
         for (int hh = 0; hh < H + HK; hh++) {
             float *v = hh < H ? q + (size_t)hh * HD : kc + (size_t)(hh - H) * HD;
@@ -445,8 +454,8 @@ int orc_eval_token(orc_model *m, int32_t tok, float *logits) {
         matvec(m, wo, att, o, D, H * HD);
         for (int i = 0; i < D; i++) h[i] += o[i] * res;
         orc_dequantize(fn->type, fn->data, D, nw);
-        if (m->xchg_f16) { round_f16(h, hx, D); rmsnorm(hx, nw, x, D, m->rms_eps); } else rmsnorm(h, nw, x, D, m->rms_eps);
-        matvec(m, wg, x, g, F, D); matvec(m, wu, x, u, F, D);
+        if (m->xchg_f16) { round_f16(h, hx, D); ps = rmsnorm(m, hx, nw, x, D, m->rms_eps); } else ps = rmsnorm(m, h, nw, x, D, m->rms_eps);
+        matvec_post(m, wg, x, g, F, D, ps); matvec_post(m, wu, x, u, F, D, ps);
         for (int i = 0; i < F; i++) g[i] = (float)((double)g[i] / (1.0 + exp(-(double)g[i]))) * u[i];
         if (m->xchg_f16) round_f16(g, g, F);
         matvec(m, wd, g, o, D, F);
@@ -458,8 +467,9 @@ int orc_eval_token(orc_model *m, int32_t tok, float *logits) {
         if (!ow) ow = te;   /* tied embeddings (granite) */
         if (!on) rc = -1; else {
             orc_dequantize(on->type, on->data, D, nw);
-            if (m->xchg_f16) { round_f16(h, hx, D); rmsnorm(hx, nw, x, D, m->rms_eps); } else rmsnorm(h, nw, x, D, m->rms_eps);
-            matvec(m, ow, x, logits, V, D);
+            float ps;
+            if (m->xchg_f16) { round_f16(h, hx, D); ps = rmsnorm(m, hx, nw, x, D, m->rms_eps); } else ps = rmsnorm(m, h, nw, x, D, m->rms_eps);
+            matvec_post(m, ow, x, logits, V, D, ps);
             if (m->logit_scale != 0.0f) { float inv = 1.0f / m->logit_scale; for (int i = 0; i < V; i++) logits[i] *= inv; }
         }
     }
