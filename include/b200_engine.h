@@ -142,11 +142,20 @@ int b200_model_batch_step_sampled(b200_model* m, const int32_t* toks, const int3
  * queue group (README.md:484).  One process per GPU; rank 0 creates a 128-byte NCCL id, the host side distributes it
  * (the Go worker would publish it on a NATS subject; tests and tools use torch.distributed), every rank then calls
  * b200_tp_init after b200_init and before opening a model.  A model opened afterwards keeps only this rank's shard
- * (attention heads, FFN columns, vocabulary rows) and is driven through b200_model_prefill_slot /
- * b200_model_batch_step with identical arguments on all ranks; the partial sums of the two row-parallel products of a
- * layer are all-reduced over NVLink (NCCL), the logits slices all-gathered. */
+ * (attention heads, FFN columns, vocabulary rows: b200_tp_shard_window).  Every rank must then make the same calls with
+ * the same arguments:
+ *   - b200_model_generate / b200_model_eval / b200_bench_decode (greedy): the persistent batch-1 kernel runs on every
+ *     rank; the partial sums of the two row-parallel products of a layer and the argmax candidates are exchanged INSIDE
+ *     the kernel as tagged words written straight into the peers' memory over NVLink (buffers shared through CUDA IPC);
+ *     b200_model_eval fills this rank's vocabulary columns of the logits array;
+ *   - b200_model_prefill_slot / b200_model_batch_step (batched rows): partial sums all-reduced with NCCL, logits slices
+ *     all-gathered. */
 int b200_tp_unique_id(void* out, size_t cap);
 int b200_tp_init(int rank, int world, const void* id, size_t n);
+/* Host arithmetic only (no GPU): the part of a GGUF tensor [N rows x K] that rank `rank` of `world` keeps.  kind is
+ * "attn_q" | "attn_k" | "attn_v" | "ffn_gate" | "ffn_up" | "output" (a row range, all of K) or "attn_output" | "ffn_down"
+ * (all rows, a K window aligned to 256-element blocks). */
+int b200_tp_shard_window(const char* kind, int64_t N, int K, int rank, int world, int64_t* row0, int64_t* nrows, int* col0, int* ncols);
 /* decode-step timing: n_steps greedy tokens from the current position of a primed context */
 int b200_bench_decode(b200_model* m, int ctx_len, int n_steps, int warmup, float* ms_per_token, double* bytes_per_token);
 /* batched-step timing (BASELINE.json metric "bs64"; config 4's bs1/bs32 on a tensor-parallel engine): n_seqs sequences at

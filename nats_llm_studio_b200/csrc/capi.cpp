@@ -317,6 +317,10 @@ int b200_model_prefill_slot(b200_model* m, int slot, const int32_t* toks, int n,
 int b200_bench_batch_step(b200_model* m, int n_seqs, int ctx, int iters, int warmup, float* ms, double* bytes) { if (!m) return fail(B200_ERR_INVALID, "null model"); return ((Model*)m)->bench_batch(n_seqs, ctx, iters, warmup, ms, bytes); }
 int b200_tp_unique_id(void* out, size_t cap) { if (!out) return fail(B200_ERR_INVALID, "null argument"); if (int rc = engine().ensure()) return rc; return engine().tp_unique_id(out, cap); }
 int b200_tp_init(int rank, int world, const void* id, size_t n) { return engine().tp_init(rank, world, id, n); }
+int b200_tp_shard_window(const char* kind, int64_t N, int K, int rank, int world, int64_t* row0, int64_t* nrows, int* col0, int* ncols) {
+    if (!row0 || !nrows || !col0 || !ncols) return fail(B200_ERR_INVALID, "null argument");
+    return tp_shard_window(kind, N, K, rank, world, row0, nrows, col0, ncols);
+}
 int b200_layout_selftest(void) { return layout_selftest(); }
 uint64_t b200_launch_count(void) { return engine().launches; }
 

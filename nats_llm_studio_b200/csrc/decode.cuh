@@ -240,6 +240,44 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
     }
 }
 
+// ------------------------------------------------------------------------------------ tensor-parallel exchange (K10)
+// All-reduce of a row pair's partial sums over the ranks, fused into the residual epilogue: every rank stores its two
+// fp32 partials as tagged words straight into every peer's receive buffer (NVLink peer stores), then polls its OWN
+// buffer for the peers' words and adds the tp_world partials in rank order — the same order on every rank, so the
+// residual stream stays bit-identical across GPUs.  No extra launch, no barrier: one store -> poll latency per
+// row-parallel product.  The buffer has two halves (wo | down): a half is rewritten one layer later, which a peer can
+// only reach after this rank has sent — hence already read — the current values.
+__device__ __forceinline__ void st_sys_v2(void* p, uint32_t a, uint32_t b) { asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(a), "r"(b) : "memory"); }
+__device__ __forceinline__ uint2 ld_sys_v2(const void* p) {
+    uint2 r; asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p) : "memory"); return r;
+}
+constexpr unsigned TP_SPIN_BUDGET = 1u << 26;            // polls before a peer is declared lost (~30 s: the ranks' hosts launch the same step at slightly different times)
+
+// whole warp; a0/a1 hold the same values in every lane on entry and on exit
+__device__ __forceinline__ void tp_allreduce_pair(const DecodeParams& P, int which, int row, uint32_t seq, int lane, float& a0, float& a1) {
+    const int W = P.tp_world, me = P.tp_rank, D = P.n_embd;
+    const int k = lane >> 1, comp = lane & 1;                         // lane -> (k-th other rank, component)
+    const int other = k + (k >= me ? 1 : 0);
+    float got = 0.f;
+    if (k < W - 1) {
+        st_sys_v2(P.rx_peer[other] + ((size_t)(which * W + me) * D + row + comp), __float_as_uint(comp ? a1 : a0), seq);
+        const uint2* src = P.rx_peer[me] + ((size_t)(which * W + other) * D + row + comp);
+        unsigned spins = *(volatile unsigned*)P.tp_error ? TP_SPIN_BUDGET : 0u;      // a peer was lost earlier in this launch: do not wait again
+        for (;;) {
+            const uint2 w = ld_sys_v2(src);
+            if (w.y == seq) { got = __uint_as_float(w.x); break; }
+            if (++spins > TP_SPIN_BUDGET) { *P.tp_error = 1u; break; }
+        }
+    }
+    float s0 = 0.f, s1 = 0.f;
+    for (int r = 0; r < W; r++) {                                     // rank order, identical everywhere
+        const int kk = r - (r > me ? 1 : 0);
+        const float p0 = __shfl_sync(0xffffffffu, got, 2 * kk), p1 = __shfl_sync(0xffffffffu, got, 2 * kk + 1);
+        s0 += r == me ? a0 : p0; s1 += r == me ? a1 : p1;
+    }
+    a0 = s0; a1 = s1;
+}
+
 // ------------------------------------------------------------------------------------ epilogues
 struct ArgBest { float v; int i; };
 
@@ -267,8 +305,8 @@ __device__ __forceinline__ void epilogue(const DecodeParams& P, const OpDesc& op
         case EPI_LOGITS: {
             a0 *= op.scale; a1 *= op.scale;
             logits_dst[row] = a0; if (row + 1 < op.n_rows) logits_dst[row + 1] = a1;
-            if (a0 > best.v) { best.v = a0; best.i = row; }
-            if (row + 1 < op.n_rows && a1 > best.v) { best.v = a1; best.i = row + 1; }
+            if (a0 > best.v) { best.v = a0; best.i = P.vocab_base + row; }
+            if (row + 1 < op.n_rows && a1 > best.v) { best.v = a1; best.i = P.vocab_base + row + 1; }
         } break;
         case EPI_ROPE_Q:
             rope_pair(P, sm, row % HD, a0, a1);
@@ -326,6 +364,7 @@ __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& o
         if (tr && warp == 0 && lane == 0) tr[5] = gtime();
         if (mine) {
             acc0 = warp_sum(acc0); acc1 = warp_sum(acc1);
+            if (P.tp_world > 1 && op.epi == EPI_RESID) tp_allreduce_pair(P, op.tp_half, 2 * (rb + wl), seq, lane, acc0, acc1);
             if (lane == 0) epilogue(P, op, sm, rb + wl, rb + wl - a, acc0 * in_scale, acc1 * in_scale, pos, seq, best, logits_dst);
         }
     }
@@ -511,7 +550,7 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
     for (int step = 0; step < P.n_steps; step++) {
         const int pos = pos0 + step;
         const bool need_lm = (step + 1 >= R.n_forced) || R.logits_all;
-        float* logits_dst = R.logits_all ? R.logits_all + (size_t)step * P.n_vocab : P.logits;
+        float* logits_dst = R.logits_all ? R.logits_all + (size_t)step * P.n_vocab_l : P.logits;
         ArgBest best; best.v = -INFINITY; best.i = 0x7fffffff;
         for (int i = 0; i < P.n_phases; i++) {
             const Phase& ph = sm.phases[i];
@@ -558,6 +597,10 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
                             if (vv > bv || (vv == bv && ix < bi)) { bv = vv; bi = ix; }
                         }
                         st_relaxed_v2(P.cand_ll + 2 * c, __float_as_uint(bv), seq); st_relaxed_v2(P.cand_ll + 2 * c + 1, (uint32_t)bi, seq);
+                        for (int r = 0; r < P.tp_world; r++) if (r != P.tp_rank) {      // vocabulary shards: every rank sees every rank's candidates
+                            uint2* dst = P.cand_peer[r] + (size_t)P.tp_rank * 2 * G + 2 * c;
+                            st_sys_v2(dst, __float_as_uint(bv), seq); st_sys_v2(dst + 1, (uint32_t)bi, seq);
+                        }
                     }
                 }
             }
@@ -575,6 +618,18 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
             for (int k = tid; k < G; k += CONSUMER_THREADS) {
                 float t[2]; ll32_poll<2>(P.cand_ll + 2 * k, seq, t);
                 const float vv = t[0]; const int ix = __float_as_int(t[1]);
+                if (vv > bv || (vv == bv && ix < bi)) { bv = vv; bi = ix; }
+            }
+            if (P.tp_world > 1) for (int k = tid; k < P.tp_world * G; k += CONSUMER_THREADS) {
+                if (k / G == P.tp_rank) continue;                       // own candidates were read above
+                const uint2* src = P.cand_peer[P.tp_rank] + 2 * (size_t)k;
+                uint2 w0, w1; unsigned spins = *(volatile unsigned*)P.tp_error ? TP_SPIN_BUDGET : 0u;
+                for (;;) {
+                    w0 = ld_sys_v2(src); w1 = ld_sys_v2(src + 1);
+                    if (w0.y == seq && w1.y == seq) break;
+                    if (++spins > TP_SPIN_BUDGET) { *P.tp_error = 1u; w0.x = __float_as_uint(-INFINITY); w1.x = 0x7fffffffu; break; }
+                }
+                const float vv = __uint_as_float(w0.x); const int ix = (int)w1.x;
                 if (vv > bv || (vv == bv && ix < bi)) { bv = vv; bi = ix; }
             }
 #pragma unroll

@@ -95,6 +95,25 @@ int Engine::all_gather(const float* src, float* dst, size_t n_per_rank) {
     return B200_OK;
 }
 
+// Which part of a GGUF tensor rank `rank` of `world` keeps.  Column-parallel tensors (attn_q/k/v by
+// heads, ffn_gate/up by FFN columns, output by vocabulary rows) keep a contiguous row range; row-parallel ones
+// (attn_output, ffn_down) keep every row and a K window, which must start and end on 256-element block boundaries.
+int tp_shard_window(const char* kind, int64_t N, int K, int rank, int world, int64_t* row0, int64_t* nrows, int* col0, int* ncols) {
+    if (!kind || world < 1 || rank < 0 || rank >= world) return fail(B200_ERR_INVALID, "bad tensor-parallel rank/world");
+    const std::string k = kind;
+    const bool by_rows = k == "attn_q" || k == "attn_k" || k == "attn_v" || k == "ffn_gate" || k == "ffn_up" || k == "output";
+    const bool by_cols = k == "attn_output" || k == "ffn_down";
+    if (!by_rows && !by_cols) return fail(B200_ERR_INVALID, "tensor kind '" + k + "' is not sharded (norms and token_embd are replicated)");
+    if (by_rows) {
+        if (N % world) return fail(B200_ERR_UNSUPPORTED, k + ": " + std::to_string(N) + " rows do not divide over " + std::to_string(world) + " ranks");
+        *nrows = N / world; *row0 = rank * *nrows; *col0 = 0; *ncols = K;
+    } else {
+        if (K % (256 * world)) return fail(B200_ERR_UNSUPPORTED, k + ": K " + std::to_string(K) + " does not divide over " + std::to_string(world) + " ranks in 256-element blocks");
+        *ncols = K / world; *col0 = rank * *ncols; *row0 = 0; *nrows = N;
+    }
+    return B200_OK;
+}
+
 // ------------------------------------------------------------------------------------ init
 int Engine::init(const b200_config* cfg) {
     std::lock_guard<std::mutex> lk(mu);
@@ -196,6 +215,8 @@ void Model::release() {
     if (engine().ready) { cudaSetDevice(engine().device); cudaStreamSynchronize(engine().stream); }
     for (auto& g : step_graph) if (g) { cudaGraphExecDestroy(g); g = nullptr; }
     step_graph.clear(); step_seen.clear(); step_launches.clear(); graph_failed = false;
+    for (int r = 0; r < 8; r++) { if (tp_peer[r] && tp_peer[r] != tp_buf) cudaIpcCloseMemHandle(tp_peer[r]); tp_peer[r] = nullptr; }
+    tp_buf = nullptr; tp_error = nullptr;
     for (void* p : owned) cudaFree(p);
     owned.clear();
     if (d_raw) { cudaFree(d_raw); d_raw = nullptr; }
@@ -314,10 +335,15 @@ int Model::commit() {
         Layer& L = layers[l]; std::string p = "blk." + std::to_string(l) + ".";
         int rc;
         if ((rc = load_vector(p + "attn_norm.weight", D, &L.attn_norm))) return rc;
-        if ((rc = load_slice(p + "attn_q.weight", gQD, D, (int64_t)tr * QD, QD, 0, D, L.wq))) return rc;          // column-parallel: by heads
-        if ((rc = load_slice(p + "attn_k.weight", gKVD, D, (int64_t)tr * KVD, KVD, 0, D, L.wk))) return rc;
-        if ((rc = load_slice(p + "attn_v.weight", gKVD, D, (int64_t)tr * KVD, KVD, 0, D, L.wv))) return rc;
-        if ((rc = load_slice(p + "attn_output.weight", D, gQD, 0, D, tr * QD, QD, L.wo))) return rc;              // row-parallel: K range
+        auto shard = [&](const char* kind, const std::string& name, int64_t N, int K, Matrix& out) -> int {
+            int64_t r0, nr; int c0, nc;
+            if (int rc2 = tp_shard_window(kind, N, K, tr, W, &r0, &nr, &c0, &nc)) return rc2;
+            return load_slice(name, N, K, r0, nr, c0, nc, out);
+        };
+        if ((rc = shard("attn_q", p + "attn_q.weight", gQD, D, L.wq))) return rc;          // column-parallel: by heads
+        if ((rc = shard("attn_k", p + "attn_k.weight", gKVD, D, L.wk))) return rc;
+        if ((rc = shard("attn_v", p + "attn_v.weight", gKVD, D, L.wv))) return rc;
+        if ((rc = shard("attn_output", p + "attn_output.weight", D, gQD, L.wo))) return rc;              // row-parallel: K range
         if ((rc = load_vector(p + "ffn_norm.weight", D, &L.ffn_norm))) return rc;
         const GgufTensor *tg = meta.tensor(p + "ffn_gate.weight"), *tu = meta.tensor(p + "ffn_up.weight");
         if (!tg || !tu) return fail(B200_ERR_INVALID, "GGUF: missing ffn_gate/ffn_up in layer " + std::to_string(l));
@@ -330,7 +356,7 @@ int Model::commit() {
         if ((rc = repack(E, d_raw + tg->offset + (size_t)tr * F * grb, L.wgu.w, tg->type, F, F, D, 0))) return rc;
         if ((rc = repack(E, d_raw + tu->offset + (size_t)tr * F * grb, L.wgu.w, tu->type, F, F, D, 1))) return rc;
         weight_bytes += 2 * (uint64_t)F * grb;
-        if ((rc = load_slice(p + "ffn_down.weight", D, gF, 0, D, tr * F, F, L.wd))) return rc;
+        if ((rc = shard("ffn_down", p + "ffn_down.weight", D, gF, L.wd))) return rc;
     }
     if (int rc = load_vector("output_norm.weight", D, &out_norm)) return rc;
     if (tp) { if (int rc = load_slice(meta.tensor("output.weight") ? "output.weight" : "token_embd.weight", gV, D, (int64_t)tr * n_vocab_l, n_vocab_l, 0, D, out_w)) return rc; }
@@ -360,9 +386,9 @@ int Model::commit() {
     if ((rc = own(&d_kv, page_elems * n_pages)) || (rc = own(&d_block_table, (size_t)n_pages))) return rc;
     std::vector<int> bt(n_pages); for (int i = 0; i < n_pages; i++) bt[i] = i;
     CK(cudaMemcpy(d_block_table, bt.data(), bt.size() * 4, cudaMemcpyHostToDevice));
-    // a tensor-parallel shard is served by the dense row path only (prefill_slot / batch_step, all ranks in lockstep):
-    // the persistent batch-1 kernel below has no exchange step between GPUs yet
-    if (tp) { committed = true; return B200_OK; }
+    // a tensor-parallel shard runs the same persistent batch-1 kernel on its slice of every matrix; the partial sums of
+    // the row-parallel products and the argmax candidates cross NVLink inside the kernel (tp_setup_exchange)
+    if (tp) { if (int rc2 = tp_setup_exchange()) return rc2; }
     int max_grp = std::max({n_groups(F), n_groups(QD), 2 * n_groups(D)});
     hown_cap = 2 * ((D / 2 + E.n_sm - 1) / E.n_sm + 2);                       // pairs per CTA slice (worst case: 1 CTA/SM) x 2 rows
     LaunchCfg lc; if (int rc2 = launch_cfg(E, max_grp, hown_cap, 5 * n_layer + 2, lc)) return rc2;
@@ -376,8 +402,8 @@ int Model::commit() {
 
     // ---- decode schedule
     std::vector<Phase> ph;
-    auto mk_op = [&](const Matrix& m, int epi, float* out, float scale, int layer) {
-        OpDesc o{}; o.w = m.w; o.type = m.type; o.n_pairs = (int)(m.N / 2); o.n_rows = (int)m.n_rows; o.n_grp = n_groups(m.K); o.epi = epi; o.out = out; o.scale = scale; o.layer = layer; return o;
+    auto mk_op = [&](const Matrix& m, int epi, float* out, float scale, int layer, int tp_half = 0) {
+        OpDesc o{}; o.tp_half = tp_half; o.w = m.w; o.type = m.type; o.n_pairs = (int)(m.N / 2); o.n_rows = (int)m.n_rows; o.n_grp = n_groups(m.K); o.epi = epi; o.out = out; o.scale = scale; o.layer = layer; return o;
     };
     auto gemv = [&](int K, int pro, const float* src, const float* nw, int layer, std::initializer_list<OpDesc> ops) {
         Phase p{}; p.kind = PH_GEMV; p.K = K; p.pro = pro; p.src = src; p.norm_w = nw; p.layer = layer; p.n_ops = 0; p.total_pairs = 0;
@@ -392,7 +418,7 @@ int Model::commit() {
         { Phase p{}; p.kind = PH_ATTN; p.layer = l; ph.push_back(p); }
         gemv(QD, PRO_ATTN, nullptr, nullptr, l, {mk_op(L.wo, EPI_RESID, nullptr, rs, l)});
         gemv(D, PRO_NORM, nullptr, L.ffn_norm, l, {mk_op(L.wgu, EPI_SWIGLU, nullptr, 1.f, l)});
-        gemv(F, PRO_ACT, nullptr, nullptr, l, {mk_op(L.wd, EPI_RESID, nullptr, rs, l)});
+        gemv(F, PRO_ACT, nullptr, nullptr, l, {mk_op(L.wd, EPI_RESID, nullptr, rs, l, 1)});
     }
     gemv(D, PRO_NORM, nullptr, out_norm, 0, {mk_op(out_w, EPI_LOGITS, d_logits, logit_scale != 0.f ? 1.f / logit_scale : 1.f, 0)});
     n_phases = (int)ph.size();
@@ -405,7 +431,7 @@ int Model::commit() {
 void Model::fill_params(DecodeParams& P) const {
     P = DecodeParams{};
     P.phases = d_phases; P.n_phases = n_phases;
-    P.n_embd = n_embd; P.n_head = n_head; P.n_head_kv = n_head_kv; P.head_dim = head_dim; P.n_rot = n_rot; P.n_vocab = n_vocab; P.n_splits = n_splits;
+    P.n_embd = n_embd; P.n_head = n_head; P.n_head_kv = n_head_kv; P.head_dim = head_dim; P.n_rot = n_rot; P.n_vocab = n_vocab; P.n_vocab_l = n_vocab_l; P.n_splits = n_splits;
     P.rms_eps = rms_eps; P.kq_scale = attn_scale != 0.f ? attn_scale : 1.0f / std::sqrt((float)head_dim); P.emb_scale = emb_scale;
     P.inv_freq = inv_freq; P.embd = tok_embd.w; P.embd_type = tok_embd.type;
     P.logits = d_logits;
@@ -418,13 +444,48 @@ void Model::fill_params(DecodeParams& P) const {
     P.kv.pages = d_kv; P.kv.block_table = d_block_table + (size_t)sync_slot * pages_per_seq; P.kv.n_layer = n_layer; P.kv.n_head_kv = n_head_kv; P.kv.head_dim = head_dim; P.kv.pages_per_seq = pages_per_seq; P.kv.n_pages = n_pages;
     P.pos = d_state + 0; P.token = d_state + 1; P.bar_ctr = (unsigned*)(d_state + 2); P.epoch = (unsigned*)(d_state + 3);
     P.out_tokens = d_out_tokens; P.n_steps = 1; P.want_argmax = 1; P.trace = d_trace;
+    const Engine& E = engine();
+    P.tp_rank = tp ? E.tp_rank : 0; P.tp_world = tp ? E.tp_world : 1; P.vocab_base = tp ? E.tp_rank * n_vocab_l : 0; P.tp_error = tp_error;
+    if (tp) for (int r = 0; r < E.tp_world; r++) { P.rx_peer[r] = (uint2*)tp_peer[r]; P.cand_peer[r] = (uint2*)((uint8_t*)tp_peer[r] + tp_rx_bytes); }
+}
+
+// Exchange buffers of the tensor-parallel batch-1 kernel: one allocation per rank ([rx: 2 x world x n_embd][candidates:
+// world x 2 x grid] tagged 8-byte words, zeroed = never valid), shared with the peers through CUDA IPC handles that
+// travel over the NCCL communicator; every rank maps every peer's buffer (NVLink peer stores land in it).
+int Model::tp_setup_exchange() {
+    Engine& E = engine(); const int W = E.tp_world, me = E.tp_rank;
+    if (W > 8) return fail(B200_ERR_UNSUPPORTED, "at most 8 tensor-parallel ranks");
+    tp_rx_bytes = (size_t)2 * W * n_embd * sizeof(uint2);
+    const size_t bytes = tp_rx_bytes + (size_t)W * 2 * E.n_sm * sizeof(uint2) + 256;
+    if (int rc = own(&tp_buf, bytes)) return rc;
+    if (int rc = own(&tp_error, (size_t)4)) return rc;
+    CK(cudaMemsetAsync(tp_buf, 0, bytes, E.stream)); CK(cudaMemsetAsync(tp_error, 0, 16, E.stream));
+    cudaIpcMemHandle_t mine; CK(cudaIpcGetMemHandle(&mine, tp_buf));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    float* d_h = nullptr; if (int rc = dalloc(&d_h, (size_t)(W + 1) * 16)) return rc;
+    CK(cudaMemcpyAsync(d_h + (size_t)W * 16, &mine, 64, cudaMemcpyHostToDevice, E.stream));
+    if (int rc = E.all_gather(d_h + (size_t)W * 16, d_h, 16)) { cudaFree(d_h); return rc; }      // ordered behind the memsets on every rank
+    std::vector<cudaIpcMemHandle_t> all((size_t)W);
+    CK(cudaMemcpyAsync(all.data(), d_h, (size_t)W * 64, cudaMemcpyDeviceToHost, E.stream));
+    CK(cudaStreamSynchronize(E.stream)); cudaFree(d_h);
+    for (int r = 0; r < W; r++) {
+        if (r == me) { tp_peer[r] = tp_buf; continue; }
+        cudaError_t e = cudaIpcOpenMemHandle(&tp_peer[r], all[(size_t)r], cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) return fail(B200_ERR_CUDA, std::string("cudaIpcOpenMemHandle (peer ") + std::to_string(r) + "): " + cudaGetErrorString(e));
+    }
+    return B200_OK;
+}
+int Model::tp_check_error() {
+    if (!tp || !tp_error) return B200_OK;
+    unsigned e = 0; CK(cudaMemcpy(&e, tp_error, 4, cudaMemcpyDeviceToHost));
+    if (e) { cudaMemset(tp_error, 0, 4); return fail(B200_ERR_CUDA, "a tensor-parallel peer did not answer inside the decode kernel (ranks must launch the same steps)"); }
+    return B200_OK;
 }
 
 // Runs `n_steps` decode steps.  forced (host, n_forced ints) are fed first.  reset: start at position 0.
 int Model::run_steps(int n_steps, const int32_t* forced, int n_forced, bool reset, float* logits_all_dev) {
     Engine& E = engine();
     if (!committed) return fail(B200_ERR_STATE, "model not committed");
-    if (tp) return fail(B200_ERR_UNSUPPORTED, "tensor-parallel shard: the batch-1 decode kernel is single-GPU");
     if (n_steps <= 0) return B200_OK;
     if (reset) { int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0; }
     if (cur_pos + n_steps > E.max_ctx) return fail(B200_ERR_INVALID, "context overflow: " + std::to_string(cur_pos + n_steps) + " > max_ctx " + std::to_string(E.max_ctx));
@@ -447,12 +508,12 @@ int Model::run_steps(int n_steps, const int32_t* forced, int n_forced, bool rese
 int Model::generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_sampling* s, int32_t* out, int* n_out, float* ttft_ms, float* decode_ms,
                     int* finish_reason, const std::chrono::steady_clock::time_point* t_submit) {
     Engine& E = engine(); if (int rc = E.ensure()) return rc;
-    if (tp) return fail(B200_ERR_UNSUPPORTED, "tensor-parallel shard: drive all ranks through b200_model_prefill_slot / b200_model_batch_step");
     std::lock_guard<std::mutex> lk(run_mu);
     if (!committed) return fail(B200_ERR_STATE, "model '" + id + "' is not loaded (closed or deleted)");
     if (n_prompt < 1 || n_gen < 1) return fail(B200_ERR_INVALID, "need at least one prompt token and one generated token");
     for (int i = 0; i < n_prompt; i++) if (prompt[i] < 0 || prompt[i] >= n_vocab) return fail(B200_ERR_INVALID, "prompt token out of range");
     const bool greedy = !s || s->temperature <= 0.f;
+    if (tp && !greedy) return fail(B200_ERR_UNSUPPORTED, "tensor-parallel shard: the synchronous path is greedy only (each rank holds a slice of the logits)");
     const int stop = s ? s->stop_token : -1; const bool ignore_eos = s && s->ignore_eos;
     const bool has_deadline = s && s->timeout_ms > 0;
     const auto deadline = (t_submit ? *t_submit : std::chrono::steady_clock::now()) + std::chrono::milliseconds(has_deadline ? s->timeout_ms : 0);
@@ -521,8 +582,9 @@ int Model::eval(const int32_t* toks, int n, float* logits_all, float* logits_las
     if (!committed) return fail(B200_ERR_STATE, "model '" + id + "' is not loaded (closed or deleted)");
     if (n < 1) return fail(B200_ERR_INVALID, "empty token list");
     for (int i = 0; i < n; i++) if (toks[i] < 0 || toks[i] >= n_vocab) return fail(B200_ERR_INVALID, "token out of range");
-    float* d_all = nullptr;
-    if (logits_all) { if (int rc = dalloc(&d_all, (size_t)n * n_vocab)) return rc; }
+    float* d_all = nullptr;                                        // [n][n_vocab_l]: a tensor-parallel rank produces its vocabulary slice
+    if (logits_all) { if (int rc = dalloc(&d_all, (size_t)n * n_vocab_l)) return rc; }
+    const size_t col0 = tp ? (size_t)E.tp_rank * n_vocab_l : 0;    // the slice lands in its columns of the caller's [n][n_vocab] array
     int rc;
     if (!logits_all && prefill_min > 0 && n - 1 >= prefill_min) {      // only the last position's logits: batched ingestion of the rest
         int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0;
@@ -531,8 +593,9 @@ int Model::eval(const int32_t* toks, int n, float* logits_all, float* logits_las
     } else rc = run_steps(n, toks, n, true, d_all);
     if (!rc) {
         cudaError_t e = cudaStreamSynchronize(E.stream);
-        if (e == cudaSuccess && logits_all) e = cudaMemcpy(logits_all, d_all, (size_t)n * n_vocab * 4, cudaMemcpyDeviceToHost);
-        if (e == cudaSuccess && logits_last) e = cudaMemcpy(logits_last, logits_all ? d_all + (size_t)(n - 1) * n_vocab : d_logits, (size_t)n_vocab * 4, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess && logits_all) e = cudaMemcpy2D(logits_all + col0, (size_t)n_vocab * 4, d_all, (size_t)n_vocab_l * 4, (size_t)n_vocab_l * 4, n, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess && logits_last) e = cudaMemcpy(logits_last + col0, logits_all ? d_all + (size_t)(n - 1) * n_vocab_l : d_logits, (size_t)n_vocab_l * 4, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess && !rc) rc = tp_check_error();
         if (e != cudaSuccess) rc = fail(B200_ERR_CUDA, cudaGetErrorString(e));
     }
     if (d_all) cudaFree(d_all);
@@ -544,7 +607,7 @@ int Model::eval(const int32_t* toks, int n, float* logits_all, float* logits_las
 double Model::bytes_per_token(int ctx) const {
     const GgufTensor* te = meta.tensor("token_embd.weight");
     double w = (double)weight_bytes;
-    if (meta.tensor("output.weight")) w -= (double)te->nbytes;
+    if (meta.tensor("output.weight") || tp) w -= (double)te->nbytes;      // a shard counts token_embd and its lm_head slice separately
     w += (double)te->nbytes / n_vocab;
     return w + (double)ctx * n_layer * 2 * n_head_kv * head_dim * 2;
 }
@@ -573,6 +636,7 @@ int Model::bench_decode(int ctx_len, int n_steps, int warmup, float* ms_per_toke
         if (FILE* f = fopen(trace_path, "wb")) { int hdr[3] = {n_steps, n_phases, grid}; fwrite(hdr, 4, 3, f); fwrite(tr.data(), 8, trace_n, f); fclose(f); }
         cudaFree(d_trace); d_trace = nullptr;
     }
+    if (!rc) rc = tp_check_error();
     if (ms_per_token) *ms_per_token = ms / n_steps;
     if (bytes) { double b = 0; for (int i = 0; i < n_steps; i++) b += bytes_per_token(ctx_len + i + 1); *bytes = b / n_steps; }
     return rc;

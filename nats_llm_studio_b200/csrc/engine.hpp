@@ -105,6 +105,10 @@ struct Model {
     int tp_reduce_add(int M, const struct QgSplit& sp);
     int load_slice(const std::string& name, int64_t N_full, int K_full, int64_t row0, int64_t nrows, int col0, int ncols, Matrix& out);
     bool tp = false; int n_vocab_l = 0; float* pf_T = nullptr;    // tensor-parallel shard: local vocab rows, partial-sum buffer
+    // tensor parallelism inside the batch-1 kernel: exchange buffers in peer memory (this rank's allocation + the peers' IPC mappings)
+    uint8_t* tp_buf = nullptr; void* tp_peer[8] = {}; size_t tp_rx_bytes = 0; unsigned* tp_error = nullptr;
+    int tp_setup_exchange();
+    int tp_check_error();
     bool use_qgemm(int M) const;
     bool tile_ready = false;
     int dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits, bool q);
@@ -133,6 +137,8 @@ int kernel_gemm_bf16(const float* A, const float* B, float* C, int M, int N, int
 int kernel_qgemm(int type, const void* raw, int64_t N, int K, const float* x, int B, float* y, int iters, float* ms);
 int kernel_dequantize_noalloc(int type, const void* d_raw, int64_t n_rows, int K, float* d_out);
 int layout_selftest();
+// rows / K window of a tensor that tensor-parallel rank `rank` of `world` keeps (host arithmetic only; Model::commit uses it)
+int tp_shard_window(const char* kind, int64_t N, int K, int rank, int world, int64_t* row0, int64_t* nrows, int* col0, int* ncols);
 
 // registry (handlers.cpp)
 struct Registry {

@@ -95,6 +95,8 @@ struct OpDesc {                 // one streamed matrix (engine layout, quant.cuh
     float* out;                 // EPI_STORE destination
     float scale;                // output scale (residual_scale, 1/logit_scale, 1)
     int layer;                  // for KV epilogues
+    int tp_half;                // EPI_RESID under tensor parallelism: which half of the peers' receive buffers (0 = wo, 1 = down)
+    int pad_;
 };
 
 struct Phase {
@@ -124,6 +126,7 @@ struct DecodeParams {
     const Phase* phases; int n_phases;
     // model scalars
     int n_embd, n_head, n_head_kv, head_dim, n_rot, n_vocab, n_splits;
+    int n_vocab_l;              // rows of this rank's lm_head (== n_vocab on one GPU): row stride of logits_all
     float rms_eps, kq_scale, emb_scale;
     const float* inv_freq;      // [n_rot/2] = base^(-2i/n_rot) / freq_factor_i
     // embedding
@@ -142,6 +145,13 @@ struct DecodeParams {
     int n_steps; int want_argmax; int max_inflight;
     int quiet;                  // 1: the producer holds back copies of later phases while the CTA polls an exchange (see Smem::ctrl)
     uint32_t l2_ahead;          // bytes per CTA the producer may prefetch into L2 beyond what the ring holds (0 = off)
+    // tensor parallelism inside the kernel (K10): this rank's shard runs the same schedule; the partial sums of the two
+    // row-parallel products of a layer and the argmax candidates are exchanged as tagged words over NVLink peer memory
+    int tp_rank, tp_world;      // tp_world == 1: single GPU (nothing below is used)
+    uint2* rx_peer[8];          // rank r's receive buffer as mapped in THIS process: [2 (wo | down)][tp_world (source rank)][n_embd] LL32 words
+    uint2* cand_peer[8];        // rank r's candidate buffer: [tp_world (source rank)][2 * grid] LL32 words
+    int vocab_base;             // first vocabulary row of this rank's lm_head slice
+    unsigned* tp_error;         // set when a peer did not answer within the spin budget (the launch then ends with garbage instead of hanging)
     long long* trace;           // optional [n_steps][n_phases][grid][4]: clock64 at phase start / prologue end / phase end, smid (debug)
 };
 

@@ -60,6 +60,7 @@ SYMBOLS = {
     "b200_gemm_bf16": (ci, [vp, vp, vp, ci, ci, ci]), "b200_qgemm": (ci, [ci, vp, C.c_int64, ci, vp, ci, vp, ci, C.POINTER(C.c_float)]), "b200_model_prefill_slot": (ci, [vp, ci, vp, ci, ci]),
     "b200_model_batch_step": (ci, [vp, vp, vp, vp, ci, vp, vp]),
     "b200_model_batch_step_sampled": (ci, [vp, vp, vp, vp, ci, vp, vp, vp, vp]),
+    "b200_tp_shard_window": (ci, [C.c_char_p, C.c_int64, ci, ci, ci, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(ci), C.POINTER(ci)]),
     "b200_tp_unique_id": (ci, [vp, sz]), "b200_tp_init": (ci, [ci, ci, vp, sz]), "b200_model_set_prefill_min": (ci, [vp, ci]),
     "b200_launch_count": (C.c_uint64, []), "b200_layout_selftest": (ci, []),
 }
@@ -248,6 +249,13 @@ class Engine:
         if n < 0:
             _check(n)
         return [Event.from_buffer_copy(buf[i]) for i in range(n)]
+
+    @staticmethod
+    def tp_shard_window(kind, N, K, rank, world):
+        """(row0, nrows, col0, ncols) of the tensor [N x K] that tensor-parallel rank `rank` of `world` keeps (host only)"""
+        r0, nr, c0, nc = C.c_int64(0), C.c_int64(0), ci(0), ci(0)
+        _check(lib().b200_tp_shard_window(kind.encode(), N, K, rank, world, C.byref(r0), C.byref(nr), C.byref(c0), C.byref(nc)))
+        return r0.value, nr.value, c0.value, nc.value
 
     @staticmethod
     def tp_unique_id():
