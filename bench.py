@@ -141,6 +141,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-batched", action="store_true", help="skip the bs64 / continuous-batching measurements (N=1 only)")
+    ap.add_argument("--no-tp", action="store_true", help="skip the Llama-3-70B tensor-parallel measurements (config 4)")
+    ap.add_argument("--tp-preset", default="llama3-70b")
+    ap.add_argument("--tp-layers", type=int, default=0, help="debug: fewer layers in the tensor-parallel model")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     W = max(a.warmup, 3); K = a.steps
@@ -251,12 +254,34 @@ def main():
             m = None
         except (Exception, SystemExit) as ex:                      # reported, never fatal for the headline line
             batched = {"error": str(ex)}; m = None
+    # ---- config 4: Llama-3-70B Q4_K_M.  N = 1: the single-GPU base (the file fits in 180 GB) through the persistent kernel.
+    # N > 1: the model tensor-parallel over the N ranks — parity on a small model first (tools/tp_check.py: shards vs the
+    # CPU oracle, results identical on all ranks), then bs1 through the persistent kernel with its in-kernel NVLink
+    # exchange and bs32 through the batched row path (NCCL).  The replica `value` above stays the headline metric.
+    tp = None
+    if not a.no_tp and not a.n_layer:
+        try:
+            import bench_tp
+            if m is not None:
+                m.close(); m = None
+            eng.shutdown()
+            gloo = dist.new_group(backend="gloo") if dist else None
+            if dist:
+                import tp_check
+                parity = tp_check.check(rank, world, local, gloo, verbose=False)
+            else:
+                parity = None
+            tp = bench_tp.measure(rank, world, local, gloo, preset=a.tp_preset, n_layer=a.tp_layers, ctx=a.ctx, steps=min(K, 32), warmup=4,
+                                  batches=(1, 32) if dist else (1,), peak=peak)
+            tp["parity"] = parity
+        except (Exception, SystemExit) as ex:
+            tp = {"error": f"{type(ex).__name__}: {ex}"}
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_total / K,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8 x int4/6/8 dp4a, fp32 accumulate", "data": "synthetic",
                 "config": config, "roofline": roofline, "cpu_baseline": cb, "e2e": e2e, "gpu_launches": l1 - l0, "clocks": clk,
                 "load_s": load_s, "engine": {k: info[k] for k in ("grid", "ring_bytes", "n_phases", "n_splits", "weight_bytes", "hbm_bytes")},
-                "batched": batched}
+                "batched": batched, "tp": tp}
         print(json.dumps(line))
     if m is not None:
         m.close()

@@ -518,7 +518,7 @@ struct DecodeRun {
 __global__ void __launch_bounds__(CTA_THREADS, 1)
 decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes, const int max_grp) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    Smem sm_ = carve_smem(smem_raw, ring_bytes, max_grp, P.hown_cap); carve_tail(sm_, P.n_phases);
+    Smem sm_ = carve_smem(smem_raw, ring_bytes, max_grp, P.hown_cap); carve_tail(sm_, P.max_segs);
     const Smem sm = sm_;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, c = blockIdx.x, G = gridDim.x;
     if (tid == 0) {
@@ -527,16 +527,23 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
         sm.ctrl[0] = 0x7fffffff;
     }
     for (int i = tid; i < P.n_btab; i += CTA_THREADS) sm.btab[i] = P.kv.block_table[i];
-    {   // schedule -> shared memory
+    constexpr int PW = (int)(sizeof(Phase) / 4);                        // words per phase descriptor
+    {   // schedule -> shared memory: all of a short schedule, or embed / lm_head / the first two layers of a model's
         const uint32_t* src = (const uint32_t*)P.phases; uint32_t* dst = (uint32_t*)sm.phases;
-        for (int i = tid; i < P.n_phases * (int)(sizeof(Phase) / 4); i += CTA_THREADS) dst[i] = __ldg(src + i);
+        if (P.sched_layers == 0) { for (int i = tid; i < P.n_phases * PW; i += CTA_THREADS) dst[i] = __ldg(src + i); }
+        else {
+            for (int i = tid; i < PW; i += CTA_THREADS) { dst[i] = __ldg(src + i); dst[PW + i] = __ldg(src + (size_t)(P.n_phases - 1) * PW + i); }
+            for (int i = tid; i < 2 * LAYER_PHASES * PW; i += CTA_THREADS) {
+                const int half = i / (LAYER_PHASES * PW), w = i - half * LAYER_PHASES * PW, layer = half % P.sched_layers;
+                dst[2 * PW + i] = __ldg(src + (size_t)(1 + layer * LAYER_PHASES) * PW + w);
+            }
+        }
     }
-    __syncthreads();
+    build_segs(sm, P, c, G, tid, CTA_THREADS, sm.ring);                 // ends with __syncthreads
 
     if (warp == CONSUMER_WARPS) {           // ===== producer warp =====
         Producer pr; pr.init(P.max_inflight);
-        const int n_seg = pr.build_segs(sm, P.n_phases, c, G, lane);
-        pr.run(sm, P, n_seg, R.n_forced, R.logits_all != nullptr, lane);
+        pr.run(sm, P, sm.ctrl[1], R.n_forced, R.logits_all != nullptr, lane);
         pr.drain(sm);
         return;
     }
@@ -545,6 +552,7 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
     uint32_t seq = *(volatile unsigned*)P.epoch;          // generation counter: one per executed phase
     const int pos0 = *(volatile int*)P.pos;
     int token = R.n_forced > 0 ? R.forced[0] : *(volatile int*)P.token;
+    uint32_t sched_pf = 0;                                  // one word of the next layer's descriptors in flight (see the phase loop)
     uint32_t stage_seq = 0;                                 // stages of this CTA consumed so far (the producer's cur.seq, on the consumer side)
     int hlo, hhi; cta_slice(P.n_embd / 2, c, G, hlo, hhi);  // hidden-state row pairs this CTA owns (== its wo/down slices)
     for (int step = 0; step < P.n_steps; step++) {
@@ -553,8 +561,16 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
         float* logits_dst = R.logits_all ? R.logits_all + (size_t)step * P.n_vocab_l : P.logits;
         ArgBest best; best.v = -INFINITY; best.i = 0x7fffffff;
         for (int i = 0; i < P.n_phases; i++) {
-            const Phase& ph = sm.phases[i];
+            const Phase& ph = sm.phases[phase_slot(P, step, i)];
             if (ph.kind == PH_GEMV && ph.op[0].epi == EPI_LOGITS && !need_lm) continue;
+            if (P.sched_layers > 0 && i > 0 && i < P.n_phases - 1 && tid < LAYER_PHASES * PW) {
+                // the layer after this one: its descriptors are requested at the layer's first phase and stored at its second
+                // (a full phase for the load to land), into the half the previous layer has left (every warp passed this
+                // layer's first prologue barrier since)
+                const int l = (i - 1) / LAYER_PHASES, j = (i - 1) - l * LAYER_PHASES;
+                if (j == 0) sched_pf = __ldg((const uint32_t*)P.phases + (size_t)(1 + ((l + 1) % P.sched_layers) * LAYER_PHASES) * PW + tid);
+                else if (j == 1) ((uint32_t*)sm.phases)[(2 + ((step * P.sched_layers + l + 1) & 1) * LAYER_PHASES) * PW + tid] = sched_pf;
+            }
             seq++;
             long long* tr = nullptr;
             if (P.trace) tr = P.trace + (((size_t)step * P.n_phases + i) * G + c) * 8;

@@ -159,17 +159,22 @@ int Engine::ensure() {
 // ------------------------------------------------------------------------------------ launch geometry
 struct LaunchCfg { int grid; uint32_t ring_bytes; int max_grp; size_t smem; };
 
-static int launch_cfg(Engine& E, int max_grp, int hown_cap, int n_phases, LaunchCfg& lc) {
+static int launch_cfg(Engine& E, int max_grp, int hown_cap, int max_segs, LaunchCfg& lc) {
     // one persistent CTA per SM owning (almost) all of its shared memory
     max_grp = std::max(max_grp, (int)(((CONSUMER_WARPS + 1) * 130 + 64) * 4 / 2336 + 1));   // the activation buffer doubles as attention scratch
     size_t per_cta = (size_t)E.smem_optin;
-    size_t fixed = smem_x_bytes(max_grp) + smem_misc_bytes(hown_cap, n_phases);
+    size_t fixed = smem_x_bytes(max_grp) + smem_misc_bytes(hown_cap, max_segs);
     // the ring allocator never splits a stage across the wrap point, so a stage plus the gap it may leave behind
     // must fit: ring >= 2 x the largest stage (otherwise the producer can wait on space that cannot exist)
     if (fixed + 2 * MAX_STAGE_BYTES + 256 > per_cta) return fail(B200_ERR_UNSUPPORTED, "activation vector does not fit in shared memory");
     lc.grid = E.n_sm;
     lc.ring_bytes = (uint32_t)((per_cta - fixed - 128) / 128 * 128);
-    if (const char* rk = getenv("B200_RING_KB")) { uint32_t want = (uint32_t)atoi(rk) * 1024u; if (want >= 2u * MAX_STAGE_BYTES && want < lc.ring_bytes) lc.ring_bytes = want / 128 * 128; }
+    // Not all of it: shared memory and L1 share one array, and what the ring does not take is L1 for the kernel's
+    // register spills and exchange polls.  164 KB (four Q4_K stages / three Q6_K stages in flight) measured best on the
+    // 8B model: 1.97 ms/token against 2.00 with the full 217 KB and 2.04 with 112 KB.  B200_RING_KB overrides.
+    uint32_t want = 164u * 1024u;
+    if (const char* rk = getenv("B200_RING_KB")) want = (uint32_t)atoi(rk) * 1024u;
+    if (want >= 2u * MAX_STAGE_BYTES && want < lc.ring_bytes) lc.ring_bytes = want / 128 * 128;
     lc.max_grp = max_grp; lc.smem = lc.ring_bytes + fixed;
     int occ = 0;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, decode_kernel, CTA_THREADS, lc.smem));
@@ -391,7 +396,8 @@ int Model::commit() {
     if (tp) { if (int rc2 = tp_setup_exchange()) return rc2; }
     int max_grp = std::max({n_groups(F), n_groups(QD), 2 * n_groups(D)});
     hown_cap = 2 * ((D / 2 + E.n_sm - 1) / E.n_sm + 2);                       // pairs per CTA slice (worst case: 1 CTA/SM) x 2 rows
-    LaunchCfg lc; if (int rc2 = launch_cfg(E, max_grp, hown_cap, 5 * n_layer + 2, lc)) return rc2;
+    max_segs = 6 * n_layer + 2;                                              // q, k, v, wo, gate/up, down per layer + lm_head
+    LaunchCfg lc; if (int rc2 = launch_cfg(E, max_grp, hown_cap, max_segs, lc)) return rc2;
     grid = lc.grid; ring_bytes = lc.ring_bytes; smem_max_grp = lc.max_grp; smem_bytes = lc.smem;
     const size_t n_ll16 = (size_t)XREP * ((size_t)D + QD + F) + 2 * (size_t)KVD, n_ll32 = (size_t)QD + (size_t)n_head * 16 * (head_dim + 2) + 2 * (size_t)grid;
     if ((rc = own(&d_ll16, n_ll16)) || (rc = own(&d_ll32, n_ll32)) || (rc = own(&d_logits, (size_t)n_vocab + 2)) || (rc = own(&d_state, (size_t)16)) ||
@@ -430,7 +436,7 @@ int Model::commit() {
 
 void Model::fill_params(DecodeParams& P) const {
     P = DecodeParams{};
-    P.phases = d_phases; P.n_phases = n_phases;
+    P.phases = d_phases; P.n_phases = n_phases; P.sched_layers = n_layer; P.max_segs = max_segs;
     P.n_embd = n_embd; P.n_head = n_head; P.n_head_kv = n_head_kv; P.head_dim = head_dim; P.n_rot = n_rot; P.n_vocab = n_vocab; P.n_vocab_l = n_vocab_l; P.n_splits = n_splits;
     P.rms_eps = rms_eps; P.kq_scale = attn_scale != 0.f ? attn_scale : 1.0f / std::sqrt((float)head_dim); P.emb_scale = emb_scale;
     P.inv_freq = inv_freq; P.embd = tok_embd.w; P.embd_type = tok_embd.type;
@@ -1224,7 +1230,7 @@ int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, flo
     int rc = B200_OK;
     LaunchCfg lc;
     auto cleanup = [&]() { cudaFree(d_raw); cudaFree(d_w); cudaFree(d_x); cudaFree(d_y); cudaFree(d_cv); cudaFree(d_st); cudaFree(d_ot); cudaFree(d_ph); };
-    if ((rc = launch_cfg(E, n_groups(K), 4, 1, lc))) return rc;
+    if ((rc = launch_cfg(E, n_groups(K), 4, 4, lc))) return rc;
     if ((rc = dalloc(&d_raw, (size_t)N * rb)) || (rc = dalloc(&d_w, repacked_bytes(type, N, K))) || (rc = dalloc(&d_x, (size_t)K)) || (rc = dalloc(&d_y, (size_t)N)) ||
         (rc = dalloc(&d_cv, (size_t)2 * lc.grid)) || (rc = dalloc(&d_st, (size_t)16)) || (rc = dalloc(&d_ot, (size_t)iters + 1)) || (rc = dalloc(&d_ph, (size_t)1))) { cleanup(); return rc; }
     cudaMemcpyAsync(d_raw, raw, (size_t)N * rb, cudaMemcpyHostToDevice, E.stream);
@@ -1235,7 +1241,7 @@ int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, flo
         Phase p{}; p.kind = PH_GEMV; p.K = K; p.pro = PRO_PLAIN; p.src = d_x; p.n_ops = 1; p.total_pairs = (int)(N / 2);
         p.op[0].w = d_w; p.op[0].type = type; p.op[0].n_pairs = (int)(N / 2); p.op[0].n_rows = (int)N; p.op[0].n_grp = n_groups(K); p.op[0].epi = EPI_STORE; p.op[0].out = d_y; p.op[0].scale = 1.f;
         cudaMemcpyAsync(d_ph, &p, sizeof p, cudaMemcpyHostToDevice, E.stream);
-        DecodeParams P{}; P.phases = d_ph; P.n_phases = 1; P.n_embd = K; P.n_head = 1; P.n_head_kv = 1; P.head_dim = 128; P.n_vocab = (int)N; P.n_splits = 1;
+        DecodeParams P{}; P.phases = d_ph; P.n_phases = 1; P.sched_layers = 0; P.max_segs = 4; P.n_embd = K; P.n_head = 1; P.n_head_kv = 1; P.head_dim = 128; P.n_vocab = (int)N; P.n_splits = 1;
         P.cand_ll = d_cv; P.hown_cap = 4; P.pos = d_st; P.token = d_st + 1; P.bar_ctr = (unsigned*)(d_st + 2); P.epoch = (unsigned*)(d_st + 3); P.out_tokens = d_ot;
         P.logits = d_y; P.n_steps = 1; P.max_inflight = 4; if (const char* e = getenv("B200_INFLIGHT")) P.max_inflight = std::max(1, atoi(e));
         if (const char* e = getenv("B200_L2_AHEAD_KB")) P.l2_ahead = (uint32_t)std::max(0, atoi(e)) * 1024u;

@@ -124,6 +124,10 @@ struct KvLayout {               // paged KV cache, fp16
 
 struct DecodeParams {
     const Phase* phases; int n_phases;
+    int sched_layers;           // > 0: the schedule is [embed][LAYER_PHASES x sched_layers][lm_head]; shared memory then keeps only the
+                                //      phases of two layers (the current one and the next, fetched while the current one runs).
+                                // 0: any schedule of at most SCHED_SLOTS phases, all resident (kernel-level GEMV entry point)
+    int max_segs;               // capacity of the per-CTA slice list (number of (phase, matrix) pairs of a token)
     // model scalars
     int n_embd, n_head, n_head_kv, head_dim, n_rot, n_vocab, n_splits;
     int n_vocab_l;              // rows of this rank's lm_head (== n_vocab on one GPU): row stride of logits_all
@@ -166,20 +170,29 @@ struct Smem {
     float* hown;                              // fp32 hidden-state rows this CTA owns (residual stream never leaves the SM)
     float2* rope;                             // (cos, sin) of this token's RoPE angles [128]
     int* btab;                                // the sequence's KV block table (page ids)
-    Phase* phases;                            // the schedule, copied from global once per launch (descriptor reads are on
-                                              // every phase's critical path; an L2 round trip each would cost microseconds)
+    Phase* phases;                            // SCHED_SLOTS phase descriptors (descriptor reads are on every phase's critical path; an
+                                              // L2 round trip each would cost microseconds): [0] embed, [1] lm_head, [2..] two layers
     struct Seg* segs;                         // this CTA's slices of the token's streamed matrices, in schedule order (producer)
     volatile int* ctrl;                       // [0] quiet_id: phase id (step * n_phases + phase) up to which copies may be issued
-                                              //     while the consumers poll an exchange; INT_MAX = no restriction
+                                              //     while the consumers poll an exchange; INT_MAX = no restriction.  [1] slices in segs[]
 };
+constexpr int LAYER_PHASES = 5;               // QKV, attention, wo, gate/up, down
+constexpr int SCHED_SLOTS = 2 + 2 * LAYER_PHASES;
+// shared-memory slot of phase i of token `step`: layers alternate between the two halves by their running number
+__device__ __forceinline__ int phase_slot(const DecodeParams& P, int step, int i) {
+    if (P.sched_layers == 0) return i;
+    if (i == 0) return 0;
+    if (i == P.n_phases - 1) return 1;
+    const int l = (i - 1) / LAYER_PHASES, j = (i - 1) - l * LAYER_PHASES;
+    return 2 + ((step * P.sched_layers + l) & 1) * LAYER_PHASES + j;
+}
 
 // One streamed slice: pairs [0, n_pairs) starting at src, n_grp groups per row, of phase `phase` of the token.
-struct Seg { const uint8_t* src; int n_pairs; short n_grp; unsigned char type, is_lm; short phase; short pad; int pad2; };
-static_assert(sizeof(Seg) == 24 || sizeof(Seg) == 32, "Seg layout");
-constexpr int MAX_SEGS_PER_PHASE = 3;
+struct Seg { const uint8_t* src; unsigned short n_pairs; unsigned char n_grp, type; unsigned short phase; unsigned char is_lm, pad; };
+static_assert(sizeof(Seg) == 16, "Seg layout");
 __host__ __device__ inline size_t smem_x_bytes(int max_grp) { return (size_t)max_grp * (2048 + 256 + 32); }
 constexpr int BTAB_MAX = 1024;           // KV pages per sequence cached in shared memory (16384 positions)
-__host__ __device__ inline size_t smem_misc_bytes(int hown_cap, int n_phases) { return NSLOT * 16 + 64 * 4 + NSLOT * 8 + 128 * 8 + ((size_t)hown_cap * 4 + 15) / 16 * 16 + BTAB_MAX * 4 + (size_t)n_phases * sizeof(Phase) + (size_t)n_phases * MAX_SEGS_PER_PHASE * sizeof(Seg) + 64 + 64; }
+__host__ __device__ inline size_t smem_misc_bytes(int hown_cap, int max_segs) { return NSLOT * 16 + 64 * 4 + NSLOT * 8 + 128 * 8 + ((size_t)hown_cap * 4 + 15) / 16 * 16 + BTAB_MAX * 4 + (size_t)SCHED_SLOTS * sizeof(Phase) + (size_t)max_segs * sizeof(Seg) + 64 + 64; }
 __device__ inline Smem carve_smem(uint8_t* base, uint32_t ring_bytes, int max_grp, int hown_cap) {   // hown_cap: multiple of 4
     Smem s; s.ring = base; s.ring_bytes = ring_bytes; uint8_t* p = base + ring_bytes;
     s.xq = (int8_t*)p; p += (size_t)max_grp * 2048;
@@ -190,9 +203,9 @@ __device__ inline Smem carve_smem(uint8_t* base, uint32_t ring_bytes, int max_gr
     return s;   // segs / ctrl are placed behind the schedule by carve_tail (they need n_phases)
 }
 
-__device__ inline void carve_tail(Smem& s, int n_phases) {
-    uint8_t* p = (uint8_t*)(s.phases + n_phases); p = (uint8_t*)(((uintptr_t)p + 15) & ~(uintptr_t)15);
-    s.segs = (Seg*)p; p += (size_t)n_phases * MAX_SEGS_PER_PHASE * sizeof(Seg);
+__device__ inline void carve_tail(Smem& s, int max_segs) {
+    uint8_t* p = (uint8_t*)(s.phases + SCHED_SLOTS); p = (uint8_t*)(((uintptr_t)p + 15) & ~(uintptr_t)15);
+    s.segs = (Seg*)p; p += (size_t)max_segs * sizeof(Seg);
     s.ctrl = (volatile int*)p;
 }
 
@@ -264,34 +277,41 @@ __device__ __forceinline__ StageDesc stage_of(const Seg& s, const SegIter& it, i
     return d;
 }
 
+// The CTA's slices of one token, in schedule order: built once per launch by the whole CTA straight from the schedule in
+// global memory (phase i by thread i: count, prefix over the counts, write).  `scratch`: n_phases bytes (the ring, still idle).
+__device__ inline void build_segs(const Smem& sm, const DecodeParams& P, int c, int G, int tid, int n_threads, unsigned char* scratch) {
+    auto slices = [&](int i, Seg* out) {
+        const Phase& ph = P.phases[i];
+        if (ph.kind != PH_GEMV) return 0;
+        int lo, hi; cta_slice(ph.total_pairs, c, G, lo, hi);
+        int off = 0, n = 0;
+        for (int o = 0; o < ph.n_ops; o++) {
+            const OpDesc& op = ph.op[o];
+            const int a = max(lo, off) - off, b = min(hi, off + op.n_pairs) - off; off += op.n_pairs;
+            if (a >= b) continue;
+            if (out) {
+                Seg sg; sg.src = op.w + (size_t)a * op.n_grp * 2u * group_bytes(op.type); sg.n_pairs = (unsigned short)(b - a); sg.n_grp = (unsigned char)op.n_grp;
+                sg.type = (unsigned char)op.type; sg.is_lm = op.epi == EPI_LOGITS; sg.phase = (unsigned short)i; sg.pad = 0;
+                out[n] = sg;
+            }
+            n++;
+        }
+        return n;
+    };
+    for (int i = tid; i < P.n_phases; i += n_threads) scratch[i] = (unsigned char)slices(i, nullptr);
+    __syncthreads();
+    for (int i = tid; i < P.n_phases; i += n_threads) {
+        int off = 0; for (int k = 0; k < i; k++) off += scratch[k];
+        if (off + scratch[i] <= P.max_segs) slices(i, sm.segs + off);
+        if (i == P.n_phases - 1) sm.ctrl[1] = min(off + scratch[i], P.max_segs);
+    }
+    __syncthreads();
+}
+
 struct Producer {
     RingCursor cur; uint32_t used, oldest;            // bytes held by unreleased stages (incl. gaps); oldest unreleased stage
     uint32_t landed, max_unlanded;                    // stages whose bytes have all arrived; cap on issued-but-unlanded stages
     __device__ void init(int inflight) { cur.init(); used = 0; oldest = 0; landed = 0; max_unlanded = (uint32_t)max(1, inflight); }
-
-    // The CTA's slices of one token, in schedule order (called once per launch by the whole producer warp).
-    __device__ int build_segs(const Smem& sm, int n_phases, int c, int G, int lane) {
-        int n = 0;
-        for (int i = 0; i < n_phases; i++) {
-            const Phase& ph = sm.phases[i];
-            if (ph.kind != PH_GEMV) continue;
-            int lo, hi; cta_slice(ph.total_pairs, c, G, lo, hi);
-            int off = 0;
-            for (int o = 0; o < ph.n_ops; o++) {
-                const OpDesc& op = ph.op[o];
-                const int a = max(lo, off) - off, b = min(hi, off + op.n_pairs) - off; off += op.n_pairs;
-                if (a >= b) continue;
-                if (lane == 0) {
-                    Seg sg; sg.src = op.w + (size_t)a * op.n_grp * 2u * group_bytes(op.type); sg.n_pairs = b - a; sg.n_grp = (short)op.n_grp;
-                    sg.type = (unsigned char)op.type; sg.is_lm = op.epi == EPI_LOGITS; sg.phase = (short)i; sg.pad = 0; sg.pad2 = 0;
-                    sm.segs[n] = sg;
-                }
-                n++;
-            }
-        }
-        __syncwarp();
-        return n;
-    }
 
     // Whole producer warp.  Walks the stage sequence of all n_steps tokens; never waits on data dependencies, only on ring
     // space — except that, while the consumers poll an exchange (ctrl[0] = id of the last phase they completed), copies of
