@@ -21,16 +21,18 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
-    if not force and not needs_build():
+def build(force=False, verbose=False, out=None, extra=()):
+    """out / extra: build a variant (other -D flags) next to the product library, e.g. for an A/B run on the GPU box"""
+    if not force and not needs_build() and out is None:
         return OUT
-    cmd = [NVCC] + FLAGS + EXTRA + (["-Xptxas", "-v"] if verbose else []) + ["-x", "cu"] + [os.path.join(CSRC, s) for s in SOURCES] + ["-o", OUT]
+    out = out or OUT
+    cmd = [NVCC] + FLAGS + EXTRA + list(extra) + (["-Xptxas", "-v"] if verbose else []) + ["-x", "cu"] + [os.path.join(CSRC, s) for s in SOURCES] + ["-o", out]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if verbose or r.returncode:
         sys.stderr.write(r.stdout + r.stderr)
     if r.returncode:
         raise RuntimeError("nvcc failed")
-    return OUT
+    return out
 
 
 if __name__ == "__main__":

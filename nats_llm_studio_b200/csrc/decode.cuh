@@ -329,7 +329,7 @@ __device__ __forceinline__ void epilogue(const DecodeParams& P, const OpDesc& op
 // Pairs [a, b) of `op`, eight pairs per stage (one per warp of a group).  A warp visits only the stages of its group's
 // row blocks: their sequence numbers follow from the slice's stage order (seg_stage_index), the ring offset of a stage
 // is published by the producer next to its barrier.  seq0: sequence number of the slice's first stage.
-template <int TYPE>
+template <int TYPE, bool XHOLD>
 __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& op, const Smem& sm, const Smem& sx, uint32_t seq0, int a, int b,
                                           int pos, int warp, int lane, uint32_t seq, float in_scale, ArgBest& best, float* logits_dst, long long* tr) {
     constexpr int GB = TYPE == T_Q4_K ? 1152 : TYPE == T_Q5_K ? 1408 : TYPE == T_Q6_K ? 1680 : 2176;
@@ -338,6 +338,11 @@ __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& o
     const int n_grp = op.n_grp, spr = (n_grp + SG - 1) / SG;
     const int wg = warp / GROUP_WARPS, wl = warp % GROUP_WARPS;
     const int n_rb = (b - a + PAIRS_PER_STAGE - 1) / PAIRS_PER_STAGE;
+    // XHOLD (inputs of at most SG groups, i.e. one stage per row block): the warp's slice of the activation vector stays in
+    // registers for all of its row blocks instead of being re-read from shared memory for every stage — in a phase with many
+    // row blocks per warp (gate/up, lm_head) those reads were 40 % of the shared-memory wavefronts
+    XRegs xh0, xh1;                                                     // XHOLD: exactly two groups (callers guarantee n_grp == SG == 2)
+    if constexpr (XHOLD) { load_x(sx, 0, lane, xh0); load_x(sx, 1, lane, xh1); }
     for (int rbi = wg; rbi < n_rb; rbi += WARP_GROUPS) {
         const int rb = a + rbi * PAIRS_PER_STAGE, np = min(PAIRS_PER_STAGE, b - rb);
         const bool mine = wl < np;
@@ -347,15 +352,21 @@ __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& o
         for (int gi = 0; gi < spr; gi++, sq += nb) {
             const int g0 = gi * SG, ng = min(SG, n_grp - g0); const uint32_t cb = ng * PU;
             const uint32_t slot = sq % NSLOT;
+            long long w0 = 0; if (tr && warp == 0 && lane == 0) w0 = clock64();
             mbar_wait(&sm.full[slot], (sq / NSLOT) & 1);
-            if (tr && warp == 0 && lane == 0 && rbi == 0 && gi == 0) tr[4] = gtime();
+            if (tr && warp == 0 && lane == 0) { tr[7] += clock64() - w0; if (rbi == 0 && gi == 0) tr[4] = gtime(); }   // tr[7]: cycles warp 0 waited for data
             if (mine) {
                 const uint8_t* unit = sm.ring + sm.q_off[slot] + wl * cb;
+                if constexpr (XHOLD) {
+                    acc0 += lane_dot<TYPE>(unit, lane, xh0); acc1 += lane_dot<TYPE>(unit + GB, lane, xh0);
+                    acc0 += lane_dot<TYPE>(unit + PU, lane, xh1); acc1 += lane_dot<TYPE>(unit + PU + GB, lane, xh1);
+                } else {
 #pragma unroll
-                for (int gg = 0; gg < SG; gg++) if (gg < ng) {
-                    XRegs x; load_x(sx, g0 + gg, lane, x);
-                    acc0 += lane_dot<TYPE>(unit + gg * PU, lane, x);
-                    acc1 += lane_dot<TYPE>(unit + gg * PU + GB, lane, x);
+                    for (int gg = 0; gg < SG; gg++) if (gg < ng) {
+                        XRegs x; load_x(sx, g0 + gg, lane, x);
+                        acc0 += lane_dot<TYPE>(unit + gg * PU, lane, x);
+                        acc1 += lane_dot<TYPE>(unit + gg * PU + GB, lane, x);
+                    }
                 }
             }
             __syncwarp();
@@ -499,12 +510,17 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
         const int a = max(lo, off) - off, b = min(hi, off + op.n_pairs) - off; off += op.n_pairs;
         if (a >= b) continue;
         const Smem& sx = (op.type == T_Q6_K) ? s2 : sm;
+        // phases with one stage per row block and several row blocks per warp keep the activation slice in registers
+        const bool xhold = stage_groups(op.type) == 2 && op.n_grp == 2 && (b - a) > WARP_GROUPS * PAIRS_PER_STAGE;
+#define B200_STREAM(T_) do { if (xhold) stream_op<T_, true>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); \
+                             else stream_op<T_, false>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); } while (0)
         switch (op.type) {
-            case T_Q4_K: stream_op<T_Q4_K>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); break;
-            case T_Q6_K: stream_op<T_Q6_K>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); break;
-            case T_Q8_0: stream_op<T_Q8_0>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); break;
-            default: stream_op<T_Q5_K>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); break;
+            case T_Q4_K: B200_STREAM(T_Q4_K); break;
+            case T_Q6_K: B200_STREAM(T_Q6_K); break;
+            case T_Q8_0: stream_op<T_Q8_0, false>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); break;
+            default: B200_STREAM(T_Q5_K); break;
         }
+#undef B200_STREAM
         stage_seq += (uint32_t)(((b - a + PAIRS_PER_STAGE - 1) / PAIRS_PER_STAGE) * stages_per_rb(op.type, op.n_grp));
     }
 }
@@ -623,7 +639,7 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
 #ifdef B200_TRACE_WAIT
             if (tr && tid == 0) { tr[6] = gtime(); tr[4] = tr[0] + (clock64() - cphase0); }   // tr[4]-tr[0] = SM cycles of the phase; tr[7] = warp 0's wait-for-data ns
 #else
-            if (tr && tid == 0) { tr[6] = gtime(); unsigned smid; asm("mov.u32 %0, %%smid;" : "=r"(smid)); tr[7] = smid; }
+            if (tr && tid == 0) tr[6] = gtime();
 #endif
         }
         // ---- next token: forced, or argmax over the per-CTA candidates (every CTA redundantly)

@@ -23,7 +23,8 @@
 namespace b200 {
 
 #ifndef B200_GROUP_WARPS
-#define B200_GROUP_WARPS 8
+#define B200_GROUP_WARPS 7      // 14 consumer warps + the producer = 15 warps: at most 4 warps per scheduler, so 128 registers per thread
+                                // (16 + 1 warps cap the kernel at 96 registers: measured 1.97 ms/token on the 8B model against 1.89)
 #endif
 constexpr int GROUP_WARPS = B200_GROUP_WARPS;   // warps that share one stage (one row pair each)
 #ifndef B200_WARP_GROUPS
@@ -39,7 +40,10 @@ constexpr int XREP = 8;                  // copies of every broadcast exchange v
                                          // every CTA costs ~0.6 us per line; CTA c reads copy c % XREP)
 // groups (of 2048 elements) per stage: one bulk copy moves a pair's run of `stage_groups` consecutive groups, which
 // are contiguous in HBM — fewer, larger copies (the single producer warp issues them one by one)
-__host__ __device__ constexpr int stage_groups(int type) { return type == 8 /*Q8_0*/ ? 1 : 2; }
+#ifndef B200_STAGE_GROUPS
+#define B200_STAGE_GROUPS 2
+#endif
+__host__ __device__ constexpr int stage_groups(int type) { return type == 8 /*Q8_0*/ ? 1 : B200_STAGE_GROUPS; }
 constexpr int MAX_STAGE_BYTES = PAIRS_PER_STAGE * 2 * 2 * 1680;   // Q6_K, two groups
 
 // ------------------------------------------------------------------------------------ PTX
@@ -425,90 +429,102 @@ __device__ __forceinline__ void k4_scales(const uint4& hdr, int j, int& sc0, int
     sc0 = f & 63; sc1 = (f >> 6) & 63; m0 = (f >> 12) & 63; m1 = (f >> 18) & 63;
 }
 
-__device__ __forceinline__ float lane_dot_q4k(const uint8_t* grp, int lane, const XRegs& x) {
-    const uint8_t* blk = grp + (lane >> 2) * 144; const int j = lane & 3;
-    const uint4 hdr = *(const uint4*)blk;                       // d, dmin, scales[12]
-    const uint4 qa = *(const uint4*)(blk + 16 + 32 * j), qb = *(const uint4*)(blk + 32 + 32 * j);
-    int s0 = 0, s1 = 0, t0 = 0, t1 = 0;                        // four independent dp4a chains (depth 4 instead of 8)
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        const uint32_t w = u4_get(qa, i), v = u4_get(qb, i);
-        s0 = dp4a_ss((int)(w & 0x0F0F0F0Fu), (int)u4_get(x.p[0], i), s0);
-        s1 = dp4a_us(w & 0xF0F0F0F0u, (int)u4_get(x.p[2], i), s1);
-        t0 = dp4a_ss((int)(v & 0x0F0F0F0Fu), (int)u4_get(x.p[1], i), t0);
-        t1 = dp4a_us(v & 0xF0F0F0F0u, (int)u4_get(x.p[3], i), t1);
-    }
-    s0 += t0; s1 += t1;
-    s1 >>= 4;                                                  // exact: every term is a multiple of 16
-    int sc0, sc1, m0, m1; k4_scales(hdr, j, sc0, sc1, m0, m1);
-    const int isum = sc0 * s0 + sc1 * s1;
-    const int msum = m0 * (x.bs[0] + x.bs[1]) + m1 * (x.bs[2] + x.bs[3]);
-    const float2 dd = __half22float2(*(const __half2*)&hdr.x);
-    return x.dx * (dd.x * (float)isum - dd.y * (float)msum);
-}
+// The lane's weights of one row's group, in registers: loading (load_w) apart from the arithmetic (dot_w).  (Putting all
+// reads of a stage in flight ahead of the arithmetic with ordered loads was tried and measured no faster: the stream loop
+// is bound by the number of instructions it issues, not by exposed shared-memory latency — DESIGN.md §3.1.)
+struct WRegs { uint4 v[5]; uint32_t s; };
+__device__ __forceinline__ uint4 lds128(const void* p) { return *(const uint4*)p; }
+__device__ __forceinline__ uint32_t lds32(const void* p) { return *(const uint32_t*)p; }
 
-__device__ __forceinline__ float lane_dot_q5k(const uint8_t* grp, int lane, const XRegs& x) {
-    const uint8_t* blk = grp + (lane >> 2) * 176; const int j = lane & 3;
-    const uint4 hdr = *(const uint4*)blk;
-    const uint4 ha = *(const uint4*)(blk + 16), hb = *(const uint4*)(blk + 32);     // qh[0..31]
-    const uint4 qa = *(const uint4*)(blk + 48 + 32 * j), qb = *(const uint4*)(blk + 64 + 32 * j);
-    int s0 = 0, s1 = 0;
+template <int TYPE>
+__device__ __forceinline__ void load_w(const uint8_t* grp, int lane, WRegs& w) {
+    if constexpr (TYPE == T_Q4_K) {
+        const uint8_t* blk = grp + (lane >> 2) * 144; const int j = lane & 3;
+        w.v[0] = lds128(blk); w.v[1] = lds128(blk + 16 + 32 * j); w.v[2] = lds128(blk + 32 + 32 * j);      // d, dmin, scales[12] | 32 + 32 nibbles
+    } else if constexpr (TYPE == T_Q5_K) {
+        const uint8_t* blk = grp + (lane >> 2) * 176; const int j = lane & 3;
+        w.v[0] = lds128(blk); w.v[1] = lds128(blk + 16); w.v[2] = lds128(blk + 32);                         // header | qh[0..31]
+        w.v[3] = lds128(blk + 48 + 32 * j); w.v[4] = lds128(blk + 64 + 32 * j);
+    } else if constexpr (TYPE == T_Q6_K) {
+        w.v[0] = lds128(grp + lane * 16); w.v[1] = lds128(grp + 512 + lane * 16); w.v[2] = lds128(grp + 1024 + lane * 16);
+        w.v[3].x = lds32(grp + 1536 + lane * 4);
+        w.s = (uint32_t)*(const unsigned short*)(grp + 1664 + (lane >> 2) * 2);
+    } else {
 #pragma unroll
-    for (int i = 0; i < 4; i++) {
-        uint32_t w = u4_get(qa, i), h = u4_get(ha, i) >> (2 * j);
-        s0 = dp4a_ss((int)((w & 0x0F0F0F0Fu) | ((h & 0x01010101u) << 4)), (int)u4_get(x.p[0], i), s0);
-        s1 = dp4a_ss((int)(((w >> 4) & 0x0F0F0F0Fu) | ((h & 0x02020202u) << 3)), (int)u4_get(x.p[2], i), s1);
-        w = u4_get(qb, i); h = u4_get(hb, i) >> (2 * j);
-        s0 = dp4a_ss((int)((w & 0x0F0F0F0Fu) | ((h & 0x01010101u) << 4)), (int)u4_get(x.p[1], i), s0);
-        s1 = dp4a_ss((int)(((w >> 4) & 0x0F0F0F0Fu) | ((h & 0x02020202u) << 3)), (int)u4_get(x.p[3], i), s1);
+        for (int p = 0; p < 4; p++) w.v[p] = lds128(grp + p * 512 + lane * 16);
+        w.s = lds32(grp + 2048 + lane * 4);
     }
-    int sc0, sc1, m0, m1; k4_scales(hdr, j, sc0, sc1, m0, m1);
-    const int isum = sc0 * s0 + sc1 * s1;
-    const int msum = m0 * (x.bs[0] + x.bs[1]) + m1 * (x.bs[2] + x.bs[3]);
-    const float2 dd = __half22float2(*(const __half2*)&hdr.x);
-    return x.dx * (dd.x * (float)isum - dd.y * (float)msum);
-}
-
-__device__ __forceinline__ float lane_dot_q6k(const uint8_t* grp, int lane, const XRegs& x) {
-    const uint4 A = *(const uint4*)(grp + lane * 16), B = *(const uint4*)(grp + 512 + lane * 16), H = *(const uint4*)(grp + 1024 + lane * 16);
-    const uint32_t sc4 = *(const uint32_t*)(grp + 1536 + lane * 4);
-    const float d = __half2float(*(const __half*)(grp + 1664 + (lane >> 2) * 2));
-    int s[4] = {0, 0, 0, 0};
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        const uint32_t a = u4_get(A, i), b = u4_get(B, i), h = u4_get(H, i);
-        s[0] = dp4a_ss((int)((a & 0x0F0F0F0Fu) | ((h << 4) & 0x30303030u)), (int)u4_get(x.p[0], i), s[0]);
-        s[1] = dp4a_ss((int)((b & 0x0F0F0F0Fu) | ((h << 2) & 0x30303030u)), (int)u4_get(x.p[1], i), s[1]);
-        s[2] = dp4a_ss((int)(((a >> 4) & 0x0F0F0F0Fu) | (h & 0x30303030u)), (int)u4_get(x.p[2], i), s[2]);
-        s[3] = dp4a_ss((int)(((b >> 4) & 0x0F0F0F0Fu) | ((h >> 2) & 0x30303030u)), (int)u4_get(x.p[3], i), s[3]);
-    }
-    int tot = 0;
-#pragma unroll
-    for (int g = 0; g < 4; g++) tot += (int)(int8_t)(sc4 >> (8 * g)) * (s[g] - 32 * x.bs[g]);
-    return x.dx * d * (float)tot;
-}
-
-__device__ __forceinline__ float lane_dot_q80(const uint8_t* grp, int lane, const XRegs& x) {
-    int s0 = 0, s1 = 0;
-#pragma unroll
-    for (int p = 0; p < 4; p++) {
-        const uint4 w = *(const uint4*)(grp + p * 512 + lane * 16);
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            if (p < 2) s0 = dp4a_ss((int)u4_get(w, i), (int)u4_get(x.p[p], i), s0);
-            else s1 = dp4a_ss((int)u4_get(w, i), (int)u4_get(x.p[p], i), s1);
-        }
-    }
-    const float2 dd = __half22float2(*(const __half2*)(grp + 2048 + lane * 4));
-    return x.dx * (dd.x * (float)s0 + dd.y * (float)s1);
 }
 
 template <int TYPE>
-__device__ __forceinline__ float lane_dot(const uint8_t* grp, int lane, const XRegs& x) {
-    if constexpr (TYPE == T_Q4_K) return lane_dot_q4k(grp, lane, x);
-    else if constexpr (TYPE == T_Q6_K) return lane_dot_q6k(grp, lane, x);
-    else if constexpr (TYPE == T_Q8_0) return lane_dot_q80(grp, lane, x);
-    else return lane_dot_q5k(grp, lane, x);
+__device__ __forceinline__ float dot_w(const WRegs& w, int lane, const XRegs& x) {
+    if constexpr (TYPE == T_Q4_K) {
+        const int j = lane & 3; const uint4& hdr = w.v[0];
+        int s0 = 0, s1 = 0, t0 = 0, t1 = 0;                        // four independent dp4a chains (depth 4 instead of 8)
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t a = u4_get(w.v[1], i), v = u4_get(w.v[2], i);
+            s0 = dp4a_ss((int)(a & 0x0F0F0F0Fu), (int)u4_get(x.p[0], i), s0);
+            s1 = dp4a_us(a & 0xF0F0F0F0u, (int)u4_get(x.p[2], i), s1);
+            t0 = dp4a_ss((int)(v & 0x0F0F0F0Fu), (int)u4_get(x.p[1], i), t0);
+            t1 = dp4a_us(v & 0xF0F0F0F0u, (int)u4_get(x.p[3], i), t1);
+        }
+        s0 += t0; s1 += t1;
+        s1 >>= 4;                                                  // exact: every term is a multiple of 16
+        int sc0, sc1, m0, m1; k4_scales(hdr, j, sc0, sc1, m0, m1);
+        const int isum = sc0 * s0 + sc1 * s1;
+        const int msum = m0 * (x.bs[0] + x.bs[1]) + m1 * (x.bs[2] + x.bs[3]);
+        const float2 dd = __half22float2(*(const __half2*)&hdr.x);
+        return x.dx * (dd.x * (float)isum - dd.y * (float)msum);
+    } else if constexpr (TYPE == T_Q5_K) {
+        const int j = lane & 3; const uint4& hdr = w.v[0];
+        int s0 = 0, s1 = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            uint32_t q = u4_get(w.v[3], i), h = u4_get(w.v[1], i) >> (2 * j);
+            s0 = dp4a_ss((int)((q & 0x0F0F0F0Fu) | ((h & 0x01010101u) << 4)), (int)u4_get(x.p[0], i), s0);
+            s1 = dp4a_ss((int)(((q >> 4) & 0x0F0F0F0Fu) | ((h & 0x02020202u) << 3)), (int)u4_get(x.p[2], i), s1);
+            q = u4_get(w.v[4], i); h = u4_get(w.v[2], i) >> (2 * j);
+            s0 = dp4a_ss((int)((q & 0x0F0F0F0Fu) | ((h & 0x01010101u) << 4)), (int)u4_get(x.p[1], i), s0);
+            s1 = dp4a_ss((int)(((q >> 4) & 0x0F0F0F0Fu) | ((h & 0x02020202u) << 3)), (int)u4_get(x.p[3], i), s1);
+        }
+        int sc0, sc1, m0, m1; k4_scales(hdr, j, sc0, sc1, m0, m1);
+        const int isum = sc0 * s0 + sc1 * s1;
+        const int msum = m0 * (x.bs[0] + x.bs[1]) + m1 * (x.bs[2] + x.bs[3]);
+        const float2 dd = __half22float2(*(const __half2*)&hdr.x);
+        return x.dx * (dd.x * (float)isum - dd.y * (float)msum);
+    } else if constexpr (TYPE == T_Q6_K) {
+        const uint32_t sc4 = w.v[3].x;
+        const float d = __half2float(__ushort_as_half((unsigned short)w.s));
+        int s[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t a = u4_get(w.v[0], i), b = u4_get(w.v[1], i), h = u4_get(w.v[2], i);
+            s[0] = dp4a_ss((int)((a & 0x0F0F0F0Fu) | ((h << 4) & 0x30303030u)), (int)u4_get(x.p[0], i), s[0]);
+            s[1] = dp4a_ss((int)((b & 0x0F0F0F0Fu) | ((h << 2) & 0x30303030u)), (int)u4_get(x.p[1], i), s[1]);
+            s[2] = dp4a_ss((int)(((a >> 4) & 0x0F0F0F0Fu) | (h & 0x30303030u)), (int)u4_get(x.p[2], i), s[2]);
+            s[3] = dp4a_ss((int)(((b >> 4) & 0x0F0F0F0Fu) | ((h >> 2) & 0x30303030u)), (int)u4_get(x.p[3], i), s[3]);
+        }
+        int tot = 0;
+#pragma unroll
+        for (int g = 0; g < 4; g++) tot += (int)(int8_t)(sc4 >> (8 * g)) * (s[g] - 32 * x.bs[g]);
+        return x.dx * d * (float)tot;
+    } else {
+        int s0 = 0, s1 = 0;
+#pragma unroll
+        for (int p = 0; p < 4; p++) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                if (p < 2) s0 = dp4a_ss((int)u4_get(w.v[p], i), (int)u4_get(x.p[p], i), s0);
+                else s1 = dp4a_ss((int)u4_get(w.v[p], i), (int)u4_get(x.p[p], i), s1);
+            }
+        }
+        const float2 dd = __half22float2(*(const __half2*)&w.s);
+        return x.dx * (dd.x * (float)s0 + dd.y * (float)s1);
+    }
 }
+
+template <int TYPE>
+__device__ __forceinline__ float lane_dot(const uint8_t* grp, int lane, const XRegs& x) { WRegs w; load_w<TYPE>(grp, lane, w); return dot_w<TYPE>(w, lane, x); }
 
 }  // namespace b200

@@ -6,7 +6,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(HERE, "libb200engine.so")
+SO_PATH = os.environ.get("B200_LIB") or os.path.join(HERE, "libb200engine.so")      # B200_LIB: an experimental build variant (tools/)
 GGML_TYPES = {"F32": 0, "F16": 1, "Q8_0": 8, "Q4_K": 12, "Q5_K": 13, "Q6_K": 14}
 SUBJECTS = ("lmstudio.list_models", "lmstudio.pull_model", "lmstudio.delete_model", "lmstudio.chat_model")
 
@@ -71,7 +71,7 @@ def lib():
     global _lib
     if _lib is None:
         from . import build as _build
-        if _build.needs_build():
+        if not os.environ.get("B200_LIB") and _build.needs_build():
             _build.build()
         L = C.CDLL(SO_PATH)
         for name, (res, args) in SYMBOLS.items():

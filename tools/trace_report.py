@@ -21,6 +21,10 @@ for kind in ["embed", "qkv", "attn", "wo", "gate_up", "down", "lm_head"]:
     tot += wall.mean() * len(idx)
     print(f"{kind:8s} " + " ".join(f"{v:6.2f}" for v in d) + f" | {np.median(x[..., 6] - x[..., 0]):6.2f} | {wall.mean():7.2f} {np.median(skew):6.2f}  x{len(idx)}")
 print(f"sum of phase wall times: {tot:.1f} us/token")
+for kind in ["qkv", "wo", "gate_up", "down", "lm_head"]:      # warp 0 of each CTA: time blocked on the ring's full-barriers during the stream loop
+    idx = [i for i, n in enumerate(names) if n == kind]
+    w = t[:, idx, :, 7] * 1e3 / 1965.0                    # cycles (t was divided by 1e3) -> us at 1965 MHz
+    print(f"  {kind:8s} warp 0 waited for data {np.median(w):6.2f} us (p90 {np.percentile(w, 90):6.2f}) of a {np.median(t[:, idx, :, 5] - t[:, idx, :, 3]):6.2f} us stream window")
 if "--attn" in sys.argv:
     idx = [i for i, n in enumerate(names) if n == "attn"]
     x = t[:, idx]
