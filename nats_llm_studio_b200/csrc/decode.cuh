@@ -108,7 +108,7 @@ __device__ __forceinline__ float embed_elem(const uint8_t* w, int type, int n_gr
 // first memory round trip overlap.
 template <int VEC>   // head_dim = 32*VEC
 __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int head, int split, int pos, uint32_t seq_in, uint32_t seq_out, int warp, int lane, long long* tr) {
-    constexpr int HD = 32 * VEC, NB = 8;
+    constexpr int HD = 32 * VEC, NB = 10;     // 14 warps x 10 positions: a 128-position split (context 512 over 4 splits) is one batch
     typedef typename std::conditional<VEC == 4, uint2, uint32_t>::type raw_t;     // VEC fp16 values
     const int n_ctx = pos + 1, chunk = (n_ctx + P.n_splits - 1) / P.n_splits;
     const int p0 = split * chunk, p1 = min(n_ctx, p0 + chunk);
@@ -139,16 +139,16 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
     }
     if (warp == 0 && lane == 0) sm.ctrl[0] = 0x7fffffff;             // q has arrived: the producer may run ahead again
     if (tr && warp == 0 && lane == 0) tr[1] = gtime();
+    // A batch is processed as a block: all NB dot products, then their NB warp reductions interleaved (independent shuffle
+    // chains instead of NB dependent ones), then one online-softmax update for the block.
     float m = -INFINITY, l = 0.f;
     for (int pb = p0 + warp; pb < p1; pb += CONSUMER_WARPS * NB) {
         if (pb != p0 + warp) load_batch(pb, kr, vr);
+        float sc[NB];
 #pragma unroll
         for (int b = 0; b < NB; b++) {
             const int p = pb + b * CONSUMER_WARPS;
-            if (p >= p1) continue;                                       // warp-uniform
-            float kf[VEC], vf[VEC];
-            if (p < pos) { unpack(kr[b], kf); unpack(vr[b], vf); }
-            else {                                                        // the token being decoded: tagged exchange words
+            if (p == pos && p < p1) {                                     // the token being decoded: tagged exchange words -> the same raw form
                 const uint32_t want = tag16_of(seq_in) << 16;
                 const uint32_t* kw = P.kv_ll + kvh * HD + lane * VEC; const uint32_t* vw = P.kv_ll + KVD + kvh * HD + lane * VEC;
                 uint32_t kk[VEC], vv[VEC];
@@ -160,19 +160,40 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
                     for (int i = 0; i < VEC; i++) bad |= (kk[i] ^ want) | (vv[i] ^ want);
                     if ((bad >> 16) == 0) break;
                 }
-#pragma unroll
-                for (int i = 0; i < VEC; i++) { kf[i] = ll16_val(kk[i]); vf[i] = ll16_val(vv[i]); }
+                if constexpr (VEC == 4) {
+                    kr[b] = make_uint2((kk[0] & 0xffffu) | (kk[1] << 16), (kk[2] & 0xffffu) | (kk[3] << 16));
+                    vr[b] = make_uint2((vv[0] & 0xffffu) | (vv[1] << 16), (vv[2] & 0xffffu) | (vv[3] << 16));
+                } else { kr[b] = (kk[0] & 0xffffu) | (kk[1] << 16); vr[b] = (vv[0] & 0xffffu) | (vv[1] << 16); }
             }
-            float s = 0.f;
+            float d = 0.f;
+            if (p < p1) {                                                 // warp-uniform
+                float kf[VEC]; unpack(kr[b], kf);
 #pragma unroll
-            for (int i = 0; i < VEC; i++) s += qv[i] * kf[i];
-            s = warp_sum(s);
-            const float mn = fmaxf(m, s), corr = __expf(m - mn), pe = __expf(s - mn);
-            l = l * corr + pe;
-#pragma unroll
-            for (int i = 0; i < VEC; i++) acc[i] = acc[i] * corr + pe * vf[i];
-            m = mn;
+                for (int i = 0; i < VEC; i++) d += qv[i] * kf[i];
+            }
+            sc[b] = d;
         }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+#pragma unroll
+            for (int b = 0; b < NB; b++) sc[b] += __shfl_xor_sync(0xffffffffu, sc[b], o);
+        }
+        float mn = m;
+#pragma unroll
+        for (int b = 0; b < NB; b++) { if (pb + b * CONSUMER_WARPS >= p1) sc[b] = -INFINITY; mn = fmaxf(mn, sc[b]); }
+        const float corr = m == -INFINITY ? 0.f : __expf(m - mn);        // mn is finite: the batch holds at least one position
+        l *= corr;
+#pragma unroll
+        for (int i = 0; i < VEC; i++) acc[i] *= corr;
+#pragma unroll
+        for (int b = 0; b < NB; b++) if (pb + b * CONSUMER_WARPS < p1) {
+            const float pe = __expf(sc[b] - mn);
+            float vf[VEC]; unpack(vr[b], vf);
+            l += pe;
+#pragma unroll
+            for (int i = 0; i < VEC; i++) acc[i] += pe * vf[i];
+        }
+        m = mn;
     }
     if (tr && warp == 0 && lane == 0) tr[2] = gtime();
     // cross-warp combine through shared memory (aliases the activation buffer, idle in this phase)
