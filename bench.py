@@ -250,6 +250,8 @@ def main():
                 eng2 = b200.Engine(device=local, max_ctx=648, max_seqs=64)
                 m2 = eng2.load_file(f"bench/batch-{mix}", model_path(a.preset, mix, a.n_layer, 0))
                 batched[mix] = bench_batch.measure(eng2, m2, peak=peak)
+                if mix == "q8_0":                                   # config 3 as the reference deploys it: requests over NATS
+                    batched[mix]["nats"] = bench_batch.measure_nats(eng2, f"bench/batch-{mix}", m2.n_vocab)
                 m2.close(); eng2.shutdown()
             m = None
         except (Exception, SystemExit) as ex:                      # reported, never fatal for the headline line

@@ -90,6 +90,16 @@ int b200_detokenize(const b200_model* m, const int32_t* toks, int n, char* out, 
  * subject is "lmstudio.list_models" | "lmstudio.pull_model" | "lmstudio.delete_model" |
  * "lmstudio.chat_model".  The reply is what msg.Respond would send. */
 int b200_handle(const char* subject, const void* payload, size_t n, char* reply, size_t cap, size_t* need);
+/* ---- the worker.  The reference describes the service (README.md:475-502: connect to NATS_URL, queue-subscribe to the
+ * four subjects with NATS_QUEUE_GROUP, reply to every request) but holds no code for it (no main, no Subscribe call).
+ * b200_worker_run is that service: a NATS core-protocol client that queue-subscribes to lmstudio.list_models / pull_model /
+ * delete_model / chat_model (and lmstudio.sync_model_from_bucket, README.md:286) and answers each message on its reply
+ * subject with the handlers' envelope.  NULL arguments take NATS_URL (default nats://127.0.0.1:4222) and NATS_QUEUE_GROUP
+ * (default lmstudio-workers) from the environment; LMSTUDIO_MODELS_DIR is honoured.  Requests are handled on n_threads
+ * threads (0 = 2 x max_seqs), so concurrent chat requests are batched by the engine.  Blocks until b200_worker_stop()
+ * (returns 0) or until the connection drops (< 0). */
+int b200_worker_run(const char* nats_url, const char* queue_group, int n_threads);
+int b200_worker_stop(void);
 /* where pull_model looks for "<identifier>.gguf" / "<identifier>" files (LMSTUDIO_MODELS_DIR) */
 int b200_set_models_dir(const char* dir);
 

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libb200engine.so")
-SOURCES = ["engine.cu", "handlers.cpp", "capi.cpp"]
+SOURCES = ["engine.cu", "handlers.cpp", "capi.cpp", "worker.cpp"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 EXTRA = os.environ.get("B200_NVCC_EXTRA", "").split()
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--expt-relaxed-constexpr",

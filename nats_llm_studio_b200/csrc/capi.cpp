@@ -292,6 +292,8 @@ int b200_handle(const char* subject, const void* payload, size_t n, char* reply,
     if (!subject) return fail(B200_ERR_INVALID, "null subject");
     return copy_out(handle_subject(subject, std::string((const char*)payload, payload ? n : 0)), reply, cap, need);
 }
+int b200_worker_run(const char* nats_url, const char* queue_group, int n_threads) { return worker_run(nats_url, queue_group, n_threads); }
+int b200_worker_stop(void) { return worker_stop(); }
 int b200_set_models_dir(const char* dir) { Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); R.models_dir = dir ? dir : ""; while (R.models_dir.size() > 1 && R.models_dir.back() == '/') R.models_dir.pop_back(); return B200_OK; }
 
 int b200_sample(const float* logits, int V, const b200_sampling* s, uint64_t step, int* token) { if (!logits || !s || !token) return fail(B200_ERR_INVALID, "null argument"); return kernel_sample(logits, V, *s, step, token); }

@@ -149,6 +149,9 @@ struct Registry {
 };
 Registry& registry();
 std::string handle_subject(const std::string& subject, const std::string& payload);
+// NATS worker (worker.cpp): queue-subscribes to the subjects and answers through handle_subject until stopped
+int worker_run(const char* url, const char* queue_group, int n_threads);
+int worker_stop();
 // blocking generation through the continuous-batching scheduler (capi.cpp): what lmstudio.chat_model uses when max_seqs > 1
 int sched_generate(const std::shared_ptr<Model>& m, const std::vector<int32_t>& prompt, const b200_sampling& s, std::vector<int32_t>& out, float* ttft_ms, float* decode_ms, int* finish_reason);
 

@@ -52,6 +52,7 @@ SYMBOLS = {
     "b200_model_generate": (ci, [vp, vp, ci, ci, C.POINTER(Sampling), vp, C.POINTER(ci), C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "b200_model_eval": (ci, [vp, vp, ci, vp, vp]), "b200_model_n_vocab": (ci, [vp]),
     "b200_tokenize": (ci, [vp, C.c_char_p, sz, vp, ci, C.POINTER(ci)]), "b200_detokenize": (ci, [vp, vp, ci, vp, sz, C.POINTER(sz)]),
+    "b200_worker_run": (ci, [C.c_char_p, C.c_char_p, ci]), "b200_worker_stop": (ci, []),
     "b200_handle": (ci, [C.c_char_p, vp, sz, vp, sz, C.POINTER(sz)]), "b200_set_models_dir": (ci, [C.c_char_p]),
     "b200_sample": (ci, [vp, ci, C.POINTER(Sampling), C.c_uint64, C.POINTER(ci)]),
     "b200_dequantize": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_dequantize_noalloc": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_gemv": (ci, [ci, vp, C.c_int64, ci, vp, vp, ci, C.POINTER(C.c_float)]),
@@ -267,6 +268,15 @@ class Engine:
     @staticmethod
     def tp_init(rank, world, nccl_id):
         _check(lib().b200_tp_init(rank, world, nccl_id, len(nccl_id) if nccl_id else 0))
+
+    @staticmethod
+    def worker_run(url=None, queue_group=None, n_threads=0):
+        """blocking: serve the lmstudio.* subjects on a NATS server until worker_stop() (run it on a thread)"""
+        return lib().b200_worker_run(url.encode() if url else None, queue_group.encode() if queue_group else None, n_threads)
+
+    @staticmethod
+    def worker_stop():
+        return lib().b200_worker_stop()
 
     def set_models_dir(self, d):
         _check(lib().b200_set_models_dir(d.encode()))

@@ -67,6 +67,47 @@ def measure(eng, m, n_req=64, gen=128, prompt_min=64, prompt_max=512, step_iters
             "roofline": roofline}
 
 
+def measure_nats(eng, model_id, n_vocab, n_req=64, gen=128, prompt_min=64, prompt_max=512, seed=7):
+    """Config 3 over the wire: n_req concurrent lmstudio.chat_model requests published to a NATS queue group (stub broker,
+    tools/nats_stub.py; the worker is csrc/worker.cpp in this process), continuous batching behind it.  Prompt lengths
+    U[prompt_min, prompt_max] tokens (byte-level vocabulary: one token per character), `gen` tokens each, greedy."""
+    import threading
+    import nats_stub
+    rng = np.random.default_rng(seed)
+    lens = rng.integers(prompt_min, prompt_max + 1, n_req)
+    reqs = [json.dumps({"model": model_id, "messages": [{"role": "user", "content": "".join(chr(97 + int(c)) for c in rng.integers(0, 26, max(1, int(n) - 4)))}],
+                        "temperature": 0, "max_tokens": gen, "ignore_eos": True}).encode() for n in lens]
+    broker = nats_stub.Broker().start()
+    t = threading.Thread(target=lambda: b200.Engine.worker_run(broker.url, None, 0), daemon=True); t.start()
+    for _ in range(500):
+        with broker.lock:
+            if broker.subs.get("lmstudio.chat_model"):
+                break
+        time.sleep(0.01)
+    clients = [nats_stub.Client(broker.url) for _ in range(8)]
+    clients[0].request("lmstudio.chat_model", reqs[0][:0] + json.dumps({"model": model_id, "messages": [{"role": "user", "content": "warm"}], "temperature": 0, "max_tokens": 4, "ignore_eos": True}).encode(), timeout=300)
+    out = [None] * n_req; lat = [0.0] * n_req
+    def work(i):
+        t0 = time.perf_counter(); out[i] = clients[i % 8].request("lmstudio.chat_model", reqs[i], timeout=600); lat[i] = time.perf_counter() - t0
+    th = [threading.Thread(target=work, args=(i,)) for i in range(n_req)]
+    t0 = time.perf_counter()
+    [x.start() for x in th]; [x.join() for x in th]
+    wall = time.perf_counter() - t0
+    n_tok = 0; ttft = []; h2d = 0; d2h = 0
+    for i, o in enumerate(out):
+        r = json.loads(o)
+        if not r["ok"] or r["data"]["http_status"] != 200:
+            raise SystemExit(f"chat over NATS failed: {o[:200]}")
+        n_tok += r["data"]["response"]["usage"]["completion_tokens"]; ttft.append(r["data"]["response"]["stats"]["time_to_first_token"] * 1e3)
+        h2d += len(reqs[i]) + 4 * r["data"]["response"]["usage"]["prompt_tokens"]; d2h += len(o)
+    for c in clients:
+        c.close()
+    b200.Engine.worker_stop(); t.join(timeout=20); broker.stop()
+    return {"requests": n_req, "generated": n_tok, "wall_s": round(wall, 3), "aggregate_tok_s": round(n_tok / wall, 1), "ttft_ms_p50": round(float(np.percentile(ttft, 50)), 1),
+            "ttft_ms_p90": round(float(np.percentile(ttft, 90)), 1), "latency_s_p50": round(float(np.percentile(lat, 50)), 3), "h2d_bytes": h2d, "d2h_bytes": d2h,
+            "path": "client -> NATS (stub broker) -> queue group -> C++ worker -> lmstudio.chat_model handler -> continuous-batching scheduler"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--preset", default="llama3-8b"); ap.add_argument("--mix", default="q8_0"); ap.add_argument("--n-layer", type=int, default=0)
