@@ -85,6 +85,15 @@ int b200_model_n_vocab(const b200_model* m);
 int b200_tokenize(const b200_model* m, const char* text, size_t n, int32_t* out, int cap, int* n_out);
 int b200_detokenize(const b200_model* m, const int32_t* toks, int n, char* out, size_t cap, size_t* need);
 
+/* Host-only forms (no GPU): the tokenizer and the chat template of a GGUF header (the first bytes of a .gguf file, up to
+ * the end of its metadata).  The reference forwards `messages` to a runtime that applies both (nats_llm_studio.go:158-167);
+ * here: byte-level BPE from tokenizer.ggml.tokens/merges (Llama-3 / GPT-2 pre-tokeniser split) and the Llama-3, granite and
+ * ChatML chat layouts, recognised from tokenizer.chat_template.  b200_gguf_render_chat takes the JSON array of
+ * {role, content} messages and returns the prompt's token ids, ending with the assistant turn's header. */
+int b200_gguf_tokenize(const void* gguf_head, size_t n, const char* text, size_t text_n, int parse_special, int32_t* out, int cap, int* n_out);
+int b200_gguf_detokenize(const void* gguf_head, size_t n, const int32_t* toks, int n_toks, char* out, size_t cap, size_t* need);
+int b200_gguf_render_chat(const void* gguf_head, size_t n, const char* messages_json, size_t json_n, int32_t* out, int cap, int* n_out);
+
 /* ---- subject handlers: same payloads in, same {ok,error,data} envelope bytes out as
  * Server.onListModels / OnPullModel / OnDeleteModel / OnChatModel (nats_llm_studio.go:228-364).
  * subject is "lmstudio.list_models" | "lmstudio.pull_model" | "lmstudio.delete_model" |

@@ -266,6 +266,35 @@ int b200_detokenize(const b200_model* m, const int32_t* toks, int n, char* out, 
     return copy_out(((const Model*)m)->detokenize(toks, n), out, cap, need);
 }
 
+// host-only forms (no GPU, no loaded model): the tokenizer and chat template of a GGUF header
+static int with_gguf_tokenizer(const void* gguf, size_t n, Tokenizer& tk) {
+    if (!gguf) return fail(B200_ERR_INVALID, "null argument");
+    GgufMeta meta; std::string err = gguf_parse((const uint8_t*)gguf, n, meta);
+    if (err == "need more") return fail(B200_ERR_MORE, "GGUF header longer than the supplied prefix");
+    if (!err.empty()) return fail(B200_ERR_INVALID, "GGUF: " + err);
+    tokenizer_from_gguf(meta, 0, tk);
+    return B200_OK;
+}
+static int copy_tokens(const std::vector<int32_t>& t, int32_t* out, int cap, int* n_out) {
+    if (n_out) *n_out = (int)t.size();
+    if (!out || cap < (int)t.size()) return out ? fail(B200_ERR_MORE, "token buffer too small") : B200_OK;
+    memcpy(out, t.data(), t.size() * 4); return B200_OK;
+}
+int b200_gguf_tokenize(const void* gguf, size_t n, const char* text, size_t tn, int parse_special, int32_t* out, int cap, int* n_out) {
+    Tokenizer tk; if (int rc = with_gguf_tokenizer(gguf, n, tk)) return rc;
+    return copy_tokens(tk.tokenize(std::string(text ? text : "", text ? tn : 0), parse_special != 0), out, cap, n_out);
+}
+int b200_gguf_detokenize(const void* gguf, size_t n, const int32_t* toks, int nt, char* out, size_t cap, size_t* need) {
+    Tokenizer tk; if (int rc = with_gguf_tokenizer(gguf, n, tk)) return rc;
+    return copy_out(tk.detokenize(toks, nt), out, cap, need);
+}
+int b200_gguf_render_chat(const void* gguf, size_t n, const char* messages_json, size_t mn, int32_t* out, int cap, int* n_out) {
+    Tokenizer tk; if (int rc = with_gguf_tokenizer(gguf, n, tk)) return rc;
+    std::vector<int32_t> t; std::string err = render_chat(tk, std::string(messages_json ? messages_json : "", messages_json ? mn : 0), t);
+    if (!err.empty()) return fail(B200_ERR_INVALID, err);
+    return copy_tokens(t, out, cap, n_out);
+}
+
 int b200_submit(b200_model* m, const int32_t* toks, int n, const b200_sampling* s, uint64_t req_id) {
     if (!m || !toks || n < 1) return fail(B200_ERR_INVALID, "bad submit arguments");
     auto sp = find_shared(m); if (!sp || !sp->committed) return fail(B200_ERR_STATE, "model is not loaded");

@@ -18,6 +18,7 @@
 
 #include "../../include/b200_engine.h"
 #include "gguf.hpp"
+#include "tokenizer.hpp"
 
 namespace b200 {
 
@@ -60,7 +61,7 @@ struct Model {
     int bos = -1, eos = -1;
     std::vector<std::string> vocab; std::vector<int> tok_type;
     // tokenizer tables
-    int byte_tok[256]; std::unordered_map<std::string, int> special; std::vector<std::string> piece;
+    Tokenizer tok;
     // upload state
     uint8_t* d_raw = nullptr; uint64_t uploaded = 0; bool committed = false;
     uint64_t weight_bytes = 0, hbm_bytes = 0;
@@ -149,6 +150,10 @@ struct Registry {
 };
 Registry& registry();
 std::string handle_subject(const std::string& subject, const std::string& payload);
+// tokenizer of a GGUF header (host only): tokenizer.ggml.* -> Tokenizer; "" or an error message
+std::string tokenizer_from_gguf(const GgufMeta& meta, int n_vocab, Tokenizer& out);
+// chat rendering (handlers.cpp): messages (parsed JSON array as text) -> prompt token ids with the model's template
+std::string render_chat(const Tokenizer& tok, const std::string& messages_json, std::vector<int32_t>& toks);
 // NATS worker (worker.cpp): queue-subscribes to the subjects and answers through handle_subject until stopped
 int worker_run(const char* url, const char* queue_group, int n_threads);
 int worker_stop();

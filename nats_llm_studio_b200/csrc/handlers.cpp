@@ -21,39 +21,19 @@ namespace b200 {
 Registry& registry() { static Registry r; return r; }
 
 // ------------------------------------------------------------------------------------ tokenizer
-void Model::build_tokenizer() {
-    for (int i = 0; i < 256; i++) byte_tok[i] = -1;
-    piece.assign(vocab.size(), "");
-    for (size_t i = 0; i < vocab.size(); i++) {
-        const std::string& s = vocab[i]; int ty = i < tok_type.size() ? tok_type[i] : 1;
-        if (ty == 6 && s.size() == 6 && s.compare(0, 3, "<0x") == 0 && s[5] == '>') {      // BYTE
-            int b = (int)strtol(s.substr(3, 2).c_str(), nullptr, 16); byte_tok[b & 255] = (int)i; piece[i] = std::string(1, (char)b);
-        } else if (ty == 3 || ty == 4) { special[s] = (int)i; piece[i] = ""; }             // CONTROL / USER_DEFINED
-        else { std::string p = s; size_t k; while ((k = p.find("\xE2\x96\x81")) != std::string::npos) p.replace(k, 3, " "); piece[i] = p; }
-    }
+std::string tokenizer_from_gguf(const GgufMeta& meta, int n_vocab, Tokenizer& out) {
+    std::vector<std::string> tokens, merges; std::vector<int> types;
+    if (auto v = meta.find("tokenizer.ggml.tokens")) tokens = v->arr_str;
+    if (auto v = meta.find("tokenizer.ggml.merges")) merges = v->arr_str;
+    if (auto v = meta.find("tokenizer.ggml.token_type")) { types.assign(v->arr_num.size(), 0); for (size_t i = 0; i < v->arr_num.size(); i++) types[i] = (int)v->arr_num[i]; }
+    out.build(tokens, types, merges, meta.str("tokenizer.ggml.model"), meta.str("tokenizer.ggml.pre"), meta.str("tokenizer.chat_template"),
+              (int)meta.num("tokenizer.ggml.bos_token_id", -1), (int)meta.num("tokenizer.ggml.eos_token_id", -1), meta.num("tokenizer.ggml.add_bos_token", 1) != 0,
+              n_vocab > 0 ? n_vocab : (int)tokens.size());
+    return "";
 }
-
-std::vector<int32_t> Model::tokenize(const std::string& text, bool parse_special) const {
-    std::vector<int32_t> out;
-    size_t i = 0;
-    while (i < text.size()) {
-        if (parse_special && text[i] == '<') {
-            bool hit = false;
-            for (auto& kv : special) if (!kv.first.empty() && text.compare(i, kv.first.size(), kv.first) == 0) { out.push_back(kv.second); i += kv.first.size(); hit = true; break; }
-            if (hit) continue;
-        }
-        int t = byte_tok[(unsigned char)text[i]];
-        out.push_back(t >= 0 ? t : (int)((unsigned char)text[i]) % std::max(1, n_vocab));
-        i++;
-    }
-    return out;
-}
-
-std::string Model::detokenize(const int32_t* toks, int n) const {
-    std::string s;
-    for (int i = 0; i < n; i++) if (toks[i] >= 0 && (size_t)toks[i] < piece.size()) s += piece[toks[i]];
-    return s;
-}
+void Model::build_tokenizer() { tokenizer_from_gguf(meta, n_vocab, tok); }
+std::vector<int32_t> Model::tokenize(const std::string& text, bool parse_special) const { return tok.tokenize(text, parse_special); }
+std::string Model::detokenize(const int32_t* toks, int n) const { return tok.detokenize(toks, n); }
 
 static std::string quant_name(int ftype) {
     switch (ftype) { case 7: return "Q8_0"; case 14: return "Q4_K_S"; case 15: return "Q4_K_M"; case 16: return "Q5_K_S"; case 17: return "Q5_K_M"; case 18: return "Q6_K"; case 1: return "F16"; case 0: return "F32"; default: return "unknown"; }
@@ -186,25 +166,39 @@ static std::string on_delete_model(const std::string& payload) {        // OnDel
 }
 
 // ------------------------------------------------------------------------------------ chat
-static std::string render_prompt(const Model& m, const Json& messages, std::vector<int32_t>& toks) {
-    // fixed minimal template: <|role|>content<|end|> ... <|assistant|>
-    if (m.bos >= 0) toks.push_back(m.bos);
-    auto special_or_text = [&](const std::string& s) {
-        auto it = m.special.find(s);
-        if (it != m.special.end()) toks.push_back(it->second);
-        else { auto t = m.tokenize(s, false); toks.insert(toks.end(), t.begin(), t.end()); }
-    };
+// The model's chat template applied to `messages` (OpenAI-style [{role, content}]), ending with the header of the
+// assistant's turn.  Families are recognised from tokenizer.chat_template's marker tokens (tokenizer.hpp); the text of a
+// message is tokenised as plain text (special-token strings inside user content stay text).
+static std::string render_messages(const Tokenizer& tk, const Json& messages, std::vector<int32_t>& toks) {
     if (messages.kind != Json::Arr) return "'messages' must be an array";
+    auto sp = [&](const std::string& s) { const int id = tk.special_id(s); if (id >= 0) toks.push_back(id); else { auto t = tk.tokenize(s, false); toks.insert(toks.end(), t.begin(), t.end()); } };
+    auto text = [&](const std::string& s) { auto t = tk.tokenize(s, false); toks.insert(toks.end(), t.begin(), t.end()); };
+    if (tk.tpl == Tokenizer::TPL_LLAMA3) sp("<|begin_of_text|>");
+    else if (tk.bos >= 0 && tk.add_bos && tk.tpl == Tokenizer::TPL_MINIMAL) toks.push_back(tk.bos);
     for (const Json& msg : messages.arr) {
         if (msg.kind != Json::Obj) return "each message must be an object";
         const Json* role = msg.get("role"); const Json* content = msg.get("content");
         if (!role || role->kind != Json::Str || !content || content->kind != Json::Str) return "each message needs string 'role' and 'content'";
-        special_or_text("<|" + role->s + "|>");
-        auto t = m.tokenize(content->s, false); toks.insert(toks.end(), t.begin(), t.end());
-        special_or_text("<|end|>");
+        switch (tk.tpl) {
+            case Tokenizer::TPL_LLAMA3: sp("<|start_header_id|>"); text(role->s); sp("<|end_header_id|>"); text("\n\n"); text(content->s); sp("<|eot_id|>"); break;     // (the template trims content; so do we not: verbatim)
+            case Tokenizer::TPL_GRANITE: sp("<|start_of_role|>"); text(role->s); sp("<|end_of_role|>"); text(content->s); sp("<|end_of_text|>"); text("\n"); break;
+            case Tokenizer::TPL_CHATML: sp("<|im_start|>"); text(role->s + "\n" + content->s); sp("<|im_end|>"); text("\n"); break;
+            default: sp("<|" + role->s + "|>"); text(content->s); sp("<|end|>"); break;
+        }
     }
-    special_or_text("<|assistant|>");
+    switch (tk.tpl) {
+        case Tokenizer::TPL_LLAMA3: sp("<|start_header_id|>"); text("assistant"); sp("<|end_header_id|>"); text("\n\n"); break;
+        case Tokenizer::TPL_GRANITE: sp("<|start_of_role|>"); text("assistant"); sp("<|end_of_role|>"); break;
+        case Tokenizer::TPL_CHATML: sp("<|im_start|>"); text("assistant\n"); break;
+        default: sp("<|assistant|>"); break;
+    }
     return "";
+}
+static std::string render_prompt(const Model& m, const Json& messages, std::vector<int32_t>& toks) { return render_messages(m.tok, messages, toks); }
+std::string render_chat(const Tokenizer& tok, const std::string& messages_json, std::vector<int32_t>& toks) {
+    Json doc; JsonParser ps(messages_json);
+    if (!ps.parse(doc)) return "invalid JSON: " + ps.err;
+    return render_messages(tok, doc, toks);
 }
 
 static Json lm_error(const std::string& message, const char* type, const char* param, const char* code) {
@@ -239,7 +233,7 @@ static std::string on_chat_model(const std::string& payload) {          // OnCha
     const int room = engine().max_ctx - (int)toks.size() - 1;
     if (room < 1) return reply(400, lm_error("prompt of " + std::to_string(toks.size()) + " tokens exceeds the context window", "invalid_request_error", "messages", "context_length_exceeded"));
     if (max_tokens <= 0 || max_tokens > room) max_tokens = std::min(room, max_tokens <= 0 ? 512 : max_tokens);
-    s.max_tokens = max_tokens; s.stop_token = -1; { auto it = m->special.find("<|end|>"); if (it != m->special.end()) s.stop_token = it->second; }
+    s.max_tokens = max_tokens; s.stop_token = m->tok.stop_token();
     const Json* ign = doc.get("ignore_eos"); s.ignore_eos = ign && ign->kind == Json::Bool && ign->b;
     // the reference bounds the handler with a 2-minute context (:328); a generation that outlives it is answered the way
     // a cancelled context would be: ok:false with Go's deadline error text.  B200_CHAT_TIMEOUT_MS overrides (tests).

@@ -52,6 +52,9 @@ SYMBOLS = {
     "b200_model_generate": (ci, [vp, vp, ci, ci, C.POINTER(Sampling), vp, C.POINTER(ci), C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "b200_model_eval": (ci, [vp, vp, ci, vp, vp]), "b200_model_n_vocab": (ci, [vp]),
     "b200_tokenize": (ci, [vp, C.c_char_p, sz, vp, ci, C.POINTER(ci)]), "b200_detokenize": (ci, [vp, vp, ci, vp, sz, C.POINTER(sz)]),
+    "b200_gguf_tokenize": (ci, [vp, sz, C.c_char_p, sz, ci, vp, ci, C.POINTER(ci)]),
+    "b200_gguf_detokenize": (ci, [vp, sz, vp, ci, vp, sz, C.POINTER(sz)]),
+    "b200_gguf_render_chat": (ci, [vp, sz, C.c_char_p, sz, vp, ci, C.POINTER(ci)]),
     "b200_worker_run": (ci, [C.c_char_p, C.c_char_p, ci]), "b200_worker_stop": (ci, []),
     "b200_handle": (ci, [C.c_char_p, vp, sz, vp, sz, C.POINTER(sz)]), "b200_set_models_dir": (ci, [C.c_char_p]),
     "b200_sample": (ci, [vp, ci, C.POINTER(Sampling), C.c_uint64, C.POINTER(ci)]),
@@ -187,6 +190,32 @@ class Model:
     def detokenize(self, toks):
         toks = np.ascontiguousarray(toks, dtype=np.int32)
         return _string_call(lambda *a: lib().b200_detokenize(self.h, toks.ctypes.data, len(toks), *a))
+
+
+class GgufTokenizer:
+    """Host-only view of a GGUF's tokenizer and chat template (no GPU): pass the file's bytes (the header suffices)."""
+
+    def __init__(self, gguf_bytes):
+        self.buf = bytes(gguf_bytes)
+
+    def _tokens(self, fn, *args):
+        n = ci(0)
+        _check(fn(self.buf, len(self.buf), *args, None, 0, C.byref(n)))
+        out = np.empty(max(n.value, 1), dtype=np.int32)
+        _check(fn(self.buf, len(self.buf), *args, out.ctypes.data, n.value, C.byref(n)))
+        return out[:n.value]
+
+    def tokenize(self, text, parse_special=False):
+        b = text.encode("utf-8") if isinstance(text, str) else text
+        return self._tokens(lib().b200_gguf_tokenize, b, len(b), int(parse_special))
+
+    def detokenize(self, toks):
+        toks = np.ascontiguousarray(toks, dtype=np.int32)
+        return _string_call(lambda *a: lib().b200_gguf_detokenize(self.buf, len(self.buf), toks.ctypes.data, len(toks), *a))
+
+    def render_chat(self, messages):
+        b = json.dumps(messages).encode()
+        return self._tokens(lib().b200_gguf_render_chat, b, len(b))
 
 
 class Engine:
