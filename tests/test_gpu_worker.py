@@ -59,3 +59,37 @@ def test_64_concurrent_chats_over_nats(golden_dir):
     m.h = None
     lib().b200_shutdown()
     assert launches > 0
+
+
+def test_sync_model_from_bucket_into_hbm(golden_dir):
+    """Config 5's path at test size: a .gguf stored as Object Store chunks -> worker -> pinned host buffers -> HBM -> on-GPU
+    repack; the synced model answers chat requests exactly like the same file loaded from disk; a corrupted digest is refused."""
+    lib().b200_shutdown()
+    eng = b200.Engine(max_ctx=512)
+    path = os.path.join(golden_dir, "tiny-llama.gguf")
+    data = open(path, "rb").read()
+    broker = nats_stub.Broker(chunk=128 * 1024).start()     # nats.go's default object chunk size
+    meta = broker.put_object("llm-models", "acme/tiny-llama/model.gguf", data)
+    broker.put_object("llm-models", "acme/bad/model.gguf", data, corrupt_digest=True)
+    t = threading.Thread(target=lambda: b200.Engine.worker_run(broker.url, None, 4), daemon=True); t.start()
+    for _ in range(300):
+        with broker.lock:
+            if broker.subs.get("lmstudio.sync_model_from_bucket"):
+                break
+        time.sleep(0.01)
+    client = nats_stub.Client(broker.url)
+    r = json.loads(client.request("lmstudio.sync_model_from_bucket", json.dumps({"bucket": "llm-models", "object_name": "acme/tiny-llama/model.gguf"}).encode()))
+    assert r["ok"], r
+    assert r["data"]["local_path"] == "hbm://acme/tiny-llama" and r["data"]["bytes"] == len(data) and r["data"]["chunks"] == meta["chunks"]
+    assert r["data"]["digest"].rstrip("=") == meta["digest"].rstrip("=")
+    ref = eng.load_file("disk/tiny", path)
+    chat = lambda mid: json.loads(client.request("lmstudio.chat_model", json.dumps({"model": mid, "messages": [{"role": "user", "content": "compare me"}], "temperature": 0, "max_tokens": 12, "ignore_eos": True}).encode()))
+    a, b = chat("acme/tiny-llama"), chat("disk/tiny")
+    assert a["ok"] and a["data"]["response"]["choices"] == b["data"]["response"]["choices"]
+    bad = json.loads(client.request("lmstudio.sync_model_from_bucket", json.dumps({"bucket": "llm-models", "object_name": "acme/bad/model.gguf"}).encode()))
+    assert not bad["ok"] and "digest mismatch" in bad["error"]
+    ids = [e["id"] for e in json.loads(client.request("lmstudio.list_models", b""))["data"]["models"]["data"]]
+    assert "acme/tiny-llama" in ids and "acme/bad" not in ids
+    client.close(); b200.Engine.worker_stop(); t.join(timeout=20); broker.stop()
+    ref.close()
+    lib().b200_shutdown()

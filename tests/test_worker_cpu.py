@@ -88,3 +88,26 @@ def test_queue_group_delivers_to_one_member():
         assert c.request("work", b"x", timeout=5) == b"ok"
     assert got["a"] + got["b"] == 20 and got["a"] > 0 and got["b"] > 0
     c.close(); broker.stop()
+
+
+def test_sync_from_bucket_reads_the_object_store(served, golden_dir):
+    """lmstudio.sync_model_from_bucket (README.md:286-318) against the stub's Object Store: validation, a missing object,
+    and — without a GPU — the transfer itself up to the point where HBM is needed (metadata record, chunk consumer and the
+    GGUF header all arrive; the engine then refuses for lack of a device, loudly, as ok:false)."""
+    import os
+    broker, client = served
+    r = json.loads(client.request("lmstudio.sync_model_from_bucket", b"{}"))
+    assert r == {"ok": False, "error": "'bucket' and 'object_name' are required", "data": None}
+    r = json.loads(client.request("lmstudio.sync_model_from_bucket", b"nonsense"))
+    assert not r["ok"] and r["error"].startswith("invalid JSON in SyncModelFromBucket")
+    req = {"bucket": "llm-models", "object_name": "acme/tiny-llama/model.gguf", "publisher": "acme", "model_dir": "tiny-llama"}
+    r = json.loads(client.request("lmstudio.sync_model_from_bucket", json.dumps(req).encode()))
+    assert not r["ok"] and "object not found" in r["error"] and r["data"]["model"] == "acme/tiny-llama"
+    broker.chunk = 100_000
+    broker.put_object("llm-models", req["object_name"], open(os.path.join(golden_dir, "tiny-llama.gguf"), "rb").read())
+    r = json.loads(client.request("lmstudio.sync_model_from_bucket", json.dumps(req).encode()))
+    import torch
+    if not torch.cuda.is_available():
+        assert not r["ok"] and "CUDA" in r["error"], r
+    else:
+        assert r["ok"], r
