@@ -216,6 +216,13 @@ Model::~Model() { release(); }
 // Frees every device allocation and forgets every pointer and "already built" flag derived from them: a request that
 // still holds the model (a queued chat, the scheduler's active sequences) finds committed == false under run_mu and
 // fails with B200_ERR_STATE instead of launching kernels on freed memory.  Caller holds run_mu (or is the destructor).
+void Model::release_staging() {
+    for (auto& sl : stage_live) cudaEventDestroy(sl.freed);
+    stage_live.clear();
+    if (d_stage) { cudaFree(d_stage); d_stage = nullptr; }
+    t_got.clear(); t_ring.clear(); t_order.clear();
+}
+
 void Model::release() {
     if (engine().ready) { cudaSetDevice(engine().device); cudaStreamSynchronize(engine().stream); }
     for (auto& g : step_graph) if (g) { cudaGraphExecDestroy(g); g = nullptr; }
@@ -224,7 +231,7 @@ void Model::release() {
     tp_buf = nullptr; tp_error = nullptr;
     for (void* p : owned) cudaFree(p);
     owned.clear();
-    if (d_raw) { cudaFree(d_raw); d_raw = nullptr; }
+    release_staging();
     committed = false;
     tok_embd = Matrix{}; out_w = Matrix{}; out_norm = nullptr; inv_freq = nullptr; layers.clear();
     d_phases = nullptr; n_phases = 0; d_logits = nullptr; d_ll16 = nullptr; d_ll32 = nullptr;
@@ -232,7 +239,7 @@ void Model::release() {
     pf_H = pf_Y = nullptr; pf_X = pf_Q = pf_ACT = pf_W = nullptr; pf_toks = nullptr; pf_T = nullptr;
     bt_logits = nullptr; bt_next = nullptr; bt_samp = nullptr; b_out = nullptr;
     bf16_ready = bf16_tried = tile_ready = false;
-    hbm_bytes = 0; weight_bytes = 0; uploaded = 0;
+    hbm_bytes = 0; weight_bytes = 0; uploaded = 0; t_done.clear(); rope_ff.clear();
 }
 
 template <typename T>
@@ -266,119 +273,176 @@ int Model::open(const std::string& id_, const uint8_t* head, size_t n) {
     build_tokenizer();
     Engine& E = engine();
     if (int rc = E.ensure()) return rc;
-    cudaError_t e = cudaMalloc((void**)&d_raw, meta.data_bytes ? meta.data_bytes : 16);
+    // tensor parallelism: this rank keeps heads / FFN columns / vocabulary rows divided by the world size (tp_shard_window)
+    const int W = E.tp_world;
+    tp = W > 1; g_head = n_head; g_head_kv = n_head_kv; g_ff = n_ff;
+    if (tp) {
+        if (n_head_kv % W || n_head % W || n_ff % (256 * W) || (n_head * head_dim / W) % 256 || n_vocab % (2 * W))
+            return fail(B200_ERR_UNSUPPORTED, "model dimensions do not divide over " + std::to_string(W) + " tensor-parallel ranks");
+        n_head /= W; n_head_kv /= W; n_ff /= W; n_vocab_l = n_vocab / W;
+    } else n_vocab_l = n_vocab;
+    layers.assign(n_layer, Layer{});
+    // ---- staging: uploads land in a ring in HBM, tensor by tensor in file order; a tensor is repacked into its final layout
+    // as soon as its last byte has arrived and its ring space is reused once that repack has run (K9 "behind the H2D
+    // stream").  Peak HBM during a load = the resident weights + the ring (at least two of the largest tensor).
+    t_order.resize(meta.tensors.size());
+    for (size_t i = 0; i < t_order.size(); i++) t_order[i] = (int)i;
+    std::sort(t_order.begin(), t_order.end(), [&](int x, int y) { return meta.tensors[x].offset < meta.tensors[y].offset; });
+    uint64_t biggest = 0; for (auto& t : meta.tensors) biggest = std::max(biggest, t.nbytes);
+    stage_bytes = std::min<uint64_t>(std::max<uint64_t>(2 * ((biggest + 255) & ~255ull) + 512, 1ull << 30), ((meta.data_bytes + 255) & ~255ull) + 512);
+    if (const char* sb = getenv("B200_STAGE_MB")) stage_bytes = std::max<uint64_t>(2 * ((biggest + 255) & ~255ull) + 512, (uint64_t)atoll(sb) << 20);
+    t_got.assign(meta.tensors.size(), 0); t_ring.assign(meta.tensors.size(), ~0ull); t_cursor = 0; stage_head = 0; next_off = 0;
+    cudaError_t e = cudaMalloc((void**)&d_stage, stage_bytes);
     if (e != cudaSuccess) return fail(B200_ERR_NOMEM, std::string("staging cudaMalloc: ") + cudaGetErrorString(e));
     return B200_OK;
 }
 
-int Model::upload(uint64_t file_off, const void* bytes, size_t n) {
-    if (committed || !d_raw) return fail(B200_ERR_STATE, "upload after commit");
+// ring space for one tensor (contiguous: the repack reads rows with a stride); blocks until earlier tenants were repacked
+int Model::stage_alloc(uint64_t nbytes, uint64_t* off) {
+    const uint64_t need = (nbytes + 255) & ~255ull;
+    if (need > stage_bytes) return fail(B200_ERR_NOMEM, "tensor larger than the staging ring");
+    if (stage_head + need > stage_bytes) stage_head = 0;
+    const uint64_t b0 = stage_head, b1 = stage_head + need;
+    while (!stage_live.empty() && stage_live.front().begin < b1 && b0 < stage_live.front().end) {
+        StageSlot& f = stage_live.front();
+        if (!f.recorded) return fail(B200_ERR_STATE, "staging ring too small for the tensors in flight");
+        CK(cudaEventSynchronize(f.freed)); cudaEventDestroy(f.freed); stage_live.pop_front();
+    }
+    *off = b0; stage_head = b1;
+    return B200_OK;
+}
+
+// Bytes [file_off, file_off + n) of the .gguf file.  Uploads must arrive in file order (a chunked Object Store read, a
+// sequential file read).  The copy is queued on the copy stream; `ticket` (optional) receives an event the caller waits on
+// before it reuses `bytes`, which therefore should be pinned memory.
+int Model::upload_async(uint64_t file_off, const void* bytes, size_t n, cudaEvent_t* ticket) {
+    if (committed || !d_stage) return fail(B200_ERR_STATE, "upload after commit");
     Engine& E = engine(); E.ensure();
     uint64_t lo = std::max<uint64_t>(file_off, meta.data_offset), hi = std::min<uint64_t>(file_off + n, meta.data_offset + meta.data_bytes);
-    if (lo >= hi) return B200_OK;                                   // header or padding bytes only
-    CK(cudaMemcpyAsync(d_raw + (lo - meta.data_offset), (const uint8_t*)bytes + (lo - file_off), hi - lo, cudaMemcpyHostToDevice, E.copy_stream));
-    CK(cudaStreamSynchronize(E.copy_stream));                       // caller may reuse its buffer on return
-    uploaded += hi - lo;
+    if (lo < hi) {
+        lo -= meta.data_offset; hi -= meta.data_offset;                          // data-section offsets
+        if (lo > next_off) return fail(B200_ERR_STATE, "uploads must arrive in file order (got data offset " + std::to_string(lo) + ", expected " + std::to_string(next_off) + ")");
+        if (hi > next_off) {
+            lo = std::max(lo, next_off);
+            const uint8_t* src = (const uint8_t*)bytes + (lo + meta.data_offset - file_off);
+            while (t_cursor < t_order.size()) {
+                const int ti = t_order[t_cursor]; const GgufTensor& t = meta.tensors[(size_t)ti];
+                if (hi <= t.offset) break;                                       // only alignment padding before the next tensor
+                const uint64_t a = std::max(lo, t.offset), b = std::min(hi, t.offset + t.nbytes);
+                if (a < b) {
+                    if (t_ring[(size_t)ti] == ~0ull) {
+                        uint64_t off; if (int rc = stage_alloc(t.nbytes, &off)) return rc;
+                        t_ring[(size_t)ti] = off;
+                        StageSlot sl{}; sl.begin = off; sl.end = off + ((t.nbytes + 255) & ~255ull); sl.recorded = false; sl.tensor = ti;
+                        CK(cudaEventCreateWithFlags(&sl.freed, cudaEventDisableTiming)); stage_live.push_back(sl);
+                    }
+                    CK(cudaMemcpyAsync(d_stage + t_ring[(size_t)ti] + (a - t.offset), src + (a - lo), b - a, cudaMemcpyHostToDevice, E.copy_stream));
+                    t_got[(size_t)ti] += b - a; uploaded += b - a;
+                }
+                if (t_got[(size_t)ti] < t.nbytes) break;                        // the rest of this tensor comes with the next upload
+                // complete: repack behind the copy, then release the ring space
+                cudaEvent_t landed; CK(cudaEventCreateWithFlags(&landed, cudaEventDisableTiming));
+                CK(cudaEventRecord(landed, E.copy_stream)); CK(cudaStreamWaitEvent(E.stream, landed, 0)); cudaEventDestroy(landed);
+                if (t.nbytes) { if (int rc = process_tensor(t, d_stage + t_ring[(size_t)ti])) return rc; }
+                for (auto& sl : stage_live) if (sl.tensor == ti) { CK(cudaEventRecord(sl.freed, E.stream)); sl.recorded = true; }
+                t_cursor++;
+            }
+            next_off = std::max(next_off, hi);
+        }
+    }
+    if (ticket) { CK(cudaEventCreateWithFlags(ticket, cudaEventDisableTiming)); CK(cudaEventRecord(*ticket, E.copy_stream)); }
+    return B200_OK;
+}
+int Model::upload(uint64_t file_off, const void* bytes, size_t n) {
+    if (int rc = upload_async(file_off, bytes, n, nullptr)) return rc;
+    CK(cudaStreamSynchronize(engine().copy_stream));                        // caller may reuse its buffer on return
     return B200_OK;
 }
 
-int Model::load_matrix(const std::string& name, int64_t N, int K, Matrix& out) {
-    const GgufTensor* t = meta.tensor(name);
-    if (!t) return fail(B200_ERR_INVALID, "GGUF: missing tensor " + name);
-    if (t->ne[0] != K || t->ne[1] != N) return fail(B200_ERR_INVALID, "GGUF: tensor " + name + " has unexpected shape");
-    if (!is_streamable(t->type)) return fail(B200_ERR_UNSUPPORTED, "tensor " + name + ": ggml type " + std::to_string(t->type) + " is not supported for matrices (Q4_K, Q5_K, Q6_K, Q8_0)");
-    const int64_t Np = N + (N & 1);                                  // odd matrices (vocab) get one zero row
-    out.type = t->type; out.N = Np; out.n_rows = N; out.K = K;
-    if (int rc = own(&out.w, repacked_bytes(t->type, Np, K))) return rc;
-    weight_bytes += t->nbytes;
-    return repack(engine(), d_raw + t->offset, out.w, t->type, Np, N, K);
-}
-
-// Tensor-parallel shard of a matrix: rows [row0, row0+nrows) x K positions [col0, col0+ncols) of the GGUF tensor.
-// Quant blocks run along K, so a row range is a contiguous byte range and a K range (block aligned) a fixed byte window
-// of every row: the repack reads it in place from the uploaded file image.
-int Model::load_slice(const std::string& name, int64_t N_full, int K_full, int64_t row0, int64_t nrows, int col0, int ncols, Matrix& out) {
-    const GgufTensor* t = meta.tensor(name);
-    if (!t) return fail(B200_ERR_INVALID, "GGUF: missing tensor " + name);
-    if (t->ne[0] != K_full || t->ne[1] != N_full) return fail(B200_ERR_INVALID, "GGUF: tensor " + name + " has unexpected shape");
-    if (!is_streamable(t->type)) return fail(B200_ERR_UNSUPPORTED, "tensor " + name + ": unsupported ggml type for matrices");
-    if (col0 % 256 || ncols % 256 || row0 + nrows > N_full || col0 + ncols > K_full) return fail(B200_ERR_UNSUPPORTED, "tensor " + name + ": shard is not aligned to 256-element blocks");
-    const int64_t Np = nrows + (nrows & 1);
-    out.type = t->type; out.N = Np; out.n_rows = nrows; out.K = ncols;
-    if (int rc = own(&out.w, repacked_bytes(t->type, Np, ncols))) return rc;
-    const size_t rrb = raw_row_bytes(t->type, K_full);
-    weight_bytes += (uint64_t)nrows * raw_row_bytes(t->type, ncols);
-    return repack(engine(), d_raw + t->offset + (size_t)row0 * rrb + (size_t)(col0 / block_elems(t->type)) * block_bytes(t->type), out.w, t->type, Np, nrows, ncols, -1, rrb);
-}
-
-int Model::load_vector(const std::string& name, int64_t n, float** out) {
-    const GgufTensor* t = meta.tensor(name);
-    if (!t) return fail(B200_ERR_INVALID, "GGUF: missing tensor " + name);
-    if (t->type != T_F32 || t->n_elems() != n) return fail(B200_ERR_UNSUPPORTED, "tensor " + name + " must be F32[" + std::to_string(n) + "]");
-    if (int rc = own(out, (size_t)n)) return rc;
-    weight_bytes += t->nbytes;
-    CK(cudaMemcpyAsync(*out, d_raw + t->offset, (size_t)n * 4, cudaMemcpyDeviceToDevice, engine().stream));
-    return B200_OK;
+// One complete tensor (device bytes at `src`, ggml row-major blocks) -> its place in the model: this rank's shard of a
+// matrix repacked into the engine layout, a norm vector copied, gate / up interleaved row-wise into one matrix.
+int Model::process_tensor(const GgufTensor& t, const uint8_t* src) {
+    Engine& E = engine(); const int W = E.tp_world, tr = E.tp_rank;
+    const int D = n_embd, F = n_ff;
+    const int64_t gQD = (int64_t)g_head * head_dim, gKVD = (int64_t)g_head_kv * head_dim;
+    auto matrix = [&](const char* kind, int64_t N_full, int K_full, Matrix& out) -> int {      // kind == nullptr: the whole matrix
+        if (t.ne[0] != K_full || t.ne[1] != N_full) return fail(B200_ERR_INVALID, "GGUF: tensor " + t.name + " has unexpected shape");
+        if (!is_streamable(t.type)) return fail(B200_ERR_UNSUPPORTED, "tensor " + t.name + ": ggml type " + std::to_string(t.type) + " is not supported for matrices (Q4_K, Q5_K, Q6_K, Q8_0)");
+        int64_t r0 = 0, nr = N_full; int c0 = 0, nc = K_full;
+        if (kind) { if (int rc = tp_shard_window(kind, N_full, K_full, tr, W, &r0, &nr, &c0, &nc)) return rc; }
+        if (c0 % 256 || nc % 256) return fail(B200_ERR_UNSUPPORTED, "tensor " + t.name + ": shard is not aligned to 256-element blocks");
+        const int64_t Np = nr + (nr & 1);                                    // odd matrices (vocab) get one zero row
+        out.type = t.type; out.N = Np; out.n_rows = nr; out.K = nc;
+        if (int rc = own(&out.w, repacked_bytes(t.type, Np, nc))) return rc;
+        const size_t rrb = raw_row_bytes(t.type, K_full);
+        weight_bytes += (uint64_t)nr * raw_row_bytes(t.type, nc);
+        return repack(E, src + (size_t)r0 * rrb + (size_t)(c0 / block_elems(t.type)) * block_bytes(t.type), out.w, t.type, Np, nr, nc, -1, rrb);
+    };
+    auto vector = [&](int64_t n, float** out) -> int {
+        if (t.type != T_F32 || t.n_elems() != n) return fail(B200_ERR_UNSUPPORTED, "tensor " + t.name + " must be F32[" + std::to_string(n) + "]");
+        if (int rc = own(out, (size_t)n)) return rc;
+        weight_bytes += t.nbytes;
+        CK(cudaMemcpyAsync(*out, src, (size_t)n * 4, cudaMemcpyDeviceToDevice, E.stream));
+        return B200_OK;
+    };
+    int rc = B200_OK;
+    if (t.name == "token_embd.weight") {
+        rc = matrix(nullptr, n_vocab, D, tok_embd);                          // replicated on every rank
+        if (!rc && tp && !meta.tensor("output.weight")) rc = matrix("output", n_vocab, D, out_w);      // tied lm_head: this rank's vocabulary rows
+    } else if (t.name == "output.weight") rc = matrix(tp ? "output" : nullptr, n_vocab, D, out_w);
+    else if (t.name == "output_norm.weight") rc = vector(D, &out_norm);
+    else if (t.name == "rope_freqs.weight") {
+        if (t.type == T_F32 && t.n_elems() == n_rot / 2) { rope_ff.assign((size_t)n_rot / 2, 1.f); CK(cudaMemcpyAsync(rope_ff.data(), src, rope_ff.size() * 4, cudaMemcpyDeviceToHost, E.stream)); CK(cudaStreamSynchronize(E.stream)); }
+    } else if (t.name.compare(0, 4, "blk.") == 0) {
+        const size_t dot = t.name.find('.', 4); if (dot == std::string::npos) return B200_OK;
+        const int l = atoi(t.name.substr(4, dot - 4).c_str()); const std::string what = t.name.substr(dot + 1);
+        if (l < 0 || l >= n_layer) return B200_OK;
+        Layer& L = layers[(size_t)l];
+        if (what == "attn_norm.weight") rc = vector(D, &L.attn_norm);
+        else if (what == "ffn_norm.weight") rc = vector(D, &L.ffn_norm);
+        else if (what == "attn_q.weight") rc = matrix("attn_q", gQD, D, L.wq);                 // column-parallel: by heads
+        else if (what == "attn_k.weight") rc = matrix("attn_k", gKVD, D, L.wk);
+        else if (what == "attn_v.weight") rc = matrix("attn_v", gKVD, D, L.wv);
+        else if (what == "attn_output.weight") rc = matrix("attn_output", D, (int)gQD, L.wo);   // row-parallel: K range
+        else if (what == "ffn_down.weight") rc = matrix("ffn_down", D, g_ff, L.wd);
+        else if (what == "ffn_gate.weight" || what == "ffn_up.weight") {                        // rows interleaved (gate_i, up_i) in one matrix
+            if (t.ne[0] != D || t.ne[1] != g_ff) return fail(B200_ERR_INVALID, "GGUF: " + t.name + " has unexpected shape");
+            if (!is_streamable(t.type)) return fail(B200_ERR_UNSUPPORTED, t.name + ": unsupported ggml type");
+            if (!L.wgu.w) {
+                L.wgu.type = t.type; L.wgu.N = 2 * (int64_t)F; L.wgu.n_rows = 2 * (int64_t)F; L.wgu.K = D;
+                if ((rc = own(&L.wgu.w, repacked_bytes(t.type, 2 * (int64_t)F, D)))) return rc;
+            } else if (L.wgu.type != t.type) return fail(B200_ERR_UNSUPPORTED, "ffn_gate and ffn_up of a layer must share a quant type");
+            const size_t grb = raw_row_bytes(t.type, D);
+            rc = repack(E, src + (size_t)tr * F * grb, L.wgu.w, t.type, F, F, D, what == "ffn_gate.weight" ? 0 : 1);
+            weight_bytes += (uint64_t)F * grb;
+        } else return B200_OK;                                                   // a tensor this engine does not use
+    } else return B200_OK;
+    if (!rc) t_done.insert(t.name);
+    return rc;
 }
 
 int Model::commit() {
     if (committed) return B200_OK;
-    if (uploaded < meta.data_bytes) return fail(B200_ERR_STATE, "commit before all tensor bytes were uploaded (" + std::to_string(uploaded) + " of " + std::to_string(meta.data_bytes) + ")");
+    if (t_cursor < t_order.size()) return fail(B200_ERR_STATE, "commit before all tensor bytes were uploaded (" + std::to_string(uploaded) + " of " + std::to_string(meta.data_bytes) + ")");
     Engine& E = engine(); if (int rc = E.ensure()) return rc;
-    const int W = E.tp_world, tr = E.tp_rank;
-    tp = W > 1;
-    const int gF = n_ff, gQD = n_head * head_dim, gKVD = n_head_kv * head_dim, gV = n_vocab;
-    if (tp) {                                                   // this rank's shard: heads, FFN columns and vocab rows divided by W
-        if (n_head_kv % W || n_head % W || n_ff % (256 * W) || (gQD / W) % 256 || n_vocab % (2 * W))
-            return fail(B200_ERR_UNSUPPORTED, "model dimensions do not divide over " + std::to_string(W) + " tensor-parallel ranks");
-        n_head /= W; n_head_kv /= W; n_ff /= W; n_vocab_l = n_vocab / W;
-    } else n_vocab_l = n_vocab;
     const int D = n_embd, F = n_ff, QD = n_head * head_dim, KVD = n_head_kv * head_dim;
-    layers.resize(n_layer);
-    if (int rc = load_matrix("token_embd.weight", gV, D, tok_embd)) return rc;
-    for (int l = 0; l < n_layer; l++) {
-        Layer& L = layers[l]; std::string p = "blk." + std::to_string(l) + ".";
-        int rc;
-        if ((rc = load_vector(p + "attn_norm.weight", D, &L.attn_norm))) return rc;
-        auto shard = [&](const char* kind, const std::string& name, int64_t N, int K, Matrix& out) -> int {
-            int64_t r0, nr; int c0, nc;
-            if (int rc2 = tp_shard_window(kind, N, K, tr, W, &r0, &nr, &c0, &nc)) return rc2;
-            return load_slice(name, N, K, r0, nr, c0, nc, out);
-        };
-        if ((rc = shard("attn_q", p + "attn_q.weight", gQD, D, L.wq))) return rc;          // column-parallel: by heads
-        if ((rc = shard("attn_k", p + "attn_k.weight", gKVD, D, L.wk))) return rc;
-        if ((rc = shard("attn_v", p + "attn_v.weight", gKVD, D, L.wv))) return rc;
-        if ((rc = shard("attn_output", p + "attn_output.weight", D, gQD, L.wo))) return rc;              // row-parallel: K range
-        if ((rc = load_vector(p + "ffn_norm.weight", D, &L.ffn_norm))) return rc;
-        const GgufTensor *tg = meta.tensor(p + "ffn_gate.weight"), *tu = meta.tensor(p + "ffn_up.weight");
-        if (!tg || !tu) return fail(B200_ERR_INVALID, "GGUF: missing ffn_gate/ffn_up in layer " + std::to_string(l));
-        if (tg->type != tu->type) return fail(B200_ERR_UNSUPPORTED, "ffn_gate and ffn_up of a layer must share a quant type");
-        if (tg->ne[0] != D || tg->ne[1] != gF || tu->ne[0] != D || tu->ne[1] != gF) return fail(B200_ERR_INVALID, "GGUF: ffn_gate/up shape");
-        if (!is_streamable(tg->type)) return fail(B200_ERR_UNSUPPORTED, "ffn_gate: unsupported ggml type");
-        L.wgu.type = tg->type; L.wgu.N = 2 * (int64_t)F; L.wgu.n_rows = 2 * (int64_t)F; L.wgu.K = D;   // rows interleaved (gate_i, up_i)
-        if ((rc = own(&L.wgu.w, repacked_bytes(tg->type, 2 * (int64_t)F, D)))) return rc;
-        const size_t grb = raw_row_bytes(tg->type, D);
-        if ((rc = repack(E, d_raw + tg->offset + (size_t)tr * F * grb, L.wgu.w, tg->type, F, F, D, 0))) return rc;
-        if ((rc = repack(E, d_raw + tu->offset + (size_t)tr * F * grb, L.wgu.w, tu->type, F, F, D, 1))) return rc;
-        weight_bytes += 2 * (uint64_t)F * grb;
-        if ((rc = shard("ffn_down", p + "ffn_down.weight", D, gF, L.wd))) return rc;
+    {   // every tensor the forward pass needs must have arrived
+        std::vector<std::string> need = {"token_embd.weight", "output_norm.weight"};
+        for (int l = 0; l < n_layer; l++) for (const char* w : {"attn_norm.weight", "attn_q.weight", "attn_k.weight", "attn_v.weight", "attn_output.weight", "ffn_norm.weight", "ffn_gate.weight", "ffn_up.weight", "ffn_down.weight"})
+            need.push_back("blk." + std::to_string(l) + "." + w);
+        for (auto& nme : need) if (!t_done.count(nme)) return fail(B200_ERR_INVALID, "GGUF: missing tensor " + nme);
     }
-    if (int rc = load_vector("output_norm.weight", D, &out_norm)) return rc;
-    if (tp) { if (int rc = load_slice(meta.tensor("output.weight") ? "output.weight" : "token_embd.weight", gV, D, (int64_t)tr * n_vocab_l, n_vocab_l, 0, D, out_w)) return rc; }
-    else if (meta.tensor("output.weight")) { if (int rc = load_matrix("output.weight", n_vocab, D, out_w)) return rc; }
-    else out_w = tok_embd;                                                        // tied embeddings
+    if (!out_w.w) out_w = tok_embd;                                              // tied embeddings
 
     // rope frequencies (optional rope_freqs.weight = per-frequency divisors, llama-3.1 style)
     std::vector<float> ff(n_rot / 2, 1.0f);
-    if (const GgufTensor* rf = meta.tensor("rope_freqs.weight")) {
-        if (rf->type == T_F32 && rf->n_elems() == n_rot / 2) { CK(cudaStreamSynchronize(E.stream)); CK(cudaMemcpy(ff.data(), d_raw + rf->offset, ff.size() * 4, cudaMemcpyDeviceToHost)); }
-    }
+    if (rope_ff.size() == ff.size()) ff = rope_ff;
     std::vector<float> inv(n_rot / 2);
     for (int i = 0; i < n_rot / 2; i++) inv[i] = (float)(std::pow((double)rope_base, -2.0 * i / n_rot) / (double)ff[i]);
     if (int rc = own(&inv_freq, inv.size())) return rc;
     CK(cudaMemcpyAsync(inv_freq, inv.data(), inv.size() * 4, cudaMemcpyHostToDevice, E.stream));
     CK(cudaStreamSynchronize(E.stream));
-    cudaFree(d_raw); d_raw = nullptr;
+    release_staging();
 
     // ---- runtime buffers
     int rc;

@@ -11,6 +11,7 @@
 #include <map>
 #include <memory>
 #include <mutex>
+#include <set>
 #include <string>
 #include <thread>
 #include <unordered_map>
@@ -63,7 +64,16 @@ struct Model {
     // tokenizer tables
     Tokenizer tok;
     // upload state
-    uint8_t* d_raw = nullptr; uint64_t uploaded = 0; bool committed = false;
+    uint64_t uploaded = 0; bool committed = false;
+    // staging ring (uploads land here tensor by tensor; see Model::open)
+    struct StageSlot { uint64_t begin, end; cudaEvent_t freed; bool recorded; int tensor; };
+    uint8_t* d_stage = nullptr; uint64_t stage_bytes = 0, stage_head = 0, next_off = 0; std::deque<StageSlot> stage_live;
+    std::vector<int> t_order; std::vector<uint64_t> t_got, t_ring; size_t t_cursor = 0; std::set<std::string> t_done; std::vector<float> rope_ff;
+    int g_head = 0, g_head_kv = 0, g_ff = 0;     // whole-model head / FFN counts (n_head, n_head_kv, n_ff are this rank's)
+    int stage_alloc(uint64_t nbytes, uint64_t* off);
+    int upload_async(uint64_t file_off, const void* bytes, size_t n, cudaEvent_t* ticket);
+    int process_tensor(const GgufTensor& t, const uint8_t* src);
+    void release_staging();
     uint64_t weight_bytes = 0, hbm_bytes = 0;
     std::vector<void*> owned;
     // weights
@@ -92,8 +102,6 @@ struct Model {
     int open(const std::string& id, const uint8_t* head, size_t n);
     int upload(uint64_t file_off, const void* bytes, size_t n);
     int commit();
-    int load_matrix(const std::string& name, int64_t N, int K, Matrix& out);
-    int load_vector(const std::string& name, int64_t n, float** out);
     void fill_params(DecodeParams& P) const;
     int run_steps(int n_steps, const int32_t* forced, int n_forced, bool reset, float* logits_all_dev);
     int generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_sampling* s, int32_t* out, int* n_out, float* ttft_ms, float* decode_ms,
@@ -105,7 +113,6 @@ struct Model {
     int ensure_bf16_weights();
     int ensure_tile_weights();
     int tp_reduce_add(int M, const struct QgSplit& sp);
-    int load_slice(const std::string& name, int64_t N_full, int K_full, int64_t row0, int64_t nrows, int col0, int ncols, Matrix& out);
     bool tp = false; int n_vocab_l = 0; float* pf_T = nullptr;    // tensor-parallel shard: local vocab rows, partial-sum buffer
     // tensor parallelism inside the batch-1 kernel: exchange buffers in peer memory (this rank's allocation + the peers' IPC mappings)
     uint8_t* tp_buf = nullptr; void* tp_peer[8] = {}; size_t tp_rx_bytes = 0; unsigned* tp_error = nullptr;

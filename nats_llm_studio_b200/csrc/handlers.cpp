@@ -11,7 +11,9 @@
 #include <cstdio>
 #include <cstring>
 #include <fstream>
+#include <fcntl.h>
 #include <sys/stat.h>
+#include <unistd.h>
 
 #include "engine.hpp"
 #include "json.hpp"
@@ -103,30 +105,77 @@ static std::string on_list_models() {                                   // onLis
 
 static bool file_exists(const std::string& p) { struct stat st; return stat(p.c_str(), &st) == 0 && S_ISREG(st.st_mode); }
 
+// A .gguf file -> HBM: reader threads fill a ring of pinned buffers (pread), the calling thread hands the buffers to the
+// engine in file order (upload_async: H2D copy queued, tensors repacked on the GPU as they complete) and a buffer is
+// refilled once its copy has finished.  Reading, copying and repacking overlap; the host side was the bound of a
+// single-threaded read -> copy -> wait loop (6 GB/s).
 int load_file_into(const std::string& id, const std::string& path, std::shared_ptr<Model>& out, std::string& log) {
     auto t0 = std::chrono::steady_clock::now();
     if (int rc0 = engine().ensure()) return rc0;                        // no GPU -> fail loudly, nothing else happens
-    FILE* f = fopen(path.c_str(), "rb");
-    if (!f) return fail(B200_ERR_NOT_FOUND, "cannot open " + path);
+    const int fd = ::open(path.c_str(), O_RDONLY);
+    if (fd < 0) return fail(B200_ERR_NOT_FOUND, "cannot open " + path);
+    struct stat st; if (fstat(fd, &st) != 0) { ::close(fd); return fail(B200_ERR_NOT_FOUND, "cannot stat " + path); }
+    const uint64_t fsize = (uint64_t)st.st_size;
     auto m = std::make_shared<Model>();
-    const size_t CH = 32u << 20;
-    uint8_t* pin[2] = {(uint8_t*)b200_pinned_alloc(CH), (uint8_t*)b200_pinned_alloc(CH)};
-    if (!pin[0] || !pin[1]) { fclose(f); b200_pinned_free(pin[0]); b200_pinned_free(pin[1]); return fail(B200_ERR_NOMEM, "pinned staging allocation failed"); }
-    int rc = B200_OK; size_t got = fread(pin[0], 1, CH, f);
-    std::vector<uint8_t> head(pin[0], pin[0] + got);
-    for (;;) {                                                          // header may exceed one chunk (128k-token vocab ~ 5 MB: fits)
-        rc = m->open(id, head.data(), head.size());
-        if (rc != B200_ERR_MORE) break;
-        size_t more = fread(pin[1], 1, CH, f); if (!more) break;
-        head.insert(head.end(), pin[1], pin[1] + more);
+    int rc = B200_OK;
+    {   // header (may exceed one read: a 128k-token vocabulary is ~5 MB)
+        std::vector<uint8_t> head; size_t want = 1u << 20;
+        for (;;) {
+            head.resize((size_t)std::min<uint64_t>(want, fsize));
+            const ssize_t g = pread(fd, head.data(), head.size(), 0);
+            if (g < 0) { ::close(fd); return fail(B200_ERR_INVALID, "read error on " + path); }
+            head.resize((size_t)g);
+            rc = m->open(id, head.data(), head.size());
+            if (rc != B200_ERR_MORE || head.size() >= fsize) break;
+            want *= 4;
+        }
+        if (rc != B200_OK) { ::close(fd); return rc; }
     }
-    if (rc == B200_OK) {
-        rc = m->upload(0, head.data(), head.size());
-        uint64_t off = head.size(); int k = 0;
-        while (rc == B200_OK) { size_t r = fread(pin[k], 1, CH, f); if (!r) break; rc = m->upload(off, pin[k], r); off += r; k ^= 1; }
-        if (rc == B200_OK) rc = m->commit();
+    const size_t CH = 32u << 20; const int NT = std::max(2, std::min(8, (int)std::thread::hardware_concurrency() / 2)), NB = NT + 2;      // a reader does ~3 GB/s out of the page cache
+    const uint64_t n_chunks = (fsize + CH - 1) / CH;
+    struct Buf { uint8_t* p = nullptr; size_t n = 0; int state = 0; uint64_t chunk = 0; cudaEvent_t ticket = nullptr; };   // 0 free, 1 reading, 2 ready, 3 copying
+    std::vector<Buf> bufs((size_t)NB);
+    for (auto& b : bufs) { b.p = (uint8_t*)b200_pinned_alloc(CH); if (!b.p) rc = fail(B200_ERR_NOMEM, "pinned staging allocation failed"); }
+    std::mutex mu; std::condition_variable cv; uint64_t next_read = 0; bool abort_all = false; const int dev = engine().device;
+    auto reader = [&]() {
+        cudaSetDevice(dev);
+        for (;;) {
+            uint64_t c; Buf* b;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                if (abort_all || next_read >= n_chunks) return;
+                c = next_read; b = &bufs[(size_t)(c % NB)];
+                cv.wait(lk, [&] { return abort_all || (next_read == c && (b->state == 0 || b->state == 3)); });   // chunk c's turn, its buffer handed back
+                if (abort_all || next_read != c) continue;
+                next_read++;
+                cudaEvent_t tk = b->state == 3 ? b->ticket : nullptr; b->state = 1; b->ticket = nullptr;
+                lk.unlock(); cv.notify_all();
+                if (tk) { cudaEventSynchronize(tk); cudaEventDestroy(tk); }                              // the copy out of this buffer has finished
+            }
+            const uint64_t off = c * CH; const size_t n = (size_t)std::min<uint64_t>(CH, fsize - off);
+            size_t got = 0; while (got < n) { const ssize_t g = pread(fd, b->p + got, n - got, (off_t)(off + got)); if (g <= 0) break; got += (size_t)g; }
+            { std::lock_guard<std::mutex> lk(mu); b->n = got; b->chunk = c; b->state = got == n ? 2 : -1; }
+            cv.notify_all();
+        }
+    };
+    std::vector<std::thread> th;
+    if (rc == B200_OK) for (int i = 0; i < NT; i++) th.emplace_back(reader);
+    for (uint64_t c = 0; c < n_chunks && rc == B200_OK; c++) {
+        Buf& b = bufs[(size_t)(c % NB)];
+        { std::unique_lock<std::mutex> lk(mu); cv.wait(lk, [&] { return (b.state == 2 || b.state == -1) && b.chunk == c; }); if (b.state == -1) rc = fail(B200_ERR_INVALID, "read error on " + path); }
+        if (rc != B200_OK) break;
+        cudaEvent_t tk = nullptr;
+        rc = m->upload_async(c * CH, b.p, b.n, &tk);
+        { std::lock_guard<std::mutex> lk(mu); b.ticket = tk; b.state = 3; }
+        cv.notify_all();
     }
-    fclose(f); b200_pinned_free(pin[0]); b200_pinned_free(pin[1]);
+    { std::lock_guard<std::mutex> lk(mu); abort_all = true; }
+    cv.notify_all();
+    for (auto& t : th) t.join();
+    ::close(fd);
+    if (rc == B200_OK) rc = m->commit();                                 // waits for the copies and the repacks
+    cudaStreamSynchronize(engine().copy_stream);
+    for (auto& b : bufs) { if (b.ticket) cudaEventDestroy(b.ticket); b200_pinned_free(b.p); }
     if (rc != B200_OK) return rc;
     double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     char buf[256]; snprintf(buf, sizeof buf, "loaded %s: %zu tensors, %llu weight bytes resident in HBM, %.0f ms", id.c_str(), m->meta.tensors.size(), (unsigned long long)m->weight_bytes, ms);
