@@ -223,7 +223,8 @@ def main():
         content = "".join(chr(97 + (i * 7) % 26) for i in range(max(1, a.ctx - 4)))
         req = json.dumps({"model": f"bench/{a.preset}-{a.mix}", "messages": [{"role": "user", "content": content}], "temperature": 0,
                           "max_tokens": K, "ignore_eos": True}).encode()
-        eng.handle("lmstudio.chat_model", json.dumps({"model": f"bench/{a.preset}-{a.mix}", "messages": [{"role": "user", "content": "warm"}], "temperature": 0, "max_tokens": 4, "ignore_eos": True}))
+        # warm-up request of the same shape (a serving worker is warm: prompt-ingestion buffers and weight copies exist)
+        eng.handle("lmstudio.chat_model", json.dumps({"model": f"bench/{a.preset}-{a.mix}", "messages": [{"role": "user", "content": content[::-1]}], "temperature": 0, "max_tokens": 4, "ignore_eos": True}))
         barrier(); t0 = time.perf_counter()
         rep_raw = eng.handle("lmstudio.chat_model", req)
         wall = time.perf_counter() - t0

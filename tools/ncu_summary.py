@@ -20,7 +20,7 @@ for r in rows[1:]:
     v_us = v / 1e3 if unit in ("ns", "nsecond") else v * 1e3 if unit in ("ms", "msecond") else v
     a = agg.setdefault(name, [0, 0.0]); a[0] += 1; a[1] += v_us
 tot = sum(a[1] for a in agg.values())
-out.append(f"# ncu launch list — `python bench.py --steps 8 --warmup 3 --no-cpu --no-e2e` ({rnd})\n")
+out.append(f"# ncu launch list — `python bench.py --steps 8 --warmup 3 --no-cpu --no-e2e --no-batched --no-tp` ({rnd})\n")
 out.append("Per-launch times under ncu are cold-cache and serialised: compare shares, not absolutes.\n")
 out.append("| kernel | launches | total us | share |\n|---|---:|---:|---:|")
 for k, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
