@@ -781,13 +781,32 @@ static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t co
 // C[M x N] (+)= A[M x K] . B[N x K]^T   (A, B bf16 device, C fp32 device)
 static int gemm_bf16(Engine& E, const __nv_bfloat16* A, const __nv_bfloat16* B, float* C, int M, int N, int K, int ldc, int mode, float scale) {
     if (K % GEMM_BK) return fail(B200_ERR_INVALID, "GEMM K must be a multiple of 64");
+    static const bool old_kernel = getenv("B200_GEMM_OLD") != nullptr;
     static bool attr = false;
-    if (!attr) { CK(cudaFuncSetAttribute(gemm_bf16_tcgen05, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM)); attr = true; }
+    if (!attr) {
+        CK(cudaFuncSetAttribute(gemm_bf16_tcgen05, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM));
+        CK(cudaFuncSetAttribute(gemm_bf16_persistent<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PGemm<256>::SMEM));
+        CK(cudaFuncSetAttribute(gemm_bf16_persistent<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PGemm<128>::SMEM));
+        attr = true;
+    }
     CUtensorMap ta, tb;
     if (int rc = make_tmap(&ta, A, (uint64_t)M, (uint64_t)K)) return rc;
-    if (int rc = make_tmap(&tb, B, (uint64_t)N, (uint64_t)K)) return rc;
-    dim3 grid((N + GEMM_BN - 1) / GEMM_BN, (M + GEMM_BM - 1) / GEMM_BM);
-    gemm_bf16_tcgen05<<<grid, GEMM_THREADS, GEMM_SMEM, E.stream>>>(ta, tb, C, M, N, K, ldc, mode, scale);
+    const int m_tiles = (M + GEMM_BM - 1) / GEMM_BM;
+    // 128 x 256 tiles when they still give every SM a tile, else 128 x 128; few rows (a test-sized product): the one-tile-per-CTA kernel
+    const bool wide = (long long)m_tiles * ((N + 255) / 256) >= E.n_sm;
+    if (old_kernel || (long long)m_tiles * ((N + 127) / 128) < E.n_sm / 2) {
+        if (int rc = make_tmap(&tb, B, (uint64_t)N, (uint64_t)K)) return rc;
+        dim3 grid((N + GEMM_BN - 1) / GEMM_BN, (M + GEMM_BM - 1) / GEMM_BM);
+        gemm_bf16_tcgen05<<<grid, GEMM_THREADS, GEMM_SMEM, E.stream>>>(ta, tb, C, M, N, K, ldc, mode, scale);
+    } else if (wide) {
+        if (int rc = make_tmap(&tb, B, (uint64_t)N, (uint64_t)K, 256)) return rc;
+        const int tiles = m_tiles * ((N + 255) / 256);
+        gemm_bf16_persistent<256><<<std::min(tiles, E.n_sm), PG_THREADS, PGemm<256>::SMEM, E.stream>>>(ta, tb, C, M, N, K, ldc, mode, scale);
+    } else {
+        if (int rc = make_tmap(&tb, B, (uint64_t)N, (uint64_t)K, 128)) return rc;
+        const int tiles = m_tiles * ((N + 127) / 128);
+        gemm_bf16_persistent<128><<<std::min(tiles, E.n_sm), PG_THREADS, PGemm<128>::SMEM, E.stream>>>(ta, tb, C, M, N, K, ldc, mode, scale);
+    }
     CK(cudaGetLastError());
     E.launches++;
     return B200_OK;

@@ -151,6 +151,114 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (warp == 0) tcgen05_dealloc(tmem_acc, GEMM_BN);
 }
 
+// ------------------------------------------------------------------------------------ the persistent GEMM
+// Same product as gemm_bf16_tcgen05, organised for throughput: one CTA per SM walks the output tiles (m fastest, so the
+// four row tiles of a 512-row chunk reuse a weight tile out of L2); 128 x BN tiles (BN = 256: the full-width UMMA shape,
+// twice the arithmetic per shared-memory byte of 128 x 128); warp-specialised — one TMA thread, one MMA thread, four
+// epilogue warps — with TWO accumulators in tensor memory, so the epilogue of tile i (tcgen05.ld, scale / residual add,
+// stores) runs while the MMAs of tile i+1 are issued.
+constexpr int PG_THREADS = 192;                              // warp 0: TMA, warp 1: MMA + TMEM owner, warps 2..5: epilogue
+template <int BN> struct PGemm {
+    static constexpr int STAGES = BN == 256 ? 4 : 6;
+    static constexpr uint32_t A_BYTES = GEMM_BM * GEMM_BK * 2, B_BYTES = BN * GEMM_BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr size_t SMEM = (size_t)STAGES * STAGE_BYTES + 1024 + 256;
+};
+template <int BN>
+__global__ void __launch_bounds__(PG_THREADS, 1)
+gemm_bf16_persistent(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, float* __restrict__ C,
+                     int M, int N, int K, int ldc, int mode, float scale) {
+    using G = PGemm<BN>;
+    extern __shared__ uint8_t gemm_smem_raw[];
+    uint8_t* base = (uint8_t*)(((uintptr_t)gemm_smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* sA = base; uint8_t* sB = base + G::STAGES * G::A_BYTES;
+    uint64_t* full = (uint64_t*)(base + (size_t)G::STAGES * G::STAGE_BYTES);
+    uint64_t* empty = full + G::STAGES; uint64_t* acc_full = empty + G::STAGES; uint64_t* acc_empty = acc_full + 2; uint32_t* tmem_slot = (uint32_t*)(acc_empty + 2);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int m_tiles = (M + GEMM_BM - 1) / GEMM_BM, n_tiles = (N + BN - 1) / BN, tiles = m_tiles * n_tiles, nkb = K / GEMM_BK;
+    if (tid == 0) {
+        for (int i = 0; i < G::STAGES; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; i++) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }      // four epilogue warps release an accumulator
+        fence_barrier_init();
+    }
+    if (warp == 1) tcgen05_alloc(tmem_slot, 2 * BN);           // two accumulators of BN fp32 columns
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {                        // ===== TMA producer =====
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+                const int m0 = (t % m_tiles) * GEMM_BM, n0 = (t / m_tiles) * BN;
+                for (int kb = 0; kb < nkb; kb++, it++) {
+                    const int s = it % G::STAGES; const uint32_t ph = (it / G::STAGES) & 1;
+                    mbar_wait(&empty[s], ph ^ 1);
+                    mbar_expect_tx(&full[s], G::STAGE_BYTES);
+                    tma_load_2d(sA + (size_t)s * G::A_BYTES, &tmap_a, kb * GEMM_BK, m0, &full[s]);
+                    tma_load_2d(sB + (size_t)s * G::B_BYTES, &tmap_b, kb * GEMM_BK, n0, &full[s]);
+                }
+            }
+        }
+    } else if (warp == 1) {                 // ===== MMA issuer =====
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN);
+            uint32_t it = 0, tl = 0;
+            for (int t = blockIdx.x; t < tiles; t += gridDim.x, tl++) {
+                const uint32_t a = tl & 1, aph = (tl >> 1) & 1;
+                mbar_wait(&acc_empty[a], aph ^ 1);              // the epilogue has drained this accumulator (first use: passes)
+                tcgen05_fence_after();
+                const uint32_t tacc = tmem_base + a * BN;
+                for (int kb = 0; kb < nkb; kb++, it++) {
+                    const int s = it % G::STAGES; const uint32_t ph = (it / G::STAGES) & 1;
+                    mbar_wait(&full[s], ph);
+                    tcgen05_fence_after();
+                    const uint64_t da = umma_desc_sw128(sA + (size_t)s * G::A_BYTES), db = umma_desc_sw128(sB + (size_t)s * G::B_BYTES);
+#pragma unroll
+                    for (int k = 0; k < GEMM_BK / 16; k++) tcgen05_mma_f16(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                    tcgen05_commit(&empty[s]);
+                }
+                tcgen05_commit(&acc_full[a]);
+            }
+        }
+    } else {                                // ===== epilogue warps: warp w may touch TMEM lanes 32 (w % 4) .. +31 =====
+        const int q = warp & 3;
+        uint32_t tl = 0;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x, tl++) {
+            const int m0 = (t % m_tiles) * GEMM_BM, n0 = (t / m_tiles) * BN;
+            const uint32_t a = tl & 1, aph = (tl >> 1) & 1;
+            mbar_wait(&acc_full[a], aph);
+            __syncwarp();
+            tcgen05_fence_after();
+            const int row = m0 + q * 32 + lane;
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(tmem_base + a * BN + ((uint32_t)(q * 32) << 16) + c, r);
+                if (row < M) {
+                    float* dst = C + (size_t)row * ldc + n0 + c;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        if (n0 + c + j + 3 < N) {
+                            float4 v = make_float4(__uint_as_float(r[j]) * scale, __uint_as_float(r[j + 1]) * scale, __uint_as_float(r[j + 2]) * scale, __uint_as_float(r[j + 3]) * scale);
+                            if (mode == 1) { const float4 o = *(const float4*)(dst + j); v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+                            *(float4*)(dst + j) = v;
+                        } else {
+                            for (int e = 0; e < 4; e++) if (n0 + c + j + e < N) { float v = __uint_as_float(r[j + e]) * scale; if (mode == 1) v += dst[j + e]; dst[j + e] = v; }
+                        }
+                    }
+                }
+            }
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[a]);
+        }
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) tcgen05_dealloc(tmem_base, 2 * BN);
+}
+
 // which sequence slot and position each activation row belongs to: a prompt chunk (pos0 + m, one slot) or a
 // decode batch (one row per sequence, explicit arrays)
 struct RowMap {

@@ -21,7 +21,10 @@ def _bf16(a):
     return u.view(np.float32)
 
 
-@pytest.mark.parametrize("shape", [(128, 128, 64), (128, 128, 256), (256, 384, 512), (100, 256, 4096), (511, 640, 1024), (1, 128, 64)])
+# the last four shapes have enough tiles for the persistent kernels: 128 x 256 tiles (ragged M and N edges, several tiles per
+# CTA so both accumulators and the ring wrap), 128 x 128 tiles, and the 8B gate/up shape
+@pytest.mark.parametrize("shape", [(128, 128, 64), (128, 128, 256), (256, 384, 512), (100, 256, 4096), (511, 640, 1024), (1, 128, 64),
+                                   (511, 19000, 192), (300, 12800, 128), (250, 4104, 320), (512, 28672, 4096)])
 def test_gemm_tcgen05_matches_numpy(engine, shape):
     M, N, K = shape
     rng = np.random.default_rng(M * 7 + N * 3 + K)
