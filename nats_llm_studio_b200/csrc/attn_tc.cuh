@@ -1,0 +1,191 @@
+// attn_tc.cuh — K7: causal prompt attention on the 5th-generation tensor cores (flash-style), for the rows of ONE
+// sequence's prompt chunk (positions pos0 .. pos0 + n_rows - 1 of sequence slot `slot`) over the paged fp16 KV cache.
+// Part of what LM Studio's /api/v0/chat/completions does behind /root/reference/nats_llm_studio.go:158-179.
+//
+// One CTA per (128-row query tile, head), 128 threads.  Per 128-position KV tile:
+//   S = Q . K^T        tcgen05.mma kind::f16, Q and K tiles staged by TMA (K-major, 128-byte swizzle), S in tensor memory
+//   softmax            thread r owns query row r (= TMEM lane r): tcgen05.ld of its 128 scores, running max / sum, the
+//                      probabilities go BACK to tensor memory as fp16 (tcgen05.st) — P never touches shared memory
+//   O += P . V         tcgen05.mma with A = P from tensor memory and B = the V tile exactly as it lies in the cache
+//                      ([position][head_dim], i.e. MN-major for this product: no transpose pass); O in tensor memory,
+//                      rescaled in place when the running max moves.
+// K and V tiles are double-buffered: the TMA loads of tile j+1 are in flight during tile j's two MMAs and softmax.
+// KV pages are 16 positions: a tile is 8 (page, 16-row) boxes per 64-column panel, addressed through the block table.
+#pragma once
+#include "prefill.cuh"
+#include "qgemm.cuh"
+
+namespace b200 {
+
+constexpr int FA_BM = 128, FA_BN = 128, FA_THREADS = 128;
+template <int HD> struct FaCfg {
+    static constexpr int PANELS = HD / 64;                          // 64-column (128-byte) swizzle panels per row
+    static constexpr uint32_t TILE_BYTES = FA_BN * HD * 2;          // one Q / K / V tile
+    static constexpr size_t SMEM = 5 * (size_t)TILE_BYTES + 1024 + 128;       // Q + 2 x (K, V)
+    static constexpr uint32_t TM_S = 0, TM_O = 128, TM_P = 128 + HD, TM_COLS = 512;
+};
+// instruction descriptor, fp16 x fp16 -> fp32; b_mn: B operand is MN-major (V: head_dim contiguous, positions are K)
+__host__ __device__ constexpr uint32_t fa_idesc(int M, int N, bool b_mn) {
+    return (1u << 4) | (0u << 7) | (0u << 10) | ((b_mn ? 1u : 0u) << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+// MN-major operand tile [64-element panels along MN][rows along K of 128 bytes], 128-byte swizzle: 8-row groups 1024 B apart
+// (stride byte offset), panels `panel_bytes` apart (leading byte offset)
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(const void* smem, uint32_t panel_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_u32(smem) & 0x3FFFF) >> 4);
+    d |= (uint64_t)((panel_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+__device__ __forceinline__ void tmem_ld_x32(uint32_t taddr, uint32_t* r) { tmem_ld_32x32b_x32_nowait(taddr, r); asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+template <int HD>
+__global__ void __launch_bounds__(FA_THREADS, 1)
+attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv, int row0, int n_rows, int pos0, int slot, int layer,
+                       int n_head, int n_head_kv, float kq_scale, KvLayout kv, __nv_bfloat16* __restrict__ O) {
+    using C = FaCfg<HD>;
+    extern __shared__ uint8_t fa_smem_raw[];
+    uint8_t* base = (uint8_t*)(((uintptr_t)fa_smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* sQ = base; uint8_t* sK = base + C::TILE_BYTES; uint8_t* sV = sK + 2 * C::TILE_BYTES;
+    uint64_t* bars = (uint64_t*)(base + 5 * (size_t)C::TILE_BYTES);
+    uint64_t *q_full = bars, *k_full = bars + 1 /*[2]*/, *v_full = bars + 3 /*[2]*/, *s_done = bars + 5, *o_done = bars + 6; uint32_t* tmem_slot = (uint32_t*)(bars + 8);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int qt = blockIdx.x, head = blockIdx.y, kvh = head / (n_head / n_head_kv);
+    const int r_lo = qt * FA_BM, rows_here = min(FA_BM, n_rows - r_lo);
+    const int last_pos = pos0 + r_lo + rows_here - 1;                 // newest position any row of this tile may see
+    const int n_kv_tiles = last_pos / FA_BN + 1;
+    if (tid == 0) { for (int i = 0; i < 7; i++) mbar_init(&bars[i], 1); fence_barrier_init(); }
+    if (warp == 0) tcgen05_alloc(tmem_slot, C::TM_COLS);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    pdl_launch_dependents(); pdl_wait();
+
+    // one KV tile: 8 pages x PANELS boxes of (64 columns x 16 positions) for K, the same for V
+    auto load_kv = [&](int j, int buf) {
+        mbar_expect_tx(&k_full[buf], C::TILE_BYTES); mbar_expect_tx(&v_full[buf], C::TILE_BYTES);
+        for (int pg = 0; pg < FA_BN / 16; pg++) {
+            const int p = min(j * FA_BN + pg * 16, last_pos);       // pages beyond the last position: re-read a valid page (masked below)
+            const int page = kv.block_table[(size_t)slot * kv.pages_per_seq + (p >> 4)];
+            const int rk = (int)(((((size_t)layer * kv.n_pages + page) * 2 + 0) * kv.n_head_kv + kvh) * 16), rv = rk + kv.n_head_kv * 16;
+            for (int pn = 0; pn < C::PANELS; pn++) {
+                tma_load_2d(sK + (size_t)buf * C::TILE_BYTES + (size_t)pn * (FA_BN * 128) + (size_t)pg * 2048, &tmap_kv, pn * 64, rk, &k_full[buf]);
+                tma_load_2d(sV + (size_t)buf * C::TILE_BYTES + (size_t)pn * (FA_BN * 128) + (size_t)pg * 2048, &tmap_kv, pn * 64, rv, &v_full[buf]);
+            }
+        }
+    };
+    if (tid == 0) {
+        mbar_expect_tx(q_full, C::TILE_BYTES);
+        for (int pn = 0; pn < C::PANELS; pn++) tma_load_2d(sQ + (size_t)pn * (FA_BM * 128), &tmap_q, head * HD + pn * 64, row0 + r_lo, q_full);
+        load_kv(0, 0);
+    }
+    const int my_pos = pos0 + r_lo + tid;                             // position of this thread's query row
+    const float sl2 = kq_scale * 1.4426950408889634f;                 // scores are kept in log2 units: exp2f((s - m) * sl2)
+    float m_run = -INFINITY, l_run = 0.f;
+    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;            // this warp's quarter of the TMEM lanes
+    for (int j = 0; j < n_kv_tiles; j++) {
+        const int buf = j & 1; const uint32_t ph = (j >> 1) & 1;
+        if (tid == 0) {
+            if (j + 1 < n_kv_tiles) {                                  // the other buffer's previous tenant is tile j-1: its P.V must have read V
+                if (j > 0) mbar_wait(o_done, (j - 1) & 1);
+                load_kv(j + 1, buf ^ 1);
+            }
+            if (j == 0) mbar_wait(q_full, 0);
+            mbar_wait(&k_full[buf], ph);
+            tcgen05_fence_after();
+            constexpr uint32_t idesc = fa_idesc(FA_BM, FA_BN, false);
+#pragma unroll
+            for (int k = 0; k < HD / 16; k++) {                        // S = Q . K^T: 16 head-dim columns per instruction
+                const uint64_t da = umma_desc_sw128(sQ + (size_t)(k / 4) * (FA_BM * 128)) + 2 * (k % 4);
+                const uint64_t db = umma_desc_sw128(sK + (size_t)buf * C::TILE_BYTES + (size_t)(k / 4) * (FA_BN * 128)) + 2 * (k % 4);
+                tcgen05_mma_f16(tmem + C::TM_S, da, db, idesc, k ? 1u : 0u);
+            }
+            tcgen05_commit(s_done);
+        }
+        // ---- softmax of this thread's row
+        mbar_wait(s_done, j & 1);
+        __syncwarp();
+        tcgen05_fence_after();
+        // two passes over the row's 128 scores, 32 at a time (registers): the maximum, then the probabilities
+        const int kv0 = j * FA_BN;
+        float m_new = m_run;
+#pragma unroll 1
+        for (int c = 0; c < FA_BN; c += 32) {
+            uint32_t sc[32]; tmem_ld_x32(tmem + C::TM_S + lane_off + c, sc);
+#pragma unroll
+            for (int i = 0; i < 32; i++) if (kv0 + c + i <= my_pos) m_new = fmaxf(m_new, __uint_as_float(sc[i]));      // causal mask (also covers positions past the end)
+        }
+        // rows beyond n_rows (tile padding) see garbage queries: harmless, never stored.  Every real row sees position 0.
+        const float corr = m_run == -INFINITY ? 0.f : exp2f((m_run - m_new) * sl2);
+        // the previous tile's P.V must have finished before P is overwritten and O rescaled
+        if (j > 0) { mbar_wait(o_done, (j - 1) & 1); tcgen05_fence_after(); }
+        float l_add = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < FA_BN; c += 32) {
+            uint32_t sc[32], pk[16]; tmem_ld_x32(tmem + C::TM_S + lane_off + c, sc);
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+                const float p0 = kv0 + c + i <= my_pos ? exp2f((__uint_as_float(sc[i]) - m_new) * sl2) : 0.f;
+                const float p1 = kv0 + c + i + 1 <= my_pos ? exp2f((__uint_as_float(sc[i + 1]) - m_new) * sl2) : 0.f;
+                const __half2 h = __floats2half2_rn(p0, p1);
+                const float2 back = __half22float2(h); l_add += back.x + back.y;      // the sum uses the rounded values the MMA will see
+                pk[i / 2] = *(const uint32_t*)&h;
+            }
+            tmem_st_x8(tmem + C::TM_P + lane_off + c / 2, pk); tmem_st_x8(tmem + C::TM_P + lane_off + c / 2 + 8, pk + 8);
+        }
+        l_run = l_run * corr + l_add; m_run = m_new;
+        if (j > 0) {                                                   // O *= corr, in place
+#pragma unroll 1
+            for (int c = 0; c < HD; c += 32) {
+                uint32_t o[32]; tmem_ld_x32(tmem + C::TM_O + lane_off + c, o);
+#pragma unroll
+                for (int i = 0; i < 32; i++) o[i] = __float_as_uint(__uint_as_float(o[i]) * corr);
+                tmem_st_x32(tmem + C::TM_O + lane_off + c, o);
+            }
+        }
+        tmem_st_wait();
+        tcgen05_fence_before();
+        __syncthreads();
+        if (tid == 0) {
+            tcgen05_fence_after();
+            mbar_wait(&v_full[buf], ph);
+            tcgen05_fence_after();
+            constexpr uint32_t idesc = fa_idesc(FA_BM, HD, true);
+#pragma unroll
+            for (int k = 0; k < FA_BN / 16; k++) {                     // O += P . V: 16 positions per instruction
+                const uint64_t db = umma_desc_mn_sw128(sV + (size_t)buf * C::TILE_BYTES + (size_t)k * 2048, FA_BN * 128);
+                tcgen05_mma_f16_ts(tmem + C::TM_O, tmem + C::TM_P + k * 8, db, idesc, (j | k) ? 1u : 0u);
+            }
+            tcgen05_commit(o_done);
+        }
+    }
+    // ---- epilogue: O / l -> bf16 row of the output [row][head * HD + d]
+    mbar_wait(o_done, (n_kv_tiles - 1) & 1);
+    __syncwarp();
+    tcgen05_fence_after();
+    const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+    const int row = row0 + r_lo + tid;
+#pragma unroll 1
+    for (int c = 0; c < HD; c += 32) {
+        uint32_t o[32]; tmem_ld_x32(tmem + C::TM_O + lane_off + c, o);
+        if (tid < rows_here) {
+            __nv_bfloat16* dst = O + (size_t)row * n_head * HD + head * HD + c;
+#pragma unroll
+            for (int i = 0; i < 32; i += 8) {
+                uint4 w;
+                __nv_bfloat162 t0 = __floats2bfloat162_rn(__uint_as_float(o[i]) * inv, __uint_as_float(o[i + 1]) * inv), t1 = __floats2bfloat162_rn(__uint_as_float(o[i + 2]) * inv, __uint_as_float(o[i + 3]) * inv);
+                __nv_bfloat162 t2 = __floats2bfloat162_rn(__uint_as_float(o[i + 4]) * inv, __uint_as_float(o[i + 5]) * inv), t3 = __floats2bfloat162_rn(__uint_as_float(o[i + 6]) * inv, __uint_as_float(o[i + 7]) * inv);
+                w.x = *(uint32_t*)&t0; w.y = *(uint32_t*)&t1; w.z = *(uint32_t*)&t2; w.w = *(uint32_t*)&t3;
+                *(uint4*)(dst + i) = w;
+            }
+        }
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 0) tcgen05_dealloc(tmem, C::TM_COLS);
+}
+
+}  // namespace b200

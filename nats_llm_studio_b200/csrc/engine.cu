@@ -14,6 +14,7 @@
 #include "decode.cuh"
 #include "prefill.cuh"
 #include "qgemm.cuh"
+#include "attn_tc.cuh"
 #include "sampler.cuh"
 
 namespace b200 {
@@ -237,7 +238,7 @@ void Model::release() {
     d_phases = nullptr; n_phases = 0; d_logits = nullptr; d_ll16 = nullptr; d_ll32 = nullptr;
     d_state = d_out_tokens = d_forced = d_block_table = nullptr; d_kv = nullptr; n_pages = 0; cur_pos = 0;
     pf_H = pf_Y = nullptr; pf_X = pf_Q = pf_ACT = pf_W = nullptr; pf_toks = nullptr; pf_T = nullptr;
-    bt_logits = nullptr; bt_next = nullptr; bt_samp = nullptr; b_out = nullptr;
+    bt_logits = nullptr; bt_next = nullptr; bt_samp = nullptr; b_out = nullptr; tmap_q = tmap_kv = nullptr;
     bf16_ready = bf16_tried = tile_ready = false;
     hbm_bytes = 0; weight_bytes = 0; uploaded = 0; t_done.clear(); rope_ff.clear();
 }
@@ -945,7 +946,7 @@ int Model::tp_reduce_add(int M, const QgSplit& sp) {
 
 // One pass of the dense path over M activation rows (a prompt chunk of one sequence, or one row per sequence of a
 // decode batch).  want_logits: also run the last layer's FFN, the final norm and the lm_head into bt_logits[M][V].
-int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits, bool q) {
+int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits, bool q, const std::vector<RowRun>* runs) {
     Engine& E = engine();
     const int D = n_embd, F = n_ff, QD = n_head * head_dim, KVD = n_head_kv * head_dim, W3 = QD + 2 * KVD;
     const float rs = res_scale != 0.f ? res_scale : 1.f, kq = attn_scale != 0.f ? attn_scale : 1.0f / std::sqrt((float)head_dim);
@@ -973,8 +974,20 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
             if (!bf16_ready) { deq(L.wq, pf_W); deq(L.wk, pf_W + (size_t)QD * D); deq(L.wv, pf_W + (size_t)(QD + KVD) * D); wqkv = pf_W; }
             if ((rc = gemm_bf16(E, pf_X, wqkv, pf_Y, M, W3, D, W3, 0, 1.f))) return rc;
         }
-        CK(launch_pdl(rope_kv_rows_kernel, dim3(nblk((long long)M * W3 / 2)), dim3(256), 0, E.stream, (const float*)pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, (const float*)inv_freq, kv, pf_Q, sp)); E.launches++; sp = none;
-        {
+        // prompt chunks made of whole runs of one sequence each: causal attention on the tensor cores (attn_tc.cuh)
+        const bool tc_off = getenv("B200_NO_ATTN_TC") != nullptr;       // read per call: tests compare the two attention kernels in one process
+        const bool tc = !q && runs && !runs->empty() && !tc_off && M >= 32;
+        CK(launch_pdl(rope_kv_rows_kernel, dim3(nblk((long long)M * W3 / 2)), dim3(256), 0, E.stream, (const float*)pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, (const float*)inv_freq, kv, pf_Q, sp, tc)); E.launches++; sp = none;
+        if (tc) {
+            if (int rc2 = ensure_attn_maps()) return rc2;
+            for (const RowRun& r : *runs) {
+                const dim3 g((r.n + FA_BM - 1) / FA_BM, n_head);
+                if (head_dim == 128) attn_prefill_tc_kernel<128><<<g, FA_THREADS, FaCfg<128>::SMEM, E.stream>>>(*(const CUtensorMap*)tmap_q, *(const CUtensorMap*)tmap_kv, r.row0, r.n, r.pos0, r.slot, l, n_head, n_head_kv, kq, kv, pf_X);
+                else attn_prefill_tc_kernel<64><<<g, FA_THREADS, FaCfg<64>::SMEM, E.stream>>>(*(const CUtensorMap*)tmap_q, *(const CUtensorMap*)tmap_kv, r.row0, r.n, r.pos0, r.slot, l, n_head, n_head_kv, kq, kv, pf_X);
+                E.launches++;
+            }
+            CK(cudaGetLastError());
+        } else {
             const int G = n_head / n_head_kv; const dim3 ag(M * n_head_kv);
 #define B200_ATTN(HD_, G_) CK(launch_pdl(attn_rows_kernel<HD_, G_>, ag, dim3(ATTN_WARPS * 32), 0, E.stream, (const __nv_bfloat16*)pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q))
             if (head_dim == 128 && G == 4) B200_ATTN(128, 4); else if (head_dim == 128 && G == 8) B200_ATTN(128, 8);
@@ -984,8 +997,8 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
             else if (head_dim == 128) attn_prefill_kernel<4><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q);
             else attn_prefill_kernel<2><<<(M * n_head + 3) / 4, 128, 0, E.stream>>>(pf_Q, M, rm, l, n_head, n_head_kv, kq, kv, pf_X, q);
 #undef B200_ATTN
+            E.launches++;
         }
-        E.launches++;
         // residual GEMM: single GPU adds into H (in the epilogue / the next norm's gather); a tensor-parallel shard holds a K
         // slice, so its product is a partial sum: complete it locally, all-reduce it over NVLink, then add it to H
         float* resid = tp ? pf_T : pf_H; const int rmode = tp ? 0 : 1;
@@ -1040,7 +1053,8 @@ int Model::prefill_slot(int slot, const int32_t* toks, int n, int pos0) {
     for (int c0 = 0; c0 < n; c0 += PREFILL_CHUNK) {
         const int M = std::min(PREFILL_CHUNK, n - c0);
         CK(cudaMemcpyAsync(pf_toks, toks + c0, (size_t)M * 4, cudaMemcpyHostToDevice, E.stream));
-        if (int rc = dense_rows(pf_toks, M, nullptr, nullptr, pos0 + c0, slot, false, false)) return rc;
+        const std::vector<RowRun> run{{0, M, pos0 + c0, slot}};
+        if (int rc = dense_rows(pf_toks, M, nullptr, nullptr, pos0 + c0, slot, false, false, &run)) return rc;
     }
     CK(cudaStreamSynchronize(E.stream));                              // toks is caller memory
     return B200_OK;
@@ -1059,8 +1073,41 @@ int Model::prefill_rows(const int32_t* toks, const int32_t* slots, const int32_t
     CK(cudaMemcpyAsync(pf_toks, toks, (size_t)M * 4, cudaMemcpyHostToDevice, E.stream));
     CK(cudaMemcpyAsync(pf_toks + Mc, pos, (size_t)M * 4, cudaMemcpyHostToDevice, E.stream));
     CK(cudaMemcpyAsync(pf_toks + 2 * Mc, slots, (size_t)M * 4, cudaMemcpyHostToDevice, E.stream));
-    if (int rc = dense_rows(pf_toks, M, pf_toks + Mc, pf_toks + 2 * Mc, 0, 0, false, false)) return rc;
+    std::vector<RowRun> runs;                                          // maximal runs of consecutive positions of one sequence
+    for (int i = 0; i < M; i++) {
+        if (!runs.empty() && runs.back().slot == slots[i] && runs.back().pos0 + runs.back().n == pos[i]) runs.back().n++;
+        else runs.push_back(RowRun{i, 1, pos[i], slots[i]});
+    }
+    if (int rc = dense_rows(pf_toks, M, pf_toks + Mc, pf_toks + 2 * Mc, 0, 0, false, false, &runs)) return rc;
     CK(cudaStreamSynchronize(E.stream));
+    return B200_OK;
+}
+
+// tensor maps of the tensor-core prompt attention: the query buffer (fp16 view of pf_Q) and the whole paged KV cache as
+// one 2-D fp16 tensor [(layer, page, K|V, kv head, position-in-page)][head_dim], boxes of one page x 64 columns
+int Model::ensure_attn_maps() {
+    if (tmap_q) return B200_OK;
+    EncodeTiledFn f = encode_tiled();
+    if (!f) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    static_assert(sizeof(CUtensorMap) == 128, "tensor map size");
+    tmap_storage.assign(2 * sizeof(CUtensorMap) + 64, 0);
+    uint8_t* al = (uint8_t*)(((uintptr_t)tmap_storage.data() + 63) & ~(uintptr_t)63);
+    CUtensorMap* mq = (CUtensorMap*)al; CUtensorMap* mkv = mq + 1;
+    const uint64_t QD = (uint64_t)n_head * head_dim;
+    {
+        cuuint64_t dims[2] = {QD, (cuuint64_t)PREFILL_CHUNK}, strides[1] = {QD * 2}; cuuint32_t box[2] = {64, (cuuint32_t)FA_BM}, estr[2] = {1, 1};
+        CUresult r = f(mq, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, pf_Q, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled (Q) failed: " + std::to_string((int)r));
+    }
+    {
+        const uint64_t rows = (uint64_t)n_layer * n_pages * 2 * n_head_kv * 16;
+        cuuint64_t dims[2] = {(cuuint64_t)head_dim, rows}, strides[1] = {(cuuint64_t)head_dim * 2}; cuuint32_t box[2] = {64, 16}, estr[2] = {1, 1};
+        CUresult r = f(mkv, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, d_kv, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled (KV) failed: " + std::to_string((int)r));
+    }
+    CK(cudaFuncSetAttribute(attn_prefill_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FaCfg<128>::SMEM));
+    CK(cudaFuncSetAttribute(attn_prefill_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FaCfg<64>::SMEM));
+    tmap_q = mq; tmap_kv = mkv;
     return B200_OK;
 }
 

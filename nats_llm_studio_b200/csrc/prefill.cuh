@@ -437,7 +437,7 @@ __global__ void __launch_bounds__(1024) rmsnorm_rows_kernel(float* __restrict__ 
 
 // QKV[m][QD + 2*KVD] fp32 -> RoPE(q) as bf16 Q[m][QD]; RoPE(k), v -> fp16 KV pages at position pos0 + m
 __global__ void rope_kv_rows_kernel(const float* __restrict__ QKV, int M, RowMap rm, int layer, int n_head, int n_head_kv, int HD, int n_rot,
-                                    const float* __restrict__ inv_freq, KvLayout kv, __nv_bfloat16* __restrict__ Q, const __grid_constant__ QgSplit sp) {
+                                    const float* __restrict__ inv_freq, KvLayout kv, __nv_bfloat16* __restrict__ Q, const __grid_constant__ QgSplit sp, bool q_f16) {
     pdl_launch_dependents(); pdl_wait();
     const int QD = n_head * HD, KVD = n_head_kv * HD, W = QD + 2 * KVD;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)M * (W / 2); i += (long long)gridDim.x * blockDim.x) {
@@ -448,7 +448,7 @@ __global__ void rope_kv_rows_kernel(const float* __restrict__ QKV, int M, RowMap
             const int d = c % HD;
             if (d < n_rot) { float sn, cs; sincosf((float)pos * inv_freq[d >> 1], &sn, &cs); const float x = a, y = b; a = x * cs - y * sn; b = x * sn + y * cs; }
         }
-        if (c < QD) *(__nv_bfloat162*)(Q + (size_t)m * QD + c) = __floats2bfloat162_rn(a, b);
+        if (c < QD) { if (q_f16) *(__half2*)((__half*)Q + (size_t)m * QD + c) = __floats2half2_rn(a, b); else *(__nv_bfloat162*)(Q + (size_t)m * QD + c) = __floats2bfloat162_rn(a, b); }      // fp16 for the tensor-core prompt attention (same type as the KV cache)
         else if (c < QD + KVD) { const int r = c - QD; *(__half2*)(kv.at_slot(slot, layer, 0, r / HD, pos) + r % HD) = __floats2half2_rn(a, b); }
         else { const int r = c - QD - KVD; *(__half2*)(kv.at_slot(slot, layer, 1, r / HD, pos) + r % HD) = __floats2half2_rn(a, b); }
     }
