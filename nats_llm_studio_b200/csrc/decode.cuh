@@ -18,6 +18,19 @@
 
 namespace b200 {
 
+// Per-warp cycle trace of one CTA (build variant -DB200_WTRACE, tools/wtrace_report.py): clock64 stamps per (step, phase, warp):
+// 0 phase start, 1 own first poll done, 2 past the first prologue barrier, 3 own quantisation done, 4 prologue done,
+// 5 first stage available, 6 stream loop done, 7 phase end.
+#ifdef B200_WTRACE
+__device__ long long* g_wtrace; __device__ int g_wtrace_cta;
+__shared__ long long* s_wt[16];
+#define WT(k) do { if ((threadIdx.x & 31) == 0) { long long* w_ = s_wt[threadIdx.x >> 5]; if (w_) w_[k] = clock64(); } } while (0)
+#define WT_ONCE(k) do { if ((threadIdx.x & 31) == 0) { long long* w_ = s_wt[threadIdx.x >> 5]; if (w_ && !w_[k]) w_[k] = clock64(); } } while (0)
+#else
+#define WT(k) do {} while (0)
+#define WT_ONCE(k) do {} while (0)
+#endif
+
 __device__ __forceinline__ long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return (long long)t; }
 
 // ------------------------------------------------------------------------------------ tagged words
@@ -134,6 +147,7 @@ __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int 
     {   // q of this head: LL32, tag of the QKV phase
         float t[VEC];
         ll32_poll<VEC>(P.q_ll + head * HD + lane * VEC, seq_in, t);
+        __syncwarp();                                                  // lanes leave the poll at different times; shuffles follow
 #pragma unroll
         for (int i = 0; i < VEC; i++) { qv[i] = t[i] * P.kq_scale; acc[i] = 0.f; }
     }
@@ -290,6 +304,7 @@ __device__ __forceinline__ void tp_allreduce_pair(const DecodeParams& P, int whi
             if (++spins > TP_SPIN_BUDGET) { *P.tp_error = 1u; break; }
         }
     }
+    __syncwarp();                                                     // lanes leave the poll at different times (and half of them skip it)
     float s0 = 0.f, s1 = 0.f;
     for (int r = 0; r < W; r++) {                                     // rank order, identical everywhere
         const int kk = r - (r > me ? 1 : 0);
@@ -350,7 +365,7 @@ __device__ __forceinline__ void epilogue(const DecodeParams& P, const OpDesc& op
 // Pairs [a, b) of `op`, eight pairs per stage (one per warp of a group).  A warp visits only the stages of its group's
 // row blocks: their sequence numbers follow from the slice's stage order (seg_stage_index), the ring offset of a stage
 // is published by the producer next to its barrier.  seq0: sequence number of the slice's first stage.
-template <int TYPE, bool XHOLD>
+template <int TYPE, bool XHOLD, bool TP>
 __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& op, const Smem& sm, const Smem& sx, uint32_t seq0, int a, int b,
                                           int pos, int warp, int lane, uint32_t seq, float in_scale, ArgBest& best, float* logits_dst, long long* tr) {
     constexpr int GB = TYPE == T_Q4_K ? 1152 : TYPE == T_Q5_K ? 1408 : TYPE == T_Q6_K ? 1680 : 2176;
@@ -376,6 +391,7 @@ __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& o
             long long w0 = 0; if (tr && warp == 0 && lane == 0) w0 = clock64();
             mbar_wait(&sm.full[slot], (sq / NSLOT) & 1);
             if (tr && warp == 0 && lane == 0) { tr[7] += clock64() - w0; if (rbi == 0 && gi == 0) tr[4] = gtime(); }   // tr[7]: cycles warp 0 waited for data
+            WT_ONCE(5);
             if (mine) {
                 const uint8_t* unit = sm.ring + sm.q_off[slot] + wl * cb;
                 if constexpr (XHOLD) {
@@ -394,9 +410,10 @@ __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& o
             if (lane == 0) mbar_arrive(&sm.empty[slot]);
         }
         if (tr && warp == 0 && lane == 0) tr[5] = gtime();
+        WT(6);
         if (mine) {
             acc0 = warp_sum(acc0); acc1 = warp_sum(acc1);
-            if (P.tp_world > 1 && op.epi == EPI_RESID) tp_allreduce_pair(P, op.tp_half, 2 * (rb + wl), seq, lane, acc0, acc1);
+            if constexpr (TP) { if (P.tp_world > 1 && op.epi == EPI_RESID) tp_allreduce_pair(P, op.tp_half, 2 * (rb + wl), seq, lane, acc0, acc1); }
             if (lane == 0) epilogue(P, op, sm, rb + wl, rb + wl - a, acc0 * in_scale, acc1 * in_scale, pos, seq, best, logits_dst);
         }
     }
@@ -404,6 +421,7 @@ __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& o
 
 // ------------------------------------------------------------------------------------ one GEMV phase (consumers)
 // seq: this phase's generation number; inputs carry seq-1's tags.
+template <int CFG>
 __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem& sm, uint32_t& stage_seq, int c, int G,
                               int pos, int tid, uint32_t seq, ArgBest& best, float* logits_dst, long long* tr) {
     const int warp = tid >> 5, lane = tid & 31;
@@ -452,7 +470,9 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
         }
         if (tid == 0) sm.ctrl[0] = 0x7fffffff;                       // inputs have arrived: the producer may run ahead again
         if (tr && tid == 0) tr[1] = tr[2] = gtime();
+        WT(1);
         consumer_sync();                                    // red[] and xq free (previous phase's readers done)
+        WT(2);
         if (tid < n_runs_pad) {
             if (!have) {
 #pragma unroll
@@ -487,7 +507,9 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
         if (second) fetch2(tid, u2, t, t2); else if (first) fetch(tid, t);
         if (tid == 0) sm.ctrl[0] = 0x7fffffff;
         if (tr && tid == 0) tr[1] = tr[2] = gtime();
+        WT(1);
         consumer_sync();                                    // xq free (previous phase's readers done)
+        WT(2);
         if (tid < n_runs_pad) {
             if (!first) {
 #pragma unroll
@@ -511,7 +533,9 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
             quantise_store(u, t);
         }
     }
+    WT(3);
     consumer_sync();
+    WT(4);
     if (ph.pro == PRO_NORM) {
         float tot = 0.f;
 #pragma unroll
@@ -533,14 +557,14 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
         const Smem& sx = (op.type == T_Q6_K) ? s2 : sm;
         // phases with one stage per row block and several row blocks per warp keep the activation slice in registers
         const bool xhold = stage_groups(op.type) == 2 && op.n_grp == 2 && (b - a) > WARP_GROUPS * PAIRS_PER_STAGE;
-#define B200_STREAM(T_) do { if (xhold) stream_op<T_, true>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); \
-                             else stream_op<T_, false>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); } while (0)
-        switch (op.type) {
-            case T_Q4_K: B200_STREAM(T_Q4_K); break;
-            case T_Q6_K: B200_STREAM(T_Q6_K); break;
-            case T_Q8_0: stream_op<T_Q8_0, false>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); break;
-            default: B200_STREAM(T_Q5_K); break;
-        }
+#define B200_STREAM(T_) do { if (xhold) stream_op<T_, true, TP>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); \
+                             else stream_op<T_, false, TP>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); } while (0)
+        constexpr bool TP = (CFG & DK_TP) != 0;
+        // only the weight types the kernel variant was built for (the host picks a variant that covers the file's types)
+        if constexpr ((CFG & DK_Q4K) != 0) { if (op.type == T_Q4_K) B200_STREAM(T_Q4_K); }
+        if constexpr ((CFG & DK_Q6K) != 0) { if (op.type == T_Q6_K) B200_STREAM(T_Q6_K); }
+        if constexpr ((CFG & DK_Q80) != 0) { if (op.type == T_Q8_0) stream_op<T_Q8_0, false, TP>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); }
+        if constexpr ((CFG & DK_Q5K) != 0) { if (op.type == T_Q5_K) B200_STREAM(T_Q5_K); }
 #undef B200_STREAM
         stage_seq += (uint32_t)(((b - a + PAIRS_PER_STAGE - 1) / PAIRS_PER_STAGE) * stages_per_rb(op.type, op.n_grp));
     }
@@ -552,8 +576,12 @@ struct DecodeRun {
     float* logits_all;                   // optional [n_steps][n_vocab]
 };
 
+// CFG (DK_* bits): what this variant of the kernel contains.  The host launches the smallest variant that covers the model
+// (head size, weight types, tensor parallelism): code the model never runs still costs instruction-cache misses and
+// registers at every phase change of a 22 k-instruction kernel (measured: +2.6 % tokens/s for the 8B Q4_K_M file).
+template <int CFG>
 __global__ void __launch_bounds__(CTA_THREADS, 1)
-decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes, const int max_grp) {
+decode_kernel_t(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes, const int max_grp) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     Smem sm_ = carve_smem(smem_raw, ring_bytes, max_grp, P.hown_cap); carve_tail(sm_, P.max_segs);
     const Smem sm = sm_;
@@ -612,6 +640,11 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
             long long* tr = nullptr;
             if (P.trace) tr = P.trace + (((size_t)step * P.n_phases + i) * G + c) * 8;
             if (tr && tid == 0) { const long long t0 = gtime(); for (int k = 0; k < 7; k++) tr[k] = t0; tr[7] = 0; }
+#ifdef B200_WTRACE
+            if (lane == 0) s_wt[warp] = (g_wtrace && c == g_wtrace_cta) ? g_wtrace + (((size_t)step * P.n_phases + i) * 16 + warp) * 8 : nullptr;
+            __syncwarp();
+            WT(0);
+#endif
             // this thread is about to poll an exchange: until its inputs have arrived the producer issues nothing beyond
             // the phases the CTA has already entered (slower warps may still be consuming those)
             if (tid == 0 && ph.kind != PH_EMBED) sm.ctrl[0] = step * P.n_phases + i - 1;
@@ -633,12 +666,12 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
                 consumer_sync();
             } else if (ph.kind == PH_ATTN) {
                 for (int it = c; it < P.n_head * P.n_splits; it += G) {
-                    if (P.head_dim == 128) attn_item<4>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane, tr);
-                    else attn_item<2>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane, tr);
+                    if constexpr ((CFG & DK_HD128) != 0) { if (P.head_dim == 128) attn_item<4>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane, tr); }
+                    if constexpr ((CFG & DK_HD64) != 0) { if (P.head_dim != 128) attn_item<2>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane, tr); }
                 }
                 if (tid == 0) sm.ctrl[0] = 0x7fffffff;                 // CTAs without an attention item polled nothing
             } else {
-                consume_phase(P, ph, sm, stage_seq, c, G, pos, tid, seq, best, logits_dst, tr);
+                consume_phase<CFG>(P, ph, sm, stage_seq, c, G, pos, tid, seq, best, logits_dst, tr);
                 if (ph.op[0].epi == EPI_LOGITS) {          // publish this CTA's argmax candidate
                     consumer_sync();
                     if (lane == 0) { sm.red[2 * warp] = best.v; sm.red[2 * warp + 1] = __int_as_float(best.i); }
@@ -650,7 +683,7 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
                             if (vv > bv || (vv == bv && ix < bi)) { bv = vv; bi = ix; }
                         }
                         st_relaxed_v2(P.cand_ll + 2 * c, __float_as_uint(bv), seq); st_relaxed_v2(P.cand_ll + 2 * c + 1, (uint32_t)bi, seq);
-                        for (int r = 0; r < P.tp_world; r++) if (r != P.tp_rank) {      // vocabulary shards: every rank sees every rank's candidates
+                        if constexpr ((CFG & DK_TP) != 0) for (int r = 0; r < P.tp_world; r++) if (r != P.tp_rank) {      // vocabulary shards: every rank sees every rank's candidates
                             uint2* dst = P.cand_peer[r] + (size_t)P.tp_rank * 2 * G + 2 * c;
                             st_sys_v2(dst, __float_as_uint(bv), seq); st_sys_v2(dst + 1, (uint32_t)bi, seq);
                         }
@@ -662,6 +695,7 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
 #else
             if (tr && tid == 0) tr[6] = gtime();
 #endif
+            WT(7);
         }
         // ---- next token: forced, or argmax over the per-CTA candidates (every CTA redundantly)
         int next;
@@ -673,7 +707,7 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
                 const float vv = t[0]; const int ix = __float_as_int(t[1]);
                 if (vv > bv || (vv == bv && ix < bi)) { bv = vv; bi = ix; }
             }
-            if (P.tp_world > 1) for (int k = tid; k < P.tp_world * G; k += CONSUMER_THREADS) {
+            if constexpr ((CFG & DK_TP) != 0) if (P.tp_world > 1) for (int k = tid; k < P.tp_world * G; k += CONSUMER_THREADS) {
                 if (k / G == P.tp_rank) continue;                       // own candidates were read above
                 const uint2* src = P.cand_peer[P.tp_rank] + 2 * (size_t)k;
                 uint2 w0, w1; unsigned spins = *(volatile unsigned*)P.tp_error ? TP_SPIN_BUDGET : 0u;
@@ -685,6 +719,10 @@ decode_kernel(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes
                 const float vv = __uint_as_float(w0.x); const int ix = (int)w1.x;
                 if (vv > bv || (vv == bv && ix < bi)) { bv = vv; bi = ix; }
             }
+            // Lanes leave the polls above at different times and most warps skip them.  Without this barrier the variants of the
+            // kernel that have no tensor-parallel block between the poll and the shuffles reduced stale registers (found by
+            // test_greedy_stream_matches_oracle when the variants were introduced).
+            __syncwarp();
 #pragma unroll
             for (int o = 16; o; o >>= 1) {
                 const float vv = __shfl_xor_sync(0xffffffffu, bv, o); const int ix = __shfl_xor_sync(0xffffffffu, bi, o);

@@ -116,6 +116,27 @@ int tp_shard_window(const char* kind, int64_t N, int K, int rank, int world, int
 }
 
 // ------------------------------------------------------------------------------------ init
+// ------------------------------------------------------------------------------------ decode kernel variants
+// The persistent kernel is instantiated for the model shapes that matter and once with everything; a model gets the
+// smallest variant covering its head size, weight types and tensor parallelism (DK_* bits, stream.cuh).
+struct DecodeVariant { int cfg; const void* fn; };
+static const DecodeVariant g_decode_variants[] = {
+    {DK_HD128 | DK_Q4K | DK_Q6K, (const void*)decode_kernel_t<DK_HD128 | DK_Q4K | DK_Q6K>},                 // Llama-3 Q4_K_M files
+    {DK_HD128 | DK_Q80, (const void*)decode_kernel_t<DK_HD128 | DK_Q80>},                                     // Q8_0 files
+    {DK_HD128 | DK_TP | DK_Q4K | DK_Q6K, (const void*)decode_kernel_t<DK_HD128 | DK_TP | DK_Q4K | DK_Q6K>},  // tensor-parallel shards of Q4_K_M files
+    {DK_HD128 | DK_HD64 | DK_TYPES, (const void*)decode_kernel_t<DK_HD128 | DK_HD64 | DK_TYPES>},            // any single-GPU model
+    {DK_ALL, (const void*)decode_kernel_t<DK_ALL>},
+};
+static int decode_variant_count() { return (int)(sizeof(g_decode_variants) / sizeof(g_decode_variants[0])); }
+static const void* decode_variant_fn(int i) { return g_decode_variants[i].fn; }
+static const void* decode_variant_for(int need) {
+    if (getenv("B200_DECODE_GENERIC")) return g_decode_variants[decode_variant_count() - 1].fn;      // A/B measurements
+    if (const char* e = getenv("B200_DECODE_VARIANT")) { const int i = atoi(e); if (i >= 0 && i < decode_variant_count() && (g_decode_variants[i].cfg & need) == need) return g_decode_variants[i].fn; }
+    for (const DecodeVariant& v : g_decode_variants) if ((v.cfg & need) == need) return v.fn;         // ordered: specific first
+    return g_decode_variants[decode_variant_count() - 1].fn;
+}
+static int dk_type_bit(int type) { return type == T_Q4_K ? DK_Q4K : type == T_Q5_K ? DK_Q5K : type == T_Q6_K ? DK_Q6K : DK_Q80; }
+
 int Engine::init(const b200_config* cfg) {
     std::lock_guard<std::mutex> lk(mu);
     if (ready) return B200_OK;
@@ -136,7 +157,13 @@ int Engine::init(const b200_config* cfg) {
     CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&aux_stream, cudaStreamNonBlocking));
-    CK(cudaFuncSetAttribute(decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin));
+    for (int i = 0; i < decode_variant_count(); i++) {
+#ifdef B200_WTRACE
+        CK(cudaFuncSetAttribute(decode_variant_fn(i), cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 1024));   // the variant has a static shared array
+#else
+        CK(cudaFuncSetAttribute(decode_variant_fn(i), cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin));
+#endif
+    }
     ready = true;
     return B200_OK;
 }
@@ -158,9 +185,9 @@ int Engine::ensure() {
 }
 
 // ------------------------------------------------------------------------------------ launch geometry
-struct LaunchCfg { int grid; uint32_t ring_bytes; int max_grp; size_t smem; };
+struct LaunchCfg { int grid; uint32_t ring_bytes; int max_grp; size_t smem; const void* kernel = nullptr; };
 
-static int launch_cfg(Engine& E, int max_grp, int hown_cap, int max_segs, LaunchCfg& lc) {
+static int launch_cfg(Engine& E, int max_grp, int hown_cap, int max_segs, int need, LaunchCfg& lc) {
     // one persistent CTA per SM owning (almost) all of its shared memory
     max_grp = std::max(max_grp, (int)(((CONSUMER_WARPS + 1) * 130 + 64) * 4 / 2336 + 1));   // the activation buffer doubles as attention scratch
     size_t per_cta = (size_t)E.smem_optin;
@@ -177,15 +204,16 @@ static int launch_cfg(Engine& E, int max_grp, int hown_cap, int max_segs, Launch
     if (const char* rk = getenv("B200_RING_KB")) want = (uint32_t)atoi(rk) * 1024u;
     if (want >= 2u * MAX_STAGE_BYTES && want < lc.ring_bytes) lc.ring_bytes = want / 128 * 128;
     lc.max_grp = max_grp; lc.smem = lc.ring_bytes + fixed;
+    lc.kernel = decode_variant_for(need);
     int occ = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, decode_kernel, CTA_THREADS, lc.smem));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, lc.kernel, CTA_THREADS, lc.smem));
     if (occ < 1) return fail(B200_ERR_CUDA, "decode kernel does not fit on an SM");
     return B200_OK;
 }
 
 static int launch_decode(Engine& E, const DecodeParams& P, const DecodeRun& R, const LaunchCfg& lc) {
     void* args[] = {(void*)&P, (void*)&R, (void*)&lc.ring_bytes, (void*)&lc.max_grp};
-    CK(cudaLaunchCooperativeKernel((void*)decode_kernel, dim3(lc.grid), dim3(CTA_THREADS), args, lc.smem, E.stream));
+    CK(cudaLaunchCooperativeKernel(lc.kernel, dim3(lc.grid), dim3(CTA_THREADS), args, lc.smem, E.stream));
     E.launches++;
     return B200_OK;
 }
@@ -462,8 +490,11 @@ int Model::commit() {
     int max_grp = std::max({n_groups(F), n_groups(QD), 2 * n_groups(D)});
     hown_cap = 2 * ((D / 2 + E.n_sm - 1) / E.n_sm + 2);                       // pairs per CTA slice (worst case: 1 CTA/SM) x 2 rows
     max_segs = 6 * n_layer + 2;                                              // q, k, v, wo, gate/up, down per layer + lm_head
-    LaunchCfg lc; if (int rc2 = launch_cfg(E, max_grp, hown_cap, max_segs, lc)) return rc2;
-    grid = lc.grid; ring_bytes = lc.ring_bytes; smem_max_grp = lc.max_grp; smem_bytes = lc.smem;
+    int need = (head_dim == 128 ? DK_HD128 : DK_HD64) | (tp ? DK_TP : 0);
+    for (const Layer& L : layers) for (const Matrix* m : {&L.wq, &L.wk, &L.wv, &L.wo, &L.wgu, &L.wd}) need |= dk_type_bit(m->type);
+    need |= dk_type_bit(out_w.type);
+    LaunchCfg lc; if (int rc2 = launch_cfg(E, max_grp, hown_cap, max_segs, need, lc)) return rc2;
+    grid = lc.grid; ring_bytes = lc.ring_bytes; smem_max_grp = lc.max_grp; smem_bytes = lc.smem; decode_fn = lc.kernel;
     const size_t n_ll16 = (size_t)XREP * ((size_t)D + QD + F) + 2 * (size_t)KVD, n_ll32 = (size_t)QD + (size_t)n_head * 16 * (head_dim + 2) + 2 * (size_t)grid;
     if ((rc = own(&d_ll16, n_ll16)) || (rc = own(&d_ll32, n_ll32)) || (rc = own(&d_logits, (size_t)n_vocab + 2)) || (rc = own(&d_state, (size_t)16)) ||
         (rc = own(&d_out_tokens, (size_t)E.max_ctx + 16)) || (rc = own(&d_forced, (size_t)E.max_ctx + 16)))
@@ -570,7 +601,7 @@ int Model::run_steps(int n_steps, const int32_t* forced, int n_forced, bool rese
     P.quiet = 1; if (const char* e = getenv("B200_QUIET")) P.quiet = atoi(e);
     P.l2_ahead = 0; if (const char* e = getenv("B200_L2_AHEAD_KB")) P.l2_ahead = (uint32_t)std::max(0, atoi(e)) * 1024u;
     DecodeRun R{}; R.forced = d_forced; R.n_forced = n_forced; R.logits_all = logits_all_dev;
-    LaunchCfg lc; lc.grid = grid; lc.ring_bytes = ring_bytes; lc.max_grp = smem_max_grp; lc.smem = smem_bytes;
+    LaunchCfg lc; lc.grid = grid; lc.ring_bytes = ring_bytes; lc.max_grp = smem_max_grp; lc.smem = smem_bytes; lc.kernel = decode_fn;
     if (int rc = launch_decode(E, P, R, lc)) return rc;
     cur_pos += n_steps;
     return B200_OK;
@@ -698,10 +729,26 @@ int Model::bench_decode(int ctx_len, int n_steps, int warmup, float* ms_per_toke
     const char* trace_path = getenv("B200_TRACE");                 // debug: per-phase clock64 stamps of 4 CTAs
     size_t trace_n = (size_t)n_steps * n_phases * grid * 8;
     if (trace_path) { CK(cudaMalloc((void**)&d_trace, trace_n * 8)); CK(cudaMemsetAsync(d_trace, 0, trace_n * 8, E.stream)); }
+#ifdef B200_WTRACE
+    long long* d_wt = nullptr; const size_t wt_n = (size_t)n_steps * n_phases * 16 * 8;
+    if (const char* wp = getenv("B200_WTRACE")) {
+        (void)wp; CK(cudaMalloc((void**)&d_wt, wt_n * 8)); CK(cudaMemsetAsync(d_wt, 0, wt_n * 8, E.stream));
+        int cta = 0; if (const char* e = getenv("B200_WTRACE_CTA")) cta = atoi(e);
+        CK(cudaMemcpyToSymbolAsync(g_wtrace, &d_wt, sizeof(d_wt), 0, cudaMemcpyHostToDevice, E.stream));
+        CK(cudaMemcpyToSymbolAsync(g_wtrace_cta, &cta, sizeof(cta), 0, cudaMemcpyHostToDevice, E.stream));
+    }
+#endif
     CK(cudaEventRecord(e0, E.stream));
     int rc = run_steps(n_steps, nullptr, 0, false, nullptr);
     CK(cudaEventRecord(e1, E.stream)); CK(cudaEventSynchronize(e1));
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1); cudaEventDestroy(e0); cudaEventDestroy(e1);
+#ifdef B200_WTRACE
+    if (d_wt) {
+        std::vector<long long> w(wt_n); cudaMemcpy(w.data(), d_wt, wt_n * 8, cudaMemcpyDeviceToHost);
+        if (FILE* f = fopen(getenv("B200_WTRACE"), "wb")) { int hdr[3] = {n_steps, n_phases, 16}; fwrite(hdr, 4, 3, f); fwrite(w.data(), 8, wt_n, f); fclose(f); }
+        long long* z = nullptr; cudaMemcpyToSymbol(g_wtrace, &z, sizeof(z)); cudaFree(d_wt);
+    }
+#endif
     if (trace_path) {
         std::vector<long long> tr(trace_n); cudaMemcpy(tr.data(), d_trace, trace_n * 8, cudaMemcpyDeviceToHost);
         if (FILE* f = fopen(trace_path, "wb")) { int hdr[3] = {n_steps, n_phases, grid}; fwrite(hdr, 4, 3, f); fwrite(tr.data(), 8, trace_n, f); fclose(f); }
@@ -1361,7 +1408,7 @@ int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, flo
     int rc = B200_OK;
     LaunchCfg lc;
     auto cleanup = [&]() { cudaFree(d_raw); cudaFree(d_w); cudaFree(d_x); cudaFree(d_y); cudaFree(d_cv); cudaFree(d_st); cudaFree(d_ot); cudaFree(d_ph); };
-    if ((rc = launch_cfg(E, n_groups(K), 4, 4, lc))) return rc;
+    if ((rc = launch_cfg(E, n_groups(K), 4, 4, DK_HD128 | dk_type_bit(type), lc))) return rc;
     if ((rc = dalloc(&d_raw, (size_t)N * rb)) || (rc = dalloc(&d_w, repacked_bytes(type, N, K))) || (rc = dalloc(&d_x, (size_t)K)) || (rc = dalloc(&d_y, (size_t)N)) ||
         (rc = dalloc(&d_cv, (size_t)2 * lc.grid)) || (rc = dalloc(&d_st, (size_t)16)) || (rc = dalloc(&d_ot, (size_t)iters + 1)) || (rc = dalloc(&d_ph, (size_t)1))) { cleanup(); return rc; }
     cudaMemcpyAsync(d_raw, raw, (size_t)N * rb, cudaMemcpyHostToDevice, E.stream);

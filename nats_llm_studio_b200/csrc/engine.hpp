@@ -86,7 +86,7 @@ struct Model {
     int sync_slot = 0;                           // KV sequence slot of the synchronous batch-1 path (generate / eval / chat with max_seqs == 1);
                                                  // with max_seqs > 1 it is an extra slot the scheduler never hands out
     int max_segs = 0;
-    int grid = 0, smem_max_grp = 0; uint32_t ring_bytes = 0; size_t smem_bytes = 0;
+    int grid = 0, smem_max_grp = 0; uint32_t ring_bytes = 0; size_t smem_bytes = 0; const void* decode_fn = nullptr;   // decode kernel variant of this model
     int cur_pos = 0;
     long long* d_trace = nullptr;
     // prefill scratch (allocated on first use)

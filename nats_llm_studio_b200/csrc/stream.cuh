@@ -22,6 +22,10 @@
 
 namespace b200 {
 
+// decode_kernel_t<CFG> variants (decode.cuh): what a variant contains
+constexpr int DK_HD128 = 1, DK_HD64 = 2, DK_TP = 4, DK_Q4K = 8, DK_Q5K = 16, DK_Q6K = 32, DK_Q80 = 64;
+constexpr int DK_TYPES = DK_Q4K | DK_Q5K | DK_Q6K | DK_Q80, DK_ALL = DK_HD128 | DK_HD64 | DK_TP | DK_TYPES;
+
 #ifndef B200_GROUP_WARPS
 #define B200_GROUP_WARPS 7      // 14 consumer warps + the producer = 15 warps: at most 4 warps per scheduler, so 128 registers per thread
                                 // (16 + 1 warps cap the kernel at 96 registers: measured 1.97 ms/token on the 8B model against 1.89)
@@ -430,8 +434,9 @@ __device__ __forceinline__ void k4_scales(const uint4& hdr, int j, int& sc0, int
 }
 
 // The lane's weights of one row's group, in registers: loading (load_w) apart from the arithmetic (dot_w).  (Putting all
-// reads of a stage in flight ahead of the arithmetic with ordered loads was tried and measured no faster: the stream loop
-// is bound by the number of instructions it issues, not by exposed shared-memory latency — DESIGN.md §3.1.)
+// reads of a stage in flight ahead of the arithmetic was tried twice — ordered loads of the whole stage (spills), and two
+// WRegs buffers loaded one unit ahead: ptxas sinks every LDS.128 back to just before its first use whatever the source
+// order, to stay inside 128 registers — DESIGN.md §3.1.)
 struct WRegs { uint4 v[5]; uint32_t s; };
 __device__ __forceinline__ uint4 lds128(const void* p) { return *(const uint4*)p; }
 __device__ __forceinline__ uint32_t lds32(const void* p) { return *(const uint32_t*)p; }
