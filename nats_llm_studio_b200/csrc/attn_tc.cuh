@@ -1,8 +1,8 @@
-// attn_tc.cuh — K7: causal prompt attention on the 5th-generation tensor cores (flash-style), for the rows of ONE
-// sequence's prompt chunk (positions pos0 .. pos0 + n_rows - 1 of sequence slot `slot`) over the paged fp16 KV cache.
+// attn_tc.cuh — K7: causal prompt attention on the 5th-generation tensor cores (flash-style), for the rows of a prompt
+// chunk (runs of consecutive positions of one sequence each, cut into query tiles) over the paged fp16 KV cache.
 // Part of what LM Studio's /api/v0/chat/completions does behind /root/reference/nats_llm_studio.go:158-179.
 //
-// One CTA per (128-row query tile, head), 128 threads.  Per 128-position KV tile:
+// One CTA per (query tile of <= 128 rows of one run, head), 128 threads.  Per 128-position KV tile:
 //   S = Q . K^T        tcgen05.mma kind::f16, Q and K tiles staged by TMA (K-major, 128-byte swizzle), S in tensor memory
 //   softmax            thread r owns query row r (= TMEM lane r): tcgen05.ld of its 128 scores, running max / sum, the
 //                      probabilities go BACK to tensor memory as fp16 (tcgen05.st) — P never touches shared memory
@@ -41,9 +41,15 @@ __device__ __forceinline__ uint64_t umma_desc_mn_sw128(const void* smem, uint32_
 }
 __device__ __forceinline__ void tmem_ld_x32(uint32_t taddr, uint32_t* r) { tmem_ld_32x32b_x32_nowait(taddr, r); asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// One launch covers every run of a prompt chunk: blockIdx.x indexes a table of query tiles {first row in the chunk, rows in
+// the tile (<= 128), position of the first row, sequence slot}.  (One launch per run made the choice of kernel — and with
+// it the rounding of a request's logits — depend on what else was packed into the chunk.)
+constexpr int FA_MAX_TILES = 64;
+struct FaTiles { int4 t[FA_MAX_TILES]; };
+
 template <int HD>
 __global__ void __launch_bounds__(FA_THREADS, 1)
-attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv, int row0, int n_rows, int pos0, int slot, int layer,
+attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv, const __grid_constant__ FaTiles tiles, int layer,
                        int n_head, int n_head_kv, float kq_scale, KvLayout kv, __nv_bfloat16* __restrict__ O) {
     using C = FaCfg<HD>;
     extern __shared__ uint8_t fa_smem_raw[];
@@ -52,9 +58,10 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_
     uint64_t* bars = (uint64_t*)(base + 5 * (size_t)C::TILE_BYTES);
     uint64_t *q_full = bars, *k_full = bars + 1 /*[2]*/, *v_full = bars + 3 /*[2]*/, *s_done = bars + 5, *o_done = bars + 6; uint32_t* tmem_slot = (uint32_t*)(bars + 8);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int qt = blockIdx.x, head = blockIdx.y, kvh = head / (n_head / n_head_kv);
-    const int r_lo = qt * FA_BM, rows_here = min(FA_BM, n_rows - r_lo);
-    const int last_pos = pos0 + r_lo + rows_here - 1;                 // newest position any row of this tile may see
+    const int head = blockIdx.y, kvh = head / (n_head / n_head_kv);
+    const int4 tile = tiles.t[blockIdx.x];
+    const int row_t = tile.x, rows_here = tile.y, pos_t = tile.z, slot = tile.w;
+    const int last_pos = pos_t + rows_here - 1;                       // newest position any row of this tile may see
     const int n_kv_tiles = last_pos / FA_BN + 1;
     if (tid == 0) { for (int i = 0; i < 7; i++) mbar_init(&bars[i], 1); fence_barrier_init(); }
     if (warp == 0) tcgen05_alloc(tmem_slot, C::TM_COLS);
@@ -79,10 +86,10 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_
     };
     if (tid == 0) {
         mbar_expect_tx(q_full, C::TILE_BYTES);
-        for (int pn = 0; pn < C::PANELS; pn++) tma_load_2d(sQ + (size_t)pn * (FA_BM * 128), &tmap_q, head * HD + pn * 64, row0 + r_lo, q_full);
+        for (int pn = 0; pn < C::PANELS; pn++) tma_load_2d(sQ + (size_t)pn * (FA_BM * 128), &tmap_q, head * HD + pn * 64, row_t, q_full);
         load_kv(0, 0);
     }
-    const int my_pos = pos0 + r_lo + tid;                             // position of this thread's query row
+    const int my_pos = pos_t + tid;                                   // position of this thread's query row
     const float sl2 = kq_scale * 1.4426950408889634f;                 // scores are kept in log2 units: exp2f((s - m) * sl2)
     float m_run = -INFINITY, l_run = 0.f;
     const uint32_t lane_off = (uint32_t)(warp * 32) << 16;            // this warp's quarter of the TMEM lanes
@@ -167,7 +174,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_
     __syncwarp();
     tcgen05_fence_after();
     const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-    const int row = row0 + r_lo + tid;
+    const int row = row_t + tid;
 #pragma unroll 1
     for (int c = 0; c < HD; c += 32) {
         uint32_t o[32]; tmem_ld_x32(tmem + C::TM_O + lane_off + c, o);

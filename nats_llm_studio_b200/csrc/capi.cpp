@@ -1,4 +1,5 @@
 // capi.cpp — extern "C" surface declared in include/b200_engine.h.
+#include <thread>
 #include <atomic>
 #include <chrono>
 #include <cstring>
@@ -24,6 +25,10 @@ struct Request {
     bool expired() const { return s.timeout_ms > 0 && std::chrono::steady_clock::now() - t_submit > std::chrono::milliseconds(s.timeout_ms); }
 };
 struct Seq { std::shared_ptr<Request> r; int slot = 0, n_fed = 0, pos = 0, cur_tok = 0, n_gen = 0; bool decoding = false; float ttft_ms = 0; std::chrono::steady_clock::time_point t_first; };
+// std::mutex is not fair: a thread that wants run_mu to delete the model could wait behind the scheduler's back-to-back
+// steps until the model's requests had all finished.  The scheduler steps aside while such a thread is waiting.
+static void yield_to_release(Model& m) { while (m.lock_waiters.load(std::memory_order_acquire) > 0) std::this_thread::sleep_for(std::chrono::microseconds(20)); }
+
 struct Scheduler {
     std::mutex mu; std::condition_variable cv_req, cv_ev;
     std::deque<std::shared_ptr<Request>> q; std::deque<b200_event> ev;
@@ -109,7 +114,7 @@ struct Scheduler {
                     if (s.n_fed == n - 1) { s.decoding = true; s.cur_tok = s.r->toks[n - 1]; s.pos = n - 1; }
                     if ((int)toks.size() == Model::PREFILL_CHUNK) break;
                 }
-                if (!toks.empty()) { std::lock_guard<std::mutex> lk(cur->run_mu); rc = cur->prefill_rows(toks.data(), slots.data(), pos.data(), (int)toks.size()); }
+                if (!toks.empty()) { yield_to_release(*cur); std::lock_guard<std::mutex> lk(cur->run_mu); rc = cur->prefill_rows(toks.data(), slots.data(), pos.data(), (int)toks.size()); }
             }
             // ---- one batched decode step for every sequence whose prompt is in the cache
             std::vector<int> idx;
@@ -117,7 +122,7 @@ struct Scheduler {
             const int B = (int)idx.size();
             std::vector<int32_t> toks(B), slots(B), pos(B), next(B), draw(B); std::vector<b200_sampling> samp(B);
             for (int j = 0; j < B; j++) { const Seq& s = active[idx[j]]; toks[j] = s.cur_tok; slots[j] = s.slot; pos[j] = s.pos; samp[j] = s.r->s; draw[j] = s.n_gen; }
-            if (rc == B200_OK && B > 0) { std::lock_guard<std::mutex> lk(cur->run_mu); rc = cur->batch_step(toks.data(), slots.data(), pos.data(), B, next.data(), nullptr, samp.data(), draw.data()); }
+            if (rc == B200_OK && B > 0) { yield_to_release(*cur); std::lock_guard<std::mutex> lk(cur->run_mu); rc = cur->batch_step(toks.data(), slots.data(), pos.data(), B, next.data(), nullptr, samp.data(), draw.data()); }
             if (rc != B200_OK) {                                   // engine failure: every active request fails
                 for (Seq& s : active) finish(s, B200_EV_ERROR, rc);
                 active.clear(); push_events(out, done); continue;
@@ -225,7 +230,7 @@ int b200_model_close(b200_model* m) {
     std::shared_ptr<Model> keep;
     { Registry& R = registry(); std::lock_guard<std::mutex> lk(R.mu); for (auto it = R.models.begin(); it != R.models.end(); ++it) if ((b200_model*)it->second.get() == m) { keep = it->second; R.models.erase(it); break; } }
     if (!keep) return fail(B200_ERR_NOT_FOUND, "model is not registered");
-    std::lock_guard<std::mutex> lk(keep->run_mu); keep->release();
+    keep->release_locked();
     return B200_OK;
 }
 int b200_model_load_file(const char* id, const char* path, b200_model** out) {

@@ -119,8 +119,9 @@ __device__ __forceinline__ float embed_elem(const uint8_t* w, int type, int n_gr
 // One item = (head, split).  Each warp owns a strided set of positions and keeps NB of them in flight at once; the
 // cached K/V loads are issued BEFORE q is polled (they do not depend on this token), so the exchange wait and the
 // first memory round trip overlap.
-template <int VEC>   // head_dim = 32*VEC
+template <int VEC, bool TR>   // head_dim = 32*VEC
 __device__ void attn_item(const DecodeParams& P, const Smem& sm, int layer, int head, int split, int pos, uint32_t seq_in, uint32_t seq_out, int warp, int lane, long long* tr) {
+    if constexpr (!TR) tr = nullptr;                                   // variants without the trace stamps: every `if (tr ...)` folds away
     constexpr int HD = 32 * VEC, NB = 10;     // 14 warps x 10 positions: a 128-position split (context 512 over 4 splits) is one batch
     typedef typename std::conditional<VEC == 4, uint2, uint32_t>::type raw_t;     // VEC fp16 values
     const int n_ctx = pos + 1, chunk = (n_ctx + P.n_splits - 1) / P.n_splits;
@@ -365,9 +366,10 @@ __device__ __forceinline__ void epilogue(const DecodeParams& P, const OpDesc& op
 // Pairs [a, b) of `op`, eight pairs per stage (one per warp of a group).  A warp visits only the stages of its group's
 // row blocks: their sequence numbers follow from the slice's stage order (seg_stage_index), the ring offset of a stage
 // is published by the producer next to its barrier.  seq0: sequence number of the slice's first stage.
-template <int TYPE, bool XHOLD, bool TP>
+template <int TYPE, bool XHOLD, bool TP, bool TR>
 __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& op, const Smem& sm, const Smem& sx, uint32_t seq0, int a, int b,
                                           int pos, int warp, int lane, uint32_t seq, float in_scale, ArgBest& best, float* logits_dst, long long* tr) {
+    if constexpr (!TR) tr = nullptr;
     constexpr int GB = TYPE == T_Q4_K ? 1152 : TYPE == T_Q5_K ? 1408 : TYPE == T_Q6_K ? 1680 : 2176;
     constexpr uint32_t PU = 2u * GB;
     constexpr int SG = stage_groups(TYPE);
@@ -424,6 +426,7 @@ __device__ __forceinline__ void stream_op(const DecodeParams& P, const OpDesc& o
 template <int CFG>
 __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem& sm, uint32_t& stage_seq, int c, int G,
                               int pos, int tid, uint32_t seq, ArgBest& best, float* logits_dst, long long* tr) {
+    if constexpr ((CFG & DK_TRACE) == 0) tr = nullptr;
     const int warp = tid >> 5, lane = tid & 31;
     // ---- activation prologue: build the int8 vector(s) in shared memory
     bool fam_std = false, fam_q6 = false;
@@ -557,13 +560,13 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
         const Smem& sx = (op.type == T_Q6_K) ? s2 : sm;
         // phases with one stage per row block and several row blocks per warp keep the activation slice in registers
         const bool xhold = stage_groups(op.type) == 2 && op.n_grp == 2 && (b - a) > WARP_GROUPS * PAIRS_PER_STAGE;
-#define B200_STREAM(T_) do { if (xhold) stream_op<T_, true, TP>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); \
-                             else stream_op<T_, false, TP>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); } while (0)
-        constexpr bool TP = (CFG & DK_TP) != 0;
+#define B200_STREAM(T_) do { if (xhold) stream_op<T_, true, TP, TR>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); \
+                             else stream_op<T_, false, TP, TR>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); } while (0)
+        constexpr bool TP = (CFG & DK_TP) != 0, TR = (CFG & DK_TRACE) != 0;
         // only the weight types the kernel variant was built for (the host picks a variant that covers the file's types)
         if constexpr ((CFG & DK_Q4K) != 0) { if (op.type == T_Q4_K) B200_STREAM(T_Q4_K); }
         if constexpr ((CFG & DK_Q6K) != 0) { if (op.type == T_Q6_K) B200_STREAM(T_Q6_K); }
-        if constexpr ((CFG & DK_Q80) != 0) { if (op.type == T_Q8_0) stream_op<T_Q8_0, false, TP>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); }
+        if constexpr ((CFG & DK_Q80) != 0) { if (op.type == T_Q8_0) stream_op<T_Q8_0, false, TP, TR>(P, op, sm, sx, stage_seq, a, b, pos, warp, lane, seq, in_scale, best, logits_dst, tr); }
         if constexpr ((CFG & DK_Q5K) != 0) { if (op.type == T_Q5_K) B200_STREAM(T_Q5_K); }
 #undef B200_STREAM
         stage_seq += (uint32_t)(((b - a + PAIRS_PER_STAGE - 1) / PAIRS_PER_STAGE) * stages_per_rb(op.type, op.n_grp));
@@ -583,8 +586,7 @@ template <int CFG>
 __global__ void __launch_bounds__(CTA_THREADS, 1)
 decode_kernel_t(const DecodeParams P, const DecodeRun R, const uint32_t ring_bytes, const int max_grp) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    Smem sm_ = carve_smem(smem_raw, ring_bytes, max_grp, P.hown_cap); carve_tail(sm_, P.max_segs);
-    const Smem sm = sm_;
+    const Smem sm = carve_smem(smem_raw, ring_bytes, max_grp, P.hown_cap);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, c = blockIdx.x, G = gridDim.x;
     if (tid == 0) {
         for (int i = 0; i < NSLOT; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], GROUP_WARPS); }
@@ -638,7 +640,7 @@ decode_kernel_t(const DecodeParams P, const DecodeRun R, const uint32_t ring_byt
             }
             seq++;
             long long* tr = nullptr;
-            if (P.trace) tr = P.trace + (((size_t)step * P.n_phases + i) * G + c) * 8;
+            if constexpr ((CFG & DK_TRACE) != 0) { if (P.trace) tr = P.trace + (((size_t)step * P.n_phases + i) * G + c) * 8; }
             if (tr && tid == 0) { const long long t0 = gtime(); for (int k = 0; k < 7; k++) tr[k] = t0; tr[7] = 0; }
 #ifdef B200_WTRACE
             if (lane == 0) s_wt[warp] = (g_wtrace && c == g_wtrace_cta) ? g_wtrace + (((size_t)step * P.n_phases + i) * 16 + warp) * 8 : nullptr;
@@ -666,8 +668,8 @@ decode_kernel_t(const DecodeParams P, const DecodeRun R, const uint32_t ring_byt
                 consumer_sync();
             } else if (ph.kind == PH_ATTN) {
                 for (int it = c; it < P.n_head * P.n_splits; it += G) {
-                    if constexpr ((CFG & DK_HD128) != 0) { if (P.head_dim == 128) attn_item<4>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane, tr); }
-                    if constexpr ((CFG & DK_HD64) != 0) { if (P.head_dim != 128) attn_item<2>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane, tr); }
+                    if constexpr ((CFG & DK_HD128) != 0) { if (P.head_dim == 128) attn_item<4, (CFG & DK_TRACE) != 0>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane, tr); }
+                    if constexpr ((CFG & DK_HD64) != 0) { if (P.head_dim != 128) attn_item<2, (CFG & DK_TRACE) != 0>(P, sm, ph.layer, it / P.n_splits, it % P.n_splits, pos, seq - 1, seq, warp, lane, tr); }
                 }
                 if (tid == 0) sm.ctrl[0] = 0x7fffffff;                 // CTAs without an attention item polled nothing
             } else {

@@ -125,6 +125,8 @@ static const DecodeVariant g_decode_variants[] = {
     {DK_HD128 | DK_Q80, (const void*)decode_kernel_t<DK_HD128 | DK_Q80>},                                     // Q8_0 files
     {DK_HD128 | DK_TP | DK_Q4K | DK_Q6K, (const void*)decode_kernel_t<DK_HD128 | DK_TP | DK_Q4K | DK_Q6K>},  // tensor-parallel shards of Q4_K_M files
     {DK_HD128 | DK_HD64 | DK_TYPES, (const void*)decode_kernel_t<DK_HD128 | DK_HD64 | DK_TYPES>},            // any single-GPU model
+    {DK_HD128 | DK_HD64 | DK_TP | DK_TYPES, (const void*)decode_kernel_t<DK_HD128 | DK_HD64 | DK_TP | DK_TYPES>},   // any model
+    {DK_HD128 | DK_Q4K | DK_Q6K | DK_TRACE, (const void*)decode_kernel_t<DK_HD128 | DK_Q4K | DK_Q6K | DK_TRACE>},  // B200_TRACE runs of the bench model
     {DK_ALL, (const void*)decode_kernel_t<DK_ALL>},
 };
 static int decode_variant_count() { return (int)(sizeof(g_decode_variants) / sizeof(g_decode_variants[0])); }
@@ -189,18 +191,20 @@ struct LaunchCfg { int grid; uint32_t ring_bytes; int max_grp; size_t smem; cons
 
 static int launch_cfg(Engine& E, int max_grp, int hown_cap, int max_segs, int need, LaunchCfg& lc) {
     // one persistent CTA per SM owning (almost) all of its shared memory
-    max_grp = std::max(max_grp, (int)(((CONSUMER_WARPS + 1) * 130 + 64) * 4 / 2336 + 1));   // the activation buffer doubles as attention scratch
+    max_grp = std::max(max_grp, (int)(((CONSUMER_WARPS + 1) * 130 + 64) * 4 / 2048 + 1));   // the int8 activation buffer doubles as attention scratch
+    if (max_grp > XG_MAX) return fail(B200_ERR_UNSUPPORTED, "activation vector longer than " + std::to_string(XG_MAX * 2048) + " elements");
     size_t per_cta = (size_t)E.smem_optin;
-    size_t fixed = smem_x_bytes(max_grp) + smem_misc_bytes(hown_cap, max_segs);
+    size_t fixed = SmemLayout::RING + smem_tail_bytes(max_grp, hown_cap, max_segs);
     // the ring allocator never splits a stage across the wrap point, so a stage plus the gap it may leave behind
     // must fit: ring >= 2 x the largest stage (otherwise the producer can wait on space that cannot exist)
     if (fixed + 2 * MAX_STAGE_BYTES + 256 > per_cta) return fail(B200_ERR_UNSUPPORTED, "activation vector does not fit in shared memory");
     lc.grid = E.n_sm;
     lc.ring_bytes = (uint32_t)((per_cta - fixed - 128) / 128 * 128);
-    // Not all of it: shared memory and L1 share one array, and what the ring does not take is L1 for the kernel's
-    // register spills and exchange polls.  164 KB (four Q4_K stages / three Q6_K stages in flight) measured best on the
-    // 8B model: 1.97 ms/token against 2.00 with the full 217 KB and 2.04 with 112 KB.  B200_RING_KB overrides.
-    uint32_t want = 164u * 1024u;
+    // Not all of it: shared memory and L1 share one 228 KB array and the split moves in steps (… 132, 164, 196, 228 KB of
+    // shared memory, counting 1 KB the system reserves per CTA).  The kernel's register spills and exchange polls live in
+    // L1, so the ring takes what is left of the 196 KB step (32 KB of L1): measured on the 8B model 587 tok/s, against 566
+    // at the 164 KB step (64 KB of L1, ring 132 KB) and 555 one byte over the 196 KB step (no L1 at all).  B200_RING_KB overrides.
+    uint32_t want = fixed + 2u * MAX_STAGE_BYTES < 195u * 1024u ? (uint32_t)(195u * 1024u - fixed) / 128 * 128 : 0u;      // 0: keep all of it
     if (const char* rk = getenv("B200_RING_KB")) want = (uint32_t)atoi(rk) * 1024u;
     if (want >= 2u * MAX_STAGE_BYTES && want < lc.ring_bytes) lc.ring_bytes = want / 128 * 128;
     lc.max_grp = max_grp; lc.smem = lc.ring_bytes + fixed;
@@ -490,7 +494,7 @@ int Model::commit() {
     int max_grp = std::max({n_groups(F), n_groups(QD), 2 * n_groups(D)});
     hown_cap = 2 * ((D / 2 + E.n_sm - 1) / E.n_sm + 2);                       // pairs per CTA slice (worst case: 1 CTA/SM) x 2 rows
     max_segs = 6 * n_layer + 2;                                              // q, k, v, wo, gate/up, down per layer + lm_head
-    int need = (head_dim == 128 ? DK_HD128 : DK_HD64) | (tp ? DK_TP : 0);
+    int need = (head_dim == 128 ? DK_HD128 : DK_HD64) | (tp ? DK_TP : 0) | (getenv("B200_TRACE") ? DK_TRACE : 0);
     for (const Layer& L : layers) for (const Matrix* m : {&L.wq, &L.wk, &L.wv, &L.wo, &L.wgu, &L.wd}) need |= dk_type_bit(m->type);
     need |= dk_type_bit(out_w.type);
     LaunchCfg lc; if (int rc2 = launch_cfg(E, max_grp, hown_cap, max_segs, need, lc)) return rc2;
@@ -599,7 +603,6 @@ int Model::run_steps(int n_steps, const int32_t* forced, int n_forced, bool rese
     if (const char* e = getenv("B200_SPLITS")) P.n_splits = std::max(1, std::min({16, atoi(e), std::max(1, grid / n_head)}));
     P.max_inflight = 4; if (const char* e = getenv("B200_INFLIGHT")) P.max_inflight = std::max(1, atoi(e));
     P.quiet = 1; if (const char* e = getenv("B200_QUIET")) P.quiet = atoi(e);
-    P.l2_ahead = 0; if (const char* e = getenv("B200_L2_AHEAD_KB")) P.l2_ahead = (uint32_t)std::max(0, atoi(e)) * 1024u;
     DecodeRun R{}; R.forced = d_forced; R.n_forced = n_forced; R.logits_all = logits_all_dev;
     LaunchCfg lc; lc.grid = grid; lc.ring_bytes = ring_bytes; lc.max_grp = smem_max_grp; lc.smem = smem_bytes; lc.kernel = decode_fn;
     if (int rc = launch_decode(E, P, R, lc)) return rc;
@@ -1023,16 +1026,24 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
         }
         // prompt chunks made of whole runs of one sequence each: causal attention on the tensor cores (attn_tc.cuh)
         const bool tc_off = getenv("B200_NO_ATTN_TC") != nullptr;       // read per call: tests compare the two attention kernels in one process
-        const bool tc = !q && runs && !runs->empty() && !tc_off && M >= 32;
+        const bool tc = !q && runs && !runs->empty() && !tc_off;        // every prompt chunk, whatever it is made of: a request's numerics must not depend on its neighbours
         CK(launch_pdl(rope_kv_rows_kernel, dim3(nblk((long long)M * W3 / 2)), dim3(256), 0, E.stream, (const float*)pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, (const float*)inv_freq, kv, pf_Q, sp, tc)); E.launches++; sp = none;
         if (tc) {
             if (int rc2 = ensure_attn_maps()) return rc2;
-            for (const RowRun& r : *runs) {
-                const dim3 g((r.n + FA_BM - 1) / FA_BM, n_head);
-                if (head_dim == 128) attn_prefill_tc_kernel<128><<<g, FA_THREADS, FaCfg<128>::SMEM, E.stream>>>(*(const CUtensorMap*)tmap_q, *(const CUtensorMap*)tmap_kv, r.row0, r.n, r.pos0, r.slot, l, n_head, n_head_kv, kq, kv, pf_X);
-                else attn_prefill_tc_kernel<64><<<g, FA_THREADS, FaCfg<64>::SMEM, E.stream>>>(*(const CUtensorMap*)tmap_q, *(const CUtensorMap*)tmap_kv, r.row0, r.n, r.pos0, r.slot, l, n_head, n_head_kv, kq, kv, pf_X);
-                E.launches++;
-            }
+            FaTiles ft; int nt = 0;
+            auto flush = [&]() {
+                if (!nt) return;
+                const dim3 g(nt, n_head);
+                if (head_dim == 128) attn_prefill_tc_kernel<128><<<g, FA_THREADS, FaCfg<128>::SMEM, E.stream>>>(*(const CUtensorMap*)tmap_q, *(const CUtensorMap*)tmap_kv, ft, l, n_head, n_head_kv, kq, kv, pf_X);
+                else attn_prefill_tc_kernel<64><<<g, FA_THREADS, FaCfg<64>::SMEM, E.stream>>>(*(const CUtensorMap*)tmap_q, *(const CUtensorMap*)tmap_kv, ft, l, n_head, n_head_kv, kq, kv, pf_X);
+                E.launches++; nt = 0;
+            };
+            for (const RowRun& r : *runs)
+                for (int o = 0; o < r.n; o += FA_BM) {
+                    ft.t[nt++] = make_int4(r.row0 + o, std::min(FA_BM, r.n - o), r.pos0 + o, r.slot);
+                    if (nt == FA_MAX_TILES) flush();
+                }
+            flush();
             CK(cudaGetLastError());
         } else {
             const int G = n_head / n_head_kv; const dim3 ag(M * n_head_kv);
@@ -1422,7 +1433,6 @@ int kernel_gemv(int type, const void* raw, int64_t N, int K, const float* x, flo
         DecodeParams P{}; P.phases = d_ph; P.n_phases = 1; P.sched_layers = 0; P.max_segs = 4; P.n_embd = K; P.n_head = 1; P.n_head_kv = 1; P.head_dim = 128; P.n_vocab = (int)N; P.n_splits = 1;
         P.cand_ll = d_cv; P.hown_cap = 4; P.pos = d_st; P.token = d_st + 1; P.bar_ctr = (unsigned*)(d_st + 2); P.epoch = (unsigned*)(d_st + 3); P.out_tokens = d_ot;
         P.logits = d_y; P.n_steps = 1; P.max_inflight = 4; if (const char* e = getenv("B200_INFLIGHT")) P.max_inflight = std::max(1, atoi(e));
-        if (const char* e = getenv("B200_L2_AHEAD_KB")) P.l2_ahead = (uint32_t)std::max(0, atoi(e)) * 1024u;
         // every step "forced" (token 0): no argmax traffic; forced[] = d_ot, zeroed, iters+1 ints
         cudaMemsetAsync(d_ot, 0, ((size_t)iters + 1) * 4, E.stream);
         DecodeRun R{}; R.forced = d_ot; R.n_forced = iters + 1;

@@ -10,6 +10,7 @@
 #include <deque>
 #include <map>
 #include <memory>
+#include <atomic>
 #include <mutex>
 #include <set>
 #include <string>
@@ -95,6 +96,8 @@ struct Model {
     float* bt_logits = nullptr; int* bt_next = nullptr; struct RowSampling* bt_samp = nullptr; __nv_bfloat16* b_out = nullptr; bool bf16_ready = false; int pages_per_seq = 0;
     int prefill_min = 32;                        // prompts shorter than this go through the decode kernel token by token
     std::mutex run_mu;
+    std::atomic<int> lock_waiters{0};            // threads that want run_mu to release the model: the scheduler steps aside for them (std::mutex is not fair)
+    void release_locked() { lock_waiters++; { std::lock_guard<std::mutex> lk(run_mu); release(); } lock_waiters--; }
 
     ~Model();
     void release();

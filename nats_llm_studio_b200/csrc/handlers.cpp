@@ -209,7 +209,7 @@ static std::string on_delete_model(const std::string& payload) {        // OnDel
     const std::string where = "hbm://" + id;
     Json data = Json::object(true); data.set("model_id", Json::string(id));
     if (!m) { data.set("dir", Json::string(where)); return envelope(false, "model directory not found: " + where, &data); }
-    { std::lock_guard<std::mutex> lk(m->run_mu); m->release(); }
+    m->release_locked();
     data.set("deleted_dir", Json::string(where));
     return envelope(true, "", &data);
 }

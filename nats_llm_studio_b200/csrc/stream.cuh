@@ -23,8 +23,8 @@
 namespace b200 {
 
 // decode_kernel_t<CFG> variants (decode.cuh): what a variant contains
-constexpr int DK_HD128 = 1, DK_HD64 = 2, DK_TP = 4, DK_Q4K = 8, DK_Q5K = 16, DK_Q6K = 32, DK_Q80 = 64;
-constexpr int DK_TYPES = DK_Q4K | DK_Q5K | DK_Q6K | DK_Q80, DK_ALL = DK_HD128 | DK_HD64 | DK_TP | DK_TYPES;
+constexpr int DK_HD128 = 1, DK_HD64 = 2, DK_TP = 4, DK_Q4K = 8, DK_Q5K = 16, DK_Q6K = 32, DK_Q80 = 64, DK_TRACE = 128;   // DK_TRACE: B200_TRACE stamps
+constexpr int DK_TYPES = DK_Q4K | DK_Q5K | DK_Q6K | DK_Q80, DK_ALL = DK_HD128 | DK_HD64 | DK_TP | DK_TYPES | DK_TRACE;
 
 #ifndef B200_GROUP_WARPS
 #define B200_GROUP_WARPS 7      // 14 consumer warps + the producer = 15 warps: at most 4 warps per scheduler, so 128 registers per thread
@@ -75,9 +75,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(CONSUMER_THREADS) : "memory"); }
@@ -156,7 +153,6 @@ struct DecodeParams {
     int* pos; int* token; int* out_tokens; unsigned* bar_ctr; unsigned* epoch;
     int n_steps; int want_argmax; int max_inflight;
     int quiet;                  // 1: the producer holds back copies of later phases while the CTA polls an exchange (see Smem::ctrl)
-    uint32_t l2_ahead;          // bytes per CTA the producer may prefetch into L2 beyond what the ring holds (0 = off)
     // tensor parallelism inside the kernel (K10): this rank's shard runs the same schedule; the partial sums of the two
     // row-parallel products of a layer and the argmax candidates are exchanged as tagged words over NVLink peer memory
     int tp_rank, tp_world;      // tp_world == 1: single GPU (nothing below is used)
@@ -198,23 +194,33 @@ __device__ __forceinline__ int phase_slot(const DecodeParams& P, int step, int i
 // One streamed slice: pairs [0, n_pairs) starting at src, n_grp groups per row, of phase `phase` of the token.
 struct Seg { const uint8_t* src; unsigned short n_pairs; unsigned char n_grp, type; unsigned short phase; unsigned char is_lm, pad; };
 static_assert(sizeof(Seg) == 16, "Seg layout");
-__host__ __device__ inline size_t smem_x_bytes(int max_grp) { return (size_t)max_grp * (2048 + 256 + 32); }
 constexpr int BTAB_MAX = 1024;           // KV pages per sequence cached in shared memory (16384 positions)
-__host__ __device__ inline size_t smem_misc_bytes(int hown_cap, int max_segs) { return NSLOT * 16 + 64 * 4 + NSLOT * 8 + 128 * 8 + ((size_t)hown_cap * 4 + 15) / 16 * 16 + BTAB_MAX * 4 + (size_t)SCHED_SLOTS * sizeof(Phase) + (size_t)max_segs * sizeof(Seg) + 64 + 64; }
-__device__ inline Smem carve_smem(uint8_t* base, uint32_t ring_bytes, int max_grp, int hown_cap) {   // hown_cap: multiple of 4
-    Smem s; s.ring = base; s.ring_bytes = ring_bytes; uint8_t* p = base + ring_bytes;
-    s.xq = (int8_t*)p; p += (size_t)max_grp * 2048;
-    s.xbs = (int16_t*)p; p += (size_t)max_grp * 256;
-    s.xd = (float*)p; p += (size_t)max_grp * 32;
-    s.full = (uint64_t*)p; p += NSLOT * 8; s.empty = (uint64_t*)p; p += NSLOT * 8;
-    s.red = (float*)p; p += 64 * 4; s.q_end = (uint32_t*)p; p += NSLOT * 4; s.q_off = (uint32_t*)p; p += NSLOT * 4; s.rope = (float2*)p; p += 128 * 8; s.hown = (float*)p; p += ((size_t)hown_cap * 4 + 15) / 16 * 16; s.btab = (int*)p; p += BTAB_MAX * 4; s.phases = (Phase*)p;
-    return s;   // segs / ctrl are placed behind the schedule by carve_tail (they need n_phases)
+constexpr int XG_MAX = 16;               // activation groups (2048 elements each) the fixed part of the layout has scale / sum slots for
+// Shared-memory layout.  Everything the stream loop and the phase changes touch sits at a COMPILE-TIME offset from the start
+// of the dynamic array (barriers, ring bookkeeping, schedule, block table, activation scales and sums, then the ring itself):
+// with the ring first and the rest behind it every one of these addresses depended on two launch parameters and was
+// re-derived (LDC, shifts, adds) inside the stage loop.  Only the int8 activation vector, the owned hidden rows and the
+// slice list, whose sizes depend on the model, follow the ring.
+struct SmemLayout {
+    static constexpr uint32_t FULL = 0, EMPTY = FULL + NSLOT * 8, Q_END = EMPTY + NSLOT * 8, Q_OFF = Q_END + NSLOT * 4, CTRL = Q_OFF + NSLOT * 4,
+                              RED = CTRL + 64, ROPE = RED + 64 * 4, BTAB = ROPE + 128 * 8, PHASES = BTAB + BTAB_MAX * 4,
+                              XD = (PHASES + SCHED_SLOTS * (uint32_t)sizeof(Phase) + 15) / 16 * 16, XBS = XD + XG_MAX * 32, RING = (XBS + XG_MAX * 256 + 127) / 128 * 128;
+};
+__host__ __device__ inline size_t smem_tail_bytes(int max_grp, int hown_cap, int max_segs) {
+    return (size_t)max_grp * 2048 + ((size_t)hown_cap * 4 + 15) / 16 * 16 + (size_t)max_segs * sizeof(Seg) + 64;
 }
-
-__device__ inline void carve_tail(Smem& s, int max_segs) {
-    uint8_t* p = (uint8_t*)(s.phases + SCHED_SLOTS); p = (uint8_t*)(((uintptr_t)p + 15) & ~(uintptr_t)15);
-    s.segs = (Seg*)p; p += (size_t)max_segs * sizeof(Seg);
-    s.ctrl = (volatile int*)p;
+__device__ inline Smem carve_smem(uint8_t* base, uint32_t ring_bytes, int max_grp, int hown_cap) {   // hown_cap: multiple of 4
+    using L = SmemLayout;
+    Smem s;
+    s.full = (uint64_t*)(base + L::FULL); s.empty = (uint64_t*)(base + L::EMPTY); s.q_end = (uint32_t*)(base + L::Q_END); s.q_off = (uint32_t*)(base + L::Q_OFF);
+    s.ctrl = (volatile int*)(base + L::CTRL); s.red = (float*)(base + L::RED); s.rope = (float2*)(base + L::ROPE); s.btab = (int*)(base + L::BTAB);
+    s.phases = (Phase*)(base + L::PHASES); s.xd = (float*)(base + L::XD); s.xbs = (int16_t*)(base + L::XBS);
+    s.ring = base + L::RING; s.ring_bytes = ring_bytes;
+    uint8_t* p = s.ring + ring_bytes;
+    s.xq = (int8_t*)p; p += (size_t)max_grp * 2048;
+    s.hown = (float*)p; p += ((size_t)hown_cap * 4 + 15) / 16 * 16;
+    s.segs = (Seg*)p;
+    return s;
 }
 
 // Deterministic ring allocator state; producer and consumers evolve identical copies.
@@ -324,12 +330,10 @@ struct Producer {
     // Whole producer warp.  Walks the stage sequence of all n_steps tokens; never waits on data dependencies, only on ring
     // space — except that, while the consumers poll an exchange (ctrl[0] = id of the last phase they completed), copies of
     // later phases are held back: the poll's replies would queue behind this SM's in-flight bulk data, and what is being
-    // fetched at that moment is never the next thing the consumers need.  While blocked on ring space the warp pulls the
-    // stages beyond the ring into L2 (cp.async.bulk.prefetch.L2), so that HBM keeps streaming through prologues and
-    // attention and the ring later refills at L2 speed.
+    // fetched at that moment is never the next thing the consumers need.  (Pulling the stages beyond the ring into L2 with
+    // cp.async.bulk.prefetch.L2 while blocked on ring space was built and measured: no gain, removed.)
     __device__ void run(const Smem& sm, const DecodeParams& P, int n_seg, int n_forced, bool logits_all, int lane) {
-        SegIter it, pf; it.init(); pf.init();
-        uint32_t issued_b = 0, pf_b = 0;                           // cumulative bytes issued to the ring / prefetched (wrap-safe differences)
+        SegIter it; it.init();
         Seg s;
         while (it.get(sm, n_seg, P.n_steps, n_forced, logits_all, s)) {
             const StageDesc d = stage_of(s, it, lane);
@@ -344,17 +348,6 @@ struct Producer {
                 const bool need_release = (cur.seq - oldest >= NSLOT) || (used + gp + bytes > sm.ring_bytes);
                 if (!quiet && !need_release) break;
                 if (need_release && mbar_test(&sm.empty[oldest % NSLOT], (oldest / NSLOT) & 1)) { used -= sm.q_end[oldest % NSLOT]; oldest++; continue; }
-                // blocked: use the time to prefetch into L2 (not while quiet — that traffic would delay the poll just the same)
-                if (!quiet && P.l2_ahead) {
-                    if ((int32_t)(pf.n - it.n) <= 0) { pf = it; pf.advance(s); pf_b = issued_b + bytes; }     // start just beyond the stage being issued
-                    Seg t;
-                    if (pf_b - (issued_b + bytes) < P.l2_ahead && pf.get(sm, n_seg, P.n_steps, n_forced, logits_all, t)) {
-                        const StageDesc e = stage_of(t, pf, lane);
-                        if (lane < e.np) bulk_prefetch_l2(e.src, e.cb);
-                        pf_b += e.np * e.cb; pf.advance(t);
-                        continue;
-                    }
-                }
                 __nanosleep(64);
             }
             uint32_t gap; const uint32_t soff = cur.place(bytes, sm.ring_bytes, gap);
@@ -363,7 +356,7 @@ struct Producer {
             if (lane == 0) { sm.q_end[slot] = gap + bytes; sm.q_off[slot] = soff; mbar_expect_tx(&sm.full[slot], bytes); }
             __syncwarp();
             if (lane < d.np) bulk_g2s(sm.ring + soff + lane * d.cb, d.src, d.cb, &sm.full[slot]);
-            cur.seq++; issued_b += bytes;
+            cur.seq++;
             it.advance(s);
         }
     }
