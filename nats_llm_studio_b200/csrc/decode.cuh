@@ -452,8 +452,12 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
 #pragma unroll
         for (int i = 0; i < 16; i++) amax = fmaxf(amax, fabsf(v[i]));
         amax = half16_max(amax);
-        if (fam_std) store_run(sm, T_Q4_K, u, v, amax);
-        if (fam_q6) store_run(s2, T_Q6_K, u, v, amax);
+        // scale rule shared with oracle/oracle.c quantise_act_256: d = amax/127, q = rint(x * (127/amax)); the codes are the
+        // same for both layout families, only their place in shared memory differs
+        const float d = amax / 127.0f, id = amax > 0.f ? 127.0f / amax : 0.f;
+        QRun q; quantise_run(v, id, q);
+        if (fam_std) store_run(sm, T_Q4_K, u, q, d);
+        if (fam_q6) store_run(s2, T_Q6_K, u, q, d);
     };
     float in_scale = 1.f;                           // factor applied to this phase's dot products in the epilogue
     if (ph.pro == PRO_NORM) {
@@ -540,9 +544,13 @@ __device__ void consume_phase(const DecodeParams& P, const Phase& ph, const Smem
     consumer_sync();
     WT(4);
     if (ph.pro == PRO_NORM) {
+        // all loads first (the loop below over shared memory compiled to 14 dependent load-add pairs), same summation order
+        float rr[(CONSUMER_WARPS + 3) / 4 * 4];
+#pragma unroll
+        for (int i = 0; i < (CONSUMER_WARPS + 3) / 4; i++) { const float4 t = *(const float4*)(sm.red + 4 * i); rr[4 * i] = t.x; rr[4 * i + 1] = t.y; rr[4 * i + 2] = t.z; rr[4 * i + 3] = t.w; }
         float tot = 0.f;
 #pragma unroll
-        for (int i = 0; i < CONSUMER_WARPS; i++) tot += sm.red[i];
+        for (int i = 0; i < CONSUMER_WARPS; i++) tot += rr[i];
         in_scale = rsqrtf(tot / (float)ph.K + P.rms_eps);
     }
     if (tr && tid == 0) tr[3] = gtime();

@@ -372,22 +372,25 @@ struct Producer {
 // ------------------------------------------------------------------------------------ activation prologue
 // Quantise 16 consecutive activations (one "run") and store them engine-permuted.
 // Scale rule (shared with oracle/oracle.c quantise_act_256): d = amax/127, q = rint(x * (127/amax)).
-__device__ __forceinline__ void store_run(const Smem& sm, int type, int u_global, const float v[16], float amax256) {
-    float d = amax256 / 127.0f, id = amax256 > 0.f ? 127.0f / amax256 : 0.f;
-    int grp = u_global / 128, u = u_global % 128, L, plane; act_slot(type, u, L, plane);
-    uint32_t w[4]; int bs = 0;
+// A quantised run: 16 int8 codes in four words and their sum.  cvt.pack.sat saturates to [-128, 127]; the scale rule maps
+// |x| <= amax to |x * id| <= 127 (+ 1 ulp), so -128 is never produced and the result equals the oracle's clamp to +-127.
+struct QRun { uint32_t w[4]; int bs; };
+__device__ __forceinline__ uint32_t pack_s8x2(int hi, int lo, uint32_t upper) {      // (upper << 16) | (s8(hi) << 8) | s8(lo)
+    uint32_t d; asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(hi), "r"(lo), "r"(upper)); return d;
+}
+__device__ __forceinline__ void quantise_run(const float v[16], float id, QRun& q) {
+    q.bs = 0;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-        uint32_t pk = 0;
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            int q = __float2int_rn(v[4 * i + j] * id); q = max(-127, min(127, q)); bs += q;
-            pk |= (uint32_t)(q & 0xff) << (8 * j);
-        }
-        w[i] = pk;
+        const int a0 = __float2int_rn(v[4 * i] * id), a1 = __float2int_rn(v[4 * i + 1] * id), a2 = __float2int_rn(v[4 * i + 2] * id), a3 = __float2int_rn(v[4 * i + 3] * id);
+        q.w[i] = pack_s8x2(a1, a0, pack_s8x2(a3, a2, 0u));
+        q.bs = __dp4a((int)q.w[i], 0x01010101, q.bs);
     }
-    *(uint4*)(sm.xq + (size_t)grp * 2048 + plane * 512 + L * 16) = make_uint4(w[0], w[1], w[2], w[3]);
-    sm.xbs[grp * 128 + L * 4 + plane] = (int16_t)bs;
+}
+__device__ __forceinline__ void store_run(const Smem& sm, int type, int u_global, const QRun& q, float d) {
+    int grp = u_global / 128, u = u_global % 128, L, plane; act_slot(type, u, L, plane);
+    *(uint4*)(sm.xq + (size_t)grp * 2048 + plane * 512 + L * 16) = make_uint4(q.w[0], q.w[1], q.w[2], q.w[3]);
+    sm.xbs[grp * 128 + L * 4 + plane] = (int16_t)q.bs;
     if ((u_global & 15) == 0) sm.xd[u_global / 16] = d;
 }
 
