@@ -47,9 +47,14 @@ __device__ __forceinline__ void tmem_ld_x32(uint32_t taddr, uint32_t* r) { tmem_
 constexpr int FA_MAX_TILES = 64;
 struct FaTiles { int4 t[FA_MAX_TILES]; };
 
-template <int HD>
+// DEC (batched decode step): one CTA per (token m, kv head).  The query tile is the G heads that share the kv head — rows
+// m * n_head + kvh * G .. of Q viewed as [token * head][head_dim] (tmap_q is that view) — all at the token's position; the
+// other rows of the 128-row MMA tile are whatever follows in Q (never stored), so only warp 0 runs the softmax.  Position and
+// slot come from the step's device-side row map (the step is a CUDA graph: nothing position-dependent may sit in the
+// launch parameters).  The output is written the way the dequant-in-GEMM kernel wants its activations: fp16, kperm4 order.
+template <int HD, bool DEC>
 __global__ void __launch_bounds__(FA_THREADS, 1)
-attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv, const __grid_constant__ FaTiles tiles, int layer,
+attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv, const __grid_constant__ FaTiles tiles, RowMap rm, int G, int layer,
                        int n_head, int n_head_kv, float kq_scale, KvLayout kv, __nv_bfloat16* __restrict__ O) {
     using C = FaCfg<HD>;
     extern __shared__ uint8_t fa_smem_raw[];
@@ -58,18 +63,19 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_
     uint64_t* bars = (uint64_t*)(base + 5 * (size_t)C::TILE_BYTES);
     uint64_t *q_full = bars, *k_full = bars + 1 /*[2]*/, *v_full = bars + 3 /*[2]*/, *s_done = bars + 5, *o_done = bars + 6; uint32_t* tmem_slot = (uint32_t*)(bars + 8);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int head = blockIdx.y, kvh = head / (n_head / n_head_kv);
-    const int4 tile = tiles.t[blockIdx.x];
-    const int row_t = tile.x, rows_here = tile.y, pos_t = tile.z, slot = tile.w;
-    const int last_pos = pos_t + rows_here - 1;                       // newest position any row of this tile may see
-    const int n_kv_tiles = last_pos / FA_BN + 1;
+    const int head = blockIdx.y, kvh = DEC ? (int)blockIdx.y : head / (n_head / n_head_kv);
     if (tid == 0) { for (int i = 0; i < 7; i++) mbar_init(&bars[i], 1); fence_barrier_init(); }
     if (warp == 0) tcgen05_alloc(tmem_slot, C::TM_COLS);
     tcgen05_fence_before();
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem = *tmem_slot;
-    pdl_launch_dependents(); pdl_wait();
+    pdl_launch_dependents(); pdl_wait();                              // Q, the new K/V rows (and the row map's owner) come from the preceding kernels
+    int row_t, rows_here, pos_t, slot;
+    if constexpr (DEC) { const int m = blockIdx.x; row_t = m * n_head + kvh * G; rows_here = G; pos_t = rm.p(m); slot = rm.s(m); }
+    else { const int4 tile = tiles.t[blockIdx.x]; row_t = tile.x; rows_here = tile.y; pos_t = tile.z; slot = tile.w; }
+    const int last_pos = DEC ? pos_t : pos_t + rows_here - 1;         // newest position any row of this tile may see
+    const int n_kv_tiles = last_pos / FA_BN + 1;
 
     // one KV tile: 8 pages x PANELS boxes of (64 columns x 16 positions) for K, the same for V
     auto load_kv = [&](int j, int buf) {
@@ -86,10 +92,10 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_
     };
     if (tid == 0) {
         mbar_expect_tx(q_full, C::TILE_BYTES);
-        for (int pn = 0; pn < C::PANELS; pn++) tma_load_2d(sQ + (size_t)pn * (FA_BM * 128), &tmap_q, head * HD + pn * 64, row_t, q_full);
+        for (int pn = 0; pn < C::PANELS; pn++) tma_load_2d(sQ + (size_t)pn * (FA_BM * 128), &tmap_q, (DEC ? 0 : head * HD) + pn * 64, row_t, q_full);
         load_kv(0, 0);
     }
-    const int my_pos = pos_t + tid;                                   // position of this thread's query row
+    const int my_pos = DEC ? pos_t : pos_t + tid;                     // position of this thread's query row
     const float sl2 = kq_scale * 1.4426950408889634f;                 // scores are kept in log2 units: exp2f((s - m) * sl2)
     float m_run = -INFINITY, l_run = 0.f;
     const uint32_t lane_off = (uint32_t)(warp * 32) << 16;            // this warp's quarter of the TMEM lanes
@@ -116,6 +122,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_
         mbar_wait(s_done, j & 1);
         __syncwarp();
         tcgen05_fence_after();
+        if (!DEC || warp == 0) {                                       // DEC: the real rows (the G heads) all sit in warp 0's lanes
         // two passes over the row's 128 scores, 32 at a time (registers): the maximum, then the probabilities
         const int kv0 = j * FA_BN;
         float m_new = m_run;
@@ -153,6 +160,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_
                 tmem_st_x32(tmem + C::TM_O + lane_off + c, o);
             }
         }
+        }
         tmem_st_wait();
         tcgen05_fence_before();
         __syncthreads();
@@ -174,6 +182,27 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_
     __syncwarp();
     tcgen05_fence_after();
     const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+    if constexpr (DEC) {
+        // rows of Q seen as [token * head][head_dim] are rows of O in the same view; fp16 in kperm4 order (0, 2, 1, 3 inside
+        // every aligned group of four) for the dequant-in-GEMM kernel that consumes them
+        if (warp == 0) {
+#pragma unroll 1
+            for (int c = 0; c < HD; c += 32) {
+                uint32_t o[32]; tmem_ld_x32(tmem + C::TM_O + lane_off + c, o);
+                if (tid < rows_here) {
+                    __half* dst = (__half*)O + (size_t)(row_t + tid) * HD + c;
+#pragma unroll
+                    for (int i = 0; i < 32; i += 8) {
+                        uint4 w;
+                        const __half2 t0 = __floats2half2_rn(clamp_h(__uint_as_float(o[i]) * inv), clamp_h(__uint_as_float(o[i + 2]) * inv)), t1 = __floats2half2_rn(clamp_h(__uint_as_float(o[i + 1]) * inv), clamp_h(__uint_as_float(o[i + 3]) * inv));
+                        const __half2 t2 = __floats2half2_rn(clamp_h(__uint_as_float(o[i + 4]) * inv), clamp_h(__uint_as_float(o[i + 6]) * inv)), t3 = __floats2half2_rn(clamp_h(__uint_as_float(o[i + 5]) * inv), clamp_h(__uint_as_float(o[i + 7]) * inv));
+                        w.x = *(const uint32_t*)&t0; w.y = *(const uint32_t*)&t1; w.z = *(const uint32_t*)&t2; w.w = *(const uint32_t*)&t3;
+                        *(uint4*)(dst + i) = w;
+                    }
+                }
+            }
+        }
+    } else {
     const int row = row_t + tid;
 #pragma unroll 1
     for (int c = 0; c < HD; c += 32) {
@@ -189,6 +218,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_
                 *(uint4*)(dst + i) = w;
             }
         }
+    }
     }
     tcgen05_fence_before();
     __syncthreads();

@@ -270,7 +270,7 @@ void Model::release() {
     d_phases = nullptr; n_phases = 0; d_logits = nullptr; d_ll16 = nullptr; d_ll32 = nullptr;
     d_state = d_out_tokens = d_forced = d_block_table = nullptr; d_kv = nullptr; n_pages = 0; cur_pos = 0;
     pf_H = pf_Y = nullptr; pf_X = pf_Q = pf_ACT = pf_W = nullptr; pf_toks = nullptr; pf_T = nullptr;
-    bt_logits = nullptr; bt_next = nullptr; bt_samp = nullptr; b_out = nullptr; tmap_q = tmap_kv = nullptr;
+    bt_logits = nullptr; bt_next = nullptr; bt_samp = nullptr; b_out = nullptr; tmap_q = tmap_kv = tmap_qd = nullptr;
     bf16_ready = bf16_tried = tile_ready = false;
     hbm_bytes = 0; weight_bytes = 0; uploaded = 0; t_done.clear(); rope_ff.clear();
 }
@@ -1027,15 +1027,26 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
         // prompt chunks made of whole runs of one sequence each: causal attention on the tensor cores (attn_tc.cuh)
         const bool tc_off = getenv("B200_NO_ATTN_TC") != nullptr;       // read per call: tests compare the two attention kernels in one process
         const bool tc = !q && runs && !runs->empty() && !tc_off;        // every prompt chunk, whatever it is made of: a request's numerics must not depend on its neighbours
-        CK(launch_pdl(rope_kv_rows_kernel, dim3(nblk((long long)M * W3 / 2)), dim3(256), 0, E.stream, (const float*)pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, (const float*)inv_freq, kv, pf_Q, sp, tc)); E.launches++; sp = none;
-        if (tc) {
+        // batched decode step: the same kernel in its DEC form (one CTA per (token, kv head), the G heads of the group as query
+        // rows) is correct (the whole GPU suite passes with it) but SLOWER than attn_rows_kernel at B = 64, ctx 512: 6.49 ms per
+        // step against 4.81 — one 160 KB CTA per SM walks its KV tiles serially.  Opt-in (B200_ATTN_TC_DEC=1) until it runs two
+        // CTAs per SM (2 KB query tile, P aliased onto S in tensor memory: 256 columns).
+        const bool tc_dec = q && !tc_off && getenv("B200_ATTN_TC_DEC") != nullptr && n_head / n_head_kv <= 32 && M <= PREFILL_CHUNK;
+        CK(launch_pdl(rope_kv_rows_kernel, dim3(nblk((long long)M * W3 / 2)), dim3(256), 0, E.stream, (const float*)pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, (const float*)inv_freq, kv, pf_Q, sp, tc || tc_dec)); E.launches++; sp = none;
+        if (tc_dec) {
+            if (int rc2 = ensure_attn_maps()) return rc2;
+            const dim3 g(M, n_head_kv); const FaTiles ft{}; const int G = n_head / n_head_kv;
+            if (head_dim == 128) CK(launch_pdl(attn_prefill_tc_kernel<128, true>, g, dim3(FA_THREADS), FaCfg<128>::SMEM, E.stream, *(const CUtensorMap*)tmap_qd, *(const CUtensorMap*)tmap_kv, ft, rm, G, l, n_head, n_head_kv, kq, kv, pf_X));
+            else CK(launch_pdl(attn_prefill_tc_kernel<64, true>, g, dim3(FA_THREADS), FaCfg<64>::SMEM, E.stream, *(const CUtensorMap*)tmap_qd, *(const CUtensorMap*)tmap_kv, ft, rm, G, l, n_head, n_head_kv, kq, kv, pf_X));
+            E.launches++;
+        } else if (tc) {
             if (int rc2 = ensure_attn_maps()) return rc2;
             FaTiles ft; int nt = 0;
             auto flush = [&]() {
                 if (!nt) return;
                 const dim3 g(nt, n_head);
-                if (head_dim == 128) attn_prefill_tc_kernel<128><<<g, FA_THREADS, FaCfg<128>::SMEM, E.stream>>>(*(const CUtensorMap*)tmap_q, *(const CUtensorMap*)tmap_kv, ft, l, n_head, n_head_kv, kq, kv, pf_X);
-                else attn_prefill_tc_kernel<64><<<g, FA_THREADS, FaCfg<64>::SMEM, E.stream>>>(*(const CUtensorMap*)tmap_q, *(const CUtensorMap*)tmap_kv, ft, l, n_head, n_head_kv, kq, kv, pf_X);
+                if (head_dim == 128) attn_prefill_tc_kernel<128, false><<<g, FA_THREADS, FaCfg<128>::SMEM, E.stream>>>(*(const CUtensorMap*)tmap_q, *(const CUtensorMap*)tmap_kv, ft, rm, 0, l, n_head, n_head_kv, kq, kv, pf_X);
+                else attn_prefill_tc_kernel<64, false><<<g, FA_THREADS, FaCfg<64>::SMEM, E.stream>>>(*(const CUtensorMap*)tmap_q, *(const CUtensorMap*)tmap_kv, ft, rm, 0, l, n_head, n_head_kv, kq, kv, pf_X);
                 E.launches++; nt = 0;
             };
             for (const RowRun& r : *runs)
@@ -1148,9 +1159,9 @@ int Model::ensure_attn_maps() {
     EncodeTiledFn f = encode_tiled();
     if (!f) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
     static_assert(sizeof(CUtensorMap) == 128, "tensor map size");
-    tmap_storage.assign(2 * sizeof(CUtensorMap) + 64, 0);
+    tmap_storage.assign(3 * sizeof(CUtensorMap) + 64, 0);
     uint8_t* al = (uint8_t*)(((uintptr_t)tmap_storage.data() + 63) & ~(uintptr_t)63);
-    CUtensorMap* mq = (CUtensorMap*)al; CUtensorMap* mkv = mq + 1;
+    CUtensorMap* mq = (CUtensorMap*)al; CUtensorMap* mkv = mq + 1; CUtensorMap* mqd = mq + 2;
     const uint64_t QD = (uint64_t)n_head * head_dim;
     {
         cuuint64_t dims[2] = {QD, (cuuint64_t)PREFILL_CHUNK}, strides[1] = {QD * 2}; cuuint32_t box[2] = {64, (cuuint32_t)FA_BM}, estr[2] = {1, 1};
@@ -1163,9 +1174,16 @@ int Model::ensure_attn_maps() {
         CUresult r = f(mkv, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, d_kv, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled (KV) failed: " + std::to_string((int)r));
     }
-    CK(cudaFuncSetAttribute(attn_prefill_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FaCfg<128>::SMEM));
-    CK(cudaFuncSetAttribute(attn_prefill_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FaCfg<64>::SMEM));
-    tmap_q = mq; tmap_kv = mkv;
+    {   // Q of a decode step seen as [token * head][head_dim]: the G heads of a kv group are G consecutive rows
+        cuuint64_t dims[2] = {(cuuint64_t)head_dim, (cuuint64_t)PREFILL_CHUNK * n_head}, strides[1] = {(cuuint64_t)head_dim * 2}; cuuint32_t box[2] = {64, (cuuint32_t)FA_BM}, estr[2] = {1, 1};
+        CUresult r = f(mqd, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, pf_Q, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled (Q, decode view) failed: " + std::to_string((int)r));
+    }
+    CK(cudaFuncSetAttribute(attn_prefill_tc_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FaCfg<128>::SMEM));
+    CK(cudaFuncSetAttribute(attn_prefill_tc_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FaCfg<64>::SMEM));
+    CK(cudaFuncSetAttribute(attn_prefill_tc_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FaCfg<128>::SMEM));
+    CK(cudaFuncSetAttribute(attn_prefill_tc_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FaCfg<64>::SMEM));
+    tmap_q = mq; tmap_kv = mkv; tmap_qd = mqd;
     return B200_OK;
 }
 

@@ -125,7 +125,7 @@ struct Model {
     bool tile_ready = false;
     struct RowRun { int row0, n, pos0, slot; };      // rows [row0, row0+n) of a chunk = positions pos0.. of sequence `slot`
     int dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_slot, int pos0, int slot0, bool want_logits, bool q, const std::vector<RowRun>* runs = nullptr);
-    int ensure_attn_maps(); void* tmap_q = nullptr; void* tmap_kv = nullptr; std::vector<uint8_t> tmap_storage;
+    int ensure_attn_maps(); void* tmap_q = nullptr; void* tmap_kv = nullptr; void* tmap_qd = nullptr; std::vector<uint8_t> tmap_storage;
     int prefill_rows(const int32_t* toks, const int32_t* slots, const int32_t* pos, int M);
     void maybe_bf16_cache();
     bool bf16_tried = false;
