@@ -200,44 +200,50 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_
 }
 
 // ------------------------------------------------------------------------------------ batched decode step
-// attn_decode_tc_kernel: the same two MMAs for ONE new position per sequence.  One CTA per (token m, kv head); the query
-// tile is the G heads that share the kv head — rows m * n_head + kvh * G .. of Q viewed as [token * head][head_dim]
-// (tmap_qd is that view, box of 8 rows) — all at the token's position.  Built to run TWO CTAs per SM, since a CTA walks
-// its KV tiles serially and the step is bound by how many bytes an SM keeps in flight:
-//   * the query tile is the 8-row swizzle atom per 64-column panel (1 KB); the MMA's other 120 A rows read whatever
-//     follows in shared memory (finite garbage), their accumulator rows are never read;
-//   * K and V are single-buffered (32 KB each at head size 128): K(j+1) is requested as soon as S(j) has been computed,
-//     V(j+1) as soon as O += P.V (j) has — each load runs under the other operand's work;
-//   * P overwrites S in tensor memory (pass 2 of the softmax writes columns [c/2, c/2+16) after reading [c, c+32)), so
-//     S|P + O fit 256 columns and two CTAs share the SM's 512;
-//   * only warp 0 holds real rows (G <= 8 of its lanes): it alone runs the softmax; a second warp issues the TMA boxes
-//     (one per lane) and the MMAs; the sequence's block table is read into shared memory once, in one round trip.
-// Position and slot come from the step's device-side row map (the step is a CUDA graph: nothing position-dependent
-// may sit in the launch parameters).  Output: fp16 in kperm4 order, the activation format of qgemm_kernel.
-template <int HD> struct FdCfg {
-    static constexpr int PANELS = HD / 64;
-    static constexpr uint32_t Q_BYTES = PANELS * 1024, KV_BYTES = FA_BN * HD * 2;          // 8 query rows | one K or V tile
-    // the A descriptor of the last panel reads 16 KB from its start: K's buffer follows Q, so that stays inside the allocation
-    static constexpr size_t SMEM = 1024 + 1024 * ((Q_BYTES + 1023) / 1024) + 2 * (size_t)KV_BYTES + 64 + BTAB_MAX * 4 + 64;   // + barriers + block table
-    static constexpr uint32_t TM_S = 0, TM_O = 128, TM_COLS = 256;
+// attn_decode_tc_kernel: attention for ONE new position per sequence, one CTA per (token m, kv head), with the MMA operands
+// SWAPPED so that every tensor-memory lane holds real data:
+//   S^T = K . Q^T     A = the K tile (M = 128 positions), B = the G query heads of the kv group padded to N = 16 rows
+//                     (rows m * n_head + kvh * G .. of Q viewed as [token * head][head_dim]); lane t = position t
+//   softmax           thread t owns position t: G scores from one tcgen05.ld, the per-head maximum by warp shuffles and one
+//                     block barrier, G exponentials, P^T written to shared memory (fp16, 128-byte swizzle, K-major B operand)
+//   O^T += V^T . P    A = the V tile as it lies in the cache ([position][head_dim] = M-major A), B = P^T; lane d = output
+//                     dimension d, 16 columns = heads; rescaled in place per column when a head's maximum moves
+// 32 TMEM columns and 76 KB of shared memory per CTA: three CTAs per SM cover each other's serial load -> S -> softmax ->
+// P.V chain.  (The query-rows-as-M form, G real rows of 128 and one warp doing the whole softmax, measured 5.4 - 6.5 ms per
+// B = 64 step against 4.81 for the CUDA-core kernel.)  Position and slot come from the step's device-side row map (the
+// step is a CUDA graph).  Output: fp16 in kperm4 order, the activation format of qgemm_kernel.  Head size 128 only.
+constexpr int FD_THREADS = 128, FD_N = 16, FD_BTAB = 256;          // FD_BTAB pages = 4096 positions per sequence
+struct FdCfg {
+    static constexpr uint32_t KV_BYTES = FA_BN * 128 * 2, QP_BYTES = 2 * FD_N * 128;        // one K or V tile | Q or P^T: 2 panels x 16 rows x 128 B
+    static constexpr size_t SMEM = 1024 + 2 * (size_t)QP_BYTES + 2 * (size_t)KV_BYTES + 64 + 4 * FD_N * 4 + FD_BTAB * 4;
+    static constexpr uint32_t TM_S = 0, TM_O = FD_N, TM_COLS = 32;
 };
+__host__ __device__ constexpr uint32_t fd_idesc(int M, int N, bool a_mn) {      // fp16 x fp16 -> fp32; a_mn: A operand is M-major
+    return (1u << 4) | (0u << 7) | (0u << 10) | ((a_mn ? 1u : 0u) << 15) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void tmem_ld_x16(uint32_t taddr, uint32_t* r) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n\ttcgen05.wait::ld.sync.aligned;"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-constexpr int FD_THREADS = 64;      // warp 0: softmax of the G real rows (TMEM lanes 0..31); warp 1: TMA loads and MMA issue
-template <int HD>
-__global__ void __launch_bounds__(FD_THREADS, 2)
+__global__ void __launch_bounds__(FD_THREADS, 3)
 attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_qd, const __grid_constant__ CUtensorMap tmap_kv, RowMap rm, int G, int layer,
                       int n_head, int n_head_kv, float kq_scale, KvLayout kv, __half* __restrict__ O) {
-    using C = FdCfg<HD>;
+    using C = FdCfg; constexpr int HD = 128;
     extern __shared__ uint8_t fd_smem_raw[];
     uint8_t* base = (uint8_t*)(((uintptr_t)fd_smem_raw + 1023) & ~(uintptr_t)1023);
-    uint8_t* sQ = base; uint8_t* sK = base + 1024 * ((C::Q_BYTES + 1023) / 1024); uint8_t* sV = sK + C::KV_BYTES;
+    uint8_t* sQ = base; uint8_t* sP = sQ + C::QP_BYTES; uint8_t* sK = sP + C::QP_BYTES; uint8_t* sV = sK + C::KV_BYTES;
     uint64_t* bars = (uint64_t*)(sV + C::KV_BYTES);
-    uint64_t *q_full = bars, *k_full = bars + 1, *v_full = bars + 2, *s_done = bars + 3, *o_done = bars + 4, *p_full = bars + 5; uint32_t* tmem_slot = (uint32_t*)(bars + 6);
-    int* s_bt = (int*)(bars + 8);                                      // this sequence's block table (pages of 16 positions)
+    uint64_t *q_full = bars, *k_full = bars + 1, *v_full = bars + 2, *s_done = bars + 3, *o_done = bars + 4; uint32_t* tmem_slot = (uint32_t*)(bars + 6);
+    float* red = (float*)(bars + 8);                                   // [4 warps][FD_N]
+    int* s_bt = (int*)(red + 4 * FD_N);                                // this sequence's block table (pages of 16 positions)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int m = blockIdx.x, kvh = blockIdx.y;
-    if (tid == 0) { for (int i = 0; i < 6; i++) mbar_init(&bars[i], 1); fence_barrier_init(); }
+    if (tid == 0) { for (int i = 0; i < 5; i++) mbar_init(&bars[i], 1); fence_barrier_init(); }
     if (warp == 0) tcgen05_alloc(tmem_slot, C::TM_COLS);
+    for (int i = tid; i < (int)C::QP_BYTES / 16; i += FD_THREADS) ((uint4*)sP)[i] = make_uint4(0, 0, 0, 0);      // rows >= G of P^T stay zero
     pdl_launch_dependents(); pdl_wait();                              // Q and the new K/V rows come from the preceding kernels
     const int row_t = m * n_head + kvh * G, pos = rm.p(m), slot = rm.s(m);
     const int n_kv_tiles = pos / FA_BN + 1;
@@ -246,121 +252,122 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_qd, const __grid_
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem = *tmem_slot;
+    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;            // this warp's quarter of the TMEM lanes
     const float sl2 = kq_scale * 1.4426950408889634f;                 // scores are kept in log2 units: exp2f((s - m) * sl2)
 
-    if (warp == 1) {
-        // ===== loads and MMAs.  A tile = 8 pages x PANELS boxes of 64 columns x 16 positions; lane i issues box i =====
-        auto load_tile = [&](int j, int which, uint8_t* dst, uint64_t* bar) {      // which: 0 = K, 1 = V
-            if (lane == 0) mbar_expect_tx(bar, C::KV_BYTES);
-            __syncwarp();
-            for (int b = lane; b < (FA_BN / 16) * C::PANELS; b += 32) {
-                const int pg = b / C::PANELS, pn = b % C::PANELS;
-                const int p = min(j * FA_BN + pg * 16, pos);       // pages beyond the position: re-read a valid page (masked in the softmax)
-                const int r = (int)(((((size_t)layer * kv.n_pages + s_bt[p >> 4]) * 2 + which) * kv.n_head_kv + kvh) * 16);
-                tma_load_2d(dst + (size_t)pn * (FA_BN * 128) + (size_t)pg * 2048, &tmap_kv, pn * 64, r, bar);
-            }
-        };
-        if (lane == 0) { mbar_expect_tx(q_full, C::Q_BYTES); for (int pn = 0; pn < C::PANELS; pn++) tma_load_2d(sQ + (size_t)pn * 1024, &tmap_qd, pn * 64, row_t, q_full); }
+    // a tile = 8 pages x 2 boxes of 64 columns x 16 positions; lane i of warp 0 issues box i
+    auto load_tile = [&](int j, int which, uint8_t* dst, uint64_t* bar) {      // which: 0 = K, 1 = V; called by all of warp 0
+        if (lane == 0) mbar_expect_tx(bar, C::KV_BYTES);
+        __syncwarp();
+        if (lane < 16) {
+            const int pg = lane >> 1, pn = lane & 1;
+            const int p = min(j * FA_BN + pg * 16, pos);           // pages beyond the position: re-read a valid page (masked in the softmax)
+            const int r = (int)(((((size_t)layer * kv.n_pages + s_bt[p >> 4]) * 2 + which) * kv.n_head_kv + kvh) * 16);
+            tma_load_2d(dst + (size_t)pn * (FA_BN * 128) + (size_t)pg * 2048, &tmap_kv, pn * 64, r, bar);
+        }
+    };
+    if (warp == 0) {
+        if (lane == 0) { mbar_expect_tx(q_full, C::QP_BYTES); for (int pn = 0; pn < 2; pn++) tma_load_2d(sQ + (size_t)pn * (FD_N * 128), &tmap_qd, pn * 64, row_t, q_full); }
         load_tile(0, 0, sK, k_full); load_tile(0, 1, sV, v_full);
-        for (int j = 0; j < n_kv_tiles; j++) {
-            const uint32_t ph = j & 1;
+    }
+    float m_run[8], l_part[8];
+#pragma unroll
+    for (int g = 0; g < 8; g++) { m_run[g] = -INFINITY; l_part[g] = 0.f; }
+    for (int j = 0; j < n_kv_tiles; j++) {
+        const uint32_t ph = j & 1;
+        if (warp == 0) {
             if (lane == 0) {
                 if (j == 0) mbar_wait(q_full, 0);
                 mbar_wait(k_full, ph);
                 tcgen05_fence_after();
-                constexpr uint32_t idesc = fa_idesc(FA_BM, FA_BN, false);
+                constexpr uint32_t idesc = fd_idesc(FA_BN, FD_N, false);
 #pragma unroll
-                for (int k = 0; k < HD / 16; k++) {                    // S = Q . K^T: 16 head-dim columns per instruction
-                    const uint64_t da = umma_desc_sw128(sQ + (size_t)(k / 4) * 1024) + 2 * (k % 4);
-                    const uint64_t db = umma_desc_sw128(sK + (size_t)(k / 4) * (FA_BN * 128)) + 2 * (k % 4);
+                for (int k = 0; k < HD / 16; k++) {                    // S^T = K . Q^T: 16 head-dim columns per instruction
+                    const uint64_t da = umma_desc_sw128(sK + (size_t)(k / 4) * (FA_BN * 128)) + 2 * (k % 4);
+                    const uint64_t db = umma_desc_sw128(sQ + (size_t)(k / 4) * (FD_N * 128)) + 2 * (k % 4);
                     tcgen05_mma_f16(tmem + C::TM_S, da, db, idesc, k ? 1u : 0u);
                 }
                 tcgen05_commit(s_done);
-                mbar_wait(s_done, ph);                                 // S(j) has read K: the buffer takes the next tile
+                if (j > 0) mbar_wait(o_done, (j - 1) & 1);             // P.V(j-1) has read V: the buffer takes this tile's V
             }
             __syncwarp();
-            if (j + 1 < n_kv_tiles) load_tile(j + 1, 0, sK, k_full);
-            if (lane == 0) {
-                mbar_wait(p_full, ph);                                 // the softmax warp has written P(j) (and rescaled O)
-                mbar_wait(v_full, ph);
-                tcgen05_fence_after();
-                constexpr uint32_t idesc = fa_idesc(FA_BM, HD, true);
-#pragma unroll
-                for (int k = 0; k < FA_BN / 16; k++) {                 // O += P . V: 16 positions per instruction
-                    const uint64_t db = umma_desc_mn_sw128(sV + (size_t)k * 2048, FA_BN * 128);
-                    tcgen05_mma_f16_ts(tmem + C::TM_O, tmem + C::TM_S + k * 8, db, idesc, (j | k) ? 1u : 0u);
-                }
-                tcgen05_commit(o_done);
-                mbar_wait(o_done, ph);                                 // P.V(j) has read V (and P: S(j+1) may overwrite it)
-            }
-            __syncwarp();
-            if (j + 1 < n_kv_tiles) load_tile(j + 1, 1, sV, v_full);
+            if (j > 0) load_tile(j, 1, sV, v_full);
         }
-    } else {
-        // ===== softmax: lane r owns query row r (rows >= G are other heads' queries or zero fill: computed, never stored) =====
-        float m_run = -INFINITY, l_run = 0.f;
-        for (int j = 0; j < n_kv_tiles; j++) {
-            mbar_wait(s_done, j & 1);                                  // commit order: S(j) done implies P.V(j-1) done, so O may be rescaled
-            __syncwarp();
-            tcgen05_fence_after();
-            const int kv0 = j * FA_BN;
-            float m_new = m_run;
-#pragma unroll 1
-            for (int c = 0; c < FA_BN; c += 32) {
-                uint32_t sc[32]; tmem_ld_x32(tmem + C::TM_S + c, sc);
-#pragma unroll
-                for (int i = 0; i < 32; i++) if (kv0 + c + i <= pos) m_new = fmaxf(m_new, __uint_as_float(sc[i]));      // positions past the token's own are masked
-            }
-            const float corr = m_run == -INFINITY ? 0.f : exp2f((m_run - m_new) * sl2);
-            float l_add = 0.f;
-#pragma unroll 1
-            for (int c = 0; c < FA_BN; c += 32) {                      // P overwrites S: columns [c/2, c/2+16) <- scores [c, c+32), all of them read before
-                uint32_t sc[32], pk[16]; tmem_ld_x32(tmem + C::TM_S + c, sc);
-#pragma unroll
-                for (int i = 0; i < 32; i += 2) {
-                    const float p0 = kv0 + c + i <= pos ? exp2f((__uint_as_float(sc[i]) - m_new) * sl2) : 0.f;
-                    const float p1 = kv0 + c + i + 1 <= pos ? exp2f((__uint_as_float(sc[i + 1]) - m_new) * sl2) : 0.f;
-                    const __half2 h = __floats2half2_rn(p0, p1);
-                    const float2 back = __half22float2(h); l_add += back.x + back.y;      // the sum uses the rounded values the MMA will see
-                    pk[i / 2] = *(const uint32_t*)&h;
-                }
-                tmem_st_x8(tmem + C::TM_S + c / 2, pk); tmem_st_x8(tmem + C::TM_S + c / 2 + 8, pk + 8);
-            }
-            l_run = l_run * corr + l_add; m_run = m_new;
-            if (j > 0) {                                               // O *= corr, in place
-#pragma unroll 1
-                for (int c = 0; c < HD; c += 32) {
-                    uint32_t o[32]; tmem_ld_x32(tmem + C::TM_O + c, o);
-#pragma unroll
-                    for (int i = 0; i < 32; i++) o[i] = __float_as_uint(__uint_as_float(o[i]) * corr);
-                    tmem_st_x32(tmem + C::TM_O + c, o);
-                }
-            }
-            tmem_st_wait();
-            tcgen05_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(p_full);
-        }
-        // ---- epilogue: rows of Q in the [token * head][head_dim] view are rows of O in the same view
-        mbar_wait(o_done, (n_kv_tiles - 1) & 1);
+        mbar_wait(s_done, ph);
         __syncwarp();
         tcgen05_fence_after();
-        const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-#pragma unroll 1
-        for (int c = 0; c < HD; c += 32) {
-            uint32_t o[32]; tmem_ld_x32(tmem + C::TM_O + c, o);
-            if (lane < G) {
-                __half* dst = O + (size_t)(row_t + lane) * HD + c;
+        if (warp == 0 && j + 1 < n_kv_tiles) load_tile(j + 1, 0, sK, k_full);      // S^T(j) has read K
+        // ---- softmax: this thread's position against the G heads
+        uint32_t sc[16]; tmem_ld_x16(tmem + C::TM_S + lane_off, sc);
+        const bool ok = j * FA_BN + tid <= pos;                        // positions past the token's own are masked
+        float mx[8];
 #pragma unroll
-                for (int i = 0; i < 32; i += 8) {                      // kperm4: (0, 2, 1, 3) inside every aligned group of four
-                    uint4 w;
-                    const __half2 t0 = __floats2half2_rn(clamp_h(__uint_as_float(o[i]) * inv), clamp_h(__uint_as_float(o[i + 2]) * inv)), t1 = __floats2half2_rn(clamp_h(__uint_as_float(o[i + 1]) * inv), clamp_h(__uint_as_float(o[i + 3]) * inv));
-                    const __half2 t2 = __floats2half2_rn(clamp_h(__uint_as_float(o[i + 4]) * inv), clamp_h(__uint_as_float(o[i + 6]) * inv)), t3 = __floats2half2_rn(clamp_h(__uint_as_float(o[i + 5]) * inv), clamp_h(__uint_as_float(o[i + 7]) * inv));
-                    w.x = *(const uint32_t*)&t0; w.y = *(const uint32_t*)&t1; w.z = *(const uint32_t*)&t2; w.w = *(const uint32_t*)&t3;
-                    *(uint4*)(dst + i) = w;
-                }
-            }
+        for (int g = 0; g < 8; g++) {
+            float v = (ok && g < G) ? __uint_as_float(sc[g]) : -INFINITY;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+            mx[g] = v;
         }
+#pragma unroll
+        for (int g = 0; g < 8; g++) if (lane == g) red[warp * FD_N + g] = mx[g];        // (mx[lane] would put the array in local memory)
+        if (j > 0) { mbar_wait(o_done, (j - 1) & 1); tcgen05_fence_after(); }       // P.V(j-1) has read P^T and written O^T
+        __syncthreads();
+        float corr[8];
+        const int panel = tid >> 6; const uint32_t colb = (uint32_t)(tid & 63) * 2;
+#pragma unroll
+        for (int g = 0; g < 8; g++) if (g < G) {
+            const float mt = fmaxf(fmaxf(red[g], red[FD_N + g]), fmaxf(red[2 * FD_N + g], red[3 * FD_N + g]));
+            const float mn = fmaxf(m_run[g], mt);                      // finite: every tile holds at least position kv0 <= pos
+            corr[g] = m_run[g] == -INFINITY ? 0.f : exp2f((m_run[g] - mn) * sl2);
+            const __half pe = __float2half_rn(ok ? exp2f((__uint_as_float(sc[g]) - mn) * sl2) : 0.f);
+            l_part[g] = l_part[g] * corr[g] + __half2float(pe);        // the sum uses the rounded value the MMA will see
+            m_run[g] = mn;
+            *(__half*)(sP + panel * (FD_N * 128) + g * 128 + (((colb >> 4) ^ (uint32_t)(g & 7)) << 4) + (colb & 15)) = pe;
+        } else corr[g] = 1.f;
+        if (j > 0) {                                                   // O^T[d][g] *= corr[g], in place; this thread's d = tid
+            uint32_t o[16]; tmem_ld_x16(tmem + C::TM_O + lane_off, o);
+#pragma unroll
+            for (int g = 0; g < 8; g++) o[g] = __float_as_uint(__uint_as_float(o[g]) * corr[g]);
+            tmem_st_x8(tmem + C::TM_O + lane_off, o);
+            tmem_st_wait();
+        }
+        fence_proxy_async_smem();                                      // P^T was written with ordinary stores; the MMA reads it through the async proxy
+        tcgen05_fence_before();
+        __syncthreads();
+        if (tid == 0) {
+            tcgen05_fence_after();
+            mbar_wait(v_full, ph);
+            tcgen05_fence_after();
+            constexpr uint32_t idesc = fd_idesc(HD, FD_N, true);
+#pragma unroll
+            for (int k = 0; k < FA_BN / 16; k++) {                     // O^T += V^T . P: 16 positions per instruction
+                const uint64_t da = umma_desc_mn_sw128(sV + (size_t)k * 2048, FA_BN * 128);
+                const uint64_t db = umma_desc_sw128(sP + (size_t)(k / 4) * (FD_N * 128)) + 2 * (k % 4);
+                tcgen05_mma_f16(tmem + C::TM_O, da, db, idesc, (j | k) ? 1u : 0u);
+            }
+            tcgen05_commit(o_done);
+        }
+    }
+    // ---- epilogue: total l per head (sum over the 128 positions' partial sums), then O^T[d][g] / l[g] -> O[(row_t + g)][d]
+#pragma unroll
+    for (int g = 0; g < 8; g++) {
+        float v = l_part[g];
+#pragma unroll
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        l_part[g] = v;
+    }
+    __syncthreads();                                                   // red[] is free (every thread has read the last tile's maxima)
+#pragma unroll
+    for (int g = 0; g < 8; g++) if (lane == g) red[warp * FD_N + g] = l_part[g];
+    mbar_wait(o_done, (n_kv_tiles - 1) & 1);
+    tcgen05_fence_after();
+    __syncthreads();
+    uint32_t o[16]; tmem_ld_x16(tmem + C::TM_O + lane_off, o);
+    const int d = tid, dp = kperm4(d);
+#pragma unroll
+    for (int g = 0; g < 8; g++) if (g < G) {
+        const float l = red[g] + red[FD_N + g] + red[2 * FD_N + g] + red[3 * FD_N + g];
+        O[(size_t)(row_t + g) * HD + dp] = __float2half_rn(clamp_h(l > 0.f ? __uint_as_float(o[g]) / l : 0.f));
     }
     tcgen05_fence_before();
     __syncthreads();

@@ -1027,18 +1027,14 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
         // prompt chunks made of whole runs of one sequence each: causal attention on the tensor cores (attn_tc.cuh)
         const bool tc_off = getenv("B200_NO_ATTN_TC") != nullptr;       // read per call: tests compare the two attention kernels in one process
         const bool tc = !q && runs && !runs->empty() && !tc_off;        // every prompt chunk, whatever it is made of: a request's numerics must not depend on its neighbours
-        // batched decode step: attn_decode_tc_kernel (one CTA per (token, kv head), the G heads of the group as query rows) is
-        // correct (the GPU suite passes with it) but still SLOWER than attn_rows_kernel at B = 64, ctx 512: 5.38 ms per step
-        // against 4.81 (first form, one 160 KB CTA per SM: 6.49; two CTAs per SM: 5.68; + warp roles, parallel TMA issue, cached
-        // block table: 5.38).  Per (token, kv head) the chain load -> S -> softmax -> P.V is serial and only G of 128 MMA rows are
-        // real; DESIGN.md §6 has the swap-AB form that would use all lanes.  Opt-in: B200_ATTN_TC_DEC=1.
-        const bool tc_dec = q && !tc_off && getenv("B200_ATTN_TC_DEC") != nullptr && n_head / n_head_kv <= 8 && M <= PREFILL_CHUNK;
+        // batched decode step, head size 128: attn_decode_tc_kernel (operands swapped: positions are the MMA's M; attn_tc.cuh).
+        // B = 64, ctx 512: 4.46 ms per step against 4.81 with attn_rows_kernel (B200_NO_ATTN_TC_DEC=1 keeps the row kernel).
+        const bool tc_dec = q && !tc_off && getenv("B200_NO_ATTN_TC_DEC") == nullptr && head_dim == 128 && n_head / n_head_kv <= 8 && M <= PREFILL_CHUNK && pages_per_seq <= FD_BTAB;
         CK(launch_pdl(rope_kv_rows_kernel, dim3(nblk((long long)M * W3 / 2)), dim3(256), 0, E.stream, (const float*)pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, (const float*)inv_freq, kv, pf_Q, sp, tc || tc_dec)); E.launches++; sp = none;
         if (tc_dec) {
             if (int rc2 = ensure_attn_maps()) return rc2;
             const dim3 g(M, n_head_kv); const int G = n_head / n_head_kv;
-            if (head_dim == 128) CK(launch_pdl(attn_decode_tc_kernel<128>, g, dim3(FD_THREADS), FdCfg<128>::SMEM, E.stream, *(const CUtensorMap*)tmap_qd, *(const CUtensorMap*)tmap_kv, rm, G, l, n_head, n_head_kv, kq, kv, (__half*)pf_X));
-            else CK(launch_pdl(attn_decode_tc_kernel<64>, g, dim3(FD_THREADS), FdCfg<64>::SMEM, E.stream, *(const CUtensorMap*)tmap_qd, *(const CUtensorMap*)tmap_kv, rm, G, l, n_head, n_head_kv, kq, kv, (__half*)pf_X));
+            CK(launch_pdl(attn_decode_tc_kernel, g, dim3(FD_THREADS), FdCfg::SMEM, E.stream, *(const CUtensorMap*)tmap_qd, *(const CUtensorMap*)tmap_kv, rm, G, l, n_head, n_head_kv, kq, kv, (__half*)pf_X));
             E.launches++;
         } else if (tc) {
             if (int rc2 = ensure_attn_maps()) return rc2;
@@ -1176,14 +1172,13 @@ int Model::ensure_attn_maps() {
         if (r != CUDA_SUCCESS) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled (KV) failed: " + std::to_string((int)r));
     }
     {   // Q of a decode step seen as [token * head][head_dim]: the G heads of a kv group are G consecutive rows
-        cuuint64_t dims[2] = {(cuuint64_t)head_dim, (cuuint64_t)PREFILL_CHUNK * n_head}, strides[1] = {(cuuint64_t)head_dim * 2}; cuuint32_t box[2] = {64, 8}, estr[2] = {1, 1};      // 8 rows = one 128-byte-swizzle atom per panel
+        cuuint64_t dims[2] = {(cuuint64_t)head_dim, (cuuint64_t)PREFILL_CHUNK * n_head}, strides[1] = {(cuuint64_t)head_dim * 2}; cuuint32_t box[2] = {64, (cuuint32_t)FD_N}, estr[2] = {1, 1};      // the G heads of a kv group, padded to the MMA's N = 16
         CUresult r = f(mqd, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, pf_Q, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled (Q, decode view) failed: " + std::to_string((int)r));
     }
     CK(cudaFuncSetAttribute(attn_prefill_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FaCfg<128>::SMEM));
     CK(cudaFuncSetAttribute(attn_prefill_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FaCfg<64>::SMEM));
-    CK(cudaFuncSetAttribute(attn_decode_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FdCfg<128>::SMEM));
-    CK(cudaFuncSetAttribute(attn_decode_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FdCfg<64>::SMEM));
+    CK(cudaFuncSetAttribute(attn_decode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FdCfg::SMEM));
     tmap_q = mq; tmap_kv = mkv; tmap_qd = mqd;
     return B200_OK;
 }
