@@ -837,26 +837,35 @@ static int gemm_bf16(Engine& E, const __nv_bfloat16* A, const __nv_bfloat16* B, 
     if (!attr) {
         CK(cudaFuncSetAttribute(gemm_bf16_tcgen05, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM));
         CK(cudaFuncSetAttribute(gemm_bf16_persistent<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PGemm<256>::SMEM));
+        CK(cudaFuncSetAttribute(gemm_bf16_persistent<224>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PGemm<224>::SMEM));
+        CK(cudaFuncSetAttribute(gemm_bf16_persistent<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PGemm<192>::SMEM));
         CK(cudaFuncSetAttribute(gemm_bf16_persistent<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PGemm<128>::SMEM));
         attr = true;
     }
     CUtensorMap ta, tb;
     if (int rc = make_tmap(&ta, A, (uint64_t)M, (uint64_t)K)) return rc;
     const int m_tiles = (M + GEMM_BM - 1) / GEMM_BM;
-    // 128 x 256 tiles when they still give every SM a tile, else 128 x 128; few rows (a test-sized product): the one-tile-per-CTA kernel
-    const bool wide = (long long)m_tiles * ((N + 255) / 256) >= E.n_sm;
+    // few rows (a test-sized product): the one-tile-per-CTA kernel
     if (old_kernel || (long long)m_tiles * ((N + 127) / 128) < E.n_sm / 2) {
         if (int rc = make_tmap(&tb, B, (uint64_t)N, (uint64_t)K)) return rc;
         dim3 grid((N + GEMM_BN - 1) / GEMM_BN, (M + GEMM_BM - 1) / GEMM_BM);
         gemm_bf16_tcgen05<<<grid, GEMM_THREADS, GEMM_SMEM, E.stream>>>(ta, tb, C, M, N, K, ldc, mode, scale);
-    } else if (wide) {
-        if (int rc = make_tmap(&tb, B, (uint64_t)N, (uint64_t)K, 256)) return rc;
-        const int tiles = m_tiles * ((N + 255) / 256);
-        gemm_bf16_persistent<256><<<std::min(tiles, E.n_sm), PG_THREADS, PGemm<256>::SMEM, E.stream>>>(ta, tb, C, M, N, K, ldc, mode, scale);
     } else {
-        if (int rc = make_tmap(&tb, B, (uint64_t)N, (uint64_t)K, 128)) return rc;
-        const int tiles = m_tiles * ((N + 127) / 128);
-        gemm_bf16_persistent<128><<<std::min(tiles, E.n_sm), PG_THREADS, PGemm<128>::SMEM, E.stream>>>(ta, tb, C, M, N, K, ldc, mode, scale);
+        // Tile width: a persistent CTA per SM walks ceil(tiles / SMs) tiles of width BN, so the product costs about
+        // rounds x (BN + a fixed per-tile part).  Llama-3-8B, 512 rows: QKV (N 6144) 2 x 128 -> 1 x 192; gate/up (N 28672)
+        // 4 x 256 -> 4 x 224; wo / down (N 4096) 1 x 128.
+        static const int widths[4] = {128, 192, 224, 256};
+        int best = 128; long long best_cost = -1;
+        for (int w : widths) {
+            const long long tiles = (long long)m_tiles * ((N + w - 1) / w), rounds = (tiles + E.n_sm - 1) / E.n_sm, cost = rounds * (w + 24);
+            if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = w; }
+        }
+        if (int rc = make_tmap(&tb, B, (uint64_t)N, (uint64_t)K, best)) return rc;
+        const int tiles = m_tiles * ((N + best - 1) / best), grid = std::min(tiles, E.n_sm);
+        if (best == 256) gemm_bf16_persistent<256><<<grid, PG_THREADS, PGemm<256>::SMEM, E.stream>>>(ta, tb, C, M, N, K, ldc, mode, scale);
+        else if (best == 224) gemm_bf16_persistent<224><<<grid, PG_THREADS, PGemm<224>::SMEM, E.stream>>>(ta, tb, C, M, N, K, ldc, mode, scale);
+        else if (best == 192) gemm_bf16_persistent<192><<<grid, PG_THREADS, PGemm<192>::SMEM, E.stream>>>(ta, tb, C, M, N, K, ldc, mode, scale);
+        else gemm_bf16_persistent<128><<<grid, PG_THREADS, PGemm<128>::SMEM, E.stream>>>(ta, tb, C, M, N, K, ldc, mode, scale);
     }
     CK(cudaGetLastError());
     E.launches++;

@@ -159,7 +159,8 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 // stores) runs while the MMAs of tile i+1 are issued.
 constexpr int PG_THREADS = 192;                              // warp 0: TMA, warp 1: MMA + TMEM owner, warps 2..5: epilogue
 template <int BN> struct PGemm {
-    static constexpr int STAGES = BN == 256 ? 4 : 6;
+    static constexpr int STAGES = BN == 256 ? 4 : BN >= 192 ? 5 : 6;
+    static constexpr uint32_t ACC_STRIDE = BN <= 128 ? 128 : 256, TM_COLS = 2 * ACC_STRIDE;      // two accumulators; TMEM allocations are powers of two
     static constexpr uint32_t A_BYTES = GEMM_BM * GEMM_BK * 2, B_BYTES = BN * GEMM_BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr size_t SMEM = (size_t)STAGES * STAGE_BYTES + 1024 + 256;
 };
@@ -180,7 +181,7 @@ gemm_bf16_persistent(const __grid_constant__ CUtensorMap tmap_a, const __grid_co
         for (int i = 0; i < 2; i++) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }      // four epilogue warps release an accumulator
         fence_barrier_init();
     }
-    if (warp == 1) tcgen05_alloc(tmem_slot, 2 * BN);           // two accumulators of BN fp32 columns
+    if (warp == 1) tcgen05_alloc(tmem_slot, G::TM_COLS);       // two accumulators of BN fp32 columns
     tcgen05_fence_before();
     __syncthreads();
     tcgen05_fence_after();
@@ -208,7 +209,7 @@ gemm_bf16_persistent(const __grid_constant__ CUtensorMap tmap_a, const __grid_co
                 const uint32_t a = tl & 1, aph = (tl >> 1) & 1;
                 mbar_wait(&acc_empty[a], aph ^ 1);              // the epilogue has drained this accumulator (first use: passes)
                 tcgen05_fence_after();
-                const uint32_t tacc = tmem_base + a * BN;
+                const uint32_t tacc = tmem_base + a * G::ACC_STRIDE;
                 for (int kb = 0; kb < nkb; kb++, it++) {
                     const int s = it % G::STAGES; const uint32_t ph = (it / G::STAGES) & 1;
                     mbar_wait(&full[s], ph);
@@ -234,7 +235,7 @@ gemm_bf16_persistent(const __grid_constant__ CUtensorMap tmap_a, const __grid_co
 #pragma unroll 1
             for (int c = 0; c < BN; c += 32) {
                 uint32_t r[32];
-                tmem_ld_32x32b_x32(tmem_base + a * BN + ((uint32_t)(q * 32) << 16) + c, r);
+                tmem_ld_32x32b_x32(tmem_base + a * G::ACC_STRIDE + ((uint32_t)(q * 32) << 16) + c, r);
                 if (row < M) {
                     float* dst = C + (size_t)row * ldc + n0 + c;
 #pragma unroll
@@ -256,7 +257,7 @@ gemm_bf16_persistent(const __grid_constant__ CUtensorMap tmap_a, const __grid_co
     }
     tcgen05_fence_before();
     __syncthreads();
-    if (warp == 1) tcgen05_dealloc(tmem_base, 2 * BN);
+    if (warp == 1) tcgen05_dealloc(tmem_base, G::TM_COLS);
 }
 
 // which sequence slot and position each activation row belongs to: a prompt chunk (pos0 + m, one slot) or a

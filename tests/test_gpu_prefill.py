@@ -21,10 +21,12 @@ def _bf16(a):
     return u.view(np.float32)
 
 
-# the last four shapes have enough tiles for the persistent kernels: 128 x 256 tiles (ragged M and N edges, several tiles per
-# CTA so both accumulators and the ring wrap), 128 x 128 tiles, and the 8B gate/up shape
+# the later shapes have enough tiles for the persistent kernels, whose tile width (128 / 192 / 224 / 256) is chosen per
+# product: ragged M and N edges, several tiles per CTA so both accumulators and the ring wrap; (511, 19000) and (300, 12800)
+# take 192-wide tiles, (512, 28672) = the 8B gate/up shape 224, (512, 9472) and (450, 28000) 256, (512, 4096) 128
 @pytest.mark.parametrize("shape", [(128, 128, 64), (128, 128, 256), (256, 384, 512), (100, 256, 4096), (511, 640, 1024), (1, 128, 64),
-                                   (511, 19000, 192), (300, 12800, 128), (250, 4104, 320), (512, 28672, 4096)])
+                                   (511, 19000, 192), (300, 12800, 128), (250, 4104, 320), (512, 28672, 4096),
+                                   (512, 9472, 128), (512, 4096, 256), (450, 28000, 64), (512, 6144, 512)])
 def test_gemm_tcgen05_matches_numpy(engine, shape):
     M, N, K = shape
     rng = np.random.default_rng(M * 7 + N * 3 + K)
