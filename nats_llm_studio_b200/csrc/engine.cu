@@ -830,6 +830,12 @@ static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t co
     return B200_OK;
 }
 // C[M x N] (+)= A[M x K] . B[N x K]^T   (A, B bf16 device, C fp32 device)
+// mode 0: C = scale * A.B^T; 1: C += ...; 2 (persistent kernels only, gemm_bf16_fuses_swiglu): C is a bf16 [M x N/2] matrix of silu(gate) * up
+static bool gemm_bf16_fuses_swiglu(const Engine& E, int M, int N) {
+    static const bool old_kernel = getenv("B200_GEMM_OLD") != nullptr, off = getenv("B200_NO_SWIGLU_FUSE") != nullptr;
+    const int m_tiles = (M + GEMM_BM - 1) / GEMM_BM;
+    return !old_kernel && !off && N % 32 == 0 && (long long)m_tiles * ((N + 127) / 128) >= E.n_sm / 2;
+}
 static int gemm_bf16(Engine& E, const __nv_bfloat16* A, const __nv_bfloat16* B, float* C, int M, int N, int K, int ldc, int mode, float scale) {
     if (K % GEMM_BK) return fail(B200_ERR_INVALID, "GEMM K must be a multiple of 64");
     static const bool old_kernel = getenv("B200_GEMM_OLD") != nullptr;
@@ -1086,12 +1092,15 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
         if (tp) sp = none;
         if (l == n_layer - 1 && !want_logits) break;                  // KV fill only: the last layer's FFN feeds nothing
         CK(launch_pdl(rmsnorm_rows_kernel, dim3(M), dim3(rms_threads), 0, E.stream, pf_H, (const float*)L.ffn_norm, D, M, rms_eps, pf_X, q, sp)); E.launches++; sp = none;
+        bool fused_act = false;
         if (q) { const QMat gu{&L.wgu, pf_Y}; if ((rc = qgemm(E, &gu, 1, pf_X, M, D, 2 * F, 0, 1.f, false, &sp))) return rc; }
         else {
             if (!bf16_ready) { deq(L.wgu, pf_W); wgu = pf_W; }
-            if ((rc = gemm_bf16(E, pf_X, wgu, pf_Y, M, 2 * F, D, 2 * F, 0, 1.f))) return rc;
+            fused_act = gemm_bf16_fuses_swiglu(E, M, 2 * F);           // SwiGLU in the GEMM's epilogue: no fp32 [M x 2F] round trip, one launch less
+            if (fused_act) { if ((rc = gemm_bf16(E, pf_X, wgu, (float*)pf_ACT, M, 2 * F, D, F, 2, 1.f))) return rc; }
+            else if ((rc = gemm_bf16(E, pf_X, wgu, pf_Y, M, 2 * F, D, 2 * F, 0, 1.f))) return rc;
         }
-        CK(launch_pdl(swiglu_rows_kernel, dim3(nblk((long long)M * F / 4)), dim3(256), 0, E.stream, (const float*)pf_Y, M, F, pf_ACT, q, sp)); E.launches++; sp = none;
+        if (!fused_act) { CK(launch_pdl(swiglu_rows_kernel, dim3(nblk((long long)M * F / 4)), dim3(256), 0, E.stream, (const float*)pf_Y, M, F, pf_ACT, q, sp)); E.launches++; sp = none; }
         if (q) { const QMat dn{&L.wd, resid}; if ((rc = qgemm(E, &dn, 1, pf_ACT, M, F, D, rmode, rs, false, &sp))) return rc; }
         else {
             if (!bf16_ready) { deq(L.wd, pf_W); wd = pf_W; }

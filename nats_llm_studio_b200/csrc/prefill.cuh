@@ -157,6 +157,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 // twice the arithmetic per shared-memory byte of 128 x 128); warp-specialised — one TMA thread, one MMA thread, four
 // epilogue warps — with TWO accumulators in tensor memory, so the epilogue of tile i (tcgen05.ld, scale / residual add,
 // stores) runs while the MMAs of tile i+1 are issued.
+__device__ __forceinline__ uint32_t pack16x2(float a, float b, bool f16);      // defined with the row kernels below
 constexpr int PG_THREADS = 192;                              // warp 0: TMA, warp 1: MMA + TMEM owner, warps 2..5: epilogue
 template <int BN> struct PGemm {
     static constexpr int STAGES = BN == 256 ? 4 : BN >= 192 ? 5 : 6;
@@ -236,7 +237,20 @@ gemm_bf16_persistent(const __grid_constant__ CUtensorMap tmap_a, const __grid_co
             for (int c = 0; c < BN; c += 32) {
                 uint32_t r[32];
                 tmem_ld_32x32b_x32(tmem_base + a * G::ACC_STRIDE + ((uint32_t)(q * 32) << 16) + c, r);
-                if (row < M) {
+                if (row < M && mode == 2) {
+                    // fused SwiGLU (gate/up rows are interleaved in the weight matrix, so columns 2i, 2i+1 are gate_i, up_i):
+                    // ACT[row][i] = bf16(silu(gate) * up), the arithmetic of swiglu_rows_kernel; C is the bf16 output, ldc its row length
+                    if (n0 + c < N) {                                  // N % 32 == 0 (checked by the host)
+                        uint32_t o[8];
+#pragma unroll
+                        for (int k = 0; k < 8; k++) {
+                            const float g0 = __uint_as_float(r[4 * k]), u0 = __uint_as_float(r[4 * k + 1]), g1 = __uint_as_float(r[4 * k + 2]), u1 = __uint_as_float(r[4 * k + 3]);
+                            o[k] = pack16x2(g0 / (1.f + __expf(-g0)) * u0, g1 / (1.f + __expf(-g1)) * u1, false);
+                        }
+                        uint4* dst = (uint4*)((__nv_bfloat16*)C + (size_t)row * ldc + (n0 + c) / 2);
+                        dst[0] = make_uint4(o[0], o[1], o[2], o[3]); dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+                    }
+                } else if (row < M) {
                     float* dst = C + (size_t)row * ldc + n0 + c;
 #pragma unroll
                     for (int j = 0; j < 32; j += 4) {
