@@ -40,8 +40,11 @@ constexpr int CONSUMER_THREADS = CONSUMER_WARPS * 32;
 constexpr int CTA_THREADS = CONSUMER_THREADS + 32;
 constexpr int PAIRS_PER_STAGE = GROUP_WARPS;
 constexpr int NSLOT = 16;                // mbarrier pairs in flight
-constexpr int XREP = 8;                  // copies of every broadcast exchange vector (an L2 slice serves ~1 sector/clk: one copy read by
-                                         // every CTA costs ~0.6 us per line; CTA c reads copy c % XREP)
+#ifndef B200_XREP
+#define B200_XREP 4
+#endif
+constexpr int XREP = B200_XREP;          // copies of every broadcast exchange vector (an L2 slice serves ~1 sector/clk: one copy read by
+                                         // every CTA costs ~0.6 us per line; CTA c reads copy c % XREP).  Measured 2, 3, 4: 611 tok/s, 8: 608, 16: 576
 // groups (of 2048 elements) per stage: one bulk copy moves a pair's run of `stage_groups` consecutive groups, which
 // are contiguous in HBM — fewer, larger copies (the single producer warp issues them one by one)
 #ifndef B200_STAGE_GROUPS
