@@ -162,3 +162,34 @@ def test_cancel_frees_the_slot_and_the_others_finish(engine, golden_dir):
                 fin[e.req_id] = e
     assert fin[902].n_generated == 3
     m.close()
+
+
+def test_tensor_core_decode_attention_matches_row_kernel_and_oracle(engine, tmp_path):
+    """attn_decode_tc_kernel (csrc/attn_tc.cuh: head size 128, operands swapped): decode steps of sequences whose contexts
+    end in different 128-position KV tiles (first tile only, tile boundaries 127/128/129, three tiles) agree with the
+    CUDA-core row kernel (B200_NO_ATTN_TC_DEC=1: same GEMMs around it) and with the fp32 oracle; rows stay independent of
+    the batch they are in."""
+    import make_gguf
+    path = str(tmp_path / "small.gguf"); make_gguf.write_model(path, make_gguf.spec_from_preset("small-llama"))
+    m = engine.load_file("bt/tcdec", path)
+    lens = [3, 128, 129, 130, 300, 17, 257]
+    prompts = _prompts(m.n_vocab, lens, seed=23); slots = np.array([5, 0, 2, 7, 1, 3, 6], np.int32)
+    tok_tc, lg_tc = _run(m, prompts, slots, 3, want_logits=True)
+    alone, lg1 = _run(m, [prompts[4]], np.array([4], np.int32), 3, want_logits=True)
+    assert np.array_equal(alone[0], tok_tc[4]) and np.array_equal(lg1[0], lg_tc[4])     # a row does not depend on its batch
+    os.environ["B200_NO_ATTN_TC_DEC"] = "1"               # read when a step is launched or captured: a second instance of the
+    try:                                                   # model, whose step graphs are captured with the row kernel
+        m2 = engine.load_file("bt/tcdec-cc", path)
+        tok_cc, lg_cc = _run(m2, prompts, slots, 3, want_logits=True)
+        m2.close()
+    finally:
+        del os.environ["B200_NO_ATTN_TC_DEC"]
+    assert np.abs(lg_tc - lg_cc).max() > 0                                # the two kernels really are different code
+    o = orc.Model(path)
+    for i, p in enumerate(prompts):
+        ref = o.forward(p, all_logits=False); scale = np.abs(ref).max()
+        d_tc, d_cc, d_x = np.abs(lg_tc[i] - ref).max() / scale, np.abs(lg_cc[i] - ref).max() / scale, np.abs(lg_tc[i] - lg_cc[i]).max() / scale
+        assert np.isfinite(lg_tc[i]).all()
+        assert d_tc <= TOL_QUANT and d_tc <= 1.15 * d_cc + 2e-3, (lens[i], d_tc, d_cc, d_x)     # no further from the oracle than the fp32-probability kernel
+        assert d_x <= 2.5e-2, (lens[i], d_x)
+    m.close()
