@@ -202,19 +202,29 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_
 // ------------------------------------------------------------------------------------ batched decode step
 // attn_decode_tc_kernel: attention for ONE new position per sequence, one CTA per (token m, kv head), with the MMA operands
 // SWAPPED so that every tensor-memory lane holds real data:
-//   S^T = K . Q^T     A = the K tile (M = 128 positions), B = the G query heads of the kv group padded to N = 16 rows
+//   S^T = K . Q^T     A = the K tile (M = 128 rows, FD_BN of them positions of the tile), B = the G query heads of the kv group padded to N = 16 rows
 //                     (rows m * n_head + kvh * G .. of Q viewed as [token * head][head_dim]); lane t = position t
 //   softmax           thread t owns position t: G scores from one tcgen05.ld, the per-head maximum by warp shuffles and one
 //                     block barrier, G exponentials, P^T written to shared memory (fp16, 128-byte swizzle, K-major B operand)
 //   O^T += V^T . P    A = the V tile as it lies in the cache ([position][head_dim] = M-major A), B = P^T; lane d = output
 //                     dimension d, 16 columns = heads; rescaled in place per column when a head's maximum moves
-// 32 TMEM columns and 76 KB of shared memory per CTA: three CTAs per SM cover each other's serial load -> S -> softmax ->
-// P.V chain.  (The query-rows-as-M form, G real rows of 128 and one warp doing the whole softmax, measured 5.4 - 6.5 ms per
+// 32 TMEM columns and 50 KB of shared memory per CTA (80-position tiles, below): four CTAs per SM cover each other's serial
+// load -> S -> softmax -> P.V chain.  (The query-rows-as-M form, G real rows of 128 and one warp doing the whole softmax, measured 5.4 - 6.5 ms per
 // B = 64 step against 4.81 for the CUDA-core kernel.)  Position and slot come from the step's device-side row map (the
 // step is a CUDA graph).  Output: fp16 in kperm4 order, the activation format of qgemm_kernel.  Head size 128 only.
 constexpr int FD_THREADS = 128, FD_N = 16, FD_BTAB = 256;          // FD_BTAB pages = 4096 positions per sequence
+// Positions per KV tile.  80 (not 128): 40 KB of K + V per CTA lets FOUR CTAs share an SM, and 64 x 8 = 512 (token, kv head)
+// items then run in one wave of 592 slots; with 128-position tiles (three CTAs per SM, 444 slots) the 68 items of the second
+// round ran alone at a fraction of the bandwidth: 40 % of the kernel's time.  The S^T MMA still has M = 128: its rows 80..127
+// read on into the next panel / the V buffer (finite garbage) and are masked.  One tile size for every batch size, so that a
+// row's rounding does not depend on its batch.
+#ifndef B200_FD_BN
+#define B200_FD_BN 80
+#endif
+constexpr int FD_BN = B200_FD_BN;
+static_assert(FD_BN % 16 == 0 && FD_BN >= 64 && FD_BN <= 128, "decode attention tile: whole pages, at least one 64-position panel");
 struct FdCfg {
-    static constexpr uint32_t KV_BYTES = FA_BN * 128 * 2, QP_BYTES = 2 * FD_N * 128;        // one K or V tile | Q or P^T: 2 panels x 16 rows x 128 B
+    static constexpr uint32_t KV_BYTES = FD_BN * 128 * 2, QP_BYTES = 2 * FD_N * 128;        // one K or V tile | Q or P^T: 2 panels x 16 rows x 128 B
     static constexpr size_t SMEM = 1024 + 2 * (size_t)QP_BYTES + 2 * (size_t)KV_BYTES + 64 + 4 * FD_N * 4 + FD_BTAB * 4;
     static constexpr uint32_t TM_S = 0, TM_O = FD_N, TM_COLS = 32;
 };
@@ -228,7 +238,7 @@ __device__ __forceinline__ void tmem_ld_x16(uint32_t taddr, uint32_t* r) {
 }
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-__global__ void __launch_bounds__(FD_THREADS, 3)
+__global__ void __launch_bounds__(FD_THREADS, FD_BN <= 80 ? 4 : 3)
 attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_qd, const __grid_constant__ CUtensorMap tmap_kv, RowMap rm, int G, int layer,
                       int n_head, int n_head_kv, float kq_scale, KvLayout kv, __half* __restrict__ O) {
     using C = FdCfg; constexpr int HD = 128;
@@ -246,7 +256,7 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_qd, const __grid_
     for (int i = tid; i < (int)C::QP_BYTES / 16; i += FD_THREADS) ((uint4*)sP)[i] = make_uint4(0, 0, 0, 0);      // rows >= G of P^T stay zero
     pdl_launch_dependents(); pdl_wait();                              // Q and the new K/V rows come from the preceding kernels
     const int row_t = m * n_head + kvh * G, pos = rm.p(m), slot = rm.s(m);
-    const int n_kv_tiles = pos / FA_BN + 1;
+    const int n_kv_tiles = pos / FD_BN + 1;
     for (int i = tid; i <= (pos >> 4); i += FD_THREADS) s_bt[i] = kv.block_table[(size_t)slot * kv.pages_per_seq + i];   // one round trip, not one per page
     tcgen05_fence_before();
     __syncthreads();
@@ -259,11 +269,11 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_qd, const __grid_
     auto load_tile = [&](int j, int which, uint8_t* dst, uint64_t* bar) {      // which: 0 = K, 1 = V; called by all of warp 0
         if (lane == 0) mbar_expect_tx(bar, C::KV_BYTES);
         __syncwarp();
-        if (lane < 16) {
+        if (lane < 2 * (FD_BN / 16)) {
             const int pg = lane >> 1, pn = lane & 1;
-            const int p = min(j * FA_BN + pg * 16, pos);           // pages beyond the position: re-read a valid page (masked in the softmax)
+            const int p = min(j * FD_BN + pg * 16, pos);           // pages beyond the position: re-read a valid page (masked in the softmax)
             const int r = (int)(((((size_t)layer * kv.n_pages + s_bt[p >> 4]) * 2 + which) * kv.n_head_kv + kvh) * 16);
-            tma_load_2d(dst + (size_t)pn * (FA_BN * 128) + (size_t)pg * 2048, &tmap_kv, pn * 64, r, bar);
+            tma_load_2d(dst + (size_t)pn * (FD_BN * 128) + (size_t)pg * 2048, &tmap_kv, pn * 64, r, bar);
         }
     };
     if (warp == 0) {
@@ -280,10 +290,10 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_qd, const __grid_
                 if (j == 0) mbar_wait(q_full, 0);
                 mbar_wait(k_full, ph);
                 tcgen05_fence_after();
-                constexpr uint32_t idesc = fd_idesc(FA_BN, FD_N, false);
+                constexpr uint32_t idesc = fd_idesc(128, FD_N, false);       // M = 128 whatever the tile: rows >= FD_BN are masked
 #pragma unroll
                 for (int k = 0; k < HD / 16; k++) {                    // S^T = K . Q^T: 16 head-dim columns per instruction
-                    const uint64_t da = umma_desc_sw128(sK + (size_t)(k / 4) * (FA_BN * 128)) + 2 * (k % 4);
+                    const uint64_t da = umma_desc_sw128(sK + (size_t)(k / 4) * (FD_BN * 128)) + 2 * (k % 4);
                     const uint64_t db = umma_desc_sw128(sQ + (size_t)(k / 4) * (FD_N * 128)) + 2 * (k % 4);
                     tcgen05_mma_f16(tmem + C::TM_S, da, db, idesc, k ? 1u : 0u);
                 }
@@ -299,7 +309,7 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_qd, const __grid_
         if (warp == 0 && j + 1 < n_kv_tiles) load_tile(j + 1, 0, sK, k_full);      // S^T(j) has read K
         // ---- softmax: this thread's position against the G heads
         uint32_t sc[16]; tmem_ld_x16(tmem + C::TM_S + lane_off, sc);
-        const bool ok = j * FA_BN + tid <= pos;                        // positions past the token's own are masked
+        const bool ok = tid < FD_BN && j * FD_BN + tid <= pos;         // rows past the tile and positions past the token's own are masked
         float mx[8];
 #pragma unroll
         for (int g = 0; g < 8; g++) {
@@ -340,8 +350,8 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_qd, const __grid_
             tcgen05_fence_after();
             constexpr uint32_t idesc = fd_idesc(HD, FD_N, true);
 #pragma unroll
-            for (int k = 0; k < FA_BN / 16; k++) {                     // O^T += V^T . P: 16 positions per instruction
-                const uint64_t da = umma_desc_mn_sw128(sV + (size_t)k * 2048, FA_BN * 128);
+            for (int k = 0; k < FD_BN / 16; k++) {                     // O^T += V^T . P: 16 positions per instruction
+                const uint64_t da = umma_desc_mn_sw128(sV + (size_t)k * 2048, FD_BN * 128);
                 const uint64_t db = umma_desc_sw128(sP + (size_t)(k / 4) * (FD_N * 128)) + 2 * (k % 4);
                 tcgen05_mma_f16(tmem + C::TM_O, da, db, idesc, (j | k) ? 1u : 0u);
             }

@@ -1043,7 +1043,7 @@ int Model::dense_rows(const int* d_toks, int M, const int* d_pos, const int* d_s
         const bool tc_off = getenv("B200_NO_ATTN_TC") != nullptr;       // read per call: tests compare the two attention kernels in one process
         const bool tc = !q && runs && !runs->empty() && !tc_off;        // every prompt chunk, whatever it is made of: a request's numerics must not depend on its neighbours
         // batched decode step, head size 128: attn_decode_tc_kernel (operands swapped: positions are the MMA's M; attn_tc.cuh).
-        // B = 64, ctx 512: 4.46 ms per step against 4.81 with attn_rows_kernel (B200_NO_ATTN_TC_DEC=1 keeps the row kernel).
+        // B = 64, ctx 512: 4.03 ms per step against 4.81 with attn_rows_kernel (B200_NO_ATTN_TC_DEC=1 keeps the row kernel).
         const bool tc_dec = q && !tc_off && getenv("B200_NO_ATTN_TC_DEC") == nullptr && head_dim == 128 && n_head / n_head_kv <= 8 && M <= PREFILL_CHUNK && pages_per_seq <= FD_BTAB;
         CK(launch_pdl(rope_kv_rows_kernel, dim3(nblk((long long)M * W3 / 2)), dim3(256), 0, E.stream, (const float*)pf_Y, M, rm, l, n_head, n_head_kv, head_dim, n_rot, (const float*)inv_freq, kv, pf_Q, sp, tc || tc_dec)); E.launches++; sp = none;
         if (tc_dec) {
