@@ -26,7 +26,9 @@ typedef struct b200_config {
     int device;          /* CUDA device ordinal */
     int max_ctx;         /* KV positions reserved per sequence (0 = 4096) */
     int max_seqs;        /* concurrent sequences the KV pool is sized for (0 = 1) */
-    uint32_t flags;      /* reserved */
+    uint32_t kv_pages;   /* KV pages (16 positions each) in a model's pool; 0 = max_seqs x max_ctx / 16: every sequence slot fully backed.
+                          * A smaller pool oversubscribes the slots: pages are handed out as sequences grow, returned when a request
+                          * ends, and the scheduler admits a request only when the pages of its prompt + max_tokens are free. */
 } b200_config;
 
 /* ggml type ids used in the kernel-level entry points (gguf/constants.py GGMLQuantizationType) */
@@ -151,6 +153,11 @@ int b200_model_set_prefill_min(b200_model* m, int n);
  * slot slots[i] at position pos[i]; logits, when not NULL, receives [n][n_vocab] fp32).  A row's result does not depend
  * on which other rows are in the batch. */
 int b200_model_prefill_slot(b200_model* m, int slot, const int32_t* toks, int n, int pos0);
+/* KV pages are allocated to a slot as its positions are written (B200_ERR_NOMEM when the pool is exhausted); a caller that
+ * drives the slots itself returns a finished sequence's pages with b200_model_release_slot.  b200_model_kv_free_pages: pages
+ * currently unassigned (< 0: error). */
+int b200_model_release_slot(b200_model* m, int slot);
+int b200_model_kv_free_pages(b200_model* m);
 int b200_model_batch_step(b200_model* m, const int32_t* toks, const int32_t* slots, const int32_t* pos, int n, int32_t* next, float* logits);
 /* The same step with per-row sampling (the `temperature`, `top_k`, `top_p`, `seed` request fields, README.md:196-205): row i
  * with samp[i].temperature > 0 draws its token with Philox(seed, draw[i]) where draw[i] = tokens that request has generated

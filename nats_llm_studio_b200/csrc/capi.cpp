@@ -86,6 +86,7 @@ struct Scheduler {
                 b200_event f{}; f.req_id = s.r->id; f.kind = kind; f.finish_reason = reason; f.n_prompt = (int)s.r->toks.size(); f.n_generated = s.n_gen; f.ttft_ms = s.ttft_ms;
                 f.decode_ms = s.n_gen ? (float)ms_since(s.t_first) : 0.f;
                 out.push_back(f); done.push_back(s.r->id); free_slots.push_back(s.slot);
+                s.r->m->kv_release(s.slot);                              // its KV pages go back to the pool
             };
             // ---- admit: a waiting request gets a sequence slot; its prompt is ingested in chunks below
             while (!waiting.empty() && !free_slots.empty() && (!cur || waiting.front()->m == cur)) {
@@ -96,8 +97,16 @@ struct Scheduler {
                 bool bad = n < 1 || n + 1 > max_ctx;
                 for (int t : r->toks) bad = bad || t < 0 || t >= r->m->n_vocab;
                 if (bad) { e.kind = B200_EV_ERROR; e.finish_reason = B200_ERR_INVALID; out.push_back(e); done.push_back(r->id); continue; }
+                // KV pages of the whole request (prompt + max_tokens, capped by max_ctx) are reserved at admission, so that no
+                // sequence can run out of pages half way; with the default pool every slot is fully backed and this always passes
+                const int want_pos = std::min(max_ctx, n + (r->s.max_tokens > 0 ? r->s.max_tokens : 256)), want_pages = (want_pos + 15) / 16;
+                if (r->m->kv_free_count() < want_pages) {
+                    if (active.empty()) { e.kind = B200_EV_ERROR; e.finish_reason = B200_ERR_NOMEM; out.push_back(e); done.push_back(r->id); continue; }   // can never fit
+                    waiting.push_front(r); break;                          // wait for running requests to return pages
+                }
                 cur = r->m;
                 Seq s; s.r = r; s.slot = free_slots.back(); free_slots.pop_back();
+                { std::lock_guard<std::mutex> lk(cur->run_mu); if (cur->committed && cur->kv_ensure(s.slot, want_pos - 1) != B200_OK) { free_slots.push_back(s.slot); e.kind = B200_EV_ERROR; e.finish_reason = B200_ERR_NOMEM; out.push_back(e); done.push_back(r->id); continue; } }
                 if (n == 1) { s.decoding = true; s.cur_tok = r->toks[0]; s.pos = 0; }
                 active.push_back(s);
             }
@@ -224,6 +233,12 @@ int b200_model_open(const char* id, const void* head, size_t n, b200_model** out
     return B200_OK;
 }
 int b200_model_upload(b200_model* m, uint64_t off, const void* bytes, size_t n) { if (!m || (!bytes && n)) return fail(B200_ERR_INVALID, "null argument"); return ((Model*)m)->upload(off, bytes, n); }
+int b200_model_release_slot(b200_model* m, int slot) {
+    if (!m) return fail(B200_ERR_INVALID, "null model");
+    Model* M = (Model*)m; if (slot < 0 || slot >= engine().max_seqs) return fail(B200_ERR_INVALID, "slot out of range");
+    M->kv_release(slot); return B200_OK;
+}
+int b200_model_kv_free_pages(b200_model* m) { if (!m) return fail(B200_ERR_INVALID, "null model"); return ((Model*)m)->kv_free_count(); }
 int b200_model_commit(b200_model* m) { if (!m) return fail(B200_ERR_INVALID, "null model"); return ((Model*)m)->commit(); }
 int b200_model_close(b200_model* m) {
     if (!m) return fail(B200_ERR_INVALID, "null model");

@@ -149,6 +149,7 @@ int Engine::init(const b200_config* cfg) {
     device = cfg ? cfg->device : 0;
     max_ctx = cfg && cfg->max_ctx > 0 ? cfg->max_ctx : 4096;
     max_seqs = cfg && cfg->max_seqs > 0 ? cfg->max_seqs : 1;
+    kv_pages = cfg ? (int)cfg->kv_pages : 0;
     // the batch-1 kernel caches a sequence's block table in shared memory (BTAB_MAX pages of 16 positions)
     if (max_ctx > 16 * BTAB_MAX) return fail(B200_ERR_UNSUPPORTED, "max_ctx " + std::to_string(max_ctx) + " exceeds the supported " + std::to_string(16 * BTAB_MAX) + " positions per sequence");
     if (device < 0 || device >= 64) return fail(B200_ERR_INVALID, "device ordinal out of range");
@@ -483,11 +484,19 @@ int Model::commit() {
     // a serving engine (max_seqs > 1) keeps one more sequence slot for the synchronous batch-1 path, so that
     // b200_model_generate / b200_model_eval never write KV pages of a request the scheduler is serving
     sync_slot = E.max_seqs > 1 ? E.max_seqs : 0;
-    n_pages = pages_per_seq * (sync_slot + 1);
+    // KV pool: by default every slot is fully backed (no request can run out of pages); b200_config.kv_pages makes the pool
+    // smaller than slots x max_ctx — the scheduler then admits a request only when its pages are free.
+    const int table_entries = pages_per_seq * (sync_slot + 1);
+    n_pages = E.kv_pages > 0 ? E.kv_pages : table_entries;
+    if (n_pages < pages_per_seq) return fail(B200_ERR_INVALID, "kv_pages " + std::to_string(n_pages) + " cannot back one sequence of max_ctx positions (" + std::to_string(pages_per_seq) + " pages)");
     size_t page_elems = (size_t)n_layer * 2 * n_head_kv * 16 * head_dim;
-    if ((rc = own(&d_kv, page_elems * n_pages)) || (rc = own(&d_block_table, (size_t)n_pages))) return rc;
-    std::vector<int> bt(n_pages); for (int i = 0; i < n_pages; i++) bt[i] = i;
-    CK(cudaMemcpy(d_block_table, bt.data(), bt.size() * 4, cudaMemcpyHostToDevice));
+    if ((rc = own(&d_kv, page_elems * n_pages)) || (rc = own(&d_block_table, (size_t)table_entries))) return rc;
+    CK(cudaMemset(d_block_table, 0, (size_t)table_entries * 4));       // unbacked entries point at page 0: never dereferenced for a live position
+    {
+        std::lock_guard<std::mutex> kl(kv_mu);
+        kv_host_table.assign(table_entries, 0); kv_slot_pages.assign(sync_slot + 1, {});
+        kv_free.clear(); for (int i = 0; i < n_pages; i++) kv_free.push_back(i);      // popped from the back: physical order is the reverse of logical order
+    }
     // a tensor-parallel shard runs the same persistent batch-1 kernel on its slice of every matrix; the partial sums of
     // the row-parallel products and the argmax candidates cross NVLink inside the kernel (tp_setup_exchange)
     if (tp) { if (int rc2 = tp_setup_exchange()) return rc2; }
@@ -589,12 +598,36 @@ int Model::tp_check_error() {
 }
 
 // Runs `n_steps` decode steps.  forced (host, n_forced ints) are fed first.  reset: start at position 0.
+// ------------------------------------------------------------------------------------ KV page allocator
+int Model::kv_ensure(int slot, int upto_pos) {
+    Engine& E = engine();
+    std::lock_guard<std::mutex> kl(kv_mu);
+    if (slot < 0 || slot >= (int)kv_slot_pages.size() || upto_pos < 0 || upto_pos >= E.max_ctx) return fail(B200_ERR_INVALID, "kv_ensure: slot or position out of range");
+    std::vector<int>& pg = kv_slot_pages[slot];
+    const int need = upto_pos / 16 + 1, first_new = (int)pg.size();
+    if (need <= first_new) return B200_OK;
+    if ((int)kv_free.size() < need - first_new) return fail(B200_ERR_NOMEM, "KV page pool exhausted: " + std::to_string(need - first_new) + " pages wanted, " + std::to_string(kv_free.size()) + " free of " + std::to_string(n_pages));
+    while ((int)pg.size() < need) { pg.push_back(kv_free.back()); kv_free.pop_back(); kv_host_table[(size_t)slot * pages_per_seq + pg.size() - 1] = pg.back(); }
+    // kv_host_table outlives the copy (it is a member; entries of a slot are only rewritten by a later kv_ensure, which the
+    // stream orders behind this one), and pageable-memory copies are staged by the runtime before the call returns
+    CK(cudaMemcpyAsync(d_block_table + (size_t)slot * pages_per_seq + first_new, kv_host_table.data() + (size_t)slot * pages_per_seq + first_new, (size_t)(need - first_new) * 4, cudaMemcpyHostToDevice, E.stream));
+    return B200_OK;
+}
+void Model::kv_release(int slot) {
+    std::lock_guard<std::mutex> kl(kv_mu);
+    if (slot < 0 || slot >= (int)kv_slot_pages.size()) return;
+    for (int p : kv_slot_pages[slot]) kv_free.push_back(p);
+    kv_slot_pages[slot].clear();
+}
+int Model::kv_free_count() { std::lock_guard<std::mutex> kl(kv_mu); return (int)kv_free.size(); }
+
 int Model::run_steps(int n_steps, const int32_t* forced, int n_forced, bool reset, float* logits_all_dev) {
     Engine& E = engine();
     if (!committed) return fail(B200_ERR_STATE, "model not committed");
     if (n_steps <= 0) return B200_OK;
     if (reset) { int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0; }
     if (cur_pos + n_steps > E.max_ctx) return fail(B200_ERR_INVALID, "context overflow: " + std::to_string(cur_pos + n_steps) + " > max_ctx " + std::to_string(E.max_ctx));
+    if (int rc = kv_ensure(sync_slot, cur_pos + n_steps - 1)) return rc;
     if (n_forced > 0) CK(cudaMemcpyAsync(d_forced, forced, (size_t)n_forced * 4, cudaMemcpyHostToDevice, E.stream));
     DecodeParams P; fill_params(P); P.n_steps = n_steps;
     // context splits per head: as many (head, split) items as there are CTAs (each split is one memory round trip);
@@ -1132,6 +1165,7 @@ int Model::prefill_slot(int slot, const int32_t* toks, int n, int pos0) {
     if (!committed) return fail(B200_ERR_STATE, "model '" + id + "' is not loaded (closed or deleted)");
     if (n <= 0) return B200_OK;
     if (pos0 + n > E.max_ctx) return fail(B200_ERR_INVALID, "context overflow in prefill");
+    if (int rc = kv_ensure(slot, pos0 + n - 1)) return rc;
     if (int rc = ensure_prefill_buffers()) return rc;
     if (n >= PREFILL_CHUNK / 2) maybe_bf16_cache();                    // long prompts: keep bf16 copies of the matrices when HBM has room (see maybe_bf16_cache)
     for (int c0 = 0; c0 < n; c0 += PREFILL_CHUNK) {
@@ -1151,6 +1185,7 @@ int Model::prefill_rows(const int32_t* toks, const int32_t* slots, const int32_t
     if (!committed) return fail(B200_ERR_STATE, "model '" + id + "' is not loaded (closed or deleted)");
     if (M < 1 || M > PREFILL_CHUNK) return fail(B200_ERR_INVALID, "prefill chunk size out of range");
     for (int i = 0; i < M; i++) if (toks[i] < 0 || toks[i] >= n_vocab || slots[i] < 0 || slots[i] >= E.max_seqs || pos[i] < 0 || pos[i] >= E.max_ctx) return fail(B200_ERR_INVALID, "bad prefill row");
+    for (int i = 0; i < M; i++) if (int rc = kv_ensure(slots[i], pos[i])) return rc;
     if (int rc = ensure_prefill_buffers()) return rc;
     if (E.max_seqs > 1) maybe_bf16_cache();
     const int Mc = PREFILL_CHUNK;
@@ -1229,6 +1264,7 @@ int Model::batch_step(const int32_t* toks, const int32_t* slots, const int32_t* 
     if (!committed) return fail(B200_ERR_STATE, "model '" + id + "' is not loaded (closed or deleted)");
     if (B < 1 || B > E.max_seqs || B > PREFILL_CHUNK) return fail(B200_ERR_INVALID, "batch size out of range");
     for (int i = 0; i < B; i++) if (toks[i] < 0 || toks[i] >= n_vocab || slots[i] < 0 || slots[i] >= E.max_seqs || pos[i] < 0 || pos[i] >= E.max_ctx) return fail(B200_ERR_INVALID, "bad batch row");
+    for (int i = 0; i < B; i++) if (int rc = kv_ensure(slots[i], pos[i])) return rc;
     if (int rc = ensure_prefill_buffers()) return rc;
     if (!use_qgemm(B)) { if (int rc = ensure_bf16_weights()) return rc; }
     const int Mc = PREFILL_CHUNK;
@@ -1309,7 +1345,7 @@ int Model::bench_batch(int B, int ctx, int iters, int warmup, float* ms_per_step
     if (!use_qgemm(B)) { if (int rc = ensure_bf16_weights()) return rc; }
     const int Mc = PREFILL_CHUNK;
     std::vector<int32_t> toks(B), pos(B, ctx), slots(B);
-    for (int i = 0; i < B; i++) { toks[i] = (int)((1000003u * (unsigned)(i + 1)) % (unsigned)n_vocab); slots[i] = i; }
+    for (int i = 0; i < B; i++) { toks[i] = (int)((1000003u * (unsigned)(i + 1)) % (unsigned)n_vocab); slots[i] = i; if (int rc = kv_ensure(i, ctx)) return rc; }
     std::vector<RowSampling> rs((size_t)B, RowSampling{});
     CK(cudaMemcpyAsync(pf_toks, toks.data(), (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));
     CK(cudaMemcpyAsync(pf_toks + Mc, pos.data(), (size_t)B * 4, cudaMemcpyHostToDevice, E.stream));

@@ -39,6 +39,7 @@ struct Engine {
     std::mutex mu;
     bool ready = false;
     int device = 0, max_ctx = 4096, max_seqs = 1, n_sm = 0, smem_per_sm = 0, smem_optin = 0;
+    int kv_pages = 0;                            // b200_config.kv_pages: pages of 16 positions in a model's KV pool (0 = every slot fully backed)
     cudaStream_t stream = nullptr, copy_stream = nullptr;
     cudaStream_t aux_stream = nullptr;           // allocation-free utility calls (never captured into a step graph)
     uint64_t launches = 0;                       // kernels launched by this library (bench.py reports it)
@@ -84,6 +85,12 @@ struct Model {
     float* d_logits = nullptr; uint32_t* d_ll16 = nullptr; uint2* d_ll32 = nullptr; int hown_cap = 0;
     int *d_state = nullptr, *d_out_tokens = nullptr, *d_forced = nullptr, *d_block_table = nullptr;
     __half* d_kv = nullptr; int n_pages = 0, n_splits = 1;
+    // ---- KV page allocator (K5): the pool's pages are handed to sequence slots on demand and returned when a request ends;
+    // the device block table [slot][page index] is what every attention kernel reads (no kernel assumes an identity map).
+    std::mutex kv_mu; std::vector<int> kv_free; std::vector<std::vector<int>> kv_slot_pages; std::vector<int> kv_host_table;
+    int kv_ensure(int slot, int upto_pos);       // back positions [0, upto_pos] of `slot`; new table entries are uploaded on the engine stream
+    void kv_release(int slot);                   // return the slot's pages (stream order keeps kernels already enqueued safe)
+    int kv_free_count();
     int sync_slot = 0;                           // KV sequence slot of the synchronous batch-1 path (generate / eval / chat with max_seqs == 1);
                                                  // with max_seqs > 1 it is an extra slot the scheduler never hands out
     int max_segs = 0;

@@ -25,7 +25,7 @@ class EngineError(RuntimeError):
 
 
 class Config(C.Structure):
-    _fields_ = [("device", C.c_int), ("max_ctx", C.c_int), ("max_seqs", C.c_int), ("flags", C.c_uint32)]
+    _fields_ = [("device", C.c_int), ("max_ctx", C.c_int), ("max_seqs", C.c_int), ("kv_pages", C.c_uint32)]
 
 
 class Sampling(C.Structure):
@@ -61,7 +61,7 @@ SYMBOLS = {
     "b200_dequantize": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_dequantize_noalloc": (ci, [ci, vp, C.c_int64, ci, vp]), "b200_gemv": (ci, [ci, vp, C.c_int64, ci, vp, vp, ci, C.POINTER(C.c_float)]),
     "b200_bench_decode": (ci, [vp, ci, ci, ci, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
     "b200_bench_batch_step": (ci, [vp, ci, ci, ci, ci, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
-    "b200_gemm_bf16": (ci, [vp, vp, vp, ci, ci, ci]), "b200_qgemm": (ci, [ci, vp, C.c_int64, ci, vp, ci, vp, ci, C.POINTER(C.c_float)]), "b200_model_prefill_slot": (ci, [vp, ci, vp, ci, ci]),
+    "b200_gemm_bf16": (ci, [vp, vp, vp, ci, ci, ci]), "b200_qgemm": (ci, [ci, vp, C.c_int64, ci, vp, ci, vp, ci, C.POINTER(C.c_float)]), "b200_model_prefill_slot": (ci, [vp, ci, vp, ci, ci]), "b200_model_release_slot": (ci, [vp, ci]), "b200_model_kv_free_pages": (ci, [vp]),
     "b200_model_batch_step": (ci, [vp, vp, vp, vp, ci, vp, vp]),
     "b200_model_batch_step_sampled": (ci, [vp, vp, vp, vp, ci, vp, vp, vp, vp]),
     "b200_tp_shard_window": (ci, [C.c_char_p, C.c_int64, ci, ci, ci, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(ci), C.POINTER(ci)]),
@@ -146,6 +146,16 @@ class Model:
         toks = np.ascontiguousarray(toks, dtype=np.int32)
         _check(lib().b200_model_prefill_slot(self.h, slot, toks.ctypes.data, len(toks), pos0))
 
+    def release_slot(self, slot):
+        """return the KV pages of sequence slot `slot` to the model's pool"""
+        _check(lib().b200_model_release_slot(self.h, slot))
+
+    def kv_free_pages(self):
+        n = lib().b200_model_kv_free_pages(self.h)
+        if n < 0:
+            _check(n)
+        return n
+
     def batch_step(self, toks, slots, pos, want_logits=False):
         toks = np.ascontiguousarray(toks, dtype=np.int32); slots = np.ascontiguousarray(slots, dtype=np.int32); pos = np.ascontiguousarray(pos, dtype=np.int32)
         nxt = np.empty(len(toks), dtype=np.int32)
@@ -221,8 +231,8 @@ class GgufTokenizer:
 class Engine:
     """Process-wide engine (one per GPU process)."""
 
-    def __init__(self, device=0, max_ctx=4096, max_seqs=1):
-        cfg = Config(device, max_ctx, max_seqs, 0)
+    def __init__(self, device=0, max_ctx=4096, max_seqs=1, kv_pages=0):
+        cfg = Config(device, max_ctx, max_seqs, kv_pages)
         _check(lib().b200_init(C.byref(cfg)))
 
     def load_file(self, model_id, path):
