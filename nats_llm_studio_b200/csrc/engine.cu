@@ -1167,7 +1167,7 @@ int Model::prefill_slot(int slot, const int32_t* toks, int n, int pos0) {
     if (pos0 + n > E.max_ctx) return fail(B200_ERR_INVALID, "context overflow in prefill");
     if (int rc = kv_ensure(slot, pos0 + n - 1)) return rc;
     if (int rc = ensure_prefill_buffers()) return rc;
-    if (n >= PREFILL_CHUNK / 2) maybe_bf16_cache();                    // long prompts: keep bf16 copies of the matrices when HBM has room (see maybe_bf16_cache)
+    if (n >= 256) maybe_bf16_cache();                                  // long prompts: keep bf16 copies of the matrices when HBM has room (see maybe_bf16_cache)
     for (int c0 = 0; c0 < n; c0 += PREFILL_CHUNK) {
         const int M = std::min(PREFILL_CHUNK, n - c0);
         CK(cudaMemcpyAsync(pf_toks, toks + c0, (size_t)M * 4, cudaMemcpyHostToDevice, E.stream));
