@@ -98,7 +98,7 @@ struct Model {
     int cur_pos = 0;
     long long* d_trace = nullptr;
     // prefill scratch (allocated on first use)
-    static constexpr int PREFILL_CHUNK = 1024;
+    static constexpr int PREFILL_CHUNK = 2048;
     float *pf_H = nullptr, *pf_Y = nullptr; __nv_bfloat16 *pf_X = nullptr, *pf_Q = nullptr, *pf_ACT = nullptr, *pf_W = nullptr; int* pf_toks = nullptr;
     float* bt_logits = nullptr; int* bt_next = nullptr; struct RowSampling* bt_samp = nullptr; __nv_bfloat16* b_out = nullptr; bool bf16_ready = false; int pages_per_seq = 0;
     int prefill_min = 32;                        // prompts shorter than this go through the decode kernel token by token
