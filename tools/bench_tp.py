@@ -53,7 +53,7 @@ def measure(rank, world, local, gloo, preset="llama3-70b", mix="q4_k_m", n_layer
         t_first = time.perf_counter() - t1
         cold = {"file_bytes": os.path.getsize(path), "load_s": round(t_load, 3), "stream_gbs": round(os.path.getsize(path) / t_load / 1e9, 2), "first_token_s": round(t_first, 3),
                 "ttft_from_file_s": round(t_load + t_first, 3), "hbm_bytes_resident": info["hbm_bytes"],
-                "path": "pread by up to 8 threads into a ring of pinned buffers -> cudaMemcpyAsync -> staging ring in HBM -> per-tensor repack behind the copy -> 16-token prompt, first token"}
+                "path": "pread by up to 12 threads into a ring of pinned buffers -> cudaMemcpyAsync -> staging ring in HBM -> per-tensor repack behind the copy -> 16-token prompt, first token"}
     out = {"workload": f"{preset} {mix}" + (f" L{n_layer}" if n_layer else "") + f", tensor-parallel x{world}, ctx {ctx}", "n_gpus": world,
            "file_bytes": os.path.getsize(path), "file_s": round(t_file, 1), "load_s": round(t_load, 1), "shard_weight_bytes": info["weight_bytes"], "cold_start": cold, "results": {}}
     if peak is None:
