@@ -625,7 +625,7 @@ int Model::run_steps(int n_steps, const int32_t* forced, int n_forced, bool rese
     Engine& E = engine();
     if (!committed) return fail(B200_ERR_STATE, "model not committed");
     if (n_steps <= 0) return B200_OK;
-    if (reset) { int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0; }
+    if (reset) { int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0; kv_release(sync_slot); }      // a new sequence: the previous one's pages go back to the pool
     if (cur_pos + n_steps > E.max_ctx) return fail(B200_ERR_INVALID, "context overflow: " + std::to_string(cur_pos + n_steps) + " > max_ctx " + std::to_string(E.max_ctx));
     if (int rc = kv_ensure(sync_slot, cur_pos + n_steps - 1)) return rc;
     if (n_forced > 0) CK(cudaMemcpyAsync(d_forced, forced, (size_t)n_forced * 4, cudaMemcpyHostToDevice, E.stream));
@@ -665,7 +665,7 @@ int Model::generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_s
         // all but the last token go through the tensor-core prefill (KV pages only), the last one through the decode
         // kernel, which produces the first generated token.
         if (prefill_min > 0 && n_prompt - 1 >= prefill_min) {
-            { int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0; }
+            { int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0; kv_release(sync_slot); }
             if ((rc = prefill(prompt, n_prompt - 1))) goto done;
             if ((rc = run_steps(1, prompt + n_prompt - 1, 1, false, nullptr))) goto done;
             CK(cudaMemcpyAsync(d_out_tokens + n_prompt - 1, d_out_tokens, 4, cudaMemcpyDeviceToDevice, E.stream));
@@ -687,7 +687,7 @@ int Model::generate(const int32_t* prompt, int n_prompt, int n_gen, const b200_s
     } else {
         // sampled: one step per launch with logits, then the sampler kernel picks the token
         if (prefill_min > 0 && n_prompt - 1 >= prefill_min) {
-            { int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0; }
+            { int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0; kv_release(sync_slot); }
             if ((rc = prefill(prompt, n_prompt - 1))) goto done;
             if ((rc = run_steps(1, prompt + n_prompt - 1, 1, false, nullptr))) goto done;
         } else if ((rc = run_steps(n_prompt, prompt, n_prompt, true, nullptr))) goto done;
@@ -725,7 +725,7 @@ int Model::eval(const int32_t* toks, int n, float* logits_all, float* logits_las
     const size_t col0 = tp ? (size_t)E.tp_rank * n_vocab_l : 0;    // the slice lands in its columns of the caller's [n][n_vocab] array
     int rc;
     if (!logits_all && prefill_min > 0 && n - 1 >= prefill_min) {      // only the last position's logits: batched ingestion of the rest
-        int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0;
+        int z = 0; CK(cudaMemcpyAsync(d_state, &z, 4, cudaMemcpyHostToDevice, E.stream)); cur_pos = 0; kv_release(sync_slot);
         rc = prefill(toks, n - 1);
         if (!rc) rc = run_steps(1, toks + n - 1, 1, false, nullptr);
     } else rc = run_steps(n, toks, n, true, d_all);
