@@ -1396,6 +1396,12 @@ int kernel_qgemm(int type, const void* raw, int64_t N, int K, const float* x, in
             cudaEventRecord(e0, E.stream);
             for (int i = 0; i < iters && !rc; i++) rc = qgemm(E, &qm, 1, d_x, B, K, (int)N, 0, 1.f, whole, &sp);
             cudaEventRecord(e1, E.stream); cudaEventSynchronize(e1);
+#ifdef B200_QG_TRACE
+            if (const char* tp_ = getenv("B200_QG_TRACE")) {          // the last launch's stamps of CTA 0
+                std::vector<long long> tr(6 * 64 * 8); cudaMemcpyFromSymbol(tr.data(), g_qgt, tr.size() * 8);
+                if (FILE* f = fopen(tp_, "wb")) { fwrite(tr.data(), 8, tr.size(), f); fclose(f); }
+            }
+#endif
             float ms = 0.f; cudaEventElapsedTime(&ms, e0, e1); if (ms_out) *ms_out = ms / iters;
             cudaEventDestroy(e0); cudaEventDestroy(e1);
         }

@@ -88,6 +88,13 @@ __global__ void tile_repack_kernel(const uint8_t* __restrict__ w, int type, int6
     }
 }
 
+// Per-role cycle trace of CTA 0 (build variant -DB200_QG_TRACE; tools/qgemm_trace.py): g_qgt[role][unit][stamp], clock64
+#ifdef B200_QG_TRACE
+__device__ long long g_qgt[6 * 64 * 8];
+#define QGT(role, it, k) do { if (blockIdx.x == 0 && (it) < 64) g_qgt[((role) * 64 + (it)) * 8 + (k)] = clock64(); } while (0)
+#else
+#define QGT(role, it, k) do {} while (0)
+#endif
 struct QSeg { const uint8_t* tl; float* C; int type, n_tiles, n_rows, step0, tile0; };
 struct QGemmParams {
     QSeg seg[3]; int n_seg, ks /*K-steps per tile*/, total_steps, n_tiles, B, ldc, mode, n_raw; float scale; float* ws; uint32_t slot_bytes;
@@ -277,6 +284,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 const QSeg& sg = P.seg[qg_seg_of_step(P, s)];
                 const int rs = it % P.n_raw; const uint32_t ph = (it / P.n_raw) & 1, bytes = qg_blob_bytes(sg.type);
                 mbar_wait(&S.raw_empty[rs], ph ^ 1);
+                QGT(0, it, 0);
                 if (P.debug & 8) { mbar_arrive(&S.raw_full[rs]); continue; }
                 mbar_expect_tx(&S.raw_full[rs], bytes);
                 bulk_g2s(S.raw + (size_t)rs * P.slot_bytes, sg.tl + (size_t)(s - sg.step0) * bytes, bytes, &S.raw_full[rs]);
@@ -290,6 +298,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 const QSeg& sg = P.seg[qg_seg_of_step(P, s)];
                 const int kstep = (s - sg.step0) % P.ks, xs = it % QG_X_STEPS;
                 mbar_wait(&S.a_empty[xs], ((it / QG_X_STEPS) & 1) ^ 1);       // freed together with the A slot of the same K-step
+                QGT(1, it, 0);
                 if (P.debug & 4) { mbar_arrive(&S.x_full[xs]); continue; }
                 mbar_expect_tx(&S.x_full[xs], QG_X_BYTES);
 #pragma unroll
@@ -308,8 +317,11 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 tcgen05_fence_after();
                 for (int i = 0; i < n_st; i++, it++) {
                     const int as = it % QG_A_STEPS, xs = it % QG_X_STEPS;
+                    QGT(2, it, 0);
                     mbar_wait(&S.a_full[as], (it / QG_A_STEPS) & 1);
+                    QGT(2, it, 1);
                     mbar_wait(&S.x_full[xs], (it / QG_X_STEPS) & 1);
+                    QGT(2, it, 2);
                     tcgen05_fence_after();
                     if (!(P.debug & 2)) {
 #pragma unroll
@@ -321,6 +333,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                         }
                     }
                     tcgen05_commit(&S.a_empty[as]);                 // one commit per K-step frees both the A slot and the X slot (same ring depth)
+                    QGT(2, it, 3);
                 }
                 tcgen05_commit(&S.acc_full[buf]);
                 s += n_st; piece++;
@@ -337,7 +350,10 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
             const int rs = it % P.n_raw, as = it % QG_A_STEPS;
             const uint32_t raw = smem_u32(S.raw) + rs * P.slot_bytes;
             const uint32_t a0 = lane_base + as * 128;           // 4 k-blocks x 32 columns per K-step
+            const int trole = (idx & 7) == 0 && lane == 0 ? 3 + grp : -1;
+            if (trole >= 0) QGT(trole, it, 0);
             mbar_wait(&S.raw_full[rs], (it / P.n_raw) & 1);
+            if (trole >= 0) QGT(trole, it, 1);
 #pragma unroll
             for (int pp = 0; pp < 2; pp++) {
                 const int p = 2 * half + pp;
@@ -350,7 +366,7 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 else if (type == T_Q6_K) dq_q6k(raw, row, p >> 1, p & 1, o);
                 else if (type == T_Q4_K) dq_k45<false>(raw, row, p, o);
                 else dq_k45<true>(raw, row, p, o);
-                if (pp == 0) { mbar_wait(&S.a_empty[as], ((it / QG_A_STEPS) & 1) ^ 1); tcgen05_fence_after(); }
+                if (pp == 0) { if (trole >= 0) QGT(trole, it, 2); mbar_wait(&S.a_empty[as], ((it / QG_A_STEPS) & 1) ^ 1); tcgen05_fence_after(); if (trole >= 0) QGT(trole, it, 3); }
                 else { __syncwarp(); if (lane == 0) mbar_arrive(&S.raw_empty[rs]); }     // every lane has its operands in registers
                 if (type == T_Q6_K) {
                     const int n = p >> 1, h = p & 1;
@@ -358,10 +374,12 @@ qgemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                     tmem_st_x8(a0 + (2 * n + 1) * 32 + 8 * h, o + 16); tmem_st_x8(a0 + (2 * n + 1) * 32 + 16 + 8 * h, o + 24);
                 } else if (!(P.debug & 64)) tmem_st_x32(a0 + p * 32, o);
             }
+            if (trole >= 0) QGT(trole, it, 4);
             tmem_st_wait();
             tcgen05_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&S.a_full[as]);
+            if (trole >= 0) QGT(trole, it, 5);
         }
     } else {                                           // ===== epilogue warps: TMEM -> C (whole tile) or fp32 partial + last-arriver reduction =====
         const int q = warp & 3;                        // TMEM lane quadrant this warp may read
