@@ -119,3 +119,27 @@ def test_tensor_core_prompt_attention(engine, golden_dir, tmp_path, preset, n):
         assert pp_x.max() <= 6e-2, (int(pp_x.argmax()), float(pp_x.max()))
         assert pp_x[:4].max() <= 2e-2, pp_x[:4]                           # the first rows see 1..4 positions: any mask slip is O(1) here
     m.close()
+
+
+def test_swiglu_in_the_gemm_epilogue_is_bit_exact(tmp_path):
+    """The gate/up product of a prompt chunk applies SwiGLU in its epilogue (gemm_bf16_persistent, mode 2) instead of writing
+    fp32 [M x 2F] and running swiglu_rows_kernel: same arithmetic, so the logits must be IDENTICAL.  The switch is read once
+    per process, hence two child processes."""
+    import subprocess, sys
+    import make_gguf
+    path = str(tmp_path / "small.gguf"); make_gguf.write_model(path, make_gguf.spec_from_preset("small-llama"))
+    script = (
+        "import sys, numpy as np, nats_llm_studio_b200 as b200\n"
+        "e = b200.Engine(max_ctx=1024); m = e.load_file('sw', sys.argv[1]); m.set_prefill_min(8)\n"
+        "p = np.random.default_rng(9).integers(0, m.n_vocab, 600).astype(np.int32)\n"
+        "np.save(sys.argv[2], m.eval(p, all_logits=False))\n")
+    outs = []
+    for fused in (True, False):
+        env = dict(os.environ); env["PYTHONPATH"] = os.path.dirname(os.path.dirname(os.path.abspath(__file__))) + os.pathsep + env.get("PYTHONPATH", "")
+        if not fused:
+            env["B200_NO_SWIGLU_FUSE"] = "1"
+        out = str(tmp_path / f"lg{int(fused)}.npy")
+        r = subprocess.run([sys.executable, "-c", script, path, out], env=env, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(np.load(out))
+    assert np.isfinite(outs[0]).all() and np.array_equal(outs[0], outs[1])
