@@ -27,10 +27,12 @@ std::string tokenizer_from_gguf(const GgufMeta& meta, int n_vocab, Tokenizer& ou
     std::vector<std::string> tokens, merges; std::vector<int> types;
     if (auto v = meta.find("tokenizer.ggml.tokens")) tokens = v->arr_str;
     if (auto v = meta.find("tokenizer.ggml.merges")) merges = v->arr_str;
+    std::vector<float> scores;
+    if (auto v = meta.find("tokenizer.ggml.scores")) { scores.assign(v->arr_num.size(), 0.f); for (size_t i = 0; i < v->arr_num.size(); i++) scores[i] = (float)v->arr_num[i]; }
     if (auto v = meta.find("tokenizer.ggml.token_type")) { types.assign(v->arr_num.size(), 0); for (size_t i = 0; i < v->arr_num.size(); i++) types[i] = (int)v->arr_num[i]; }
     out.build(tokens, types, merges, meta.str("tokenizer.ggml.model"), meta.str("tokenizer.ggml.pre"), meta.str("tokenizer.chat_template"),
               (int)meta.num("tokenizer.ggml.bos_token_id", -1), (int)meta.num("tokenizer.ggml.eos_token_id", -1), meta.num("tokenizer.ggml.add_bos_token", 1) != 0,
-              n_vocab > 0 ? n_vocab : (int)tokens.size());
+              n_vocab > 0 ? n_vocab : (int)tokens.size(), scores, meta.num("tokenizer.ggml.add_space_prefix", 1) != 0);
     return "";
 }
 void Model::build_tokenizer() { tokenizer_from_gguf(meta, n_vocab, tok); }
@@ -223,6 +225,19 @@ static std::string render_messages(const Tokenizer& tk, const Json& messages, st
     if (messages.kind != Json::Arr) return "'messages' must be an array";
     auto sp = [&](const std::string& s) { const int id = tk.special_id(s); if (id >= 0) toks.push_back(id); else { auto t = tk.tokenize(s, false); toks.insert(toks.end(), t.begin(), t.end()); } };
     auto text = [&](const std::string& s) { auto t = tk.tokenize(s, false); toks.insert(toks.end(), t.begin(), t.end()); };
+    if (tk.tpl == Tokenizer::TPL_LLAMA2) {
+        // Llama-2 / Mistral layout: <s>[INST] <<SYS>>\n{system}\n<</SYS>>\n\n{user} [/INST] {assistant} </s><s>[INST] ...   (BOS per user turn)
+        std::string sys;
+        for (const Json& msg : messages.arr) {
+            if (msg.kind != Json::Obj) return "each message must be an object";
+            const Json* role = msg.get("role"); const Json* content = msg.get("content");
+            if (!role || role->kind != Json::Str || !content || content->kind != Json::Str) return "each message needs string 'role' and 'content'";
+            if (role->s == "system") sys = "<<SYS>>\n" + content->s + "\n<</SYS>>\n\n";
+            else if (role->s == "assistant") { text(content->s); if (tk.eos >= 0) toks.push_back(tk.eos); }
+            else { if (tk.bos >= 0) toks.push_back(tk.bos); text("[INST] " + sys + content->s + " [/INST]"); sys.clear(); }
+        }
+        return "";
+    }
     if (tk.tpl == Tokenizer::TPL_LLAMA3) sp("<|begin_of_text|>");
     else if (tk.bos >= 0 && tk.add_bos && tk.tpl == Tokenizer::TPL_MINIMAL) toks.push_back(tk.bos);
     for (const Json& msg : messages.arr) {

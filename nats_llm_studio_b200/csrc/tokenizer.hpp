@@ -6,13 +6,17 @@
 //     GPT-2's).  The split is hand-coded (no regex engine, no ICU): Unicode letters are "every code point >= 0x80 that is
 //     not in a short list of punctuation/space ranges", digits are ASCII — exact on ASCII, approximate beyond.
 //     Checked against Hugging Face `tokenizers` on a trained vocabulary (tests/golden/make_tokenizer_golden.py).
+//   * tokenizer.ggml.model == "llama" with scores: SentencePiece BPE as llama.cpp applies it to Llama-2 / Mistral style
+//     vocabularies (spaces -> U+2581 with the dummy prefix, score-ordered bigram merges, <0xXX> byte fallback).  Checked
+//     against `sentencepiece` on a trained model (tests/golden/make_spm_golden.py).
 //   * anything else (the synthetic byte-level vocabulary of tools/make_gguf.py): one token per byte.
 // Chat templates: tokenizer.chat_template is Jinja; it is not executed — the template's family is recognised from its
-// marker tokens (Llama-3 headers, granite roles, ChatML) and rendered natively; unknown templates fall back to the
+// marker tokens (Llama-3 headers, granite roles, ChatML) or its [INST] markers (Llama-2) and rendered natively; unknown templates fall back to the
 // minimal <|role|> form of the synthetic vocabulary.
 #pragma once
 #include <algorithm>
 #include <cstdint>
+#include <queue>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -20,8 +24,8 @@
 namespace b200 {
 
 struct Tokenizer {
-    enum Kind { BYTES, BPE } kind = BYTES;
-    enum Template { TPL_MINIMAL, TPL_LLAMA3, TPL_GRANITE, TPL_CHATML } tpl = TPL_MINIMAL;
+    enum Kind { BYTES, BPE, SPM } kind = BYTES;
+    enum Template { TPL_MINIMAL, TPL_LLAMA3, TPL_GRANITE, TPL_CHATML, TPL_LLAMA2 } tpl = TPL_MINIMAL;
     bool llama3_split = false;
     std::vector<std::string> piece;                        // token id -> text it stands for (detokenisation)
     std::unordered_map<std::string, int> special;          // control / user-defined tokens, matched verbatim when parse_special
@@ -31,7 +35,8 @@ struct Tokenizer {
     std::unordered_map<std::string, int> rank;             // BPE: "left right" -> merge priority
     std::string b2u[256];                                  // GPT-2 byte -> unicode character (UTF-8)
     std::unordered_map<uint32_t, int> u2b;
-    int n_vocab = 0, bos = -1, eos = -1; bool add_bos = true;
+    std::vector<float> score;                              // SPM: piece score (merge priority)
+    int n_vocab = 0, bos = -1, eos = -1; bool add_bos = true, add_space_prefix = true;
 
     // ---------------------------------------------------------------- construction
     static void utf8_put(uint32_t c, std::string& s) {
@@ -50,8 +55,9 @@ struct Tokenizer {
         i += 1; return c;
     }
     void build(const std::vector<std::string>& tokens, const std::vector<int>& types, const std::vector<std::string>& merges, const std::string& model,
-               const std::string& pre, const std::string& chat_template, int bos_, int eos_, bool add_bos_, int n_vocab_) {
-        n_vocab = n_vocab_; bos = bos_; eos = eos_; add_bos = add_bos_;
+               const std::string& pre, const std::string& chat_template, int bos_, int eos_, bool add_bos_, int n_vocab_,
+               const std::vector<float>& scores = {}, bool add_space_prefix_ = true) {
+        n_vocab = n_vocab_; bos = bos_; eos = eos_; add_bos = add_bos_; add_space_prefix = add_space_prefix_; score = scores;
         for (int i = 0; i < 256; i++) byte_tok[i] = -1;
         {   // GPT-2's reversible byte <-> printable-character map
             int n = 0;
@@ -61,12 +67,13 @@ struct Tokenizer {
                 b2u[b].clear(); utf8_put(cp, b2u[b]); u2b[cp] = b;
             }
         }
-        kind = (model == "gpt2" && !merges.empty()) ? BPE : BYTES;
+        kind = (model == "gpt2" && !merges.empty()) ? BPE : (model == "llama" && scores.size() == tokens.size() && !tokens.empty()) ? SPM : BYTES;
         llama3_split = pre == "llama-bpe" || pre == "llama3" || pre == "llama-v3";
         piece.assign(tokens.size(), ""); special.clear(); vocab.clear(); rank.clear();
         for (size_t i = 0; i < tokens.size(); i++) {
             const std::string& s = tokens[i]; const int ty = i < types.size() ? types[i] : 1;
             if (ty == 3 || ty == 4) { special[s] = (int)i; piece[i] = ty == 4 ? s : ""; if (kind == BPE) vocab[s] = (int)i; continue; }   // CONTROL prints nothing
+            if (kind == SPM && ty == 2) { piece[i] = ""; continue; }                                       // UNKNOWN: never produced (byte fallback), prints nothing
             if (kind == BPE) {
                 vocab[s] = (int)i;
                 std::string raw; size_t k = 0;
@@ -74,13 +81,14 @@ struct Tokenizer {
                 piece[i] = raw;
             } else if (ty == 6 && s.size() == 6 && s.compare(0, 3, "<0x") == 0 && s[5] == '>') {      // BYTE
                 const int b = (int)strtol(s.substr(3, 2).c_str(), nullptr, 16); byte_tok[b & 255] = (int)i; piece[i] = std::string(1, (char)b);
-            } else { std::string p = s; size_t k; while ((k = p.find("\xE2\x96\x81")) != std::string::npos) p.replace(k, 3, " "); piece[i] = p; }
+            } else { if (kind == SPM) vocab[s] = (int)i; std::string p = s; size_t k; while ((k = p.find("\xE2\x96\x81")) != std::string::npos) p.replace(k, 3, " "); piece[i] = p; }
         }
         for (size_t i = 0; i < merges.size(); i++) rank[merges[i]] = (int)i;
         special_sorted.clear(); for (auto& kv : special) if (!kv.first.empty()) special_sorted.push_back(kv.first);
         std::sort(special_sorted.begin(), special_sorted.end(), [](const std::string& a, const std::string& b) { return a.size() != b.size() ? a.size() > b.size() : a < b; });
         auto has = [&](const char* t) { return chat_template.find(t) != std::string::npos && special.count(t); };
-        tpl = has("<|start_header_id|>") ? TPL_LLAMA3 : has("<|start_of_role|>") ? TPL_GRANITE : has("<|im_start|>") ? TPL_CHATML : TPL_MINIMAL;
+        tpl = has("<|start_header_id|>") ? TPL_LLAMA3 : has("<|start_of_role|>") ? TPL_GRANITE : has("<|im_start|>") ? TPL_CHATML
+            : chat_template.find("[INST]") != std::string::npos ? TPL_LLAMA2 : TPL_MINIMAL;
     }
 
     // ---------------------------------------------------------------- character classes (see the header comment)
@@ -157,10 +165,48 @@ struct Tokenizer {
         }
     }
 
+    // SentencePiece BPE as llama.cpp's "llama" vocabulary applies it (llm_tokenizer_spm): spaces become U+2581 (one is prepended
+    // to a fragment that starts the text or follows a special token when add_space_prefix), the text is cut into UTF-8
+    // characters, and the adjacent pair whose concatenation is a piece with the highest score is merged until none is left
+    // (ties: the leftmost); what is still not a piece falls back to <0xXX> byte tokens.
+    void spm(const std::string& frag, bool prefix, std::vector<int32_t>& out) const {
+        std::string t;
+        if (prefix) t += "\xE2\x96\x81";
+        for (char c : frag) { if (c == ' ') t += "\xE2\x96\x81"; else t.push_back(c); }
+        struct Sym { size_t off, len; int prev, next; };
+        std::vector<Sym> sym;
+        for (size_t i = 0; i < t.size();) { size_t i0 = i; utf8_get(t, i); sym.push_back({i0, i - i0, (int)sym.size() - 1, -1}); if (sym.size() > 1) sym[sym.size() - 2].next = (int)sym.size() - 1; }
+        struct Bi { float sc; int left, right; size_t len; };
+        auto worse = [](const Bi& a, const Bi& b) { return a.sc < b.sc || (a.sc == b.sc && a.left > b.left); };
+        std::priority_queue<Bi, std::vector<Bi>, decltype(worse)> pq(worse);
+        auto try_add = [&](int l, int r) {
+            if (l < 0 || r < 0) return;
+            auto it = vocab.find(t.substr(sym[l].off, sym[l].len + sym[r].len));
+            if (it != vocab.end() && (size_t)it->second < score.size()) pq.push({score[it->second], l, r, sym[l].len + sym[r].len});
+        };
+        for (int i = 1; i < (int)sym.size(); i++) try_add(i - 1, i);
+        while (!pq.empty()) {
+            const Bi b = pq.top(); pq.pop();
+            Sym& L = sym[b.left]; Sym& R = sym[b.right];
+            if (L.len == 0 || R.len == 0 || L.len + R.len != b.len || L.next != b.right) continue;       // one side was merged away since
+            L.len += R.len; R.len = 0; L.next = R.next; if (R.next >= 0) sym[R.next].prev = b.left;
+            try_add(L.prev, b.left); try_add(b.left, L.next);
+        }
+        for (int i = sym.empty() ? -1 : 0; i >= 0; i = sym[i].next) {
+            if (sym[i].len == 0) continue;
+            const std::string p = t.substr(sym[i].off, sym[i].len);
+            auto it = vocab.find(p);
+            if (it != vocab.end()) { out.push_back(it->second); continue; }
+            for (unsigned char c : p) { const int bt = byte_tok[c]; if (bt >= 0) out.push_back(bt); }
+        }
+    }
+
     std::vector<int32_t> tokenize(const std::string& text, bool parse_special) const {
         std::vector<int32_t> out;
+        bool after_special = true;                                              // SPM: the text start counts as "after a special token" (BOS)
         auto plain = [&](const std::string& seg) {
             if (seg.empty()) return;
+            if (kind == SPM) { spm(seg, add_space_prefix && after_special, out); after_special = false; return; }
             if (kind == BPE) { std::vector<std::pair<size_t, size_t>> parts; pre_split(seg, parts); for (auto& p : parts) bpe(seg.substr(p.first, p.second - p.first), out); }
             else for (unsigned char c : seg) { const int t = byte_tok[c]; out.push_back(t >= 0 ? t : (int)c % std::max(1, n_vocab)); }
         };
@@ -169,7 +215,7 @@ struct Tokenizer {
         while (i < text.size()) {
             bool hit = false;
             if (text[i] == '<' || kind == BPE) for (const std::string& sp : special_sorted)
-                if (text.compare(i, sp.size(), sp) == 0) { plain(text.substr(start, i - start)); out.push_back(special.at(sp)); i += sp.size(); start = i; hit = true; break; }
+                if (text.compare(i, sp.size(), sp) == 0) { plain(text.substr(start, i - start)); out.push_back(special.at(sp)); after_special = true; i += sp.size(); start = i; hit = true; break; }
             if (!hit) i++;
         }
         plain(text.substr(start));
@@ -178,12 +224,13 @@ struct Tokenizer {
     std::string detokenize(const int32_t* toks, int n) const {
         std::string s;
         for (int i = 0; i < n; i++) if (toks[i] >= 0 && (size_t)toks[i] < piece.size()) s += piece[toks[i]];
+        if (kind == SPM && add_space_prefix && !s.empty() && s[0] == ' ') s.erase(0, 1);      // the dummy prefix of the first fragment
         return s;
     }
     int special_id(const std::string& s) const { auto it = special.find(s); return it == special.end() ? -1 : it->second; }
     // token that ends an assistant turn in this template (-1: none beyond EOS)
     int stop_token() const {
-        switch (tpl) { case TPL_LLAMA3: return special_id("<|eot_id|>"); case TPL_GRANITE: return special_id("<|end_of_text|>"); case TPL_CHATML: return special_id("<|im_end|>"); default: return special_id("<|end|>"); }
+        switch (tpl) { case TPL_LLAMA2: return eos; case TPL_LLAMA3: return special_id("<|eot_id|>"); case TPL_GRANITE: return special_id("<|end_of_text|>"); case TPL_CHATML: return special_id("<|im_end|>"); default: return special_id("<|end|>"); }
     }
 };
 

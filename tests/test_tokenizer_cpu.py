@@ -46,3 +46,18 @@ def test_synthetic_byte_vocabulary_still_works(golden_dir):
     assert tk.detokenize(ids[:3]) == b"hi " and len(ids) == 4
     chat = tk.render_chat([{"role": "user", "content": "yo"}]).tolist()
     assert len(chat) == 1 + 1 + 2 + 1 + 1                   # bos, <|user|>, y, o, <|end|>, <|assistant|>
+
+
+def test_sentencepiece_vocabulary_matches_sentencepiece(golden_dir):
+    """tokenizer.ggml.model = "llama" (Llama-2 / Mistral style GGUFs): score-ordered bigram merges, U+2581 spaces with the dummy
+    prefix, byte fallback — against `sentencepiece` itself (tests/golden/make_spm_golden.py), and the [INST] chat layout."""
+    g = json.load(open(os.path.join(golden_dir, "spm_golden.json")))
+    tk = b200.GgufTokenizer(open(os.path.join(golden_dir, g["gguf"]), "rb").read())
+    for text, ids in g["encode"].items():
+        got = tk.tokenize(text).tolist()
+        assert got == ids, (text, got, ids)
+        assert tk.detokenize(ids).decode("utf-8") == g["decode"][text], text
+    assert tk.tokenize("<s>", parse_special=True).tolist() == [g["bos"]]
+    assert g["bos"] not in tk.tokenize("<s>", parse_special=False).tolist()                        # user text never becomes a control token
+    for chat in g["chats"]:
+        assert tk.render_chat(chat["messages"]).tolist() == chat["ids"], chat["messages"]
