@@ -3,8 +3,8 @@
 // the GGUF's own tokenizer is implemented:
 //   * tokenizer.ggml.model == "gpt2": byte-level BPE (tokens + merges from the GGUF; Llama-3 and granite-3 use it) with
 //     the pre-tokeniser split named by tokenizer.ggml.pre ("llama-bpe"/"llama3": the Llama-3 pattern; anything else:
-//     GPT-2's).  The split is hand-coded (no regex engine, no ICU): Unicode letters are "every code point >= 0x80 that is
-//     not in a short list of punctuation/space ranges", digits are ASCII — exact on ASCII, approximate beyond.
+//     GPT-2's).  The split is hand-coded (no regex engine, no ICU); \p{L} and \p{N} come from generated range tables
+//     (unicode_tables.hpp, tools/make_unicode_tables.py), \s is the Unicode White_Space set.
 //     Checked against Hugging Face `tokenizers` on a trained vocabulary (tests/golden/make_tokenizer_golden.py).
 //   * tokenizer.ggml.model == "llama" with scores: SentencePiece BPE as llama.cpp applies it to Llama-2 / Mistral style
 //     vocabularies (spaces -> U+2581 with the dummy prefix, score-ordered bigram merges, <0xXX> byte fallback).  Checked
@@ -20,6 +20,8 @@
 #include <string>
 #include <unordered_map>
 #include <vector>
+
+#include "unicode_tables.hpp"
 
 namespace b200 {
 
@@ -93,14 +95,10 @@ struct Tokenizer {
 
     // ---------------------------------------------------------------- character classes (see the header comment)
     static bool is_space(uint32_t c) { return c == ' ' || (c >= 9 && c <= 13) || c == 0x85 || c == 0xA0 || c == 0x1680 || (c >= 0x2000 && c <= 0x200A) || c == 0x2028 || c == 0x2029 || c == 0x202F || c == 0x205F || c == 0x3000; }
-    static bool is_digit(uint32_t c) { return c >= '0' && c <= '9'; }
-    static bool is_letter(uint32_t c) {
+    static bool is_digit(uint32_t c) { return c < 0x80 ? (c >= '0' && c <= '9') : uni_in(UNI_NUMBER, (int)(sizeof(UNI_NUMBER) / sizeof(UNI_NUMBER[0])), c); }      // \p{N}
+    static bool is_letter(uint32_t c) {                                                                                                                 // \p{L}
         if (c < 0x80) return (c >= 'a' && c <= 'z') || (c >= 'A' && c <= 'Z');
-        if (is_space(c)) return false;
-        if ((c >= 0xA1 && c <= 0xA9) || (c >= 0xAB && c <= 0xB4) || (c >= 0xB6 && c <= 0xB9) || (c >= 0xBB && c <= 0xBF) || c == 0xD7 || c == 0xF7) return false;   // Latin-1 signs
-        if ((c >= 0x2010 && c <= 0x206F) || (c >= 0x20A0 && c <= 0x20CF) || (c >= 0x2190 && c <= 0x2BFF) || (c >= 0x3001 && c <= 0x303F) || (c >= 0xFE10 && c <= 0xFE6F) ||
-            (c >= 0xFF01 && c <= 0xFF0F) || (c >= 0xFF1A && c <= 0xFF20) || (c >= 0x1F000 && c <= 0x1FAFF)) return false;                                            // punctuation, arrows, symbols, emoji
-        return true;
+        return uni_in(UNI_LETTER, (int)(sizeof(UNI_LETTER) / sizeof(UNI_LETTER[0])), c);
     }
 
     // Splits text into pre-tokens (byte ranges) the way the model's pattern does.  Llama-3:

@@ -23,7 +23,9 @@ CORPUS = ["The quick brown fox jumps over the lazy dog. ", "Hello, world! This i
           "email@example.com http://example.org/path?query=1&b=2 #hashtag @mention $100 50% (parens) [brackets] {braces}\n"] * 4
 TEXTS = ["Hello world", "Hello, world! It's a test.", "  two spaces   three", "line1\nline2\n\n\nline5   \n  indented", "I'M SHOUTING, DON'T YOU'LL WE'VE",
          "12345678 9 10 007", "x=1;y=2;//c", "tabs\tand\r\nCRLF", "naïve café über", "日本語 text 中文!", "trailing space ", " leading", "a", "", "!!!???...", "end.\n",
-         "snake_case CamelCase kebab-case 3.14", "The year 2024 was… fine — really"]
+         "snake_case CamelCase kebab-case 3.14", "The year 2024 was… fine — really",
+         # scripts, numerals and symbols beyond ASCII: \\p{L} / \\p{N} classes of the pre-tokeniser
+         "Привет, мир! Ελληνικά עברית العربية हिन्दी ไทย", "x² + y³ = ½ ٣٤٥ ३४५ Ⅻ ① 12345", "price: 100€ ±5% → ok ✓ 😀👍 done", "a\u0301 e\u0308 combining marks", "ｆｕｌｌwidth １２３ 𝒜𝓑 𝟙𝟚𝟛"]
 CHATS = [[{"role": "user", "content": "Hi there"}], [{"role": "system", "content": "You are terse."}, {"role": "user", "content": "Say hello from NATS client in Go."}],
          [{"role": "user", "content": "a"}, {"role": "assistant", "content": "b\n"}, {"role": "user", "content": "<|eot_id|> is text here"}]]
 TEMPLATE = ("{% set loop_messages = messages %}{% for message in loop_messages %}{% set content = '<|start_header_id|>' + message['role'] + '<|end_header_id|>\n\n'+ message['content'] + '<|eot_id|>' %}"
