@@ -316,15 +316,33 @@ static std::string on_chat_model(const std::string& payload) {          // OnCha
     double wall_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     bool stopped = reason == B200_FINISH_STOP;
     int n_text = stopped ? n_out - 1 : n_out;
+    // OpenAI `stop`: a string or an array of strings; the text ends before the first occurrence of any of them (the stop string
+    // itself is not returned) and finish_reason is "stop".  Matched on the detokenised text, so a stop string may span tokens.
+    std::vector<std::string> stops;
+    if (const Json* st = doc.get("stop")) {
+        if (st->kind == Json::Str && !st->s.empty()) stops.push_back(st->s);
+        else if (st->kind == Json::Arr) for (const Json& e : st->arr) if (e.kind == Json::Str && !e.s.empty()) stops.push_back(e.s);
+    }
+    std::string content; bool stop_string = false; int n_used = n_out;
+    if (!stops.empty()) {
+        for (int i = 0; i < n_text && !stop_string; i++) {
+            const std::string acc = m->detokenize(out.data(), i + 1);
+            size_t cut = std::string::npos;
+            for (const std::string& sx : stops) cut = std::min(cut, acc.find(sx));
+            if (cut != std::string::npos) { content = acc.substr(0, cut); stop_string = true; n_used = i + 1; }
+        }
+    }
+    if (!stop_string) content = m->detokenize(out.data(), n_text);
+    else stopped = true;
     static std::atomic<uint64_t> counter{0};
     char idbuf[64]; snprintf(idbuf, sizeof idbuf, "chatcmpl-%012llx", (unsigned long long)(++counter));
-    Json message = Json::object(); message.set("role", Json::string("assistant")).set("content", Json::string(m->detokenize(out.data(), n_text)));
+    Json message = Json::object(); message.set("role", Json::string("assistant")).set("content", Json::string(content));
     Json choice = Json::object(); choice.set("index", Json::integer(0)).set("logprobs", Json::null()).set("finish_reason", Json::string(stopped ? "stop" : "length")).set("message", message);
     Json choices = Json::array(); choices.push(choice);
-    Json usage = Json::object(); usage.set("prompt_tokens", Json::integer((long long)toks.size())).set("completion_tokens", Json::integer(n_out)).set("total_tokens", Json::integer((long long)toks.size() + n_out));
+    Json usage = Json::object(); usage.set("prompt_tokens", Json::integer((long long)toks.size())).set("completion_tokens", Json::integer(n_used)).set("total_tokens", Json::integer((long long)toks.size() + n_used));
     Json stats = Json::object();
     stats.set("tokens_per_second", Json::number(n_out > 1 && dec > 0 ? (n_out - 1) / (dec * 1e-3) : 0.0)).set("time_to_first_token", Json::number(ttft * 1e-3))
-        .set("generation_time", Json::number(wall_s)).set("stop_reason", Json::string(stopped ? "eosFound" : "maxPredictedTokensReached"));
+        .set("generation_time", Json::number(wall_s)).set("stop_reason", Json::string(stop_string ? "stopStringFound" : stopped ? "eosFound" : "maxPredictedTokensReached"));
     Json info = Json::object(); info.set("arch", Json::string(m->arch)).set("quant", Json::string(quant_name((int)m->meta.num("general.file_type", -1)))).set("format", Json::string("gguf")).set("context_length", Json::integer(engine().max_ctx));
     Json fmts = Json::array(); fmts.push(Json::string("gguf"));
     Json runtime = Json::object(); runtime.set("name", Json::string("b200-gguf-engine")).set("version", Json::string("0.1.0")).set("supported_formats", fmts);

@@ -162,6 +162,18 @@ def test_subject_handlers_end_to_end(engine, golden_dir):
     # greedy chat is reproducible and equals generate() on the rendered prompt
     rep2 = json.loads(engine.handle("lmstudio.chat_model", json.dumps(req)))
     assert rep2["data"]["response"]["choices"][0]["message"]["content"] == r["choices"][0]["message"]["content"]
+    # OpenAI `stop`: the text ends before the first occurrence of a stop string (which may span tokens); usage counts the
+    # tokens consumed; finish_reason becomes "stop".  The byte-level test vocabulary makes any 2-byte substring a valid stop.
+    full = json.loads(engine.handle("lmstudio.chat_model", json.dumps({**req, "ignore_eos": True})))["data"]["response"]
+    text = full["choices"][0]["message"]["content"]
+    if len(text) >= 6:
+        stop = text[3:5]; cut = text.find(stop)
+        for st in (stop, ["\x00never\x00", stop]):
+            r2 = json.loads(engine.handle("lmstudio.chat_model", json.dumps({**req, "ignore_eos": True, "stop": st})))["data"]["response"]
+            assert r2["choices"][0]["message"]["content"] == text[:cut] and r2["choices"][0]["finish_reason"] == "stop"
+            assert r2["usage"]["completion_tokens"] < full["usage"]["completion_tokens"] and r2["stats"]["stop_reason"] == "stopStringFound"
+        same = json.loads(engine.handle("lmstudio.chat_model", json.dumps({**req, "ignore_eos": True, "stop": "\x00never\x00"})))["data"]["response"]
+        assert same["choices"][0]["message"]["content"] == text and same["choices"][0]["finish_reason"] == full["choices"][0]["finish_reason"]
     unknown = json.loads(engine.handle("lmstudio.chat_model", json.dumps({"model": "ghost", "messages": []})))
     assert unknown["ok"] and unknown["data"]["http_status"] == 404          # status is forwarded, never inspected (:173-178)
     deleted = json.loads(engine.handle("lmstudio.delete_model", json.dumps({"model_id": "tiny-llama"})))
